@@ -1,0 +1,173 @@
+/* okvis_cuda - C ABI of the B200 (sm_100a) BRISK frontend hot path of OKVIS2-X.
+ *
+ * Plain C, opaque handles, int status return (0 = OK), no exceptions and no
+ * torch / OpenCV / Eigen types across the boundary. Caller owns every host
+ * buffer; the library copies in and out and keeps no caller pointer after a
+ * call returns. There is NO CPU fallback: without a CUDA device every compute
+ * entry point returns OKC_ERR_CUDA.
+ *
+ * Each entry point names the reference interface it replaces
+ * (paths relative to the OKVIS2-X tree; "brisk/" = external/brisk/).
+ */
+#ifndef OKVIS_CUDA_H_
+#define OKVIS_CUDA_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+enum {
+  OKC_OK = 0,
+  OKC_ERR_INVALID = 1,   /* bad argument; mirrors the reference's std::runtime_error cases */
+  OKC_ERR_CUDA = 2,      /* CUDA runtime error or no device */
+  OKC_ERR_CAPACITY = 3   /* an output buffer or internal scratch is too small */
+};
+
+/* Same 28-byte layout as cv::KeyPoint {Point2f pt; float size, angle, response; int octave, class_id}. */
+typedef struct okc_keypoint {
+  float x, y, size, angle, response;
+  int32_t octave, class_id;
+} okc_keypoint;
+
+#define OKC_DESC_BYTES 48 /* 384-bit BRISK2 descriptor; brisk/src/brisk-descriptor-extractor.cc:291-297 */
+#define OKC_NO_MATCH 0xffffffffffffffffull
+
+typedef struct okc_context okc_context; /* one per process and device */
+typedef struct okc_camera okc_camera;   /* one per camera: stream, scratch, maps (like the per-camera
+                                           detector/extractor pair of Frontend.cpp:2637-2656) */
+
+const char* okc_last_error_string(void);
+int okc_version(void);
+
+/* device < 0: use the current device. */
+int okc_context_create(int device, okc_context** ctx);
+int okc_context_destroy(okc_context* ctx);
+int okc_context_device(const okc_context* ctx);
+
+/* Replaces: brisk::BriskDescriptorExtractor::setCameraProperties (brisk/include/brisk/brisk-descriptor-extractor.h:112-118)
+ * as called from Frontend::detectAndDescribe (okvis_frontend/src/Frontend.cpp:214-231).
+ * rays: float[H*W*3] (CV_32FC3) or NULL; jacobians: float[H*W*6] (CV_32FC6) or NULL (both or neither).
+ * max_keypoints bounds the per-image keypoint capacity (scratch is sized once). */
+int okc_camera_create(okc_context* ctx, int width, int height, const float* rays, const float* jacobians,
+                      float virtual_focal_length, int max_keypoints, okc_camera** cam);
+int okc_camera_destroy(okc_camera* cam);
+
+typedef struct okc_detect_params {
+  double uniformity_radius;   /* FrontendParameters::detection_threshold -> ctor arg 1 (Frontend.cpp:2645-2648) */
+  uint64_t octaves;           /* only 0 is implemented (every shipped config); >0 returns OKC_ERR_INVALID */
+  double absolute_threshold;
+  uint64_t max_num_keypoints;
+} okc_detect_params;
+
+typedef struct okc_describe_params {
+  int rotation_invariant;     /* okvis: true  (Frontend.cpp:125) */
+  int scale_invariant;        /* okvis: false (Frontend.cpp:126); true returns OKC_ERR_INVALID */
+  float extraction_direction[3]; /* setExtractionDirection (Frontend.cpp:234-238); used when maps are set */
+} okc_describe_params;
+
+/* Replaces brisk::ScaleSpaceFeatureDetector<HarrisScoreCalculator>::detect
+ * (brisk/include/brisk/scale-space-feature-detector.h:89-163) as called by okvis::Frame::detect
+ * (okvis_cv/include/okvis/implementation/Frame.hpp:120-134).
+ * image: u8, continuous rows (stride == width, as the reference demands, :95-97).
+ * keypoints[capacity] receives *n keypoints in the reference order (descending score). */
+int okc_detect(okc_camera* cam, const uint8_t* image, const okc_detect_params* p, okc_keypoint* keypoints,
+               int capacity, int* n);
+
+/* Replaces brisk::BriskDescriptorExtractor::compute / doDescriptorComputation
+ * (brisk/src/brisk-descriptor-extractor.cc:575-805) as called by okvis::Frame::describe (Frame.hpp:140-155).
+ * keypoints is in/out: border-filtered in order (n shrinks), angle written back. descriptors: u8[n*48]. */
+int okc_describe(okc_camera* cam, const uint8_t* image, const okc_describe_params* p, okc_keypoint* keypoints,
+                 int* n, uint8_t* descriptors);
+
+/* Fused detect + describe of Frontend::detectAndDescribe -> MultiFrame::detect + describe
+ * (Frontend.cpp:204-262): image uploaded once, keypoints never leave the device between the stages. */
+int okc_detect_describe(okc_camera* cam, const uint8_t* image, const okc_detect_params* dp,
+                        const okc_describe_params* xp, okc_keypoint* keypoints, int capacity, int* n,
+                        uint8_t* descriptors);
+
+/* Same, asynchronous halves for overlapping several cameras (one std::thread per camera in
+ * ThreadedSlam.cpp:676-708 becomes one stream per camera): enqueue returns immediately,
+ * finish waits for that camera's stream and copies the results out. */
+int okc_detect_describe_enqueue(okc_camera* cam, const uint8_t* image, const okc_detect_params* dp,
+                                const okc_describe_params* xp);
+int okc_detect_describe_finish(okc_camera* cam, okc_keypoint* keypoints, int capacity, int* n,
+                               uint8_t* descriptors);
+
+/* Intermediate products, for parity tests (not used by the reference's callers):
+ * scores int32[H*W] = brisk::HarrisScoresSSE (brisk/src/harris-scores.cc:65-301);
+ * candidates {int32 score; uint16 x, y}[cap] = HarrisScoreCalculator::Get2dMaxima
+ * (brisk/src/harris-score-calculator.cc:70-119) sorted by (score desc, raster asc). */
+int okc_debug_scores(okc_camera* cam, const uint8_t* image, int32_t* scores);
+int okc_debug_candidates(okc_camera* cam, const uint8_t* image, int absolute_threshold, void* candidates, int cap,
+                         int* n);
+
+/* ---- Matching. Replaces the loops around brisk::Hamming::PopcntofXORed(a, b, 3)
+ * (brisk/include/brisk/internal/hamming-inl.h:95-144) in okvis_frontend/src/Frontend.cpp. ---- */
+
+/* Plain brute force: for each query the map row with the smallest Hamming distance strictly below
+ * `threshold`, first row wins ties (strict '<' running minimum). Frontend::verifyRecognisedPlace
+ * (Frontend.cpp:316-345) and the 10k x 1M sweep. best[q] = (dist << 32) | (index + index_offset), or
+ * OKC_NO_MATCH. Host buffers. */
+int okc_match_batched(okc_context* ctx, const uint8_t* queries, int nq, const uint8_t* map, int64_t nm,
+                      uint32_t threshold, uint64_t index_offset, uint64_t* best);
+
+/* Device-resident variant for sharded maps: upload once, sweep many times. */
+typedef struct okc_descriptor_set okc_descriptor_set;
+int okc_descriptor_set_create(okc_context* ctx, const uint8_t* rows, int64_t n, okc_descriptor_set** set);
+int okc_descriptor_set_destroy(okc_descriptor_set* set);
+/* best_device != NULL: leave the result in this device buffer (uint64[nq]) for a following NCCL gather
+ * and skip the copy to best_host (may be NULL). stream_handle: a cudaStream_t or 0. */
+int okc_match_sets(okc_context* ctx, const okc_descriptor_set* queries, const okc_descriptor_set* map,
+                   uint32_t threshold, uint64_t index_offset, uint64_t* best_host, void* best_device,
+                   void* stream_handle);
+
+/* 3D-2D map matching, Frontend::matchToMapByThread (Frontend.cpp:1744-1827) for all thread slices at once.
+ * Keypoint k (descriptor queries[k], position kp_xy[2k..]) with use[k] != 0 is compared with every
+ * descriptor row m (owner landmark slot map_owner[m], ascending = std::map order) whose landmark projection
+ * proj_xy[2*owner] lies within sqrt(thresh_sq) pixels. Outputs per k: best_dist[k] (double, init = threshold),
+ * best_owner[k] (landmark slot or -1). Per thread slice t (num_slices = num_matching_threads): ctrs[t] and
+ * repr_errors[t] exactly as the reference accumulates them (improvement events in landmark-major order,
+ * final division included; NaN when ctrs[t] == 0). */
+int okc_match_to_map(okc_context* ctx, const uint8_t* queries, const double* kp_xy, const uint8_t* use, int nk,
+                     const uint8_t* map, const int32_t* map_owner, int nm, const double* proj_xy, int num_landmarks,
+                     double thresh_sq, double hamming_threshold, int num_slices, double* best_dist,
+                     int32_t* best_owner, uint64_t* ctrs, double* repr_errors);
+
+/* 2D-2D stereo matching, the k0/k1 loops of Frontend::matchStereo (Frontend.cpp:2259-2316) with
+ * triangulation::triangulateFast (okvis_frontend/src/stereo_triangulation.cpp:30-111) on the device in FP64.
+ * Per camera i: descriptors desc_i[n_i*48], keypoint sizes size_i[n_i], back-projections e_C_i[n_i*3] with
+ * validity flags bp_valid_i[n_i], pose T_WC_i as row-major 3x3 rotation C_i[9] and position r_i[3], mean focal
+ * length f_i. Outputs per k0: dist[k0] (double, = threshold when unmatched), k1_match[k0], hp_W[4*k0..]
+ * (normalised homogeneous point), initialisable[k0]. */
+typedef struct okc_stereo_view {
+  const uint8_t* desc;
+  const double* size;
+  const double* e_C;
+  const uint8_t* bp_valid;
+  int n;
+  double C_WC[9];
+  double r_WC[3];
+  double f;
+} okc_stereo_view;
+int okc_match_stereo(okc_context* ctx, const okc_stereo_view* v0, const okc_stereo_view* v1,
+                     double hamming_threshold, double* dist, int32_t* k1_match, double* hp_W,
+                     uint8_t* initialisable);
+
+/* 3D-2D matching of not-yet-initialised landmarks, Frontend::matchToMapByThreadUnitialised
+ * (Frontend.cpp:1830-1956): epipolar-plane, divergence, triangulateFast and 0.2 m gates on the device in FP64.
+ * Per map row m: owner slot, ray e_W[3m..], origin r_W[3m..]. Per keypoint k: e_W (world ray), use flag and
+ * previous landmark slot (or -1; loop-closure mode only, Frontend.cpp:1941-1944). */
+int okc_match_to_map_uninitialised(okc_context* ctx, const uint8_t* queries, const double* kp_e_W,
+                                   const uint8_t* use, const int32_t* previous_owner, int nk, const uint8_t* map,
+                                   const int32_t* map_owner, const double* map_e_W, const double* map_r_W, int nm,
+                                   const double r_WC[3], double focal_length, double hamming_threshold,
+                                   int num_slices, double* best_dist, int32_t* best_owner, double* hps_W,
+                                   uint8_t* hps_written, uint64_t* ctrs);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* OKVIS_CUDA_H_ */

@@ -1,0 +1,290 @@
+"""okvis2-x_b200: host-side mirror (Python, ctypes) of the okvis_cuda C ABI.
+
+The product is `libokvis_cuda.so` (hand-written sm_100a kernels behind include/okvis_cuda.h). This package
+only loads it and mirrors the reference's call surface for the hot path:
+
+  okvis::MultiFrame::detect / describe (okvis_cv/include/okvis/MultiFrame.hpp:158-164)   -> Camera.detect / describe
+  Frontend::detectAndDescribe (okvis_frontend/src/Frontend.cpp:204-262)                  -> Camera.detect_describe
+  Frontend matching loops (Frontend.cpp:316-345, 1744-1956, 2259-2316)                   -> Context.match_*
+
+There is no CPU fallback: a missing library or a missing GPU raises.
+The directory name has a hyphen, so import it through `load()` in __graft_entry__.py (alias `okvis2x_b200`).
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libokvis_cuda.so")
+
+KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"), ("response", "<f4"),
+                     ("octave", "<i4"), ("class_id", "<i4")])
+PWS_DTYPE = np.dtype([("score", "<i4"), ("x", "<u2"), ("y", "<u2")])
+NO_MATCH = np.uint64(0xFFFFFFFFFFFFFFFF)
+
+EXPORTS = [
+    "okc_last_error_string", "okc_version", "okc_context_create", "okc_context_destroy", "okc_context_device",
+    "okc_camera_create", "okc_camera_destroy", "okc_detect", "okc_describe", "okc_detect_describe",
+    "okc_detect_describe_enqueue", "okc_detect_describe_finish", "okc_debug_scores", "okc_debug_candidates",
+    "okc_match_batched", "okc_descriptor_set_create", "okc_descriptor_set_destroy", "okc_match_sets",
+    "okc_match_to_map", "okc_match_stereo", "okc_match_to_map_uninitialised",
+]
+
+
+class OkcError(RuntimeError):
+    pass
+
+
+class DetectParams(C.Structure):
+    _fields_ = [("uniformity_radius", C.c_double), ("octaves", C.c_uint64), ("absolute_threshold", C.c_double),
+                ("max_num_keypoints", C.c_uint64)]
+
+
+class DescribeParams(C.Structure):
+    _fields_ = [("rotation_invariant", C.c_int), ("scale_invariant", C.c_int), ("extraction_direction", C.c_float * 3)]
+
+
+class StereoView(C.Structure):
+    _fields_ = [("desc", C.c_void_p), ("size", C.c_void_p), ("e_C", C.c_void_p), ("bp_valid", C.c_void_p),
+                ("n", C.c_int), ("C_WC", C.c_double * 9), ("r_WC", C.c_double * 3), ("f", C.c_double)]
+
+
+_lib = None
+
+
+def lib():
+    """Load libokvis_cuda.so (fails loudly when it has not been built: run __graft_entry__.build())."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise OkcError("%s is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'`" % LIB_PATH)
+        L = C.CDLL(LIB_PATH)
+        vp, i, u32, u64, i64, d, f = C.c_void_p, C.c_int, C.c_uint32, C.c_uint64, C.c_int64, C.c_double, C.c_float
+        L.okc_last_error_string.restype = C.c_char_p
+        L.okc_context_create.argtypes = [i, C.POINTER(vp)]
+        L.okc_context_destroy.argtypes = [vp]
+        L.okc_camera_create.argtypes = [vp, i, i, vp, vp, f, i, C.POINTER(vp)]
+        L.okc_camera_destroy.argtypes = [vp]
+        L.okc_detect.argtypes = [vp, vp, C.POINTER(DetectParams), vp, i, C.POINTER(i)]
+        L.okc_describe.argtypes = [vp, vp, C.POINTER(DescribeParams), vp, C.POINTER(i), vp]
+        L.okc_detect_describe.argtypes = [vp, vp, C.POINTER(DetectParams), C.POINTER(DescribeParams), vp, i,
+                                          C.POINTER(i), vp]
+        L.okc_detect_describe_enqueue.argtypes = [vp, vp, C.POINTER(DetectParams), C.POINTER(DescribeParams)]
+        L.okc_detect_describe_finish.argtypes = [vp, vp, i, C.POINTER(i), vp]
+        L.okc_debug_scores.argtypes = [vp, vp, vp]
+        L.okc_debug_candidates.argtypes = [vp, vp, i, vp, i, C.POINTER(i)]
+        L.okc_debug_host_tables.argtypes = [vp, C.POINTER(i), C.POINTER(i), vp, vp, vp]
+        L.okc_debug_set_match_prefix.argtypes = [i]
+        L.okc_match_batched.argtypes = [vp, vp, i, vp, i64, u32, u64, vp]
+        L.okc_descriptor_set_create.argtypes = [vp, vp, i64, C.POINTER(vp)]
+        L.okc_descriptor_set_destroy.argtypes = [vp]
+        L.okc_descriptor_set_device_ptr.argtypes = [vp]
+        L.okc_descriptor_set_device_ptr.restype = vp
+        L.okc_match_sets.argtypes = [vp, vp, vp, u32, u64, vp, vp, vp]
+        L.okc_match_to_map.argtypes = [vp, vp, vp, vp, i, vp, vp, i, vp, i, d, d, i, vp, vp, vp, vp]
+        L.okc_match_stereo.argtypes = [vp, C.POINTER(StereoView), C.POINTER(StereoView), d, vp, vp, vp, vp]
+        _lib = L
+    return _lib
+
+
+def _check(rc, what):
+    if rc != 0:
+        raise OkcError("%s failed (code %d): %s" % (what, rc, lib().okc_last_error_string().decode()))
+
+
+def _p(a):
+    return C.c_void_p(a.ctypes.data) if a is not None else None
+
+
+def host_tables():
+    """Pattern tables as built on the host at context creation (no GPU needed)."""
+    pts = np.zeros((1024, 66, 3), np.float32)
+    lp = np.zeros((856, 4), np.int32)
+    sp = np.zeros((384, 2), np.uint8)
+    lut = np.zeros((31, 31), np.float32)
+    bs, bd = C.c_int(0), C.c_int(0)
+    _check(lib().okc_debug_host_tables(_p(pts), C.byref(bs), C.byref(bd), _p(lp), _p(sp), _p(lut)), "host_tables")
+    return dict(points=pts, basicscale=bs.value, border=bd.value, long_pairs=lp, short_pairs=sp, lut=lut)
+
+
+class Context:
+    def __init__(self, device=-1):
+        self.h = C.c_void_p()
+        _check(lib().okc_context_create(device, C.byref(self.h)), "okc_context_create")
+
+    def close(self):
+        if self.h:
+            lib().okc_context_destroy(self.h)
+            self.h = C.c_void_p()
+
+    # -- brute force (Frontend::verifyRecognisedPlace, Frontend.cpp:316-345; the 10k x 1M sweep) --
+    def match_batched(self, queries, mp, threshold=60, index_offset=0):
+        q = np.ascontiguousarray(queries, np.uint8).reshape(-1, 48)
+        m = np.ascontiguousarray(mp, np.uint8).reshape(-1, 48)
+        best = np.empty(len(q), np.uint64)
+        _check(lib().okc_match_batched(self.h, _p(q), len(q), _p(m), len(m), int(threshold), int(index_offset),
+                                       _p(best)), "okc_match_batched")
+        return best
+
+    def descriptor_set(self, rows):
+        return DescriptorSet(self, rows)
+
+    def match_sets(self, qset, mset, threshold=60, index_offset=0, best_device=None, stream=None, want_host=True):
+        best = np.empty(qset.n, np.uint64) if want_host else None
+        _check(lib().okc_match_sets(self.h, qset.h, mset.h, int(threshold), int(index_offset), _p(best),
+                                    C.c_void_p(best_device) if best_device else None,
+                                    C.c_void_p(stream) if stream else None), "okc_match_sets")
+        return best
+
+    # -- Frontend::matchToMapByThread, Frontend.cpp:1744-1827 --
+    def match_to_map(self, queries, kp_xy, use, mp, map_owner, proj_xy, thresh_sq, hamming_threshold=60.0,
+                     num_slices=4):
+        q = np.ascontiguousarray(queries, np.uint8).reshape(-1, 48)
+        kp = np.ascontiguousarray(kp_xy, np.float64).reshape(-1, 2)
+        us = np.ascontiguousarray(use, np.uint8)
+        m = np.ascontiguousarray(mp, np.uint8).reshape(-1, 48)
+        ow = np.ascontiguousarray(map_owner, np.int32)
+        pr = np.ascontiguousarray(proj_xy, np.float64).reshape(-1, 2)
+        nk = len(q)
+        bd = np.empty(nk, np.float64)
+        bo = np.empty(nk, np.int32)
+        ctrs = np.zeros(num_slices, np.uint64)
+        errs = np.zeros(num_slices, np.float64)
+        _check(lib().okc_match_to_map(self.h, _p(q), _p(kp), _p(us), nk, _p(m), _p(ow), len(m), _p(pr), len(pr),
+                                      float(thresh_sq), float(hamming_threshold), int(num_slices), _p(bd), _p(bo),
+                                      _p(ctrs), _p(errs)), "okc_match_to_map")
+        return bd, bo, ctrs, errs
+
+    # -- Frontend::matchStereo inner loops, Frontend.cpp:2259-2316 --
+    def match_stereo(self, view0, view1, hamming_threshold=60.0):
+        keep = []
+
+        def mk(v):
+            s = StereoView()
+            desc = np.ascontiguousarray(v["desc"], np.uint8).reshape(-1, 48)
+            size = np.ascontiguousarray(v["size"], np.float64)
+            e_C = np.ascontiguousarray(v["e_C"], np.float64).reshape(-1, 3)
+            bpv = np.ascontiguousarray(v["bp_valid"], np.uint8)
+            keep.extend([desc, size, e_C, bpv])
+            s.desc, s.size, s.e_C, s.bp_valid = desc.ctypes.data, size.ctypes.data, e_C.ctypes.data, bpv.ctypes.data
+            s.n = len(desc)
+            s.C_WC[:] = list(np.asarray(v["C_WC"], np.float64).reshape(9))
+            s.r_WC[:] = list(np.asarray(v["r_WC"], np.float64).reshape(3))
+            s.f = float(v["f"])
+            return s
+
+        s0, s1 = mk(view0), mk(view1)
+        n0 = s0.n
+        dist = np.empty(n0, np.float64)
+        k1 = np.empty(n0, np.int32)
+        hp = np.empty((n0, 4), np.float64)
+        init = np.empty(n0, np.uint8)
+        _check(lib().okc_match_stereo(self.h, C.byref(s0), C.byref(s1), float(hamming_threshold), _p(dist), _p(k1),
+                                      _p(hp), _p(init)), "okc_match_stereo")
+        return dist, k1, hp, init
+
+
+class DescriptorSet:
+    def __init__(self, ctx, rows):
+        r = np.ascontiguousarray(rows, np.uint8).reshape(-1, 48)
+        self.n = len(r)
+        self.h = C.c_void_p()
+        _check(lib().okc_descriptor_set_create(ctx.h, _p(r), self.n, C.byref(self.h)), "okc_descriptor_set_create")
+
+    def close(self):
+        if self.h:
+            lib().okc_descriptor_set_destroy(self.h)
+            self.h = C.c_void_p()
+
+
+class Camera:
+    """One camera of a MultiFrame: owns a stream, device scratch and (optionally) the camera-awareness maps."""
+
+    def __init__(self, ctx, width, height, rays=None, jacobians=None, focal=500.0, max_keypoints=4096):
+        self.ctx, self.W, self.H, self.max_kp = ctx, width, height, max_keypoints
+        self.h = C.c_void_p()
+        if rays is not None:
+            rays = np.ascontiguousarray(rays, np.float32)
+            jacobians = np.ascontiguousarray(jacobians, np.float32)
+            assert rays.shape == (height, width, 3) and jacobians.shape == (height, width, 6)
+        _check(lib().okc_camera_create(ctx.h, width, height, _p(rays), _p(jacobians), float(focal), max_keypoints,
+                                       C.byref(self.h)), "okc_camera_create")
+
+    def close(self):
+        if self.h:
+            lib().okc_camera_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def _img(self, image):
+        img = np.asarray(image)
+        # the reference throws std::runtime_error for non-continuous / non-8-bit / multi-channel input
+        # (scale-space-feature-detector.h:95-97)
+        if img.dtype != np.uint8 or img.ndim != 2 or not img.flags["C_CONTIGUOUS"]:
+            raise OkcError("BRISK requires continuous 1-channel 8-bit images")
+        if img.shape != (self.H, self.W):
+            raise OkcError("image shape %s does not match the camera (%d, %d)" % (img.shape, self.H, self.W))
+        return img
+
+    @staticmethod
+    def _dp(radius, octaves, abs_threshold, max_kpt):
+        return DetectParams(float(radius), int(octaves), float(abs_threshold), int(max_kpt))
+
+    @staticmethod
+    def _xp(rotation_invariant, scale_invariant, direction):
+        x = DescribeParams(int(rotation_invariant), int(scale_invariant))
+        x.extraction_direction[:] = [float(v) for v in direction]
+        return x
+
+    def detect(self, image, radius, octaves, abs_threshold, max_kpt):
+        img = self._img(image)
+        kp = np.zeros(self.max_kp, KP_DTYPE)
+        n = C.c_int(0)
+        dp = self._dp(radius, octaves, abs_threshold, max_kpt)
+        _check(lib().okc_detect(self.h, _p(img), C.byref(dp), _p(kp), self.max_kp, C.byref(n)), "okc_detect")
+        return kp[:n.value].copy()
+
+    def describe(self, image, keypoints, rotation_invariant=True, scale_invariant=False, direction=(0.0, 1.0, 0.0)):
+        img = self._img(image)
+        kp = np.zeros(max(len(keypoints), 1), KP_DTYPE)
+        kp[:len(keypoints)] = keypoints
+        n = C.c_int(len(keypoints))
+        desc = np.zeros((max(len(keypoints), 1), 48), np.uint8)
+        xp = self._xp(rotation_invariant, scale_invariant, direction)
+        _check(lib().okc_describe(self.h, _p(img), C.byref(xp), _p(kp), C.byref(n), _p(desc)), "okc_describe")
+        return kp[:n.value].copy(), desc[:n.value].copy()
+
+    def detect_describe(self, image, radius, octaves, abs_threshold, max_kpt, rotation_invariant=True,
+                        scale_invariant=False, direction=(0.0, 1.0, 0.0)):
+        self.enqueue(image, radius, octaves, abs_threshold, max_kpt, rotation_invariant, scale_invariant, direction)
+        return self.finish()
+
+    def enqueue(self, image, radius, octaves, abs_threshold, max_kpt, rotation_invariant=True, scale_invariant=False,
+                direction=(0.0, 1.0, 0.0)):
+        img = self._img(image)
+        dp = self._dp(radius, octaves, abs_threshold, max_kpt)
+        xp = self._xp(rotation_invariant, scale_invariant, direction)
+        _check(lib().okc_detect_describe_enqueue(self.h, _p(img), C.byref(dp), C.byref(xp)),
+               "okc_detect_describe_enqueue")
+
+    def finish(self):
+        kp = np.zeros(self.max_kp, KP_DTYPE)
+        desc = np.zeros((self.max_kp, 48), np.uint8)
+        n = C.c_int(0)
+        _check(lib().okc_detect_describe_finish(self.h, _p(kp), self.max_kp, C.byref(n), _p(desc)),
+               "okc_detect_describe_finish")
+        return kp[:n.value].copy(), desc[:n.value].copy()
+
+    def debug_scores(self, image):
+        img = self._img(image)
+        out = np.zeros((self.H, self.W), np.int32)
+        _check(lib().okc_debug_scores(self.h, _p(img), _p(out)), "okc_debug_scores")
+        return out
+
+    def debug_candidates(self, image, abs_threshold, cap=1 << 17):
+        img = self._img(image)
+        out = np.zeros(cap, PWS_DTYPE)
+        n = C.c_int(0)
+        _check(lib().okc_debug_candidates(self.h, _p(img), int(abs_threshold), _p(out), cap, C.byref(n)),
+               "okc_debug_candidates")
+        return out[:n.value].copy()

@@ -1,0 +1,311 @@
+// Descriptor extraction kernels: one warp per keypoint.
+//
+// Follows brisk::BriskDescriptorExtractor::doDescriptorComputation
+// (brisk/src/brisk-descriptor-extractor.cc:575-805) and SmoothedIntensity<uchar,int> (:355-535).
+// Every float/double operation is written in the reference's evaluation order and precision
+// (the file is compiled with --fmad=false); int sums wrap like the reference's int.
+//
+// The reference builds an integral image (brisk/include/brisk/internal/integral-image.h:66-174) and reads
+// 12 taps of it per sample when the box is larger than 2 px; the box sums are exact integers, so here each
+// lane adds the pixels of its box directly (<= ~12x12 u8 reads, L1/L2 hits) and no (H+1)x(W+1) int32 image
+// is ever written to HBM. The weighted sum is identical term by term.
+#include "common.cuh"
+
+namespace okc {
+
+constexpr int kWarpsPerBlock = 8;
+
+// ---- border filter: ordered compaction (brisk-descriptor-extractor.cc:601-627, RoiPredicate :537-541) ----
+__global__ void __launch_bounds__(1024) border_filter_kernel(const okc_keypoint* __restrict__ in,
+                                                             const int* __restrict__ n_in_ptr,
+                                                             okc_keypoint* __restrict__ out, int* __restrict__ counters,
+                                                             int W, int H, int border, int maxOut) {
+  __shared__ int s_warpcnt[32], s_warpoff[32], s_total;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int n = *n_in_ptr;
+  const float minX = (float)border, minY = (float)border, maxX = (float)(W - border), maxY = (float)(H - border);
+  int base_out = 0;
+  for (int base = 0; base < n; base += 1024) {
+    const int i = base + tid;
+    bool keep = false;
+    okc_keypoint kp;
+    if (i < n) {
+      kp = in[i];
+      keep = !((kp.x < minX) || (kp.x >= maxX) || (kp.y < minY) || (kp.y >= maxY));
+    }
+    const unsigned ballot = __ballot_sync(0xffffffffu, keep);
+    if (lane == 0) s_warpcnt[warp] = __popc(ballot);
+    __syncthreads();
+    if (warp == 0) {
+      int c = s_warpcnt[lane], incl = c;
+      for (int d = 1; d < 32; d <<= 1) {
+        int t = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d) incl += t;
+      }
+      s_warpoff[lane] = incl - c;
+      if (lane == 31) s_total = incl;
+    }
+    __syncthreads();
+    if (keep) {
+      const int pos = base_out + s_warpoff[warp] + __popc(ballot & ((1u << lane) - 1u));
+      if (pos < maxOut) out[pos] = kp;
+    }
+    base_out += s_total;
+    __syncthreads();
+  }
+  if (tid == 0) counters[2] = base_out < maxOut ? base_out : maxOut;
+}
+
+// ---- SmoothedIntensity<unsigned char, int> ----
+__device__ __forceinline__ int smoothed_intensity(const uint8_t* __restrict__ img, int W, int H, float key_x,
+                                                  float key_y, PatternPoint p0, bool warped, const float* warp,
+                                                  float warpScale) {
+  float bx = p0.x, by = p0.y, bs = p0.sigma;
+  if (warped) {
+    bx = warp[0] * p0.x + warp[1] * p0.y;
+    by = warp[2] * p0.x + warp[3] * p0.y;
+    bs = warpScale * p0.sigma;
+  }
+  const float xf = bx + key_x;
+  const float yf = by + key_y;
+  const int x = (int)xf;
+  const int y = (int)yf;
+  const float sigma_half = bs;
+  const float area = (float)(4.0 * (double)sigma_half * (double)sigma_half);
+  const float x_1 = xf - sigma_half, x1 = xf + sigma_half;
+  const float y_1 = yf - sigma_half, y1 = yf + sigma_half;
+
+  if (sigma_half < 0.5f) {
+    if (x < 0 || x > W - 2 || y < 0 || y > H - 2) return -1;
+    const int r_x = (int)((xf - (float)x) * 1024.0f);
+    const int r_y = (int)((yf - (float)y) * 1024.0f);
+    const int r_x_1 = 1024 - r_x, r_y_1 = 1024 - r_y;
+    const uint8_t* p = img + x + (size_t)y * W;
+    int ret = r_x_1 * r_y_1 * (int)p[0];
+    ret += r_x * r_y_1 * (int)p[1];
+    ret += r_x * r_y * (int)p[W + 1];
+    ret += r_x_1 * r_y * (int)p[W];
+    return ret / 1024;
+  }
+  if (x_1 < 0.0f) return -1;
+  if (x1 > (float)(W - 1)) return -1;
+  if (y_1 < 0.0f) return -1;
+  if (y1 > (float)(H - 1)) return -1;
+
+  const int scaling = (int)(4194304.0 / (double)area);
+  const int scaling2 = (int)((double)((float)scaling * area) / 1024.0);
+  const int x_left = (int)((double)x_1 + 0.5);
+  const int y_top = (int)((double)y_1 + 0.5);
+  const int x_right = (int)((double)x1 + 0.5);
+  const int y_bottom = (int)((double)y1 + 0.5);
+  const float r_x_1 = (float)((double)((float)x_left - x_1) + 0.5);
+  const float r_y_1 = (float)((double)((float)y_top - y_1) + 0.5);
+  const float r_x1 = (float)((double)(x1 - (float)x_right) + 0.5);
+  const float r_y1 = (float)((double)(y1 - (float)y_bottom) + 0.5);
+  const int dx = x_right - x_left - 1;
+  const int dy = y_bottom - y_top - 1;
+  const float fs = (float)scaling;
+  const int A = (int)((r_x_1 * r_y_1) * fs);
+  const int B = (int)((r_x1 * r_y_1) * fs);
+  const int C = (int)((r_x1 * r_y1) * fs);
+  const int D = (int)((r_x_1 * r_y1) * fs);
+  const int r_x_1_i = (int)(r_x_1 * fs);
+  const int r_y_1_i = (int)(r_y_1 * fs);
+  const int r_x1_i = (int)(r_x1 * fs);
+  const int r_y1_i = (int)(r_y1 * fs);
+
+  // corners, edges, interior: the same weighted terms as :450-534 (integral-image path and loop path)
+  const uint8_t* row = img + x_left + (size_t)y_top * W;
+  int top = 0, bottom = 0, left = 0, right = 0, middle = 0;
+  for (int c = 1; c <= dx; ++c) top += (int)row[c];
+  int ret = A * (int)row[0] + B * (int)row[dx + 1];
+  for (int r = 1; r <= dy; ++r) {
+    row += W;
+    left += (int)row[0];
+    right += (int)row[dx + 1];
+    for (int c = 1; c <= dx; ++c) middle += (int)row[c];
+  }
+  row += W;
+  for (int c = 1; c <= dx; ++c) bottom += (int)row[c];
+  ret += D * (int)row[0] + C * (int)row[dx + 1];
+  ret += top * r_y_1_i + middle * scaling + left * r_x_1_i + right * r_x1_i + bottom * r_y1_i;
+  return ret / scaling2;
+}
+
+// cv::normalize(Vec3f): norm in double, scale in double, cast to float (OpenCV matx.hpp).
+__device__ __forceinline__ void cv_normalize3(const float v[3], float out[3]) {
+  double s = 0.0;
+  for (int i = 0; i < 3; ++i) {
+    double e = (double)v[i];
+    s += e * e;
+  }
+  const double nv = sqrt(s);
+  const double inv = nv != 0.0 ? 1.0 / nv : 0.0;
+  for (int i = 0; i < 3; ++i) out[i] = (float)((double)v[i] * inv);
+}
+__device__ __forceinline__ void cross3f(const float a[3], const float b[3], float o[3]) {
+  o[0] = a[1] * b[2] - a[2] * b[1];
+  o[1] = a[2] * b[0] - a[0] * b[2];
+  o[2] = a[0] * b[1] - a[1] * b[0];
+}
+__device__ __forceinline__ float dot3f(const float a[3], const float b[3]) {
+  float s = 0.0f;
+  s += a[0] * b[0];
+  s += a[1] * b[1];
+  s += a[2] * b[2];
+  return s;
+}
+// Jacobi helper of cv::eigen (OpenCV lapack.cpp, JacobiImpl_<float>::hypot)
+__device__ __forceinline__ float jhypot(float a, float b) {
+  a = fabsf(a);
+  b = fabsf(b);
+  if (a > b) {
+    b /= a;
+    return a * sqrtf(1 + b * b);
+  }
+  if (b > 0) {
+    a /= b;
+    return b * sqrtf(1 + a * a);
+  }
+  return 0.0f;
+}
+
+__global__ void __launch_bounds__(kWarpsPerBlock * 32)
+describe_kernel(const uint8_t* __restrict__ img, okc_keypoint* __restrict__ kps, uint8_t* __restrict__ desc,
+                const int* __restrict__ counters, const float* __restrict__ rays, const float* __restrict__ jac,
+                const PatternPoint* __restrict__ pattern, const uchar2* __restrict__ short_pairs,
+                const LongPair* __restrict__ long_pairs, DescribeArgs a) {
+  __shared__ int s_values[kWarpsPerBlock][kPoints + 2];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int k = blockIdx.x * kWarpsPerBlock + warp;
+  if (k >= counters[2]) return;
+  int* values = s_values[warp];
+  const int W = a.width, H = a.height;
+
+  okc_keypoint kp = kps[k];
+  const float x = kp.x, y = kp.y;
+
+  // ---- camera-aware warp (:654-725); every lane computes it redundantly ----
+  bool warped = false, directional = false;
+  float warp4[4] = {0.f, 0.f, 0.f, 0.f};
+  float sigmaScale = 1.0f;
+  if (a.camera_aware) {
+    const int x0 = (int)floorf(x), y0 = (int)floorf(y);
+    const float dx = x - (float)x0, dy = y - (float)y0;
+    const float w_tl = (1.0f - dx) * (1.0f - dy);
+    const float w_tr = dx * (1.0f - dy);
+    const float w_bl = (1.0f - dx) * dy;
+    const float w_br = dx * dy;
+    float d_tl[3], d_tr[3], d_bl[3], d_br[3];
+    const float* r0 = rays + ((size_t)y0 * W + x0) * 3;
+    const float* r1 = r0 + (size_t)W * 3;
+    for (int i = 0; i < 3; ++i) {
+      d_tl[i] = __ldg(r0 + i);
+      d_tr[i] = __ldg(r0 + 3 + i);
+      d_bl[i] = __ldg(r1 + i);
+      d_br[i] = __ldg(r1 + 3 + i);
+    }
+    if ((double)dot3f(d_tl, d_tl) > 1e-12 && (double)dot3f(d_tr, d_tr) > 1e-12 && (double)dot3f(d_bl, d_bl) > 1e-12 &&
+        (double)dot3f(d_br, d_br) > 1e-12) {
+      float dir[3];
+      for (int i = 0; i < 3; ++i) dir[i] = ((w_tl * d_tl[i] + w_tr * d_tr[i]) + w_bl * d_bl[i]) + w_br * d_br[i];
+      float eu[3], ev[3], t[3];
+      cross3f(a.dir, dir, eu);
+      if ((double)(eu[0] * eu[0] + eu[1] * eu[1] + eu[2] * eu[2]) > 0.01) directional = true;
+      cv_normalize3(eu, t);
+      for (int i = 0; i < 3; ++i) eu[i] = t[i] * a.inv_f;
+      cross3f(dir, eu, t);
+      cv_normalize3(t, ev);
+      for (int i = 0; i < 3; ++i) ev[i] = ev[i] * a.inv_f;
+      const int xm = (int)roundf(x), ym = (int)roundf(y);
+      const float* jp = jac + ((size_t)ym * W + xm) * 6;
+      float J[6];
+      for (int i = 0; i < 6; ++i) J[i] = __ldg(jp + i);
+      // warp = J(2x3) * [eu ev](3x2) through cv::gemm: double accumulation in k order, cast to float
+      for (int r = 0; r < 2; ++r) {
+        double s0 = 0.0, s1 = 0.0;
+        for (int c = 0; c < 3; ++c) {
+          s0 += (double)J[r * 3 + c] * (double)eu[c];
+          s1 += (double)J[r * 3 + c] * (double)ev[c];
+        }
+        warp4[r * 2 + 0] = (float)s0;
+        warp4[r * 2 + 1] = (float)s1;
+      }
+      // cv::eigen(2x2 float): one Jacobi rotation on the upper off-diagonal; only the eigenvalues matter
+      float W0 = warp4[0], W1 = warp4[3];
+      const float p = warp4[1];
+      if (fabsf(p) > 1.1920928955078125e-7f) {
+        const float yy = (W1 - W0) * 0.5f;
+        float t2 = fabsf(yy) + jhypot(p, yy);
+        t2 = (p / t2) * p;
+        if (yy < 0) t2 = -t2;
+        W0 -= t2;
+        W1 += t2;
+      }
+      sigmaScale = (float)(0.5 * ((double)fabsf(W0) + (double)fabsf(W1)));
+      if (directional) kp.angle = (float)(atan2((double)warp4[3], (double)warp4[1]) / 3.14159265358979323846 * 180.0);
+      warped = true;
+    }
+  }
+
+  // ---- orientation (:731-784) ----
+  int theta;
+  if (kp.angle == -1.0f) {
+    if (!a.rotation_invariant) {
+      theta = 0;
+    } else {
+      for (int i = lane; i < kPoints; i += 32)
+        values[i] = smoothed_intensity(img, W, H, x, y, pattern[i], false, warp4, 1.0f);
+      __syncwarp();
+      int direction0 = 0, direction1 = 0;
+      for (int p = lane; p < kLongPairs; p += 32) {
+        const LongPair lp = long_pairs[p];
+        const int delta_t = values[lp.i] - values[lp.j];
+        direction0 += delta_t * lp.wdx / 1024;
+        direction1 += delta_t * lp.wdy / 1024;
+      }
+      for (int o = 16; o > 0; o >>= 1) {
+        direction0 += __shfl_xor_sync(0xffffffffu, direction0, o);
+        direction1 += __shfl_xor_sync(0xffffffffu, direction1, o);
+      }
+      __syncwarp();
+      kp.angle = (float)(atan2((double)(float)direction1, (double)(float)direction0) / 3.14159265358979323846 * 180.0);
+      theta = (int)((double)(1024.0f * kp.angle) / 360.0 + 0.5);
+      if (theta < 0) theta += kNRot;
+      if (theta >= kNRot) theta -= kNRot;
+    }
+  } else {
+    if (!a.rotation_invariant) {
+      theta = 0;
+    } else {
+      theta = (int)(1024.0 * ((double)kp.angle / 360.0) + 0.5);
+      if (theta < 0) theta += kNRot;
+      if (theta >= kNRot) theta -= kNRot;
+    }
+  }
+
+  // ---- sampling in the final direction (:786-797) and bit tests (:543-568) ----
+  const PatternPoint* pat = pattern + (size_t)(directional ? 0 : theta) * kPoints;
+  for (int i = lane; i < kPoints; i += 32)
+    values[i] = smoothed_intensity(img, W, H, x, y, pat[i], warped, warp4, sigmaScale);
+  __syncwarp();
+  uint32_t* out = reinterpret_cast<uint32_t*>(desc + (size_t)k * OKC_DESC_BYTES);
+#pragma unroll
+  for (int w = 0; w < kDescWords; ++w) {
+    const uchar2 sp = short_pairs[w * 32 + lane];
+    const unsigned bits = __ballot_sync(0xffffffffu, values[sp.x] > values[sp.y]);
+    if (lane == 0) out[w] = bits;
+  }
+  if (lane == 0) kps[k].angle = kp.angle;
+}
+
+void launch_describe(const uint8_t* image, const okc_keypoint* kp_in, const int* n_in, okc_keypoint* kp_out,
+                     uint8_t* desc, int* counters, const float* rays, const float* jac, const PatternTables& t,
+                     const DescribeArgs& a, int max_kp, cudaStream_t s) {
+  border_filter_kernel<<<1, 1024, 0, s>>>(kp_in, n_in, kp_out, counters, a.width, a.height, t.border, max_kp);
+  const int blocks = (max_kp + kWarpsPerBlock - 1) / kWarpsPerBlock;
+  describe_kernel<<<blocks, kWarpsPerBlock * 32, 0, s>>>(image, kp_out, desc, counters, rays, jac, t.points,
+                                                         t.short_pairs, t.long_pairs, a);
+}
+
+}  // namespace okc

@@ -1,0 +1,389 @@
+// Hamming matching kernels.
+//
+// All of them replace loops around brisk::Hamming::PopcntofXORed(a, b, 3)
+// (brisk/include/brisk/internal/hamming-inl.h:95-144): popcount(a XOR b) over 384 bits, and a strict '<'
+// running minimum, so the FIRST candidate in iteration order wins ties.
+//
+// No tensor cores: the work is XOR + POPC on 12 x u32 per pair. Descriptors are read as uint4 (3 per row).
+#include "common.cuh"
+
+namespace okc {
+
+// ----------------------------------------------------------------------------------------------
+// A. plain brute force, queries in registers, map rows streamed through shared memory
+// ----------------------------------------------------------------------------------------------
+constexpr int kMbThreads = 256;
+constexpr int kMbQpt = 4;                       // queries per thread
+constexpr int kMbQTile = kMbThreads * kMbQpt;   // 1024 queries per CTA
+constexpr int kMbRows = 128;                    // map rows per shared-memory stage (6 KB)
+
+__device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
+  unsigned s = static_cast<unsigned>(__cvta_generic_to_shared(smem));
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(s), "l"(gmem));
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N)); }
+
+// best[q] (u64, pre-set to ~0) receives min over rows of (dist << 32 | global row index) with dist < threshold.
+// PREFIX = number of leading 32-bit words summed before the early-out test "partial >= current best"
+// (exact: the full distance can only be larger). PREFIX = 12 disables the early-out.
+template <int PREFIX>
+__global__ void __launch_bounds__(kMbThreads)
+hamming_best_kernel(const uint4* __restrict__ queries, int nq, const uint4* __restrict__ map, long long nm,
+                    int rowsPerChunk, unsigned threshold, unsigned long long indexOffset,
+                    unsigned long long* __restrict__ best) {
+  __shared__ uint4 stage[2][kMbRows * 3];
+  const int tid = threadIdx.x;
+  const int qbase = blockIdx.y * kMbQTile;
+  const long long row0 = (long long)blockIdx.x * rowsPerChunk;
+  long long rowsLeft = nm - row0;
+  if (rowsLeft > rowsPerChunk) rowsLeft = rowsPerChunk;
+  if (rowsLeft <= 0) return;
+
+  unsigned q[kMbQpt][kDescWords];
+  unsigned bestd[kMbQpt], besti[kMbQpt];
+#pragma unroll
+  for (int j = 0; j < kMbQpt; ++j) {
+    const int qi = qbase + j * kMbThreads + tid;
+    bestd[j] = qi < nq ? threshold : 0u;  // 0: nothing can be strictly smaller -> lane idles
+    besti[j] = 0xffffffffu;
+    const int qs = qi < nq ? qi : 0;
+#pragma unroll
+    for (int w = 0; w < 3; ++w) {
+      const uint4 v = __ldg(queries + (size_t)qs * 3 + w);
+      q[j][4 * w + 0] = v.x;
+      q[j][4 * w + 1] = v.y;
+      q[j][4 * w + 2] = v.z;
+      q[j][4 * w + 3] = v.w;
+    }
+  }
+
+  const int nStages = (int)((rowsLeft + kMbRows - 1) / kMbRows);
+  auto issue = [&](int s) {
+    const long long r = row0 + (long long)s * kMbRows;
+    long long cnt = rowsLeft - (long long)s * kMbRows;
+    if (cnt > kMbRows) cnt = kMbRows;
+    const uint4* src = map + r * 3;
+    uint4* dst = stage[s & 1];
+    for (int i = tid; i < (int)cnt * 3; i += kMbThreads) cp_async16(dst + i, src + i);
+    cp_async_commit();
+  };
+  issue(0);
+  for (int s = 0; s < nStages; ++s) {
+    if (s + 1 < nStages) {
+      issue(s + 1);
+      cp_async_wait<1>();
+    } else {
+      cp_async_wait<0>();
+    }
+    __syncthreads();
+    long long cnt = rowsLeft - (long long)s * kMbRows;
+    if (cnt > kMbRows) cnt = kMbRows;
+    const uint4* rows = stage[s & 1];
+    const unsigned rowIdx0 = (unsigned)(s * kMbRows);
+#pragma unroll 2
+    for (int r = 0; r < (int)cnt; ++r) {
+      const uint4 m0 = rows[r * 3 + 0], m1 = rows[r * 3 + 1], m2 = rows[r * 3 + 2];
+      const unsigned m[kDescWords] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w, m2.x, m2.y, m2.z, m2.w};
+#pragma unroll
+      for (int j = 0; j < kMbQpt; ++j) {
+        unsigned d = 0;
+#pragma unroll
+        for (int w = 0; w < PREFIX; ++w) d += __popc(q[j][w] ^ m[w]);
+        if (d < bestd[j]) {
+#pragma unroll
+          for (int w = PREFIX; w < kDescWords; ++w) d += __popc(q[j][w] ^ m[w]);
+          if (d < bestd[j]) {
+            bestd[j] = d;
+            besti[j] = rowIdx0 + r;
+          }
+        }
+      }
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int j = 0; j < kMbQpt; ++j) {
+    const int qi = qbase + j * kMbThreads + tid;
+    if (qi < nq && besti[j] != 0xffffffffu) {
+      const unsigned long long key =
+          ((unsigned long long)bestd[j] << 32) | ((unsigned long long)(row0 + besti[j]) + indexOffset);
+      atomicMin(best + qi, key);
+    }
+  }
+}
+
+static int pick_rows_per_chunk(int nq, long long nm) {
+  // Aim at >= 4 waves of 148 SMs x 2 CTAs, chunks a multiple of the stage size, at least one stage.
+  const long long qTiles = (nq + kMbQTile - 1) / kMbQTile;
+  long long wantChunks = (148LL * 2 * 4 + qTiles - 1) / qTiles;
+  long long rows = (nm + wantChunks - 1) / wantChunks;
+  rows = ((rows + kMbRows - 1) / kMbRows) * kMbRows;
+  if (rows < kMbRows) rows = kMbRows;
+  if (rows > 65536) rows = 65536;
+  return (int)rows;
+}
+
+int g_match_prefix = 6;  // tunable for experiments (okc_debug_set_match_prefix)
+
+int launch_hamming_best(const void* queries, int nq, const void* map, long long nm, unsigned threshold,
+                        unsigned long long indexOffset, unsigned long long* best, cudaStream_t s) {
+  if (nq <= 0) return 0;
+  cudaMemsetAsync(best, 0xff, sizeof(unsigned long long) * (size_t)nq, s);
+  if (nm <= 0) return 0;
+  const int rowsPerChunk = pick_rows_per_chunk(nq, nm);
+  dim3 grid((unsigned)((nm + rowsPerChunk - 1) / rowsPerChunk), (unsigned)((nq + kMbQTile - 1) / kMbQTile));
+  const uint4* q4 = static_cast<const uint4*>(queries);
+  const uint4* m4 = static_cast<const uint4*>(map);
+  switch (g_match_prefix) {
+    case 4: hamming_best_kernel<4><<<grid, kMbThreads, 0, s>>>(q4, nq, m4, nm, rowsPerChunk, threshold, indexOffset, best); break;
+    case 5: hamming_best_kernel<5><<<grid, kMbThreads, 0, s>>>(q4, nq, m4, nm, rowsPerChunk, threshold, indexOffset, best); break;
+    case 8: hamming_best_kernel<8><<<grid, kMbThreads, 0, s>>>(q4, nq, m4, nm, rowsPerChunk, threshold, indexOffset, best); break;
+    case 12: hamming_best_kernel<12><<<grid, kMbThreads, 0, s>>>(q4, nq, m4, nm, rowsPerChunk, threshold, indexOffset, best); break;
+    default: hamming_best_kernel<6><<<grid, kMbThreads, 0, s>>>(q4, nq, m4, nm, rowsPerChunk, threshold, indexOffset, best); break;
+  }
+  return (int)(grid.x * grid.y);
+}
+
+// ----------------------------------------------------------------------------------------------
+// shared helpers for the small gated matchers: one warp per keypoint, lanes stride over the other side
+// ----------------------------------------------------------------------------------------------
+__device__ __forceinline__ void load_desc(const uint8_t* base, size_t row, unsigned d[kDescWords]) {
+  const uint4* p = reinterpret_cast<const uint4*>(base) + row * 3;
+  const uint4 a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + 2);
+  d[0] = a.x; d[1] = a.y; d[2] = a.z; d[3] = a.w;
+  d[4] = b.x; d[5] = b.y; d[6] = b.z; d[7] = b.w;
+  d[8] = c.x; d[9] = c.y; d[10] = c.z; d[11] = c.w;
+}
+__device__ __forceinline__ unsigned hamming384(const unsigned a[kDescWords], const unsigned b[kDescWords]) {
+  unsigned d = 0;
+#pragma unroll
+  for (int w = 0; w < kDescWords; ++w) d += __popc(a[w] ^ b[w]);
+  return d;
+}
+
+// ----------------------------------------------------------------------------------------------
+// B. 3D-2D map matching with the pixel gate, Frontend::matchToMapByThread (Frontend.cpp:1744-1827)
+// ----------------------------------------------------------------------------------------------
+// One warp per keypoint k. Rows m are visited in ascending order (= landmark-major, descriptor-minor, the
+// reference's iteration order for a fixed k). Every improvement of the running minimum is an "event"; the
+// events (k, m) are appended to a list so that the host adapter can rebuild ctrs[] / reprErrors[] in the
+// reference's accumulation order.
+__global__ void __launch_bounds__(256)
+match_to_map_kernel(const uint8_t* __restrict__ queries, const double* __restrict__ kp_xy,
+                    const uint8_t* __restrict__ use, int nk, const uint8_t* __restrict__ map,
+                    const int* __restrict__ owner, int nm, const double* __restrict__ proj_xy, double threshSq,
+                    double hammingThreshold, double* __restrict__ bestDist, int* __restrict__ bestOwner,
+                    unsigned long long* __restrict__ events, int eventCap, int* __restrict__ eventCount) {
+  const int lane = threadIdx.x & 31;
+  const int k = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (k >= nk) return;
+  double best = hammingThreshold;
+  int bestO = -1;
+  if (use[k]) {
+    unsigned q[kDescWords];
+    load_desc(queries, k, q);
+    const double kx = kp_xy[2 * k], ky = kp_xy[2 * k + 1];
+    for (int base = 0; base < nm; base += 32) {
+      const int m = base + lane;
+      double d = 1e9;
+      int o = -1;
+      if (m < nm) {
+        o = owner[m];
+        const double rx = proj_xy[2 * o] - kx, ry = proj_xy[2 * o + 1] - ky;
+        if (!(rx * rx + ry * ry > threshSq)) {
+          unsigned r[kDescWords];
+          load_desc(map, m, r);
+          d = (double)hamming384(q, r);
+        }
+      }
+      unsigned pending = __ballot_sync(0xffffffffu, d < best);
+      while (pending) {  // rare: replay the candidates of this group in row order
+        const int src = __ffs(pending) - 1;
+        pending &= pending - 1;
+        const double dc = __shfl_sync(0xffffffffu, d, src);
+        const int oc = __shfl_sync(0xffffffffu, o, src);
+        if (dc < best) {
+          best = dc;
+          bestO = oc;
+          if (lane == 0) {
+            const int e = atomicAdd(eventCount, 1);
+            if (e < eventCap) events[e] = ((unsigned long long)(unsigned)(base + src) << 32) | (unsigned)k;
+          }
+        }
+      }
+    }
+  }
+  if (lane == 0) {
+    bestDist[k] = best;
+    bestOwner[k] = bestO;
+  }
+}
+
+void launch_match_to_map(const uint8_t* queries, const double* kp_xy, const uint8_t* use, int nk, const uint8_t* map,
+                         const int* owner, int nm, const double* proj_xy, double threshSq, double hammingThreshold,
+                         double* bestDist, int* bestOwner, unsigned long long* events, int eventCap, int* eventCount,
+                         cudaStream_t s) {
+  if (nk <= 0) return;
+  const int warpsPerBlock = 8;
+  const int blocks = (nk + warpsPerBlock - 1) / warpsPerBlock;
+  match_to_map_kernel<<<blocks, warpsPerBlock * 32, 0, s>>>(queries, kp_xy, use, nk, map, owner, nm, proj_xy, threshSq,
+                                                           hammingThreshold, bestDist, bestOwner, events, eventCap,
+                                                           eventCount);
+}
+
+// ----------------------------------------------------------------------------------------------
+// FP64 geometry shared by the 2D-2D and uninitialised-landmark matchers.
+// Eigen expressions are written out in plain doubles: dot of 3-vectors = (x0*y0 + x1*y1) + x2*y2,
+// normalized() = v / sqrt(v.v) (element-wise division), Matrix2d::computeInverseWithCheck = |det| > 1e-12.
+// ----------------------------------------------------------------------------------------------
+struct V3 { double x, y, z; };
+__device__ __forceinline__ V3 v3(double x, double y, double z) { V3 r; r.x = x; r.y = y; r.z = z; return r; }
+__device__ __forceinline__ V3 operator+(V3 a, V3 b) { return v3(a.x + b.x, a.y + b.y, a.z + b.z); }
+__device__ __forceinline__ V3 operator-(V3 a, V3 b) { return v3(a.x - b.x, a.y - b.y, a.z - b.z); }
+__device__ __forceinline__ V3 operator*(double s, V3 a) { return v3(s * a.x, s * a.y, s * a.z); }
+__device__ __forceinline__ double dot(V3 a, V3 b) { return (a.x * b.x + a.y * b.y) + a.z * b.z; }
+__device__ __forceinline__ V3 cross(V3 a, V3 b) {
+  return v3(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x);
+}
+__device__ __forceinline__ double norm(V3 a) { return sqrt(dot(a, a)); }
+__device__ __forceinline__ V3 normalized(V3 a) {
+  const double z = dot(a, a);
+  if (z > 0.0) {
+    const double n = sqrt(z);
+    return v3(a.x / n, a.y / n, a.z / n);
+  }
+  return a;
+}
+__device__ __forceinline__ V3 matvec(const double* C, V3 v) {  // row-major 3x3
+  return v3((C[0] * v.x + C[1] * v.y) + C[2] * v.z, (C[3] * v.x + C[4] * v.y) + C[5] * v.z,
+            (C[6] * v.x + C[7] * v.y) + C[8] * v.z);
+}
+__device__ __forceinline__ V3 matTvec(const double* C, V3 v) {  // C^T * v
+  return v3((C[0] * v.x + C[3] * v.y) + C[6] * v.z, (C[1] * v.x + C[4] * v.y) + C[7] * v.z,
+            (C[2] * v.x + C[5] * v.y) + C[8] * v.z);
+}
+
+// triangulation::triangulateFast (okvis_frontend/src/stereo_triangulation.cpp:30-111). Returns the
+// (non-normalised) homogeneous point with w = 1.
+__device__ V3 triangulate_fast(V3 p1, V3 e1, V3 p2, V3 e2, double sigma, bool& isValid, bool& isParallel) {
+  isParallel = false;
+  isValid = true;
+  const V3 t12 = p2 - p1;
+  const double b0 = dot(t12, e1), b1 = dot(t12, e2);
+  const double A00 = dot(e1, e1), A10 = dot(e1, e2), A01 = -A10, A11 = -dot(e2, e2);
+  const double det = A00 * A11 - A01 * A10;
+  const bool invertible = fabs(det) > 1.0e-12;
+  double l0 = 0.0, l1 = 0.0;
+  if (invertible) {
+    const double invdet = 1.0 / det;
+    const double i00 = A11 * invdet, i01 = -A01 * invdet, i10 = -A10 * invdet, i11 = A00 * invdet;
+    l0 = i00 * b0 + i01 * b1;
+    l1 = i10 * b0 + i11 * b1;
+  }
+  const double c26 = cos(2.6 * sigma);
+  if (!invertible || l0 < 0.01 || l1 < 0.01) {
+    isParallel = true;
+    const V3 m = p1 + 0.5 * t12;
+    const double tn = norm(t12);
+    const V3 midpoint = m + (40.0 * (0.01 > tn ? 0.01 : tn)) * (e1 + e2);
+    if (dot(e1, normalized(midpoint - p1)) < c26) isValid = false;
+    if (dot(e2, normalized(midpoint - p2)) < c26) isValid = false;
+    return midpoint;
+  }
+  const V3 xm = l0 * e1 + p1;
+  const V3 xn = l1 * e2 + p2;
+  const V3 s = xm + xn;
+  const V3 midpoint = v3(s.x / 2.0, s.y / 2.0, s.z / 2.0);
+  if (dot(e1, normalized(midpoint - p1)) < c26) isValid = false;
+  if (dot(e2, normalized(midpoint - p2)) < c26) isValid = false;
+  if (dot(normalized(midpoint - p2), normalized(midpoint - p1)) > cos(6.0 * sigma)) isParallel = true;
+  return midpoint;
+}
+
+// ----------------------------------------------------------------------------------------------
+// C. 2D-2D stereo matching, Frontend::matchStereo inner loops (Frontend.cpp:2259-2316)
+// ----------------------------------------------------------------------------------------------
+struct StereoDev {
+  const uint8_t* desc;
+  const double* size;
+  const double* e_C;
+  const uint8_t* bp_valid;
+  int n;
+  double C[9];
+  double r[3];
+  double f;
+};
+
+__global__ void __launch_bounds__(256)
+match_stereo_kernel(StereoDev v0, StereoDev v1, double hammingThreshold, double* __restrict__ outDist,
+                    int* __restrict__ outK1, double* __restrict__ outHp, uint8_t* __restrict__ outInit) {
+  const int lane = threadIdx.x & 31;
+  const int k0 = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (k0 >= v0.n) return;
+  unsigned q[kDescWords];
+  load_desc(v0.desc, k0, q);
+  double distances = hammingThreshold;
+  bool initialisable = false;
+  V3 hps = v3(0.0, 0.0, 0.0);
+  int k1_match = 0;
+  const V3 r0 = v3(v0.r[0], v0.r[1], v0.r[2]), r1 = v3(v1.r[0], v1.r[1], v1.r[2]);
+
+  for (int base = 0; base < v1.n; base += 32) {
+    const int k1 = base + lane;
+    double d = 1e9;
+    if (k1 < v1.n) {
+      unsigned r[kDescWords];
+      load_desc(v1.desc, k1, r);
+      d = (double)hamming384(q, r);
+    }
+    unsigned pending = __ballot_sync(0xffffffffu, d < distances);
+    while (pending) {  // sparse: geometry only for candidates below the running best, in k1 order
+      const int src = __ffs(pending) - 1;
+      pending &= pending - 1;
+      const double dc = __shfl_sync(0xffffffffu, d, src);
+      const int kc = base + src;
+      if (!(dc < distances)) continue;
+      if (!v0.bp_valid[k0]) continue;
+      if (!v1.bp_valid[kc]) continue;
+      const double sigma = fmax(v0.size[k0] / v0.f, v1.size[kc] / v1.f) * 0.125;
+      const V3 e0_W = normalized(matvec(v0.C, v3(v0.e_C[3 * k0], v0.e_C[3 * k0 + 1], v0.e_C[3 * k0 + 2])));
+      const V3 e1_W = normalized(matvec(v1.C, v3(v1.e_C[3 * kc], v1.e_C[3 * kc + 1], v1.e_C[3 * kc + 2])));
+      bool isValid = false, isParallel = false;
+      const V3 hp = triangulate_fast(r0, e0_W, r1, e1_W, sigma, isValid, isParallel);
+      // T_WC.inverse() * hp_W with w = 1: C^T * p + (-(C^T * r)) * 1; z / w compared with 0.1
+      const V3 t0 = matTvec(v0.C, r0), t1 = matTvec(v1.C, r1);
+      const V3 c0 = matTvec(v0.C, hp), c1 = matTvec(v1.C, hp);
+      const double z0 = c0.z + (-t0.z) * 1.0, z1 = c1.z + (-t1.z) * 1.0;
+      if (z0 / 1.0 < 0.1) isValid = false;
+      if (z1 / 1.0 < 0.1) isValid = false;
+      if (dot(e0_W, e1_W) < 0.8) isValid = false;
+      if (isValid) {
+        distances = dc;
+        hps = hp;
+        k1_match = kc;
+        initialisable = !isParallel;
+      }
+    }
+  }
+  if (lane == 0) {
+    outDist[k0] = distances;
+    outK1[k0] = k1_match;
+    outHp[4 * k0 + 0] = hps.x / 1.0;
+    outHp[4 * k0 + 1] = hps.y / 1.0;
+    outHp[4 * k0 + 2] = hps.z / 1.0;
+    outHp[4 * k0 + 3] = 1.0;
+    outInit[k0] = initialisable ? 1 : 0;
+  }
+}
+
+void launch_match_stereo(const StereoDev& v0, const StereoDev& v1, double hammingThreshold, double* outDist,
+                         int* outK1, double* outHp, uint8_t* outInit, cudaStream_t s) {
+  if (v0.n <= 0) return;
+  const int warpsPerBlock = 8;
+  const int blocks = (v0.n + warpsPerBlock - 1) / warpsPerBlock;
+  match_stereo_kernel<<<blocks, warpsPerBlock * 32, 0, s>>>(v0, v1, hammingThreshold, outDist, outK1, outHp, outInit);
+}
+
+}  // namespace okc

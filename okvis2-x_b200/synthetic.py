@@ -1,0 +1,169 @@
+"""Seeded synthetic inputs of the shapes BASELINE.json names.
+
+Used by tests/, bench.py and __graft_entry__.smoke(); everything is a pure function of the seed so that the
+CUDA path and the oracle see identical bytes. Camera-awareness maps follow the construction of
+okvis_cv/include/okvis/cameras/implementation/PinholeCamera.hpp:172-200 (rays = normalised back-projection,
+Jacobian = d(project)/d(point) at the ray) for a pinhole + radial-tangential camera; they are an INPUT of the
+path (to both the product and the oracle), not part of it.
+"""
+import numpy as np
+
+# config/euroc/okvis2.yaml:3-33 and its frontend_parameters block
+EUROC = dict(
+    width=752, height=480,
+    cams=[dict(f=(458.654880721, 457.296696463), c=(367.215803962, 248.37534061),
+               d=(-0.28340811217, 0.0739590738929, 0.000193595028569, 1.76187114545e-05),
+               T_SC=[0.0148655429818, -0.999880929698, 0.00414029679422, -0.0216401454975,
+                     0.999557249008, 0.0149672133247, 0.025715529948, -0.064676986768,
+                     -0.0257744366974, 0.00375618835797, 0.999660727178, 0.00981073058949, 0, 0, 0, 1]),
+          dict(f=(457.587426604, 456.13442556), c=(379.99944652, 255.238185386),
+               d=(-0.283683654496, 0.0745128430929, -0.000104738949098, -3.55590700274e-05),
+               T_SC=[0.0125552670891, -0.999755099723, 0.0182237714554, -0.0198435579556,
+                     0.999598781151, 0.0130119051815, 0.0251588363115, 0.0453689425024,
+                     -0.0253898008918, 0.0179005838253, 0.999517347078, 0.00786212447038, 0, 0, 0, 1])],
+    radius=38.0, abs_threshold=150.0, max_kpt=700, octaves=0, matching_threshold=60.0, slices=4)
+D455 = dict(width=848, height=480, radius=30.0, abs_threshold=5.0, max_kpt=2500, octaves=0, matching_threshold=60.0,
+            slices=3)
+HILTI = dict(width=720, height=540, radius=50.0, abs_threshold=20.0, max_kpt=700, octaves=0, matching_threshold=60.0,
+             slices=4)
+
+
+def scene_image(width, height, seed, rects=400, noise=3):
+    """Random grey rectangles on a mid-grey canvas, 3x3 box blur, +-noise uniform noise (config 1 generator)."""
+    rng = np.random.default_rng(seed)
+    img = np.full((height, width), 128.0, np.float32)
+    for _ in range(rects):
+        x0, y0 = int(rng.integers(0, width)), int(rng.integers(0, height))
+        w, h = (int(v) for v in rng.integers(8, 120, 2))
+        img[y0:y0 + h, x0:x0 + w] = float(rng.integers(0, 256))
+    p = np.pad(img, 1, mode="edge")
+    img = sum(p[dy:dy + height, dx:dx + width] for dy in range(3) for dx in range(3)) / 9.0
+    img = img + rng.integers(-noise, noise + 1, (height, width))
+    return np.clip(img, 0, 255).astype(np.uint8)
+
+
+def noise_image(width, height, seed):
+    """i.i.d. uniform u8: the reference's own test input (okvis_cv/test/TestFrame.cpp:62-65), worst case for NMS."""
+    return np.random.default_rng(seed).integers(0, 256, (height, width), dtype=np.uint8)
+
+
+def stereo_pair(width, height, seed, rects=400):
+    """Left image + right image = left shifted by a per-row-band constant integer disparity of 8..40 px."""
+    rng = np.random.default_rng(seed + 1000)
+    wide = scene_image(width + 64, height, seed, rects)
+    left = np.ascontiguousarray(wide[:, 48:48 + width])
+    right = np.empty_like(left)
+    band = 0
+    while band < height:
+        hgt = int(rng.integers(24, 96))
+        disp = int(rng.integers(8, 41))
+        right[band:band + hgt] = wide[band:band + hgt, 48 - disp:48 - disp + width]
+        band += hgt
+    return left, np.ascontiguousarray(right)
+
+
+def _radtan_distort(x, y, d):
+    k1, k2, p1, p2 = d
+    mx2, my2, mxy = x * x, y * y, x * y
+    rho2 = mx2 + my2
+    rad = k1 * rho2 + k2 * rho2 * rho2
+    xd = x + x * rad + 2.0 * p1 * mxy + p2 * (rho2 + 2.0 * mx2)
+    yd = y + y * rad + 2.0 * p2 * mxy + p1 * (rho2 + 2.0 * my2)
+    # Jacobian of the distortion
+    j00 = 1 + rad + k1 * 2.0 * mx2 + k2 * rho2 * 4 * mx2 + 2.0 * p1 * y + 6 * p2 * x
+    j01 = k1 * 2.0 * x * y + k2 * 4 * rho2 * x * y + p1 * 2.0 * x + 2.0 * p2 * y
+    j10 = j01
+    j11 = 1 + rad + k1 * 2.0 * my2 + k2 * rho2 * 4 * my2 + 6 * p1 * y + 2.0 * p2 * x
+    return xd, yd, j00, j01, j10, j11
+
+
+def camera_maps(width, height, f, c, d):
+    """(rays float32 HxWx3, jacobians float32 HxWx6) for a pinhole + radtan camera (Appendix E of SURVEY.md)."""
+    fu, fv = f
+    cu, cv = c
+    u, v = np.meshgrid(np.arange(width, dtype=np.float64), np.arange(height, dtype=np.float64))
+    xd, yd = (u - cu) / fu, (v - cv) / fv
+    x, y = xd.copy(), yd.copy()
+    for _ in range(5):  # Gauss-Newton undistortion
+        xx, yy, j00, j01, j10, j11 = _radtan_distort(x, y, d)
+        ex, ey = xd - xx, yd - yy
+        # solve (J^T J) dx = J^T e
+        a, b, cc = j00 * j00 + j10 * j10, j00 * j01 + j10 * j11, j01 * j01 + j11 * j11
+        gx, gy = j00 * ex + j10 * ey, j01 * ex + j11 * ey
+        det = a * cc - b * b
+        x = x + (cc * gx - b * gy) / det
+        y = y + (-b * gx + a * gy) / det
+    xx, yy, j00, j01, j10, j11 = _radtan_distort(x, y, d)
+    ok = (xd - xx) ** 2 + (yd - yy) ** 2 < 1e-4
+    n = np.sqrt(x * x + y * y + 1.0)
+    rays = np.stack([x / n, y / n, 1.0 / n], -1)
+    rays[~ok] = 0.0
+    # project(ray): point Jacobian (PinholeCamera.hpp impl:336-346) at the normalised ray
+    X, Y, Z = rays[..., 0], rays[..., 1], np.where(ok, rays[..., 2], 1.0)
+    px, py = X / Z, Y / Z
+    _, _, d00, d01, d10, d11 = _radtan_distort(px, py, d)
+    rz, rz2 = 1.0 / Z, 1.0 / (Z * Z)
+    J = np.stack([fu * d00 * rz, fu * d01 * rz, -fu * (X * d00 + Y * d01) * rz2,
+                  fv * d10 * rz, fv * d11 * rz, -fv * (X * d10 + Y * d11) * rz2], -1)
+    J[~ok] = 0.0
+    return np.ascontiguousarray(rays, np.float32), np.ascontiguousarray(J, np.float32)
+
+
+def random_descriptors(n, seed):
+    return np.random.default_rng(seed).integers(0, 256, (n, 48), dtype=np.uint8)
+
+
+def flip_bits(desc, nflips, rng):
+    """Copy of descriptor rows with nflips[i] distinct random bits flipped in row i."""
+    out = desc.copy()
+    for i in range(len(out)):
+        k = int(nflips[i])
+        if k <= 0:
+            continue
+        bits = rng.choice(384, size=k, replace=False)
+        np.bitwise_xor.at(out[i], bits // 8, (1 << (bits % 8)).astype(np.uint8))
+    return out
+
+
+def sweep_inputs(nq, nm, seed=5, planted_frac=0.5, max_flips=80):
+    """Config 5: i.i.d. descriptors; for planted_frac of the queries one map row = query with U{0..max_flips} flips."""
+    rng = np.random.default_rng(seed)
+    q = rng.integers(0, 256, (nq, 48), dtype=np.uint8)
+    m = rng.integers(0, 256, (nm, 48), dtype=np.uint8)
+    planted = rng.random(nq) < planted_frac
+    idx = rng.integers(0, nm, nq)
+    flips = rng.integers(0, max_flips + 1, nq)
+    sel = np.nonzero(planted)[0]
+    m[idx[sel]] = flip_bits(q[sel], flips[sel], rng)
+    return q, m
+
+
+def map_window(desc, kp_xy, num_landmarks, seed, width, height, is3d_frac=0.7):
+    """Config 2: a keyframe-window of landmarks built from frame descriptors.
+
+    Returns dict(map rows [M,48], owner [M] (landmark slot, ascending), proj [L,2], is3d [L]).
+    Landmark l copies descriptor (l mod K) with Binomial(384, 0.05) flips, 1..3 rows each; its projection is the
+    keypoint position + N(0, 5 px) for the first K landmarks and uniform in the image for the rest.
+    """
+    rng = np.random.default_rng(seed)
+    K = len(desc)
+    rows, owner = [], []
+    proj = np.zeros((num_landmarks, 2), np.float64)
+    for l in range(num_landmarks):
+        nd = int(rng.integers(1, 4))
+        if K > 0:
+            src = l % K
+            base = np.repeat(desc[src:src + 1], nd, 0)
+            if l < K:
+                r = flip_bits(base, rng.binomial(384, 0.05, nd), rng)
+                proj[l] = kp_xy[src] + rng.normal(0.0, 5.0, 2)
+            else:
+                r = rng.integers(0, 256, (nd, 48), dtype=np.uint8)
+                proj[l] = rng.random(2) * (width, height)
+        else:
+            r = rng.integers(0, 256, (nd, 48), dtype=np.uint8)
+            proj[l] = rng.random(2) * (width, height)
+        rows.append(r)
+        owner += [l] * nd
+    return dict(map=np.concatenate(rows, 0) if rows else np.zeros((0, 48), np.uint8),
+                owner=np.asarray(owner, np.int32), proj=proj, is3d=rng.random(num_landmarks) < is3d_frac)

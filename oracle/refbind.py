@@ -1,0 +1,245 @@
+"""TEST INFRASTRUCTURE ONLY. ctypes bindings of the oracle libraries.
+
+  oracle/_ref/libbrisk_ref.so  - the reference's own external/brisk sources (see oracle/Makefile, ref_capi.cc)
+  oracle/liboracle_port.so     - our CPU restatement of the matchers / geometry (oracle/port/*.cc)
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may import this.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+REF_PATH = os.path.join(_HERE, "_ref", "libbrisk_ref.so")
+PORT_PATH = os.path.join(_HERE, "liboracle_port.so")
+
+KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"), ("response", "<f4"),
+                     ("octave", "<i4"), ("class_id", "<i4")])
+PWS_DTYPE = np.dtype([("score", "<i4"), ("x", "<u2"), ("y", "<u2")])
+assert KP_DTYPE.itemsize == 28 and PWS_DTYPE.itemsize == 8
+
+_vp, _i, _d, _u64, _f = C.c_void_p, C.c_int, C.c_double, C.c_uint64, C.c_float
+
+
+def _ptr(a):
+    return C.c_void_p(a.ctypes.data)
+
+
+def aligned(shape, dtype, align=64):
+    """numpy array whose data pointer is `align`-byte aligned (brisk::Hamming dereferences __m128i*)."""
+    dtype = np.dtype(dtype)
+    n = int(np.prod(shape)) * dtype.itemsize
+    raw = np.zeros(n + align, np.uint8)
+    off = (-raw.ctypes.data) % align
+    return raw[off:off + n].view(dtype).reshape(shape)
+
+
+class Ref:
+    """The compiled reference (brisk) behind C entry points."""
+
+    def __init__(self):
+        if not os.path.exists(REF_PATH):
+            raise FileNotFoundError(REF_PATH + " missing: run `make -C oracle` where /root/reference exists")
+        L = self.L = C.CDLL(REF_PATH)
+        L.ref_harris.argtypes = [_vp, _i, _i, _vp]
+        L.ref_maxima.argtypes = [_vp, _i, _i, _i, _vp, _i]
+        L.ref_uniformity.argtypes = [_vp, _i, _d, _i, _i, _u64]
+        L.ref_lut.argtypes = [_vp]
+        L.ref_detect.argtypes = [_vp, _i, _i, _d, _u64, _d, _u64, _vp, _i]
+        L.ref_extractor_create.argtypes = [_i, _i]
+        L.ref_extractor_create.restype = _vp
+        L.ref_extractor_destroy.argtypes = [_vp]
+        L.ref_extractor_set_camera.argtypes = [_vp, _vp, _vp, _i, _i, _f]
+        L.ref_extractor_set_direction.argtypes = [_vp, _vp]
+        L.ref_describe.argtypes = [_vp, _vp, _i, _i, _vp, _i, _vp]
+        L.ref_integral.argtypes = [_vp, _i, _i, _vp]
+        L.ref_pattern_points.argtypes = [_vp, _i, _vp]
+        L.ref_pattern_meta.argtypes = [_vp, _vp, _vp, _vp, _vp, _i]
+        L.ref_hamming.argtypes = [_vp, _vp, _i]
+        L.ref_hamming.restype = C.c_uint32
+        L.ref_hamming_best.argtypes = [_vp, _i, _vp, _i, C.c_uint32, _vp]
+
+    @staticmethod
+    def _img(img):
+        img = np.ascontiguousarray(img, np.uint8)
+        assert img.ndim == 2
+        return img
+
+    def harris(self, img):
+        img = self._img(img)
+        out = np.zeros(img.shape, np.int32)
+        self.L.ref_harris(_ptr(img), img.shape[0], img.shape[1], _ptr(out))
+        return out
+
+    def maxima(self, img, abs_threshold, cap=1 << 20):
+        img = self._img(img)
+        out = np.zeros(cap, PWS_DTYPE)
+        n = self.L.ref_maxima(_ptr(img), img.shape[0], img.shape[1], int(abs_threshold), _ptr(out), cap)
+        assert n <= cap
+        return out[:n].copy()
+
+    def uniformity(self, points, radius, rows, cols, max_kpt):
+        pts = np.ascontiguousarray(points, PWS_DTYPE).copy()
+        n = self.L.ref_uniformity(_ptr(pts), len(pts), float(radius), rows, cols, int(max_kpt))
+        return pts[:n].copy()
+
+    def lut(self):
+        out = np.zeros((31, 31), np.float32)
+        self.L.ref_lut(_ptr(out))
+        return out
+
+    def detect(self, img, radius, octaves, abs_threshold, max_kpt, cap=1 << 17):
+        img = self._img(img)
+        out = np.zeros(cap, KP_DTYPE)
+        n = self.L.ref_detect(_ptr(img), img.shape[0], img.shape[1], float(radius), int(octaves), float(abs_threshold),
+                              int(max_kpt), _ptr(out), cap)
+        if n < 0:
+            raise RuntimeError("reference detector threw")
+        assert n <= cap
+        return out[:n].copy()
+
+    def integral(self, img):
+        img = self._img(img)
+        out = np.zeros((img.shape[0] + 1, img.shape[1] + 1), np.int32)
+        self.L.ref_integral(_ptr(img), img.shape[0], img.shape[1], _ptr(out))
+        return out
+
+    def hamming(self, a, b):
+        aa, bb = aligned(48, np.uint8), aligned(48, np.uint8)
+        aa[:] = a
+        bb[:] = b
+        return int(self.L.ref_hamming(_ptr(aa), _ptr(bb), 3))
+
+    def hamming_best(self, queries, mp, threshold):
+        q = aligned(queries.shape, np.uint8)
+        m = aligned(mp.shape, np.uint8)
+        q[:] = queries
+        m[:] = mp
+        best = np.zeros(len(q), np.uint64)
+        self.L.ref_hamming_best(_ptr(q), len(q), _ptr(m), len(m), int(threshold), _ptr(best))
+        return best
+
+
+class RefExtractor:
+    """brisk::BriskDescriptorExtractor(rotationInvariant, scaleInvariant) of the compiled reference."""
+
+    def __init__(self, ref, rotation_invariant=True, scale_invariant=False):
+        self.ref = ref
+        self.h = C.c_void_p(ref.L.ref_extractor_create(int(rotation_invariant), int(scale_invariant)))
+
+    def close(self):
+        if self.h:
+            self.ref.L.ref_extractor_destroy(self.h)
+            self.h = None
+
+    def set_camera(self, rays, jacobians, focal):
+        rays = np.ascontiguousarray(rays, np.float32)
+        jacobians = np.ascontiguousarray(jacobians, np.float32)
+        rows, cols = rays.shape[:2]
+        assert rays.shape == (rows, cols, 3) and jacobians.shape == (rows, cols, 6)
+        self.ref.L.ref_extractor_set_camera(self.h, _ptr(rays), _ptr(jacobians), rows, cols, float(focal))
+
+    def set_direction(self, d):
+        d = np.ascontiguousarray(d, np.float32)
+        self.ref.L.ref_extractor_set_direction(self.h, _ptr(d))
+
+    def describe(self, img, keypoints):
+        img = Ref._img(img)
+        kp = np.ascontiguousarray(keypoints, KP_DTYPE).copy()
+        desc = aligned((max(len(kp), 1), 48), np.uint8)
+        n = self.ref.L.ref_describe(self.h, _ptr(img), img.shape[0], img.shape[1], _ptr(kp), len(kp), _ptr(desc))
+        if n < 0:
+            raise RuntimeError("reference extractor threw")
+        return kp[:n].copy(), desc[:n].copy()
+
+    def pattern(self, scale):
+        out = np.zeros((1024, 66, 3), np.float32)
+        self.ref.L.ref_pattern_points(self.h, int(scale), _ptr(out))
+        return out
+
+    def meta(self):
+        sl = np.zeros(64, np.float32)
+        sz = np.zeros(64, np.uint32)
+        sp = np.zeros((384, 2), np.uint32)
+        lp = np.zeros((856, 4), np.int32)
+        n = self.ref.L.ref_pattern_meta(self.h, _ptr(sl), _ptr(sz), _ptr(sp), _ptr(lp), 856)
+        assert n == 856
+        return sl, sz, sp, lp
+
+
+class PortStereoView(C.Structure):
+    _fields_ = [("desc", C.c_void_p), ("size", C.c_void_p), ("e_C", C.c_void_p), ("bp_valid", C.c_void_p),
+                ("n", C.c_int), ("C", C.c_double * 9), ("r", C.c_double * 3), ("f", C.c_double)]
+
+
+class Port:
+    """Our CPU restatement of the Frontend.cpp matchers (oracle/port/matchers.cc)."""
+
+    def __init__(self):
+        if not os.path.exists(PORT_PATH):
+            raise FileNotFoundError(PORT_PATH + " missing: run `make -C oracle port`")
+        L = self.L = C.CDLL(PORT_PATH)
+        L.port_hamming.argtypes = [_vp, _vp]
+        L.port_hamming.restype = C.c_uint32
+        L.port_hamming_best.argtypes = [_vp, _i, _vp, C.c_int64, C.c_uint32, _u64, _vp, _i]
+        L.port_match_to_map_thread.argtypes = [_i, _i, _vp, _vp, _vp, _i, _vp, _vp, _i, _vp, _vp, _d, _vp, _vp, _vp,
+                                               _vp]
+        L.port_match_stereo.argtypes = [C.POINTER(PortStereoView), C.POINTER(PortStereoView), _d, _vp, _vp, _vp, _vp]
+
+    def hamming_best(self, queries, mp, threshold, index_offset=0, nthreads=1):
+        q = np.ascontiguousarray(queries, np.uint8).reshape(-1, 48)
+        m = np.ascontiguousarray(mp, np.uint8).reshape(-1, 48)
+        best = np.zeros(len(q), np.uint64)
+        self.L.port_hamming_best(_ptr(q), len(q), _ptr(m), len(m), int(threshold), int(index_offset), _ptr(best),
+                                 int(nthreads))
+        return best
+
+    def match_to_map(self, queries, kp_xy, use, mp, owner, proj_xy, is3d, thresh_sq, threshold, num_slices):
+        """All thread slices of matchToMapByThread, run one after another (they touch disjoint k)."""
+        q = np.ascontiguousarray(queries, np.uint8).reshape(-1, 48)
+        kp = np.ascontiguousarray(kp_xy, np.float64).reshape(-1, 2)
+        us = np.ascontiguousarray(use, np.uint8)
+        m = np.ascontiguousarray(mp, np.uint8).reshape(-1, 48)
+        pr = np.ascontiguousarray(proj_xy, np.float64).reshape(-1, 2)
+        L = len(pr)
+        owner = np.asarray(owner, np.int64)
+        assert np.all(np.diff(owner) >= 0)
+        row_start = np.searchsorted(owner, np.arange(L + 1)).astype(np.int32)
+        i3 = np.ascontiguousarray(is3d, np.uint8) if is3d is not None else None
+        nk = len(q)
+        dist = np.full(nk, float(threshold), np.float64)
+        ids = np.full(nk, -1, np.int32)
+        ctrs = np.zeros(num_slices, np.uint64)
+        errs = np.zeros(num_slices, np.float64)
+        for t in range(num_slices):
+            self.L.port_match_to_map_thread(t, num_slices, _ptr(q), _ptr(kp), _ptr(us), nk, _ptr(m), _ptr(row_start), L,
+                                            _ptr(pr), _ptr(i3) if i3 is not None else None, float(thresh_sq),
+                                            _ptr(dist), _ptr(ids), _ptr(ctrs), _ptr(errs))
+        return dist, ids, ctrs, errs
+
+    def match_stereo(self, view0, view1, threshold):
+        keep = []
+
+        def mk(v):
+            s = PortStereoView()
+            desc = np.ascontiguousarray(v["desc"], np.uint8).reshape(-1, 48)
+            size = np.ascontiguousarray(v["size"], np.float64)
+            e_C = np.ascontiguousarray(v["e_C"], np.float64).reshape(-1, 3)
+            bpv = np.ascontiguousarray(v["bp_valid"], np.uint8)
+            keep.extend([desc, size, e_C, bpv])
+            s.desc, s.size, s.e_C, s.bp_valid = desc.ctypes.data, size.ctypes.data, e_C.ctypes.data, bpv.ctypes.data
+            s.n = len(desc)
+            s.C[:] = list(np.asarray(v["C_WC"], np.float64).reshape(9))
+            s.r[:] = list(np.asarray(v["r_WC"], np.float64).reshape(3))
+            s.f = float(v["f"])
+            return s
+
+        s0, s1 = mk(view0), mk(view1)
+        n0 = s0.n
+        dist = np.empty(n0, np.float64)
+        k1 = np.empty(n0, np.int32)
+        hp = np.empty((n0, 4), np.float64)
+        init = np.empty(n0, np.uint8)
+        self.L.port_match_stereo(C.byref(s0), C.byref(s1), float(threshold), _ptr(dist), _ptr(k1), _ptr(hp), _ptr(init))
+        return dist, k1, hp, init
