@@ -127,7 +127,14 @@ __device__ __forceinline__ int smoothed_intensity(const uint8_t* __restrict__ im
   }
   row += W;
   for (int c = 1; c <= dx; ++c) bottom += (int)row[c];
-  ret += D * (int)row[0] + C * (int)row[dx + 1];
+  if (dx + dy > 2) {
+    // Reference quirk kept on purpose: on the integral-image path the two lower corner pixels are fetched with
+    // "ptr += dy * imagecols + 1" (:459), i.e. from row y_top + dy and one column to the right.
+    const uint8_t* q = img + x_left + (size_t)y_top * W + (dx + 1) + (size_t)dy * W + 1;
+    ret += C * (int)q[0] + D * (int)q[-(dx + 1)];
+  } else {
+    ret += D * (int)row[0] + C * (int)row[dx + 1];
+  }
   ret += top * r_y_1_i + middle * scaling + left * r_x_1_i + right * r_x1_i + bottom * r_y1_i;
   return ret / scaling2;
 }

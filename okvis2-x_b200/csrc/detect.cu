@@ -385,7 +385,9 @@ void launch_select_keypoints(const int32_t* scores, uint64_t* cand, int* counter
     int dev = 0, maxOptin = 0;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&maxOptin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
-    g_select_smem = maxOptin - 8192;  // leave room for the static arrays
+    cudaFuncAttributes fa;
+    cudaFuncGetAttributes(&fa, select_keypoints_kernel);
+    g_select_smem = (maxOptin - (int)fa.sharedSizeBytes - 1024) & ~15;  // dynamic part beside the static arrays
     cudaFuncSetAttribute(select_keypoints_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, g_select_smem);
   }
   select_keypoints_kernel<<<1, kSelThreads, g_select_smem, s>>>(scores, cand, counters, occ_global, lut, out, a.width,
