@@ -10,6 +10,7 @@
 // the way okvis::Frontend does (okvis_frontend/src/Frontend.cpp:2637-2656) and
 // copies their results into plain buffers. Used by tests/ and bench.py's
 // cpu_baseline / --impl reference legs only.
+#include <algorithm>
 #include <cstdint>
 #include <cstring>
 #include <stdexcept>
@@ -196,6 +197,41 @@ void ref_hamming_best(const uint8_t* queries, int nq, const uint8_t* map, int nm
     }
     best[q] = bi == 0xffffffffu ? ~0ull : (static_cast<uint64_t>(bd) << 32) | bi;
   }
+}
+
+// The three OpenCV-defined pieces of arithmetic on the extractor path live in the cv shim (OpenCV's C++ sources
+// are neither in /root/reference nor in this image). These entry points expose the shim's versions so that
+// tests/test_oracle_pins.py can pin them against goldens produced by the Python cv2 4.13 wheel
+// (tests/golden/make_golden.py): cv::eigen (brisk-descriptor-extractor.cc:716-719), the 2x3 * 3x2 Mat product
+// (:712) and cv::normalize(Vec3f) (:689-690).
+void shim_eigen2x2(const float* a /*4, row-major*/, float* ev /*2*/) {
+  cv::Mat m(2, 2, CV_32FC1);
+  std::memcpy(m.data, a, 4 * sizeof(float));
+  cv::Vec2f e;
+  cv::eigen(m, e);
+  ev[0] = e[0];
+  ev[1] = e[1];
+}
+void shim_gemm_2x3_3x2(const float* a /*6*/, const float* b /*6*/, float* out /*4*/) {
+  cv::Mat A(2, 3, CV_32FC1), B(3, 2, CV_32FC1);
+  std::memcpy(A.data, a, 6 * sizeof(float));
+  std::memcpy(B.data, b, 6 * sizeof(float));
+  cv::Mat d = A * B;
+  std::memcpy(out, d.data, 4 * sizeof(float));
+}
+void shim_normalize3(const float* v, float* out) {
+  cv::Vec3f r = cv::normalize(cv::Vec3f(v[0], v[1], v[2]));
+  out[0] = r[0];
+  out[1] = r[1];
+  out[2] = r[2];
+}
+
+// std::sort exactly as EnforceKeyPointUniformity calls it (uniformity-enforcement-inl.h:67): the reference's own
+// PointWithScore::operator< (score-calculator.h:94-96) under this toolchain's libstdc++ introsort. The order of
+// equal scores is what the device emulation has to reproduce.
+void ref_std_sort(void* inout, int n) {
+  Pws* p = static_cast<Pws*>(inout);
+  std::sort(p, p + n);
 }
 
 }  // extern "C"

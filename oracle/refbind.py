@@ -59,6 +59,30 @@ class Ref:
         L.ref_hamming.argtypes = [_vp, _vp, _i]
         L.ref_hamming.restype = C.c_uint32
         L.ref_hamming_best.argtypes = [_vp, _i, _vp, _i, C.c_uint32, _vp]
+        L.ref_std_sort.argtypes = [_vp, _i]
+        L.shim_eigen2x2.argtypes = [_vp, _vp]
+        L.shim_gemm_2x3_3x2.argtypes = [_vp, _vp, _vp]
+        L.shim_normalize3.argtypes = [_vp, _vp]
+
+    # the cv shim's restatement of OpenCV arithmetic (pinned against cv2 goldens in tests/test_oracle_pins.py)
+    def shim_eigen2x2(self, a):
+        a = np.ascontiguousarray(a, np.float32).reshape(4)
+        out = np.zeros(2, np.float32)
+        self.L.shim_eigen2x2(_ptr(a), _ptr(out))
+        return out
+
+    def shim_gemm(self, a, b):
+        a = np.ascontiguousarray(a, np.float32).reshape(6)
+        b = np.ascontiguousarray(b, np.float32).reshape(6)
+        out = np.zeros(4, np.float32)
+        self.L.shim_gemm_2x3_3x2(_ptr(a), _ptr(b), _ptr(out))
+        return out.reshape(2, 2)
+
+    def shim_normalize3(self, v):
+        v = np.ascontiguousarray(v, np.float32).reshape(3)
+        out = np.zeros(3, np.float32)
+        self.L.shim_normalize3(_ptr(v), _ptr(out))
+        return out
 
     @staticmethod
     def _img(img):
@@ -83,6 +107,12 @@ class Ref:
         pts = np.ascontiguousarray(points, PWS_DTYPE).copy()
         n = self.L.ref_uniformity(_ptr(pts), len(pts), float(radius), rows, cols, int(max_kpt))
         return pts[:n].copy()
+
+    def std_sort(self, points):
+        """std::sort of PointWithScore (the reference's operator<, libstdc++ introsort) - tie order included."""
+        pts = np.ascontiguousarray(points, PWS_DTYPE).copy()
+        self.L.ref_std_sort(_ptr(pts), len(pts))
+        return pts
 
     def lut(self):
         out = np.zeros((31, 31), np.float32)
