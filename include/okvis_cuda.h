@@ -167,6 +167,41 @@ int okc_match_to_map_uninitialised(okc_context* ctx, const uint8_t* queries, con
                                    int num_slices, double* best_dist, int32_t* best_owner, double* hps_W,
                                    uint8_t* hps_written, uint64_t* ctrs);
 
+/* ---- Frame pipeline: the per-frame sequence of Frontend::detectAndDescribe followed by Frontend::matchToMap
+ * (ThreadedSlam.cpp:676-717 -> Frontend.cpp:204-262, 1335-1536) with every intermediate product left in HBM.
+ * The queries of the map match are the camera handle's own descriptors/keypoints of the frame just described,
+ * every keypoint is "unassociated" (a fresh frame has no landmark ids yet), and only the match result crosses
+ * the bus. One stream per camera, as one std::thread per camera in the reference. ---- */
+
+/* Same as okc_detect_describe_enqueue but the image is already in device memory (u8[H*W], stride == width). */
+int okc_detect_describe_enqueue_device(okc_camera* cam, const void* image_device, const okc_detect_params* dp,
+                                       const okc_describe_params* xp);
+
+/* The descriptor pool of the landmarks to match (Frontend.cpp:1365-1411): rows map[nm*48] in landmark-major order
+ * (std::map order), map_owner[m] = landmark slot of row m, ascending. Uploaded once, reused for every frame while
+ * the keyframe window does not change. */
+typedef struct okc_map_window okc_map_window;
+int okc_map_window_create(okc_context* ctx, const uint8_t* map, const int32_t* map_owner, int nm, int num_landmarks,
+                          okc_map_window** win);
+int okc_map_window_destroy(okc_map_window* win);
+
+/* Frontend::matchToMapByThread (Frontend.cpp:1744-1827) of the frame last enqueued on `cam` against `win`, on the
+ * camera's stream. proj_xy: double[2*num_landmarks] landmark projections for this frame's pose, in host memory
+ * (proj_on_device == 0; copied) or already in device memory (proj_on_device != 0). */
+int okc_camera_match_to_map_enqueue(okc_camera* cam, const okc_map_window* win, const double* proj_xy,
+                                    int proj_on_device, double thresh_sq, double hamming_threshold);
+/* Waits for the camera's stream, then returns what okc_detect_describe_finish and okc_match_to_map return. */
+int okc_camera_frame_finish(okc_camera* cam, const okc_map_window* win, int num_slices, okc_keypoint* keypoints,
+                            int capacity, int* n, uint8_t* descriptors, double* best_dist, int32_t* best_owner,
+                            uint64_t* ctrs, double* repr_errors);
+
+/* Measurement hooks: the camera's cudaStream_t (to bracket enqueued work with CUDA events from a harness), and
+ * per-kernel device times of the last frame enqueued while timing was enabled (CUDA events around every launch on
+ * the camera's stream). names: '\n'-separated kernel labels. */
+void* okc_camera_stream(okc_camera* cam);
+int okc_debug_kernel_timing(okc_camera* cam, int enable);
+int okc_debug_kernel_times(okc_camera* cam, char* names, int names_cap, float* ms, int cap, int* n);
+
 #ifdef __cplusplus
 }
 #endif

@@ -29,6 +29,9 @@ EXPORTS = [
     "okc_detect_describe_enqueue", "okc_detect_describe_finish", "okc_debug_scores", "okc_debug_candidates",
     "okc_match_batched", "okc_descriptor_set_create", "okc_descriptor_set_destroy", "okc_match_sets",
     "okc_match_to_map", "okc_match_stereo", "okc_match_to_map_uninitialised",
+    "okc_detect_describe_enqueue_device", "okc_map_window_create", "okc_map_window_destroy",
+    "okc_camera_match_to_map_enqueue", "okc_camera_frame_finish", "okc_camera_stream", "okc_debug_kernel_timing",
+    "okc_debug_kernel_times",
 ]
 
 
@@ -84,6 +87,15 @@ def lib():
         L.okc_match_sets.argtypes = [vp, vp, vp, u32, u64, vp, vp, vp]
         L.okc_match_to_map.argtypes = [vp, vp, vp, vp, i, vp, vp, i, vp, i, d, d, i, vp, vp, vp, vp]
         L.okc_match_stereo.argtypes = [vp, C.POINTER(StereoView), C.POINTER(StereoView), d, vp, vp, vp, vp]
+        L.okc_detect_describe_enqueue_device.argtypes = [vp, vp, C.POINTER(DetectParams), C.POINTER(DescribeParams)]
+        L.okc_map_window_create.argtypes = [vp, vp, vp, i, i, C.POINTER(vp)]
+        L.okc_map_window_destroy.argtypes = [vp]
+        L.okc_camera_match_to_map_enqueue.argtypes = [vp, vp, vp, i, d, d]
+        L.okc_camera_frame_finish.argtypes = [vp, vp, i, vp, i, C.POINTER(i), vp, vp, vp, vp, vp]
+        L.okc_camera_stream.argtypes = [vp]
+        L.okc_camera_stream.restype = vp
+        L.okc_debug_kernel_timing.argtypes = [vp, i]
+        L.okc_debug_kernel_times.argtypes = [vp, vp, i, vp, i, C.POINTER(i)]
         _lib = L
     return _lib
 
@@ -198,6 +210,24 @@ class DescriptorSet:
             self.h = C.c_void_p()
 
 
+class MapWindow:
+    """Descriptor pool of the landmarks to match (Frontend.cpp:1365-1411), resident on the device."""
+
+    def __init__(self, ctx, rows, owner, num_landmarks):
+        r = np.ascontiguousarray(rows, np.uint8).reshape(-1, 48)
+        o = np.ascontiguousarray(owner, np.int32)
+        assert len(r) == len(o)
+        self.nm, self.num_landmarks = len(r), int(num_landmarks)
+        self.h = C.c_void_p()
+        _check(lib().okc_map_window_create(ctx.h, _p(r), _p(o), self.nm, self.num_landmarks, C.byref(self.h)),
+               "okc_map_window_create")
+
+    def close(self):
+        if self.h:
+            lib().okc_map_window_destroy(self.h)
+            self.h = C.c_void_p()
+
+
 class Camera:
     """One camera of a MultiFrame: owns a stream, device scratch and (optionally) the camera-awareness maps."""
 
@@ -274,6 +304,52 @@ class Camera:
         _check(lib().okc_detect_describe_finish(self.h, _p(kp), self.max_kp, C.byref(n), _p(desc)),
                "okc_detect_describe_finish")
         return kp[:n.value].copy(), desc[:n.value].copy()
+
+    # -- frame pipeline: detect -> describe -> matchToMap with everything resident in HBM --
+    def enqueue_device(self, image_ptr, radius, octaves, abs_threshold, max_kpt, rotation_invariant=True,
+                       scale_invariant=False, direction=(0.0, 1.0, 0.0)):
+        """image_ptr: device address of a u8[H*W] image (e.g. torch_tensor.data_ptr())."""
+        dp = self._dp(radius, octaves, abs_threshold, max_kpt)
+        xp = self._xp(rotation_invariant, scale_invariant, direction)
+        _check(lib().okc_detect_describe_enqueue_device(self.h, C.c_void_p(image_ptr), C.byref(dp), C.byref(xp)),
+               "okc_detect_describe_enqueue_device")
+
+    def match_to_map_enqueue(self, window, proj_xy, thresh_sq, hamming_threshold=60.0, proj_device_ptr=None):
+        if proj_device_ptr is not None:
+            _check(lib().okc_camera_match_to_map_enqueue(self.h, window.h, C.c_void_p(proj_device_ptr), 1,
+                                                         float(thresh_sq), float(hamming_threshold)),
+                   "okc_camera_match_to_map_enqueue")
+            return
+        pr = np.ascontiguousarray(proj_xy, np.float64).reshape(-1, 2)
+        assert len(pr) == window.num_landmarks
+        _check(lib().okc_camera_match_to_map_enqueue(self.h, window.h, _p(pr), 0, float(thresh_sq),
+                                                     float(hamming_threshold)), "okc_camera_match_to_map_enqueue")
+
+    def frame_finish(self, window, num_slices=4):
+        kp = np.zeros(self.max_kp, KP_DTYPE)
+        desc = np.zeros((self.max_kp, 48), np.uint8)
+        n = C.c_int(0)
+        bd = np.empty(self.max_kp, np.float64)
+        bo = np.empty(self.max_kp, np.int32)
+        ctrs = np.zeros(num_slices, np.uint64)
+        errs = np.zeros(num_slices, np.float64)
+        _check(lib().okc_camera_frame_finish(self.h, window.h, int(num_slices), _p(kp), self.max_kp, C.byref(n),
+                                             _p(desc), _p(bd), _p(bo), _p(ctrs), _p(errs)), "okc_camera_frame_finish")
+        k = n.value
+        return kp[:k].copy(), desc[:k].copy(), bd[:k].copy(), bo[:k].copy(), ctrs, errs
+
+    def stream(self):
+        return lib().okc_camera_stream(self.h)
+
+    def kernel_timing(self, enable):
+        _check(lib().okc_debug_kernel_timing(self.h, int(bool(enable))), "okc_debug_kernel_timing")
+
+    def kernel_times(self):
+        names = C.create_string_buffer(512)
+        ms = np.zeros(16, np.float32)
+        n = C.c_int(0)
+        _check(lib().okc_debug_kernel_times(self.h, names, 512, _p(ms), 16, C.byref(n)), "okc_debug_kernel_times")
+        return list(zip(names.value.decode().split("\n"), [float(v) for v in ms[:n.value]])) if n.value else []
 
     def debug_scores(self, image):
         img = self._img(image)

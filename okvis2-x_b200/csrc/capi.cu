@@ -81,6 +81,32 @@ struct okc_camera {
   uint8_t* h_desc = nullptr;
   int* h_counters = nullptr;
   bool pending = false;
+  // frame pipeline (capi_frame.inc): map-match outputs of the frame in flight
+  double* d_proj = nullptr;       // 2 * proj_cap doubles
+  double* h_proj = nullptr;       // pinned copy (the event replay needs the projections on the host)
+  int proj_cap = 0;
+  uint8_t* d_match = nullptr;     // [best_dist | best_owner | events | count] block
+  uint8_t* h_match = nullptr;
+  size_t match_bytes = 0;
+  int event_cap = 0;
+  int match_landmarks = -1;       // >= 0: a map match is in flight for that many landmarks
+  bool proj_dirty_host = false;   // projections were given as a device pointer: fetch them at finish
+  // per-kernel timing (okc_debug_kernel_timing)
+  static constexpr int kMaxMarks = 10;
+  bool timing = false;
+  cudaEvent_t ev[kMaxMarks + 1] = {};
+  const char* ev_name[kMaxMarks] = {};
+  int n_marks = 0;
+  void timing_begin() {
+    if (!timing) return;
+    n_marks = 0;
+    cudaEventRecord(ev[0], stream);
+  }
+  void mark(const char* name) {  // call right after the launch of kernel `name`
+    if (!timing || n_marks >= kMaxMarks) return;
+    ev_name[n_marks] = name;
+    cudaEventRecord(ev[++n_marks], stream);
+  }
 };
 
 struct okc_descriptor_set {
@@ -227,6 +253,12 @@ int okc_camera_destroy(okc_camera* c) {
   cudaFreeHost(c->h_kp);
   cudaFreeHost(c->h_desc);
   cudaFreeHost(c->h_counters);
+  cudaFree(c->d_proj);
+  cudaFreeHost(c->h_proj);
+  cudaFree(c->d_match);
+  cudaFreeHost(c->h_match);
+  for (auto& e : c->ev)
+    if (e) cudaEventDestroy(e);
   cudaStreamDestroy(c->stream);
   delete c;
   return OKC_OK;
@@ -278,17 +310,20 @@ static int upload_image(okc_camera* cam, const uint8_t* image) {
   return OKC_OK;
 }
 
-static int enqueue_detect(okc_camera* cam, const DetectArgs& a) {
+static int enqueue_detect(okc_camera* cam, const uint8_t* image, const DetectArgs& a) {
   OKC_CUDA_TRY(cudaMemsetAsync(cam->s.counters, 0, 8 * sizeof(int), cam->stream));
-  launch_harris_nms(cam->s.image, cam->s.scores, cam->s.cand, cam->s.counters, a, cam->stream);
+  cam->timing_begin();
+  launch_harris_nms(image, cam->s.scores, cam->s.cand, cam->s.counters, a, cam->stream);
+  cam->mark("harris_nms");
   launch_select_keypoints(cam->s.scores, cam->s.cand, cam->s.counters, cam->s.occupancy, cam->ctx->tables.lut,
                           cam->s.kp_detect, a, cam->stream);
+  cam->mark("select_keypoints");
   OKC_CUDA_TRY(cudaGetLastError());
   return OKC_OK;
 }
 
-static int enqueue_describe(okc_camera* cam, const okc_describe_params* p, const okc_keypoint* kp_in_dev,
-                            const int* n_in_dev) {
+static int enqueue_describe(okc_camera* cam, const uint8_t* image, const okc_describe_params* p,
+                            const okc_keypoint* kp_in_dev, const int* n_in_dev) {
   if (p->scale_invariant) {
     set_error("scale_invariant extraction is not implemented: OKVIS2-X constructs the extractor with false");
     return OKC_ERR_INVALID;
@@ -302,8 +337,9 @@ static int enqueue_describe(okc_camera* cam, const okc_describe_params* p, const
   d.dir[1] = p->extraction_direction[1];
   d.dir[2] = p->extraction_direction[2];
   d.inv_f = 1.0f / cam->focal;
-  launch_describe(cam->s.image, kp_in_dev, n_in_dev, cam->s.kp_desc, cam->s.desc, cam->s.counters, cam->rays, cam->jac,
+  launch_describe(image, kp_in_dev, n_in_dev, cam->s.kp_desc, cam->s.desc, cam->s.counters, cam->rays, cam->jac,
                   cam->ctx->tables, d, cam->max_kp, cam->stream);
+  cam->mark("border_filter+describe");
   OKC_CUDA_TRY(cudaGetLastError());
   return OKC_OK;
 }
@@ -331,7 +367,7 @@ int okc_detect(okc_camera* cam, const uint8_t* image, const okc_detect_params* p
   OKC_CUDA_TRY(cudaSetDevice(cam->ctx->device));
   if ((rc = ensure_occupancy(cam, a))) return rc;
   if ((rc = upload_image(cam, image))) return rc;
-  if ((rc = enqueue_detect(cam, a))) return rc;
+  if ((rc = enqueue_detect(cam, cam->s.image, a))) return rc;
   OKC_CUDA_TRY(cudaMemcpyAsync(cam->h_counters, cam->s.counters, 8 * sizeof(int), cudaMemcpyDeviceToHost, cam->stream));
   OKC_CUDA_TRY(cudaMemcpyAsync(cam->h_kp, cam->s.kp_detect, (size_t)cam->max_kp * sizeof(okc_keypoint),
                                cudaMemcpyDeviceToHost, cam->stream));
@@ -364,7 +400,8 @@ int okc_describe(okc_camera* cam, const uint8_t* image, const okc_describe_param
                                cam->stream));
   OKC_CUDA_TRY(cudaMemcpyAsync(cam->s.kp_detect, cam->h_kp, (size_t)*n * sizeof(okc_keypoint), cudaMemcpyHostToDevice,
                                cam->stream));
-  if ((rc = enqueue_describe(cam, p, cam->s.kp_detect, cam->s.counters + 1))) return rc;
+  cam->timing_begin();
+  if ((rc = enqueue_describe(cam, cam->s.image, p, cam->s.kp_detect, cam->s.counters + 1))) return rc;
   return okc_detect_describe_finish(cam, keypoints, *n, n, descriptors);
 }
 
@@ -377,8 +414,8 @@ int okc_detect_describe_enqueue(okc_camera* cam, const uint8_t* image, const okc
   OKC_CUDA_TRY(cudaSetDevice(cam->ctx->device));
   if ((rc = ensure_occupancy(cam, a))) return rc;
   if ((rc = upload_image(cam, image))) return rc;
-  if ((rc = enqueue_detect(cam, a))) return rc;
-  if ((rc = enqueue_describe(cam, xp, cam->s.kp_detect, cam->s.counters + 1))) return rc;
+  if ((rc = enqueue_detect(cam, cam->s.image, a))) return rc;
+  if ((rc = enqueue_describe(cam, cam->s.image, xp, cam->s.kp_detect, cam->s.counters + 1))) return rc;
   return OKC_OK;
 }
 
@@ -467,3 +504,4 @@ int okc_debug_candidates(okc_camera* cam, const uint8_t* image, int absolute_thr
 }  // extern "C"
 
 #include "capi_match.inc"
+#include "capi_frame.inc"

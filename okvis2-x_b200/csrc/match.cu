@@ -172,19 +172,23 @@ __device__ __forceinline__ unsigned hamming384(const unsigned a[kDescWords], con
 // reference's accumulation order.
 __global__ void __launch_bounds__(256)
 match_to_map_kernel(const uint8_t* __restrict__ queries, const double* __restrict__ kp_xy,
-                    const uint8_t* __restrict__ use, int nk, const uint8_t* __restrict__ map,
+                    const okc_keypoint* __restrict__ kp_f, const uint8_t* __restrict__ use, int nkMax,
+                    const int* __restrict__ nkDev, const uint8_t* __restrict__ map,
                     const int* __restrict__ owner, int nm, const double* __restrict__ proj_xy, double threshSq,
                     double hammingThreshold, double* __restrict__ bestDist, int* __restrict__ bestOwner,
                     unsigned long long* __restrict__ events, int eventCap, int* __restrict__ eventCount) {
   const int lane = threadIdx.x & 31;
   const int k = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  // nkDev: the keypoint count is still on the device (frame pipeline: queries are the camera's own descriptors)
+  const int nk = nkDev ? min(*nkDev, nkMax) : nkMax;
   if (k >= nk) return;
   double best = hammingThreshold;
   int bestO = -1;
-  if (use[k]) {
+  if (!use || use[k]) {
     unsigned q[kDescWords];
     load_desc(queries, k, q);
-    const double kx = kp_xy[2 * k], ky = kp_xy[2 * k + 1];
+    // cv::KeyPoint floats widen exactly to the Eigen::Vector2d the reference compares with (Frontend.cpp:1787-1790)
+    const double kx = kp_f ? (double)kp_f[k].x : kp_xy[2 * k], ky = kp_f ? (double)kp_f[k].y : kp_xy[2 * k + 1];
     for (int base = 0; base < nm; base += 32) {
       const int m = base + lane;
       double d = 1e9;
@@ -221,16 +225,16 @@ match_to_map_kernel(const uint8_t* __restrict__ queries, const double* __restric
   }
 }
 
-void launch_match_to_map(const uint8_t* queries, const double* kp_xy, const uint8_t* use, int nk, const uint8_t* map,
-                         const int* owner, int nm, const double* proj_xy, double threshSq, double hammingThreshold,
-                         double* bestDist, int* bestOwner, unsigned long long* events, int eventCap, int* eventCount,
-                         cudaStream_t s) {
-  if (nk <= 0) return;
+void launch_match_to_map(const uint8_t* queries, const double* kp_xy, const okc_keypoint* kp_f, const uint8_t* use,
+                         int nkMax, const int* nkDev, const uint8_t* map, const int* owner, int nm,
+                         const double* proj_xy, double threshSq, double hammingThreshold, double* bestDist,
+                         int* bestOwner, unsigned long long* events, int eventCap, int* eventCount, cudaStream_t s) {
+  if (nkMax <= 0) return;
   const int warpsPerBlock = 8;
-  const int blocks = (nk + warpsPerBlock - 1) / warpsPerBlock;
-  match_to_map_kernel<<<blocks, warpsPerBlock * 32, 0, s>>>(queries, kp_xy, use, nk, map, owner, nm, proj_xy, threshSq,
-                                                           hammingThreshold, bestDist, bestOwner, events, eventCap,
-                                                           eventCount);
+  const int blocks = (nkMax + warpsPerBlock - 1) / warpsPerBlock;
+  match_to_map_kernel<<<blocks, warpsPerBlock * 32, 0, s>>>(queries, kp_xy, kp_f, use, nkMax, nkDev, map, owner, nm,
+                                                           proj_xy, threshSq, hammingThreshold, bestDist, bestOwner,
+                                                           events, eventCap, eventCount);
 }
 
 // ----------------------------------------------------------------------------------------------

@@ -184,3 +184,56 @@ def test_match_stereo_vs_port(mod, ctx, port, syn):
         assert got[2].tobytes() == want[2].tobytes(), "hp_W"
         assert np.array_equal(got[3], want[3]), "initialisable"
     assert (got[0] < 60.0).sum() > 50
+
+
+def test_frame_pipeline_equals_separate_calls(mod, ctx, port, syn):
+    """detect -> describe -> matchToMap with everything resident in HBM == the three host-buffer calls == oracle."""
+    import torch
+    W, H = 752, 480
+    c = syn.EUROC["cams"][0]
+    rays, jac = syn.camera_maps(W, H, c["f"], c["c"], c["d"])
+    cam = mod.Camera(ctx, W, H, rays, jac, focal=c["f"][0], max_keypoints=1024)
+    direction = (0.05, 0.99, 0.1)
+    img0 = syn.scene_image(W, H, 1)
+    kp0, desc0 = cam.detect_describe(img0, 38.0, 0, 150.0, 700, direction=direction)
+    kp_xy0 = np.stack([kp0["x"], kp0["y"]], 1).astype(np.float64)
+    win = syn.map_window(desc0, kp_xy0, 2000, 7, W, H)
+    sel = win["is3d"][win["owner"]]
+    # 3-D landmarks only, slots renumbered densely (what Frontend::matchToMap hands to matchToMapByThread)
+    slots = np.cumsum(win["is3d"]) - 1
+    m3, o3, proj3 = win["map"][sel], slots[win["owner"][sel]].astype(np.int32), win["proj"][win["is3d"]]
+    window = mod.MapWindow(ctx, m3, o3, len(proj3))
+    gate = (3.0 + 0.5 * (c["f"][0] + c["f"][1]) * 0.06) ** 2
+    for seed, on_device in ((1, False), (2, True), (1, True)):
+        img = syn.scene_image(W, H, seed)
+        d_img = torch.from_numpy(img).cuda()
+        torch.cuda.synchronize()
+        cam.enqueue_device(d_img.data_ptr(), 38.0, 0, 150.0, 700, direction=direction)
+        if on_device:
+            d_proj = torch.from_numpy(proj3).cuda()
+            torch.cuda.synchronize()
+            cam.match_to_map_enqueue(window, None, gate, 60.0, proj_device_ptr=d_proj.data_ptr())
+        else:
+            cam.match_to_map_enqueue(window, proj3, gate, 60.0)
+        kp, desc, bd, bo, ctrs, errs = cam.frame_finish(window, 4)
+        kp2, desc2 = cam.detect_describe(img, 38.0, 0, 150.0, 700, direction=direction)
+        assert kp.tobytes() == kp2.tobytes() and np.array_equal(desc, desc2)
+        kp_xy = np.stack([kp["x"], kp["y"]], 1).astype(np.float64)
+        use = np.ones(len(kp), np.uint8)
+        bd2, bo2, ctrs2, errs2 = ctx.match_to_map(desc, kp_xy, use, m3, o3, proj3, gate, 60.0, 4)
+        pd, po, pc, pe = port.match_to_map(desc, kp_xy, use, m3, o3, proj3, None, gate, 60.0, 4)
+        for a, b, cc in ((bd, bd2, pd), (bo, bo2, po), (ctrs, ctrs2, pc)):
+            assert np.array_equal(a, b) and np.array_equal(a, cc)
+        assert errs.tobytes() == errs2.tobytes() == pe.tobytes()
+        if seed == 1:
+            assert (bo >= 0).sum() > 100
+    cam.kernel_timing(True)
+    cam.enqueue_device(d_img.data_ptr(), 38.0, 0, 150.0, 700, direction=direction)
+    cam.match_to_map_enqueue(window, proj3, gate, 60.0)
+    times = cam.kernel_times()
+    cam.frame_finish(window, 4)
+    cam.kernel_timing(False)
+    assert [n for n, _ in times] == ["harris_nms", "select_keypoints", "border_filter+describe", "match_to_map"]
+    assert all(t > 0 for _, t in times)
+    window.close()
+    cam.close()
