@@ -167,3 +167,44 @@ def map_window(desc, kp_xy, num_landmarks, seed, width, height, is3d_frac=0.7):
         owner += [l] * nd
     return dict(map=np.concatenate(rows, 0) if rows else np.zeros((0, 48), np.uint8),
                 owner=np.asarray(owner, np.int32), proj=proj, is3d=rng.random(num_landmarks) < is3d_frac)
+
+
+def stereo_sequence(n_frames, width=752, height=480, seed=2, rects=900, step=(2, 1)):
+    """Config 2: a stereo sequence cut from one master canvas translated by `step` px per frame.
+
+    Returns (left [n,H,W] u8, right [n,H,W] u8, shift [n,2] = (dx, dy) of frame f relative to frame 0). The right
+    image is the left view displaced by a per-row-band integer disparity of 8..40 px (constant over the sequence).
+    """
+    mw, mh = width + step[0] * (n_frames - 1) + 64, height + step[1] * (n_frames - 1)
+    master = scene_image(mw, mh, seed, rects=rects)
+    rng = np.random.default_rng(seed + 1000)
+    disp = np.zeros(mh, np.int64)
+    band = 0
+    while band < mh:
+        hgt = int(rng.integers(24, 96))
+        disp[band:band + hgt] = int(rng.integers(8, 41))
+        band += hgt
+    cols = np.arange(mw)[None, :] - disp[:, None]
+    master_r = np.take_along_axis(master, np.clip(cols, 0, mw - 1), axis=1)
+    left = np.empty((n_frames, height, width), np.uint8)
+    right = np.empty_like(left)
+    shift = np.zeros((n_frames, 2), np.int64)
+    for f in range(n_frames):
+        x0, y0 = 48 + step[0] * f, step[1] * f
+        left[f] = master[y0:y0 + height, x0:x0 + width]
+        right[f] = master_r[y0:y0 + height, x0:x0 + width]
+        shift[f] = (step[0] * f, step[1] * f)
+    return left, right, shift
+
+
+def sequence_window(desc0, kp_xy0, shift, num_landmarks, seed, width, height):
+    """Keyframe window for stereo_sequence: landmarks from frame 0's descriptors (map_window), 3-D ones only with
+    densely renumbered slots, and per-frame projections = frame-0 projection moved with the canvas."""
+    win = map_window(desc0, kp_xy0, num_landmarks, seed, width, height)
+    sel = win["is3d"][win["owner"]]
+    slots = np.cumsum(win["is3d"]) - 1
+    rows = np.ascontiguousarray(win["map"][sel])
+    owner = slots[win["owner"][sel]].astype(np.int32)
+    proj0 = win["proj"][win["is3d"]]
+    proj = proj0[None, :, :] - shift[:, None, :].astype(np.float64)
+    return rows, owner, np.ascontiguousarray(proj)
