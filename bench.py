@@ -411,7 +411,9 @@ def run_sweep(st, rank, world, iters=5):
     best = torch.empty(nq, dtype=torch.int64, device="cuda")
     gathered = torch.empty(world * nq, dtype=torch.int64, device="cuda") if world > 1 else None
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
-    cur = torch.cuda.current_stream()
+    # a non-default stream: handle 0 would select the library's own stream, which torch events do not see
+    cur = torch.cuda.Stream()
+    torch.cuda.set_stream(cur)
     times, ktimes = [], []
     for it in range(iters + 2):
         flush.fill_(it & 0xff)

@@ -32,20 +32,21 @@ def test_match_batched_ties_first_row_wins(mod, ctx, port):
     rng = np.random.default_rng(7)
     q = rng.integers(0, 256, (64, 48), dtype=np.uint8)
     m = rng.integers(0, 256, (20000, 48), dtype=np.uint8)
-    # the same near-duplicate planted at several rows, across stage / chunk / CTA boundaries
-    rows = [3, 127, 128, 129, 4095, 4096, 9999, 19999]
+    # query i: the same near-duplicate planted at several rows (across stage / chunk / CTA boundaries); the first wins
+    base = [3, 127, 128, 129, 4095, 4096, 9999, 19000]
+    first = {}
     for i in range(64):
         d = q[i].copy()
         d[i % 48] ^= 1
-        for r in rows[i % 3:]:
+        rows = [r + 7 * i for r in base[i % 5:]]
+        for r in rows:
             m[r] = d
-        got_row = rows[i % 3]
-        m[got_row] = d
-    # only the last assignment per row survives; recompute the truth with the oracle
+        first[i] = rows[0]
     want = port.hamming_best(q, m, 60)
     got = ctx.match_batched(q, m, 60)
     assert np.array_equal(got, want)
-    assert (got != mod.NO_MATCH).sum() >= 8
+    for i in range(64):
+        assert got[i] == (1 << 32) | first[i]
     # threshold semantics: strict '<'
     q2 = q[:1].copy()
     m2 = np.repeat(q2, 3, 0)
@@ -155,10 +156,15 @@ def test_match_to_map_edge_cases(mod, ctx, port, syn):
 
 
 def stereo_views(mod, ctx, syn, W=752, H=480, seed=1):
-    """Two EuRoC cameras looking at a synthetic stereo pair; e_C = pinhole back-projection of the keypoints."""
-    left, right = syn.stereo_pair(W, H, seed)
+    """An ideal rectified rig (both cameras = EuRoC cam0 intrinsics without distortion, camera 1 displaced by the
+    11 cm baseline along the camera x axis) looking at a synthetic stereo pair; e_C = pinhole back-projection."""
+    # stereo_pair returns (img, img displaced by +disp px): a feature sits at larger x in the second image, so the
+    # second image is the LEFT camera of a real rig (x_right = x_left - d) and the first one the RIGHT camera
+    right_cam, left_cam = syn.stereo_pair(W, H, seed)
+    c = syn.EUROC["cams"][0]
+    T0 = np.asarray(c["T_SC"], np.float64).reshape(4, 4)
     views = []
-    for img, c in zip((left, right), syn.EUROC["cams"]):
+    for i, img in enumerate((right_cam, left_cam)):   # view 0 = right camera (at +11 cm along x), view 1 = left
         cam = mod.Camera(ctx, W, H, max_keypoints=4096)
         kp, desc = cam.detect_describe(img, 38.0, 0, 150.0, 700)
         cam.close()
@@ -166,11 +172,12 @@ def stereo_views(mod, ctx, syn, W=752, H=480, seed=1):
         y = (kp["y"].astype(np.float64) - c["c"][1]) / c["f"][1]
         e = np.stack([x, y, np.ones_like(x)], 1)
         e /= np.linalg.norm(e, axis=1, keepdims=True)
-        T = np.asarray(c["T_SC"], np.float64).reshape(4, 4)
         bpv = np.ones(len(kp), np.uint8)
         bpv[::17] = 0
-        views.append(dict(desc=desc, size=kp["size"].astype(np.float64), e_C=e, bp_valid=bpv, C_WC=T[:3, :3],
-                          r_WC=T[:3, 3], f=0.5 * (c["f"][0] + c["f"][1])))
+        C_WC = T0[:3, :3]
+        r_WC = T0[:3, 3] + (C_WC @ np.asarray([0.11, 0.0, 0.0]) if i == 0 else 0.0)
+        views.append(dict(desc=desc, size=kp["size"].astype(np.float64), e_C=e, bp_valid=bpv, C_WC=C_WC,
+                          r_WC=r_WC, f=0.5 * (c["f"][0] + c["f"][1])))
     return views
 
 
