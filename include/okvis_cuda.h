@@ -99,7 +99,8 @@ int okc_detect_describe_finish(okc_camera* cam, okc_keypoint* keypoints, int cap
 /* Intermediate products, for parity tests (not used by the reference's callers):
  * scores int32[H*W] = brisk::HarrisScoresSSE (brisk/src/harris-scores.cc:65-301);
  * candidates {int32 score; uint16 x, y}[cap] = HarrisScoreCalculator::Get2dMaxima
- * (brisk/src/harris-score-calculator.cc:70-119) sorted by (score desc, raster asc). */
+ * (brisk/src/harris-score-calculator.cc:70-119) in the order std::sort leaves them at the top of
+ * EnforceKeyPointUniformity (uniformity-enforcement-inl.h:67; libstdc++ introsort, tie order included). */
 int okc_debug_scores(okc_camera* cam, const uint8_t* image, int32_t* scores);
 int okc_debug_candidates(okc_camera* cam, const uint8_t* image, int absolute_threshold, void* candidates, int cap,
                          int* n);

@@ -79,6 +79,7 @@ def lib():
         L.okc_debug_candidates.argtypes = [vp, vp, i, vp, i, C.POINTER(i)]
         L.okc_debug_host_tables.argtypes = [vp, C.POINTER(i), C.POINTER(i), vp, vp, vp]
         L.okc_debug_set_match_prefix.argtypes = [i]
+        L.okc_debug_std_sort.argtypes = [vp, vp, i, vp]
         L.okc_match_batched.argtypes = [vp, vp, i, vp, i64, u32, u64, vp]
         L.okc_descriptor_set_create.argtypes = [vp, vp, i64, C.POINTER(vp)]
         L.okc_descriptor_set_destroy.argtypes = [vp]
@@ -350,6 +351,13 @@ class Camera:
         n = C.c_int(0)
         _check(lib().okc_debug_kernel_times(self.h, names, 512, _p(ms), 16, C.byref(n)), "okc_debug_kernel_times")
         return list(zip(names.value.decode().split("\n"), [float(v) for v in ms[:n.value]])) if n.value else []
+
+    def debug_std_sort(self, scores):
+        """Permutation the device's std::sort reproduction gives to `scores` (descending, libstdc++ tie order)."""
+        sc = np.ascontiguousarray(scores, np.int32)
+        order = np.zeros(max(len(sc), 1), np.uint32)
+        _check(lib().okc_debug_std_sort(self.h, _p(sc), len(sc), _p(order)), "okc_debug_std_sort")
+        return order[:len(sc)].copy()
 
     def debug_scores(self, image):
         img = self._img(image)

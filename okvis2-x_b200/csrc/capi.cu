@@ -6,6 +6,7 @@
 #include <cstring>
 #include <mutex>
 #include <new>
+#include <vector>
 
 #include "common.cuh"
 #include "pattern.h"
@@ -216,6 +217,8 @@ int okc_camera_create(okc_context* ctx, int width, int height, const float* rays
   OKC_CUDA_TRY(cudaMalloc(&c->s.image, px));
   OKC_CUDA_TRY(cudaMalloc(&c->s.scores, px * sizeof(int32_t)));
   OKC_CUDA_TRY(cudaMalloc(&c->s.cand, ((size_t)kCandCap + max_keypoints) * sizeof(uint64_t)));
+  OKC_CUDA_TRY(cudaMalloc(&c->s.bitmap, (size_t)height * ((width + 31) / 32) * sizeof(uint32_t)));
+  OKC_CUDA_TRY(cudaMalloc(&c->s.order_scratch, order_scratch_bytes()));
   OKC_CUDA_TRY(cudaMalloc(&c->s.counters, 8 * sizeof(int)));
   OKC_CUDA_TRY(cudaMalloc(&c->s.kp_detect, (size_t)max_keypoints * sizeof(okc_keypoint)));
   OKC_CUDA_TRY(cudaMalloc(&c->s.kp_desc, (size_t)max_keypoints * sizeof(okc_keypoint)));
@@ -242,6 +245,8 @@ int okc_camera_destroy(okc_camera* c) {
   cudaFree(c->s.image);
   cudaFree(c->s.scores);
   cudaFree(c->s.cand);
+  cudaFree(c->s.bitmap);
+  cudaFree(c->s.order_scratch);
   cudaFree(c->s.counters);
   cudaFree(c->s.kp_detect);
   cudaFree(c->s.kp_desc);
@@ -313,8 +318,11 @@ static int upload_image(okc_camera* cam, const uint8_t* image) {
 static int enqueue_detect(okc_camera* cam, const uint8_t* image, const DetectArgs& a) {
   OKC_CUDA_TRY(cudaMemsetAsync(cam->s.counters, 0, 8 * sizeof(int), cam->stream));
   cam->timing_begin();
-  launch_harris_nms(image, cam->s.scores, cam->s.cand, cam->s.counters, a, cam->stream);
+  launch_harris_nms(image, cam->s.scores, cam->s.bitmap, a, cam->stream);
   cam->mark("harris_nms");
+  launch_order_candidates(cam->s.scores, cam->s.bitmap, cam->s.cand, cam->s.counters, cam->s.order_scratch, a,
+                          cam->stream);
+  cam->mark("order_candidates");
   launch_select_keypoints(cam->s.scores, cam->s.cand, cam->s.counters, cam->s.occupancy, cam->ctx->tables.lut,
                           cam->s.kp_detect, a, cam->stream);
   cam->mark("select_keypoints");
@@ -459,7 +467,7 @@ int okc_debug_scores(okc_camera* cam, const uint8_t* image, int32_t* scores) {
   a.height = cam->H;
   a.abs_threshold = 0x7fffffff;
   OKC_CUDA_TRY(cudaMemsetAsync(cam->s.counters, 0, 8 * sizeof(int), cam->stream));
-  launch_harris_nms(cam->s.image, cam->s.scores, cam->s.cand, cam->s.counters, a, cam->stream);
+  launch_harris_nms(cam->s.image, cam->s.scores, cam->s.bitmap, a, cam->stream);
   OKC_CUDA_TRY(cudaMemcpyAsync(scores, cam->s.scores, (size_t)cam->W * cam->H * sizeof(int32_t), cudaMemcpyDeviceToHost,
                                cam->stream));
   OKC_CUDA_TRY(cudaStreamSynchronize(cam->stream));
@@ -477,17 +485,19 @@ int okc_debug_candidates(okc_camera* cam, const uint8_t* image, int absolute_thr
   a.height = cam->H;
   a.abs_threshold = absolute_threshold;
   OKC_CUDA_TRY(cudaMemsetAsync(cam->s.counters, 0, 8 * sizeof(int), cam->stream));
-  launch_harris_nms(cam->s.image, cam->s.scores, cam->s.cand, cam->s.counters, a, cam->stream);
+  launch_harris_nms(cam->s.image, cam->s.scores, cam->s.bitmap, a, cam->stream);
+  launch_order_candidates(cam->s.scores, cam->s.bitmap, cam->s.cand, cam->s.counters, cam->s.order_scratch, a,
+                          cam->stream);
   OKC_CUDA_TRY(cudaMemcpyAsync(cam->h_counters, cam->s.counters, 4 * sizeof(int), cudaMemcpyDeviceToHost, cam->stream));
   OKC_CUDA_TRY(cudaStreamSynchronize(cam->stream));
   int cnt = cam->h_counters[0];
-  if (cnt > kCandCap || cnt > cap) {
+  if (cam->h_counters[3] == 1 || cnt > cap) {
     set_error("okc_debug_candidates: %d candidates exceed capacity", cnt);
     return OKC_ERR_CAPACITY;
   }
+  // device order = the reference's std::sort order (no host sort here)
   uint64_t* keys = new uint64_t[cnt > 0 ? cnt : 1];
   OKC_CUDA_TRY(cudaMemcpy(keys, cam->s.cand, (size_t)cnt * sizeof(uint64_t), cudaMemcpyDeviceToHost));
-  std::sort(keys, keys + cnt);
   struct Pws { int32_t score; uint16_t x, y; };
   Pws* out = static_cast<Pws*>(candidates);
   for (int i = 0; i < cnt; ++i) {
@@ -498,6 +508,33 @@ int okc_debug_candidates(okc_camera* cam, const uint8_t* image, int absolute_thr
   }
   delete[] keys;
   *n = cnt;
+  return OKC_OK;
+}
+
+// Test hook for the std::sort reproduction alone: sorts n (<= W*H) arbitrary scores given in "raster order" and
+// returns the permutation (order[i] = input index of the i-th output element).
+int okc_debug_std_sort(okc_camera* cam, const int32_t* in_scores, int n, uint32_t* order) {
+  if (!cam || !in_scores || !order || n < 0 || (size_t)n > (size_t)cam->W * cam->H || n > kCandCap) return OKC_ERR_INVALID;
+  OKC_CUDA_TRY(cudaSetDevice(cam->ctx->device));
+  const int wpr = (cam->W + 31) / 32;
+  std::vector<uint32_t> bm((size_t)cam->H * wpr, 0u);
+  for (int r = 0; r < n; ++r) {
+    const int y = r / cam->W, x = r % cam->W;
+    bm[(size_t)y * wpr + (x >> 5)] |= 1u << (x & 31);
+  }
+  DetectArgs a{};
+  a.width = cam->W;
+  a.height = cam->H;
+  OKC_CUDA_TRY(cudaMemcpyAsync(cam->s.bitmap, bm.data(), bm.size() * 4, cudaMemcpyHostToDevice, cam->stream));
+  OKC_CUDA_TRY(cudaMemcpyAsync(cam->s.scores, in_scores, (size_t)n * 4, cudaMemcpyHostToDevice, cam->stream));
+  OKC_CUDA_TRY(cudaMemsetAsync(cam->s.counters, 0, 8 * sizeof(int), cam->stream));
+  launch_order_candidates(cam->s.scores, cam->s.bitmap, cam->s.cand, cam->s.counters, cam->s.order_scratch, a,
+                          cam->stream);
+  OKC_CUDA_TRY(cudaGetLastError());
+  std::vector<uint64_t> keys((size_t)n + 1);
+  OKC_CUDA_TRY(cudaMemcpyAsync(keys.data(), cam->s.cand, (size_t)n * 8, cudaMemcpyDeviceToHost, cam->stream));
+  OKC_CUDA_TRY(cudaStreamSynchronize(cam->stream));
+  for (int i = 0; i < n; ++i) order[i] = (uint32_t)keys[i];
   return OKC_OK;
 }
 

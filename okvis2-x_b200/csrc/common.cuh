@@ -11,7 +11,6 @@ namespace okc {
 
 constexpr int kDescWords = 12;         // 48 bytes = 12 x u32 = 3 x uint4
 constexpr int kCandCap = 131072;       // candidate capacity per image (power of two, for the bitonic network)
-constexpr int kSortSmemMax = 16384;    // candidates sorted in shared memory up to this count
 constexpr int kNRot = 1024;            // brisk n_rot_
 constexpr int kPoints = 66;
 constexpr int kShortPairs = 384;
@@ -42,7 +41,9 @@ struct PatternTables {
 struct DeviceImageScratch {
   uint8_t* image;          // H*W
   int32_t* scores;         // H*W
-  uint64_t* cand;          // kCandCap keys
+  uint64_t* cand;          // kCandCap keys (std::sort order) + max_keypoints kept keys
+  uint32_t* bitmap;        // H * ceil(W/32) words: NMS survivors
+  uint8_t* order_scratch;  // order_candidates_kernel arrays when the candidates do not fit in shared memory
   int* counters;           // [0]=candidate count, [1]=kept count, [2]=described count, [3]=overflow flag
   uint8_t* occupancy;      // global fallback for the uniformity occupancy image
   size_t occupancy_bytes;
@@ -67,8 +68,10 @@ struct DescribeArgs {
   float inv_f;             // 1.0f / virtualFocalLength_
 };
 
-void launch_harris_nms(const uint8_t* image, int32_t* scores, uint64_t* cand, int* counters, const DetectArgs& a,
-                       cudaStream_t s);
+void launch_harris_nms(const uint8_t* image, int32_t* scores, uint32_t* bitmap, const DetectArgs& a, cudaStream_t s);
+size_t order_scratch_bytes();
+void launch_order_candidates(const int32_t* scores, const uint32_t* bitmap, uint64_t* cand, int* counters,
+                             uint8_t* gscratch, const DetectArgs& a, cudaStream_t s);
 void launch_select_keypoints(const int32_t* scores, uint64_t* cand, int* counters, uint8_t* occ_global,
                              const float* lut, okc_keypoint* out, const DetectArgs& a, cudaStream_t s);
 void launch_describe(const uint8_t* image, const okc_keypoint* kp_in, const int* n_in, okc_keypoint* kp_out,

@@ -3,12 +3,15 @@
 //  harris_nms_kernel   = brisk::HarrisScoresSSE (brisk/src/harris-scores.cc:65-301) fused with
 //                        HarrisScoreCalculator::Get2dMaxima (brisk/src/harris-score-calculator.cc:70-119):
 //                        one pass over the u8 image, no int16 planes in HBM; writes the int32 score map
-//                        (needed by the sub-pixel fit) and appends NMS survivors as 64-bit sort keys.
-//  select_keypoints_kernel = EnforceKeyPointUniformity (brisk/include/brisk/internal/uniformity-enforcement-inl.h:57-207)
+//                        (needed by the sub-pixel fit) and a bitmap of the NMS survivors.
+//  order_candidates_kernel = the std::sort at the top of EnforceKeyPointUniformity, tie order included
+//                        (libstdc++ introsort reproduced exactly; see the comment at the kernel).
+//  select_keypoints_kernel = the greedy loop of EnforceKeyPointUniformity
+//                        (brisk/include/brisk/internal/uniformity-enforcement-inl.h:57-207)
 //                        + the Subpixel2D tail of DetectScaleSpaceMaxima
 //                        (brisk/include/brisk/internal/scale-space-layer-inl.h:394-420, 568-701):
-//                        one CTA per image sorts the candidates (bitonic network), runs the greedy
-//                        occupancy loop with the occupancy image in shared memory, then refines.
+//                        one CTA per image runs the greedy occupancy loop with the occupancy image in
+//                        shared memory, then refines.
 #include "common.cuh"
 
 namespace okc {
@@ -23,8 +26,8 @@ constexpr int PRW = TX + 4, PRH = TY + 4;   // gradient-product tile, halo 2
 constexpr int SCW = TX + 2, SCH = TY + 2;   // score tile, halo 1 (NMS neighbours)
 
 __global__ void __launch_bounds__(256) harris_nms_kernel(const uint8_t* __restrict__ img, int32_t* __restrict__ scores,
-                                                         uint64_t* __restrict__ cand, int* __restrict__ counters,
-                                                         int W, int H, int absThreshold) {
+                                                         uint32_t* __restrict__ bitmap, int W, int H,
+                                                         int absThreshold) {
   __shared__ uint8_t px[PXH][PXW + 2];
   __shared__ short pxx[PRH][PRW], pxy[PRH][PRW], pyy[PRH][PRW];
   __shared__ int sc[SCH][SCW];
@@ -88,41 +91,38 @@ __global__ void __launch_bounds__(256) harris_nms_kernel(const uint8_t* __restri
   __syncthreads();
 
   // 4. write scores; NMS on rows [2, H-2), cols [2, W-2): keep if >= threshold and no neighbour is
-  //    strictly greater (plateaus survive), harris-score-calculator.cc:76-117.
+  //    strictly greater (plateaus survive), harris-score-calculator.cc:76-117. Survivors are published as a
+  //    bitmap (one word per 32-pixel tile row), so that the next kernel can rebuild the reference's RASTER
+  //    candidate order without a sort. Each warp owns one tile row per iteration (TX == 32).
+  const int wordsPerRow = (W + 31) >> 5;
   for (int i = tid; i < TX * TY; i += 256) {
     int ly = i / TX, lx = i - ly * TX;
     int gx = x0 + lx, gy = y0 + ly;
-    if (gx >= W || gy >= H) continue;
-    int cy = ly + 1, cx = lx + 1;
-    int c = sc[cy][cx];
-    scores[(size_t)gy * W + gx] = c;
-    if (gx < 2 || gx >= W - 2 || gy < 2 || gy >= H - 2) continue;
-    if (c < absThreshold) continue;
-    if (sc[cy][cx + 1] > c || sc[cy][cx - 1] > c || sc[cy + 1][cx] > c || sc[cy - 1][cx] > c ||
-        sc[cy + 1][cx + 1] > c || sc[cy + 1][cx - 1] > c || sc[cy - 1][cx + 1] > c || sc[cy - 1][cx - 1] > c)
-      continue;
-    int slot = atomicAdd(&counters[0], 1);
-    if (slot < kCandCap) cand[slot] = cand_key(c, (uint32_t)(gy * W + gx));
-    else counters[3] = 1;
+    bool isMax = false;
+    if (gx < W && gy < H) {
+      int cy = ly + 1, cx = lx + 1;
+      int c = sc[cy][cx];
+      scores[(size_t)gy * W + gx] = c;
+      if (gx >= 2 && gx < W - 2 && gy >= 2 && gy < H - 2 && c >= absThreshold)
+        isMax = !(sc[cy][cx + 1] > c || sc[cy][cx - 1] > c || sc[cy + 1][cx] > c || sc[cy - 1][cx] > c ||
+                  sc[cy + 1][cx + 1] > c || sc[cy + 1][cx - 1] > c || sc[cy - 1][cx + 1] > c ||
+                  sc[cy - 1][cx - 1] > c);
+    }
+    const unsigned word = __ballot_sync(0xffffffffu, isMax);
+    if (lx == 0 && gy < H) bitmap[(size_t)gy * wordsPerRow + blockIdx.x] = word;
   }
 }
 
-void launch_harris_nms(const uint8_t* image, int32_t* scores, uint64_t* cand, int* counters, const DetectArgs& a,
-                       cudaStream_t s) {
+void launch_harris_nms(const uint8_t* image, int32_t* scores, uint32_t* bitmap, const DetectArgs& a, cudaStream_t s) {
   dim3 grid((a.width + TX - 1) / TX, (a.height + TY - 1) / TY);
-  harris_nms_kernel<<<grid, dim3(32, 8), 0, s>>>(image, scores, cand, counters, a.width, a.height, a.abs_threshold);
+  harris_nms_kernel<<<grid, dim3(32, 8), 0, s>>>(image, scores, bitmap, a.width, a.height, a.abs_threshold);
 }
-
-// ----------------------------------------------------------------------------------------------
-// sort + greedy uniformity + sub-pixel refinement: one CTA per image
-// ----------------------------------------------------------------------------------------------
-constexpr int kSelThreads = 1024;
 
 __device__ __forceinline__ void bitonic_sort(uint64_t* keys, int npad) {
   // keys[0..npad) ascending; npad is a power of two; all threads of the CTA participate.
   for (int k = 2; k <= npad; k <<= 1) {
     for (int j = k >> 1; j > 0; j >>= 1) {
-      for (int i = threadIdx.x; i < npad; i += kSelThreads) {
+      for (int i = threadIdx.x; i < npad; i += 1024) {
         int ixj = i ^ j;
         if (ixj > i) {
           uint64_t a = keys[i], b = keys[ixj];
@@ -137,6 +137,301 @@ __device__ __forceinline__ void bitonic_sort(uint64_t* keys, int npad) {
     }
   }
 }
+
+// ----------------------------------------------------------------------------------------------
+// order_candidates: raster-ordered candidate list + the reference's std::sort order
+// ----------------------------------------------------------------------------------------------
+// EnforceKeyPointUniformity starts with std::sort(points.begin(), points.end()) over the raster-ordered
+// Get2dMaxima output with PointWithScore::operator< = "score > other.score"
+// (uniformity-enforcement-inl.h:67, score-calculator.h:94-96). Scores tie often (they are quantised by the >>16
+// and >>4 shifts), std::sort is not stable, and the order of equal scores decides both which points the greedy
+// loop keeps and the index order of the output keypoints. So the device reproduces libstdc++'s introsort exactly:
+//   * __introsort_loop = a tree of Hoare partitions (median-of-3 pivot moved to the front, unguarded partition,
+//     recursion while a range has > 16 elements, heapsort when the depth limit 2*floor(log2 n) is exhausted).
+//     Ranges at the same depth are disjoint, so they are processed level by level, one warp per range; the
+//     sequential two-pointer partition is replaced by its closed form: the i-th "left stop" (score <= pivot,
+//     scanning up) is swapped with the i-th "right stop" (score >= pivot, scanning down) while L_i < R_i.
+//   * __final_insertion_sort is a stable insertion sort, i.e. the final order = a stable sort by score of the
+//     array the partition phase leaves behind -> one bitonic sort on (score desc, position asc) keys.
+// tools/introsort_model.py checks this formulation against the real std::sort (oracle/_ref) on tie-heavy and
+// adversarial (heapsort-triggering) inputs.
+constexpr int kOrdThreads = 1024;
+constexpr int kOrdSmemCap = 8192;                         // candidates handled entirely in shared memory
+constexpr int kOrdQueueSmem = 512;                        // >= kOrdSmemCap / 17 ranges per level
+constexpr int kOrdQueueGlobal = kCandCap / 16;            // >= kCandCap / 17
+
+struct OrdArrays {
+  int* sc;          // score
+  uint32_t* ra;     // raster index y * W + x
+  int* lp;          // left stops of the range being partitioned (positions), stored inside the range
+  int* rp;          // right stops
+  int2* q[2];       // range queues of the current / next level
+  uint64_t* keys;   // final sort keys (may alias sc/lp/rp: they are dead by then)
+};
+
+__device__ __forceinline__ void ord_swap(const OrdArrays& A, int i, int j) {
+  const int s = A.sc[i];
+  A.sc[i] = A.sc[j];
+  A.sc[j] = s;
+  const uint32_t r = A.ra[i];
+  A.ra[i] = A.ra[j];
+  A.ra[j] = r;
+}
+
+// std::__partial_sort(first, last, last) = make_heap + sort_heap with comp(x, y) = x.score > y.score
+// (bits/stl_heap.h: __adjust_heap / __push_heap). Sequential; only reached on adversarial inputs.
+__device__ void ord_heap_sort(const OrdArrays& A, int f, int l) {
+  const int n = l - f;
+  if (n < 2) return;
+  auto adjust = [&](int hole, int length, int vs, uint32_t vr) {
+    const int top = hole;
+    int child = hole;
+    while (child < (length - 1) / 2) {
+      child = 2 * (child + 1);
+      if (A.sc[f + child] > A.sc[f + child - 1]) --child;
+      A.sc[f + hole] = A.sc[f + child];
+      A.ra[f + hole] = A.ra[f + child];
+      hole = child;
+    }
+    if ((length & 1) == 0 && child == (length - 2) / 2) {
+      child = 2 * (child + 1);
+      A.sc[f + hole] = A.sc[f + child - 1];
+      A.ra[f + hole] = A.ra[f + child - 1];
+      hole = child - 1;
+    }
+    int parent = (hole - 1) / 2;
+    while (hole > top && A.sc[f + parent] > vs) {
+      A.sc[f + hole] = A.sc[f + parent];
+      A.ra[f + hole] = A.ra[f + parent];
+      hole = parent;
+      parent = (hole - 1) / 2;
+    }
+    A.sc[f + hole] = vs;
+    A.ra[f + hole] = vr;
+  };
+  for (int parent = (n - 2) / 2;; --parent) {
+    adjust(parent, n, A.sc[f + parent], A.ra[f + parent]);
+    if (parent == 0) break;
+  }
+  for (int last = n - 1; last > 0; --last) {
+    const int vs = A.sc[f + last];
+    const uint32_t vr = A.ra[f + last];
+    A.sc[f + last] = A.sc[f];
+    A.ra[f + last] = A.ra[f];
+    adjust(0, last, vs, vr);
+  }
+}
+
+// std::__unguarded_partition_pivot on [f, l) by one warp; returns the cut.
+__device__ int ord_warp_partition(const OrdArrays& A, int f, int l, int lane) {
+  if (lane == 0) {  // __move_median_to_first(first, first + 1, mid, last - 1)
+    const int a = f + 1, b = f + (l - f) / 2, c = l - 1;
+    const int sa = A.sc[a], sb = A.sc[b], s_c = A.sc[c];
+    int pick;
+    if (sa > sb) pick = (sb > s_c) ? b : ((sa > s_c) ? c : a);
+    else pick = (sa > s_c) ? a : ((sb > s_c) ? c : b);
+    ord_swap(A, f, pick);
+  }
+  __syncwarp();
+  const int pv = A.sc[f];
+  const int len = l - f;
+  const unsigned lt = (1u << lane) - 1u;
+  int nL = 0, nR = 0;
+  for (int base = 0; base < len; base += 32) {
+    const int i = base + lane;
+    const int pL = f + 1 + i, pR = l - 1 - i;
+    const bool isL = pL < l && !(A.sc[pL] > pv);   // "while (comp(*first, pivot)) ++first" stops here
+    const bool isR = i < len && !(pv > A.sc[pR]);  // "while (comp(pivot, *last)) --last" stops here (f = sentinel)
+    const unsigned bL = __ballot_sync(0xffffffffu, isL), bR = __ballot_sync(0xffffffffu, isR);
+    if (isL) A.lp[f + 1 + nL + __popc(bL & lt)] = pL;
+    if (isR) A.rp[f + nR + __popc(bR & lt)] = pR;
+    nL += __popc(bL);
+    nR += __popc(bR);
+  }
+  __syncwarp();
+  const int m = nL < nR ? nL : nR;
+  int t = 0;  // number of swaps: leading pairs with L_i < R_i
+  for (int base = 0; base < m; base += 32) {
+    const int i = base + lane;
+    const bool ok = i < m && A.lp[f + 1 + i] < A.rp[f + i];
+    const unsigned b = __ballot_sync(0xffffffffu, ok);
+    if (b == 0xffffffffu) {
+      t += 32;
+      continue;
+    }
+    t += __ffs(~b) - 1;
+    break;
+  }
+  for (int i = lane; i < t; i += 32) ord_swap(A, A.lp[f + 1 + i], A.rp[f + i]);
+  int cut;
+  if (t == 0) {
+    cut = nL > 0 ? A.lp[f + 1] : l;
+  } else {
+    cut = A.rp[f + t - 1];
+    if (t < nL) {
+      const int nextL = A.lp[f + 1 + t];
+      if (nextL < cut) cut = nextL;
+    }
+  }
+  __syncwarp();
+  return cut;
+}
+
+__global__ void __launch_bounds__(kOrdThreads, 1)
+order_candidates_kernel(const int32_t* __restrict__ scores, const uint32_t* __restrict__ bitmap,
+                        uint64_t* __restrict__ cand, int* __restrict__ counters, uint8_t* __restrict__ gscratch,
+                        int W, int H) {
+  extern __shared__ __align__(16) uint8_t smem[];
+  __shared__ int s_warp[32];
+  __shared__ int s_n, s_qcount[2];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+
+  // ---- A. candidate count and raster-ordered offsets from the bitmap ----
+  const int wordsPerRow = (W + 31) >> 5;
+  const int words = H * wordsPerRow;
+  const int chunk = (words + kOrdThreads - 1) / kOrdThreads;
+  const int w0 = tid * chunk, w1 = min(words, w0 + chunk);
+  int mine = 0;
+  for (int w = w0; w < w1; ++w) mine += __popc(bitmap[w]);
+  int incl = mine;
+  for (int d = 1; d < 32; d <<= 1) {
+    const int v = __shfl_up_sync(0xffffffffu, incl, d);
+    if (lane >= d) incl += v;
+  }
+  if (lane == 31) s_warp[warp] = incl;
+  __syncthreads();
+  if (warp == 0) {
+    int v = s_warp[lane], iv = v;
+    for (int d = 1; d < 32; d <<= 1) {
+      const int u = __shfl_up_sync(0xffffffffu, iv, d);
+      if (lane >= d) iv += u;
+    }
+    s_warp[lane] = iv - v;
+    if (lane == 31) s_n = iv;
+  }
+  __syncthreads();
+  int total = s_n;
+  if (total > kCandCap) {
+    if (tid == 0) {
+      counters[0] = kCandCap;
+      counters[3] = 1;  // overflow: reported by the C ABI as OKC_ERR_CAPACITY
+    }
+    return;
+  }
+  const int n = total;
+  if (tid == 0) counters[0] = n;
+  if (n == 0) return;
+
+  OrdArrays A;
+  const bool inSmem = n <= kOrdSmemCap;
+  {
+    uint8_t* base = inSmem ? smem : gscratch;
+    const size_t cap = inSmem ? kOrdSmemCap : kCandCap;
+    const size_t qcap = inSmem ? kOrdQueueSmem : kOrdQueueGlobal;
+    A.ra = reinterpret_cast<uint32_t*>(base);
+    A.q[0] = reinterpret_cast<int2*>(base + cap * 4);
+    A.q[1] = A.q[0] + qcap;
+    uint8_t* u = base + cap * 4 + 2 * qcap * 8;
+    A.sc = reinterpret_cast<int*>(u);
+    A.lp = A.sc + cap;
+    A.rp = A.lp + cap;
+    // shared memory: the keys overlay sc/lp/rp (12 * cap bytes >= 8 * cap); global: their own region
+    A.keys = inSmem ? reinterpret_cast<uint64_t*>(u) : reinterpret_cast<uint64_t*>(u + cap * 12);
+  }
+  {
+    int pos = s_warp[warp] + incl - mine;
+    for (int w = w0; w < w1; ++w) {
+      unsigned bits = bitmap[w];
+      const int y = w / wordsPerRow, xb = (w - y * wordsPerRow) << 5;
+      while (bits) {
+        const int b = __ffs(bits) - 1;
+        bits &= bits - 1;
+        const uint32_t raster = (uint32_t)(y * W + xb + b);
+        A.sc[pos] = scores[raster];
+        A.ra[pos] = raster;
+        ++pos;
+      }
+    }
+  }
+  if (tid == 0) {
+    A.q[0][0] = make_int2(0, n);
+    s_qcount[0] = n > 16 ? 1 : 0;
+    s_qcount[1] = 0;
+  }
+  __syncthreads();
+
+  // ---- B. introsort partition phase, level by level ----
+  int depthLimit = 2 * (31 - __clz(n));
+  int cur = 0;
+  while (true) {
+    const int cnt = s_qcount[cur];
+    if (cnt == 0) break;
+    for (int s = warp; s < cnt; s += kOrdThreads / 32) {
+      const int2 r = A.q[cur][s];
+      if (depthLimit == 0) {
+        if (lane == 0) ord_heap_sort(A, r.x, r.y);
+        continue;
+      }
+      const int cut = ord_warp_partition(A, r.x, r.y, lane);
+      if (lane == 0) {
+        if (cut - r.x > 16) A.q[cur ^ 1][atomicAdd(&s_qcount[cur ^ 1], 1)] = make_int2(r.x, cut);
+        if (r.y - cut > 16) A.q[cur ^ 1][atomicAdd(&s_qcount[cur ^ 1], 1)] = make_int2(cut, r.y);
+      }
+    }
+    __syncthreads();
+    if (tid == 0) s_qcount[cur] = 0;
+    cur ^= 1;
+    --depthLimit;
+    __syncthreads();
+  }
+
+  // ---- C. __final_insertion_sort == stable sort by score (desc) of what the partitions left ----
+  int npad = 1;
+  while (npad < n) npad <<= 1;
+  if (inSmem) {
+    int mys[kOrdSmemCap / kOrdThreads];
+#pragma unroll
+    for (int k = 0; k < kOrdSmemCap / kOrdThreads; ++k) {
+      const int i = tid + k * kOrdThreads;
+      mys[k] = i < n ? A.sc[i] : 0;
+    }
+    __syncthreads();  // sc/lp/rp are dead from here on: the keys overlay them
+#pragma unroll
+    for (int k = 0; k < kOrdSmemCap / kOrdThreads; ++k) {
+      const int i = tid + k * kOrdThreads;
+      if (i < npad) A.keys[i] = i < n ? cand_key(mys[k], (uint32_t)i) : ~0ull;
+    }
+  } else {
+    for (int i = tid; i < npad; i += kOrdThreads) A.keys[i] = i < n ? cand_key(A.sc[i], (uint32_t)i) : ~0ull;
+  }
+  __syncthreads();
+  bitonic_sort(A.keys, npad);
+  for (int i = tid; i < n; i += kOrdThreads) {
+    const uint64_t k = A.keys[i];
+    cand[i] = cand_key(cand_score(k), A.ra[(uint32_t)k]);
+  }
+}
+
+constexpr size_t kOrdSmemBytes = (size_t)kOrdSmemCap * 4 + 2 * (size_t)kOrdQueueSmem * 8 + (size_t)kOrdSmemCap * 12;
+size_t order_scratch_bytes() {
+  return (size_t)kCandCap * 4 + 2 * (size_t)kOrdQueueGlobal * 8 + (size_t)kCandCap * 12 + (size_t)kCandCap * 8 + 256;
+}
+
+void launch_order_candidates(const int32_t* scores, const uint32_t* bitmap, uint64_t* cand, int* counters,
+                             uint8_t* gscratch, const DetectArgs& a, cudaStream_t s) {
+  static bool configured = false;
+  if (!configured) {
+    cudaFuncSetAttribute(order_candidates_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kOrdSmemBytes);
+    configured = true;
+  }
+  order_candidates_kernel<<<1, kOrdThreads, kOrdSmemBytes, s>>>(scores, bitmap, cand, counters, gscratch, a.width,
+                                                                 a.height);
+}
+
+// ----------------------------------------------------------------------------------------------
+// greedy uniformity + sub-pixel refinement: one CTA per image
+// ----------------------------------------------------------------------------------------------
+constexpr int kSelThreads = 1024;
 
 // Subpixel2D, scale-space-layer-inl.h:568-701. Returns only the deltas (the refined peak value is
 // computed and discarded by the caller in the reference, :403-411).
@@ -250,22 +545,7 @@ select_keypoints_kernel(const int32_t* __restrict__ scores, uint64_t* __restrict
     return;
   }
 
-  // ---- sort (std::sort by score desc; raster index breaks ties, see DESIGN.md "ties") ----
-  int npad = 1;
-  while (npad < n) npad <<= 1;
-  if (npad <= kSortSmemMax && npad * 8 <= smemBytes) {
-    uint64_t* keys = reinterpret_cast<uint64_t*>(smem);
-    for (int i = tid; i < npad; i += kSelThreads) keys[i] = i < n ? cand[i] : ~0ull;
-    __syncthreads();
-    bitonic_sort(keys, npad);
-    for (int i = tid; i < n; i += kSelThreads) cand[i] = keys[i];
-  } else {
-    for (int i = n + tid; i < npad; i += kSelThreads) cand[i] = ~0ull;
-    __syncthreads();
-    bitonic_sort(cand, npad);
-  }
-  __threadfence_block();
-  __syncthreads();
+  // cand[0..n) arrives in the reference's std::sort order (order_candidates_kernel)
 
   // ---- occupancy image: only [0, occRows) x [0, occCols) of the reference's (H*ceil+32)x(W*ceil+32) image is
   //      ever addressed (uniformity-enforcement-inl.h:75-86); keep it in shared memory when it fits ----

@@ -176,3 +176,40 @@ def cam_describe_ref_equal(mod, ctx, ref, img, rkp):
     cam.close()
     ext.close()
     return kd, dd
+
+
+def _ref_order(ref, scores):
+    import refbind
+    n = len(scores)
+    pts = np.zeros(n, refbind.PWS_DTYPE)
+    pts["score"] = scores
+    pts["x"] = np.arange(n) % 65536
+    pts["y"] = np.arange(n) // 65536
+    out = ref.std_sort(pts)
+    return out["y"].astype(np.int64) * 65536 + out["x"]
+
+
+def test_std_sort_reproduction(mod, ctx, ref):
+    """The device reproduces libstdc++ std::sort (tie order included) on tie-heavy, sorted, constant and
+    heapsort-triggering inputs, in shared memory (n <= 8192) and in the global-memory path."""
+    cam = mod.Camera(ctx, 752, 480, max_keypoints=64)
+    rng = np.random.default_rng(0)
+    cases = []
+    for trial in range(40):
+        n = int(rng.integers(0, 9000))
+        cases.append(rng.integers(0, int(rng.choice([2, 5, 50, 1000, 10 ** 6])), n))
+    for n in (1, 2, 16, 17, 18, 33, 8191, 8192, 8193, 30000, 131072):
+        cases.append(rng.integers(-50, 50, n))
+        cases.append(rng.integers(-2 ** 31, 2 ** 31 - 1, n))
+    cases += [np.arange(5000), np.arange(5000)[::-1].copy(), np.zeros(4000, np.int64)]
+    for n in (2000, 4096, 20000):  # median-of-3 killers: reach the depth limit -> heapsort fallback
+        k = n // 2
+        kill = np.zeros(n, np.int64)
+        i = np.arange(k)
+        kill[:k] = np.where(i % 2 == 0, i + 1, k + i + 1)
+        kill[k:] = 2 * (i + 1)
+        cases += [kill, -kill]
+    for sc in cases:
+        got = cam.debug_std_sort(sc).astype(np.int64)
+        assert np.array_equal(got, _ref_order(ref, sc)), "n=%d" % len(sc)
+    cam.close()
