@@ -240,7 +240,8 @@ def test_frame_pipeline_equals_separate_calls(mod, ctx, port, syn):
     times = cam.kernel_times()
     cam.frame_finish(window, 4)
     cam.kernel_timing(False)
-    assert [n for n, _ in times] == ["harris_nms", "select_keypoints", "border_filter+describe", "match_to_map"]
+    assert [n for n, _ in times] == ["harris_nms", "order_candidates", "select_keypoints", "border_filter+describe",
+                                       "match_to_map"]
     assert all(t > 0 for _, t in times)
     window.close()
     cam.close()
