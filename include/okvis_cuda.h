@@ -196,6 +196,35 @@ int okc_camera_frame_finish(okc_camera* cam, const okc_map_window* win, int num_
                             int capacity, int* n, uint8_t* descriptors, double* best_dist, int32_t* best_owner,
                             uint64_t* ctrs, double* repr_errors);
 
+/* ---- Batches: several images per launch chain. A batch has n_slots image slots; slot i carries an image of camera
+ * cams[i] (a camera may own several slots: frames of a sequence; or the slots are the cameras of one multiframe,
+ * okvis::MultiFrame, MultiFrame.hpp:307-312). One enqueue runs detect -> describe (-> matchToMap) for all slots with
+ * ONE kernel launch per stage (grid.z = slot), which is how the 148 SMs are kept busy by 0.36 MB images; several
+ * batches may be in flight at once (each owns a stream). Replaces the one-std::thread-per-camera fan-out of
+ * ThreadedSlam.cpp:676-708 and the per-camera loop of Frontend::matchToMap (Frontend.cpp:1519-1536). ---- */
+typedef struct okc_batch okc_batch;
+int okc_batch_create(okc_context* ctx, okc_camera* const* cams, int n_slots, okc_batch** batch);
+int okc_batch_destroy(okc_batch* batch);
+int okc_batch_size(const okc_batch* batch);
+/* images[i]: u8[H*W]; host memory (pinned buffers are DMA'd in place, pageable ones are staged) or, with
+ * images_on_device != 0, device memory. xp: n_slots describe parameter blocks (extraction direction per slot).
+ * windows == NULL: no map match; else windows[i] (may be NULL per slot), proj_xy[i] = double[2*num_landmarks] in
+ * host memory (or device memory with proj_on_device != 0), thresh_sq[i] = squared pixel gate of slot i. */
+int okc_batch_enqueue(okc_batch* batch, const uint8_t* const* images, int images_on_device,
+                      const okc_detect_params* dp, const okc_describe_params* xp,
+                      const okc_map_window* const* windows, const double* const* proj_xy, int proj_on_device,
+                      const double* thresh_sq, double hamming_threshold);
+/* Waits for the batch's stream and brings every slot's results to the host (two copies for the whole batch). */
+int okc_batch_finish(okc_batch* batch);
+/* After okc_batch_finish: what okc_detect_describe_finish / okc_match_to_map return, for one slot. */
+int okc_batch_slot_frame(okc_batch* batch, int slot, okc_keypoint* keypoints, int capacity, int* n,
+                         uint8_t* descriptors);
+int okc_batch_slot_matches(okc_batch* batch, int slot, int num_slices, double* best_dist, int32_t* best_owner,
+                           uint64_t* ctrs, double* repr_errors);
+void* okc_batch_stream(okc_batch* batch);
+int okc_debug_batch_kernel_timing(okc_batch* batch, int enable);
+int okc_debug_batch_kernel_times(okc_batch* batch, char* names, int names_cap, float* ms, int cap, int* n);
+
 /* Measurement hooks: the camera's cudaStream_t (to bracket enqueued work with CUDA events from a harness), and
  * per-kernel device times of the last frame enqueued while timing was enabled (CUDA events around every launch on
  * the camera's stream). names: '\n'-separated kernel labels. */

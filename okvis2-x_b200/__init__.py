@@ -31,7 +31,9 @@ EXPORTS = [
     "okc_match_to_map", "okc_match_stereo", "okc_match_to_map_uninitialised",
     "okc_detect_describe_enqueue_device", "okc_map_window_create", "okc_map_window_destroy",
     "okc_camera_match_to_map_enqueue", "okc_camera_frame_finish", "okc_camera_stream", "okc_debug_kernel_timing",
-    "okc_debug_kernel_times",
+    "okc_debug_kernel_times", "okc_batch_create", "okc_batch_destroy", "okc_batch_size", "okc_batch_enqueue",
+    "okc_batch_finish", "okc_batch_slot_frame", "okc_batch_slot_matches", "okc_batch_stream",
+    "okc_debug_batch_kernel_timing", "okc_debug_batch_kernel_times",
 ]
 
 
@@ -97,6 +99,17 @@ def lib():
         L.okc_camera_stream.restype = vp
         L.okc_debug_kernel_timing.argtypes = [vp, i]
         L.okc_debug_kernel_times.argtypes = [vp, vp, i, vp, i, C.POINTER(i)]
+        L.okc_batch_create.argtypes = [vp, vp, i, C.POINTER(vp)]
+        L.okc_batch_destroy.argtypes = [vp]
+        L.okc_batch_size.argtypes = [vp]
+        L.okc_batch_enqueue.argtypes = [vp, vp, i, C.POINTER(DetectParams), vp, vp, vp, i, vp, d]
+        L.okc_batch_finish.argtypes = [vp]
+        L.okc_batch_slot_frame.argtypes = [vp, i, vp, i, C.POINTER(i), vp]
+        L.okc_batch_slot_matches.argtypes = [vp, i, i, vp, vp, vp, vp]
+        L.okc_batch_stream.argtypes = [vp]
+        L.okc_batch_stream.restype = vp
+        L.okc_debug_batch_kernel_timing.argtypes = [vp, i]
+        L.okc_debug_batch_kernel_times.argtypes = [vp, vp, i, vp, i, C.POINTER(i)]
         _lib = L
     return _lib
 
@@ -372,3 +385,98 @@ class Camera:
         _check(lib().okc_debug_candidates(self.h, _p(img), int(abs_threshold), _p(out), cap, C.byref(n)),
                "okc_debug_candidates")
         return out[:n.value].copy()
+
+
+class Batch:
+    """n_slots images per launch chain (cameras of a multiframe and/or frames of a sequence); see okvis_cuda.h."""
+
+    def __init__(self, ctx, cams):
+        self.ctx, self.cams, self.n = ctx, list(cams), len(cams)
+        self.max_kp = cams[0].max_kp
+        arr = (C.c_void_p * self.n)(*[c.h for c in cams])
+        self.h = C.c_void_p()
+        _check(lib().okc_batch_create(ctx.h, arr, self.n, C.byref(self.h)), "okc_batch_create")
+        self._xp = (DescribeParams * self.n)()
+        self._img = (C.c_void_p * self.n)()
+        self._win = (C.c_void_p * self.n)()
+        self._proj = (C.c_void_p * self.n)()
+        self._gate = (C.c_double * self.n)()
+        self._keep = None
+
+    def close(self):
+        if self.h:
+            lib().okc_batch_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def enqueue(self, images, radius, octaves, abs_threshold, max_kpt, directions, rotation_invariant=True,
+                images_on_device=False, windows=None, proj=None, gates=None, hamming_threshold=60.0,
+                proj_on_device=False):
+        """images: n arrays (host) or n device addresses; directions: n 3-vectors; windows/proj/gates: per slot."""
+        keep = []
+        for k in range(self.n):
+            if images_on_device:
+                self._img[k] = int(images[k])
+            else:
+                a = images[k]
+                if isinstance(a, np.ndarray):
+                    a = self.cams[k]._img(a)
+                    keep.append(a)
+                    self._img[k] = a.ctypes.data
+                else:
+                    self._img[k] = int(a)  # raw host address (e.g. a pinned torch tensor's data_ptr())
+            self._xp[k].rotation_invariant = int(rotation_invariant)
+            self._xp[k].scale_invariant = 0
+            self._xp[k].extraction_direction[:] = [float(v) for v in directions[k]]
+        dp = DetectParams(float(radius), int(octaves), float(abs_threshold), int(max_kpt))
+        if windows is None:
+            _check(lib().okc_batch_enqueue(self.h, self._img, int(images_on_device), C.byref(dp), self._xp, None, None,
+                                           0, None, float(hamming_threshold)), "okc_batch_enqueue")
+        else:
+            for k in range(self.n):
+                self._win[k] = windows[k].h if windows[k] is not None else None
+                if proj_on_device or not isinstance(proj[k], np.ndarray):
+                    self._proj[k] = int(proj[k])
+                else:
+                    p = np.ascontiguousarray(proj[k], np.float64)
+                    keep.append(p)
+                    self._proj[k] = p.ctypes.data
+                self._gate[k] = float(gates[k])
+            _check(lib().okc_batch_enqueue(self.h, self._img, int(images_on_device), C.byref(dp), self._xp, self._win,
+                                           self._proj, int(proj_on_device), self._gate, float(hamming_threshold)),
+                   "okc_batch_enqueue")
+        self._keep = keep  # host buffers stay alive until finish()
+
+    def finish(self):
+        _check(lib().okc_batch_finish(self.h), "okc_batch_finish")
+        self._keep = None
+
+    def slot_frame(self, slot):
+        kp = np.empty(self.max_kp, KP_DTYPE)
+        desc = np.empty((self.max_kp, 48), np.uint8)
+        n = C.c_int(0)
+        _check(lib().okc_batch_slot_frame(self.h, slot, _p(kp), self.max_kp, C.byref(n), _p(desc)),
+               "okc_batch_slot_frame")
+        return kp[:n.value], desc[:n.value]
+
+    def slot_matches(self, slot, nk, num_slices=4):
+        bd = np.empty(self.max_kp, np.float64)
+        bo = np.empty(self.max_kp, np.int32)
+        ctrs = np.zeros(num_slices, np.uint64)
+        errs = np.zeros(num_slices, np.float64)
+        _check(lib().okc_batch_slot_matches(self.h, slot, int(num_slices), _p(bd), _p(bo), _p(ctrs), _p(errs)),
+               "okc_batch_slot_matches")
+        return bd[:nk], bo[:nk], ctrs, errs
+
+    def stream(self):
+        return lib().okc_batch_stream(self.h)
+
+    def kernel_timing(self, enable):
+        _check(lib().okc_debug_batch_kernel_timing(self.h, int(bool(enable))), "okc_debug_batch_kernel_timing")
+
+    def kernel_times(self):
+        names = C.create_string_buffer(512)
+        ms = np.zeros(16, np.float32)
+        n = C.c_int(0)
+        _check(lib().okc_debug_batch_kernel_times(self.h, names, 512, _p(ms), 16, C.byref(n)),
+               "okc_debug_batch_kernel_times")
+        return list(zip(names.value.decode().split("\n"), [float(v) for v in ms[:n.value]])) if n.value else []

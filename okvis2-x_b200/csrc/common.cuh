@@ -38,18 +38,40 @@ struct PatternTables {
   int basicscale;
 };
 
-struct DeviceImageScratch {
-  uint8_t* image;          // H*W
-  int32_t* scores;         // H*W
-  uint64_t* cand;          // kCandCap keys (std::sort order) + max_keypoints kept keys
+// One image of a batch ("slot"). Every kernel of the path is launched once per BATCH and indexes its slot with
+// blockIdx (.z for the tiled kernels, .x for the one-CTA-per-image kernels), so that a multi-camera frame or several
+// frames of a sequence fill the 148 SMs with one launch chain. The array lives in device memory; all pointers are
+// fixed at batch creation except the ones marked (per enqueue), which the host refreshes with one small H2D copy.
+struct Slot {
+  // detect
+  const uint8_t* image;    // (per enqueue) H*W u8: the slot's own upload buffer or a caller's device image
+  int32_t* scores;         // H*W Harris scores
   uint32_t* bitmap;        // H * ceil(W/32) words: NMS survivors
-  uint8_t* order_scratch;  // order_candidates_kernel arrays when the candidates do not fit in shared memory
-  int* counters;           // [0]=candidate count, [1]=kept count, [2]=described count, [3]=overflow flag
+  uint64_t* cand;          // kCandCap keys (std::sort order) + max_keypoints kept keys
+  uint8_t* order_scratch;  // order_candidates arrays when the candidates do not fit in shared memory
   uint8_t* occupancy;      // global fallback for the uniformity occupancy image
-  size_t occupancy_bytes;
+  int* counters;           // [0]=candidates [1]=kept [2]=described [3]=overflow flag [4]=match events
   okc_keypoint* kp_detect; // max_keypoints
-  okc_keypoint* kp_desc;   // max_keypoints (after border filter)
-  uint8_t* desc;           // max_keypoints * 48
+  // describe
+  okc_keypoint* kp_desc;   // max_keypoints (after the border filter)   } in the batch's output arena
+  uint8_t* desc;           // max_keypoints * 48                        }
+  const float* rays;       // camera-awareness maps of the slot's camera (or null)
+  const float* jac;
+  float inv_f;             // 1.0f / virtualFocalLength_
+  int camera_aware;
+  // map match (frame pipeline)
+  const uint8_t* map;      // (per enqueue) descriptor pool rows
+  const int* owner;        // (per enqueue) row -> landmark slot
+  const double* proj;      // (per enqueue) landmark projections of this frame
+  double thresh_sq;        // (per enqueue)
+  int nm;                  // (per enqueue) rows in the pool (map == null: no match for this slot)
+  int event_slab;          // events [0, slab) live in the output arena, the rest in events_overflow
+  int event_cap;
+  double* best_dist;       // max_keypoints   } output arena
+  int* best_owner;         // max_keypoints   }
+  unsigned long long* events;
+  unsigned long long* events_overflow;
+  float dir[3];            // (per enqueue) extraction direction (gravity in this camera's frame)
 };
 
 struct DetectArgs {
@@ -63,20 +85,17 @@ struct DetectArgs {
 struct DescribeArgs {
   int width, height;
   int rotation_invariant;
-  int camera_aware;
-  float dir[3];
-  float inv_f;             // 1.0f / virtualFocalLength_
 };
 
-void launch_harris_nms(const uint8_t* image, int32_t* scores, uint32_t* bitmap, const DetectArgs& a, cudaStream_t s);
+// All launchers: `slots` = device array, `n` = number of slots in this launch.
+void launch_harris_nms(const Slot* slots, int n, const DetectArgs& a, cudaStream_t s);
 size_t order_scratch_bytes();
-void launch_order_candidates(const int32_t* scores, const uint32_t* bitmap, uint64_t* cand, int* counters,
-                             uint8_t* gscratch, const DetectArgs& a, cudaStream_t s);
-void launch_select_keypoints(const int32_t* scores, uint64_t* cand, int* counters, uint8_t* occ_global,
-                             const float* lut, okc_keypoint* out, const DetectArgs& a, cudaStream_t s);
-void launch_describe(const uint8_t* image, const okc_keypoint* kp_in, const int* n_in, okc_keypoint* kp_out,
-                     uint8_t* desc, int* counters, const float* rays, const float* jac, const PatternTables& t,
-                     const DescribeArgs& a, int max_kp, cudaStream_t s);
+void launch_order_candidates(const Slot* slots, int n, const DetectArgs& a, cudaStream_t s);
+void launch_select_keypoints(const Slot* slots, int n, const float* lut, const DetectArgs& a, cudaStream_t s);
+// kp_from_detect: describe the keypoints the detector left in kp_detect (count = counters[1])
+void launch_describe(const Slot* slots, int n, const PatternTables& t, const DescribeArgs& a, int max_kp,
+                     cudaStream_t s);
+void launch_match_to_map_slots(const Slot* slots, int n, int max_kp, double hammingThreshold, cudaStream_t s);
 
 void set_error(const char* fmt, ...);
 

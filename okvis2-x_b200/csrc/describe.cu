@@ -16,13 +16,15 @@ namespace okc {
 constexpr int kWarpsPerBlock = 8;
 
 // ---- border filter: ordered compaction (brisk-descriptor-extractor.cc:601-627, RoiPredicate :537-541) ----
-__global__ void __launch_bounds__(1024) border_filter_kernel(const okc_keypoint* __restrict__ in,
-                                                             const int* __restrict__ n_in_ptr,
-                                                             okc_keypoint* __restrict__ out, int* __restrict__ counters,
-                                                             int W, int H, int border, int maxOut) {
+__global__ void __launch_bounds__(1024) border_filter_kernel(const Slot* __restrict__ slots, int W, int H, int border,
+                                                             int maxOut) {
+  const Slot& slot = slots[blockIdx.x];
+  const okc_keypoint* __restrict__ in = slot.kp_detect;
+  okc_keypoint* __restrict__ out = slot.kp_desc;
+  int* __restrict__ counters = slot.counters;
   __shared__ int s_warpcnt[32], s_warpoff[32], s_total;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int n = *n_in_ptr;
+  const int n = counters[1];
   const float minX = (float)border, minY = (float)border, maxX = (float)(W - border), maxY = (float)(H - border);
   int base_out = 0;
   for (int base = 0; base < n; base += 1024) {
@@ -178,14 +180,18 @@ __device__ __forceinline__ float jhypot(float a, float b) {
 }
 
 __global__ void __launch_bounds__(kWarpsPerBlock * 32)
-describe_kernel(const uint8_t* __restrict__ img, okc_keypoint* __restrict__ kps, uint8_t* __restrict__ desc,
-                const int* __restrict__ counters, const float* __restrict__ rays, const float* __restrict__ jac,
-                const PatternPoint* __restrict__ pattern, const uchar2* __restrict__ short_pairs,
-                const LongPair* __restrict__ long_pairs, DescribeArgs a) {
+describe_kernel(const Slot* __restrict__ slots, const PatternPoint* __restrict__ pattern,
+                const uchar2* __restrict__ short_pairs, const LongPair* __restrict__ long_pairs, DescribeArgs a) {
+  const Slot& slot = slots[blockIdx.z];
+  const uint8_t* __restrict__ img = slot.image;
+  okc_keypoint* __restrict__ kps = slot.kp_desc;
+  uint8_t* __restrict__ desc = slot.desc;
+  const float* __restrict__ rays = slot.rays;
+  const float* __restrict__ jac = slot.jac;
   __shared__ int s_values[kWarpsPerBlock][kPoints + 2];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int k = blockIdx.x * kWarpsPerBlock + warp;
-  if (k >= counters[2]) return;
+  if (k >= slot.counters[2]) return;
   int* values = s_values[warp];
   const int W = a.width, H = a.height;
 
@@ -196,7 +202,7 @@ describe_kernel(const uint8_t* __restrict__ img, okc_keypoint* __restrict__ kps,
   bool warped = false, directional = false;
   float warp4[4] = {0.f, 0.f, 0.f, 0.f};
   float sigmaScale = 1.0f;
-  if (a.camera_aware) {
+  if (slot.camera_aware) {
     const int x0 = (int)floorf(x), y0 = (int)floorf(y);
     const float dx = x - (float)x0, dy = y - (float)y0;
     const float w_tl = (1.0f - dx) * (1.0f - dy);
@@ -217,13 +223,13 @@ describe_kernel(const uint8_t* __restrict__ img, okc_keypoint* __restrict__ kps,
       float dir[3];
       for (int i = 0; i < 3; ++i) dir[i] = ((w_tl * d_tl[i] + w_tr * d_tr[i]) + w_bl * d_bl[i]) + w_br * d_br[i];
       float eu[3], ev[3], t[3];
-      cross3f(a.dir, dir, eu);
+      cross3f(slot.dir, dir, eu);
       if ((double)(eu[0] * eu[0] + eu[1] * eu[1] + eu[2] * eu[2]) > 0.01) directional = true;
       cv_normalize3(eu, t);
-      for (int i = 0; i < 3; ++i) eu[i] = t[i] * a.inv_f;
+      for (int i = 0; i < 3; ++i) eu[i] = t[i] * slot.inv_f;
       cross3f(dir, eu, t);
       cv_normalize3(t, ev);
-      for (int i = 0; i < 3; ++i) ev[i] = ev[i] * a.inv_f;
+      for (int i = 0; i < 3; ++i) ev[i] = ev[i] * slot.inv_f;
       const int xm = (int)roundf(x), ym = (int)roundf(y);
       const float* jp = jac + ((size_t)ym * W + xm) * 6;
       float J[6];
@@ -306,13 +312,11 @@ describe_kernel(const uint8_t* __restrict__ img, okc_keypoint* __restrict__ kps,
   if (lane == 0) kps[k].angle = kp.angle;
 }
 
-void launch_describe(const uint8_t* image, const okc_keypoint* kp_in, const int* n_in, okc_keypoint* kp_out,
-                     uint8_t* desc, int* counters, const float* rays, const float* jac, const PatternTables& t,
-                     const DescribeArgs& a, int max_kp, cudaStream_t s) {
-  border_filter_kernel<<<1, 1024, 0, s>>>(kp_in, n_in, kp_out, counters, a.width, a.height, t.border, max_kp);
-  const int blocks = (max_kp + kWarpsPerBlock - 1) / kWarpsPerBlock;
-  describe_kernel<<<blocks, kWarpsPerBlock * 32, 0, s>>>(image, kp_out, desc, counters, rays, jac, t.points,
-                                                         t.short_pairs, t.long_pairs, a);
+void launch_describe(const Slot* slots, int n, const PatternTables& t, const DescribeArgs& a, int max_kp,
+                     cudaStream_t s) {
+  border_filter_kernel<<<n, 1024, 0, s>>>(slots, a.width, a.height, t.border, max_kp);
+  dim3 grid((max_kp + kWarpsPerBlock - 1) / kWarpsPerBlock, 1, n);
+  describe_kernel<<<grid, kWarpsPerBlock * 32, 0, s>>>(slots, t.points, t.short_pairs, t.long_pairs, a);
 }
 
 }  // namespace okc

@@ -25,9 +25,12 @@ constexpr int PXW = TX + 6, PXH = TY + 6;   // pixel tile, halo 3
 constexpr int PRW = TX + 4, PRH = TY + 4;   // gradient-product tile, halo 2
 constexpr int SCW = TX + 2, SCH = TY + 2;   // score tile, halo 1 (NMS neighbours)
 
-__global__ void __launch_bounds__(256) harris_nms_kernel(const uint8_t* __restrict__ img, int32_t* __restrict__ scores,
-                                                         uint32_t* __restrict__ bitmap, int W, int H,
+__global__ void __launch_bounds__(256) harris_nms_kernel(const Slot* __restrict__ slots, int W, int H,
                                                          int absThreshold) {
+  const Slot& slot = slots[blockIdx.z];
+  const uint8_t* __restrict__ img = slot.image;
+  int32_t* __restrict__ scores = slot.scores;
+  uint32_t* __restrict__ bitmap = slot.bitmap;
   __shared__ uint8_t px[PXH][PXW + 2];
   __shared__ short pxx[PRH][PRW], pxy[PRH][PRW], pyy[PRH][PRW];
   __shared__ int sc[SCH][SCW];
@@ -113,9 +116,9 @@ __global__ void __launch_bounds__(256) harris_nms_kernel(const uint8_t* __restri
   }
 }
 
-void launch_harris_nms(const uint8_t* image, int32_t* scores, uint32_t* bitmap, const DetectArgs& a, cudaStream_t s) {
-  dim3 grid((a.width + TX - 1) / TX, (a.height + TY - 1) / TY);
-  harris_nms_kernel<<<grid, dim3(32, 8), 0, s>>>(image, scores, bitmap, a.width, a.height, a.abs_threshold);
+void launch_harris_nms(const Slot* slots, int n, const DetectArgs& a, cudaStream_t s) {
+  dim3 grid((a.width + TX - 1) / TX, (a.height + TY - 1) / TY, n);
+  harris_nms_kernel<<<grid, dim3(32, 8), 0, s>>>(slots, a.width, a.height, a.abs_threshold);
 }
 
 __device__ __forceinline__ void bitonic_sort(uint64_t* keys, int npad) {
@@ -278,9 +281,13 @@ __device__ int ord_warp_partition(const OrdArrays& A, int f, int l, int lane) {
 }
 
 __global__ void __launch_bounds__(kOrdThreads, 1)
-order_candidates_kernel(const int32_t* __restrict__ scores, const uint32_t* __restrict__ bitmap,
-                        uint64_t* __restrict__ cand, int* __restrict__ counters, uint8_t* __restrict__ gscratch,
-                        int W, int H) {
+order_candidates_kernel(const Slot* __restrict__ slots, int W, int H) {
+  const Slot& slot = slots[blockIdx.x];
+  const int32_t* __restrict__ scores = slot.scores;
+  const uint32_t* __restrict__ bitmap = slot.bitmap;
+  uint64_t* __restrict__ cand = slot.cand;
+  int* __restrict__ counters = slot.counters;
+  uint8_t* __restrict__ gscratch = slot.order_scratch;
   extern __shared__ __align__(16) uint8_t smem[];
   __shared__ int s_warp[32];
   __shared__ int s_n, s_qcount[2];
@@ -417,15 +424,13 @@ size_t order_scratch_bytes() {
   return (size_t)kCandCap * 4 + 2 * (size_t)kOrdQueueGlobal * 8 + (size_t)kCandCap * 12 + (size_t)kCandCap * 8 + 256;
 }
 
-void launch_order_candidates(const int32_t* scores, const uint32_t* bitmap, uint64_t* cand, int* counters,
-                             uint8_t* gscratch, const DetectArgs& a, cudaStream_t s) {
+void launch_order_candidates(const Slot* slots, int n, const DetectArgs& a, cudaStream_t s) {
   static bool configured = false;
   if (!configured) {
     cudaFuncSetAttribute(order_candidates_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kOrdSmemBytes);
     configured = true;
   }
-  order_candidates_kernel<<<1, kOrdThreads, kOrdSmemBytes, s>>>(scores, bitmap, cand, counters, gscratch, a.width,
-                                                                 a.height);
+  order_candidates_kernel<<<n, kOrdThreads, kOrdSmemBytes, s>>>(slots, a.width, a.height);
 }
 
 // ----------------------------------------------------------------------------------------------
@@ -525,10 +530,14 @@ __device__ void subpixel2d(double s_0_0, double s_0_1, double s_0_2, double s_1_
 }
 
 __global__ void __launch_bounds__(kSelThreads, 1)
-select_keypoints_kernel(const int32_t* __restrict__ scores, uint64_t* __restrict__ cand, int* __restrict__ counters,
-                        uint8_t* __restrict__ occ_global, const float* __restrict__ lut_global,
-                        okc_keypoint* __restrict__ out, int W, int H, float scaling, unsigned long long maxKpt,
-                        int maxOut, int smemBytes) {
+select_keypoints_kernel(const Slot* __restrict__ slots, const float* __restrict__ lut_global, int W, int H,
+                        float scaling, unsigned long long maxKpt, int maxOut, int smemBytes) {
+  const Slot& slot = slots[blockIdx.x];
+  const int32_t* __restrict__ scores = slot.scores;
+  uint64_t* __restrict__ cand = slot.cand;
+  int* __restrict__ counters = slot.counters;
+  uint8_t* __restrict__ occ_global = slot.occupancy;
+  okc_keypoint* __restrict__ out = slot.kp_detect;
   extern __shared__ __align__(16) uint8_t smem[];
   __shared__ float lut[31 * 31];
   __shared__ int s_off[kSelThreads];
@@ -659,8 +668,7 @@ select_keypoints_kernel(const int32_t* __restrict__ scores, uint64_t* __restrict
 
 static int g_select_smem = 0;
 
-void launch_select_keypoints(const int32_t* scores, uint64_t* cand, int* counters, uint8_t* occ_global,
-                             const float* lut, okc_keypoint* out, const DetectArgs& a, cudaStream_t s) {
+void launch_select_keypoints(const Slot* slots, int n, const float* lut, const DetectArgs& a, cudaStream_t s) {
   if (g_select_smem == 0) {
     int dev = 0, maxOptin = 0;
     cudaGetDevice(&dev);
@@ -670,9 +678,14 @@ void launch_select_keypoints(const int32_t* scores, uint64_t* cand, int* counter
     g_select_smem = (maxOptin - (int)fa.sharedSizeBytes - 1024) & ~15;  // dynamic part beside the static arrays
     cudaFuncSetAttribute(select_keypoints_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, g_select_smem);
   }
-  select_keypoints_kernel<<<1, kSelThreads, g_select_smem, s>>>(scores, cand, counters, occ_global, lut, out, a.width,
-                                                                a.height, a.scaling, a.max_kpt, a.max_out,
-                                                                g_select_smem);
+  // only as much dynamic shared memory as the occupancy image needs (more CTAs per SM when several images
+  // are selected at once); the global fallback is used when it does not fit
+  const size_t occRows = (size_t)((float)(a.height - 3) * a.scaling + 16.0f) + 17;
+  const size_t occStride = (((size_t)((float)(a.width - 3) * a.scaling + 16.0f) + 17) + 15) & ~(size_t)15;
+  size_t want = occRows * occStride;
+  int smem = want <= (size_t)g_select_smem ? (int)((want + 15) & ~(size_t)15) : 0;
+  select_keypoints_kernel<<<n, kSelThreads, smem, s>>>(slots, lut, a.width, a.height, a.scaling, a.max_kpt, a.max_out,
+                                                       smem);
 }
 
 }  // namespace okc

@@ -170,13 +170,16 @@ __device__ __forceinline__ unsigned hamming384(const unsigned a[kDescWords], con
 // reference's iteration order for a fixed k). Every improvement of the running minimum is an "event"; the
 // events (k, m) are appended to a list so that the host adapter can rebuild ctrs[] / reprErrors[] in the
 // reference's accumulation order.
-__global__ void __launch_bounds__(256)
-match_to_map_kernel(const uint8_t* __restrict__ queries, const double* __restrict__ kp_xy,
+__device__ __forceinline__ void
+match_to_map_body(const uint8_t* __restrict__ queries, const double* __restrict__ kp_xy,
                     const okc_keypoint* __restrict__ kp_f, const uint8_t* __restrict__ use, int nkMax,
                     const int* __restrict__ nkDev, const uint8_t* __restrict__ map,
                     const int* __restrict__ owner, int nm, const double* __restrict__ proj_xy, double threshSq,
                     double hammingThreshold, double* __restrict__ bestDist, int* __restrict__ bestOwner,
-                    unsigned long long* __restrict__ events, int eventCap, int* __restrict__ eventCount) {
+                    unsigned long long* __restrict__ events, int eventSlab,
+                    unsigned long long* __restrict__ eventsOverflow, int eventCap, int* __restrict__ eventCount) {
+  // events [0, eventSlab) go to `events` (the part of the output block that always travels to the host), the rest up
+  // to eventCap to `eventsOverflow` (fetched only when needed)
   const int lane = threadIdx.x & 31;
   const int k = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   // nkDev: the keypoint count is still on the device (frame pipeline: queries are the camera's own descriptors)
@@ -213,7 +216,9 @@ match_to_map_kernel(const uint8_t* __restrict__ queries, const double* __restric
           bestO = oc;
           if (lane == 0) {
             const int e = atomicAdd(eventCount, 1);
-            if (e < eventCap) events[e] = ((unsigned long long)(unsigned)(base + src) << 32) | (unsigned)k;
+            const unsigned long long ev = ((unsigned long long)(unsigned)(base + src) << 32) | (unsigned)k;
+            if (e < eventSlab) events[e] = ev;
+            else if (e < eventCap) eventsOverflow[e - eventSlab] = ev;
           }
         }
       }
@@ -223,6 +228,35 @@ match_to_map_kernel(const uint8_t* __restrict__ queries, const double* __restric
     bestDist[k] = best;
     bestOwner[k] = bestO;
   }
+}
+
+__global__ void __launch_bounds__(256)
+match_to_map_kernel(const uint8_t* __restrict__ queries, const double* __restrict__ kp_xy,
+                    const okc_keypoint* __restrict__ kp_f, const uint8_t* __restrict__ use, int nkMax,
+                    const int* __restrict__ nkDev, const uint8_t* __restrict__ map, const int* __restrict__ owner,
+                    int nm, const double* __restrict__ proj_xy, double threshSq, double hammingThreshold,
+                    double* __restrict__ bestDist, int* __restrict__ bestOwner, unsigned long long* __restrict__ events,
+                    int eventCap, int* __restrict__ eventCount) {
+  match_to_map_body(queries, kp_xy, kp_f, use, nkMax, nkDev, map, owner, nm, proj_xy, threshSq, hammingThreshold,
+                    bestDist, bestOwner, events, eventCap, nullptr, eventCap, eventCount);
+}
+
+// Frame-pipeline form: one launch for all slots of a batch; queries are the slot's own descriptors / keypoints of
+// the frame just described (count still on the device), every keypoint unassociated.
+__global__ void __launch_bounds__(256)
+match_to_map_slots_kernel(const Slot* __restrict__ slots, int maxKp, double hammingThreshold) {
+  const Slot& slot = slots[blockIdx.z];
+  if (slot.map == nullptr) return;  // no map match requested for this slot
+  match_to_map_body(slot.desc, nullptr, slot.kp_desc, nullptr, maxKp, slot.counters + 2, slot.map, slot.owner, slot.nm,
+                    slot.proj, slot.thresh_sq, hammingThreshold, slot.best_dist, slot.best_owner, slot.events,
+                    slot.event_slab, slot.events_overflow, slot.event_cap, slot.counters + 4);
+}
+
+void launch_match_to_map_slots(const Slot* slots, int n, int max_kp, double hammingThreshold, cudaStream_t s) {
+  if (n <= 0 || max_kp <= 0) return;
+  const int warpsPerBlock = 8;
+  dim3 grid((max_kp + warpsPerBlock - 1) / warpsPerBlock, 1, n);
+  match_to_map_slots_kernel<<<grid, warpsPerBlock * 32, 0, s>>>(slots, max_kp, hammingThreshold);
 }
 
 void launch_match_to_map(const uint8_t* queries, const double* kp_xy, const okc_keypoint* kp_f, const uint8_t* use,

@@ -245,3 +245,70 @@ def test_frame_pipeline_equals_separate_calls(mod, ctx, port, syn):
     assert all(t > 0 for _, t in times)
     window.close()
     cam.close()
+
+
+@pytest.mark.parametrize("on_device", [False, True])
+def test_batch_equals_single_calls(on_device, mod, ctx, port, syn):
+    """A batch of 6 slots (3 stereo frames of a sequence: cam0, cam1, cam0, ...) == the single-camera entry points,
+    slot by slot, with and without the map match; host (pageable / pinned) and device inputs."""
+    import torch
+    W, H = 752, 480
+    cams = []
+    for c in syn.EUROC["cams"]:
+        rays, jac = syn.camera_maps(W, H, c["f"], c["c"], c["d"])
+        cams.append(mod.Camera(ctx, W, H, rays, jac, focal=c["f"][0], max_keypoints=768))
+    left, right, shift = syn.stereo_sequence(3, W, H, seed=2)
+    imgs = [left[0], right[0], left[1], right[1], left[2], right[2]]
+    slot_cams = [cams[k % 2] for k in range(6)]
+    dirs = [(0.05, 0.99, 0.1) if k % 2 == 0 else (-0.02, 0.98, 0.15) for k in range(6)]
+    single = [slot_cams[k].detect_describe(imgs[k], 38.0, 0, 150.0, 700, direction=dirs[k]) for k in range(6)]
+    wins_h = []
+    for cam_i in range(2):
+        kp, desc = single[cam_i]
+        kp_xy = np.stack([kp["x"], kp["y"]], 1).astype(np.float64)
+        wins_h.append(syn.sequence_window(desc, kp_xy, shift, 1500, 7 + cam_i, W, H))
+    wins = [mod.MapWindow(ctx, r, o, p.shape[1]) for r, o, p in wins_h]
+    gates = [(3.0 + 0.5 * (c["f"][0] + c["f"][1]) * 0.06) ** 2 for c in syn.EUROC["cams"]]
+    batch = mod.Batch(ctx, slot_cams)
+    keep = []
+    if on_device:
+        d = [torch.from_numpy(i).cuda() for i in imgs]
+        dp = [torch.from_numpy(np.ascontiguousarray(wins_h[k % 2][2][k // 2])).cuda() for k in range(6)]
+        torch.cuda.synchronize()
+        keep = [d, dp]
+        img_arg, proj_arg = [t.data_ptr() for t in d], [t.data_ptr() for t in dp]
+    else:
+        pinned = torch.from_numpy(imgs[1]).pin_memory()   # one pinned source among pageable ones
+        keep = [pinned]
+        img_arg = [imgs[0], pinned.data_ptr()] + imgs[2:]
+        proj_arg = [np.ascontiguousarray(wins_h[k % 2][2][k // 2]) for k in range(6)]
+    # without the map match
+    batch.enqueue(img_arg, 38.0, 0, 150.0, 700, dirs, images_on_device=on_device)
+    batch.finish()
+    for k in range(6):
+        kp, desc = batch.slot_frame(k)
+        assert kp.tobytes() == single[k][0].tobytes() and np.array_equal(desc, single[k][1]), k
+    # with it, twice (idempotent handles)
+    for rep in range(2):
+        batch.enqueue(img_arg, 38.0, 0, 150.0, 700, dirs, images_on_device=on_device,
+                      windows=[wins[k % 2] for k in range(6)], proj=proj_arg, gates=[gates[k % 2] for k in range(6)],
+                      proj_on_device=on_device)
+        batch.finish()
+        for k in range(6):
+            kp, desc = batch.slot_frame(k)
+            assert kp.tobytes() == single[k][0].tobytes() and np.array_equal(desc, single[k][1]), k
+            bd, bo, ctrs, errs = batch.slot_matches(k, len(kp), 4)
+            rows, owner, proj = wins_h[k % 2]
+            kp_xy = np.stack([kp["x"], kp["y"]], 1).astype(np.float64)
+            pd, po, pc, pe = port.match_to_map(desc, kp_xy, np.ones(len(kp), np.uint8), rows, owner, proj[k // 2], None,
+                                               gates[k % 2], 60.0, 4)
+            assert np.array_equal(bd, pd) and np.array_equal(bo, po) and np.array_equal(ctrs, pc), k
+            assert errs.tobytes() == pe.tobytes(), k
+            if k < 2:
+                assert (bo >= 0).sum() > 100
+    batch.close()
+    for w in wins:
+        w.close()
+    for c in cams:
+        c.close()
+    del keep
