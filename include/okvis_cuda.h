@@ -188,13 +188,15 @@ int okc_map_window_destroy(okc_map_window* win);
 
 /* Frontend::matchToMapByThread (Frontend.cpp:1744-1827) of the frame last enqueued on `cam` against `win`, on the
  * camera's stream. proj_xy: double[2*num_landmarks] landmark projections for this frame's pose, in host memory
- * (proj_on_device == 0; copied) or already in device memory (proj_on_device != 0). */
+ * (proj_on_device == 0; copied) or already in device memory (proj_on_device != 0). num_slices =
+ * num_matching_threads (<= 64): ctrs[] / repr_errors[] are accumulated per thread slice, in the reference's order, by a
+ * kernel (match_stats) - the improvement events never leave the device. */
 int okc_camera_match_to_map_enqueue(okc_camera* cam, const okc_map_window* win, const double* proj_xy,
-                                    int proj_on_device, double thresh_sq, double hamming_threshold);
+                                    int proj_on_device, double thresh_sq, double hamming_threshold, int num_slices);
 /* Waits for the camera's stream, then returns what okc_detect_describe_finish and okc_match_to_map return. */
-int okc_camera_frame_finish(okc_camera* cam, const okc_map_window* win, int num_slices, okc_keypoint* keypoints,
-                            int capacity, int* n, uint8_t* descriptors, double* best_dist, int32_t* best_owner,
-                            uint64_t* ctrs, double* repr_errors);
+int okc_camera_frame_finish(okc_camera* cam, const okc_map_window* win, okc_keypoint* keypoints, int capacity, int* n,
+                            uint8_t* descriptors, double* best_dist, int32_t* best_owner, uint64_t* ctrs,
+                            double* repr_errors);
 
 /* ---- Batches: several images per launch chain. A batch has n_slots image slots; slot i carries an image of camera
  * cams[i] (a camera may own several slots: frames of a sequence; or the slots are the cameras of one multiframe,
@@ -213,14 +215,19 @@ int okc_batch_size(const okc_batch* batch);
 int okc_batch_enqueue(okc_batch* batch, const uint8_t* const* images, int images_on_device,
                       const okc_detect_params* dp, const okc_describe_params* xp,
                       const okc_map_window* const* windows, const double* const* proj_xy, int proj_on_device,
-                      const double* thresh_sq, double hamming_threshold);
+                      const double* thresh_sq, double hamming_threshold, int num_slices);
 /* Waits for the batch's stream and brings every slot's results to the host (two copies for the whole batch). */
 int okc_batch_finish(okc_batch* batch);
 /* After okc_batch_finish: what okc_detect_describe_finish / okc_match_to_map return, for one slot. */
 int okc_batch_slot_frame(okc_batch* batch, int slot, okc_keypoint* keypoints, int capacity, int* n,
                          uint8_t* descriptors);
-int okc_batch_slot_matches(okc_batch* batch, int slot, int num_slices, double* best_dist, int32_t* best_owner,
-                           uint64_t* ctrs, double* repr_errors);
+int okc_batch_slot_matches(okc_batch* batch, int slot, double* best_dist, int32_t* best_owner, uint64_t* ctrs,
+                           double* repr_errors);
+/* All slots at once into caller arrays with stride max_keypoints per slot: keypoints[n_slots*max_kp],
+ * counts[n_slots], descriptors[n_slots*max_kp*48], and (NULL to skip) best_dist / best_owner [n_slots*max_kp],
+ * ctrs / repr_errors [n_slots*num_slices]. */
+int okc_batch_read_all(okc_batch* batch, okc_keypoint* keypoints, int32_t* counts, uint8_t* descriptors,
+                       double* best_dist, int32_t* best_owner, uint64_t* ctrs, double* repr_errors);
 void* okc_batch_stream(okc_batch* batch);
 int okc_debug_batch_kernel_timing(okc_batch* batch, int enable);
 int okc_debug_batch_kernel_times(okc_batch* batch, char* names, int names_cap, float* ms, int cap, int* n);

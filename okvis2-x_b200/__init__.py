@@ -32,7 +32,7 @@ EXPORTS = [
     "okc_detect_describe_enqueue_device", "okc_map_window_create", "okc_map_window_destroy",
     "okc_camera_match_to_map_enqueue", "okc_camera_frame_finish", "okc_camera_stream", "okc_debug_kernel_timing",
     "okc_debug_kernel_times", "okc_batch_create", "okc_batch_destroy", "okc_batch_size", "okc_batch_enqueue",
-    "okc_batch_finish", "okc_batch_slot_frame", "okc_batch_slot_matches", "okc_batch_stream",
+    "okc_batch_finish", "okc_batch_slot_frame", "okc_batch_slot_matches", "okc_batch_read_all", "okc_batch_stream",
     "okc_debug_batch_kernel_timing", "okc_debug_batch_kernel_times",
 ]
 
@@ -93,8 +93,8 @@ def lib():
         L.okc_detect_describe_enqueue_device.argtypes = [vp, vp, C.POINTER(DetectParams), C.POINTER(DescribeParams)]
         L.okc_map_window_create.argtypes = [vp, vp, vp, i, i, C.POINTER(vp)]
         L.okc_map_window_destroy.argtypes = [vp]
-        L.okc_camera_match_to_map_enqueue.argtypes = [vp, vp, vp, i, d, d]
-        L.okc_camera_frame_finish.argtypes = [vp, vp, i, vp, i, C.POINTER(i), vp, vp, vp, vp, vp]
+        L.okc_camera_match_to_map_enqueue.argtypes = [vp, vp, vp, i, d, d, i]
+        L.okc_camera_frame_finish.argtypes = [vp, vp, vp, i, C.POINTER(i), vp, vp, vp, vp, vp]
         L.okc_camera_stream.argtypes = [vp]
         L.okc_camera_stream.restype = vp
         L.okc_debug_kernel_timing.argtypes = [vp, i]
@@ -102,10 +102,11 @@ def lib():
         L.okc_batch_create.argtypes = [vp, vp, i, C.POINTER(vp)]
         L.okc_batch_destroy.argtypes = [vp]
         L.okc_batch_size.argtypes = [vp]
-        L.okc_batch_enqueue.argtypes = [vp, vp, i, C.POINTER(DetectParams), vp, vp, vp, i, vp, d]
+        L.okc_batch_enqueue.argtypes = [vp, vp, i, C.POINTER(DetectParams), vp, vp, vp, i, vp, d, i]
+        L.okc_batch_read_all.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp]
         L.okc_batch_finish.argtypes = [vp]
         L.okc_batch_slot_frame.argtypes = [vp, i, vp, i, C.POINTER(i), vp]
-        L.okc_batch_slot_matches.argtypes = [vp, i, i, vp, vp, vp, vp]
+        L.okc_batch_slot_matches.argtypes = [vp, i, vp, vp, vp, vp]
         L.okc_batch_stream.argtypes = [vp]
         L.okc_batch_stream.restype = vp
         L.okc_debug_batch_kernel_timing.argtypes = [vp, i]
@@ -328,27 +329,30 @@ class Camera:
         _check(lib().okc_detect_describe_enqueue_device(self.h, C.c_void_p(image_ptr), C.byref(dp), C.byref(xp)),
                "okc_detect_describe_enqueue_device")
 
-    def match_to_map_enqueue(self, window, proj_xy, thresh_sq, hamming_threshold=60.0, proj_device_ptr=None):
+    def match_to_map_enqueue(self, window, proj_xy, thresh_sq, hamming_threshold=60.0, proj_device_ptr=None,
+                             num_slices=4):
+        self._slices = int(num_slices)
         if proj_device_ptr is not None:
             _check(lib().okc_camera_match_to_map_enqueue(self.h, window.h, C.c_void_p(proj_device_ptr), 1,
-                                                         float(thresh_sq), float(hamming_threshold)),
+                                                         float(thresh_sq), float(hamming_threshold), self._slices),
                    "okc_camera_match_to_map_enqueue")
             return
         pr = np.ascontiguousarray(proj_xy, np.float64).reshape(-1, 2)
         assert len(pr) == window.num_landmarks
         _check(lib().okc_camera_match_to_map_enqueue(self.h, window.h, _p(pr), 0, float(thresh_sq),
-                                                     float(hamming_threshold)), "okc_camera_match_to_map_enqueue")
+                                                     float(hamming_threshold), self._slices),
+               "okc_camera_match_to_map_enqueue")
 
-    def frame_finish(self, window, num_slices=4):
+    def frame_finish(self, window):
         kp = np.zeros(self.max_kp, KP_DTYPE)
         desc = np.zeros((self.max_kp, 48), np.uint8)
         n = C.c_int(0)
         bd = np.empty(self.max_kp, np.float64)
         bo = np.empty(self.max_kp, np.int32)
-        ctrs = np.zeros(num_slices, np.uint64)
-        errs = np.zeros(num_slices, np.float64)
-        _check(lib().okc_camera_frame_finish(self.h, window.h, int(num_slices), _p(kp), self.max_kp, C.byref(n),
-                                             _p(desc), _p(bd), _p(bo), _p(ctrs), _p(errs)), "okc_camera_frame_finish")
+        ctrs = np.zeros(self._slices, np.uint64)
+        errs = np.zeros(self._slices, np.float64)
+        _check(lib().okc_camera_frame_finish(self.h, window.h, _p(kp), self.max_kp, C.byref(n), _p(desc), _p(bd),
+                                             _p(bo), _p(ctrs), _p(errs)), "okc_camera_frame_finish")
         k = n.value
         return kp[:k].copy(), desc[:k].copy(), bd[:k].copy(), bo[:k].copy(), ctrs, errs
 
@@ -410,7 +414,7 @@ class Batch:
 
     def enqueue(self, images, radius, octaves, abs_threshold, max_kpt, directions, rotation_invariant=True,
                 images_on_device=False, windows=None, proj=None, gates=None, hamming_threshold=60.0,
-                proj_on_device=False):
+                proj_on_device=False, num_slices=4):
         """images: n arrays (host) or n device addresses; directions: n 3-vectors; windows/proj/gates: per slot."""
         keep = []
         for k in range(self.n):
@@ -430,7 +434,7 @@ class Batch:
         dp = DetectParams(float(radius), int(octaves), float(abs_threshold), int(max_kpt))
         if windows is None:
             _check(lib().okc_batch_enqueue(self.h, self._img, int(images_on_device), C.byref(dp), self._xp, None, None,
-                                           0, None, float(hamming_threshold)), "okc_batch_enqueue")
+                                           0, None, float(hamming_threshold), 1), "okc_batch_enqueue")
         else:
             for k in range(self.n):
                 self._win[k] = windows[k].h if windows[k] is not None else None
@@ -442,8 +446,10 @@ class Batch:
                     self._proj[k] = p.ctypes.data
                 self._gate[k] = float(gates[k])
             _check(lib().okc_batch_enqueue(self.h, self._img, int(images_on_device), C.byref(dp), self._xp, self._win,
-                                           self._proj, int(proj_on_device), self._gate, float(hamming_threshold)),
-                   "okc_batch_enqueue")
+                                           self._proj, int(proj_on_device), self._gate, float(hamming_threshold),
+                                           int(num_slices)), "okc_batch_enqueue")
+        self._slices = int(num_slices)
+        self._matching = windows is not None
         self._keep = keep  # host buffers stay alive until finish()
 
     def finish(self):
@@ -458,14 +464,30 @@ class Batch:
                "okc_batch_slot_frame")
         return kp[:n.value], desc[:n.value]
 
-    def slot_matches(self, slot, nk, num_slices=4):
+    def slot_matches(self, slot, nk):
         bd = np.empty(self.max_kp, np.float64)
         bo = np.empty(self.max_kp, np.int32)
-        ctrs = np.zeros(num_slices, np.uint64)
-        errs = np.zeros(num_slices, np.float64)
-        _check(lib().okc_batch_slot_matches(self.h, slot, int(num_slices), _p(bd), _p(bo), _p(ctrs), _p(errs)),
+        ctrs = np.zeros(self._slices, np.uint64)
+        errs = np.zeros(self._slices, np.float64)
+        _check(lib().okc_batch_slot_matches(self.h, slot, _p(bd), _p(bo), _p(ctrs), _p(errs)),
                "okc_batch_slot_matches")
         return bd[:nk], bo[:nk], ctrs, errs
+
+    def read_all(self, out=None):
+        """All slots at once into (reusable) arrays: dict(kp [n,max_kp], n [n], desc [n,max_kp,48], dist, owner,
+        ctrs [n,slices], errs [n,slices])."""
+        if out is None:
+            out = dict(kp=np.empty((self.n, self.max_kp), KP_DTYPE), n=np.zeros(self.n, np.int32),
+                       desc=np.empty((self.n, self.max_kp, 48), np.uint8),
+                       dist=np.empty((self.n, self.max_kp), np.float64), owner=np.empty((self.n, self.max_kp), np.int32),
+                       ctrs=np.zeros((self.n, 64), np.uint64), errs=np.zeros((self.n, 64), np.float64))
+        m = self._matching
+        ctrs = out["ctrs"].reshape(-1)
+        errs = out["errs"].reshape(-1)
+        _check(lib().okc_batch_read_all(self.h, _p(out["kp"]), _p(out["n"]), _p(out["desc"]),
+                                        _p(out["dist"]) if m else None, _p(out["owner"]) if m else None,
+                                        _p(ctrs) if m else None, _p(errs) if m else None), "okc_batch_read_all")
+        return out
 
     def stream(self):
         return lib().okc_batch_stream(self.h)

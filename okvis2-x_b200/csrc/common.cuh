@@ -38,6 +38,10 @@ struct PatternTables {
   int basicscale;
 };
 
+constexpr int kMaxSlices = 64;
+// ctrs[t] and the not-yet-divided reprErrors[t] of Frontend::matchToMapByThread (Frontend.cpp:1767, 1820-1821)
+struct MatchStats { unsigned long long count; double sum; };
+
 // One image of a batch ("slot"). Every kernel of the path is launched once per BATCH and indexes its slot with
 // blockIdx (.z for the tiled kernels, .x for the one-CTA-per-image kernels), so that a multi-camera frame or several
 // frames of a sequence fill the 148 SMs with one launch chain. The array lives in device memory; all pointers are
@@ -65,12 +69,13 @@ struct Slot {
   const double* proj;      // (per enqueue) landmark projections of this frame
   double thresh_sq;        // (per enqueue)
   int nm;                  // (per enqueue) rows in the pool (map == null: no match for this slot)
-  int event_slab;          // events [0, slab) live in the output arena, the rest in events_overflow
+  int num_slices;          // (per enqueue) num_matching_threads: ctrs / reprErrors are defined per thread slice
   int event_cap;
   double* best_dist;       // max_keypoints   } output arena
   int* best_owner;         // max_keypoints   }
-  unsigned long long* events;
-  unsigned long long* events_overflow;
+  MatchStats* stats;       // kMaxSlices      }
+  unsigned long long* events;   // event_cap improvement events (k, row); consumed on the device by match_stats
+  unsigned long long* sort_scratch;  // pow2(event_cap) keys, used when the events do not fit in shared memory
   float dir[3];            // (per enqueue) extraction direction (gravity in this camera's frame)
 };
 
@@ -96,6 +101,7 @@ void launch_select_keypoints(const Slot* slots, int n, const float* lut, const D
 void launch_describe(const Slot* slots, int n, const PatternTables& t, const DescribeArgs& a, int max_kp,
                      cudaStream_t s);
 void launch_match_to_map_slots(const Slot* slots, int n, int max_kp, double hammingThreshold, cudaStream_t s);
+void launch_match_stats(const Slot* slots, int n, cudaStream_t s);
 
 void set_error(const char* fmt, ...);
 

@@ -249,7 +249,7 @@ match_to_map_slots_kernel(const Slot* __restrict__ slots, int maxKp, double hamm
   if (slot.map == nullptr) return;  // no map match requested for this slot
   match_to_map_body(slot.desc, nullptr, slot.kp_desc, nullptr, maxKp, slot.counters + 2, slot.map, slot.owner, slot.nm,
                     slot.proj, slot.thresh_sq, hammingThreshold, slot.best_dist, slot.best_owner, slot.events,
-                    slot.event_slab, slot.events_overflow, slot.event_cap, slot.counters + 4);
+                    slot.event_cap, nullptr, slot.event_cap, slot.counters + 4);
 }
 
 void launch_match_to_map_slots(const Slot* slots, int n, int max_kp, double hammingThreshold, cudaStream_t s) {
@@ -269,6 +269,94 @@ void launch_match_to_map(const uint8_t* queries, const double* kp_xy, const okc_
   match_to_map_kernel<<<blocks, warpsPerBlock * 32, 0, s>>>(queries, kp_xy, kp_f, use, nkMax, nkDev, map, owner, nm,
                                                            proj_xy, threshSq, hammingThreshold, bestDist, bestOwner,
                                                            events, eventCap, eventCount);
+}
+
+// ----------------------------------------------------------------------------------------------
+// ctrs[] / reprErrors[] of matchToMapByThread, on the device
+// ----------------------------------------------------------------------------------------------
+// The reference counts every improvement of a keypoint's running best and adds its reprojection distance to a
+// double accumulator, per thread slice, in ITS iteration order: landmark-major, then keypoint, then descriptor row
+// (Frontend.cpp:1785-1826). The match kernel logs the improvements as (row, k) events in arbitrary order; this kernel
+// sorts them by (slice, landmark, k, event index) - events of one k are logged in row order by one warp, so the
+// event index orders them - and lets one thread per slice add the distances sequentially, which reproduces the
+// reference's sums bit for bit. The final division (NaN for an empty slice) is done by the host at finish.
+constexpr int kStatsThreads = 1024;
+constexpr int kStatsSmemEvents = 8192;
+
+__global__ void __launch_bounds__(kStatsThreads, 1) match_stats_kernel(const Slot* __restrict__ slots) {
+  extern __shared__ __align__(16) unsigned long long s_keys[];  // kStatsSmemEvents keys (dynamic: 64 KB)
+  __shared__ int s_begin[kMaxSlices + 1];
+  const Slot& slot = slots[blockIdx.x];
+  if (slot.map == nullptr) return;
+  const int tid = threadIdx.x;
+  const int T = slot.num_slices;
+  int E = slot.counters[4];
+  if (E > slot.event_cap) E = slot.event_cap;  // overflow is reported by the host from counters[4]
+  const int nk = slot.counters[2];
+  const int segment = nk / T;
+  if (tid <= T) s_begin[tid] = E;
+  int npad = 1;
+  while (npad < E) npad <<= 1;
+  unsigned long long* keys = npad <= kStatsSmemEvents ? s_keys : slot.sort_scratch;
+  // key = slice(6) | landmark(24) | k(16) | event index(18)
+  for (int i = tid; i < npad; i += kStatsThreads) {
+    unsigned long long key = ~0ull;
+    if (i < E) {
+      const unsigned long long ev = slot.events[i];
+      const unsigned m = (unsigned)(ev >> 32), k = (unsigned)ev;
+      unsigned t = segment == 0 ? (unsigned)(T - 1) : k / (unsigned)segment;
+      if (t > (unsigned)(T - 1)) t = (unsigned)(T - 1);
+      key = ((unsigned long long)t << 58) | ((unsigned long long)(unsigned)slot.owner[m] << 34) |
+            ((unsigned long long)k << 18) | (unsigned long long)i;
+    }
+    keys[i] = key;
+  }
+  __syncthreads();
+  for (int kk = 2; kk <= npad; kk <<= 1) {
+    for (int j = kk >> 1; j > 0; j >>= 1) {
+      for (int i = tid; i < npad; i += kStatsThreads) {
+        const int ixj = i ^ j;
+        if (ixj > i) {
+          const unsigned long long a = keys[i], b = keys[ixj];
+          if ((a > b) == ((i & kk) == 0)) {
+            keys[i] = b;
+            keys[ixj] = a;
+          }
+        }
+      }
+      __syncthreads();
+    }
+  }
+  // slice boundaries: first index whose slice field is >= t
+  for (int i = tid; i < E; i += kStatsThreads) {
+    const int t = (int)(keys[i] >> 58);
+    const int tprev = i == 0 ? -1 : (int)(keys[i - 1] >> 58);
+    for (int u = tprev + 1; u <= t; ++u) s_begin[u] = i;
+  }
+  __syncthreads();
+  if (tid < T) {
+    // s_begin[u] for slices after the last populated one stayed E; empty slices in between were filled above
+    const int b = s_begin[tid], e = s_begin[tid + 1];
+    double sum = 0.0;
+    for (int i = b; i < e; ++i) {
+      const unsigned long long key = keys[i];
+      const unsigned o = (unsigned)(key >> 34) & 0xffffffu, k = (unsigned)(key >> 18) & 0xffffu;
+      const double rx = slot.proj[2 * o] - (double)slot.kp_desc[k].x, ry = slot.proj[2 * o + 1] - (double)slot.kp_desc[k].y;
+      sum += sqrt(rx * rx + ry * ry);
+    }
+    slot.stats[tid].count = (unsigned long long)(e - b);
+    slot.stats[tid].sum = sum;
+  }
+}
+
+void launch_match_stats(const Slot* slots, int n, cudaStream_t s) {
+  if (n <= 0) return;
+  static bool configured = false;
+  if (!configured) {
+    cudaFuncSetAttribute(match_stats_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kStatsSmemEvents * 8);
+    configured = true;
+  }
+  match_stats_kernel<<<n, kStatsThreads, kStatsSmemEvents * 8, s>>>(slots);
 }
 
 // ----------------------------------------------------------------------------------------------

@@ -211,7 +211,7 @@ def test_frame_pipeline_equals_separate_calls(mod, ctx, port, syn):
     m3, o3, proj3 = win["map"][sel], slots[win["owner"][sel]].astype(np.int32), win["proj"][win["is3d"]]
     window = mod.MapWindow(ctx, m3, o3, len(proj3))
     gate = (3.0 + 0.5 * (c["f"][0] + c["f"][1]) * 0.06) ** 2
-    for seed, on_device in ((1, False), (2, True), (1, True)):
+    for seed, on_device, slices in ((1, False, 4), (2, True, 3), (1, True, 7)):
         img = syn.scene_image(W, H, seed)
         d_img = torch.from_numpy(img).cuda()
         torch.cuda.synchronize()
@@ -219,16 +219,16 @@ def test_frame_pipeline_equals_separate_calls(mod, ctx, port, syn):
         if on_device:
             d_proj = torch.from_numpy(proj3).cuda()
             torch.cuda.synchronize()
-            cam.match_to_map_enqueue(window, None, gate, 60.0, proj_device_ptr=d_proj.data_ptr())
+            cam.match_to_map_enqueue(window, None, gate, 60.0, proj_device_ptr=d_proj.data_ptr(), num_slices=slices)
         else:
-            cam.match_to_map_enqueue(window, proj3, gate, 60.0)
-        kp, desc, bd, bo, ctrs, errs = cam.frame_finish(window, 4)
+            cam.match_to_map_enqueue(window, proj3, gate, 60.0, num_slices=slices)
+        kp, desc, bd, bo, ctrs, errs = cam.frame_finish(window)
         kp2, desc2 = cam.detect_describe(img, 38.0, 0, 150.0, 700, direction=direction)
         assert kp.tobytes() == kp2.tobytes() and np.array_equal(desc, desc2)
         kp_xy = np.stack([kp["x"], kp["y"]], 1).astype(np.float64)
         use = np.ones(len(kp), np.uint8)
-        bd2, bo2, ctrs2, errs2 = ctx.match_to_map(desc, kp_xy, use, m3, o3, proj3, gate, 60.0, 4)
-        pd, po, pc, pe = port.match_to_map(desc, kp_xy, use, m3, o3, proj3, None, gate, 60.0, 4)
+        bd2, bo2, ctrs2, errs2 = ctx.match_to_map(desc, kp_xy, use, m3, o3, proj3, gate, 60.0, slices)
+        pd, po, pc, pe = port.match_to_map(desc, kp_xy, use, m3, o3, proj3, None, gate, 60.0, slices)
         for a, b, cc in ((bd, bd2, pd), (bo, bo2, po), (ctrs, ctrs2, pc)):
             assert np.array_equal(a, b) and np.array_equal(a, cc)
         assert errs.tobytes() == errs2.tobytes() == pe.tobytes()
@@ -238,10 +238,10 @@ def test_frame_pipeline_equals_separate_calls(mod, ctx, port, syn):
     cam.enqueue_device(d_img.data_ptr(), 38.0, 0, 150.0, 700, direction=direction)
     cam.match_to_map_enqueue(window, proj3, gate, 60.0)
     times = cam.kernel_times()
-    cam.frame_finish(window, 4)
+    cam.frame_finish(window)
     cam.kernel_timing(False)
     assert [n for n, _ in times] == ["harris_nms", "order_candidates", "select_keypoints", "border_filter+describe",
-                                       "match_to_map"]
+                                       "match_to_map", "match_stats"]
     assert all(t > 0 for _, t in times)
     window.close()
     cam.close()
@@ -297,7 +297,7 @@ def test_batch_equals_single_calls(on_device, mod, ctx, port, syn):
         for k in range(6):
             kp, desc = batch.slot_frame(k)
             assert kp.tobytes() == single[k][0].tobytes() and np.array_equal(desc, single[k][1]), k
-            bd, bo, ctrs, errs = batch.slot_matches(k, len(kp), 4)
+            bd, bo, ctrs, errs = batch.slot_matches(k, len(kp))
             rows, owner, proj = wins_h[k % 2]
             kp_xy = np.stack([kp["x"], kp["y"]], 1).astype(np.float64)
             pd, po, pc, pe = port.match_to_map(desc, kp_xy, np.ones(len(kp), np.uint8), rows, owner, proj[k // 2], None,
@@ -306,6 +306,16 @@ def test_batch_equals_single_calls(on_device, mod, ctx, port, syn):
             assert errs.tobytes() == pe.tobytes(), k
             if k < 2:
                 assert (bo >= 0).sum() > 100
+        allr = batch.read_all()
+        for k in range(6):
+            n = int(allr["n"][k])
+            kp, desc = batch.slot_frame(k)
+            bd, bo, ctrs, errs = batch.slot_matches(k, n)
+            assert n == len(kp) and allr["kp"][k, :n].tobytes() == kp.tobytes()
+            assert np.array_equal(allr["desc"][k, :n], desc) and np.array_equal(allr["dist"][k, :n], bd)
+            assert np.array_equal(allr["owner"][k, :n], bo)
+            assert np.array_equal(allr["ctrs"].reshape(-1)[k * 4:k * 4 + 4], ctrs)
+            assert allr["errs"].reshape(-1)[k * 4:k * 4 + 4].tobytes() == errs.tobytes()
     batch.close()
     for w in wins:
         w.close()
