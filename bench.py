@@ -39,8 +39,8 @@ DIRECTION = (0.05, 0.99, 0.1)   # gravity in the camera frame (Frontend.cpp:234-
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=200)
-    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=2000)
+    ap.add_argument("--warmup", type=int, default=40)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--frames-per-batch", type=int, default=8, help="stereo frames per launch chain")
     ap.add_argument("--in-flight", type=int, default=4, help="batches in flight (one stream each)")
