@@ -42,8 +42,8 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=2000)
     ap.add_argument("--warmup", type=int, default=40)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--frames-per-batch", type=int, default=8, help="stereo frames per launch chain")
-    ap.add_argument("--in-flight", type=int, default=4, help="batches in flight (one stream each)")
+    ap.add_argument("--frames-per-batch", type=int, default=16, help="stereo frames per launch chain")
+    ap.add_argument("--in-flight", type=int, default=6, help="batches in flight (one stream each)")
     ap.add_argument("--no-sweep", action="store_true", help="skip the 10k x 1M matcher sweep in `extra`")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()
@@ -292,7 +292,8 @@ def run_b200(args, rank, world):
     h_img = [torch.from_numpy(wl["images"][c]).pin_memory() for c in range(2)]
     img_stride = W * H
     proj_strides = [win_h[c][2].shape[1] * 16 for c in range(2)]
-    frame_of = lambda k: (rank + k * world) % N_FRAMES
+    sh = importlib.import_module("okvis2x_b200.sharding")
+    frame_of = lambda k: sh.frame_of(k, rank, world, N_FRAMES)
 
     def make_batches(nframes):
         return [mod.Batch(ctx, [cams[i % 2] for i in range(2 * nframes)]) for _ in range(D)]
@@ -464,11 +465,11 @@ def run_sweep(st, rank, world, iters=5):
     torch, dist, mod, ctx, syn = st["torch"], st["dist"], st["mod"], st["ctx"], st["syn"]
     nq, nm = 10000, 1000000
     q, m = syn.sweep_inputs(nq, nm, seed=5)
-    per = (nm + world - 1) // world
-    lo, hi = rank * per, min(nm, (rank + 1) * per)
+    import importlib
+    sh = importlib.import_module("okvis2x_b200.sharding")
+    lo, hi = sh.map_row_shard(rank, world, nm)
     qs, ms = ctx.descriptor_set(q), ctx.descriptor_set(m[lo:hi])
     best = torch.empty(nq, dtype=torch.int64, device="cuda")
-    gathered = torch.empty(world * nq, dtype=torch.int64, device="cuda") if world > 1 else None
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
     # a non-default stream: handle 0 would select the library's own stream, which torch events do not see
     cur = torch.cuda.Stream()
@@ -484,12 +485,7 @@ def run_sweep(st, rank, world, iters=5):
         ctx.match_sets(qs, ms, 60, index_offset=lo, best_device=best.data_ptr(), stream=cur.cuda_stream,
                        want_host=False)
         e1.record(cur)
-        if world > 1:
-            dist.all_gather_into_tensor(gathered, best)
-            # uint64 keys compare like int64 except NO_MATCH (-1): map it above everything before the min
-            res = torch.where(gathered < 0, torch.iinfo(torch.int64).max, gathered).view(world, nq).min(0).values
-        else:
-            res = best
+        res = sh.merge_best(best, world, dist)   # NCCL all-gather + min (identity at world == 1)
         e2.record(cur)
         e2.synchronize()
         if it >= 2:
@@ -503,7 +499,7 @@ def run_sweep(st, rank, world, iters=5):
     peak, _ = peaks()
     pairs = float(nq) * nm
     alg = (nq + nm) * 48 + nq * 8
-    matched = int((res != (torch.iinfo(torch.int64).max if world > 1 else -1)).sum().item())
+    matched = int((res != sh.NO_MATCH_I64).sum().item())
     for s in (qs, ms):
         s.close()
     return {"workload": "configs[4]: 10k x 1M descriptors (48 B), threshold 60, map rows sharded over ranks",
