@@ -157,6 +157,16 @@ int okc_match_stereo(okc_context* ctx, const okc_stereo_view* v0, const okc_ster
                      double hamming_threshold, double* dist, int32_t* k1_match, double* hp_W,
                      uint8_t* initialisable);
 
+/* 2D-2D matching against an older keyframe, the worker lambda of Frontend::matchMotionStereo (Frontend.cpp:2053-2137).
+ * v0 = older frame (all keypoints; use0[k0] != 0 where the estimator-state tests of :2056-2084 let k0 through),
+ * v1 = the current frame's UNMATCHED keypoints packed contiguously as the reference packs desc1 (:2034-2047);
+ * k1_match indexes that packed list (-1: none). Outputs per k0 as MatchInfo (:1959-1966) before the 4 px
+ * reprojection check of :2140-2147, which needs the camera model and stays in the adapter: dist (= threshold when
+ * unmatched), k1, hp_W (w = 1), initialisable, quality = acos(...). */
+int okc_match_motion_stereo(okc_context* ctx, const okc_stereo_view* v0, const uint8_t* use0, const okc_stereo_view* v1,
+                            double hamming_threshold, double* dist, int32_t* k1_match, double* hp_W,
+                            uint8_t* initialisable, double* quality);
+
 /* 3D-2D matching of not-yet-initialised landmarks, Frontend::matchToMapByThreadUnitialised
  * (Frontend.cpp:1830-1956): epipolar-plane, divergence, triangulateFast and 0.2 m gates on the device in FP64.
  * Per map row m: owner slot, ray e_W[3m..], origin r_W[3m..]. Per keypoint k: e_W (world ray), use flag and

@@ -28,7 +28,7 @@ EXPORTS = [
     "okc_camera_create", "okc_camera_destroy", "okc_detect", "okc_describe", "okc_detect_describe",
     "okc_detect_describe_enqueue", "okc_detect_describe_finish", "okc_debug_scores", "okc_debug_candidates",
     "okc_match_batched", "okc_descriptor_set_create", "okc_descriptor_set_destroy", "okc_match_sets",
-    "okc_match_to_map", "okc_match_stereo", "okc_match_to_map_uninitialised",
+    "okc_match_to_map", "okc_match_stereo", "okc_match_to_map_uninitialised", "okc_match_motion_stereo",
     "okc_detect_describe_enqueue_device", "okc_map_window_create", "okc_map_window_destroy",
     "okc_camera_match_to_map_enqueue", "okc_camera_frame_finish", "okc_camera_stream", "okc_debug_kernel_timing",
     "okc_debug_kernel_times", "okc_batch_create", "okc_batch_destroy", "okc_batch_size", "okc_batch_enqueue",
@@ -90,6 +90,10 @@ def lib():
         L.okc_match_sets.argtypes = [vp, vp, vp, u32, u64, vp, vp, vp]
         L.okc_match_to_map.argtypes = [vp, vp, vp, vp, i, vp, vp, i, vp, i, d, d, i, vp, vp, vp, vp]
         L.okc_match_stereo.argtypes = [vp, C.POINTER(StereoView), C.POINTER(StereoView), d, vp, vp, vp, vp]
+        L.okc_match_motion_stereo.argtypes = [vp, C.POINTER(StereoView), vp, C.POINTER(StereoView), d, vp, vp, vp, vp,
+                                              vp]
+        L.okc_match_to_map_uninitialised.argtypes = [vp, vp, vp, vp, vp, i, vp, vp, vp, vp, i, vp, d, d, i, vp, vp, vp,
+                                                     vp, vp]
         L.okc_detect_describe_enqueue_device.argtypes = [vp, vp, C.POINTER(DetectParams), C.POINTER(DescribeParams)]
         L.okc_map_window_create.argtypes = [vp, vp, vp, i, i, C.POINTER(vp)]
         L.okc_map_window_destroy.argtypes = [vp]
@@ -182,6 +186,60 @@ class Context:
                                       float(thresh_sq), float(hamming_threshold), int(num_slices), _p(bd), _p(bo),
                                       _p(ctrs), _p(errs)), "okc_match_to_map")
         return bd, bo, ctrs, errs
+
+    # -- Frontend::matchToMapByThreadUnitialised, Frontend.cpp:1830-1956 --
+    def match_to_map_uninitialised(self, queries, kp_e_W, use, previous_owner, mp, map_owner, map_e_W, map_r_W, r_WC,
+                                   focal, hamming_threshold=60.0, num_slices=4):
+        q = np.ascontiguousarray(queries, np.uint8).reshape(-1, 48)
+        ke = np.ascontiguousarray(kp_e_W, np.float64).reshape(-1, 3)
+        us = np.ascontiguousarray(use, np.uint8)
+        pv = np.ascontiguousarray(previous_owner, np.int32) if previous_owner is not None else None
+        m = np.ascontiguousarray(mp, np.uint8).reshape(-1, 48)
+        ow = np.ascontiguousarray(map_owner, np.int32)
+        me = np.ascontiguousarray(map_e_W, np.float64).reshape(-1, 3)
+        mr = np.ascontiguousarray(map_r_W, np.float64).reshape(-1, 3)
+        rc = np.ascontiguousarray(r_WC, np.float64)
+        nk = len(q)
+        bd = np.empty(max(nk, 1), np.float64)
+        bo = np.empty(max(nk, 1), np.int32)
+        hps = np.zeros((max(nk, 1), 4), np.float64)
+        hw = np.zeros(max(nk, 1), np.uint8)
+        ctrs = np.zeros(num_slices, np.uint64)
+        _check(lib().okc_match_to_map_uninitialised(self.h, _p(q), _p(ke), _p(us), _p(pv), nk, _p(m), _p(ow), _p(me),
+                                                    _p(mr), len(m), _p(rc), float(focal), float(hamming_threshold),
+                                                    int(num_slices), _p(bd), _p(bo), _p(hps), _p(hw), _p(ctrs)),
+               "okc_match_to_map_uninitialised")
+        return bd[:nk], bo[:nk], hps[:nk], hw[:nk], ctrs
+
+    # -- worker lambda of Frontend::matchMotionStereo, Frontend.cpp:2053-2137 --
+    def match_motion_stereo(self, view0, use0, view1, hamming_threshold=60.0):
+        keep = []
+        s0, s1 = self._view(view0, keep), self._view(view1, keep)
+        u0 = np.ascontiguousarray(use0, np.uint8)
+        n0 = s0.n
+        dist = np.empty(n0, np.float64)
+        k1 = np.empty(n0, np.int32)
+        hp = np.empty((n0, 4), np.float64)
+        init = np.empty(n0, np.uint8)
+        qual = np.empty(n0, np.float64)
+        _check(lib().okc_match_motion_stereo(self.h, C.byref(s0), _p(u0), C.byref(s1), float(hamming_threshold),
+                                             _p(dist), _p(k1), _p(hp), _p(init), _p(qual)), "okc_match_motion_stereo")
+        return dist, k1, hp, init, qual
+
+    @staticmethod
+    def _view(v, keep):
+        s = StereoView()
+        desc = np.ascontiguousarray(v["desc"], np.uint8).reshape(-1, 48)
+        size = np.ascontiguousarray(v["size"], np.float64)
+        e_C = np.ascontiguousarray(v["e_C"], np.float64).reshape(-1, 3)
+        bpv = np.ascontiguousarray(v["bp_valid"], np.uint8)
+        keep.extend([desc, size, e_C, bpv])
+        s.desc, s.size, s.e_C, s.bp_valid = desc.ctypes.data, size.ctypes.data, e_C.ctypes.data, bpv.ctypes.data
+        s.n = len(desc)
+        s.C_WC[:] = list(np.asarray(v["C_WC"], np.float64).reshape(9))
+        s.r_WC[:] = list(np.asarray(v["r_WC"], np.float64).reshape(3))
+        s.f = float(v["f"])
+        return s
 
     # -- Frontend::matchStereo inner loops, Frontend.cpp:2259-2316 --
     def match_stereo(self, view0, view1, hamming_threshold=60.0):

@@ -393,7 +393,9 @@ __device__ __forceinline__ V3 matTvec(const double* C, V3 v) {  // C^T * v
 
 // triangulation::triangulateFast (okvis_frontend/src/stereo_triangulation.cpp:30-111). Returns the
 // (non-normalised) homogeneous point with w = 1.
-__device__ V3 triangulate_fast(V3 p1, V3 e1, V3 p2, V3 e2, double sigma, bool& isValid, bool& isParallel) {
+// c26 = cos(2.6 sigma), c60 = cos(6 sigma): passed in so that a caller with a per-call sigma can use the host libm's
+// values (what the reference's CPU code evaluates); the per-pair callers evaluate them on the device.
+__device__ V3 triangulate_fast(V3 p1, V3 e1, V3 p2, V3 e2, double c26, double c60, bool& isValid, bool& isParallel) {
   isParallel = false;
   isValid = true;
   const V3 t12 = p2 - p1;
@@ -408,7 +410,6 @@ __device__ V3 triangulate_fast(V3 p1, V3 e1, V3 p2, V3 e2, double sigma, bool& i
     l0 = i00 * b0 + i01 * b1;
     l1 = i10 * b0 + i11 * b1;
   }
-  const double c26 = cos(2.6 * sigma);
   if (!invertible || l0 < 0.01 || l1 < 0.01) {
     isParallel = true;
     const V3 m = p1 + 0.5 * t12;
@@ -424,7 +425,7 @@ __device__ V3 triangulate_fast(V3 p1, V3 e1, V3 p2, V3 e2, double sigma, bool& i
   const V3 midpoint = v3(s.x / 2.0, s.y / 2.0, s.z / 2.0);
   if (dot(e1, normalized(midpoint - p1)) < c26) isValid = false;
   if (dot(e2, normalized(midpoint - p2)) < c26) isValid = false;
-  if (dot(normalized(midpoint - p2), normalized(midpoint - p1)) > cos(6.0 * sigma)) isParallel = true;
+  if (dot(normalized(midpoint - p2), normalized(midpoint - p1)) > c60) isParallel = true;
   return midpoint;
 }
 
@@ -442,18 +443,36 @@ struct StereoDev {
   double f;
 };
 
+// MOTION = false: Frontend::matchStereo (Frontend.cpp:2259-2316).
+// MOTION = true : the worker lambda of Frontend::matchMotionStereo (Frontend.cpp:2053-2137): k0 must be eligible
+// (use0: not an initialised landmark, not observed, back-projection valid - estimator state, decided by the
+// caller), sigma from size0 only, an extra e0.e1 >= 0.5 pre-gate, 0.2 m depth gates, and the triangulation quality
+// acos(...) of the accepted match as an additional output.
+template <bool MOTION>
 __global__ void __launch_bounds__(256)
-match_stereo_kernel(StereoDev v0, StereoDev v1, double hammingThreshold, double* __restrict__ outDist,
-                    int* __restrict__ outK1, double* __restrict__ outHp, uint8_t* __restrict__ outInit) {
+match_stereo_kernel(StereoDev v0, StereoDev v1, const uint8_t* __restrict__ use0, double hammingThreshold,
+                    double* __restrict__ outDist, int* __restrict__ outK1, double* __restrict__ outHp,
+                    uint8_t* __restrict__ outInit, double* __restrict__ outQuality) {
   const int lane = threadIdx.x & 31;
   const int k0 = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   if (k0 >= v0.n) return;
+  if (MOTION && !(use0[k0] && v0.bp_valid[k0])) {
+    if (lane == 0) {
+      outDist[k0] = hammingThreshold;
+      outK1[k0] = -1;
+      outHp[4 * k0 + 0] = outHp[4 * k0 + 1] = outHp[4 * k0 + 2] = outHp[4 * k0 + 3] = 0.0;
+      outInit[k0] = 0;
+      outQuality[k0] = 0.0;
+    }
+    return;
+  }
   unsigned q[kDescWords];
   load_desc(v0.desc, k0, q);
   double distances = hammingThreshold;
   bool initialisable = false;
   V3 hps = v3(0.0, 0.0, 0.0);
-  int k1_match = 0;
+  int k1_match = MOTION ? -1 : 0;
+  double quality = 0.0;
   const V3 r0 = v3(v0.r[0], v0.r[1], v0.r[2]), r1 = v3(v1.r[0], v1.r[1], v1.r[2]);
 
   for (int base = 0; base < v1.n; base += 32) {
@@ -473,23 +492,27 @@ match_stereo_kernel(StereoDev v0, StereoDev v1, double hammingThreshold, double*
       if (!(dc < distances)) continue;
       if (!v0.bp_valid[k0]) continue;
       if (!v1.bp_valid[kc]) continue;
-      const double sigma = fmax(v0.size[k0] / v0.f, v1.size[kc] / v1.f) * 0.125;
+      const double sigma = MOTION ? v0.size[k0] / v0.f * 0.125 : fmax(v0.size[k0] / v0.f, v1.size[kc] / v1.f) * 0.125;
       const V3 e0_W = normalized(matvec(v0.C, v3(v0.e_C[3 * k0], v0.e_C[3 * k0 + 1], v0.e_C[3 * k0 + 2])));
       const V3 e1_W = normalized(matvec(v1.C, v3(v1.e_C[3 * kc], v1.e_C[3 * kc + 1], v1.e_C[3 * kc + 2])));
+      if (MOTION && dot(e0_W, e1_W) < 0.5) continue;
       bool isValid = false, isParallel = false;
-      const V3 hp = triangulate_fast(r0, e0_W, r1, e1_W, sigma, isValid, isParallel);
+      const V3 hp = triangulate_fast(r0, e0_W, r1, e1_W, cos(2.6 * sigma), cos(6.0 * sigma), isValid, isParallel);
+      if (MOTION && !isValid) continue;
       // T_WC.inverse() * hp_W with w = 1: C^T * p + (-(C^T * r)) * 1; z / w compared with 0.1
       const V3 t0 = matTvec(v0.C, r0), t1 = matTvec(v1.C, r1);
       const V3 c0 = matTvec(v0.C, hp), c1 = matTvec(v1.C, hp);
       const double z0 = c0.z + (-t0.z) * 1.0, z1 = c1.z + (-t1.z) * 1.0;
-      if (z0 / 1.0 < 0.1) isValid = false;
-      if (z1 / 1.0 < 0.1) isValid = false;
+      const double minDepth = MOTION ? 0.2 : 0.1;
+      if (z0 / 1.0 < minDepth) isValid = false;
+      if (z1 / 1.0 < minDepth) isValid = false;
       if (dot(e0_W, e1_W) < 0.8) isValid = false;
       if (isValid) {
         distances = dc;
         hps = hp;
         k1_match = kc;
         initialisable = !isParallel;
+        if (MOTION) quality = acos(dot(normalized(hp - r0), normalized(hp - r1)));
       }
     }
   }
@@ -499,17 +522,133 @@ match_stereo_kernel(StereoDev v0, StereoDev v1, double hammingThreshold, double*
     outHp[4 * k0 + 0] = hps.x / 1.0;
     outHp[4 * k0 + 1] = hps.y / 1.0;
     outHp[4 * k0 + 2] = hps.z / 1.0;
-    outHp[4 * k0 + 3] = 1.0;
+    outHp[4 * k0 + 3] = (MOTION && k1_match < 0) ? 0.0 : 1.0;
     outInit[k0] = initialisable ? 1 : 0;
+    if (MOTION) outQuality[k0] = quality;
   }
 }
 
-void launch_match_stereo(const StereoDev& v0, const StereoDev& v1, double hammingThreshold, double* outDist,
-                         int* outK1, double* outHp, uint8_t* outInit, cudaStream_t s) {
+void launch_match_stereo(const StereoDev& v0, const StereoDev& v1, const uint8_t* use0, bool motion,
+                         double hammingThreshold, double* outDist, int* outK1, double* outHp, uint8_t* outInit,
+                         double* outQuality, cudaStream_t s) {
   if (v0.n <= 0) return;
   const int warpsPerBlock = 8;
   const int blocks = (v0.n + warpsPerBlock - 1) / warpsPerBlock;
-  match_stereo_kernel<<<blocks, warpsPerBlock * 32, 0, s>>>(v0, v1, hammingThreshold, outDist, outK1, outHp, outInit);
+  if (motion)
+    match_stereo_kernel<true><<<blocks, warpsPerBlock * 32, 0, s>>>(v0, v1, use0, hammingThreshold, outDist, outK1,
+                                                                   outHp, outInit, outQuality);
+  else
+    match_stereo_kernel<false><<<blocks, warpsPerBlock * 32, 0, s>>>(v0, v1, use0, hammingThreshold, outDist, outK1,
+                                                                    outHp, outInit, outQuality);
+}
+
+// ----------------------------------------------------------------------------------------------
+// D. 3D-2D matching of uninitialised landmarks, Frontend::matchToMapByThreadUnitialised (Frontend.cpp:1830-1956)
+// ----------------------------------------------------------------------------------------------
+// One warp per keypoint, rows in landmark-major order. A row that beats the running best must pass, in this order:
+// the epipolar-plane / divergence test unless the rays are (nearly) parallel (:1907-1917), triangulateFast valid
+// (:1922-1927), >= 0.2 m from both centres (:1930-1936). Loop-closure rule (:1941-1944): an accepted row of the
+// keypoint's previous landmark only counts and ends that landmark's rows for this keypoint. hps_W is overwritten
+// only by non-parallel accepts (stale value kept otherwise, :1946-1951).
+struct UninitArgs {
+  double r_WC[3];
+  double cos26Sigma, cos6Sigma;   // sigma = 1 / focalLength; cos(2.6 sigma), cos(6 sigma) from the host's libm
+  double hammingThreshold;
+};
+
+__global__ void __launch_bounds__(256)
+match_uninitialised_kernel(const uint8_t* __restrict__ queries, const double* __restrict__ kp_e_W,
+                           const uint8_t* __restrict__ use, const int* __restrict__ previousOwner, int nk,
+                           const uint8_t* __restrict__ map, const int* __restrict__ owner,
+                           const double* __restrict__ map_e_W, const double* __restrict__ map_r_W, int nm,
+                           UninitArgs a, double* __restrict__ outDist, int* __restrict__ outOwner,
+                           double* __restrict__ outHp, uint8_t* __restrict__ outHpWritten,
+                           unsigned* __restrict__ outCtr) {
+  const int lane = threadIdx.x & 31;
+  const int k = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (k >= nk) return;
+  double best = a.hammingThreshold;
+  int bestO = -1, skipOwner = -1;
+  unsigned ctr = 0;
+  V3 hps = v3(0.0, 0.0, 0.0);
+  bool hpWritten = false;
+  if (use[k]) {
+    unsigned q[kDescWords];
+    load_desc(queries, k, q);
+    const V3 e1_W = v3(kp_e_W[3 * k], kp_e_W[3 * k + 1], kp_e_W[3 * k + 2]);
+    const V3 rC = v3(a.r_WC[0], a.r_WC[1], a.r_WC[2]);
+    const int prev = previousOwner ? previousOwner[k] : -1;
+    for (int base = 0; base < nm; base += 32) {
+      const int m = base + lane;
+      double d = 1e9;
+      if (m < nm) {
+        unsigned r[kDescWords];
+        load_desc(map, m, r);
+        d = (double)hamming384(q, r);
+      }
+      unsigned pending = __ballot_sync(0xffffffffu, d < best);
+      while (pending) {
+        const int src = __ffs(pending) - 1;
+        pending &= pending - 1;
+        const double dc = __shfl_sync(0xffffffffu, d, src);
+        const int mc = base + src;
+        if (!(dc < best)) continue;
+        const int oc = owner[mc];
+        if (oc == skipOwner) continue;  // "break" out of this landmark's descriptor loop happened earlier
+        const V3 e0_W = v3(map_e_W[3 * mc], map_e_W[3 * mc + 1], map_e_W[3 * mc + 2]);
+        const V3 r0_W = v3(map_r_W[3 * mc], map_r_W[3 * mc + 1], map_r_W[3 * mc + 2]);
+        if (dot(e0_W, e1_W) < a.cos6Sigma) {
+          const V3 et_W = normalized(rC - r0_W);
+          const V3 n0_W = normalized(cross(e0_W, et_W));
+          const V3 n1_W = normalized(cross(e1_W, et_W));
+          if (dot(n0_W, n1_W) < a.cos6Sigma) continue;                             // not in the epipolar plane
+          if (dot(cross(e0_W, e1_W), normalized(n0_W + n0_W)) > 0.0) continue;     // divergent rays ("n0 + n0" sic)
+        }
+        bool isValid = false, isParallel = false;
+        const V3 hp = triangulate_fast(r0_W, e0_W, rC, e1_W, a.cos26Sigma, a.cos6Sigma, isValid, isParallel);
+        if (!isValid) continue;
+        const V3 p_W = v3(hp.x / 1.0, hp.y / 1.0, hp.z / 1.0);
+        if (norm(p_W - r0_W) < 0.2) isValid = false;
+        if (norm(p_W - rC) < 0.2) isValid = false;
+        if (!isValid) continue;
+        if (oc == prev) {
+          ++ctr;
+          skipOwner = oc;
+          continue;
+        }
+        best = dc;
+        bestO = oc;
+        ++ctr;
+        if (!isParallel) {
+          hps = hp;
+          hpWritten = true;
+        }
+      }
+    }
+  }
+  if (lane == 0) {
+    outDist[k] = best;
+    outOwner[k] = bestO;
+    outHp[4 * k + 0] = hps.x;
+    outHp[4 * k + 1] = hps.y;
+    outHp[4 * k + 2] = hps.z;
+    outHp[4 * k + 3] = hpWritten ? 1.0 : 0.0;
+    outHpWritten[k] = hpWritten ? 1 : 0;
+    outCtr[k] = ctr;
+  }
+}
+
+void launch_match_uninitialised(const uint8_t* queries, const double* kp_e_W, const uint8_t* use,
+                                const int* previousOwner, int nk, const uint8_t* map, const int* owner,
+                                const double* map_e_W, const double* map_r_W, int nm, const UninitArgs& a,
+                                double* outDist, int* outOwner, double* outHp, uint8_t* outHpWritten, unsigned* outCtr,
+                                cudaStream_t s) {
+  if (nk <= 0) return;
+  const int warpsPerBlock = 8;
+  const int blocks = (nk + warpsPerBlock - 1) / warpsPerBlock;
+  match_uninitialised_kernel<<<blocks, warpsPerBlock * 32, 0, s>>>(queries, kp_e_W, use, previousOwner, nk, map, owner,
+                                                                  map_e_W, map_r_W, nm, a, outDist, outOwner, outHp,
+                                                                  outHpWritten, outCtr);
 }
 
 }  // namespace okc

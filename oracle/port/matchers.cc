@@ -214,4 +214,118 @@ void port_match_stereo(const PortStereoView* v0, const PortStereoView* v1, doubl
   }
 }
 
+// Frontend::matchToMapByThreadUnitialised for thread slice threadIdx of numThreads (Frontend.cpp:1830-1956).
+// The caller passes only the landmarks this call iterates over (not is3d, and inside the loop-closure set when one
+// is given, :1876-1886) as slots 0..L-1 in std::map order; rows of slot l are map[rowStart[l] .. rowStart[l+1])
+// with their rays e_W / origins r_W (LandmarkToMatch::e_W, r_W columns). kp_e_W[k] = T_WC1.C() * e1_C.normalized()
+// (:1862-1863); use[k] as computed at :1860-1870; previousOwner[k] = slot of multiFrame->landmarkId(im,k) or -1.
+// distances / lmIds / hps_W (xyzw, zero-initialised) are in/out like the reference's vectors.
+void port_match_uninit_thread(int threadIdx, int numThreads, const uint8_t* ddata, const double* kp_e_W,
+                              const uint8_t* use, const int32_t* previousOwner, int numKeypoints, const uint8_t* map,
+                              const int32_t* rowStart, int numLandmarks, const double* map_e_W,
+                              const double* map_r_W, const double* r_WC, double focalLength, double* distances,
+                              int32_t* lmIds, double* hps_W, uint8_t* hpsWritten, uint64_t* ctrs) {
+  ctrs[threadIdx] = 0;
+  const size_t segment = static_cast<size_t>(numKeypoints) / numThreads;
+  const size_t startK = segment * threadIdx;
+  const size_t endK = threadIdx + 1 == numThreads ? static_cast<size_t>(numKeypoints) : startK + segment;
+  const double sigma = 1.0 / focalLength;
+  const double cos6Sigma = std::cos(6.0 * sigma);
+  const V3 rC = mk(r_WC[0], r_WC[1], r_WC[2]);
+  for (int l = 0; l < numLandmarks; ++l) {
+    for (size_t k = startK; k < endK; k++) {
+      if (!use[k]) continue;
+      const V3 e1_W = mk(kp_e_W[3 * k], kp_e_W[3 * k + 1], kp_e_W[3 * k + 2]);
+      const uint8_t* descriptorK = ddata + k * 48;
+      for (int r = rowStart[l]; r < rowStart[l + 1]; ++r) {
+        const double dist = hamming48(descriptorK, map + static_cast<size_t>(r) * 48);
+        if (dist < distances[k]) {
+          const V3 e0_W = mk(map_e_W[3 * r], map_e_W[3 * r + 1], map_e_W[3 * r + 2]);
+          const V3 r0_W = mk(map_r_W[3 * r], map_r_W[3 * r + 1], map_r_W[3 * r + 2]);
+          if (dot(e0_W, e1_W) < cos6Sigma) {
+            const V3 et_W = normalized(sub(rC, r0_W));
+            const V3 n0_W = normalized(cross(e0_W, et_W));
+            const V3 n1_W = normalized(cross(e1_W, et_W));
+            if (dot(n0_W, n1_W) < cos6Sigma) continue;
+            if (dot(cross(e0_W, e1_W), normalized(add(n0_W, n0_W))) > 0.0) continue;  // "n0_W + n0_W" sic (:1914)
+          }
+          bool isValid = false, isParallel = false;
+          const V3 hp = triangulateFast(r0_W, e0_W, rC, e1_W, sigma, isValid, isParallel);
+          if (!isValid) continue;
+          const V3 p_W = mk(hp.x / 1.0, hp.y / 1.0, hp.z / 1.0);
+          if (norm(sub(p_W, r0_W)) < 0.2) isValid = false;
+          if (norm(sub(p_W, rC)) < 0.2) isValid = false;
+          if (!isValid) continue;
+          if (previousOwner && l == previousOwner[k]) {
+            ctrs[threadIdx]++;
+            break;
+          }
+          distances[k] = dist;
+          lmIds[k] = l;
+          ctrs[threadIdx]++;
+          if (!isParallel) {
+            hps_W[4 * k + 0] = hp.x;
+            hps_W[4 * k + 1] = hp.y;
+            hps_W[4 * k + 2] = hp.z;
+            hps_W[4 * k + 3] = 1.0;
+            hpsWritten[k] = 1;
+          }
+        }
+      }
+    }
+  }
+}
+
+// Worker lambda of Frontend::matchMotionStereo for all k0 (Frontend.cpp:2053-2137), up to (not including) the
+// reprojection check of :2140-2147. use0[k0] folds the estimator-state tests (:2056-2064, 2082-2084).
+void port_match_motion_stereo(const PortStereoView* v0, const uint8_t* use0, const PortStereoView* v1, double threshold,
+                              double* outDist, int32_t* outK1, double* outHp, uint8_t* outInit, double* outQuality) {
+  const V3 r0 = mk(v0->r[0], v0->r[1], v0->r[2]), r1 = mk(v1->r[0], v1->r[1], v1->r[2]);
+  for (int k0 = 0; k0 < v0->n; ++k0) {
+    uint32_t distances = static_cast<uint32_t>(threshold);
+    bool initialisable = false;
+    double quality = 0.0;
+    V3 hps = mk(0, 0, 0);
+    double hw = 0.0;
+    int k1_max = -1;
+    if (use0[k0] && v0->bp_valid[k0]) {
+      const V3 e0_W = normalized(matvec(v0->C, mk(v0->e_C[3 * k0], v0->e_C[3 * k0 + 1], v0->e_C[3 * k0 + 2])));
+      const double sigma = v0->size[k0] / v0->f * 0.125;
+      for (int kk = 0; kk < v1->n; ++kk) {
+        const uint32_t dist = hamming48(v0->desc + 48 * static_cast<size_t>(k0), v1->desc + 48 * static_cast<size_t>(kk));
+        if (dist < distances) {
+          bool isValid = false, isParallel = false;
+          if (!v1->bp_valid[kk]) continue;
+          const V3 e1_W = normalized(matvec(v1->C, mk(v1->e_C[3 * kk], v1->e_C[3 * kk + 1], v1->e_C[3 * kk + 2])));
+          if (dot(e0_W, e1_W) < 0.5) continue;
+          const V3 hp = triangulateFast(r0, e0_W, r1, e1_W, sigma, isValid, isParallel);
+          if (!isValid) continue;
+          const V3 t0 = matTvec(v0->C, r0), t1 = matTvec(v1->C, r1);
+          const V3 c0 = matTvec(v0->C, hp), c1 = matTvec(v1->C, hp);
+          const double z0 = c0.z + (-t0.z) * 1.0, z1 = c1.z + (-t1.z) * 1.0;
+          if (dot(e0_W, e1_W) < 0.8) isValid = false;
+          if (z0 / 1.0 < 0.2) isValid = false;
+          if (z1 / 1.0 < 0.2) isValid = false;
+          if (isValid) {
+            k1_max = kk;
+            distances = dist;
+            quality = std::acos(dot(normalized(sub(hp, r0)), normalized(sub(hp, r1))));
+            hps = hp;
+            hw = 1.0;
+            initialisable = !isParallel;
+          }
+        }
+      }
+    }
+    outDist[k0] = static_cast<double>(distances);
+    outK1[k0] = k1_max;
+    outHp[4 * k0 + 0] = hps.x;
+    outHp[4 * k0 + 1] = hps.y;
+    outHp[4 * k0 + 2] = hps.z;
+    outHp[4 * k0 + 3] = hw;
+    outInit[k0] = initialisable ? 1 : 0;
+    outQuality[k0] = quality;
+  }
+}
+
 }  // extern "C"

@@ -216,6 +216,10 @@ class Port:
         L.port_match_to_map_thread.argtypes = [_i, _i, _vp, _vp, _vp, _i, _vp, _vp, _i, _vp, _vp, _d, _vp, _vp, _vp,
                                                _vp]
         L.port_match_stereo.argtypes = [C.POINTER(PortStereoView), C.POINTER(PortStereoView), _d, _vp, _vp, _vp, _vp]
+        L.port_match_motion_stereo.argtypes = [C.POINTER(PortStereoView), _vp, C.POINTER(PortStereoView), _d, _vp, _vp,
+                                               _vp, _vp, _vp]
+        L.port_match_uninit_thread.argtypes = [_i, _i, _vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _vp, _vp, _vp, _d, _vp,
+                                               _vp, _vp, _vp, _vp]
 
     def hamming_best(self, queries, mp, threshold, index_offset=0, nthreads=1):
         q = np.ascontiguousarray(queries, np.uint8).reshape(-1, 48)
@@ -247,6 +251,61 @@ class Port:
                                             _ptr(pr), _ptr(i3) if i3 is not None else None, float(thresh_sq),
                                             _ptr(dist), _ptr(ids), _ptr(ctrs), _ptr(errs))
         return dist, ids, ctrs, errs
+
+    def match_to_map_uninitialised(self, queries, kp_e_W, use, previous_owner, mp, owner, map_e_W, map_r_W,
+                                   num_landmarks, r_WC, focal, threshold, num_slices):
+        """All thread slices of matchToMapByThreadUnitialised, one after another."""
+        q = np.ascontiguousarray(queries, np.uint8).reshape(-1, 48)
+        ke = np.ascontiguousarray(kp_e_W, np.float64).reshape(-1, 3)
+        us = np.ascontiguousarray(use, np.uint8)
+        pv = np.ascontiguousarray(previous_owner, np.int32) if previous_owner is not None else None
+        m = np.ascontiguousarray(mp, np.uint8).reshape(-1, 48)
+        me = np.ascontiguousarray(map_e_W, np.float64).reshape(-1, 3)
+        mr = np.ascontiguousarray(map_r_W, np.float64).reshape(-1, 3)
+        rc = np.ascontiguousarray(r_WC, np.float64)
+        owner = np.asarray(owner, np.int64)
+        row_start = np.searchsorted(owner, np.arange(num_landmarks + 1)).astype(np.int32)
+        nk = len(q)
+        dist = np.full(nk, float(threshold), np.float64)
+        ids = np.full(nk, -1, np.int32)
+        hps = np.zeros((nk, 4), np.float64)
+        hw = np.zeros(nk, np.uint8)
+        ctrs = np.zeros(num_slices, np.uint64)
+        for t in range(num_slices):
+            self.L.port_match_uninit_thread(t, num_slices, _ptr(q), _ptr(ke), _ptr(us), _ptr(pv) if pv is not None else None,
+                                            nk, _ptr(m), _ptr(row_start), int(num_landmarks), _ptr(me), _ptr(mr),
+                                            _ptr(rc), float(focal), _ptr(dist), _ptr(ids), _ptr(hps), _ptr(hw),
+                                            _ptr(ctrs))
+        return dist, ids, hps, hw, ctrs
+
+    @staticmethod
+    def _view(v, keep):
+        s = PortStereoView()
+        desc = np.ascontiguousarray(v["desc"], np.uint8).reshape(-1, 48)
+        size = np.ascontiguousarray(v["size"], np.float64)
+        e_C = np.ascontiguousarray(v["e_C"], np.float64).reshape(-1, 3)
+        bpv = np.ascontiguousarray(v["bp_valid"], np.uint8)
+        keep.extend([desc, size, e_C, bpv])
+        s.desc, s.size, s.e_C, s.bp_valid = desc.ctypes.data, size.ctypes.data, e_C.ctypes.data, bpv.ctypes.data
+        s.n = len(desc)
+        s.C[:] = list(np.asarray(v["C_WC"], np.float64).reshape(9))
+        s.r[:] = list(np.asarray(v["r_WC"], np.float64).reshape(3))
+        s.f = float(v["f"])
+        return s
+
+    def match_motion_stereo(self, view0, use0, view1, threshold):
+        keep = []
+        s0, s1 = self._view(view0, keep), self._view(view1, keep)
+        u0 = np.ascontiguousarray(use0, np.uint8)
+        n0 = s0.n
+        dist = np.empty(n0, np.float64)
+        k1 = np.empty(n0, np.int32)
+        hp = np.empty((n0, 4), np.float64)
+        init = np.empty(n0, np.uint8)
+        qual = np.empty(n0, np.float64)
+        self.L.port_match_motion_stereo(C.byref(s0), _ptr(u0), C.byref(s1), float(threshold), _ptr(dist), _ptr(k1),
+                                        _ptr(hp), _ptr(init), _ptr(qual))
+        return dist, k1, hp, init, qual
 
     def match_stereo(self, view0, view1, threshold):
         keep = []

@@ -322,3 +322,67 @@ def test_batch_equals_single_calls(on_device, mod, ctx, port, syn):
     for c in cams:
         c.close()
     del keep
+
+
+def _world_rays(v):
+    e = v["e_C"] @ np.asarray(v["C_WC"]).T
+    return e / np.linalg.norm(e, axis=1, keepdims=True)
+
+
+@pytest.mark.parametrize("slices,with_previous", [(4, False), (3, True), (1, True)])
+def test_match_to_map_uninitialised_vs_port(slices, with_previous, mod, ctx, port, syn):
+    """Row a15: landmarks = the other view's keypoints (1-3 descriptor rows each, ray + origin per row)."""
+    v0, v1 = stereo_views(mod, ctx, syn)
+    rng = np.random.default_rng(42)
+    rows, owner, e_rows, r_rows = [], [], [], []
+    e0 = _world_rays(v0)
+    for j in range(len(v0["desc"])):
+        nd = int(rng.integers(1, 4))
+        base = np.repeat(v0["desc"][j:j + 1], nd, 0)
+        rows.append(syn.flip_bits(base, rng.binomial(384, 0.03, nd), rng))
+        owner += [j] * nd
+        e_rows += [e0[j]] * nd
+        r_rows += [np.asarray(v0["r_WC"])] * nd
+    rows = np.concatenate(rows)
+    owner = np.asarray(owner, np.int32)
+    e_rows, r_rows = np.asarray(e_rows), np.asarray(r_rows)
+    kp_e = _world_rays(v1)
+    use = (v1["bp_valid"] > 0) & (np.arange(len(kp_e)) % 13 != 0)
+    prev = None
+    if with_previous:
+        # loop-closure mode: some keypoints already carry the landmark they will match again (:1941-1944)
+        first = ctx.match_to_map_uninitialised(v1["desc"], kp_e, use, None, rows, owner, e_rows, r_rows, v1["r_WC"],
+                                               v1["f"], 60.0, slices)
+        prev = np.full(len(kp_e), -1, np.int32)
+        hit = np.nonzero(first[1] >= 0)[0]
+        prev[hit[::2]] = first[1][hit[::2]]
+        prev[hit[1::4]] = 0
+    got = ctx.match_to_map_uninitialised(v1["desc"], kp_e, use, prev, rows, owner, e_rows, r_rows, v1["r_WC"], v1["f"],
+                                         60.0, slices)
+    want = port.match_to_map_uninitialised(v1["desc"], kp_e, use, prev, rows, owner, e_rows, r_rows, len(v0["desc"]),
+                                           v1["r_WC"], v1["f"], 60.0, slices)
+    assert np.array_equal(got[0], want[0]), "distances"
+    assert np.array_equal(got[1], want[1]), "landmark slots"
+    assert got[2].tobytes() == want[2].tobytes(), "hps_W"
+    assert np.array_equal(got[3], want[3]), "hps written"
+    assert np.array_equal(got[4], want[4]), "ctrs"
+    assert (want[1] >= 0).sum() > (10 if with_previous else 50)
+    assert want[4].sum() >= (want[1] >= 0).sum()
+
+
+def test_match_motion_stereo_vs_port(mod, ctx, port, syn):
+    """Row a16: older keyframe vs the unmatched keypoints of the current frame (packed), per camera."""
+    v0, v1 = stereo_views(mod, ctx, syn)
+    for a, b in ((v0, v1), (v1, v0)):
+        use0 = (np.arange(len(a["desc"])) % 7 != 0).astype(np.uint8)
+        keep1 = np.nonzero(np.arange(len(b["desc"])) % 5 != 0)[0]   # the reference packs the unmatched k1 (:2034-2047)
+        packed = dict(b, desc=b["desc"][keep1], size=b["size"][keep1], e_C=b["e_C"][keep1], bp_valid=b["bp_valid"][keep1])
+        got = ctx.match_motion_stereo(a, use0, packed, 60.0)
+        want = port.match_motion_stereo(a, use0, packed, 60.0)
+        assert np.array_equal(got[0], want[0]), "distances"
+        assert np.array_equal(got[1], want[1]), "k1"
+        assert got[2].tobytes() == want[2].tobytes(), "hp_W"
+        assert np.array_equal(got[3], want[3]), "initialisable"
+        # quality = acos(...): device libm vs glibc, float tolerance of BASELINE.json (1e-4), in practice <= 1 ulp
+        assert np.allclose(got[4], want[4], rtol=0, atol=1e-12)
+        assert (want[1] >= 0).sum() > 50 and np.all(want[1][use0 == 0] == -1)
