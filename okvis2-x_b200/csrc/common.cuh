@@ -50,7 +50,7 @@ struct Slot {
   // detect
   const uint8_t* image;    // (per enqueue) H*W u8: the slot's own upload buffer or a caller's device image
   int32_t* scores;         // H*W Harris scores
-  uint32_t* bitmap;        // H * ceil(W/32) words: NMS survivors
+  uint32_t* bitmap;        // harris_bitmap_words(W, H) words: NMS survivors (layout: see harris_nms_kernel)
   uint64_t* cand;          // kCandCap keys (std::sort order) + max_keypoints kept keys
   uint8_t* order_scratch;  // order_candidates arrays when the candidates do not fit in shared memory
   uint8_t* occupancy;      // global fallback for the uniformity occupancy image
@@ -93,7 +93,10 @@ struct DescribeArgs {
 };
 
 // All launchers: `slots` = device array, `n` = number of slots in this launch.
-void launch_harris_nms(const Slot* slots, int n, const DetectArgs& a, cudaStream_t s);
+// aligned: every slot's image pointer is 4-byte aligned and width % 4 == 0 (32-bit pixel loads, int4 score stores)
+void launch_harris_nms(const Slot* slots, int n, const DetectArgs& a, cudaStream_t s, bool aligned);
+size_t harris_bitmap_words(int W, int H);
+void harris_bitmap_pos(int W, int x, int y, size_t* word, int* bit);
 size_t order_scratch_bytes();
 void launch_order_candidates(const Slot* slots, int n, const DetectArgs& a, cudaStream_t s);
 void launch_select_keypoints(const Slot* slots, int n, const float* lut, const DetectArgs& a, cudaStream_t s);

@@ -19,106 +19,187 @@ namespace okc {
 // ----------------------------------------------------------------------------------------------
 // Harris score + 8-neighbour NMS
 // ----------------------------------------------------------------------------------------------
-constexpr int TX = 32;   // score tile width  (outputs per CTA)
-constexpr int TY = 16;   // score tile height
-constexpr int PXW = TX + 6, PXH = TY + 6;   // pixel tile, halo 3
-constexpr int PRW = TX + 4, PRH = TY + 4;   // gradient-product tile, halo 2
-constexpr int SCW = TX + 2, SCH = TY + 2;   // score tile, halo 1 (NMS neighbours)
+// Register-marching stencil: a warp owns a strip of 128 columns (4 consecutive columns per lane) and walks down
+// kHarrisRows output rows; every intermediate (Scharr partial sums, gradient products, horizontally smoothed
+// products, scores, row maxima) lives in registers, neighbours across lanes come from warp shuffles, and there is
+// no shared memory and no block-level synchronisation. Lanes 0 and 31 only feed their neighbours (halo), so a
+// warp emits 120 columns. Per pixel this is ~60 integer operations against ~320 in a shared-memory tile
+// formulation (index arithmetic, byte accesses, four barriers) - the kernel is issue-bound, so that is the time.
+//
+// Arithmetic (brisk/src/harris-scores.cc:124-296): with h = I[x-1] - I[x+1] and s = 3 I[x-1] + 10 I[x] + 3 I[x+1]
+// per row, dx = (3 h[y-1] + 10 h[y] + 3 h[y+1]) << 3, dy = (s[y-1] - s[y+1]) << 3 (both fit int16 as in the
+// reference), products (a*b) >> 16 (= _mm_mulhi_epi16), 3x3 binomial smoothing as one integer sum >> 4, score =
+// dxdx*dydy - dxdy^2 - (((dxdx + dydy) >> 1)^2) / 5. Scores are defined on rows 2..H-3, cols 2..W-3 and 0 on the
+// frame (Mat::zeros, :73).
+//
+// NMS survivors (harris-score-calculator.cc:76-117: >= threshold, no neighbour strictly greater) are published as a
+// bitmap with kStripWords words per (row, strip): bit b of word j of strip s is column 120 s - 4 + 32 j + b.
+// Row-major, strip-major, bit-ascending order = raster order, which order_candidates_kernel relies on.
+constexpr int kHarrisRows = 48;      // output rows per warp
+constexpr int kStripCols = 120;      // output columns per warp
+constexpr int kStripWords = 4;
 
-__global__ void __launch_bounds__(256) harris_nms_kernel(const Slot* __restrict__ slots, int W, int H,
+__host__ __device__ inline int harris_strips(int W) { return (W + kStripCols - 1) / kStripCols; }
+
+template <bool ALIGNED>
+__global__ void __launch_bounds__(128) harris_nms_kernel(const Slot* __restrict__ slots, int W, int H,
                                                          int absThreshold) {
   const Slot& slot = slots[blockIdx.z];
   const uint8_t* __restrict__ img = slot.image;
   int32_t* __restrict__ scores = slot.scores;
   uint32_t* __restrict__ bitmap = slot.bitmap;
-  __shared__ uint8_t px[PXH][PXW + 2];
-  __shared__ short pxx[PRH][PRW], pxy[PRH][PRW], pyy[PRH][PRW];
-  __shared__ int sc[SCH][SCW];
+  const int lane = threadIdx.x & 31;
+  const int strip = blockIdx.x;
+  const int q0 = (blockIdx.y * 4 + (threadIdx.x >> 5)) * kHarrisRows;
+  if (q0 >= H) return;
+  const int q1 = min(H, q0 + kHarrisRows);
+  const int x = strip * kStripCols - 4 + 4 * lane;  // first of this lane's 4 columns
+  const int wordsPerRow = harris_strips(W) * kStripWords;
+  const bool emit = lane >= 1 && lane <= 30;
 
-  const int tid = threadIdx.y * blockDim.x + threadIdx.x;
-  const int x0 = blockIdx.x * TX, y0 = blockIdx.y * TY;
+  int hA[4] = {0, 0, 0, 0}, hB[4] = {0, 0, 0, 0}, sA[4] = {0, 0, 0, 0}, sB[4] = {0, 0, 0, 0};
+  int xxA[4] = {0, 0, 0, 0}, xxB[4] = {0, 0, 0, 0}, xyA[4] = {0, 0, 0, 0}, xyB[4] = {0, 0, 0, 0};
+  int yyA[4] = {0, 0, 0, 0}, yyB[4] = {0, 0, 0, 0};
+  int scB[4] = {0, 0, 0, 0}, lrB[4] = {0, 0, 0, 0}, mA[4] = {0, 0, 0, 0}, mB[4] = {0, 0, 0, 0};
 
-  // 1. pixel tile (zero outside the image; such pixels never reach a valid score)
-  for (int i = tid; i < PXH * PXW; i += 256) {
-    int ly = i / PXW, lx = i - ly * PXW;
-    int gx = x0 - 3 + lx, gy = y0 - 3 + ly;
-    uint8_t v = 0;
-    if (gx >= 0 && gx < W && gy >= 0 && gy < H) v = __ldg(img + (size_t)gy * W + gx);
-    px[ly][lx] = v;
-  }
-  __syncthreads();
-
-  // 2. Scharr gradients (<<3, int16) and their products (mulhi = >>16), harris-scores.cc:124-206.
-  //    Defined on rows 1..H-2, cols 1..W-2 only.
-  for (int i = tid; i < PRH * PRW; i += 256) {
-    int ly = i / PRW, lx = i - ly * PRW;
-    int gx = x0 - 2 + lx, gy = y0 - 2 + ly;
-    short vxx = 0, vxy = 0, vyy = 0;
-    if (gx >= 1 && gx <= W - 2 && gy >= 1 && gy <= H - 2) {
-      int cy = ly + 1, cx = lx + 1;  // centre in px[][]
-      int a00 = px[cy - 1][cx - 1], a01 = px[cy - 1][cx], a02 = px[cy - 1][cx + 1];
-      int a10 = px[cy][cx - 1], a12 = px[cy][cx + 1];
-      int a20 = px[cy + 1][cx - 1], a21 = px[cy + 1][cx], a22 = px[cy + 1][cx + 1];
-      int dx = (10 * (a10 - a12) + 3 * (a00 - a02) + 3 * (a20 - a22)) << 3;
-      int dy = (10 * (a01 - a21) + 3 * (a00 - a20) + 3 * (a02 - a22)) << 3;
-      vxx = (short)((dx * dx) >> 16);
-      vyy = (short)((dy * dy) >> 16);
-      vxy = (short)((dx * dy) >> 16);
+  for (int r = q0 - 3; r <= q1 + 2; ++r) {
+    // ---- 1. pixels of row r (clamped; rows/columns outside the image never reach a valid score) ----
+    const int rr = r < 0 ? 0 : (r >= H ? H - 1 : r);
+    unsigned w = 0;
+    if (ALIGNED) {
+      if (x >= 0 && x < W) w = __ldg(reinterpret_cast<const unsigned*>(img + (size_t)rr * W + x));
+    } else {
+#pragma unroll
+      for (int c = 0; c < 4; ++c)
+        if (x + c >= 0 && x + c < W) w |= (unsigned)__ldg(img + (size_t)rr * W + x + c) << (8 * c);
     }
-    pxx[ly][lx] = vxx;
-    pxy[ly][lx] = vxy;
-    pyy[ly][lx] = vyy;
-  }
-  __syncthreads();
-
-  // 3. 3x3 binomial smoothing (>>4, arithmetic) and the score, harris-scores.cc:231-296.
-  //    Valid on rows 2..H-3, cols 2..W-3; the 2-pixel frame stays 0 (Mat::zeros).
-  for (int i = tid; i < SCH * SCW; i += 256) {
-    int ly = i / SCW, lx = i - ly * SCW;
-    int gx = x0 - 1 + lx, gy = y0 - 1 + ly;
-    int s = 0;
-    if (gx >= 2 && gx <= W - 3 && gy >= 2 && gy <= H - 3) {
-      int cy = ly + 1, cx = lx + 1;  // centre in the product tiles
-#define OKC_SMOOTH(P)                                                                             \
-  ((4 * (int)P[cy][cx] + 2 * ((int)P[cy - 1][cx] + (int)P[cy + 1][cx] + (int)P[cy][cx - 1] + (int)P[cy][cx + 1]) + \
-    ((int)P[cy - 1][cx - 1] + (int)P[cy - 1][cx + 1] + (int)P[cy + 1][cx - 1] + (int)P[cy + 1][cx + 1])) >> 4)
-      int dxdx = OKC_SMOOTH(pxx);
-      int dxdy = OKC_SMOOTH(pxy);
-      int dydy = OKC_SMOOTH(pyy);
-#undef OKC_SMOOTH
-      int t = (dxdx + dydy) >> 1;
-      s = dxdx * dydy - dxdy * dxdy - (t * t) / 5;
+    const unsigned wl = __shfl_up_sync(0xffffffffu, w, 1), wr = __shfl_down_sync(0xffffffffu, w, 1);
+    int px[6];
+    px[0] = (int)(wl >> 24);
+    px[1] = (int)(w & 0xff);
+    px[2] = (int)((w >> 8) & 0xff);
+    px[3] = (int)((w >> 16) & 0xff);
+    px[4] = (int)(w >> 24);
+    px[5] = (int)(wr & 0xff);
+    int h2[4], s2[4];
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      h2[c] = px[c] - px[c + 2];
+      s2[c] = 3 * (px[c] + px[c + 2]) + 10 * px[c + 1];
     }
-    sc[ly][lx] = s;
-  }
-  __syncthreads();
-
-  // 4. write scores; NMS on rows [2, H-2), cols [2, W-2): keep if >= threshold and no neighbour is
-  //    strictly greater (plateaus survive), harris-score-calculator.cc:76-117. Survivors are published as a
-  //    bitmap (one word per 32-pixel tile row), so that the next kernel can rebuild the reference's RASTER
-  //    candidate order without a sort. Each warp owns one tile row per iteration (TX == 32).
-  const int wordsPerRow = (W + 31) >> 5;
-  for (int i = tid; i < TX * TY; i += 256) {
-    int ly = i / TX, lx = i - ly * TX;
-    int gx = x0 + lx, gy = y0 + ly;
-    bool isMax = false;
-    if (gx < W && gy < H) {
-      int cy = ly + 1, cx = lx + 1;
-      int c = sc[cy][cx];
-      scores[(size_t)gy * W + gx] = c;
-      if (gx >= 2 && gx < W - 2 && gy >= 2 && gy < H - 2 && c >= absThreshold)
-        isMax = !(sc[cy][cx + 1] > c || sc[cy][cx - 1] > c || sc[cy + 1][cx] > c || sc[cy - 1][cx] > c ||
-                  sc[cy + 1][cx + 1] > c || sc[cy + 1][cx - 1] > c || sc[cy - 1][cx + 1] > c ||
-                  sc[cy - 1][cx - 1] > c);
+    // ---- 2. gradients and products of row r-1, horizontally smoothed ----
+    int pxx[4], pxy[4], pyy[4];
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      const int dx = (3 * (hA[c] + h2[c]) + 10 * hB[c]) << 3;
+      const int dy = (sA[c] - s2[c]) << 3;
+      pxx[c] = (dx * dx) >> 16;
+      pxy[c] = (dx * dy) >> 16;
+      pyy[c] = (dy * dy) >> 16;
     }
-    const unsigned word = __ballot_sync(0xffffffffu, isMax);
-    if (lx == 0 && gy < H) bitmap[(size_t)gy * wordsPerRow + blockIdx.x] = word;
+    int xx2[4], xy2[4], yy2[4];
+    {
+      const int lxx = __shfl_up_sync(0xffffffffu, pxx[3], 1), rxx = __shfl_down_sync(0xffffffffu, pxx[0], 1);
+      const int lxy = __shfl_up_sync(0xffffffffu, pxy[3], 1), rxy = __shfl_down_sync(0xffffffffu, pxy[0], 1);
+      const int lyy = __shfl_up_sync(0xffffffffu, pyy[3], 1), ryy = __shfl_down_sync(0xffffffffu, pyy[0], 1);
+      xx2[0] = lxx + 2 * pxx[0] + pxx[1];
+      xx2[1] = pxx[0] + 2 * pxx[1] + pxx[2];
+      xx2[2] = pxx[1] + 2 * pxx[2] + pxx[3];
+      xx2[3] = pxx[2] + 2 * pxx[3] + rxx;
+      xy2[0] = lxy + 2 * pxy[0] + pxy[1];
+      xy2[1] = pxy[0] + 2 * pxy[1] + pxy[2];
+      xy2[2] = pxy[1] + 2 * pxy[2] + pxy[3];
+      xy2[3] = pxy[2] + 2 * pxy[3] + rxy;
+      yy2[0] = lyy + 2 * pyy[0] + pyy[1];
+      yy2[1] = pyy[0] + 2 * pyy[1] + pyy[2];
+      yy2[2] = pyy[1] + 2 * pyy[2] + pyy[3];
+      yy2[3] = pyy[2] + 2 * pyy[3] + ryy;
+    }
+    // ---- 3. score of row p = r-2 ----
+    const int p = r - 2;
+    const bool rowValid = p >= 2 && p <= H - 3;
+    int sc2[4];
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      const int a = (xxA[c] + 2 * xxB[c] + xx2[c]) >> 4;
+      const int b = (yyA[c] + 2 * yyB[c] + yy2[c]) >> 4;
+      const int d = (xyA[c] + 2 * xyB[c] + xy2[c]) >> 4;
+      const int t = (a + b) >> 1;
+      const int v = a * b - d * d - (int)((unsigned)(t * t) / 5u);
+      sc2[c] = (rowValid && x + c >= 2 && x + c <= W - 3) ? v : 0;
+    }
+    if (emit && p >= q0 && p < q1 && x < W) {
+      int32_t* dst = scores + (size_t)p * W + x;
+      if (ALIGNED) {
+        *reinterpret_cast<int4*>(dst) = make_int4(sc2[0], sc2[1], sc2[2], sc2[3]);
+      } else {
+#pragma unroll
+        for (int c = 0; c < 4; ++c)
+          if (x + c < W) dst[c] = sc2[c];
+      }
+    }
+    const int ls = __shfl_up_sync(0xffffffffu, sc2[3], 1), rs = __shfl_down_sync(0xffffffffu, sc2[0], 1);
+    int m2[4], lr2[4];
+    lr2[0] = max(ls, sc2[1]);
+    lr2[1] = max(sc2[0], sc2[2]);
+    lr2[2] = max(sc2[1], sc2[3]);
+    lr2[3] = max(sc2[2], rs);
+#pragma unroll
+    for (int c = 0; c < 4; ++c) m2[c] = max(lr2[c], sc2[c]);
+    // ---- 4. NMS of row q = r-3: top = row r-4 (mA), middle = row r-3 (scB, lrB), bottom = row r-2 (m2) ----
+    const int q = r - 3;
+    if (q >= q0 && q < q1) {   // warp-uniform
+      unsigned nib = 0;
+      if (emit && q >= 2 && q <= H - 3) {
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          const int ctr = scB[c];
+          const bool isMax = x + c >= 2 && x + c <= W - 3 && ctr >= absThreshold &&
+                             ctr >= max(max(mA[c], m2[c]), lrB[c]);
+          nib |= (isMax ? 1u : 0u) << c;
+        }
+      }
+      unsigned v = nib << (4 * (lane & 7));
+      v |= __shfl_xor_sync(0xffffffffu, v, 1);
+      v |= __shfl_xor_sync(0xffffffffu, v, 2);
+      v |= __shfl_xor_sync(0xffffffffu, v, 4);
+      if ((lane & 7) == 0) bitmap[(size_t)q * wordsPerRow + strip * kStripWords + (lane >> 3)] = v;
+    }
+    // ---- 5. rotate the row windows ----
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      hA[c] = hB[c];
+      hB[c] = h2[c];
+      sA[c] = sB[c];
+      sB[c] = s2[c];
+      xxA[c] = xxB[c];
+      xxB[c] = xx2[c];
+      xyA[c] = xyB[c];
+      xyB[c] = xy2[c];
+      yyA[c] = yyB[c];
+      yyB[c] = yy2[c];
+      mA[c] = mB[c];
+      mB[c] = m2[c];
+      scB[c] = sc2[c];
+      lrB[c] = lr2[c];
+    }
   }
 }
 
-void launch_harris_nms(const Slot* slots, int n, const DetectArgs& a, cudaStream_t s) {
-  dim3 grid((a.width + TX - 1) / TX, (a.height + TY - 1) / TY, n);
-  harris_nms_kernel<<<grid, dim3(32, 8), 0, s>>>(slots, a.width, a.height, a.abs_threshold);
+void launch_harris_nms(const Slot* slots, int n, const DetectArgs& a, cudaStream_t s, bool aligned) {
+  const int chunks = (a.height + kHarrisRows - 1) / kHarrisRows;
+  dim3 grid(harris_strips(a.width), (chunks + 3) / 4, n);
+  if (aligned) harris_nms_kernel<true><<<grid, 128, 0, s>>>(slots, a.width, a.height, a.abs_threshold);
+  else harris_nms_kernel<false><<<grid, 128, 0, s>>>(slots, a.width, a.height, a.abs_threshold);
+}
+
+size_t harris_bitmap_words(int W, int H) { return (size_t)H * harris_strips(W) * kStripWords; }
+
+// position of pixel (x, y) in the bitmap (host helper for tests / debug entry points)
+void harris_bitmap_pos(int W, int x, int y, size_t* word, int* bit) {
+  const int strip = x / kStripCols, off = x - (strip * kStripCols - 4);
+  *word = (size_t)y * harris_strips(W) * kStripWords + (size_t)strip * kStripWords + (off >> 5);
+  *bit = off & 31;
 }
 
 __device__ __forceinline__ void bitonic_sort(uint64_t* keys, int npad) {
@@ -294,7 +375,7 @@ order_candidates_kernel(const Slot* __restrict__ slots, int W, int H) {
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
   // ---- A. candidate count and raster-ordered offsets from the bitmap ----
-  const int wordsPerRow = (W + 31) >> 5;
+  const int wordsPerRow = harris_strips(W) * kStripWords;
   const int words = H * wordsPerRow;
   const int chunk = (words + kOrdThreads - 1) / kOrdThreads;
   const int w0 = tid * chunk, w1 = min(words, w0 + chunk);
@@ -349,7 +430,8 @@ order_candidates_kernel(const Slot* __restrict__ slots, int W, int H) {
     int pos = s_warp[warp] + incl - mine;
     for (int w = w0; w < w1; ++w) {
       unsigned bits = bitmap[w];
-      const int y = w / wordsPerRow, xb = (w - y * wordsPerRow) << 5;
+      const int y = w / wordsPerRow, rem = w - y * wordsPerRow;
+      const int xb = (rem / kStripWords) * kStripCols - 4 + ((rem % kStripWords) << 5);
       while (bits) {
         const int b = __ffs(bits) - 1;
         bits &= bits - 1;

@@ -12,6 +12,7 @@ namespace okc {
 // ----------------------------------------------------------------------------------------------
 // A. plain brute force, queries in registers, map rows streamed through shared memory
 // ----------------------------------------------------------------------------------------------
+constexpr int kMapTile = 512;                   // map rows staged per block iteration by the gated matchers
 constexpr int kMbThreads = 256;
 constexpr int kMbQpt = 4;                       // queries per thread
 constexpr int kMbQTile = kMbThreads * kMbQpt;   // 1024 queries per CTA
@@ -180,28 +181,50 @@ match_to_map_body(const uint8_t* __restrict__ queries, const double* __restrict_
                     unsigned long long* __restrict__ eventsOverflow, int eventCap, int* __restrict__ eventCount) {
   // events [0, eventSlab) go to `events` (the part of the output block that always travels to the host), the rest up
   // to eventCap to `eventsOverflow` (fetched only when needed)
+  // The 8 warps (= 8 keypoints) of a block walk the same map rows: each tile of kMapTile rows has its landmark slot
+  // and projection staged in shared memory once per block (one coalesced owner load + one gather per row), so the
+  // per-pair work of a warp is a shared-memory read, the FP64 gate, and - for the ~1 % of pairs inside the gate - the
+  // 48-byte row and 12 popcounts.
+  __shared__ double s_px[kMapTile], s_py[kMapTile];
+  __shared__ int s_owner[kMapTile];
   const int lane = threadIdx.x & 31;
   const int k = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   // nkDev: the keypoint count is still on the device (frame pipeline: queries are the camera's own descriptors)
   const int nk = nkDev ? min(*nkDev, nkMax) : nkMax;
-  if (k >= nk) return;
+  if ((int)((blockIdx.x * blockDim.x) >> 5) >= nk) return;   // whole block past the last keypoint
+  const bool active = k < nk && (!use || use[k]);
   double best = hammingThreshold;
   int bestO = -1;
-  if (!use || use[k]) {
-    unsigned q[kDescWords];
+  unsigned q[kDescWords];
+  double kx = 0.0, ky = 0.0;
+  if (active) {
     load_desc(queries, k, q);
     // cv::KeyPoint floats widen exactly to the Eigen::Vector2d the reference compares with (Frontend.cpp:1787-1790)
-    const double kx = kp_f ? (double)kp_f[k].x : kp_xy[2 * k], ky = kp_f ? (double)kp_f[k].y : kp_xy[2 * k + 1];
-    for (int base = 0; base < nm; base += 32) {
-      const int m = base + lane;
-      double d = 1e9;
-      int o = -1;
+    kx = kp_f ? (double)kp_f[k].x : kp_xy[2 * k];
+    ky = kp_f ? (double)kp_f[k].y : kp_xy[2 * k + 1];
+  }
+  for (int tile = 0; tile < nm; tile += kMapTile) {
+    __syncthreads();
+    for (int i = threadIdx.x; i < kMapTile; i += blockDim.x) {
+      const int m = tile + i;
       if (m < nm) {
-        o = owner[m];
-        const double rx = proj_xy[2 * o] - kx, ry = proj_xy[2 * o + 1] - ky;
+        const int o = owner[m];
+        s_owner[i] = o;
+        s_px[i] = proj_xy[2 * o];
+        s_py[i] = proj_xy[2 * o + 1];
+      }
+    }
+    __syncthreads();
+    if (!active) continue;
+    const int cnt = min(kMapTile, nm - tile);
+    for (int base = 0; base < cnt; base += 32) {
+      const int i = base + lane;
+      double d = 1e9;
+      if (i < cnt) {
+        const double rx = s_px[i] - kx, ry = s_py[i] - ky;
         if (!(rx * rx + ry * ry > threshSq)) {
           unsigned r[kDescWords];
-          load_desc(map, m, r);
+          load_desc(map, tile + i, r);
           d = (double)hamming384(q, r);
         }
       }
@@ -210,13 +233,12 @@ match_to_map_body(const uint8_t* __restrict__ queries, const double* __restrict_
         const int src = __ffs(pending) - 1;
         pending &= pending - 1;
         const double dc = __shfl_sync(0xffffffffu, d, src);
-        const int oc = __shfl_sync(0xffffffffu, o, src);
         if (dc < best) {
           best = dc;
-          bestO = oc;
+          bestO = s_owner[base + src];
           if (lane == 0) {
             const int e = atomicAdd(eventCount, 1);
-            const unsigned long long ev = ((unsigned long long)(unsigned)(base + src) << 32) | (unsigned)k;
+            const unsigned long long ev = ((unsigned long long)(unsigned)(tile + base + src) << 32) | (unsigned)k;
             if (e < eventSlab) events[e] = ev;
             else if (e < eventCap) eventsOverflow[e - eventSlab] = ev;
           }
@@ -224,6 +246,7 @@ match_to_map_body(const uint8_t* __restrict__ queries, const double* __restrict_
       }
     }
   }
+  if (k >= nk) return;
   if (lane == 0) {
     bestDist[k] = best;
     bestOwner[k] = bestO;
