@@ -35,14 +35,15 @@ namespace okc {
 // NMS survivors (harris-score-calculator.cc:76-117: >= threshold, no neighbour strictly greater) are published as a
 // bitmap with kStripWords words per (row, strip): bit b of word j of strip s is column 120 s - 4 + 32 j + b.
 // Row-major, strip-major, bit-ascending order = raster order, which order_candidates_kernel relies on.
-constexpr int kHarrisRows = 48;      // output rows per warp
+constexpr int kHarrisRows = 32;      // output rows per warp
+constexpr int kHarrisWarps = 2;      // warps per block (independent: no shared memory, no barriers)
 constexpr int kStripCols = 120;      // output columns per warp
 constexpr int kStripWords = 4;
 
 __host__ __device__ inline int harris_strips(int W) { return (W + kStripCols - 1) / kStripCols; }
 
 template <bool ALIGNED>
-__global__ void __launch_bounds__(128) harris_nms_kernel(const Slot* __restrict__ slots, int W, int H,
+__global__ void __launch_bounds__(32 * kHarrisWarps) harris_nms_kernel(const Slot* __restrict__ slots, int W, int H,
                                                          int absThreshold) {
   const Slot& slot = slots[blockIdx.z];
   const uint8_t* __restrict__ img = slot.image;
@@ -50,7 +51,7 @@ __global__ void __launch_bounds__(128) harris_nms_kernel(const Slot* __restrict_
   uint32_t* __restrict__ bitmap = slot.bitmap;
   const int lane = threadIdx.x & 31;
   const int strip = blockIdx.x;
-  const int q0 = (blockIdx.y * 4 + (threadIdx.x >> 5)) * kHarrisRows;
+  const int q0 = (blockIdx.y * kHarrisWarps + (threadIdx.x >> 5)) * kHarrisRows;
   if (q0 >= H) return;
   const int q1 = min(H, q0 + kHarrisRows);
   const int x = strip * kStripCols - 4 + 4 * lane;  // first of this lane's 4 columns
@@ -62,8 +63,8 @@ __global__ void __launch_bounds__(128) harris_nms_kernel(const Slot* __restrict_
   int yyA[4] = {0, 0, 0, 0}, yyB[4] = {0, 0, 0, 0};
   int scB[4] = {0, 0, 0, 0}, lrB[4] = {0, 0, 0, 0}, mA[4] = {0, 0, 0, 0}, mB[4] = {0, 0, 0, 0};
 
-  for (int r = q0 - 3; r <= q1 + 2; ++r) {
-    // ---- 1. pixels of row r (clamped; rows/columns outside the image never reach a valid score) ----
+  // pixels of row r (clamped; rows/columns outside the image never reach a valid score)
+  auto load_row = [&](int r) -> unsigned {
     const int rr = r < 0 ? 0 : (r >= H ? H - 1 : r);
     unsigned w = 0;
     if (ALIGNED) {
@@ -73,6 +74,14 @@ __global__ void __launch_bounds__(128) harris_nms_kernel(const Slot* __restrict_
       for (int c = 0; c < 4; ++c)
         if (x + c >= 0 && x + c < W) w |= (unsigned)__ldg(img + (size_t)rr * W + x + c) << (8 * c);
     }
+    return w;
+  };
+  unsigned wNext = load_row(q0 - 3), wNext2 = load_row(q0 - 2);
+  for (int r = q0 - 3; r <= q1 + 2; ++r) {
+    // ---- 1. pixels of row r; rows r+1, r+2 are already in flight ----
+    const unsigned w = wNext;
+    wNext = wNext2;
+    wNext2 = load_row(r + 2);
     const unsigned wl = __shfl_up_sync(0xffffffffu, w, 1), wr = __shfl_down_sync(0xffffffffu, w, 1);
     int px[6];
     px[0] = (int)(wl >> 24);
@@ -188,9 +197,9 @@ __global__ void __launch_bounds__(128) harris_nms_kernel(const Slot* __restrict_
 
 void launch_harris_nms(const Slot* slots, int n, const DetectArgs& a, cudaStream_t s, bool aligned) {
   const int chunks = (a.height + kHarrisRows - 1) / kHarrisRows;
-  dim3 grid(harris_strips(a.width), (chunks + 3) / 4, n);
-  if (aligned) harris_nms_kernel<true><<<grid, 128, 0, s>>>(slots, a.width, a.height, a.abs_threshold);
-  else harris_nms_kernel<false><<<grid, 128, 0, s>>>(slots, a.width, a.height, a.abs_threshold);
+  dim3 grid(harris_strips(a.width), (chunks + kHarrisWarps - 1) / kHarrisWarps, n);
+  if (aligned) harris_nms_kernel<true><<<grid, 32 * kHarrisWarps, 0, s>>>(slots, a.width, a.height, a.abs_threshold);
+  else harris_nms_kernel<false><<<grid, 32 * kHarrisWarps, 0, s>>>(slots, a.width, a.height, a.abs_threshold);
 }
 
 size_t harris_bitmap_words(int W, int H) { return (size_t)H * harris_strips(W) * kStripWords; }

@@ -26,6 +26,25 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N)); }
 
+// Carry-save popcount of the first 5 words (160 bits): two full adders and a half adder turn 5 POPC into 3
+// (POPC issues at a quarter of the LOP3 rate and is what bounds the plain loop). Exact.
+__device__ __forceinline__ unsigned lop3_xor3(unsigned a, unsigned b, unsigned c) {
+  unsigned d;
+  asm("lop3.b32 %0, %1, %2, %3, 0x96;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+  return d;
+}
+__device__ __forceinline__ unsigned lop3_maj(unsigned a, unsigned b, unsigned c) {
+  unsigned d;
+  asm("lop3.b32 %0, %1, %2, %3, 0xE8;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+  return d;
+}
+__device__ __forceinline__ unsigned csa_popc5(unsigned x0, unsigned x1, unsigned x2, unsigned x3, unsigned x4) {
+  const unsigned s1 = lop3_xor3(x0, x1, x2), c1 = lop3_maj(x0, x1, x2);
+  const unsigned s2 = lop3_xor3(s1, x3, x4), c2 = lop3_maj(s1, x3, x4);
+  const unsigned s3 = c1 ^ c2, c3 = c1 & c2;
+  return __popc(s2) + 2u * __popc(s3) + 4u * __popc(c3);
+}
+
 // best[q] (u64, pre-set to ~0) receives min over rows of (dist << 32 | global row index) with dist < threshold.
 // PREFIX = number of leading 32-bit words summed before the early-out test "partial >= current best"
 // (exact: the full distance can only be larger). PREFIX = 12 disables the early-out.
@@ -90,8 +109,12 @@ hamming_best_kernel(const uint4* __restrict__ queries, int nq, const uint4* __re
 #pragma unroll
       for (int j = 0; j < kMbQpt; ++j) {
         unsigned d = 0;
+        if (PREFIX == 5) {
+          d = csa_popc5(q[j][0] ^ m[0], q[j][1] ^ m[1], q[j][2] ^ m[2], q[j][3] ^ m[3], q[j][4] ^ m[4]);
+        } else {
 #pragma unroll
-        for (int w = 0; w < PREFIX; ++w) d += __popc(q[j][w] ^ m[w]);
+          for (int w = 0; w < PREFIX; ++w) d += __popc(q[j][w] ^ m[w]);
+        }
         if (d < bestd[j]) {
 #pragma unroll
           for (int w = PREFIX; w < kDescWords; ++w) d += __popc(q[j][w] ^ m[w]);
@@ -126,7 +149,7 @@ static int pick_rows_per_chunk(int nq, long long nm) {
   return (int)rows;
 }
 
-int g_match_prefix = 6;  // tunable for experiments (okc_debug_set_match_prefix)
+int g_match_prefix = 5;  // 5 = carry-save prefix (default); 4/6/8/12 = plain prefixes kept for experiments
 
 int launch_hamming_best(const void* queries, int nq, const void* map, long long nm, unsigned threshold,
                         unsigned long long indexOffset, unsigned long long* best, cudaStream_t s) {
@@ -139,10 +162,10 @@ int launch_hamming_best(const void* queries, int nq, const void* map, long long 
   const uint4* m4 = static_cast<const uint4*>(map);
   switch (g_match_prefix) {
     case 4: hamming_best_kernel<4><<<grid, kMbThreads, 0, s>>>(q4, nq, m4, nm, rowsPerChunk, threshold, indexOffset, best); break;
-    case 5: hamming_best_kernel<5><<<grid, kMbThreads, 0, s>>>(q4, nq, m4, nm, rowsPerChunk, threshold, indexOffset, best); break;
+    case 6: hamming_best_kernel<6><<<grid, kMbThreads, 0, s>>>(q4, nq, m4, nm, rowsPerChunk, threshold, indexOffset, best); break;
     case 8: hamming_best_kernel<8><<<grid, kMbThreads, 0, s>>>(q4, nq, m4, nm, rowsPerChunk, threshold, indexOffset, best); break;
     case 12: hamming_best_kernel<12><<<grid, kMbThreads, 0, s>>>(q4, nq, m4, nm, rowsPerChunk, threshold, indexOffset, best); break;
-    default: hamming_best_kernel<6><<<grid, kMbThreads, 0, s>>>(q4, nq, m4, nm, rowsPerChunk, threshold, indexOffset, best); break;
+    default: hamming_best_kernel<5><<<grid, kMbThreads, 0, s>>>(q4, nq, m4, nm, rowsPerChunk, threshold, indexOffset, best); break;
   }
   return (int)(grid.x * grid.y);
 }

@@ -59,11 +59,11 @@ def test_match_batched_early_out_variants_agree(mod, ctx, syn):
     q, m = syn.sweep_inputs(1100, 30000, seed=9)
     base = ctx.match_batched(q, m, 60)
     try:
-        for pre in (4, 5, 8, 12):
+        for pre in (4, 6, 8, 12):
             mod.lib().okc_debug_set_match_prefix(pre)
             assert np.array_equal(ctx.match_batched(q, m, 60), base), pre
     finally:
-        mod.lib().okc_debug_set_match_prefix(6)
+        mod.lib().okc_debug_set_match_prefix(5)
 
 
 def test_match_sets_sharded_min_equals_full(mod, ctx, port, syn):
