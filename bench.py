@@ -270,6 +270,9 @@ def run_b200(args, rank, world):
         raise SystemExit("bench.py: no CUDA device (okvis_cuda has no CPU fallback)")
     torch.cuda.set_device(local)
     if world > 1:
+        # keep stdout to the one JSON line: NCCL prints its version banner there when NCCL_DEBUG=VERSION
+        if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     mod = g.load()
     mod.lib()
