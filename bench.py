@@ -368,8 +368,10 @@ def run_b200(args, rank, world):
     start.record(cur)
     for s in all_streams:
         s.wait_event(start)
+    t_host = time.perf_counter()
     for j, (hs, n, imgs, proj) in enumerate(work):
         enqueue(hs[j % D], n, imgs, proj, True)
+    t_host = time.perf_counter() - t_host
     for s in all_streams:
         e = torch.cuda.Event()
         e.record(s)
@@ -451,6 +453,7 @@ def run_b200(args, rank, world):
                                "vs 2000-landmark window",
                    "frames_in_pool": N_FRAMES, "keypoints_per_image": K, "map_rows_per_camera": M,
                    "frames_per_batch": F, "batches_in_flight": D,
+                   "host_enqueue_us_per_batch": round(t_host / max(len(work), 1) * 1e6, 1),
                    "l2": "inputs larger than L2 (144 MB image pool cycled)", "sharding": "frames round-robin over ranks"},
         "e2e": {"value": round(world * args.steps / (e2e_ms * 1e-3), 2), "unit": "frames/s",
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": round(e2e_ms / args.steps, 5)},
