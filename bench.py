@@ -293,41 +293,42 @@ def run_b200(args, rank, world):
     d_img = [torch.from_numpy(wl["images"][c]).cuda() for c in range(2)]
     d_proj = [torch.from_numpy(win_h[c][2]).cuda() for c in range(2)]
     h_img = [torch.from_numpy(wl["images"][c]).pin_memory() for c in range(2)]
+    h_proj = [torch.from_numpy(win_h[c][2]).pin_memory() for c in range(2)]
     img_stride = W * H
     proj_strides = [win_h[c][2].shape[1] * 16 for c in range(2)]
     sh = importlib.import_module("okvis2x_b200.sharding")
     frame_of = lambda k: sh.frame_of(k, rank, world, N_FRAMES)
 
     def make_batches(nframes):
-        return [mod.Batch(ctx, [cams[i % 2] for i in range(2 * nframes)]) for _ in range(D)]
+        return [mod.Batch(ctx, [cams[s // nframes] for s in range(2 * nframes)]) for _ in range(D)]
 
     batches = make_batches(F)
     rem = args.steps % F
     rem_batches = make_batches(rem) if rem else None
-    dirs_cache = {}
-
+    # slot order inside a batch: camera-major (slot c * nframes + i = frame i, camera c), so that consecutive frames of
+    # one camera are adjacent in the pinned host pool and travel in one copy
     def slot_args(k0, nframes, device):
-        """Per-slot argument lists of the batch that covers steps k0 .. k0+nframes-1 (slot 2i+c = frame i, camera c)."""
-        imgs, proj = [], []
-        for i in range(nframes):
-            f = frame_of(k0 + i)
-            for c in range(2):
-                if device:
-                    imgs.append(d_img[c].data_ptr() + f * img_stride)
-                    proj.append(d_proj[c].data_ptr() + f * proj_strides[c])
-                else:
-                    imgs.append(h_img[c].data_ptr() + f * img_stride)
-                    proj.append(win_h[c][2][f])
+        """Address arrays (np.uint64) of the batch that covers steps k0 .. k0+nframes-1."""
+        imgs = np.empty(2 * nframes, np.uint64)
+        proj = np.empty(2 * nframes, np.uint64)
+        for c in range(2):
+            ib = (d_img[c] if device else h_img[c]).data_ptr()
+            pb = (d_proj[c] if device else h_proj[c]).data_ptr()
+            for i in range(nframes):
+                f = frame_of(k0 + i)
+                imgs[c * nframes + i] = ib + f * img_stride
+                proj[c * nframes + i] = pb + f * proj_strides[c]
         return imgs, proj
 
+    configured = set()
+
     def enqueue(batch, nframes, imgs, proj, device):
-        key = nframes
-        if key not in dirs_cache:
-            dirs_cache[key] = ([DIRECTION] * (2 * nframes), [windows[i % 2] for i in range(2 * nframes)],
-                               [gates[i % 2] for i in range(2 * nframes)])
-        dirs, wins, gts = dirs_cache[key]
-        batch.enqueue(imgs, *det, dirs, images_on_device=device, windows=wins, proj=proj, gates=gts,
-                      hamming_threshold=60.0, proj_on_device=device, num_slices=slices)
+        if id(batch) not in configured:
+            batch.configure(*det, [DIRECTION] * (2 * nframes), windows=[windows[s // nframes] for s in range(2 * nframes)],
+                            gates=[gates[s // nframes] for s in range(2 * nframes)], hamming_threshold=60.0,
+                            num_slices=slices)
+            configured.add(id(batch))
+        batch.enqueue_addrs(imgs, device, proj, device)
 
     def plan(k_begin, k_end, device):
         """[(batch handle list, nframes, imgs, proj)] covering steps [k_begin, k_end)."""
@@ -531,9 +532,8 @@ def run_cpu_baseline(st, budget_s=12.0):
     def keep(k0, nframes, r):
         for i in range(nframes):
             for c in range(2):
-                s = 2 * i + c
+                s = c * nframes + i
                 n = int(r["n"][s])
-                sl = r["ctrs"].reshape(-1).shape[0] // r["ctrs"].shape[0]
                 gpu[(k0 + i, c)] = (r["kp"][s, :n].copy(), r["desc"][s, :n].copy(), r["dist"][s, :n].copy(),
                                     r["owner"][s, :n].copy())
     st["run_e2e"](0, n_check, keep)

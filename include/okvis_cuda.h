@@ -198,7 +198,8 @@ int okc_map_window_destroy(okc_map_window* win);
 
 /* Frontend::matchToMapByThread (Frontend.cpp:1744-1827) of the frame last enqueued on `cam` against `win`, on the
  * camera's stream. proj_xy: double[2*num_landmarks] landmark projections for this frame's pose, in host memory
- * (proj_on_device == 0; copied) or already in device memory (proj_on_device != 0). num_slices =
+ * (proj_on_device == 0; copied) or already in device memory (proj_on_device != 0; used in place until the finish).
+ * num_slices =
  * num_matching_threads (<= 64): ctrs[] / repr_errors[] are accumulated per thread slice, in the reference's order, by a
  * kernel (match_stats) - the improvement events never leave the device. */
 int okc_camera_match_to_map_enqueue(okc_camera* cam, const okc_map_window* win, const double* proj_xy,
@@ -221,7 +222,9 @@ int okc_batch_size(const okc_batch* batch);
 /* images[i]: u8[H*W]; host memory (pinned buffers are DMA'd in place, pageable ones are staged) or, with
  * images_on_device != 0, device memory. xp: n_slots describe parameter blocks (extraction direction per slot).
  * windows == NULL: no map match; else windows[i] (may be NULL per slot), proj_xy[i] = double[2*num_landmarks] in
- * host memory (or device memory with proj_on_device != 0), thresh_sq[i] = squared pixel gate of slot i. */
+ * host memory (copied) or, with proj_on_device != 0, device memory that is used in place and must stay valid and
+ * unchanged until okc_batch_finish. thresh_sq[i] = squared pixel gate of slot i. Host images that are adjacent in
+ * pinned memory (a ring of frames) are uploaded with one copy. */
 int okc_batch_enqueue(okc_batch* batch, const uint8_t* const* images, int images_on_device,
                       const okc_detect_params* dp, const okc_describe_params* xp,
                       const okc_map_window* const* windows, const double* const* proj_xy, int proj_on_device,

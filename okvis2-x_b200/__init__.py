@@ -510,6 +510,30 @@ class Batch:
         self._matching = windows is not None
         self._keep = keep  # host buffers stay alive until finish()
 
+    # -- low-overhead form for pipelines: per-slot settings once, then only address arrays per enqueue --
+    def configure(self, radius, octaves, abs_threshold, max_kpt, directions, rotation_invariant=True, windows=None,
+                  gates=None, hamming_threshold=60.0, num_slices=4):
+        self._dp = DetectParams(float(radius), int(octaves), float(abs_threshold), int(max_kpt))
+        for k in range(self.n):
+            self._xp[k].rotation_invariant = int(rotation_invariant)
+            self._xp[k].scale_invariant = 0
+            self._xp[k].extraction_direction[:] = [float(v) for v in directions[k]]
+            if windows is not None:
+                self._win[k] = windows[k].h if windows[k] is not None else None
+                self._gate[k] = float(gates[k])
+        self._matching = windows is not None
+        self._slices = int(num_slices) if windows is not None else 1
+        self._thr = float(hamming_threshold)
+
+    def enqueue_addrs(self, image_addrs, images_on_device, proj_addrs=None, proj_on_device=False):
+        """image_addrs / proj_addrs: contiguous np.uint64 arrays of n host or device addresses (u8[H*W] images,
+        double[2*L] projections). The arrays themselves are only read during the call."""
+        m = self._matching
+        _check(lib().okc_batch_enqueue(self.h, C.c_void_p(image_addrs.ctypes.data), int(images_on_device),
+                                       C.byref(self._dp), self._xp, self._win if m else None,
+                                       C.c_void_p(proj_addrs.ctypes.data) if m else None, int(proj_on_device),
+                                       self._gate if m else None, self._thr, self._slices), "okc_batch_enqueue")
+
     def finish(self):
         _check(lib().okc_batch_finish(self.h), "okc_batch_finish")
         self._keep = None
