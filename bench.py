@@ -252,6 +252,21 @@ def pad256(n):
     return (n + 255) & ~255
 
 
+def ncu_traffic(kernel, images_per_launch):
+    """DRAM bytes per launch of `kernel` from the newest committed ncu capture (profiles/*/traffic.json), or None when
+    there is none for this batch size. Never measured under this run: it is the committed profile's number."""
+    import glob
+    key = {"border_filter+describe": "describe_kernel", "match_to_map": "match_to_map_slots"}.get(kernel, kernel)
+    for path in sorted(glob.glob(os.path.join(ROOT, "profiles", "*", "traffic.json")), reverse=True):
+        try:
+            d = json.load(open(path))
+            if d.get("images_per_launch") == images_per_launch and key in d.get("kernels", {}):
+                return d["kernels"][key]["dram_bytes_per_launch"]
+        except (OSError, ValueError, KeyError):
+            continue
+    return None
+
+
 def stage_bytes(kernel, W, H, K, M):
     """ALGORITHMIC bytes of the stage a kernel belongs to, per image (DESIGN.md 'Roofline')."""
     if kernel in ("harris_nms", "order_candidates", "select_keypoints"):
@@ -440,7 +455,7 @@ def run_b200(args, rank, world):
     alg = stage_bytes(dom, W, H, K, M) * 2 * F
     achieved = alg / (kernel_ms[dom] * 1e-3) / 1e9
     roofline = {"bound": "hbm", "kernel": dom, "achieved": round(achieved, 3), "peak": peak, "unit": "GB/s",
-                "frac": round(achieved / peak, 6), "traffic": None, "peak_source": peak_src,
+                "frac": round(achieved / peak, 6), "traffic": ncu_traffic(dom, 2 * F), "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": alg, "images_per_launch": 2 * F,
                 "kernel_ms": {n: round(v, 5) for n, v in kernel_ms.items()},
                 "note": "per-launch times of one batch running alone; in the timed loop %d batches overlap" % D}
