@@ -57,7 +57,8 @@ int okc_camera_destroy(okc_camera* cam);
 
 typedef struct okc_detect_params {
   double uniformity_radius;   /* FrontendParameters::detection_threshold -> ctor arg 1 (Frontend.cpp:2645-2648) */
-  uint64_t octaves;           /* only 0 is implemented (every shipped config); >0 returns OKC_ERR_INVALID */
+  uint64_t octaves;           /* 0 in every shipped config; > 0 (scale space, 2*octaves layers, <= 8) is available
+                                 through the single-camera entry points, not through okc_batch_* */
   double absolute_threshold;
   uint64_t max_num_keypoints;
 } okc_detect_params;

@@ -105,6 +105,9 @@ int okc_context_create(int device, okc_context** out) {
   OKC_CUDA_TRY(cudaMalloc(&c->tables.short_pairs, t.short_pairs.size()));
   OKC_CUDA_TRY(cudaMalloc(&c->tables.long_pairs, t.long_pairs.size() * sizeof(HostLongPair)));
   OKC_CUDA_TRY(cudaMalloc(&c->tables.lut, t.lut.size() * sizeof(float)));
+  OKC_CUDA_TRY(cudaMalloc(&c->tables.lut_upper, t.lut_upper.size() * sizeof(float)));
+  OKC_CUDA_TRY(cudaMemcpy(c->tables.lut_upper, t.lut_upper.data(), t.lut_upper.size() * sizeof(float),
+                          cudaMemcpyHostToDevice));
   OKC_CUDA_TRY(cudaMemcpy(c->tables.points, t.points.data(), t.points.size() * sizeof(HostPatternPoint),
                           cudaMemcpyHostToDevice));
   OKC_CUDA_TRY(cudaMemcpy(c->tables.short_pairs, t.short_pairs.data(), t.short_pairs.size(), cudaMemcpyHostToDevice));
@@ -125,6 +128,7 @@ int okc_context_destroy(okc_context* c) {
   cudaFree(c->tables.short_pairs);
   cudaFree(c->tables.long_pairs);
   cudaFree(c->tables.lut);
+  cudaFree(c->tables.lut_upper);
   for (auto& b : c->d) b.release();
   for (auto& b : c->h) b.release();
   cudaStreamDestroy(c->stream);

@@ -34,6 +34,7 @@ struct PatternTables {
   uchar2* short_pairs;     // [384] (i, j)
   LongPair* long_pairs;    // [856]
   float* lut;              // [31*31] uniformity LUT, layer 0
+  float* lut_upper;        // [31*31] uniformity LUT, layers >= 1 (octaves > 0)
   int border;              // sizeList_[basicscale]
   int basicscale;
 };
@@ -85,6 +86,9 @@ struct DetectArgs {
   float scaling;           // (float)(15.0 / (float)radius)
   unsigned long long max_kpt;
   int max_out;             // capacity of kp_detect
+  // keypoint coordinates of the layer: x = kp_scale * ((x + dx) + kp_offset) (scale-space-layer-inl.h:412-419)
+  double kp_scale = 1.0, kp_offset = 0.0;
+  int octave = 0;          // _layerNumber / 2
 };
 
 struct DescribeArgs {
@@ -105,6 +109,13 @@ void launch_describe(const Slot* slots, int n, const PatternTables& t, const Des
                      cudaStream_t s);
 void launch_match_to_map_slots(const Slot* slots, int n, int max_kp, double hammingThreshold, cudaStream_t s);
 void launch_match_stats(const Slot* slots, int n, cudaStream_t s);
+// scale space (octaves > 0)
+void launch_halfsample8(const uint8_t* src, int sw, int sh, uint8_t* dst, cudaStream_t s);
+void launch_twothirdsample8(const uint8_t* src, int sw, int sh, uint8_t* dst, cudaStream_t s);
+void launch_scale_nms(const int32_t* scores, uint32_t* bitmap, int W, int H, const int32_t* aboveScores, int aW,
+                      int aH, double aScale, double aOffset, int aStep, const int32_t* belowScores, int bW, int bH,
+                      double bScale, double bOffset, int bStep, cudaStream_t s);
+void launch_concat_layers(const Slot* layers, int nLayers, const Slot& out, int maxOut, cudaStream_t s);
 
 void set_error(const char* fmt, ...);
 

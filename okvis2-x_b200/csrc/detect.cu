@@ -622,7 +622,8 @@ __device__ void subpixel2d(double s_0_0, double s_0_1, double s_0_2, double s_1_
 
 __global__ void __launch_bounds__(kSelThreads, 1)
 select_keypoints_kernel(const Slot* __restrict__ slots, const float* __restrict__ lut_global, int W, int H,
-                        float scaling, unsigned long long maxKpt, int maxOut, int smemBytes) {
+                        float scaling, unsigned long long maxKpt, int maxOut, int smemBytes, double kpScale,
+                        double kpOffset, int octave) {
   const Slot& slot = slots[blockIdx.x];
   const int32_t* __restrict__ scores = slot.scores;
   uint64_t* __restrict__ cand = slot.cand;
@@ -745,13 +746,13 @@ select_keypoints_kernel(const Slot* __restrict__ slots, const float* __restrict_
     subpixel2d((double)c[-W - 1], (double)c[-W], (double)c[-W + 1], (double)c[-1], (double)c[0], (double)c[1],
                (double)c[W - 1], (double)c[W], (double)c[W + 1], dx, dy);
     okc_keypoint kp;
-    // _scale * ((it->x + delta_x) + _offset): (float)(1.0 * ((double)((float)x + dx) + 0.0))
-    kp.x = (float)(1.0 * ((double)((float)u + dx) + 0.0));
-    kp.y = (float)(1.0 * ((double)((float)v + dy) + 0.0));
-    kp.size = 12.0f;
+    // _scale * ((it->x + delta_x) + _offset): (float + float) widened, the rest in double, narrowed on assignment
+    kp.x = (float)(kpScale * ((double)((float)u + dx) + kpOffset));
+    kp.y = (float)(kpScale * ((double)((float)v + dy) + kpOffset));
+    kp.size = (float)(kpScale * 12.0);
     kp.angle = -1.0f;
     kp.response = (float)score;
-    kp.octave = 0;
+    kp.octave = octave;
     kp.class_id = -1;
     out[i] = kp;
   }
@@ -776,7 +777,174 @@ void launch_select_keypoints(const Slot* slots, int n, const float* lut, const D
   size_t want = occRows * occStride;
   int smem = want <= (size_t)g_select_smem ? (int)((want + 15) & ~(size_t)15) : 0;
   select_keypoints_kernel<<<n, kSelThreads, smem, s>>>(slots, lut, a.width, a.height, a.scaling, a.max_kpt, a.max_out,
-                                                       smem);
+                                                       smem, a.kp_scale, a.kp_offset, a.octave);
+}
+
+// ----------------------------------------------------------------------------------------------
+// Scale space (octaves > 0) - cold in every shipped config, so built for exactness
+// and reuse of the single-layer kernels rather than for speed: one launch chain per layer.
+// ----------------------------------------------------------------------------------------------
+// brisk::Halfsample8 (brisk/src/image-down-sampling.cc:161-415, SSE path): three rounding rules by column region.
+//   body     (dst col < 16*(cols/16/2)): avg(avg_v(2c), avg_v(2c+1)), avg(a,b) = (a+b+1)>>1, avg_v = vertical avg
+//   half end (cols/16 odd, next 8 dst cols): (avg_v(2c) + avg_v(2c+1)) / 2   (truncating)
+//   leftover ((cols%16)/2 dst cols): (a + b + c + d + 2) / 4
+__global__ void halfsample8_kernel(const uint8_t* __restrict__ src, int sw, int sh, uint8_t* __restrict__ dst) {
+  const int dw = sw / 2, dh = sh / 2;
+  const int c = blockIdx.x * blockDim.x + threadIdx.x, r = blockIdx.y;
+  if (c >= dw || r >= dh) return;
+  const int hsize = sw / 16, bodyCols = 16 * (hsize / 2), halfCols = (hsize & 1) ? 8 : 0;
+  const uint8_t* p1 = src + (size_t)(2 * r) * sw + 2 * c;
+  const uint8_t* p2 = p1 + sw;
+  const int a = p1[0], b = p1[1], cc = p2[0], d = p2[1];
+  int v;
+  if (c < bodyCols) {
+    const int v0 = (a + cc + 1) >> 1, v1 = (b + d + 1) >> 1;
+    v = (v0 + v1 + 1) >> 1;
+  } else if (c < bodyCols + halfCols) {
+    const int v0 = (a + cc + 1) >> 1, v1 = (b + d + 1) >> 1;
+    v = (v0 + v1) / 2;
+  } else {
+    v = (a + b + cc + d + 2) / 4;
+  }
+  dst[(size_t)r * dw + c] = (uint8_t)v;
+}
+
+// brisk::Twothirdsample8 (:573-814, SSE path). Per 3x3 source block -> 2x2 destination block.
+//   body (src col block < cols/15): vertical u = avg(avg(first, second), first) (lower: third), horizontal
+//        out[2t] = avg(avg(u[3t], u[3t+1]), u[3t]), out[2t+1] = avg(avg(u[3t+2], u[3t+1]), u[3t+2])
+//   remainder: (4*A1 + 2*(A2 + B1 + 1) + B2 + 1) / 9 and its mirrored forms
+__global__ void twothirdsample8_kernel(const uint8_t* __restrict__ src, int sw, int sh, uint8_t* __restrict__ dst) {
+  const int dw = (sw / 3) * 2, dh = (sh / 3) * 2;
+  const int t = blockIdx.x * blockDim.x + threadIdx.x, rb = blockIdx.y;  // 3x3 block column / row
+  if (t >= sw / 3 || rb >= sh / 3) return;
+  const uint8_t* p = src + (size_t)(3 * rb) * sw + 3 * t;
+  const int A1 = p[0], A2 = p[1], A3 = p[2], B1 = p[sw], B2 = p[sw + 1], B3 = p[sw + 2];
+  const int C1 = p[2 * sw], C2 = p[2 * sw + 1], C3 = p[2 * sw + 2];
+  int o00, o01, o10, o11;
+  if (3 * t < 15 * (sw / 15)) {
+    auto avg = [](int x, int y) { return (x + y + 1) >> 1; };
+    const int u0 = avg(avg(A1, B1), A1), u1 = avg(avg(A2, B2), A2), u2 = avg(avg(A3, B3), A3);
+    const int l0 = avg(avg(C1, B1), C1), l1 = avg(avg(C2, B2), C2), l2 = avg(avg(C3, B3), C3);
+    o00 = avg(avg(u0, u1), u0);
+    o01 = avg(avg(u2, u1), u2);
+    o10 = avg(avg(l0, l1), l0);
+    o11 = avg(avg(l2, l1), l2);
+  } else {
+    o00 = ((4 * A1 + 2 * (A2 + B1 + 1) + B2 + 1) / 9) & 0xff;
+    o01 = ((4 * A3 + 2 * (A2 + B3 + 1) + B2 + 1) / 9) & 0xff;
+    o10 = ((4 * C1 + 2 * (C2 + B1 + 1) + B2 + 1) / 9) & 0xff;
+    o11 = ((4 * C3 + 2 * (C2 + B3 + 1) + B2 + 1) / 9) & 0xff;
+  }
+  uint8_t* q = dst + (size_t)(2 * rb) * dw + 2 * t;
+  q[0] = (uint8_t)o00;
+  q[1] = (uint8_t)o01;
+  q[dw] = (uint8_t)o10;
+  q[dw + 1] = (uint8_t)o11;
+}
+
+void launch_halfsample8(const uint8_t* src, int sw, int sh, uint8_t* dst, cudaStream_t s) {
+  if (sw / 2 <= 0 || sh / 2 <= 0) return;
+  dim3 grid((sw / 2 + 127) / 128, sh / 2);
+  halfsample8_kernel<<<grid, 128, 0, s>>>(src, sw, sh, dst);
+}
+void launch_twothirdsample8(const uint8_t* src, int sw, int sh, uint8_t* dst, cudaStream_t s) {
+  if (sw / 3 <= 0 || sh / 3 <= 0) return;
+  dim3 grid((sw / 3 + 127) / 128, sh / 3);
+  twothirdsample8_kernel<<<grid, 128, 0, s>>>(src, sw, sh, dst);
+}
+
+// HarrisScoreCalculator::Score(double u, double v) (brisk/include/brisk/harris-score-calculator.h:69-87)
+__device__ __forceinline__ double score_bilinear(const int32_t* __restrict__ sc, int W, int H, double u, double v) {
+  const int ui = (int)u, vi = (int)v;
+  if (ui + 1 >= W || vi + 1 >= H || ui < 0 || vi < 0) return 0.0;
+  const double ru = u - (double)ui, rv = v - (double)vi;
+  const double omu = 1.0 - ru, omv = 1.0 - rv;
+  const int32_t* p = sc + (size_t)vi * W + ui;
+  return omv * (omu * (double)p[0] + ru * (double)p[1]) + rv * (omu * (double)p[W] + ru * (double)p[W + 1]);
+}
+
+// 3-D non-maximum suppression of ScaleSpaceLayer::DetectScaleSpaceMaxima (scale-space-layer-inl.h:230-378): a 2-D
+// maximum survives only if it is not smaller than 9 bilinear samples of the layer above and/or below.
+// one_over_scale_* is the reference's int truncation of 1.0 / scale (1 above, 0 below - the nine "below" probes
+// coincide). Candidates live in the NMS bitmap; failing bits are cleared in place, raster order is untouched.
+struct LayerLink {
+  const int32_t* scores;
+  int W, H;
+  double scale, offset;
+  int step;
+};
+__global__ void scale_nms_kernel(const int32_t* __restrict__ scores, uint32_t* __restrict__ bitmap, int W, int H,
+                                 LayerLink above, LayerLink below) {
+  const int wordsPerRow = harris_strips(W) * kStripWords;
+  const int w = blockIdx.x * blockDim.x + threadIdx.x;
+  if (w >= H * wordsPerRow) return;
+  unsigned bits = bitmap[w];
+  if (!bits) return;
+  const int y = w / wordsPerRow, rem = w - y * wordsPerRow;
+  const int xb = (rem / kStripWords) * kStripCols - 4 + ((rem % kStripWords) << 5);
+  unsigned keep = bits;
+  while (bits) {
+    const int b = __ffs(bits) - 1;
+    bits &= bits - 1;
+    const int x = xb + b;
+    const double center = (double)scores[(size_t)y * W + x];
+    bool ok = true;
+    const int dxs[9] = {0, 1, -1, 0, 0, 1, 1, -1, -1}, dys[9] = {0, 0, 0, 1, -1, 1, -1, 1, -1};
+    if (above.scores) {
+      for (int i = 0; i < 9 && ok; ++i) {
+        const double u = (double)(x + dxs[i] * above.step), v = (double)(y + dys[i] * above.step);
+        if (center < score_bilinear(above.scores, above.W, above.H, above.scale * (u + above.offset),
+                                    above.scale * (v + above.offset)))
+          ok = false;
+      }
+    }
+    if (ok && below.scores) {
+      for (int i = 0; i < 9 && ok; ++i) {
+        const double u = (double)(x + dxs[i] * below.step), v = (double)(y + dys[i] * below.step);
+        if (center < score_bilinear(below.scores, below.W, below.H, below.scale * (u + below.offset),
+                                    below.scale * (v + below.offset)))
+          ok = false;
+      }
+    }
+    if (!ok) keep &= ~(1u << b);
+  }
+  bitmap[w] = keep;
+}
+
+void launch_scale_nms(const int32_t* scores, uint32_t* bitmap, int W, int H, const int32_t* aboveScores, int aW,
+                      int aH, double aScale, double aOffset, int aStep, const int32_t* belowScores, int bW, int bH,
+                      double bScale, double bOffset, int bStep, cudaStream_t s) {
+  LayerLink a{aboveScores, aW, aH, aScale, aOffset, aStep}, b{belowScores, bW, bH, bScale, bOffset, bStep};
+  const int words = (int)harris_bitmap_words(W, H);
+  scale_nms_kernel<<<(words + 127) / 128, 128, 0, s>>>(scores, bitmap, W, H, a, b);
+}
+
+// Appends the per-layer keypoints in layer order (detectImpl's loop, scale-space-feature-detector.h:157-162).
+__global__ void concat_layers_kernel(const Slot* __restrict__ layers, int nLayers, Slot out, int maxOut) {
+  __shared__ int s_off[33];
+  if (threadIdx.x == 0) {
+    int off = 0, flag = 0;
+    for (int l = 0; l < nLayers; ++l) {
+      s_off[l] = off;
+      off += layers[l].counters[1];
+      if (layers[l].counters[3]) flag = layers[l].counters[3];
+    }
+    s_off[nLayers] = off;
+    if (off > maxOut) flag = 2;
+    out.counters[0] = layers[0].counters[0];
+    out.counters[1] = off < maxOut ? off : maxOut;
+    if (flag) out.counters[3] = flag;
+  }
+  __syncthreads();
+  for (int l = 0; l < nLayers; ++l) {
+    const int n = s_off[l + 1] - s_off[l];
+    for (int i = threadIdx.x; i < n; i += blockDim.x)
+      if (s_off[l] + i < maxOut) out.kp_detect[s_off[l] + i] = layers[l].kp_detect[i];
+  }
+}
+
+void launch_concat_layers(const Slot* layers, int nLayers, const Slot& out, int maxOut, cudaStream_t s) {
+  concat_layers_kernel<<<1, 256, 0, s>>>(layers, nLayers, out, maxOut);
 }
 
 }  // namespace okc

@@ -82,6 +82,12 @@ void build_host_tables(HostTables* t) {
           1 - sqrt(sqrt(sqrt(static_cast<double>((15 - x) * (15 - x) + (15 - y) * (15 - y))))) /
                   sqrt(sqrt(sqrt(static_cast<double>(15 * 15)))),
           0.0);
+  // upper layers (scale-space-layer-inl.h:185-193): max(1 - d^2 / 15^2, 0)
+  t->lut_upper.resize(31 * 31);
+  for (int x = 0; x < 31; ++x)
+    for (int y = 0; y < 31; ++y)
+      t->lut_upper[y * 31 + x] = static_cast<float>(std::max(
+          1 - static_cast<double>((15 - x) * (15 - x) + (15 - y) * (15 - y)) / static_cast<double>(15 * 15), 0.0));
 }
 
 }  // namespace okc

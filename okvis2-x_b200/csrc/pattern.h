@@ -14,7 +14,8 @@ struct HostTables {
   std::vector<HostPatternPoint> points;    // [1024][66]
   std::vector<unsigned char> short_pairs;  // [384][2] (i, j)
   std::vector<HostLongPair> long_pairs;    // [856]
-  std::vector<float> lut;                  // [31][31]
+  std::vector<float> lut;                  // [31][31] layer 0
+  std::vector<float> lut_upper;            // [31][31] layers >= 1
 };
 
 void build_host_tables(HostTables* t);

@@ -157,9 +157,9 @@ def test_edge_cases(mod, ctx, ref, syn):
     # capacity overflow is reported, not truncated silently
     with pytest.raises(mod.OkcError):
         cam.detect(img, 2.0, 0, 1.0, 100000)
-    # octaves > 0 is refused loudly (not implemented), never silently computed as octaves = 0
+    # more octaves than the image can carry is refused loudly
     with pytest.raises(mod.OkcError):
-        cam2.detect(img, 10.0, 1, 20.0, 700)
+        cam2.detect(img, 10.0, 6, 20.0, 700)
     cam.close()
     cam2.close()
 
@@ -212,4 +212,27 @@ def test_std_sort_reproduction(mod, ctx, ref):
     for sc in cases:
         got = cam.debug_std_sort(sc).astype(np.int64)
         assert np.array_equal(got, _ref_order(ref, sc)), "n=%d" % len(sc)
+    cam.close()
+
+
+@pytest.mark.parametrize("octaves", [1, 2, 3])
+@pytest.mark.parametrize("name", ["euroc-scene", "euroc-noise", "d455-scene", "odd-size"])
+def test_scale_space_detect(name, octaves, cases, mod, ctx, ref):
+    """Row a6: 2*octaves layers (two-third / half sampling with the reference's region-dependent rounding), per-layer
+    Harris + 2-D NMS, 3-D NMS against bilinear scores of the neighbouring layers, per-layer uniformity budgets."""
+    import refbind
+    cfg, img = cases[name]
+    H, W = img.shape
+    cam = mod.Camera(ctx, W, H, max_keypoints=4096)
+    kp = cam.detect(img, cfg["radius"], octaves, cfg["abs_threshold"], cfg["max_kpt"])
+    rkp = ref.detect(img, cfg["radius"], octaves, cfg["abs_threshold"], cfg["max_kpt"])
+    assert len(rkp) > 30 and len(np.unique(rkp["octave"])) >= min(octaves, 2)
+    kp_assert_close(kp, rkp, TOL)
+    # fused detect + describe on the base image (scale_invariant = false ignores the keypoint size)
+    kf, df = cam.detect_describe(img, cfg["radius"], octaves, cfg["abs_threshold"], cfg["max_kpt"])
+    ext = refbind.RefExtractor(ref)
+    rkd, rdd = ext.describe(img, rkp)
+    ext.close()
+    kp_assert_close(kf, rkd, TOL)
+    assert np.array_equal(df, rdd)
     cam.close()
