@@ -6,6 +6,7 @@
 //
 // No tensor cores: the work is XOR + POPC on 12 x u32 per pair. Descriptors are read as uint4 (3 per row).
 #include "common.cuh"
+#include <cstdlib>
 
 namespace okc {
 
@@ -138,10 +139,165 @@ hamming_best_kernel(const uint4* __restrict__ queries, int nq, const uint4* __re
   }
 }
 
-static int pick_rows_per_chunk(int nq, long long nm) {
-  // Aim at >= 4 waves of 148 SMs x 2 CTAs, chunks a multiple of the stage size, at least one stage.
+// ----------------------------------------------------------------------------------------------
+// A'. the default sweep kernel: 2-POPC lower bound over the first 6 words, exact distance only when it passes
+// ----------------------------------------------------------------------------------------------
+// The CSA-prefix kernel above keeps the ALU pipe (LOP3/ISETP, 77 % busy) and the XU pipe (POPC, 73 % busy) equally
+// loaded (profiles/r01_ncu_v3), so only fewer operations per pair help. Per bit position let n = number of differing
+// words among x0..x5 (x_i = q_i ^ m_i). With ones = parity(n), c1 = maj(x0,x1,x2), c2 = maj(x3,x4,x5),
+// c3 = (x0^x1^x2) & (x3^x4^x5):   n >= ones + 2*(c1|c2|c3), hence
+//     LB = popc(ones) + 2*popc(c1|c2|c3) <= popcount of the 6-word prefix <= full distance,
+// and "LB >= running best" rejects exactly (the reference's update is a strict '<', Frontend.cpp:334-339).
+// For unrelated descriptors LB ~ 73 +- 3.9 against a threshold of 60: 4e-4 of the pairs reach the exact path.
+// XORs of q with m are folded into the adders through per-side precomputed combinations
+// (maj(a,b,c) = ((a^b)&(a^c))^a with a^b = (q0^q1)^(m0^m1)): 10 LOP3 + 2 POPC per pair instead of 11 + 3.
+// The map-side combinations are built once per staged row in shared memory.
+constexpr int kLbWords = 12;  // 9 used: {m0, m0^m1, m0^m2, m0^m1^m2, m3, m3^m4, m3^m5, m3^m4^m5, m0^..^m5}, padded to 48 B
+
+__device__ __forceinline__ unsigned lop3_and_xor(unsigned a, unsigned b, unsigned c) {  // a & (b ^ c)
+  unsigned d;
+  asm("lop3.b32 %0, %1, %2, %3, 0x60;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+  return d;
+}
+__device__ __forceinline__ unsigned lop3_or3(unsigned a, unsigned b, unsigned c) {
+  unsigned d;
+  asm("lop3.b32 %0, %1, %2, %3, 0xFE;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+  return d;
+}
+__device__ __forceinline__ void lb_combine(const unsigned w[6], unsigned c[9]) {
+  c[0] = w[0];
+  c[1] = w[0] ^ w[1];
+  c[2] = w[0] ^ w[2];
+  c[3] = c[1] ^ w[2];
+  c[4] = w[3];
+  c[5] = w[3] ^ w[4];
+  c[6] = w[3] ^ w[5];
+  c[7] = c[5] ^ w[5];
+  c[8] = c[3] ^ c[7];
+}
+
+// z += LB << (8 * J) for one (query, map row) pair; q and (ma, mb, ms) hold the combinations of lb_combine.
+template <int J>
+__device__ __forceinline__ unsigned lb_accum(unsigned z, const unsigned (&q)[9], const uint4& ma, const uint4& mb, unsigned ms) {
+  const unsigned t1 = q[1] ^ ma.y;                                   // x0 ^ x1
+  const unsigned c1 = lop3_xor3(lop3_and_xor(t1, q[2], ma.z), q[0], ma.x);
+  const unsigned u1 = q[5] ^ mb.y;                                   // x3 ^ x4
+  const unsigned c2 = lop3_xor3(lop3_and_xor(u1, q[6], mb.z), q[4], mb.x);
+  const unsigned s1 = q[3] ^ ma.w;                                   // x0 ^ x1 ^ x2
+  const unsigned c3 = lop3_and_xor(s1, q[7], mb.w);
+  const unsigned hi = lop3_or3(c1, c2, c3);
+  const unsigned ones = q[8] ^ ms;
+  asm("mad.lo.u32 %0, %1, %2, %0;" : "+r"(z) : "r"((unsigned)__popc(hi)), "n"(2u << (8 * J)));
+  asm("mad.lo.u32 %0, %1, %2, %0;" : "+r"(z) : "r"((unsigned)__popc(ones)), "n"(1u << (8 * J)));
+  return z;
+}
+
+__global__ void __launch_bounds__(kMbThreads, 3)
+hamming_best_lb_kernel(const uint4* __restrict__ queries, int nq, const uint4* __restrict__ map, long long nm,
+                       int rowsPerChunk, unsigned threshold, unsigned long long indexOffset,
+                       unsigned long long* __restrict__ best) {
+  __shared__ uint4 stage[2][kMbRows * 3];          // raw rows (exact path)
+  __shared__ uint4 comb[kMbRows * (kLbWords / 4)]; // combinations of the first 6 words
+  const int tid = threadIdx.x;
+  const int qbase = blockIdx.y * kMbQTile;
+  const long long row0 = (long long)blockIdx.x * rowsPerChunk;
+  long long rowsLeft = nm - row0;
+  if (rowsLeft > rowsPerChunk) rowsLeft = rowsPerChunk;
+  if (rowsLeft <= 0) return;
+
+  unsigned qc[kMbQpt][9];
+  unsigned bestd[kMbQpt], besti[kMbQpt];
+#pragma unroll
+  for (int j = 0; j < kMbQpt; ++j) {
+    const int qi = qbase + j * kMbThreads + tid;
+    bestd[j] = qi < nq ? threshold : 0u;  // 0: nothing can be strictly smaller -> lane idles
+    besti[j] = 0xffffffffu;
+    const int qs = qi < nq ? qi : 0;
+    const uint4 v0 = __ldg(queries + (size_t)qs * 3), v1 = __ldg(queries + (size_t)qs * 3 + 1);
+    const unsigned w[6] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y};
+    lb_combine(w, qc[j]);
+  }
+  unsigned zbase = 0;
+#pragma unroll
+  for (int j = 0; j < kMbQpt; ++j) zbase |= (128u - (bestd[j] < 128u ? bestd[j] : 128u)) << (8 * j);
+
+  const int nStages = (int)((rowsLeft + kMbRows - 1) / kMbRows);
+  auto issue = [&](int s) {
+    const long long r = row0 + (long long)s * kMbRows;
+    long long cnt = rowsLeft - (long long)s * kMbRows;
+    if (cnt > kMbRows) cnt = kMbRows;
+    const uint4* src = map + r * 3;
+    uint4* dst = stage[s & 1];
+    for (int i = tid; i < (int)cnt * 3; i += kMbThreads) cp_async16(dst + i, src + i);
+    cp_async_commit();
+  };
+  issue(0);
+  for (int s = 0; s < nStages; ++s) {
+    cp_async_wait<0>();
+    __syncthreads();  // stage s landed; every thread is done with comb of stage s-1
+    long long cnt = rowsLeft - (long long)s * kMbRows;
+    if (cnt > kMbRows) cnt = kMbRows;
+    const uint4* rows = stage[s & 1];
+    if (tid < (int)cnt) {
+      const uint4 a = rows[tid * 3], b = rows[tid * 3 + 1];
+      const unsigned w[6] = {a.x, a.y, a.z, a.w, b.x, b.y};
+      unsigned c[9];
+      lb_combine(w, c);
+      comb[tid * 3 + 0] = make_uint4(c[0], c[1], c[2], c[3]);
+      comb[tid * 3 + 1] = make_uint4(c[4], c[5], c[6], c[7]);
+      comb[tid * 3 + 2] = make_uint4(c[8], 0u, 0u, 0u);
+    }
+    if (s + 1 < nStages) issue(s + 1);  // stage[(s+1)&1] was last read in iteration s-1, before the barrier above
+    __syncthreads();
+    const unsigned rowIdx0 = (unsigned)(s * kMbRows);
+#pragma unroll 2
+    for (int r = 0; r < (int)cnt; ++r) {
+      const uint4 ma = comb[r * 3 + 0], mb = comb[r * 3 + 1];
+      const unsigned ms = reinterpret_cast<const unsigned*>(comb + r * 3 + 2)[0];
+      // byte j of z = 128 + LB_j - min(best_j, 128): bit 7 clear <=> LB_j < best_j (LB <= 96, so no carries between
+      // bytes). The sums run on the FMA pipe (IMAD), leaving the ALU pipe to the LOP3s; one LOP3 tests all four pairs.
+      unsigned z = zbase;
+      z = lb_accum<0>(z, qc[0], ma, mb, ms);
+      z = lb_accum<1>(z, qc[1], ma, mb, ms);
+      z = lb_accum<2>(z, qc[2], ma, mb, ms);
+      z = lb_accum<3>(z, qc[3], ma, mb, ms);
+      if ((~z & 0x80808080u) != 0u) {
+        const uint4 m0 = rows[r * 3 + 0], m1 = rows[r * 3 + 1], m2 = rows[r * 3 + 2];
+#pragma unroll
+        for (int j = 0; j < kMbQpt; ++j) {
+          if (((z >> (8 * j + 7)) & 1u) == 0u) {
+            const uint4* qp = queries + (size_t)(qbase + j * kMbThreads + tid) * 3;  // bestd > 0 implies qi < nq
+            const uint4 q0 = __ldg(qp), q1 = __ldg(qp + 1), q2 = __ldg(qp + 2);
+            const unsigned d = __popc(q0.x ^ m0.x) + __popc(q0.y ^ m0.y) + __popc(q0.z ^ m0.z) + __popc(q0.w ^ m0.w) +
+                               __popc(q1.x ^ m1.x) + __popc(q1.y ^ m1.y) + __popc(q1.z ^ m1.z) + __popc(q1.w ^ m1.w) +
+                               __popc(q2.x ^ m2.x) + __popc(q2.y ^ m2.y) + __popc(q2.z ^ m2.z) + __popc(q2.w ^ m2.w);
+            if (d < bestd[j]) {
+              bestd[j] = d;
+              besti[j] = rowIdx0 + r;
+              zbase = (zbase & ~(0xffu << (8 * j))) | ((128u - (d < 128u ? d : 128u)) << (8 * j));
+            }
+          }
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < kMbQpt; ++j) {
+    const int qi = qbase + j * kMbThreads + tid;
+    if (qi < nq && besti[j] != 0xffffffffu) {
+      const unsigned long long key =
+          ((unsigned long long)bestd[j] << 32) | ((unsigned long long)(row0 + besti[j]) + indexOffset);
+      atomicMin(best + qi, key);
+    }
+  }
+}
+
+static int pick_rows_per_chunk(int nq, long long nm, int ctasPerSm) {
+  // Aim at 16 waves of 148 SMs x resident CTAs (measured: 2 waves 1189, 4 -> 1270, 16 -> 1350 Gpairs/s on the
+  // 10k x 1M sweep: the tail of the last wave is what small grids lose), chunks a multiple of the stage size.
   const long long qTiles = (nq + kMbQTile - 1) / kMbQTile;
-  long long wantChunks = (148LL * 2 * 4 + qTiles - 1) / qTiles;
+  static const int waves = getenv("OKC_SWEEP_WAVES") ? atoi(getenv("OKC_SWEEP_WAVES")) : 16;
+  long long wantChunks = (148LL * ctasPerSm * waves + qTiles - 1) / qTiles;
   long long rows = (nm + wantChunks - 1) / wantChunks;
   rows = ((rows + kMbRows - 1) / kMbRows) * kMbRows;
   if (rows < kMbRows) rows = kMbRows;
@@ -149,23 +305,24 @@ static int pick_rows_per_chunk(int nq, long long nm) {
   return (int)rows;
 }
 
-int g_match_prefix = 5;  // 5 = carry-save prefix (default); 4/6/8/12 = plain prefixes kept for experiments
+int g_match_prefix = 0;  // 0 = 2-POPC lower bound (default); 5 = carry-save prefix; 4/6/8/12 = plain prefixes (experiments)
 
 int launch_hamming_best(const void* queries, int nq, const void* map, long long nm, unsigned threshold,
                         unsigned long long indexOffset, unsigned long long* best, cudaStream_t s) {
   if (nq <= 0) return 0;
   cudaMemsetAsync(best, 0xff, sizeof(unsigned long long) * (size_t)nq, s);
   if (nm <= 0) return 0;
-  const int rowsPerChunk = pick_rows_per_chunk(nq, nm);
+  const int rowsPerChunk = pick_rows_per_chunk(nq, nm, g_match_prefix == 0 ? 3 : 2);
   dim3 grid((unsigned)((nm + rowsPerChunk - 1) / rowsPerChunk), (unsigned)((nq + kMbQTile - 1) / kMbQTile));
   const uint4* q4 = static_cast<const uint4*>(queries);
   const uint4* m4 = static_cast<const uint4*>(map);
   switch (g_match_prefix) {
+    case 0: hamming_best_lb_kernel<<<grid, kMbThreads, 0, s>>>(q4, nq, m4, nm, rowsPerChunk, threshold, indexOffset, best); break;
     case 4: hamming_best_kernel<4><<<grid, kMbThreads, 0, s>>>(q4, nq, m4, nm, rowsPerChunk, threshold, indexOffset, best); break;
     case 6: hamming_best_kernel<6><<<grid, kMbThreads, 0, s>>>(q4, nq, m4, nm, rowsPerChunk, threshold, indexOffset, best); break;
     case 8: hamming_best_kernel<8><<<grid, kMbThreads, 0, s>>>(q4, nq, m4, nm, rowsPerChunk, threshold, indexOffset, best); break;
     case 12: hamming_best_kernel<12><<<grid, kMbThreads, 0, s>>>(q4, nq, m4, nm, rowsPerChunk, threshold, indexOffset, best); break;
-    default: hamming_best_kernel<5><<<grid, kMbThreads, 0, s>>>(q4, nq, m4, nm, rowsPerChunk, threshold, indexOffset, best); break;
+    case 5: default: hamming_best_kernel<5><<<grid, kMbThreads, 0, s>>>(q4, nq, m4, nm, rowsPerChunk, threshold, indexOffset, best); break;
   }
   return (int)(grid.x * grid.y);
 }

@@ -59,11 +59,17 @@ def test_match_batched_early_out_variants_agree(mod, ctx, syn):
     q, m = syn.sweep_inputs(1100, 30000, seed=9)
     base = ctx.match_batched(q, m, 60)
     try:
-        for pre in (4, 6, 8, 12):
+        for pre in (4, 5, 6, 8, 12):
             mod.lib().okc_debug_set_match_prefix(pre)
             assert np.array_equal(ctx.match_batched(q, m, 60), base), pre
+        # thresholds at which the lower-bound kernel takes its exact path for most / all pairs
+        mod.lib().okc_debug_set_match_prefix(12)
+        loose = [ctx.match_batched(q[:300], m[:5000], t) for t in (80, 200, 385)]
+        mod.lib().okc_debug_set_match_prefix(0)
+        for t, want in zip((80, 200, 385), loose):
+            assert np.array_equal(ctx.match_batched(q[:300], m[:5000], t), want), t
     finally:
-        mod.lib().okc_debug_set_match_prefix(5)
+        mod.lib().okc_debug_set_match_prefix(0)
 
 
 def test_match_sets_sharded_min_equals_full(mod, ctx, port, syn):

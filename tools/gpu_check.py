@@ -91,7 +91,7 @@ t = time.time()
 best = ctx.match_batched(q, m, 60)
 check("match_batched 1500x40000", np.array_equal(best, port.hamming_best(q, m, 60, nthreads=8)),
       "matches=%d" % int((best != mod.NO_MATCH).sum()))
-for pre in (4, 5, 8, 12, 6):
+for pre in (4, 5, 8, 12, 6, 0):
     mod.lib().okc_debug_set_match_prefix(pre)
     check("match_batched prefix=%d" % pre, np.array_equal(ctx.match_batched(q, m, 60), best))
 check("match_batched empty map", np.all(ctx.match_batched(q[:5], m[:0], 60) == mod.NO_MATCH))
