@@ -17,12 +17,12 @@ bench)
   timeout 900 python bench.py > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench exit $?"
   cat gpurun_out/bench.json; tail -5 gpurun_out/bench.err ;;
 ncu)
-  CMD="python bench.py --steps 16 --warmup 8 --no-sweep --no-cpu-baseline"
+  CMD="python bench.py --steps 6 --warmup 3 --no-sweep --no-cpu-baseline"
   timeout 600 $CMD > gpurun_out/ncu_plain.log 2>&1 &&
   timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_run.log 2>&1
   echo "ncu exit $?"; tail -3 gpurun_out/ncu_run.log ;;
 full)
-  CMD="python bench.py --steps 16 --warmup 8 --no-sweep --no-cpu-baseline"
+  CMD="python bench.py --steps 6 --warmup 3 --no-sweep --no-cpu-baseline"
   timeout 600 $CMD > gpurun_out/ncu_plain2.log 2>&1 || { echo "plain run failed"; tail -5 gpurun_out/ncu_plain2.log; continue; }
   for K in ${NCU_KERNELS:-harris_nms describe_kernel match_to_map_slots select_keypoints}; do
     timeout 900 ncu --set full --clock-control none --import-source on -k regex:$K -s 3 -c 1 -f -o gpurun_out/prof_$K $CMD > gpurun_out/ncu_full_$K.log 2>&1
