@@ -77,12 +77,20 @@ namespace okc {
 int launch_hamming_best(const void* queries, int nq, const void* map, long long nm, unsigned threshold,
                         unsigned long long indexOffset, unsigned long long* best, cudaStream_t s);
 extern int g_match_prefix;
+extern int g_select_wave;
 }  // namespace okc
 
 extern "C" {
 
 const char* okc_last_error_string(void) { return g_err; }
 int okc_version(void) { return 100; }
+
+/* A/B switch for tests: 2 = gather kernel, 0 = sequential-visit stamping kernel. */
+int okc_debug_set_select_wave(int on) {
+  if (on != 0 && on != 2) return OKC_ERR_INVALID;
+  okc::g_select_wave = on;
+  return OKC_OK;
+}
 
 int okc_context_create(int device, okc_context** out) {
   if (!out) return OKC_ERR_INVALID;

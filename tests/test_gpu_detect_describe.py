@@ -236,3 +236,26 @@ def test_scale_space_detect(name, octaves, cases, mod, ctx, ref):
     kp_assert_close(kf, rkd, TOL)
     assert np.array_equal(df, rdd)
     cam.close()
+
+
+@pytest.mark.parametrize("name", CASE_NAMES)
+def test_selection_kernels_agree(name, cases, mod, ctx):
+    """The gather form of the uniformity selection (no occupancy image) against the sequential-visit stamping
+    kernel, which follows the reference loop literally: same keypoints, same order, binding and non-binding keypoint
+    caps, small radius (dense acceptance) included."""
+    cfg, img = cases[name]
+    h, w = img.shape
+    cam = mod.Camera(ctx, w, h, max_keypoints=4096)
+    try:
+        for radius, thr, cap in [(cfg["radius"], cfg["abs_threshold"], cfg["max_kpt"]), (cfg["radius"], 5.0, 50),
+                                 (20.0, cfg["abs_threshold"], 4000), (cfg["radius"], 1.0, 0)]:
+            mod.lib().okc_debug_set_select_wave(0)
+            want = cam.detect(img, radius, 0, thr, cap)
+            for variant in (2,):
+                mod.lib().okc_debug_set_select_wave(variant)
+                got = cam.detect(img, radius, 0, thr, cap)
+                assert len(got) == len(want), (variant, radius, thr, cap, len(got), len(want))
+                assert got.tobytes() == want.tobytes(), (variant, radius, thr, cap)
+    finally:
+        mod.lib().okc_debug_set_select_wave(0)
+        cam.close()
