@@ -58,10 +58,24 @@ __global__ void __launch_bounds__(1024) border_filter_kernel(const Slot* __restr
   if (tid == 0) counters[2] = base_out < maxOut ? base_out : maxOut;
 }
 
-// ---- SmoothedIntensity<unsigned char, int> ----
-__device__ __forceinline__ int smoothed_intensity(const uint8_t* __restrict__ img, int W, int H, float key_x,
-                                                  float key_y, PatternPoint p0, bool warped, const float* warp,
-                                                  float warpScale) {
+// ---- SmoothedIntensity<unsigned char, int> (brisk-descriptor-extractor.cc:355-535) ----
+// Split in two so that a box can be summed by one lane or row-wise by several: box_params() does the float -> int
+// weight arithmetic once, box_row() returns the integer contribution of one box row. The reference's result is a
+// linear combination of pixel sums in int32, so the order of the additions is free.
+struct BoxParams {
+  int mode;                  // 0: box leaves the image (-1), 1: sigma < 0.5 bilinear tap (value ready), 2: weighted box
+  int value;                 // result for modes 0 and 1
+  int x_left, y_top, dx, dy;
+  int A, B, C, D;            // corner weights
+  int wx0, wy0, wx1, wy1;    // r_x_1_i (left column), r_y_1_i (top row), r_x1_i (right column), r_y1_i (bottom row)
+  int scaling, scaling2;
+};
+
+__device__ __forceinline__ BoxParams box_params(const uint8_t* __restrict__ img, int W, int H, float key_x, float key_y,
+                                                PatternPoint p0, bool warped, const float* warp, float warpScale) {
+  BoxParams b;
+  b.mode = 0;
+  b.value = -1;
   float bx = p0.x, by = p0.y, bs = p0.sigma;
   if (warped) {
     bx = warp[0] * p0.x + warp[1] * p0.y;
@@ -78,7 +92,7 @@ __device__ __forceinline__ int smoothed_intensity(const uint8_t* __restrict__ im
   const float y_1 = yf - sigma_half, y1 = yf + sigma_half;
 
   if (sigma_half < 0.5f) {
-    if (x < 0 || x > W - 2 || y < 0 || y > H - 2) return -1;
+    if (x < 0 || x > W - 2 || y < 0 || y > H - 2) return b;
     const int r_x = (int)((xf - (float)x) * 1024.0f);
     const int r_y = (int)((yf - (float)y) * 1024.0f);
     const int r_x_1 = 1024 - r_x, r_y_1 = 1024 - r_y;
@@ -87,58 +101,118 @@ __device__ __forceinline__ int smoothed_intensity(const uint8_t* __restrict__ im
     ret += r_x * r_y_1 * (int)p[1];
     ret += r_x * r_y * (int)p[W + 1];
     ret += r_x_1 * r_y * (int)p[W];
-    return ret / 1024;
+    b.mode = 1;
+    b.value = ret / 1024;
+    return b;
   }
-  if (x_1 < 0.0f) return -1;
-  if (x1 > (float)(W - 1)) return -1;
-  if (y_1 < 0.0f) return -1;
-  if (y1 > (float)(H - 1)) return -1;
+  if (x_1 < 0.0f) return b;
+  if (x1 > (float)(W - 1)) return b;
+  if (y_1 < 0.0f) return b;
+  if (y1 > (float)(H - 1)) return b;
 
-  const int scaling = (int)(4194304.0 / (double)area);
-  const int scaling2 = (int)((double)((float)scaling * area) / 1024.0);
-  const int x_left = (int)((double)x_1 + 0.5);
-  const int y_top = (int)((double)y_1 + 0.5);
+  b.mode = 2;
+  b.scaling = (int)(4194304.0 / (double)area);
+  b.scaling2 = (int)((double)((float)b.scaling * area) / 1024.0);
+  b.x_left = (int)((double)x_1 + 0.5);
+  b.y_top = (int)((double)y_1 + 0.5);
   const int x_right = (int)((double)x1 + 0.5);
   const int y_bottom = (int)((double)y1 + 0.5);
-  const float r_x_1 = (float)((double)((float)x_left - x_1) + 0.5);
-  const float r_y_1 = (float)((double)((float)y_top - y_1) + 0.5);
+  const float r_x_1 = (float)((double)((float)b.x_left - x_1) + 0.5);
+  const float r_y_1 = (float)((double)((float)b.y_top - y_1) + 0.5);
   const float r_x1 = (float)((double)(x1 - (float)x_right) + 0.5);
   const float r_y1 = (float)((double)(y1 - (float)y_bottom) + 0.5);
-  const int dx = x_right - x_left - 1;
-  const int dy = y_bottom - y_top - 1;
-  const float fs = (float)scaling;
-  const int A = (int)((r_x_1 * r_y_1) * fs);
-  const int B = (int)((r_x1 * r_y_1) * fs);
-  const int C = (int)((r_x1 * r_y1) * fs);
-  const int D = (int)((r_x_1 * r_y1) * fs);
-  const int r_x_1_i = (int)(r_x_1 * fs);
-  const int r_y_1_i = (int)(r_y_1 * fs);
-  const int r_x1_i = (int)(r_x1 * fs);
-  const int r_y1_i = (int)(r_y1 * fs);
+  b.dx = x_right - b.x_left - 1;
+  b.dy = y_bottom - b.y_top - 1;
+  const float fs = (float)b.scaling;
+  b.A = (int)((r_x_1 * r_y_1) * fs);
+  b.B = (int)((r_x1 * r_y_1) * fs);
+  b.C = (int)((r_x1 * r_y1) * fs);
+  b.D = (int)((r_x_1 * r_y1) * fs);
+  b.wx0 = (int)(r_x_1 * fs);
+  b.wy0 = (int)(r_y_1 * fs);
+  b.wx1 = (int)(r_x1 * fs);
+  b.wy1 = (int)(r_y1 * fs);
+  return b;
+}
 
-  // corners, edges, interior: the same weighted terms as :450-534 (integral-image path and loop path)
-  const uint8_t* row = img + x_left + (size_t)y_top * W;
-  int top = 0, bottom = 0, left = 0, right = 0, middle = 0;
-  for (int c = 1; c <= dx; ++c) top += (int)row[c];
-  int ret = A * (int)row[0] + B * (int)row[dx + 1];
-  for (int r = 1; r <= dy; ++r) {
-    row += W;
-    left += (int)row[0];
-    right += (int)row[dx + 1];
-    for (int c = 1; c <= dx; ++c) middle += (int)row[c];
+// Rows of a box: 0 = top, 1..nMid = middle, nMid + 1 = bottom, with nMid = max(dy, 0) exactly as the reference's
+// loops advance the row pointer (:450-534, integral-image path and loop path give the same weighted terms).
+__device__ __forceinline__ int box_rows(const BoxParams& b) { return (b.dy > 0 ? b.dy : 0) + 2; }
+
+// kWords: the image base and the row pitch are multiples of 4, so a row segment is read as aligned 32-bit words
+// (one L1 sector lookup per 4 pixels instead of per pixel; the byte loads of scattered boxes are what bounds this
+// kernel) and the interior bytes are summed with a masked dp4a.
+template <bool kWords>
+__device__ __forceinline__ int box_row(const uint8_t* __restrict__ img, int W, const BoxParams& b, int r) {
+  const uint8_t* row = img + b.x_left + (size_t)(b.y_top + r) * W;
+  int mid = 0, first, last;
+  if (kWords) {
+    const unsigned* wrow = reinterpret_cast<const unsigned*>(img + (size_t)(b.y_top + r) * W);
+    const int p0 = b.x_left, pl = b.x_left + b.dx + 1;       // columns of row[0] and row[dx + 1]
+    const int w0 = p0 >> 2, w1 = pl >> 2;
+    unsigned wordFirst = 0, wordLast = 0, acc = 0;
+    for (int w = w0; w <= w1; ++w) {
+      const unsigned v = __ldg(wrow + w);
+      if (w == w0) wordFirst = v;
+      if (w == w1) wordLast = v;
+      const int lo = (p0 + 1 > 4 * w ? p0 + 1 : 4 * w) - 4 * w;            // interior bytes p0+1 .. pl-1 of this word
+      const int hi = (pl - 1 < 4 * w + 3 ? pl - 1 : 4 * w + 3) - 4 * w;
+      if (hi >= lo) {
+        const unsigned mask = (0xffffffffu >> (8 * (3 - hi))) & (0xffffffffu << (8 * lo));
+        acc = __dp4a(v & mask, 0x01010101u, acc);
+      }
+    }
+    mid = (int)acc;
+    first = (int)((wordFirst >> (8 * (p0 & 3))) & 0xffu);
+    last = (int)((wordLast >> (8 * (pl & 3))) & 0xffu);
+  } else {
+    for (int c = 1; c <= b.dx; ++c) mid += (int)row[c];
+    first = (int)row[0];
+    last = (int)row[b.dx + 1];
   }
-  row += W;
-  for (int c = 1; c <= dx; ++c) bottom += (int)row[c];
-  if (dx + dy > 2) {
+  if (r == 0) return b.A * first + b.B * last + mid * b.wy0;
+  if (r < box_rows(b) - 1) return first * b.wx0 + last * b.wx1 + mid * b.scaling;
+  int ret = mid * b.wy1;
+  if (b.dx + b.dy > 2) {
     // Reference quirk kept on purpose: on the integral-image path the two lower corner pixels are fetched with
     // "ptr += dy * imagecols + 1" (:459), i.e. from row y_top + dy and one column to the right.
-    const uint8_t* q = img + x_left + (size_t)y_top * W + (dx + 1) + (size_t)dy * W + 1;
-    ret += C * (int)q[0] + D * (int)q[-(dx + 1)];
+    const uint8_t* q = img + b.x_left + (size_t)b.y_top * W + (b.dx + 1) + (size_t)b.dy * W + 1;
+    ret += b.C * (int)q[0] + b.D * (int)q[-(b.dx + 1)];
   } else {
-    ret += D * (int)row[0] + C * (int)row[dx + 1];
+    ret += b.D * first + b.C * last;
   }
-  ret += top * r_y_1_i + middle * scaling + left * r_x_1_i + right * r_x1_i + bottom * r_y1_i;
-  return ret / scaling2;
+  return ret;
+}
+
+template <bool kWords>
+__device__ __forceinline__ int smoothed_intensity(const uint8_t* __restrict__ img, int W, int H, float key_x,
+                                                  float key_y, PatternPoint p0, bool warped, const float* warp,
+                                                  float warpScale) {
+  const BoxParams b = box_params(img, W, H, key_x, key_y, p0, warped, warp, warpScale);
+  if (b.mode != 2) return b.value;
+  int ret = 0;
+  const int rows = box_rows(b);
+  for (int r = 0; r < rows; ++r) ret += box_row<kWords>(img, W, b, r);
+  return ret / b.scaling2;
+}
+
+// All 66 samples of one keypoint by one warp: samples 0..63 one per lane in two passes; the last two (outermost
+// ring, the largest boxes) row-wise by a half-warp each instead of a third pass with 30 idle lanes.
+static_assert(kPoints == 66, "sample_pattern splits 66 samples as 2 x 32 + 2");
+template <bool kWords>
+__device__ __forceinline__ void sample_pattern(const uint8_t* __restrict__ img, int W, int H, float x, float y,
+                                               const PatternPoint* __restrict__ pat, bool warped, const float* warp,
+                                               float warpScale, int lane, int* values) {
+  for (int i = lane; i < 64; i += 32) values[i] = smoothed_intensity<kWords>(img, W, H, x, y, pat[i], warped, warp, warpScale);
+  const int s = 64 + (lane >> 4), j = lane & 15;
+  const BoxParams b = box_params(img, W, H, x, y, pat[s], warped, warp, warpScale);
+  int part = 0;
+  if (b.mode == 2) {
+    const int rows = box_rows(b);
+    for (int r = j; r < rows; r += 16) part += box_row<kWords>(img, W, b, r);
+  }
+  for (int o = 8; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+  if (j == 0) values[s] = b.mode == 2 ? part / b.scaling2 : b.value;
 }
 
 // cv::normalize(Vec3f): norm in double, scale in double, cast to float (OpenCV matx.hpp).
@@ -194,6 +268,7 @@ describe_kernel(const Slot* __restrict__ slots, const PatternPoint* __restrict__
   if (k >= slot.counters[2]) return;
   int* values = s_values[warp];
   const int W = a.width, H = a.height;
+  const bool words = (W & 3) == 0 && (reinterpret_cast<uintptr_t>(img) & 3) == 0;   // uniform per slot
 
   okc_keypoint kp = kps[k];
   const float x = kp.x, y = kp.y;
@@ -267,8 +342,8 @@ describe_kernel(const Slot* __restrict__ slots, const PatternPoint* __restrict__
     if (!a.rotation_invariant) {
       theta = 0;
     } else {
-      for (int i = lane; i < kPoints; i += 32)
-        values[i] = smoothed_intensity(img, W, H, x, y, pattern[i], false, warp4, 1.0f);
+      if (words) sample_pattern<true>(img, W, H, x, y, pattern, false, warp4, 1.0f, lane, values);
+      else sample_pattern<false>(img, W, H, x, y, pattern, false, warp4, 1.0f, lane, values);
       __syncwarp();
       int direction0 = 0, direction1 = 0;
       for (int p = lane; p < kLongPairs; p += 32) {
@@ -299,8 +374,8 @@ describe_kernel(const Slot* __restrict__ slots, const PatternPoint* __restrict__
 
   // ---- sampling in the final direction (:786-797) and bit tests (:543-568) ----
   const PatternPoint* pat = pattern + (size_t)(directional ? 0 : theta) * kPoints;
-  for (int i = lane; i < kPoints; i += 32)
-    values[i] = smoothed_intensity(img, W, H, x, y, pat[i], warped, warp4, sigmaScale);
+  if (words) sample_pattern<true>(img, W, H, x, y, pat, warped, warp4, sigmaScale, lane, values);
+  else sample_pattern<false>(img, W, H, x, y, pat, warped, warp4, sigmaScale, lane, values);
   __syncwarp();
   uint32_t* out = reinterpret_cast<uint32_t*>(desc + (size_t)k * OKC_DESC_BYTES);
 #pragma unroll
