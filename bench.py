@@ -33,6 +33,7 @@ sys.path.insert(0, ROOT)
 
 N_FRAMES = 200          # image pool: 200 x 2 x 360 960 B = 144 MB, larger than the 126 MB L2
 NUM_LANDMARKS = 2000
+E2E_REPEATS = 3
 MAX_KP = 768            # camera handle capacity (config budget is 700)
 DIRECTION = (0.05, 0.99, 0.1)   # gravity in the camera frame (Frontend.cpp:234-238); any fixed unit-ish vector
 
@@ -427,11 +428,16 @@ def run_b200(args, rank, world):
                 keep(pk, pn, r)
 
     run_e2e(0, max(F * D, warm))
-    barrier()
-    t0 = time.perf_counter()
-    run_e2e(warm, warm + frames)
-    torch.cuda.synchronize()
-    e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1e3)
+    # the K-step e2e region is timed E2E_REPEATS times and the median is reported: it moves ~45 GB/s over PCIe and a
+    # single host hiccup (page faults of the pinned pools, the clock sampler) otherwise decides the number
+    e2e_runs = []
+    for _ in range(E2E_REPEATS):
+        barrier()
+        t0 = time.perf_counter()
+        run_e2e(warm, warm + frames)
+        torch.cuda.synchronize()
+        e2e_runs.append(max_over_ranks((time.perf_counter() - t0) * 1e3))
+    e2e_ms = float(np.median(e2e_runs))
     barrier()
     clocks = sampler.stop() if sampler else None
     # ---- latency of ONE stereo frame through the C ABI with host buffers (what a SLAM front end waits for) ----
@@ -488,8 +494,10 @@ def run_b200(args, rank, world):
                    "host_enqueue_us_per_batch": round(t_host / max(len(work), 1) * 1e6, 1),
                    "l2": "inputs larger than L2 (144 MB image pool cycled)", "sharding": "frames round-robin over ranks"},
         "e2e": {"value": round(world * frames / (e2e_ms * 1e-3), 2), "unit": "frames/s",
-                "h2d_bytes_per_step": h2d * F, "d2h_bytes_per_step": d2h * F, "ms_per_step": round(e2e_ms / n_steps, 5)},
-        "gpu_launches": 7 * n_batches,
+                "h2d_bytes_per_step": h2d * F, "d2h_bytes_per_step": d2h * F, "ms_per_step": round(e2e_ms / n_steps, 5),
+                "timed": "median of %d runs of K steps (ms: %s)" % (E2E_REPEATS, ", ".join("%.1f" % v for v in e2e_runs)),
+                "pcie_gbs": round(world * frames * (h2d + d2h) / (e2e_ms * 1e-3) / 1e9 / world, 1)},
+        "gpu_launches": 8 * n_batches,   # harris_nms, order, select, border_filter, describe, bin_projections, match, stats
         "roofline": roofline,
         "clocks": clocks,
     }

@@ -82,6 +82,7 @@ def lib():
         L.okc_debug_host_tables.argtypes = [vp, C.POINTER(i), C.POINTER(i), vp, vp, vp]
         L.okc_debug_set_match_prefix.argtypes = [i]
         L.okc_debug_set_select_wave.argtypes = [i]
+        L.okc_debug_set_match_binned.argtypes = [i]
         L.okc_debug_batch_counter.argtypes = [vp, i, i, C.POINTER(i)]
         L.okc_debug_std_sort.argtypes = [vp, vp, i, vp]
         L.okc_match_batched.argtypes = [vp, vp, i, vp, i64, u32, u64, vp]

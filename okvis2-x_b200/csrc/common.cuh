@@ -78,6 +78,15 @@ struct Slot {
   unsigned long long* events;   // event_cap improvement events (k, row); consumed on the device by match_stats
   unsigned long long* sort_scratch;  // pow2(event_cap) keys, used when the events do not fit in shared memory
   float dir[3];            // (per enqueue) extraction direction (gravity in this camera's frame)
+  // spatial bins of the landmark projections (bin_projections_kernel), rebuilt per enqueue: rows of the pool grouped
+  // by the cell their projection falls into, ascending row index inside a cell
+  int* bin_start;          // bins_x * bins_y + 1 offsets, then [ncells + 1] = 1 if a projection is not finite
+  int* bin_rows;           // nm row indices
+  double* bin_px;          // nm projections in bin order
+  double* bin_py;
+  int* bin_owner;          // nm landmark slots in bin order
+  int bins_x, bins_y;      // 0: no bins for this slot (full scan)
+  double bin_pad, bin_cell;   // cell(p) = floor((p + bin_pad) / bin_cell), bin_cell >= gate radius + 2 px = bin_pad
 };
 
 struct DetectArgs {
@@ -109,6 +118,9 @@ void launch_describe(const Slot* slots, int n, const PatternTables& t, const Des
                      cudaStream_t s);
 void launch_match_to_map_slots(const Slot* slots, int n, int max_kp, double hammingThreshold, cudaStream_t s);
 void launch_match_stats(const Slot* slots, int n, cudaStream_t s);
+void launch_bin_projections(const Slot* slots, int n, cudaStream_t s);
+void launch_match_to_map_binned(const Slot* slots, int n, int max_kp, double hammingThreshold, cudaStream_t s);
+constexpr int kMaxBinCells = 4096;
 // scale space (octaves > 0)
 void launch_halfsample8(const uint8_t* src, int sw, int sh, uint8_t* dst, cudaStream_t s);
 void launch_twothirdsample8(const uint8_t* src, int sw, int sh, uint8_t* dst, cudaStream_t s);

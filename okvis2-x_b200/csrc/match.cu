@@ -455,6 +455,249 @@ match_to_map_slots_kernel(const Slot* __restrict__ slots, int maxKp, double hamm
                     slot.event_cap, nullptr, slot.event_cap, slot.counters + 4);
 }
 
+// ----------------------------------------------------------------------------------------------
+// B'. the same 3D-2D match through spatial bins of the projections (frame pipeline default)
+// ----------------------------------------------------------------------------------------------
+// The pixel gate of Frontend.cpp:1793-1796 keeps ~1 % of the (keypoint, row) pairs, yet the scan above evaluates it
+// for all of them. bin_projections_kernel groups the rows of a slot's pool by the cell (side >= gate radius + 2 px)
+// their landmark projection falls into, ascending row index inside a cell; a keypoint then only visits the 3x3 cells
+// around its own. Exactness: the bins only preselect - the FP64 gate itself is evaluated unchanged on every visited
+// row - and the reference's iteration order matters only for rows that can improve the running best, i.e. rows with
+// dist < threshold: those few "hits" are collected and replayed in ascending row order, which reproduces best,
+// owner and the improvement events (ctrs / reprErrors) of the full scan.
+constexpr int kBinThreads = 1024;
+
+__device__ __forceinline__ int bin_cell_of(double p, double pad, double cell, int n) {
+  const double c = floor((p + pad) / cell);
+  if (!(c >= 0.0 && c < (double)n)) return c != c || fabs(p) == INFINITY ? -2 : -1;   // -2: not finite
+  return (int)c;
+}
+
+__global__ void __launch_bounds__(kBinThreads, 1) bin_projections_kernel(const Slot* __restrict__ slots) {
+  const Slot& slot = slots[blockIdx.x];
+  if (slot.map == nullptr || slot.bins_x == 0) return;
+  __shared__ int s_cnt[kMaxBinCells];
+  __shared__ int s_warp[32];
+  __shared__ int s_flag;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int ncells = slot.bins_x * slot.bins_y, nm = slot.nm;
+  for (int c = tid; c < kMaxBinCells; c += kBinThreads) s_cnt[c] = 0;
+  if (tid == 0) s_flag = 0;
+  __syncthreads();
+  auto cell_of_row = [&](int m, double* px, double* py, int* o) {
+    *o = slot.owner[m];
+    *px = slot.proj[2 * *o];
+    *py = slot.proj[2 * *o + 1];
+    const int cx = bin_cell_of(*px, slot.bin_pad, slot.bin_cell, slot.bins_x);
+    const int cy = bin_cell_of(*py, slot.bin_pad, slot.bin_cell, slot.bins_y);
+    if (cx == -2 || cy == -2) return -2;
+    if (cx < 0 || cy < 0) return -1;
+    return cy * slot.bins_x + cx;
+  };
+  for (int m = tid; m < nm; m += kBinThreads) {
+    double px, py;
+    int o;
+    const int c = cell_of_row(m, &px, &py, &o);
+    if (c >= 0) atomicAdd(&s_cnt[c], 1);
+    else if (c == -2) s_flag = 1;
+  }
+  __syncthreads();
+  // exclusive scan of the cell counts: 4 cells per thread, warp scan, scan of the warp totals
+  int v[4], sum = 0;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    v[j] = s_cnt[tid * 4 + j];
+    sum += v[j];
+  }
+  int incl = sum;
+  for (int d = 1; d < 32; d <<= 1) {
+    const int t = __shfl_up_sync(0xffffffffu, incl, d);
+    if (lane >= d) incl += t;
+  }
+  if (lane == 31) s_warp[warp] = incl;
+  __syncthreads();
+  if (warp == 0) {
+    const int w = s_warp[lane];
+    int wi = w;
+    for (int d = 1; d < 32; d <<= 1) {
+      const int t = __shfl_up_sync(0xffffffffu, wi, d);
+      if (lane >= d) wi += t;
+    }
+    s_warp[lane] = wi - w;
+  }
+  __syncthreads();
+  int run = s_warp[warp] + incl - sum;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const int c = tid * 4 + j;
+    if (c <= ncells) slot.bin_start[c] = run;   // entry [ncells] = number of binned rows
+    s_cnt[c] = run;                             // becomes the fill cursor
+    run += v[j];
+  }
+  if (tid == 0) slot.bin_start[ncells + 1] = s_flag;
+  __syncthreads();
+  for (int m = tid; m < nm; m += kBinThreads) {
+    double px, py;
+    int o;
+    const int c = cell_of_row(m, &px, &py, &o);
+    if (c >= 0) slot.bin_rows[atomicAdd(&s_cnt[c], 1)] = m;
+  }
+  __syncthreads();
+  // ascending row index inside each cell (the fill order of the atomics is arbitrary): the lists are short
+  for (int c = tid; c < ncells; c += kBinThreads) {
+    const int b = slot.bin_start[c], e = s_cnt[c];
+    for (int i = b + 1; i < e; ++i) {
+      const int x = slot.bin_rows[i];
+      int j = i - 1;
+      while (j >= b && slot.bin_rows[j] > x) {
+        slot.bin_rows[j + 1] = slot.bin_rows[j];
+        --j;
+      }
+      slot.bin_rows[j + 1] = x;
+    }
+  }
+  __syncthreads();
+  const int total = slot.bin_start[ncells];
+  for (int i = tid; i < total; i += kBinThreads) {
+    const int m = slot.bin_rows[i];
+    const int o = slot.owner[m];
+    slot.bin_owner[i] = o;
+    slot.bin_px[i] = slot.proj[2 * o];
+    slot.bin_py[i] = slot.proj[2 * o + 1];
+  }
+}
+
+void launch_bin_projections(const Slot* slots, int n, cudaStream_t s) {
+  if (n > 0) bin_projections_kernel<<<n, kBinThreads, 0, s>>>(slots);
+}
+
+constexpr int kBinnedWarps = 8;
+constexpr int kMaxHits = 64;   // rows inside the gate with dist < threshold, per keypoint (2 per lane); more: full scan
+
+__global__ void __launch_bounds__(kBinnedWarps * 32)
+match_to_map_binned_kernel(const Slot* __restrict__ slots, int maxKp, double hammingThreshold) {
+  const Slot& slot = slots[blockIdx.z];
+  if (slot.map == nullptr) return;
+  const int lane = threadIdx.x & 31;
+  const int k = blockIdx.x * kBinnedWarps + (threadIdx.x >> 5);
+  const int nk = min(slot.counters[2], maxKp);
+  if (k >= nk) return;
+  unsigned q[kDescWords];
+  load_desc(slot.desc, k, q);
+  // cv::KeyPoint floats widen exactly to the Eigen::Vector2d the reference compares with (Frontend.cpp:1787-1790)
+  const double kx = (double)slot.kp_desc[k].x, ky = (double)slot.kp_desc[k].y;
+  const double threshSq = slot.thresh_sq;
+  const int ncells = slot.bins_x * slot.bins_y;
+
+  // hits of this keypoint, two per lane: row index, distance (an integer in [0, 384]), landmark slot
+  int hm[2] = {0x7fffffff, 0x7fffffff}, ho[2] = {-1, -1};
+  unsigned hd[2] = {0, 0};
+  int nh = 0;            // hits held by this lane
+  bool overflow = false;
+  const bool binned = slot.bins_x > 0 && slot.bin_start[ncells + 1] == 0;
+  auto consider = [&](bool inRange, int m, int o, double px, double py) {
+    bool hit = false;
+    unsigned d = 0;
+    if (inRange) {
+      const double rx = px - kx, ry = py - ky;
+      if (!(rx * rx + ry * ry > threshSq)) {
+        unsigned r[kDescWords];
+        load_desc(slot.map, m, r);
+        d = hamming384(q, r);
+        hit = (double)d < hammingThreshold;
+      }
+    }
+    if (hit) {
+      if (nh < 2) {
+        hm[nh] = m;
+        hd[nh] = d;
+        ho[nh] = o;
+        ++nh;
+      } else {
+        overflow = true;
+      }
+    }
+  };
+  if (binned) {
+    const int cx = bin_cell_of(kx, slot.bin_pad, slot.bin_cell, slot.bins_x);
+    const int cy = bin_cell_of(ky, slot.bin_pad, slot.bin_cell, slot.bins_y);
+    if (cx >= 0 && cy >= 0) {   // (always, for a keypoint inside the image)
+      const int x0 = cx > 0 ? cx - 1 : 0, x1 = cx + 1 < slot.bins_x ? cx + 1 : slot.bins_x - 1;
+      for (int yy = cy - 1; yy <= cy + 1; ++yy) {
+        if (yy < 0 || yy >= slot.bins_y) continue;
+        const int b = slot.bin_start[yy * slot.bins_x + x0], e = slot.bin_start[yy * slot.bins_x + x1 + 1];
+        for (int base = b; base < e; base += 32) {
+          const int i = base + lane;
+          const bool in = i < e;
+          consider(in, in ? slot.bin_rows[i] : 0, in ? slot.bin_owner[i] : 0, in ? slot.bin_px[i] : 0.0,
+                   in ? slot.bin_py[i] : 0.0);
+        }
+      }
+    }
+  }
+  double best = hammingThreshold;
+  int bestO = -1;
+  auto improve = [&](unsigned d, int m, int o) {   // uniform across the warp
+    if ((double)d < best) {
+      best = (double)d;
+      bestO = o;
+      if (lane == 0) {
+        const int e = atomicAdd(slot.counters + 4, 1);
+        if (e < slot.event_cap) slot.events[e] = ((unsigned long long)(unsigned)m << 32) | (unsigned)k;
+      }
+    }
+  };
+  if (binned && !__any_sync(0xffffffffu, overflow)) {
+    // replay the hits in ascending row order (row indices are unique: a row lies in exactly one cell)
+    for (;;) {
+      const int mine = hm[0] < hm[1] ? hm[0] : hm[1];
+      const int mmin = __reduce_min_sync(0xffffffffu, mine);
+      if (mmin == 0x7fffffff) break;
+      const int src = __ffs(__ballot_sync(0xffffffffu, mine == mmin)) - 1;
+      const bool first = hm[0] == mmin;
+      const unsigned d = __shfl_sync(0xffffffffu, first ? hd[0] : hd[1], src);
+      const int o = __shfl_sync(0xffffffffu, first ? ho[0] : ho[1], src);
+      if (lane == src) {
+        if (first) hm[0] = 0x7fffffff;
+        else hm[1] = 0x7fffffff;
+      }
+      improve(d, mmin, o);
+    }
+  } else {
+    // full scan in row order (no bins for this slot, a non-finite projection, or too many hits): rare
+    for (int base = 0; base < slot.nm; base += 32) {
+      const int m = base + lane;
+      unsigned d = 0xffffffffu;
+      int o = -1;
+      if (m < slot.nm) {
+        o = slot.owner[m];
+        const double rx = slot.proj[2 * o] - kx, ry = slot.proj[2 * o + 1] - ky;
+        if (!(rx * rx + ry * ry > threshSq)) {
+          unsigned r[kDescWords];
+          load_desc(slot.map, m, r);
+          d = hamming384(q, r);
+        }
+      }
+      unsigned pending = __ballot_sync(0xffffffffu, d != 0xffffffffu && (double)d < best);
+      while (pending) {
+        const int src = __ffs(pending) - 1;
+        pending &= pending - 1;
+        improve(__shfl_sync(0xffffffffu, d, src), base + src, __shfl_sync(0xffffffffu, o, src));
+      }
+    }
+  }
+  if (lane == 0) {
+    slot.best_dist[k] = best;
+    slot.best_owner[k] = bestO;
+  }
+}
+
+void launch_match_to_map_binned(const Slot* slots, int n, int max_kp, double hammingThreshold, cudaStream_t s) {
+  if (n <= 0 || max_kp <= 0) return;
+  dim3 grid((max_kp + kBinnedWarps - 1) / kBinnedWarps, 1, n);
+  match_to_map_binned_kernel<<<grid, kBinnedWarps * 32, 0, s>>>(slots, max_kp, hammingThreshold);
+}
+
 void launch_match_to_map_slots(const Slot* slots, int n, int max_kp, double hammingThreshold, cudaStream_t s) {
   if (n <= 0 || max_kp <= 0) return;
   const int warpsPerBlock = 8;

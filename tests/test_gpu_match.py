@@ -247,7 +247,7 @@ def test_frame_pipeline_equals_separate_calls(mod, ctx, port, syn):
     cam.frame_finish(window)
     cam.kernel_timing(False)
     assert [n for n, _ in times] == ["harris_nms", "order_candidates", "select_keypoints", "border_filter+describe",
-                                       "match_to_map", "match_stats"]
+                                       "bin_projections", "match_to_map", "match_stats"]
     assert all(t > 0 for _, t in times)
     window.close()
     cam.close()
@@ -392,3 +392,66 @@ def test_match_motion_stereo_vs_port(mod, ctx, port, syn):
         # quality = acos(...): device libm vs glibc, float tolerance of BASELINE.json (1e-4), in practice <= 1 ulp
         assert np.allclose(got[4], want[4], rtol=0, atol=1e-12)
         assert (want[1] >= 0).sum() > 50 and np.all(want[1][use0 == 0] == -1)
+
+
+def test_binned_map_match_equals_tile_scan(mod, ctx, port, syn):
+    """Frame-pipeline map match through spatial bins of the projections (default) against the scan of every row and
+    against the port: ordinary window, a non-finite projection (bins unusable -> ordered full scan), projections far
+    outside the image, a tiny gate (grid coarsened to the cell cap), and one keypoint with more hits than the per-warp
+    hit buffer holds (100 copies of its descriptor projected onto it)."""
+    W, H = 752, 480
+    cam = mod.Camera(ctx, W, H, max_keypoints=768)
+    img = syn.scene_image(W, H, 1)
+    kp, desc = cam.detect_describe(img, 38.0, 0, 150.0, 700)
+    kp_xy = np.stack([kp["x"], kp["y"]], 1).astype(np.float64)
+    win = syn.map_window(desc, kp_xy, 1500, 7, W, H)
+    rows, owner, proj = win["map"], win["owner"].astype(np.int32), win["proj"].copy()
+    gate = (3.0 + 458.0 * 0.06) ** 2
+
+    def variants():
+        yield "plain", rows, owner, proj, gate
+        p = proj.copy()
+        p[5] = (np.nan, 10.0)
+        p[9] = (np.inf, -np.inf)
+        yield "nonfinite", rows, owner, p, gate
+        p = proj.copy()
+        p[::7] = p[::7] * 50.0 - 9000.0
+        yield "far-outside", rows, owner, p, gate
+        yield "tiny-gate", rows, owner, proj, 0.25
+        # 100 extra rows = descriptor of keypoint 3 with 0..5 flipped bits, all owned by fresh landmarks projected on it
+        extra = np.repeat(desc[3:4], 100, 0).copy()
+        for j in range(100):
+            for bit in range(j % 6):
+                extra[j, bit] ^= 1 << (j % 8)
+        r2 = np.concatenate([rows, extra])
+        L = proj.shape[0]
+        o2 = np.concatenate([owner, np.arange(L, L + 100, dtype=np.int32)])
+        p2 = np.concatenate([proj, np.repeat(kp_xy[3:4], 100, 0) + 0.5])
+        yield "hit-overflow", r2, o2, p2, gate
+
+    try:
+        for name, r, o, p, g in variants():
+            w = mod.MapWindow(ctx, r, o, p.shape[0])
+            res = []
+            for binned in (0, 1):
+                mod.lib().okc_debug_set_match_binned(binned)
+                batch = mod.Batch(ctx, [cam])
+                batch.enqueue([img], 38.0, 0, 150.0, 700, [(0.0, 1.0, 0.0)], windows=[w], proj=[np.ascontiguousarray(p)],
+                              gates=[g], num_slices=4)
+                batch.finish()
+                k2, d2 = batch.slot_frame(0)
+                assert k2.tobytes() == kp.tobytes() and np.array_equal(d2, desc)
+                res.append(batch.slot_matches(0, len(kp)))
+                batch.close()
+            pd, po, pc, pe = port.match_to_map(desc, kp_xy, np.ones(len(kp), np.uint8), r, o, p, None, g, 60.0, 4)
+            for bd, bo, ctrs, errs in res:
+                assert np.array_equal(bd, pd) and np.array_equal(bo, po), name
+                assert np.array_equal(ctrs, pc), name
+                if name == "nonfinite":   # NaN payloads are not part of the contract
+                    assert np.array_equal(errs, pe, equal_nan=True), name
+                else:
+                    assert errs.tobytes() == pe.tobytes(), name
+            w.close()
+    finally:
+        mod.lib().okc_debug_set_match_binned(1)
+        cam.close()
