@@ -14,6 +14,7 @@
 //                        shared memory, then refines.
 #include "common.cuh"
 #include <cstdlib>
+#include <type_traits>
 
 namespace okc {
 
@@ -59,10 +60,11 @@ __global__ void __launch_bounds__(32 * kHarrisWarps) harris_nms_kernel(const Slo
   const int wordsPerRow = harris_strips(W) * kStripWords;
   const bool emit = lane >= 1 && lane <= 30;
 
-  int hA[4] = {0, 0, 0, 0}, hB[4] = {0, 0, 0, 0}, sA[4] = {0, 0, 0, 0}, sB[4] = {0, 0, 0, 0};
-  int xxA[4] = {0, 0, 0, 0}, xxB[4] = {0, 0, 0, 0}, xyA[4] = {0, 0, 0, 0}, xyB[4] = {0, 0, 0, 0};
-  int yyA[4] = {0, 0, 0, 0}, yyB[4] = {0, 0, 0, 0};
-  int scB[4] = {0, 0, 0, 0}, lrB[4] = {0, 0, 0, 0}, mA[4] = {0, 0, 0, 0}, mB[4] = {0, 0, 0, 0};
+  // Row histories: slot [P] receives the row computed in a step, [(P+1)%3] holds the row before the previous one ("A"),
+  // [(P+2)%3] the previous one ("B"). P advances with the row, the loop is unrolled by 3 and the slots are fixed
+  // registers: no register-to-register rotation (it was 110 of the 382 instructions of a step).
+  int hH[3][4] = {}, sH[3][4] = {}, xxH[3][4] = {}, xyH[3][4] = {}, yyH[3][4] = {}, mH[3][4] = {}, scH[3][4] = {},
+      lrH[3][4] = {};
 
   // pixels of row r (clamped; rows/columns outside the image never reach a valid score)
   auto load_row = [&](int r) -> unsigned {
@@ -78,7 +80,8 @@ __global__ void __launch_bounds__(32 * kHarrisWarps) harris_nms_kernel(const Slo
     return w;
   };
   unsigned wNext = load_row(q0 - 3), wNext2 = load_row(q0 - 2);
-  for (int r = q0 - 3; r <= q1 + 2; ++r) {
+  auto step = [&](auto Pc, int r) {
+    constexpr int P = decltype(Pc)::value, A = (P + 1) % 3, B = (P + 2) % 3;
     // ---- 1. pixels of row r; rows r+1, r+2 are already in flight ----
     const unsigned w = wNext;
     wNext = wNext2;
@@ -91,18 +94,16 @@ __global__ void __launch_bounds__(32 * kHarrisWarps) harris_nms_kernel(const Slo
     px[3] = (int)((w >> 16) & 0xff);
     px[4] = (int)(w >> 24);
     px[5] = (int)(wr & 0xff);
-    int h2[4], s2[4];
-#pragma unroll
-    for (int c = 0; c < 4; ++c) {
-      h2[c] = px[c] - px[c + 2];
-      s2[c] = 3 * (px[c] + px[c + 2]) + 10 * px[c + 1];
-    }
     // ---- 2. gradients and products of row r-1, horizontally smoothed ----
     int pxx[4], pxy[4], pyy[4];
 #pragma unroll
     for (int c = 0; c < 4; ++c) {
-      const int dx = (3 * (hA[c] + h2[c]) + 10 * hB[c]) << 3;
-      const int dy = (sA[c] - s2[c]) << 3;
+      const int h2 = px[c] - px[c + 2];
+      const int s2 = 3 * (px[c] + px[c + 2]) + 10 * px[c + 1];
+      const int dx = (3 * (hH[A][c] + h2) + 10 * hH[B][c]) << 3;
+      const int dy = (sH[A][c] - s2) << 3;
+      hH[P][c] = h2;
+      sH[P][c] = s2;
       pxx[c] = (dx * dx) >> 16;
       pxy[c] = (dx * dy) >> 16;
       pyy[c] = (dy * dy) >> 16;
@@ -128,44 +129,49 @@ __global__ void __launch_bounds__(32 * kHarrisWarps) harris_nms_kernel(const Slo
     // ---- 3. score of row p = r-2 ----
     const int p = r - 2;
     const bool rowValid = p >= 2 && p <= H - 3;
-    int sc2[4];
 #pragma unroll
     for (int c = 0; c < 4; ++c) {
-      const int a = (xxA[c] + 2 * xxB[c] + xx2[c]) >> 4;
-      const int b = (yyA[c] + 2 * yyB[c] + yy2[c]) >> 4;
-      const int d = (xyA[c] + 2 * xyB[c] + xy2[c]) >> 4;
+      const int a = (xxH[A][c] + 2 * xxH[B][c] + xx2[c]) >> 4;
+      const int b = (yyH[A][c] + 2 * yyH[B][c] + yy2[c]) >> 4;
+      const int d = (xyH[A][c] + 2 * xyH[B][c] + xy2[c]) >> 4;
       const int t = (a + b) >> 1;
       const int v = a * b - d * d - (int)((unsigned)(t * t) / 5u);
-      sc2[c] = (rowValid && x + c >= 2 && x + c <= W - 3) ? v : 0;
+      xxH[P][c] = xx2[c];
+      xyH[P][c] = xy2[c];
+      yyH[P][c] = yy2[c];
+      scH[P][c] = (rowValid && x + c >= 2 && x + c <= W - 3) ? v : 0;
     }
     if (emit && p >= q0 && p < q1 && x < W) {
       int32_t* dst = scores + (size_t)p * W + x;
       if (ALIGNED) {
-        *reinterpret_cast<int4*>(dst) = make_int4(sc2[0], sc2[1], sc2[2], sc2[3]);
+        *reinterpret_cast<int4*>(dst) = make_int4(scH[P][0], scH[P][1], scH[P][2], scH[P][3]);
       } else {
 #pragma unroll
         for (int c = 0; c < 4; ++c)
-          if (x + c < W) dst[c] = sc2[c];
+          if (x + c < W) dst[c] = scH[P][c];
       }
     }
-    const int ls = __shfl_up_sync(0xffffffffu, sc2[3], 1), rs = __shfl_down_sync(0xffffffffu, sc2[0], 1);
-    int m2[4], lr2[4];
-    lr2[0] = max(ls, sc2[1]);
-    lr2[1] = max(sc2[0], sc2[2]);
-    lr2[2] = max(sc2[1], sc2[3]);
-    lr2[3] = max(sc2[2], rs);
+    const int ls = __shfl_up_sync(0xffffffffu, scH[P][3], 1), rs = __shfl_down_sync(0xffffffffu, scH[P][0], 1);
+    lrH[P][0] = max(ls, scH[P][1]);
+    lrH[P][1] = max(scH[P][0], scH[P][2]);
+    lrH[P][2] = max(scH[P][1], scH[P][3]);
+    lrH[P][3] = max(scH[P][2], rs);
+    int mTop[4];   // row r-4, read before slot P of the maxima history is overwritten
 #pragma unroll
-    for (int c = 0; c < 4; ++c) m2[c] = max(lr2[c], sc2[c]);
-    // ---- 4. NMS of row q = r-3: top = row r-4 (mA), middle = row r-3 (scB, lrB), bottom = row r-2 (m2) ----
+    for (int c = 0; c < 4; ++c) {
+      mTop[c] = mH[A][c];
+      mH[P][c] = max(lrH[P][c], scH[P][c]);
+    }
+    // ---- 4. NMS of row q = r-3: top = row r-4, middle = row r-3 (slot B), bottom = row r-2 (slot P) ----
     const int q = r - 3;
     if (q >= q0 && q < q1) {   // warp-uniform
       unsigned nib = 0;
       if (emit && q >= 2 && q <= H - 3) {
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
-          const int ctr = scB[c];
+          const int ctr = scH[B][c];
           const bool isMax = x + c >= 2 && x + c <= W - 3 && ctr >= absThreshold &&
-                             ctr >= max(max(mA[c], m2[c]), lrB[c]);
+                             ctr >= max(max(mTop[c], mH[P][c]), lrH[B][c]);
           nib |= (isMax ? 1u : 0u) << c;
         }
       }
@@ -175,24 +181,12 @@ __global__ void __launch_bounds__(32 * kHarrisWarps) harris_nms_kernel(const Slo
       v |= __shfl_xor_sync(0xffffffffu, v, 4);
       if ((lane & 7) == 0) bitmap[(size_t)q * wordsPerRow + strip * kStripWords + (lane >> 3)] = v;
     }
-    // ---- 5. rotate the row windows ----
-#pragma unroll
-    for (int c = 0; c < 4; ++c) {
-      hA[c] = hB[c];
-      hB[c] = h2[c];
-      sA[c] = sB[c];
-      sB[c] = s2[c];
-      xxA[c] = xxB[c];
-      xxB[c] = xx2[c];
-      xyA[c] = xyB[c];
-      xyB[c] = xy2[c];
-      yyA[c] = yyB[c];
-      yyB[c] = yy2[c];
-      mA[c] = mB[c];
-      mB[c] = m2[c];
-      scB[c] = sc2[c];
-      lrB[c] = lr2[c];
-    }
+  };
+  // rows q0-3 .. q1+2, three per trip (an extra step or two past the end only see clamped rows and emit nothing)
+  for (int r = q0 - 3; r <= q1 + 2; r += 3) {
+    step(std::integral_constant<int, 0>{}, r);
+    step(std::integral_constant<int, 1>{}, r + 1);
+    step(std::integral_constant<int, 2>{}, r + 2);
   }
 }
 
