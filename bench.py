@@ -258,12 +258,15 @@ def ncu_traffic(kernel, images_per_launch):
     """DRAM bytes per launch of `kernel` from the newest committed ncu capture (profiles/*/traffic.json), or None when
     there is none for this batch size. Never measured under this run: it is the committed profile's number."""
     import glob
-    key = {"border_filter+describe": "describe_kernel", "match_to_map": "match_to_map_slots"}.get(kernel, kernel)
+    key = {"border_filter+describe": "describe_kernel", "match_to_map": "match_to_map_binned"}.get(kernel, kernel)
     for path in sorted(glob.glob(os.path.join(ROOT, "profiles", "*", "traffic.json")), reverse=True):
         try:
             d = json.load(open(path))
-            if d.get("images_per_launch") == images_per_launch and key in d.get("kernels", {}):
-                return d["kernels"][key]["dram_bytes_per_launch"]
+            if d.get("images_per_launch") != images_per_launch:
+                continue
+            for name, v in d.get("kernels", {}).items():
+                if name.startswith(key):
+                    return v["dram_bytes_per_launch"]
         except (OSError, ValueError, KeyError):
             continue
     return None

@@ -8,7 +8,18 @@ WANT = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum
         "launch__registers_per_thread", "sm__throughput.avg.pct_of_peak_sustained_elapsed",
         "gpu__compute_memory_throughput.avg.pct_of_peak_sustained_elapsed", "sm__warps_active.avg.pct_of_peak_sustained_active",
         "smsp__issue_active.avg.pct_of_peak_sustained_active", "smsp__inst_executed.sum", "l1tex__t_sector_hit_rate.pct",
-        "lts__t_sector_hit_rate.pct", "launch__waves_per_multiprocessor"]
+        "lts__t_sector_hit_rate.pct", "launch__waves_per_multiprocessor",
+        "sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active", "sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active",
+        "sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active", "sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active",
+        "sm__inst_executed_pipe_fp64.avg.pct_of_peak_sustained_active",
+        "l1tex__data_pipe_lsu_wavefronts.avg.pct_of_peak_sustained_elapsed",
+        "smsp__average_warps_issue_stalled_barrier_per_issue_active.ratio",
+        "smsp__average_warps_issue_stalled_long_scoreboard_per_issue_active.ratio",
+        "smsp__average_warps_issue_stalled_short_scoreboard_per_issue_active.ratio",
+        "smsp__average_warps_issue_stalled_wait_per_issue_active.ratio",
+        "smsp__average_warps_issue_stalled_math_pipe_throttle_per_issue_active.ratio",
+        "smsp__average_warps_issue_stalled_lg_throttle_per_issue_active.ratio",
+        "smsp__average_warps_issue_stalled_mio_throttle_per_issue_active.ratio"]
 UNIT = {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0}
 lines = ["# ncu summary (%s)" % tag, ""]
 traffic = {}
@@ -53,5 +64,8 @@ for f in sorted(os.listdir("gpurun_out")):
         pass
     lines.append("")
 open(os.path.join(out, "summary.md"), "w").write("\n".join(lines))
-json.dump(traffic, open(os.path.join(out, "traffic.json"), "w"), indent=1)
+json.dump({"_note": "dram__bytes_read.sum + dram__bytes_write.sum per launch from one `ncu --set full` capture per kernel of "
+                    "`python bench.py --steps 6 --warmup 3 --no-cpu-baseline` (tools/ncu_round.sh; frames_per_batch 16 = 32 "
+                    "images per launch); hamming_best_lb from the 10k x 1M sweep of the same run",
+           "images_per_launch": 32, "kernels": traffic}, open(os.path.join(out, "traffic.json"), "w"), indent=1)
 print("\n".join(lines))
