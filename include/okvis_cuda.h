@@ -179,6 +179,40 @@ int okc_match_to_map_uninitialised(okc_context* ctx, const uint8_t* queries, con
                                    int num_slices, double* best_dist, int32_t* best_owner, double* hps_W,
                                    uint8_t* hps_written, uint64_t* ctrs);
 
+/* ---- Camera geometry next to the path (rows f2 and the first half of f1). FP64 on the device.
+ * The Eigen evaluation order is restated, not pinned (Eigen is not available where this was built): results agree
+ * with the CPU restatement in oracle/port bit for bit and with the reference up to that caveat. ---- */
+#define OKC_DISTORTION_NONE 0        /* cameras::NoDistortion */
+#define OKC_DISTORTION_RADTAN 1      /* cameras::RadialTangentialDistortion: k = {k1, k2, p1, p2} */
+#define OKC_DISTORTION_EQUIDISTANT 2 /* cameras::EquidistantDistortion:      k = {k1, k2, k3, k4} */
+typedef struct okc_pinhole {         /* cameras::PinholeCamera<D> intrinsics (okvis_cv/include/okvis/cameras/PinholeCamera.hpp) */
+  int width, height;
+  double fu, fv, cu, cv;
+  int distortion;
+  double k[8];
+} okc_pinhole;
+/* cameras::ProjectionStatus (okvis_cv/include/okvis/cameras/CameraBase.hpp:38-45) */
+#define OKC_PROJ_SUCCESSFUL 0
+#define OKC_PROJ_OUTSIDE_IMAGE 1
+#define OKC_PROJ_MASKED 2
+#define OKC_PROJ_BEHIND 3
+#define OKC_PROJ_INVALID 4
+
+/* okvis::Frame::computeBackProjections (okvis_cv/include/okvis/implementation/Frame.hpp:158-173): for every keypoint
+ * PinholeCamera::backProject (PinholeCamera.hpp:566-585) = unscale, D::undistort (Gauss-Newton on D::distort),
+ * direction (x, y, 1). e_C[3k..] receives the direction also when the iteration did not succeed (as the reference
+ * stores it), valid[k] the success flag, *n_valid the return value of computeBackProjections. Host buffers. */
+int okc_back_project(okc_context* ctx, const okc_pinhole* cam, const okc_keypoint* keypoints, int n, double* e_C,
+                     uint8_t* valid, int* n_valid);
+
+/* Field-of-view test of the landmark loop of Frontend::matchToMap (Frontend.cpp:1376-1407): hp_C = T_CW * hp_W
+ * (T_CW = 3x3 rotation, row-major, followed by the translation: 12 doubles), projectHomogeneous, and the window
+ * [-repr_threshold, width + repr_threshold] x [-repr_threshold, height + repr_threshold]. Per landmark:
+ * proj_xy[2l..] (the projection that becomes LandmarkToMatch::projection and the proj_xy input of okc_match_to_map),
+ * status[l] (OKC_PROJ_*), visible[l] = landmark survives the `continue`s of :1393-1405. Host buffers. */
+int okc_project_landmarks(okc_context* ctx, const okc_pinhole* cam, const double T_CW[12], const double* hp_W, int n,
+                          double repr_threshold, double* proj_xy, uint8_t* status, uint8_t* visible);
+
 /* ---- Frame pipeline: the per-frame sequence of Frontend::detectAndDescribe followed by Frontend::matchToMap
  * (ThreadedSlam.cpp:676-717 -> Frontend.cpp:204-262, 1335-1536) with every intermediate product left in HBM.
  * The queries of the map match are the camera handle's own descriptors/keypoints of the frame just described,

@@ -46,6 +46,21 @@ class DetectParams(C.Structure):
                 ("max_num_keypoints", C.c_uint64)]
 
 
+class Pinhole(C.Structure):
+    """okc_pinhole: cameras::PinholeCamera<D> intrinsics. distortion: 0 none, 1 radial-tangential (k1, k2, p1, p2),
+    2 equidistant (k1..k4)."""
+    _fields_ = [("width", C.c_int), ("height", C.c_int), ("fu", C.c_double), ("fv", C.c_double), ("cu", C.c_double),
+                ("cv", C.c_double), ("distortion", C.c_int), ("k", C.c_double * 8)]
+
+    @staticmethod
+    def make(width, height, f, c, distortion, k):
+        p = Pinhole(int(width), int(height), float(f[0]), float(f[1]), float(c[0]), float(c[1]),
+                    {"none": 0, "radialtangential": 1, "equidistant": 2}.get(distortion, distortion))
+        for i, v in enumerate(k):
+            p.k[i] = float(v)
+        return p
+
+
 class DescribeParams(C.Structure):
     _fields_ = [("rotation_invariant", C.c_int), ("scale_invariant", C.c_int), ("extraction_direction", C.c_float * 3)]
 
@@ -82,6 +97,8 @@ def lib():
         L.okc_debug_host_tables.argtypes = [vp, C.POINTER(i), C.POINTER(i), vp, vp, vp]
         L.okc_debug_set_match_prefix.argtypes = [i]
         L.okc_debug_set_select_wave.argtypes = [i]
+        L.okc_back_project.argtypes = [vp, vp, vp, i, vp, vp, C.POINTER(i)]
+        L.okc_project_landmarks.argtypes = [vp, vp, vp, vp, i, C.c_double, vp, vp, vp]
         L.okc_debug_set_match_binned.argtypes = [i]
         L.okc_debug_batch_counter.argtypes = [vp, i, i, C.POINTER(i)]
         L.okc_debug_std_sort.argtypes = [vp, vp, i, vp]
@@ -151,6 +168,27 @@ class Context:
         if self.h:
             lib().okc_context_destroy(self.h)
             self.h = C.c_void_p()
+
+    # -- camera geometry (Frame::computeBackProjections; FoV test of Frontend::matchToMap) --
+    def back_project(self, cam, keypoints):
+        kp = np.ascontiguousarray(keypoints, KP_DTYPE)
+        n = len(kp)
+        e = np.zeros((max(n, 1), 3), np.float64)
+        valid = np.zeros(max(n, 1), np.uint8)
+        nv = C.c_int(0)
+        _check(lib().okc_back_project(self.h, C.byref(cam), _p(kp), n, _p(e), _p(valid), C.byref(nv)), "okc_back_project")
+        return e[:n], valid[:n], nv.value
+
+    def project_landmarks(self, cam, T_CW, hp_W, repr_threshold):
+        T = np.ascontiguousarray(T_CW, np.float64).reshape(12)
+        h = np.ascontiguousarray(hp_W, np.float64).reshape(-1, 4)
+        n = len(h)
+        proj = np.zeros((max(n, 1), 2), np.float64)
+        status = np.zeros(max(n, 1), np.uint8)
+        vis = np.zeros(max(n, 1), np.uint8)
+        _check(lib().okc_project_landmarks(self.h, C.byref(cam), _p(T), _p(h), n, float(repr_threshold), _p(proj),
+                                           _p(status), _p(vis)), "okc_project_landmarks")
+        return proj[:n], status[:n], vis[:n]
 
     # -- brute force (Frontend::verifyRecognisedPlace, Frontend.cpp:316-345; the 10k x 1M sweep) --
     def match_batched(self, queries, mp, threshold=60, index_offset=0):

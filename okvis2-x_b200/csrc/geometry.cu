@@ -1,0 +1,305 @@
+// Camera geometry next to the hot path (SURVEY.md section 8(f), rows f2 and the first half of f1).
+//
+//  back_project_kernel     = okvis::Frame::computeBackProjections (okvis_cv/include/okvis/implementation/Frame.hpp:158-173)
+//                            -> PinholeCamera<D>::backProject (cameras/implementation/PinholeCamera.hpp:566-585)
+//                            -> D::undistort, Gauss-Newton on D::distort
+//                               (RadialTangentialDistortion.hpp:70-112, 194-233; EquidistantDistortion.hpp:87-160, 299-332)
+//  project_landmarks_kernel = the field-of-view test at the top of the landmark loop of Frontend::matchToMap
+//                            (okvis_frontend/src/Frontend.cpp:1376-1407): hp_C = T_CW * hp_W
+//                            (kinematics/implementation/Transformation.hpp:251-258), projectHomogeneous
+//                            (PinholeCamera.hpp:249-283, 485-496), the +-reprThreshold window.
+//
+// FP64, one thread per keypoint / landmark, compiled with --fmad=false like everything else: every operation is
+// rounded separately, as in the reference's x86-64 build without FMA. The Eigen expressions are written out in the
+// order Eigen evaluates them for fixed 2x2 / 3x3 sizes (inverse = adjugate * (1 / det); products coefficient by
+// coefficient). Eigen itself is not in this image, so this order is restated, not pinned.
+#include "common.cuh"
+
+namespace okc {
+
+struct Mat2 { double a, b, c, d; };  // [a b; c d]
+
+// D::distort with the 2x2 Jacobian wrt. the undistorted point. Returns false where the reference's distort does.
+__host__ __device__ inline bool distort_point(const okc_pinhole& cam, double u0, double u1, double* d0, double* d1,
+                                              Mat2* J) {
+  if (cam.distortion == OKC_DISTORTION_RADTAN) {
+    const double k1 = cam.k[0], k2 = cam.k[1], p1 = cam.k[2], p2 = cam.k[3];
+    const double mx_u = u0 * u0, my_u = u1 * u1, mxy_u = u0 * u1;
+    const double rho_u = mx_u + my_u;
+    const double rad_dist_u = k1 * rho_u + k2 * rho_u * rho_u;
+    *d0 = u0 + u0 * rad_dist_u + 2.0 * p1 * mxy_u + p2 * (rho_u + 2.0 * mx_u);
+    *d1 = u1 + u1 * rad_dist_u + 2.0 * p2 * mxy_u + p1 * (rho_u + 2.0 * my_u);
+    if (J) {
+      J->a = 1 + rad_dist_u + k1 * 2.0 * mx_u + k2 * rho_u * 4 * mx_u + 2.0 * p1 * u1 + 6 * p2 * u0;
+      J->c = k1 * 2.0 * u0 * u1 + k2 * 4 * rho_u * u0 * u1 + p1 * 2.0 * u0 + 2.0 * p2 * u1;
+      J->b = J->c;
+      J->d = 1 + rad_dist_u + k1 * 2.0 * my_u + k2 * rho_u * 4 * my_u + 6 * p1 * u1 + 2.0 * p2 * u0;
+    }
+    return true;
+  }
+  if (cam.distortion == OKC_DISTORTION_EQUIDISTANT) {
+    const double k1 = cam.k[0], k2 = cam.k[1], k3 = cam.k[2], k4 = cam.k[3];
+    const double r = sqrt(u0 * u0 + u1 * u1);
+    const double theta = atan(r);
+    const double theta2 = theta * theta;
+    const double theta4 = theta2 * theta2;
+    const double theta6 = theta4 * theta2;
+    const double theta8 = theta4 * theta4;
+    const double thetad = theta * (1.0 + k1 * theta2 + k2 * theta4 + k3 * theta6 + k4 * theta8);
+    const double scaling = (r > 1e-8) ? thetad / r : 1.0;
+    *d0 = scaling * u0;
+    *d1 = scaling * u1;
+    if (J) {
+      if (r > 1e-8) {
+        // "mostly matlab generated" (EquidistantDistortion.hpp:108-150), same temporaries
+        double t2, t3, t4, t6, t7, t8, t9, t11, t17, t18, t19, t20, t25;
+        t2 = u0 * u0;
+        t3 = u1 * u1;
+        t4 = t2 + t3;
+        t6 = atan(sqrt(t4));
+        t7 = t6 * t6;
+        t8 = 1.0 / sqrt(t4);
+        t9 = t7 * t7;
+        t11 = 1.0 / ((t2 + t3) + 1.0);
+        t17 = (((k1 * t7 + k2 * t9) + k3 * t7 * t9) + k4 * (t9 * t9)) + 1.0;
+        t18 = 1.0 / t4;
+        t19 = 1.0 / sqrt(t4 * t4 * t4);
+        t20 = t6 * t8 * t17;
+        t25 = ((k2 * t6 * t7 * t8 * t11 * u1 * 4.0 + k3 * t6 * t8 * t9 * t11 * u1 * 6.0) +
+               k4 * t6 * t7 * t8 * t9 * t11 * u1 * 8.0) +
+              k1 * t6 * t8 * t11 * u1 * 2.0;
+        t4 = ((k2 * t6 * t7 * t8 * t11 * u0 * 4.0 + k3 * t6 * t8 * t9 * t11 * u0 * 6.0) +
+              k4 * t6 * t7 * t8 * t9 * t11 * u0 * 8.0) +
+             k1 * t6 * t8 * t11 * u0 * 2.0;
+        t7 = t11 * t17 * t18 * u0 * u1;
+        J->b = (t7 + t6 * t8 * t25 * u0) - t6 * t17 * t19 * u0 * u1;
+        J->d = ((t20 - t3 * t6 * t17 * t19) + t3 * t11 * t17 * t18) + t6 * t8 * t25 * u1;
+        J->a = ((t20 - t2 * t6 * t17 * t19) + t2 * t11 * t17 * t18) + t6 * t8 * t4 * u0;
+        J->c = (t7 + t6 * t8 * t4 * u1) - t6 * t17 * t19 * u0 * u1;
+      } else {
+        J->a = 1.0;  // J.setIdentity() (EquidistantDistortion.hpp, r <= 1e-8 branch)
+        J->b = 0.0;
+        J->c = 0.0;
+        J->d = 1.0;
+      }
+    }
+    return true;
+  }
+  *d0 = u0;  // NoDistortion
+  *d1 = u1;
+  if (J) {
+    J->a = 1.0;
+    J->b = 0.0;
+    J->c = 0.0;
+    J->d = 1.0;
+  }
+  return true;
+}
+
+// D::undistort: Gauss-Newton from the distorted point; success once chi2 < 1e-6 was seen, stop at chi2 < 1e-15.
+// radtan: 5 iterations (RadialTangentialDistortion.hpp:200), equidistant: 20 (EquidistantDistortion.hpp:304).
+__host__ __device__ inline bool undistort_point(const okc_pinhole& cam, double y0, double y1, double* x0, double* x1) {
+  if (cam.distortion == OKC_DISTORTION_NONE) {
+    *x0 = y0;
+    *x1 = y1;
+    return true;
+  }
+  double xb0 = y0, xb1 = y1;
+  const int n = cam.distortion == OKC_DISTORTION_EQUIDISTANT ? 20 : 5;
+  bool success = false;
+  for (int i = 0; i < n; ++i) {
+    double t0, t1;
+    Mat2 E;
+    distort_point(cam, xb0, xb1, &t0, &t1, &E);
+    const double e0 = y0 - t0, e1 = y1 - t1;
+    // E2 = E^T * E
+    Mat2 E2;
+    E2.a = E.a * E.a + E.c * E.c;
+    E2.b = E.a * E.b + E.c * E.d;
+    E2.c = E.b * E.a + E.d * E.c;
+    E2.d = E.b * E.b + E.d * E.d;
+    // E2.inverse(): adjugate times 1/det
+    const double invdet = 1.0 / (E2.a * E2.d - E2.c * E2.b);
+    Mat2 I;
+    I.a = E2.d * invdet;
+    I.c = -E2.c * invdet;
+    I.b = -E2.b * invdet;
+    I.d = E2.a * invdet;
+    // (E2^-1 * E^T) * e
+    Mat2 M;
+    M.a = I.a * E.a + I.b * E.b;
+    M.b = I.a * E.c + I.b * E.d;
+    M.c = I.c * E.a + I.d * E.b;
+    M.d = I.c * E.c + I.d * E.d;
+    xb0 += M.a * e0 + M.b * e1;
+    xb1 += M.c * e0 + M.d * e1;
+    const double chi2 = e0 * e0 + e1 * e1;
+    if (chi2 < 1e-6) success = true;
+    if (chi2 < 1e-15) {
+      success = true;
+      break;
+    }
+  }
+  *x0 = xb0;
+  *x1 = xb1;
+  return success;
+}
+
+// PinholeCamera::project (PinholeCamera.hpp:249-283). Status codes = cameras::ProjectionStatus (CameraBase.hpp:38-45).
+__host__ __device__ inline int project_point(const okc_pinhole& cam, double p0, double p1, double p2, double* u, double* v) {
+  if (fabs(p2) < 1.0e-12) return OKC_PROJ_INVALID;
+  const double rz = 1.0 / p2;
+  double d0, d1;
+  if (!distort_point(cam, p0 * rz, p1 * rz, &d0, &d1, nullptr)) return OKC_PROJ_INVALID;
+  *u = cam.fu * d0 + cam.cu;
+  *v = cam.fv * d1 + cam.cv;
+  // isInImage, then isMasked (no mask images here), then the sign of z
+  if (*u < 0.0 || *v < 0.0 || *u >= (double)cam.width || *v >= (double)cam.height) return OKC_PROJ_OUTSIDE_IMAGE;
+  return p2 > 0.0 ? OKC_PROJ_SUCCESSFUL : OKC_PROJ_BEHIND;
+}
+
+__global__ void back_project_kernel(okc_pinhole cam, const okc_keypoint* __restrict__ kps, int n,
+                                    double* __restrict__ e_C, uint8_t* __restrict__ valid, int* __restrict__ nValid) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  bool ok = false;
+  if (k < n) {
+    // Eigen::Vector2d(ckp.pt.x, ckp.pt.y): the floats widen exactly
+    const double y0 = ((double)kps[k].x - cam.cu) * (1.0 / cam.fu);
+    const double y1 = ((double)kps[k].y - cam.cv) * (1.0 / cam.fv);
+    double x0, x1;
+    ok = undistort_point(cam, y0, y1, &x0, &x1);
+    e_C[3 * k] = x0;
+    e_C[3 * k + 1] = x1;
+    e_C[3 * k + 2] = 1.0;
+    valid[k] = ok ? 1 : 0;
+  }
+  const unsigned m = __ballot_sync(0xffffffffu, ok);
+  if ((threadIdx.x & 31) == 0 && m) atomicAdd(nValid, __popc(m));
+}
+
+// T = {C row-major 3x3, r}: hp_C = [C * hp_W.head<3>() + r * hp_W[3]; hp_W[3]]
+__global__ void project_landmarks_kernel(okc_pinhole cam, const double* __restrict__ T_CW,
+                                         const double* __restrict__ hp_W, int n, double reprThreshold,
+                                         double* __restrict__ proj_xy, uint8_t* __restrict__ status,
+                                         uint8_t* __restrict__ visible) {
+  const int l = blockIdx.x * blockDim.x + threadIdx.x;
+  if (l >= n) return;
+  const double x = hp_W[4 * l], y = hp_W[4 * l + 1], z = hp_W[4 * l + 2], s = hp_W[4 * l + 3];
+  double c[3];
+  for (int i = 0; i < 3; ++i)
+    c[i] = ((T_CW[3 * i] * x + T_CW[3 * i + 1] * y) + T_CW[3 * i + 2] * z) + T_CW[9 + i] * s;
+  // projectHomogeneous: head, negated when the homogeneous coordinate is negative
+  if (s < 0) {
+    c[0] = -c[0];
+    c[1] = -c[1];
+    c[2] = -c[2];
+  }
+  double u = 0.0, v = 0.0;
+  const int st = project_point(cam, c[0], c[1], c[2], &u, &v);
+  bool vis = !(st == OKC_PROJ_INVALID || st == OKC_PROJ_BEHIND);
+  if (vis) {
+    const double maxU = (double)cam.width + reprThreshold, maxV = (double)cam.height + reprThreshold;
+    if (u < -reprThreshold || v < -reprThreshold || u > maxU || v > maxV) vis = false;
+  }
+  proj_xy[2 * l] = u;
+  proj_xy[2 * l + 1] = v;
+  status[l] = (uint8_t)st;
+  visible[l] = vis ? 1 : 0;
+}
+
+int check_pinhole(const okc_pinhole* cam) {
+  if (!cam || cam->width <= 0 || cam->height <= 0) return OKC_ERR_INVALID;
+  if (cam->distortion != OKC_DISTORTION_NONE && cam->distortion != OKC_DISTORTION_RADTAN &&
+      cam->distortion != OKC_DISTORTION_EQUIDISTANT) {
+    set_error("distortion model %d is not implemented (radialtangential8 is used by no shipped configuration)",
+              cam->distortion);
+    return OKC_ERR_INVALID;
+  }
+  return OKC_OK;
+}
+
+void launch_back_project(const okc_pinhole& cam, const okc_keypoint* kps, int n, double* e_C, uint8_t* valid,
+                         int* nValid, cudaStream_t s) {
+  if (n > 0) back_project_kernel<<<(n + 127) / 128, 128, 0, s>>>(cam, kps, n, e_C, valid, nValid);
+}
+
+void launch_project_landmarks(const okc_pinhole& cam, const double* T_CW, const double* hp_W, int n,
+                              double reprThreshold, double* proj_xy, uint8_t* status, uint8_t* visible,
+                              cudaStream_t s) {
+  if (n > 0)
+    project_landmarks_kernel<<<(n + 127) / 128, 128, 0, s>>>(cam, T_CW, hp_W, n, reprThreshold, proj_xy, status,
+                                                              visible);
+}
+
+
+}  // namespace okc
+
+struct okc_context;
+int okc_context_device(const okc_context* ctx);
+
+extern "C" {
+
+int okc_back_project(okc_context* ctx, const okc_pinhole* cam, const okc_keypoint* keypoints, int n, double* e_C,
+                     uint8_t* valid, int* n_valid) {
+  if (!ctx || n < 0 || (n > 0 && (!keypoints || !e_C || !valid))) return OKC_ERR_INVALID;
+  if (int rc = okc::check_pinhole(cam)) return rc;
+  if (n_valid) *n_valid = 0;
+  if (n == 0) return OKC_OK;
+  OKC_CUDA_TRY(cudaSetDevice(okc_context_device(ctx)));
+  uint8_t* d = nullptr;
+  const size_t oKp = 0, oE = (size_t)n * sizeof(okc_keypoint), oV = oE + (size_t)n * 24, oN = (oV + n + 15) & ~(size_t)15;
+  OKC_CUDA_TRY(cudaMalloc(&d, oN + 16));
+  int rc = OKC_OK;
+  auto fail = [&](cudaError_t e, const char* what) {
+    if (e != cudaSuccess && rc == OKC_OK) {
+      okc::set_error("%s failed: %s", what, cudaGetErrorString(e));
+      rc = OKC_ERR_CUDA;
+    }
+  };
+  fail(cudaMemcpy(d + oKp, keypoints, (size_t)n * sizeof(okc_keypoint), cudaMemcpyHostToDevice), "cudaMemcpy");
+  fail(cudaMemset(d + oN, 0, 16), "cudaMemset");
+  if (rc == OKC_OK) {
+    okc::launch_back_project(*cam, reinterpret_cast<const okc_keypoint*>(d + oKp), n, reinterpret_cast<double*>(d + oE),
+                             d + oV, reinterpret_cast<int*>(d + oN), nullptr);
+    fail(cudaGetLastError(), "back_project_kernel");
+    fail(cudaMemcpy(e_C, d + oE, (size_t)n * 24, cudaMemcpyDeviceToHost), "cudaMemcpy");
+    fail(cudaMemcpy(valid, d + oV, (size_t)n, cudaMemcpyDeviceToHost), "cudaMemcpy");
+    int nv = 0;
+    fail(cudaMemcpy(&nv, d + oN, sizeof(int), cudaMemcpyDeviceToHost), "cudaMemcpy");
+    if (n_valid) *n_valid = nv;
+  }
+  cudaFree(d);
+  return rc;
+}
+
+int okc_project_landmarks(okc_context* ctx, const okc_pinhole* cam, const double T_CW[12], const double* hp_W, int n,
+                          double repr_threshold, double* proj_xy, uint8_t* status, uint8_t* visible) {
+  if (!ctx || !T_CW || n < 0 || (n > 0 && (!hp_W || !proj_xy || !status || !visible))) return OKC_ERR_INVALID;
+  if (int rc = okc::check_pinhole(cam)) return rc;
+  if (n == 0) return OKC_OK;
+  OKC_CUDA_TRY(cudaSetDevice(okc_context_device(ctx)));
+  uint8_t* d = nullptr;
+  const size_t oT = 0, oH = 128, oP = oH + (size_t)n * 32, oS = oP + (size_t)n * 16, oV = oS + (size_t)n;
+  OKC_CUDA_TRY(cudaMalloc(&d, oV + n));
+  int rc = OKC_OK;
+  auto fail = [&](cudaError_t e, const char* what) {
+    if (e != cudaSuccess && rc == OKC_OK) {
+      okc::set_error("%s failed: %s", what, cudaGetErrorString(e));
+      rc = OKC_ERR_CUDA;
+    }
+  };
+  fail(cudaMemcpy(d + oT, T_CW, 12 * sizeof(double), cudaMemcpyHostToDevice), "cudaMemcpy");
+  fail(cudaMemcpy(d + oH, hp_W, (size_t)n * 32, cudaMemcpyHostToDevice), "cudaMemcpy");
+  if (rc == OKC_OK) {
+    okc::launch_project_landmarks(*cam, reinterpret_cast<const double*>(d + oT), reinterpret_cast<const double*>(d + oH),
+                                  n, repr_threshold, reinterpret_cast<double*>(d + oP), d + oS, d + oV, nullptr);
+    fail(cudaGetLastError(), "project_landmarks_kernel");
+    fail(cudaMemcpy(proj_xy, d + oP, (size_t)n * 16, cudaMemcpyDeviceToHost), "cudaMemcpy");
+    fail(cudaMemcpy(status, d + oS, (size_t)n, cudaMemcpyDeviceToHost), "cudaMemcpy");
+    fail(cudaMemcpy(visible, d + oV, (size_t)n, cudaMemcpyDeviceToHost), "cudaMemcpy");
+  }
+  cudaFree(d);
+  return rc;
+}
+
+}  // extern "C"

@@ -1,0 +1,192 @@
+// TEST INFRASTRUCTURE ONLY (oracle): CPU restatement of the camera geometry next to the hot path.
+//   port_back_project      - okvis::Frame::computeBackProjections (okvis_cv/include/okvis/implementation/Frame.hpp:158-173)
+//                            through PinholeCamera::backProject (cameras/implementation/PinholeCamera.hpp:566-585) and
+//                            the distortion models' undistort / distort
+//                            (RadialTangentialDistortion.hpp:70-112, 194-233; EquidistantDistortion.hpp:87-189, 299-332)
+//   port_project_landmarks - the FoV test of Frontend::matchToMap (okvis_frontend/src/Frontend.cpp:1376-1407)
+// okvis_cv needs Eigen, which this image does not have, so the 2x2 / 3x3 Eigen expressions are written out with plain
+// doubles (small fixed-size Eigen products are evaluated coefficient by coefficient; Matrix2d::inverse() is the
+// adjugate scaled by 1/det). PARITY UNPINNED by upstream: the reference has no golden values for these functions.
+#include <cmath>
+#include <cstdint>
+
+namespace {
+
+struct Pinhole {  // layout of okc_pinhole (include/okvis_cuda.h)
+  int width, height;
+  double fu, fv, cu, cv;
+  int distortion;  // 0 none, 1 radial-tangential, 2 equidistant
+  double k[8];
+};
+
+struct KeyPoint { float x, y, size, angle, response; int octave, class_id; };
+
+typedef double M22[2][2];
+
+bool distort(const Pinhole& c, const double u[2], double out[2], M22* Jp) {
+  if (c.distortion == 1) {
+    const double k1_ = c.k[0], k2_ = c.k[1], p1_ = c.k[2], p2_ = c.k[3];
+    const double u0 = u[0], u1 = u[1];
+    const double mx_u = u0 * u0;
+    const double my_u = u1 * u1;
+    const double mxy_u = u0 * u1;
+    const double rho_u = mx_u + my_u;
+    const double rad_dist_u = k1_ * rho_u + k2_ * rho_u * rho_u;
+    out[0] = u0 + u0 * rad_dist_u + 2.0 * p1_ * mxy_u + p2_ * (rho_u + 2.0 * mx_u);
+    out[1] = u1 + u1 * rad_dist_u + 2.0 * p2_ * mxy_u + p1_ * (rho_u + 2.0 * my_u);
+    if (Jp) {
+      M22& J = *Jp;
+      J[0][0] = 1 + rad_dist_u + k1_ * 2.0 * mx_u + k2_ * rho_u * 4 * mx_u + 2.0 * p1_ * u1 + 6 * p2_ * u0;
+      J[1][0] = k1_ * 2.0 * u0 * u1 + k2_ * 4 * rho_u * u0 * u1 + p1_ * 2.0 * u0 + 2.0 * p2_ * u1;
+      J[0][1] = J[1][0];
+      J[1][1] = 1 + rad_dist_u + k1_ * 2.0 * my_u + k2_ * rho_u * 4 * my_u + 6 * p1_ * u1 + 2.0 * p2_ * u0;
+    }
+    return true;
+  }
+  if (c.distortion == 2) {
+    const double k1_ = c.k[0], k2_ = c.k[1], k3_ = c.k[2], k4_ = c.k[3];
+    const double u0 = u[0], u1 = u[1];
+    const double r = std::sqrt(u0 * u0 + u1 * u1);
+    const double theta = std::atan(r);
+    const double theta2 = theta * theta;
+    const double theta4 = theta2 * theta2;
+    const double theta6 = theta4 * theta2;
+    const double theta8 = theta4 * theta4;
+    const double thetad = theta * (1.0 + k1_ * theta2 + k2_ * theta4 + k3_ * theta6 + k4_ * theta8);
+    const double scaling = (r > 1e-8) ? thetad / r : 1.0;
+    out[0] = scaling * u0;
+    out[1] = scaling * u1;
+    if (Jp) {
+      M22& J = *Jp;
+      if (r > 1e-8) {
+        double t2 = u0 * u0;
+        double t3 = u1 * u1;
+        double t4 = t2 + t3;
+        double t6 = std::atan(std::sqrt(t4));
+        double t7 = t6 * t6;
+        double t8 = 1.0 / std::sqrt(t4);
+        double t9 = t7 * t7;
+        double t11 = 1.0 / ((t2 + t3) + 1.0);
+        double t17 = (((k1_ * t7 + k2_ * t9) + k3_ * t7 * t9) + k4_ * (t9 * t9)) + 1.0;
+        double t18 = 1.0 / t4;
+        double t19 = 1.0 / std::sqrt(t4 * t4 * t4);
+        double t20 = t6 * t8 * t17;
+        double t25 = ((k2_ * t6 * t7 * t8 * t11 * u1 * 4.0 + k3_ * t6 * t8 * t9 * t11 * u1 * 6.0) +
+                      k4_ * t6 * t7 * t8 * t9 * t11 * u1 * 8.0) +
+                     k1_ * t6 * t8 * t11 * u1 * 2.0;
+        t4 = ((k2_ * t6 * t7 * t8 * t11 * u0 * 4.0 + k3_ * t6 * t8 * t9 * t11 * u0 * 6.0) +
+              k4_ * t6 * t7 * t8 * t9 * t11 * u0 * 8.0) +
+             k1_ * t6 * t8 * t11 * u0 * 2.0;
+        t7 = t11 * t17 * t18 * u0 * u1;
+        J[0][1] = (t7 + t6 * t8 * t25 * u0) - t6 * t17 * t19 * u0 * u1;
+        J[1][1] = ((t20 - t3 * t6 * t17 * t19) + t3 * t11 * t17 * t18) + t6 * t8 * t25 * u1;
+        J[0][0] = ((t20 - t2 * t6 * t17 * t19) + t2 * t11 * t17 * t18) + t6 * t8 * t4 * u0;
+        J[1][0] = (t7 + t6 * t8 * t4 * u1) - t6 * t17 * t19 * u0 * u1;
+      } else {
+        J[0][0] = J[1][1] = 1.0;
+        J[0][1] = J[1][0] = 0.0;
+      }
+    }
+    return true;
+  }
+  out[0] = u[0];
+  out[1] = u[1];
+  if (Jp) {
+    (*Jp)[0][0] = (*Jp)[1][1] = 1.0;
+    (*Jp)[0][1] = (*Jp)[1][0] = 0.0;
+  }
+  return true;
+}
+
+bool undistort(const Pinhole& c, const double y[2], double x[2]) {
+  if (c.distortion == 0) {
+    x[0] = y[0];
+    x[1] = y[1];
+    return true;
+  }
+  double x_bar[2] = {y[0], y[1]};
+  const int n = c.distortion == 2 ? 20 : 5;
+  bool success = false;
+  for (int i = 0; i < n; i++) {
+    double x_tmp[2];
+    M22 E;
+    distort(c, x_bar, x_tmp, &E);
+    const double e[2] = {y[0] - x_tmp[0], y[1] - x_tmp[1]};
+    M22 E2, inv, M;
+    for (int r = 0; r < 2; ++r)
+      for (int q = 0; q < 2; ++q) E2[r][q] = E[0][r] * E[0][q] + E[1][r] * E[1][q];   // E^T * E
+    const double invdet = 1.0 / (E2[0][0] * E2[1][1] - E2[1][0] * E2[0][1]);
+    inv[0][0] = E2[1][1] * invdet;
+    inv[1][0] = -E2[1][0] * invdet;
+    inv[0][1] = -E2[0][1] * invdet;
+    inv[1][1] = E2[0][0] * invdet;
+    for (int r = 0; r < 2; ++r)
+      for (int q = 0; q < 2; ++q) M[r][q] = inv[r][0] * E[q][0] + inv[r][1] * E[q][1];  // inv * E^T
+    for (int r = 0; r < 2; ++r) x_bar[r] += M[r][0] * e[0] + M[r][1] * e[1];
+    const double chi2 = e[0] * e[0] + e[1] * e[1];
+    if (chi2 < 1e-6) success = true;
+    if (chi2 < 1e-15) {
+      success = true;
+      break;
+    }
+  }
+  x[0] = x_bar[0];
+  x[1] = x_bar[1];
+  return success;
+}
+
+}  // namespace
+
+extern "C" {
+
+int port_back_project(const Pinhole* cam, const KeyPoint* kps, int n, double* e_C, uint8_t* valid) {
+  int ctr = 0;
+  const double one_over_fu = 1.0 / cam->fu, one_over_fv = 1.0 / cam->fv;
+  for (int k = 0; k < n; ++k) {
+    const double p2[2] = {((double)kps[k].x - cam->cu) * one_over_fu, ((double)kps[k].y - cam->cv) * one_over_fv};
+    double und[2];
+    const bool ok = undistort(*cam, p2, und);
+    e_C[3 * k] = und[0];
+    e_C[3 * k + 1] = und[1];
+    e_C[3 * k + 2] = 1.0;
+    valid[k] = ok;
+    ctr += ok;
+  }
+  return ctr;
+}
+
+// status: 0 Successful, 1 OutsideImage, 2 Masked, 3 Behind, 4 Invalid (cameras::ProjectionStatus)
+void port_project_landmarks(const Pinhole* cam, const double* T_CW, const double* hp_W, int n, double reprThreshold,
+                            double* proj_xy, uint8_t* status, uint8_t* visible) {
+  const double maxU = cam->width + reprThreshold, maxV = cam->height + reprThreshold;
+  for (int l = 0; l < n; ++l) {
+    const double* h = hp_W + 4 * l;
+    double p[3];
+    for (int i = 0; i < 3; ++i)
+      p[i] = ((T_CW[3 * i] * h[0] + T_CW[3 * i + 1] * h[1]) + T_CW[3 * i + 2] * h[2]) + T_CW[9 + i] * h[3];
+    if (h[3] < 0)
+      for (int i = 0; i < 3; ++i) p[i] = -p[i];
+    double kp[2] = {0.0, 0.0};
+    int st;
+    if (std::fabs(p[2]) < 1.0e-12) {
+      st = 4;
+    } else {
+      const double rz = 1.0 / p[2];
+      const double und[2] = {p[0] * rz, p[1] * rz};
+      double dist[2];
+      distort(*cam, und, dist, nullptr);
+      kp[0] = cam->fu * dist[0] + cam->cu;
+      kp[1] = cam->fv * dist[1] + cam->cv;
+      if (kp[0] < 0.0 || kp[1] < 0.0 || kp[0] >= cam->width || kp[1] >= cam->height) st = 1;
+      else st = p[2] > 0.0 ? 0 : 3;
+    }
+    bool vis = !(st == 4 || st == 3);
+    if (vis && (kp[0] < -reprThreshold || kp[1] < -reprThreshold || kp[0] > maxU || kp[1] > maxV)) vis = false;
+    proj_xy[2 * l] = kp[0];
+    proj_xy[2 * l + 1] = kp[1];
+    status[l] = (uint8_t)st;
+    visible[l] = vis;
+  }
+}
+
+}  // extern "C"

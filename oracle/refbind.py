@@ -221,6 +221,28 @@ class Port:
         L.port_match_uninit_thread.argtypes = [_i, _i, _vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _vp, _vp, _vp, _d, _vp,
                                                _vp, _vp, _vp, _vp]
 
+    def back_project(self, cam, keypoints):
+        """cam: a ctypes structure with the okc_pinhole layout; keypoints: 28-byte cv::KeyPoint records."""
+        kp = np.ascontiguousarray(keypoints)
+        n = len(kp)
+        e = np.zeros((max(n, 1), 3), np.float64)
+        valid = np.zeros(max(n, 1), np.uint8)
+        self.L.port_back_project.argtypes = [_vp, _vp, _i, _vp, _vp]
+        nv = self.L.port_back_project(C.byref(cam), _ptr(kp), n, _ptr(e), _ptr(valid))
+        return e[:n], valid[:n], int(nv)
+
+    def project_landmarks(self, cam, T_CW, hp_W, repr_threshold):
+        T = np.ascontiguousarray(T_CW, np.float64).reshape(12)
+        h = np.ascontiguousarray(hp_W, np.float64).reshape(-1, 4)
+        n = len(h)
+        proj = np.zeros((max(n, 1), 2), np.float64)
+        status = np.zeros(max(n, 1), np.uint8)
+        vis = np.zeros(max(n, 1), np.uint8)
+        self.L.port_project_landmarks.argtypes = [_vp, _vp, _vp, _i, _d, _vp, _vp, _vp]
+        self.L.port_project_landmarks(C.byref(cam), _ptr(T), _ptr(h), n, float(repr_threshold), _ptr(proj), _ptr(status),
+                                      _ptr(vis))
+        return proj[:n], status[:n], vis[:n]
+
     def hamming_best(self, queries, mp, threshold, index_offset=0, nthreads=1):
         q = np.ascontiguousarray(queries, np.uint8).reshape(-1, 48)
         m = np.ascontiguousarray(mp, np.uint8).reshape(-1, 48)

@@ -1,0 +1,90 @@
+"""GPU parity of the camera geometry next to the path (SURVEY.md 8(f) rows f2 / f1 first half) against the CPU
+restatement in oracle/port/camera.cc. Tolerances: radial-tangential and undistorted cameras use +, -, *, / only ->
+bit-exact; the equidistant model calls atan/sqrt, whose device and glibc versions may differ in the last ulp -> 1e-12.
+Parity with the reference itself is unpinned (Eigen / okvis_cv cannot be built here)."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+EQUI = dict(f=(351.3, 351.5), c=(367.7, 253.8), d=(-0.03696, -0.008917, 0.008912, -0.003785))   # Hilti-like
+
+
+def _cams(mod, syn):
+    e = syn.EUROC["cams"][0]
+    return {
+        "radtan": (mod.Pinhole.make(752, 480, e["f"], e["c"], "radialtangential", e["d"]), 0.0),
+        "equidistant": (mod.Pinhole.make(720, 540, EQUI["f"], EQUI["c"], "equidistant", EQUI["d"]), 1e-12),
+        "none": (mod.Pinhole.make(640, 480, (500.0, 501.0), (320.5, 239.5), "none", ()), 0.0),
+    }
+
+
+def _keypoints(mod, w, h, n, seed):
+    rng = np.random.default_rng(seed)
+    kp = np.zeros(n, mod.KP_DTYPE)
+    kp["x"] = rng.uniform(0, w, n).astype(np.float32)
+    kp["y"] = rng.uniform(0, h, n).astype(np.float32)
+    kp["x"][:4] = (0.0, w - 1.0, 0.0, w - 1.0)          # image corners: strongest distortion
+    kp["y"][:4] = (0.0, 0.0, h - 1.0, h - 1.0)
+    return kp
+
+
+@pytest.mark.parametrize("model", ["radtan", "equidistant", "none"])
+def test_back_project_vs_port(model, mod, ctx, port, syn):
+    cam, tol = _cams(mod, syn)[model]
+    kp = _keypoints(mod, cam.width, cam.height, 3000, 3)
+    if model == "radtan":
+        kp["x"][4], kp["y"][4] = 5000.0, -4000.0         # far outside: Gauss-Newton does not converge in 5 steps
+    e, valid, nv = ctx.back_project(cam, kp)
+    pe, pvalid, pnv = port.back_project(cam, kp)
+    assert np.array_equal(valid, pvalid) and nv == pnv == int(valid.sum())
+    if tol == 0.0:
+        assert e.tobytes() == pe.tobytes()
+    else:
+        assert float(np.abs(e - pe).max()) <= tol
+    assert np.all(e[:, 2] == 1.0) and valid[:4].all()
+    if model == "radtan":
+        assert valid[4] == 0
+    # empty input
+    e0, v0, n0 = ctx.back_project(cam, kp[:0])
+    assert len(e0) == 0 and n0 == 0
+
+
+@pytest.mark.parametrize("model", ["radtan", "equidistant", "none"])
+def test_project_landmarks_vs_port(model, mod, ctx, port, syn):
+    cam, tol = _cams(mod, syn)[model]
+    rng = np.random.default_rng(11)
+    n = 4000
+    hp = np.concatenate([rng.uniform(-6, 6, (n, 2)), rng.uniform(-2, 12, (n, 1)), np.ones((n, 1))], 1)
+    hp[::5] *= rng.uniform(0.2, 3.0, (len(hp[::5]), 1))          # arbitrary positive homogeneous scale
+    hp[1::7] *= -1.0                                             # negative scale: projectHomogeneous negates the head
+    hp[3] = (0.3, 0.2, 0.0, 1.0)                                 # on the camera plane
+    a = 0.3
+    C_ = np.array([[np.cos(a), 0, np.sin(a)], [0, 1, 0], [-np.sin(a), 0, np.cos(a)]])
+    T = np.concatenate([C_.reshape(9), [0.1, -0.05, 0.4]])
+    thr = 3.0 + 0.06 * cam.fu
+    proj, status, vis = ctx.project_landmarks(cam, T, hp, thr)
+    pproj, pstatus, pvis = port.project_landmarks(cam, T, hp, thr)
+    assert np.array_equal(status, pstatus) and np.array_equal(vis, pvis)
+    if tol == 0.0:
+        assert proj.tobytes() == pproj.tobytes()
+    else:
+        assert float(np.abs(proj - pproj).max()) <= tol * 1e3      # pixels: tolerance scaled by the focal length
+    assert set(np.unique(status)) >= {0, 1, 3} and 0 < vis.sum() < n
+    assert vis[status == 3].sum() == 0 and vis[status == 0].all()
+    # a visible landmark's projection back-projects onto its ray
+    ok = np.flatnonzero(status == 0)[:200]
+    kp = np.zeros(len(ok), mod.KP_DTYPE)
+    kp["x"], kp["y"] = proj[ok, 0].astype(np.float32), proj[ok, 1].astype(np.float32)
+    e, valid, _ = ctx.back_project(cam, kp)
+    s = np.where(hp[ok, 3:4] < 0, -1.0, 1.0)
+    pc = s * ((hp[ok, :3] @ C_.T) + T[9:] * hp[ok, 3:4])
+    ray = pc / pc[:, 2:3]
+    assert valid.all() and float(np.abs(e - ray).max()) < 5e-3     # float32 pixel rounding of the keypoint
+
+
+def test_rejects_unknown_distortion(mod, ctx):
+    cam = mod.Pinhole.make(640, 480, (500.0, 500.0), (320.0, 240.0), 3, ())
+    kp = np.zeros(1, mod.KP_DTYPE)
+    with pytest.raises(Exception):
+        ctx.back_project(cam, kp)

@@ -143,3 +143,27 @@ def test_host_pattern_tables_equal_reference_constructor(mod, ref):
     assert np.array_equal(t["long_pairs"], long_pairs)
     assert np.array_equal(t["lut"], ref.lut())
     ext.close()
+
+
+def test_port_camera_geometry_against_numpy_restatement(port, syn, mod):
+    """The oracle's back-projection (oracle/port/camera.cc) against the independent numpy Gauss-Newton of
+    synthetic.camera_maps (radial-tangential): same rays up to normalisation; and distort(undistort(y)) = y."""
+    e = syn.EUROC["cams"][0]
+    W, H = 752, 480
+    cam = mod.Pinhole.make(W, H, e["f"], e["c"], "radialtangential", e["d"])
+    kp = np.zeros(W * 8, mod.KP_DTYPE)
+    ys = np.array([0, 1, 100, 239, 240, 300, 478, 479])
+    kp["x"] = np.tile(np.arange(W, dtype=np.float32), 8)
+    kp["y"] = np.repeat(ys.astype(np.float32), W)
+    rays, valid, nv = port.back_project(cam, kp)
+    assert valid.all() and nv == len(kp)
+    maps, _ = syn.camera_maps(W, H, e["f"], e["c"], e["d"])
+    want = maps[ys].reshape(-1, 3).astype(np.float64)
+    got = rays / np.linalg.norm(rays, axis=1, keepdims=True)
+    assert float(np.abs(got - want).max()) < 1e-6          # the maps are float32
+    # projecting the ray returns the pixel
+    T = np.concatenate([np.eye(3).reshape(9), np.zeros(3)])
+    hp = np.concatenate([rays, np.ones((len(rays), 1))], 1)
+    proj, status, vis = port.project_landmarks(cam, T, hp, 30.0)
+    assert float(np.abs(proj[:, 0] - kp["x"]).max()) < 1e-6 and float(np.abs(proj[:, 1] - kp["y"]).max()) < 1e-6
+    assert vis.all() and set(np.unique(status)) <= {0, 1}   # border pixels may land at -1e-13: OutsideImage, still visible
