@@ -213,6 +213,16 @@ int okc_back_project(okc_context* ctx, const okc_pinhole* cam, const okc_keypoin
 int okc_project_landmarks(okc_context* ctx, const okc_pinhole* cam, const double T_CW[12], const double* hp_W, int n,
                           double repr_threshold, double* proj_xy, uint8_t* status, uint8_t* visible);
 
+/* Keyframe-overlap masks of Frontend::doWeNeedANewKeyframe (okvis_frontend/src/Frontend.cpp:1186-1295), SURVEY 8(f)
+ * row f3: per view (one camera image of one multiframe, width[v] x height[v]) the H/10 x W/10 "detections" mask (a
+ * filled cv::circle of radius int(min(rows, cols) * 0.09) at cv::Point(pt * 0.1) for every keypoint) and "matches"
+ * mask (the same for keypoints with matched[k] != 0: landmarkId != 0 for the current frame, landmarkId in the
+ * current frame's id set for the other frames - decided by the caller), and cv::countNonZero of their AND
+ * (intersection[v]) and OR (uni[v]). Keypoints of view v = keypoints[kp_offset[v] .. kp_offset[v+1]). The caller
+ * sums the counts over the cameras of a multiframe and forms the ratios (:1233, :1280). Host buffers. */
+int okc_keyframe_overlap(okc_context* ctx, int n_views, const int* width, const int* height, const int64_t* kp_offset,
+                         const okc_keypoint* keypoints, const uint8_t* matched, int32_t* intersection, int32_t* uni);
+
 /* ---- Frame pipeline: the per-frame sequence of Frontend::detectAndDescribe followed by Frontend::matchToMap
  * (ThreadedSlam.cpp:676-717 -> Frontend.cpp:204-262, 1335-1536) with every intermediate product left in HBM.
  * The queries of the map match are the camera handle's own descriptors/keypoints of the frame just described,

@@ -98,6 +98,7 @@ def lib():
         L.okc_debug_set_match_prefix.argtypes = [i]
         L.okc_debug_set_select_wave.argtypes = [i]
         L.okc_back_project.argtypes = [vp, vp, vp, i, vp, vp, C.POINTER(i)]
+        L.okc_keyframe_overlap.argtypes = [vp, i, vp, vp, vp, vp, vp, vp, vp]
         L.okc_project_landmarks.argtypes = [vp, vp, vp, vp, i, C.c_double, vp, vp, vp]
         L.okc_debug_set_match_binned.argtypes = [i]
         L.okc_debug_batch_counter.argtypes = [vp, i, i, C.POINTER(i)]
@@ -189,6 +190,20 @@ class Context:
         _check(lib().okc_project_landmarks(self.h, C.byref(cam), _p(T), _p(h), n, float(repr_threshold), _p(proj),
                                            _p(status), _p(vis)), "okc_project_landmarks")
         return proj[:n], status[:n], vis[:n]
+
+    def keyframe_overlap(self, widths, heights, kp_offset, keypoints, matched):
+        """Frontend::doWeNeedANewKeyframe masks: (intersection[v], union[v]) pixel counts per view."""
+        w = np.ascontiguousarray(widths, np.int32)
+        h = np.ascontiguousarray(heights, np.int32)
+        off = np.ascontiguousarray(kp_offset, np.int64)
+        kp = np.ascontiguousarray(keypoints, KP_DTYPE)
+        m = np.ascontiguousarray(matched, np.uint8)
+        n = len(w)
+        inter = np.zeros(max(n, 1), np.int32)
+        uni = np.zeros(max(n, 1), np.int32)
+        _check(lib().okc_keyframe_overlap(self.h, n, _p(w), _p(h), _p(off), _p(kp), _p(m), _p(inter), _p(uni)),
+               "okc_keyframe_overlap")
+        return inter[:n], uni[:n]
 
     # -- brute force (Frontend::verifyRecognisedPlace, Frontend.cpp:316-345; the 10k x 1M sweep) --
     def match_batched(self, queries, mp, threshold=60, index_offset=0):

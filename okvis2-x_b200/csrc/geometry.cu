@@ -303,3 +303,126 @@ int okc_project_landmarks(okc_context* ctx, const okc_pinhole* cam, const double
 }
 
 }  // extern "C"
+
+// ----------------------------------------------------------------------------------------------
+// Keyframe-overlap rasterisation of Frontend::doWeNeedANewKeyframe (okvis_frontend/src/Frontend.cpp:1186-1295):
+// per (frame, camera) two H/10 x W/10 masks - every keypoint / every matched keypoint drawn as a filled circle of
+// radius int(min(rows, cols) * 0.09) at cv::Point(keypoint.pt * 0.1) - and the pixel counts of their AND and OR.
+// cv::circle(..., cv::FILLED) fills, for each row dy, the columns |dx| <= floor(sqrt(r^2 - dy^2)), clipped to the
+// image (pinned against cv2 4.13 goldens, tests/golden/overlap_discs.npz). One CTA per view, masks in shared memory;
+// the stores are idempotent (255), so overlapping circles need no ordering.
+// ----------------------------------------------------------------------------------------------
+namespace okc {
+
+constexpr int kOverlapThreads = 256;
+
+__global__ void __launch_bounds__(kOverlapThreads)
+keyframe_overlap_kernel(const int* __restrict__ width, const int* __restrict__ height,
+                        const long long* __restrict__ kpOffset, const okc_keypoint* __restrict__ kps,
+                        const uint8_t* __restrict__ matched, int* __restrict__ interCount, int* __restrict__ unionCount) {
+  extern __shared__ uint8_t masks[];   // detections | matches
+  __shared__ int s_inter, s_union;
+  const int view = blockIdx.x;
+  const int rows = height[view] / 10, cols = width[view] / 10;
+  const int cells = rows * cols;
+  uint8_t* det = masks;
+  uint8_t* mat = masks + cells;
+  for (int i = threadIdx.x; i < 2 * cells; i += kOverlapThreads) masks[i] = 0;
+  if (threadIdx.x == 0) s_inter = s_union = 0;
+  __syncthreads();
+  const int r = (int)((double)(rows < cols ? rows : cols) * 0.09);
+  const long long k0 = kpOffset[view], k1 = kpOffset[view + 1];
+  for (long long k = k0 + threadIdx.x; k < k1; k += kOverlapThreads) {
+    // keypoint.pt * 0.1: Point2f * double -> float; Point2f -> cv::Point rounds half to even (cvRound)
+    const int cx = __float2int_rn((float)((double)kps[k].x * 0.1));
+    const int cy = __float2int_rn((float)((double)kps[k].y * 0.1));
+    const bool m = matched[k] != 0;
+    for (int dy = -r; dy <= r; ++dy) {
+      const int y = cy + dy;
+      if (y < 0 || y >= rows) continue;
+      const int hw = (int)sqrt((double)(r * r - dy * dy));
+      int xa = cx - hw, xb = cx + hw;
+      xa = xa < 0 ? 0 : xa;
+      xb = xb >= cols ? cols - 1 : xb;
+      for (int x = xa; x <= xb; ++x) {
+        det[y * cols + x] = 255;
+        if (m) mat[y * cols + x] = 255;
+      }
+    }
+  }
+  __syncthreads();
+  int ci = 0, cu = 0;
+  for (int i = threadIdx.x; i < cells; i += kOverlapThreads) {
+    ci += (det[i] & mat[i]) != 0;
+    cu += (det[i] | mat[i]) != 0;
+  }
+  for (int d = 16; d > 0; d >>= 1) {
+    ci += __shfl_down_sync(0xffffffffu, ci, d);
+    cu += __shfl_down_sync(0xffffffffu, cu, d);
+  }
+  if ((threadIdx.x & 31) == 0) {
+    atomicAdd(&s_inter, ci);
+    atomicAdd(&s_union, cu);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    interCount[view] = s_inter;
+    unionCount[view] = s_union;
+  }
+}
+
+}  // namespace okc
+
+extern "C" int okc_keyframe_overlap(okc_context* ctx, int n_views, const int* width, const int* height,
+                                    const int64_t* kp_offset, const okc_keypoint* keypoints, const uint8_t* matched,
+                                    int32_t* intersection, int32_t* uni) {
+  if (!ctx || n_views < 0 || (n_views > 0 && (!width || !height || !kp_offset || !intersection || !uni)))
+    return OKC_ERR_INVALID;
+  if (n_views == 0) return OKC_OK;
+  const int64_t nk = kp_offset[n_views];
+  if (kp_offset[0] != 0 || nk < 0 || (nk > 0 && (!keypoints || !matched))) return OKC_ERR_INVALID;
+  size_t smem = 0;
+  for (int v = 0; v < n_views; ++v) {
+    if (width[v] < 10 || height[v] < 10 || kp_offset[v + 1] < kp_offset[v]) return OKC_ERR_INVALID;
+    const size_t need = 2 * (size_t)(width[v] / 10) * (size_t)(height[v] / 10);
+    smem = need > smem ? need : smem;
+  }
+  if (smem > 200 * 1024) {
+    okc::set_error("okc_keyframe_overlap: image too large for the shared-memory masks");
+    return OKC_ERR_INVALID;
+  }
+  OKC_CUDA_TRY(cudaSetDevice(okc_context_device(ctx)));
+  const size_t oW = 0, oH = oW + (size_t)n_views * 4, oO = (oH + (size_t)n_views * 4 + 7) & ~(size_t)7,
+               oK = oO + (size_t)(n_views + 1) * 8, oM = oK + (size_t)nk * sizeof(okc_keypoint),
+               oI = (oM + (size_t)nk + 7) & ~(size_t)7, oU = oI + (size_t)n_views * 4, total = oU + (size_t)n_views * 4;
+  uint8_t* d = nullptr;
+  OKC_CUDA_TRY(cudaMalloc(&d, total));
+  int rc = OKC_OK;
+  auto fail = [&](cudaError_t e, const char* what) {
+    if (e != cudaSuccess && rc == OKC_OK) {
+      okc::set_error("%s failed: %s", what, cudaGetErrorString(e));
+      rc = OKC_ERR_CUDA;
+    }
+  };
+  fail(cudaMemcpy(d + oW, width, (size_t)n_views * 4, cudaMemcpyHostToDevice), "cudaMemcpy");
+  fail(cudaMemcpy(d + oH, height, (size_t)n_views * 4, cudaMemcpyHostToDevice), "cudaMemcpy");
+  fail(cudaMemcpy(d + oO, kp_offset, (size_t)(n_views + 1) * 8, cudaMemcpyHostToDevice), "cudaMemcpy");
+  if (nk > 0) {
+    fail(cudaMemcpy(d + oK, keypoints, (size_t)nk * sizeof(okc_keypoint), cudaMemcpyHostToDevice), "cudaMemcpy");
+    fail(cudaMemcpy(d + oM, matched, (size_t)nk, cudaMemcpyHostToDevice), "cudaMemcpy");
+  }
+  if (rc == OKC_OK) {
+    if (smem > 48 * 1024)
+      fail(cudaFuncSetAttribute(okc::keyframe_overlap_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
+           "cudaFuncSetAttribute");
+    okc::keyframe_overlap_kernel<<<n_views, okc::kOverlapThreads, smem>>>(
+        reinterpret_cast<const int*>(d + oW), reinterpret_cast<const int*>(d + oH),
+        reinterpret_cast<const long long*>(d + oO), reinterpret_cast<const okc_keypoint*>(d + oK), d + oM,
+        reinterpret_cast<int*>(d + oI), reinterpret_cast<int*>(d + oU));
+    fail(cudaGetLastError(), "keyframe_overlap_kernel");
+    fail(cudaMemcpy(intersection, d + oI, (size_t)n_views * 4, cudaMemcpyDeviceToHost), "cudaMemcpy");
+    fail(cudaMemcpy(uni, d + oU, (size_t)n_views * 4, cudaMemcpyDeviceToHost), "cudaMemcpy");
+  }
+  cudaFree(d);
+  return rc;
+}

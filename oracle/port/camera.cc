@@ -190,3 +190,40 @@ void port_project_landmarks(const Pinhole* cam, const double* T_CW, const double
 }
 
 }  // extern "C"
+
+// Keyframe-overlap masks of Frontend::doWeNeedANewKeyframe (okvis_frontend/src/Frontend.cpp:1199-1231, 1255-1278):
+// cv::circle(mask, keypoint.pt * 0.1, int(radius), 255, cv::FILLED) restated as the integer disc OpenCV draws
+// (pinned against cv2 4.13 in tests/golden/overlap_goldens.npz), cv::bitwise_and / bitwise_or / countNonZero.
+#include <cstring>
+#include <vector>
+extern "C" void port_keyframe_overlap(int n_views, const int* width, const int* height, const int64_t* kp_offset,
+                                      const KeyPoint* kps, const uint8_t* matched, int32_t* inter, int32_t* uni) {
+  for (int v = 0; v < n_views; ++v) {
+    const int rows = height[v] / 10, cols = width[v] / 10;
+    std::vector<uint8_t> det((size_t)rows * cols, 0), mat((size_t)rows * cols, 0);
+    const double radius = double(rows < cols ? rows : cols) * 0.09;
+    const int r = int(radius);
+    for (int64_t k = kp_offset[v]; k < kp_offset[v + 1]; ++k) {
+      const float fx = float(double(kps[k].x) * 0.1), fy = float(double(kps[k].y) * 0.1);   // Point2f * double
+      const int cx = (int)lrintf(fx), cy = (int)lrintf(fy);                                 // cvRound
+      for (int dy = -r; dy <= r; ++dy) {
+        const int y = cy + dy;
+        if (y < 0 || y >= rows) continue;
+        int hw = 0;
+        while ((hw + 1) * (hw + 1) + dy * dy <= r * r) ++hw;
+        for (int x = cx - hw; x <= cx + hw; ++x) {
+          if (x < 0 || x >= cols) continue;
+          det[(size_t)y * cols + x] = 255;
+          if (matched[k]) mat[(size_t)y * cols + x] = 255;
+        }
+      }
+    }
+    int ci = 0, cu = 0;
+    for (size_t i = 0; i < det.size(); ++i) {
+      ci += (det[i] & mat[i]) != 0;
+      cu += (det[i] | mat[i]) != 0;
+    }
+    inter[v] = ci;
+    uni[v] = cu;
+  }
+}

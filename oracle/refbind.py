@@ -243,6 +243,18 @@ class Port:
                                       _ptr(vis))
         return proj[:n], status[:n], vis[:n]
 
+    def keyframe_overlap(self, widths, heights, kp_offset, keypoints, matched):
+        w = np.ascontiguousarray(widths, np.int32)
+        h = np.ascontiguousarray(heights, np.int32)
+        off = np.ascontiguousarray(kp_offset, np.int64)
+        kp = np.ascontiguousarray(keypoints)
+        m = np.ascontiguousarray(matched, np.uint8)
+        inter = np.zeros(max(len(w), 1), np.int32)
+        uni = np.zeros(max(len(w), 1), np.int32)
+        self.L.port_keyframe_overlap.argtypes = [_i, _vp, _vp, _vp, _vp, _vp, _vp, _vp]
+        self.L.port_keyframe_overlap(len(w), _ptr(w), _ptr(h), _ptr(off), _ptr(kp), _ptr(m), _ptr(inter), _ptr(uni))
+        return inter[:len(w)], uni[:len(w)]
+
     def hamming_best(self, queries, mp, threshold, index_offset=0, nthreads=1):
         q = np.ascontiguousarray(queries, np.uint8).reshape(-1, 48)
         m = np.ascontiguousarray(mp, np.uint8).reshape(-1, 48)

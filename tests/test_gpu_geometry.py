@@ -88,3 +88,27 @@ def test_rejects_unknown_distortion(mod, ctx):
     kp = np.zeros(1, mod.KP_DTYPE)
     with pytest.raises(Exception):
         ctx.back_project(cam, kp)
+
+
+def test_keyframe_overlap_vs_goldens_and_port(mod, ctx, port):
+    """Frontend::doWeNeedANewKeyframe masks: cv2-drawn goldens, then random views against the port."""
+    import os
+    from conftest import GOLDEN
+    g = np.load(os.path.join(GOLDEN, "overlap_goldens.npz"))
+    inter, uni = ctx.keyframe_overlap(g["width"], g["height"], g["kp_offset"], g["keypoints"], g["matched"])
+    assert np.array_equal(inter, g["intersection"]) and np.array_equal(uni, g["union"])
+    rng = np.random.default_rng(5)
+    w, h, off, kps, ms = [], [], [0], [], []
+    for v in range(40):
+        W, H = int(rng.integers(100, 1500)), int(rng.integers(100, 1100))
+        n = int(rng.integers(0, 900))
+        kp = np.zeros(n, mod.KP_DTYPE)
+        kp["x"] = rng.uniform(-5, W + 5, n).astype(np.float32)     # slightly outside too: clipped discs
+        kp["y"] = rng.uniform(-5, H + 5, n).astype(np.float32)
+        w.append(W); h.append(H); off.append(off[-1] + n); kps.append(kp)
+        ms.append((rng.uniform(0, 1, n) < rng.uniform(0, 1)).astype(np.uint8))
+    args = (w, h, off, np.concatenate(kps), np.concatenate(ms))
+    gi, gu = ctx.keyframe_overlap(*args)
+    pi, pu = port.keyframe_overlap(*args)
+    assert np.array_equal(gi, pi) and np.array_equal(gu, pu)
+    assert np.all(gi <= gu)

@@ -167,3 +167,11 @@ def test_port_camera_geometry_against_numpy_restatement(port, syn, mod):
     proj, status, vis = port.project_landmarks(cam, T, hp, 30.0)
     assert float(np.abs(proj[:, 0] - kp["x"]).max()) < 1e-6 and float(np.abs(proj[:, 1] - kp["y"]).max()) < 1e-6
     assert vis.all() and set(np.unique(status)) <= {0, 1}   # border pixels may land at -1e-13: OutsideImage, still visible
+
+
+def test_port_keyframe_overlap_equals_cv2_goldens(port):
+    """oracle/port keyframe-overlap masks against counts drawn with the real cv2.circle / countNonZero
+    (tests/golden/make_overlap_golden.py, OpenCV 4.13)."""
+    g = np.load(os.path.join(GOLDEN, "overlap_goldens.npz"))
+    inter, uni = port.keyframe_overlap(g["width"], g["height"], g["kp_offset"], g["keypoints"], g["matched"])
+    assert np.array_equal(inter, g["intersection"]) and np.array_equal(uni, g["union"])
