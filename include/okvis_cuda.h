@@ -223,6 +223,33 @@ int okc_project_landmarks(okc_context* ctx, const okc_pinhole* cam, const double
 int okc_keyframe_overlap(okc_context* ctx, int n_views, const int* width, const int* height, const int64_t* kp_offset,
                          const okc_keypoint* keypoints, const uint8_t* matched, int32_t* intersection, int32_t* uni);
 
+/* Landmark preparation of Frontend::matchToMap, second half (Frontend.cpp:1409-1500), SURVEY 8(f) row f1: for every
+ * landmark with visible[l] != 0 (okc_project_landmarks) walk its observations obs_offset[l] .. obs_offset[l+1] in the
+ * order given (the reference iterates the observation set in reverse: newest first), set is3d[l] (:1433-1439), drop
+ * observations beyond 0.6 rad viewpoint change or 50 % scale change (not in loop-closure mode), keep the best three by
+ * score with the reference's replace-the-worst-slot rule, and pack the pool swept by okc_match_to_map /
+ * okc_match_to_map_uninitialised: rows[l] = o + 1 rows per visible landmark (landmarks ascending, 0 for invisible
+ * ones), *nm rows in total, per row the 48-byte descriptor, owner (landmark index), e_W = C_WC_old * e_C.normalized(),
+ * r_W = camera centre, filled (0: the slot was never written - the reference leaves such a row uninitialised, here it
+ * is zero) and row_obs (index of the observation inside the landmark's list, -1). Output capacity: 3 rows per landmark.
+ * An observation refers to view obs_view (one camera image of an older multiframe: pose, rows row0 .. of the shared
+ * descriptor / back-projection pools) and keypoint obs_kp inside it. focal_sum = focalLengthU() + focalLengthV()
+ * (:1361-1363). Host buffers. */
+typedef struct okc_landmark_views {
+  int n_views;
+  const double* C_WC;   /* n_views x 9, row-major rotation of T_WC_old = T_WS_old * T_SC */
+  const double* r_WC;   /* n_views x 3 */
+  const int64_t* row0;  /* n_views: first pool row of the view (ascending) */
+  const uint8_t* desc;  /* n_rows x 48 */
+  const double* e_C;    /* n_rows x 3: Frame::backProjections_ (okc_back_project) */
+  int64_t n_rows;
+} okc_landmark_views;
+int okc_prepare_landmarks(okc_context* ctx, const okc_landmark_views* views, int n_landmarks, const double* hp_W,
+                          const double* quality, const uint8_t* visible, const int64_t* obs_offset,
+                          const int32_t* obs_view, const int32_t* obs_kp, const double r_WC1[3], double focal_sum,
+                          int loop_closure, uint8_t* is3d, int32_t* rows, int32_t* nm, uint8_t* pool, int32_t* owner,
+                          double* e_W, double* r_W, uint8_t* filled, int32_t* row_obs);
+
 /* ---- Frame pipeline: the per-frame sequence of Frontend::detectAndDescribe followed by Frontend::matchToMap
  * (ThreadedSlam.cpp:676-717 -> Frontend.cpp:204-262, 1335-1536) with every intermediate product left in HBM.
  * The queries of the map match are the camera handle's own descriptors/keypoints of the frame just described,

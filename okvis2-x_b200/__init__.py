@@ -61,6 +61,11 @@ class Pinhole(C.Structure):
         return p
 
 
+class LandmarkViews(C.Structure):
+    _fields_ = [("n_views", C.c_int), ("C_WC", C.c_void_p), ("r_WC", C.c_void_p), ("row0", C.c_void_p),
+                ("desc", C.c_void_p), ("e_C", C.c_void_p), ("n_rows", C.c_int64)]
+
+
 class DescribeParams(C.Structure):
     _fields_ = [("rotation_invariant", C.c_int), ("scale_invariant", C.c_int), ("extraction_direction", C.c_float * 3)]
 
@@ -99,6 +104,8 @@ def lib():
         L.okc_debug_set_select_wave.argtypes = [i]
         L.okc_back_project.argtypes = [vp, vp, vp, i, vp, vp, C.POINTER(i)]
         L.okc_keyframe_overlap.argtypes = [vp, i, vp, vp, vp, vp, vp, vp, vp]
+        L.okc_prepare_landmarks.argtypes = [vp, vp, i, vp, vp, vp, vp, vp, vp, vp, C.c_double, i, vp, vp, C.POINTER(i), vp,
+                                            vp, vp, vp, vp, vp]
         L.okc_project_landmarks.argtypes = [vp, vp, vp, vp, i, C.c_double, vp, vp, vp]
         L.okc_debug_set_match_binned.argtypes = [i]
         L.okc_debug_batch_counter.argtypes = [vp, i, i, C.POINTER(i)]
@@ -190,6 +197,39 @@ class Context:
         _check(lib().okc_project_landmarks(self.h, C.byref(cam), _p(T), _p(h), n, float(repr_threshold), _p(proj),
                                            _p(status), _p(vis)), "okc_project_landmarks")
         return proj[:n], status[:n], vis[:n]
+
+    def prepare_landmarks(self, views, hp_W, quality, visible, obs_offset, obs_view, obs_kp, r_WC1, focal_sum,
+                          loop_closure=False):
+        """views: dict(C_WC [V,9], r_WC [V,3], row0 [V], desc [N,48], e_C [N,3]). Returns dict(is3d, rows, nm, pool,
+        owner, e_W, r_W, filled, row_obs) (Frontend.cpp:1409-1500)."""
+        Cw = np.ascontiguousarray(views["C_WC"], np.float64).reshape(-1, 9)
+        rw = np.ascontiguousarray(views["r_WC"], np.float64).reshape(-1, 3)
+        row0 = np.ascontiguousarray(views["row0"], np.int64)
+        desc = np.ascontiguousarray(views["desc"], np.uint8).reshape(-1, 48)
+        eC = np.ascontiguousarray(views["e_C"], np.float64).reshape(-1, 3)
+        lv = LandmarkViews(len(Cw), Cw.ctypes.data, rw.ctypes.data, row0.ctypes.data, desc.ctypes.data, eC.ctypes.data,
+                           len(desc))
+        hp = np.ascontiguousarray(hp_W, np.float64).reshape(-1, 4)
+        L = len(hp)
+        q = np.ascontiguousarray(quality, np.float64)
+        vis = np.ascontiguousarray(visible, np.uint8)
+        off = np.ascontiguousarray(obs_offset, np.int64)
+        ov = np.ascontiguousarray(obs_view, np.int32)
+        ok = np.ascontiguousarray(obs_kp, np.int32)
+        r1 = np.ascontiguousarray(r_WC1, np.float64).reshape(3)
+        cap = max(3 * L, 1)
+        out = dict(is3d=np.zeros(max(L, 1), np.uint8), rows=np.zeros(max(L, 1), np.int32), pool=np.zeros((cap, 48), np.uint8),
+                   owner=np.zeros(cap, np.int32), e_W=np.zeros((cap, 3)), r_W=np.zeros((cap, 3)),
+                   filled=np.zeros(cap, np.uint8), row_obs=np.zeros(cap, np.int32))
+        nm = C.c_int(0)
+        _check(lib().okc_prepare_landmarks(self.h, C.byref(lv), L, _p(hp), _p(q), _p(vis), _p(off), _p(ov), _p(ok), _p(r1),
+                                           float(focal_sum), int(bool(loop_closure)), _p(out["is3d"]), _p(out["rows"]),
+                                           C.byref(nm), _p(out["pool"]), _p(out["owner"]), _p(out["e_W"]), _p(out["r_W"]),
+                                           _p(out["filled"]), _p(out["row_obs"])), "okc_prepare_landmarks")
+        n = nm.value
+        res = {k: (v[:L] if k in ("is3d", "rows") else v[:n]) for k, v in out.items()}
+        res["nm"] = n
+        return res
 
     def keyframe_overlap(self, widths, heights, kp_offset, keypoints, matched):
         """Frontend::doWeNeedANewKeyframe masks: (intersection[v], union[v]) pixel counts per view."""

@@ -426,3 +426,286 @@ extern "C" int okc_keyframe_overlap(okc_context* ctx, int n_views, const int* wi
   cudaFree(d);
   return rc;
 }
+
+// ----------------------------------------------------------------------------------------------
+// Landmark preparation of Frontend::matchToMap, second half (okvis_frontend/src/Frontend.cpp:1409-1500, SURVEY 8(f)
+// row f1): per visible landmark walk its observations (newest first), decide is3d (:1433-1439), drop observations
+// with more than 0.6 rad viewpoint change or 50 % scale change (:1442-1453), keep the best 3 by
+// score = 0.5 * (acos(cosViewpointChange) / 0.6 + scaleChange / 0.5) with the reference's "replace the worst slot"
+// rule (:1455-1487), and pack the kept descriptor rows, world rays and camera centres into the pool that
+// matchToMapByThread / matchToMapByThreadUnitialised sweep (rows of a landmark contiguous, landmarks ascending).
+// One thread per landmark; Eigen's 3-vector expressions written out ((x0 y0 + x1 y1) + x2 y2, normalized() = v /
+// sqrt(v.v) when v.v > 0). acos / cos come from the device math library: scores can differ from glibc's in the last
+// ulp, which matters only for exact ties between observation scores.
+// ----------------------------------------------------------------------------------------------
+namespace okc {
+
+struct PrepareArgs {
+  const double* hp_W;          // L x 4
+  const double* quality;       // L
+  const uint8_t* visible;      // L (okc_project_landmarks)
+  const long long* obs_offset; // L + 1
+  const int* obs_view;         // per observation: view (frame, camera) index, in the reference's iteration order
+  const int* obs_kp;           // per observation: keypoint index inside the view
+  const double* view_C;        // V x 9, T_WC_old.C() row-major
+  const double* view_r;        // V x 3, T_WC_old.r()
+  const long long* view_row0;  // V: first row of the view in the descriptor / back-projection pools
+  const uint8_t* desc;         // N x 48
+  const double* e_C;           // N x 3 (Frame::backProjections_)
+  double r_WC1[3];             // T_WC1.r() of the camera being matched
+  double focal_sum;            // focalLengthU() + focalLengthV() (Frontend.cpp:1361-1363)
+  int loop_closure;            // loopClosureLandmarksToUseExclusively != nullptr
+  int L;
+  // per landmark, 3 slots
+  uint8_t* is3d;
+  int* rows;                   // o + 1 for visible landmarks, 0 otherwise
+  int* slot_obs;               // L x 3: observation index that filled the slot (-1: never written)
+};
+
+__device__ __forceinline__ double dot3(const double a[3], const double b[3]) { return (a[0] * b[0] + a[1] * b[1]) + a[2] * b[2]; }
+__device__ __forceinline__ void normalized3(const double v[3], double o[3]) {
+  const double n2 = dot3(v, v);
+  if (n2 > 0.0) {
+    const double n = sqrt(n2);
+    o[0] = v[0] / n;
+    o[1] = v[1] / n;
+    o[2] = v[2] / n;
+  } else {
+    o[0] = v[0];
+    o[1] = v[1];
+    o[2] = v[2];
+  }
+}
+
+__global__ void prune_observations_kernel(PrepareArgs a) {
+  const int l = blockIdx.x * blockDim.x + threadIdx.x;
+  if (l >= a.L) return;
+  int* so = a.slot_obs + 3 * l;
+  so[0] = so[1] = so[2] = -1;
+  a.is3d[l] = 0;
+  a.rows[l] = 0;
+  if (!a.visible[l]) return;
+  const double* hp = a.hp_W + 4 * l;
+  const double p_W[3] = {hp[0] / hp[3], hp[1] / hp[3], hp[2] / hp[3]};
+  const double r_W[3] = {p_W[0] - a.r_WC1[0], p_W[1] - a.r_WC1[1], p_W[2] - a.r_WC1[2]};
+  double e_W[3];
+  normalized3(r_W, e_W);
+  const double rn = sqrt(dot3(r_W, r_W));
+  const double r = rn > 0.01 ? rn : 0.01;   // std::max(0.01, r_W.norm())
+  const double quality = a.quality[l];
+  const double cos06 = cos(0.6), cos3d = cos(10.0 / a.focal_sum);
+  double best[3] = {1.0, 1.0, 1.0};
+  bool is3d = false;
+  int o = 0;
+  for (long long i = a.obs_offset[l]; i < a.obs_offset[l + 1]; ++i) {
+    const int v = a.obs_view[i];
+    const double* ro = a.view_r + 3 * v;
+    const double r_W_old[3] = {p_W[0] - ro[0], p_W[1] - ro[1], p_W[2] - ro[2]};
+    if (!is3d) {
+      const double s = 0.2 / a.focal_sum / quality;
+      const double r_close[3] = {r_W[0] - s * r_W_old[0], r_W[1] - s * r_W_old[1], r_W[2] - s * r_W_old[2]};
+      double n1[3], n2[3];
+      normalized3(r_W, n1);
+      normalized3(r_close, n2);
+      if (dot3(n1, n2) > cos3d) is3d = true;
+    }
+    double eo[3];
+    normalized3(r_W_old, eo);
+    const double cosV = dot3(e_W, eo);
+    if (cosV < cos06 && !a.loop_closure) continue;
+    const double scaleChange = fabs(r - sqrt(dot3(r_W_old, r_W_old))) / r;
+    if (scaleChange > 0.5 && !a.loop_closure) continue;
+    const double score = 0.5 * (acos(cosV) / 0.6 + scaleChange / 0.5);
+    double worst = 0.0;
+    int worstIdx = 0;
+    for (int n = 0; n < 3; ++n) {
+      if (best[n] > worst) {
+        worst = best[n];
+        worstIdx = n;
+      }
+    }
+    if (score < best[worstIdx]) {
+      so[worstIdx] = (int)(i - a.obs_offset[l]);
+      o = o > worstIdx ? o : worstIdx;
+      best[worstIdx] = score;
+    }
+  }
+  a.is3d[l] = is3d ? 1 : 0;
+  a.rows[l] = o + 1;
+}
+
+// exclusive scan of rows[] -> row_offset[L + 1] (one block; L is a few thousand)
+__global__ void __launch_bounds__(1024) scan_rows_kernel(const int* __restrict__ rows, int L, int* __restrict__ offset) {
+  __shared__ int s_part[1024];
+  const int tid = threadIdx.x;
+  const int per = (L + 1023) / 1024;
+  const int b = tid * per, e = min(L, b + per);
+  int sum = 0;
+  for (int i = b; i < e; ++i) sum += rows[i];
+  s_part[tid] = sum;
+  __syncthreads();
+  for (int d = 1; d < 1024; d <<= 1) {
+    const int t = tid >= d ? s_part[tid - d] : 0;
+    __syncthreads();
+    s_part[tid] += t;
+    __syncthreads();
+  }
+  int run = s_part[tid] - sum;
+  for (int i = b; i < e; ++i) {
+    offset[i] = run;
+    run += rows[i];
+  }
+  if (tid == 1023) offset[L] = s_part[1023];
+}
+
+// pool rows: descriptor, owner (landmark index), e_W = C_old * e_C.normalized(), r_W = r_old, filled flag
+__global__ void pack_pool_kernel(PrepareArgs a, const int* __restrict__ offset, uint8_t* __restrict__ pool,
+                                 int* __restrict__ owner, double* __restrict__ e_W, double* __restrict__ r_W,
+                                 uint8_t* __restrict__ filled, int* __restrict__ row_obs) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  const int l = t / 3, n = t - 3 * l;
+  if (l >= a.L || n >= a.rows[l]) return;
+  const int row = offset[l] + n;
+  const int so = a.slot_obs[3 * l + n];
+  owner[row] = l;
+  filled[row] = so >= 0;
+  row_obs[row] = so;
+  uint4* dst = reinterpret_cast<uint4*>(pool) + (size_t)row * 3;
+  if (so < 0) {   // the reference leaves such a row uninitialised (cv::Mat / Eigen resize); zeros here
+    dst[0] = dst[1] = dst[2] = make_uint4(0, 0, 0, 0);
+    for (int i = 0; i < 3; ++i) e_W[3 * row + i] = r_W[3 * row + i] = 0.0;
+    return;
+  }
+  const long long i = a.obs_offset[l] + so;
+  const int v = a.obs_view[i];
+  const long long src = a.view_row0[v] + a.obs_kp[i];
+  const uint4* s4 = reinterpret_cast<const uint4*>(a.desc) + (size_t)src * 3;
+  dst[0] = s4[0];
+  dst[1] = s4[1];
+  dst[2] = s4[2];
+  const double ec[3] = {a.e_C[3 * src], a.e_C[3 * src + 1], a.e_C[3 * src + 2]};
+  double en[3];
+  normalized3(ec, en);
+  const double* C = a.view_C + 9 * v;
+  for (int r = 0; r < 3; ++r) {
+    e_W[3 * row + r] = (C[3 * r] * en[0] + C[3 * r + 1] * en[1]) + C[3 * r + 2] * en[2];
+    r_W[3 * row + r] = a.view_r[3 * v + r];
+  }
+}
+
+}  // namespace okc
+
+extern "C" int okc_prepare_landmarks(okc_context* ctx, const okc_landmark_views* views, int n_landmarks,
+                                     const double* hp_W, const double* quality, const uint8_t* visible,
+                                     const int64_t* obs_offset, const int32_t* obs_view, const int32_t* obs_kp,
+                                     const double r_WC1[3], double focal_sum, int loop_closure, uint8_t* is3d,
+                                     int32_t* rows, int32_t* nm, uint8_t* pool, int32_t* owner, double* e_W,
+                                     double* r_W, uint8_t* filled, int32_t* row_obs) {
+  const int L = n_landmarks;
+  if (!ctx || !views || L < 0 || !r_WC1 || !nm) return OKC_ERR_INVALID;
+  *nm = 0;
+  if (L == 0) return OKC_OK;
+  if (!hp_W || !quality || !visible || !obs_offset || !is3d || !rows || !pool || !owner || !e_W || !r_W || !filled ||
+      !row_obs || views->n_views < 0 || views->n_rows < 0)
+    return OKC_ERR_INVALID;
+  const int64_t nObs = obs_offset[L];
+  if (obs_offset[0] != 0 || nObs < 0 || (nObs > 0 && (!obs_view || !obs_kp))) return OKC_ERR_INVALID;
+  for (int l = 0; l < L; ++l)
+    if (obs_offset[l + 1] < obs_offset[l]) return OKC_ERR_INVALID;
+  const int V = views->n_views;
+  for (int64_t i = 0; i < nObs; ++i) {
+    const int v = obs_view[i];
+    if (v < 0 || v >= V) return OKC_ERR_INVALID;
+    const int64_t end = v + 1 < V ? views->row0[v + 1] : views->n_rows;
+    if (obs_kp[i] < 0 || views->row0[v] + obs_kp[i] >= end) {
+      okc::set_error("okc_prepare_landmarks: observation %lld points outside its view", (long long)i);
+      return OKC_ERR_INVALID;
+    }
+  }
+  OKC_CUDA_TRY(cudaSetDevice(okc_context_device(ctx)));
+  // one device block: inputs, then outputs
+  size_t off = 0;
+  auto take = [&](size_t bytes) {
+    const size_t o = off;
+    off = (off + bytes + 255) & ~(size_t)255;
+    return o;
+  };
+  const size_t N = (size_t)views->n_rows;
+  const size_t oHp = take((size_t)L * 32), oQ = take((size_t)L * 8), oVis = take((size_t)L), oOff = take((size_t)(L + 1) * 8),
+               oOv = take((size_t)nObs * 4), oOk = take((size_t)nObs * 4), oC = take((size_t)V * 72),
+               oR = take((size_t)V * 24), oRow0 = take((size_t)V * 8), oDesc = take(N * 48), oEc = take(N * 24),
+               oIs3d = take((size_t)L), oRows = take((size_t)L * 4), oSlot = take((size_t)L * 12),
+               oRowOff = take((size_t)(L + 1) * 4), oPool = take((size_t)L * 3 * 48), oOwner = take((size_t)L * 12),
+               oEw = take((size_t)L * 72), oRw = take((size_t)L * 72), oFill = take((size_t)L * 3),
+               oRobs = take((size_t)L * 12);
+  uint8_t* d = nullptr;
+  OKC_CUDA_TRY(cudaMalloc(&d, off));
+  int rc = OKC_OK;
+  auto fail = [&](cudaError_t e, const char* what) {
+    if (e != cudaSuccess && rc == OKC_OK) {
+      okc::set_error("%s failed: %s", what, cudaGetErrorString(e));
+      rc = OKC_ERR_CUDA;
+    }
+  };
+  auto up = [&](size_t o, const void* src, size_t bytes) {
+    if (bytes) fail(cudaMemcpy(d + o, src, bytes, cudaMemcpyHostToDevice), "cudaMemcpy");
+  };
+  up(oHp, hp_W, (size_t)L * 32);
+  up(oQ, quality, (size_t)L * 8);
+  up(oVis, visible, (size_t)L);
+  up(oOff, obs_offset, (size_t)(L + 1) * 8);
+  up(oOv, obs_view, (size_t)nObs * 4);
+  up(oOk, obs_kp, (size_t)nObs * 4);
+  up(oC, views->C_WC, (size_t)V * 72);
+  up(oR, views->r_WC, (size_t)V * 24);
+  up(oRow0, views->row0, (size_t)V * 8);
+  up(oDesc, views->desc, N * 48);
+  up(oEc, views->e_C, N * 24);
+  if (rc == OKC_OK) {
+    okc::PrepareArgs a;
+    a.hp_W = reinterpret_cast<const double*>(d + oHp);
+    a.quality = reinterpret_cast<const double*>(d + oQ);
+    a.visible = d + oVis;
+    a.obs_offset = reinterpret_cast<const long long*>(d + oOff);
+    a.obs_view = reinterpret_cast<const int*>(d + oOv);
+    a.obs_kp = reinterpret_cast<const int*>(d + oOk);
+    a.view_C = reinterpret_cast<const double*>(d + oC);
+    a.view_r = reinterpret_cast<const double*>(d + oR);
+    a.view_row0 = reinterpret_cast<const long long*>(d + oRow0);
+    a.desc = d + oDesc;
+    a.e_C = reinterpret_cast<const double*>(d + oEc);
+    for (int i = 0; i < 3; ++i) a.r_WC1[i] = r_WC1[i];
+    a.focal_sum = focal_sum;
+    a.loop_closure = loop_closure ? 1 : 0;
+    a.L = L;
+    a.is3d = d + oIs3d;
+    a.rows = reinterpret_cast<int*>(d + oRows);
+    a.slot_obs = reinterpret_cast<int*>(d + oSlot);
+    okc::prune_observations_kernel<<<(L + 127) / 128, 128>>>(a);
+    okc::scan_rows_kernel<<<1, 1024>>>(a.rows, L, reinterpret_cast<int*>(d + oRowOff));
+    okc::pack_pool_kernel<<<(3 * L + 127) / 128, 128>>>(a, reinterpret_cast<const int*>(d + oRowOff), d + oPool,
+                                                        reinterpret_cast<int*>(d + oOwner),
+                                                        reinterpret_cast<double*>(d + oEw),
+                                                        reinterpret_cast<double*>(d + oRw), d + oFill,
+                                                        reinterpret_cast<int*>(d + oRobs));
+    fail(cudaGetLastError(), "okc_prepare_landmarks kernels");
+    int total = 0;
+    fail(cudaMemcpy(&total, d + oRowOff + (size_t)L * 4, 4, cudaMemcpyDeviceToHost), "cudaMemcpy");
+    auto down = [&](void* dst, size_t o, size_t bytes) {
+      if (bytes) fail(cudaMemcpy(dst, d + o, bytes, cudaMemcpyDeviceToHost), "cudaMemcpy");
+    };
+    down(is3d, oIs3d, (size_t)L);
+    down(rows, oRows, (size_t)L * 4);
+    if (rc == OKC_OK) {
+      down(pool, oPool, (size_t)total * 48);
+      down(owner, oOwner, (size_t)total * 4);
+      down(e_W, oEw, (size_t)total * 24);
+      down(r_W, oRw, (size_t)total * 24);
+      down(filled, oFill, (size_t)total);
+      down(row_obs, oRobs, (size_t)total * 4);
+      *nm = total;
+    }
+  }
+  cudaFree(d);
+  return rc;
+}

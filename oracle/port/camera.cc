@@ -7,6 +7,7 @@
 // okvis_cv needs Eigen, which this image does not have, so the 2x2 / 3x3 Eigen expressions are written out with plain
 // doubles (small fixed-size Eigen products are evaluated coefficient by coefficient; Matrix2d::inverse() is the
 // adjugate scaled by 1/det). PARITY UNPINNED by upstream: the reference has no golden values for these functions.
+#include <algorithm>
 #include <cmath>
 #include <cstdint>
 
@@ -226,4 +227,100 @@ extern "C" void port_keyframe_overlap(int n_views, const int* width, const int* 
     inter[v] = ci;
     uni[v] = cu;
   }
+}
+
+// Landmark preparation of Frontend::matchToMap, second half (okvis_frontend/src/Frontend.cpp:1409-1500): restated
+// with plain doubles in the reference's statement order. Eigen pieces: normalized() = v / sqrt(v.v) (v.v > 0),
+// 3-vector sums (x0 y0 + x1 y1) + x2 y2.
+namespace {
+struct V3 { double x, y, z; };
+inline V3 sub(V3 a, V3 b) { return {a.x - b.x, a.y - b.y, a.z - b.z}; }
+inline V3 mul(double s, V3 a) { return {s * a.x, s * a.y, s * a.z}; }
+inline double dot(V3 a, V3 b) { return (a.x * b.x + a.y * b.y) + a.z * b.z; }
+inline double norm(V3 a) { return std::sqrt(dot(a, a)); }
+inline V3 normalized(V3 a) {
+  const double n2 = dot(a, a);
+  if (n2 > 0.0) {
+    const double n = std::sqrt(n2);
+    return {a.x / n, a.y / n, a.z / n};
+  }
+  return a;
+}
+}  // namespace
+
+extern "C" int port_prepare_landmarks(int n_views, const double* C_WC, const double* r_WC, const int64_t* row0,
+                                      const uint8_t* desc, const double* e_C, int L, const double* hp_W,
+                                      const double* quality, const uint8_t* visible, const int64_t* obs_offset,
+                                      const int32_t* obs_view, const int32_t* obs_kp, const double* r_WC1,
+                                      double focalLength, int loopClosure, uint8_t* is3dOut, int32_t* rowsOut,
+                                      uint8_t* pool, int32_t* owner, double* e_W, double* r_Wout, uint8_t* filled,
+                                      int32_t* row_obs) {
+  (void)n_views;
+  int nm = 0;
+  for (int l = 0; l < L; ++l) {
+    is3dOut[l] = 0;
+    rowsOut[l] = 0;
+    if (!visible[l]) continue;
+    bool is3d = false;
+    const double* hp = hp_W + 4 * l;
+    const V3 p_W = {hp[0] / hp[3], hp[1] / hp[3], hp[2] / hp[3]};
+    const V3 r_W = sub(p_W, V3{r_WC1[0], r_WC1[1], r_WC1[2]});
+    const V3 e = normalized(r_W);
+    const double r = std::max(0.01, norm(r_W));
+    const double q = quality[l];
+    double bestScores[3] = {1.0, 1.0, 1.0};
+    int slot[3] = {-1, -1, -1};
+    size_t o = 0;
+    for (int64_t i = obs_offset[l]; i < obs_offset[l + 1]; ++i) {
+      const int v = obs_view[i];
+      const V3 r_old = {r_WC[3 * v], r_WC[3 * v + 1], r_WC[3 * v + 2]};
+      const V3 r_W_old = sub(p_W, r_old);
+      if (!is3d) {
+        const V3 r_close_W = sub(r_W, mul(0.2 / focalLength / q, r_W_old));
+        const double cosA = dot(normalized(r_W), normalized(r_close_W));
+        if (cosA > std::cos(10.0 / focalLength)) is3d = true;
+      }
+      const double cosViewpointChange = dot(e, normalized(r_W_old));
+      if (cosViewpointChange < std::cos(0.6) && !loopClosure) continue;
+      const double scaleChange = std::fabs(r - norm(r_W_old)) / r;
+      if ((scaleChange > 0.5) && !loopClosure) continue;
+      const double score = 0.5 * (std::acos(cosViewpointChange) / 0.6 + scaleChange / 0.5);
+      double worstScore = 0.0;
+      size_t worstIdx = 0;
+      for (size_t n = 0; n < 3; ++n) {
+        if (bestScores[n] > worstScore) {
+          worstScore = bestScores[n];
+          worstIdx = n;
+        }
+      }
+      if (score < bestScores[worstIdx]) {
+        slot[worstIdx] = int(i - obs_offset[l]);
+        o = std::max(o, worstIdx);
+        bestScores[worstIdx] = score;
+      }
+    }
+    is3dOut[l] = is3d;
+    rowsOut[l] = int(o + 1);
+    for (size_t n = 0; n <= o; ++n, ++nm) {
+      owner[nm] = l;
+      row_obs[nm] = slot[n];
+      filled[nm] = slot[n] >= 0;
+      if (slot[n] < 0) {
+        std::memset(pool + (size_t)nm * 48, 0, 48);
+        for (int c = 0; c < 3; ++c) e_W[3 * nm + c] = r_Wout[3 * nm + c] = 0.0;
+        continue;
+      }
+      const int64_t i = obs_offset[l] + slot[n];
+      const int v = obs_view[i];
+      const int64_t src = row0[v] + obs_kp[i];
+      std::memcpy(pool + (size_t)nm * 48, desc + (size_t)src * 48, 48);
+      const V3 en = normalized(V3{e_C[3 * src], e_C[3 * src + 1], e_C[3 * src + 2]});
+      const double* C = C_WC + 9 * v;
+      for (int c = 0; c < 3; ++c) {
+        e_W[3 * nm + c] = (C[3 * c] * en.x + C[3 * c + 1] * en.y) + C[3 * c + 2] * en.z;
+        r_Wout[3 * nm + c] = r_WC[3 * v + c];
+      }
+    }
+  }
+  return nm;
 }

@@ -243,6 +243,36 @@ class Port:
                                       _ptr(vis))
         return proj[:n], status[:n], vis[:n]
 
+    def prepare_landmarks(self, views, hp_W, quality, visible, obs_offset, obs_view, obs_kp, r_WC1, focal_sum,
+                          loop_closure=False):
+        Cw = np.ascontiguousarray(views["C_WC"], np.float64).reshape(-1, 9)
+        rw = np.ascontiguousarray(views["r_WC"], np.float64).reshape(-1, 3)
+        row0 = np.ascontiguousarray(views["row0"], np.int64)
+        desc = np.ascontiguousarray(views["desc"], np.uint8).reshape(-1, 48)
+        eC = np.ascontiguousarray(views["e_C"], np.float64).reshape(-1, 3)
+        hp = np.ascontiguousarray(hp_W, np.float64).reshape(-1, 4)
+        L = len(hp)
+        q = np.ascontiguousarray(quality, np.float64)
+        vis = np.ascontiguousarray(visible, np.uint8)
+        off = np.ascontiguousarray(obs_offset, np.int64)
+        ov = np.ascontiguousarray(obs_view, np.int32)
+        ok = np.ascontiguousarray(obs_kp, np.int32)
+        r1 = np.ascontiguousarray(r_WC1, np.float64).reshape(3)
+        cap = max(3 * L, 1)
+        out = dict(is3d=np.zeros(max(L, 1), np.uint8), rows=np.zeros(max(L, 1), np.int32), pool=np.zeros((cap, 48), np.uint8),
+                   owner=np.zeros(cap, np.int32), e_W=np.zeros((cap, 3)), r_W=np.zeros((cap, 3)),
+                   filled=np.zeros(cap, np.uint8), row_obs=np.zeros(cap, np.int32))
+        f = self.L.port_prepare_landmarks
+        f.argtypes = [_i, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _d, _i, _vp, _vp, _vp, _vp, _vp,
+                      _vp, _vp, _vp]
+        n = f(len(Cw), _ptr(Cw), _ptr(rw), _ptr(row0), _ptr(desc), _ptr(eC), L, _ptr(hp), _ptr(q), _ptr(vis), _ptr(off),
+              _ptr(ov), _ptr(ok), _ptr(r1), float(focal_sum), int(bool(loop_closure)), _ptr(out["is3d"]), _ptr(out["rows"]),
+              _ptr(out["pool"]), _ptr(out["owner"]), _ptr(out["e_W"]), _ptr(out["r_W"]), _ptr(out["filled"]),
+              _ptr(out["row_obs"]))
+        res = {k: (v[:L] if k in ("is3d", "rows") else v[:n]) for k, v in out.items()}
+        res["nm"] = int(n)
+        return res
+
     def keyframe_overlap(self, widths, heights, kp_offset, keypoints, matched):
         w = np.ascontiguousarray(widths, np.int32)
         h = np.ascontiguousarray(heights, np.int32)

@@ -112,3 +112,71 @@ def test_keyframe_overlap_vs_goldens_and_port(mod, ctx, port):
     pi, pu = port.keyframe_overlap(*args)
     assert np.array_equal(gi, pi) and np.array_equal(gu, pu)
     assert np.all(gi <= gu)
+
+
+def _landmark_scene(seed, L=3000, frames=6):
+    rng = np.random.default_rng(seed)
+    V = 2 * frames
+    # cameras on a short trajectory looking down +z, small rotations
+    C_WC, r_WC = [], []
+    for v in range(V):
+        a, b = rng.normal(0, 0.15, 2)
+        Ry = np.array([[np.cos(a), 0, np.sin(a)], [0, 1, 0], [-np.sin(a), 0, np.cos(a)]])
+        Rx = np.array([[1, 0, 0], [0, np.cos(b), -np.sin(b)], [0, np.sin(b), np.cos(b)]])
+        C_WC.append((Ry @ Rx).reshape(9))
+        r_WC.append(np.array([0.4 * (v // 2) + 0.11 * (v % 2), rng.normal(0, 0.05), rng.normal(0, 0.3)]))
+    kp_per_view = rng.integers(200, 700, V)
+    row0 = np.concatenate([[0], np.cumsum(kp_per_view)[:-1]]).astype(np.int64)
+    N = int(kp_per_view.sum())
+    desc = rng.integers(0, 256, (N, 48), dtype=np.uint8)
+    e_C = np.concatenate([rng.uniform(-0.8, 0.8, (N, 2)), np.ones((N, 1))], 1)
+    p = np.concatenate([rng.uniform(-4, 6, (L, 1)), rng.uniform(-3, 3, (L, 1)), rng.uniform(0.3, 25, (L, 1))], 1)
+    w = rng.uniform(0.5, 2.0, (L, 1))
+    hp_W = np.concatenate([p * w, w], 1)
+    quality = rng.uniform(0.001, 1.0, L)
+    quality[::9] = 1e-4
+    visible = (rng.uniform(0, 1, L) < 0.8).astype(np.uint8)
+    n_obs = rng.integers(0, 9, L)
+    n_obs[:5] = 0
+    obs_offset = np.concatenate([[0], np.cumsum(n_obs)]).astype(np.int64)
+    obs_view = rng.integers(0, V, int(n_obs.sum())).astype(np.int32)
+    obs_kp = (rng.uniform(0, 1, len(obs_view)) * kp_per_view[obs_view]).astype(np.int32)
+    views = dict(C_WC=np.array(C_WC), r_WC=np.array(r_WC), row0=row0, desc=desc, e_C=e_C)
+    return views, hp_W, quality, visible, obs_offset, obs_view, obs_kp
+
+
+@pytest.mark.parametrize("loop_closure", [False, True])
+def test_prepare_landmarks_vs_port(loop_closure, mod, ctx, port):
+    """Frontend::matchToMap landmark preparation (Frontend.cpp:1409-1500): is3d, best-3 descriptor choice, packed pool."""
+    views, hp_W, quality, visible, off, ov, ok = _landmark_scene(21)
+    r1 = np.array([1.0, 0.02, -0.1])
+    fsum = 458.65 + 457.30
+    got = ctx.prepare_landmarks(views, hp_W, quality, visible, off, ov, ok, r1, fsum, loop_closure)
+    want = port.prepare_landmarks(views, hp_W, quality, visible, off, ov, ok, r1, fsum, loop_closure)
+    assert got["nm"] == want["nm"] > 0
+    for k in ("is3d", "rows", "owner", "filled", "row_obs", "pool"):
+        assert np.array_equal(got[k], want[k]), k
+    for k in ("e_W", "r_W"):
+        assert got[k].tobytes() == want[k].tobytes(), k
+    rows = got["rows"]
+    assert np.all(rows[visible == 0] == 0) and np.all(rows[visible != 0] >= 1) and rows.max() == 3
+    assert 0 < got["is3d"].sum() < visible.sum()
+    assert np.all(np.diff(got["owner"]) >= 0)                       # landmarks ascending = std::map order
+    assert (got["filled"] == 0).sum() > 0                           # landmarks without a usable observation keep 1 row
+    if not loop_closure:
+        # every kept row satisfies the two pruning rules it was selected under
+        l = got["owner"][got["filled"] != 0]
+        assert len(l) and len(l) < got["nm"] + 1
+    # the pool feeds the map matcher as is
+    e = np.linalg.norm(got["e_W"][got["filled"] != 0], axis=1)
+    assert float(np.abs(e - 1.0).max()) < 1e-12
+
+
+def test_prepare_landmarks_rejects_bad_observations(mod, ctx):
+    views, hp_W, quality, visible, off, ov, ok = _landmark_scene(3, L=50)
+    bad = ok.copy()
+    bad[0] = 10 ** 6
+    with pytest.raises(Exception):
+        ctx.prepare_landmarks(views, hp_W, quality, visible, off, ov, bad, np.zeros(3), 900.0)
+    empty = ctx.prepare_landmarks(views, hp_W[:0], quality[:0], visible[:0], off[:1], ov[:0], ok[:0], np.zeros(3), 900.0)
+    assert empty["nm"] == 0
