@@ -250,6 +250,24 @@ int okc_prepare_landmarks(okc_context* ctx, const okc_landmark_views* views, int
                           int loop_closure, uint8_t* is3d, int32_t* rows, int32_t* nm, uint8_t* pool, int32_t* owner,
                           double* e_W, double* r_W, uint8_t* filled, int32_t* row_obs);
 
+/* Place recognition, front half: DBoW2::TemplatedVocabulary<FBrisk>::transform of every
+ * descriptor of a frame (external/DBoW2/include/DBoW2/TemplatedVocabulary.h:1216-1257; distance = FBrisk::distance =
+ * the 48-byte Hamming primitive, okvis_frontend/src/FBrisk.cpp:62-65), as TemplatedDatabase::query / add call it for
+ * Frontend::getFilteredDBoWResult and the database fill (Frontend.cpp:605-671, 791-806).
+ * okc_vocabulary_create: the n nodes of the vocabulary file (resources/small_voc.yml.gz: k = 9, L = 3, 819 nodes) in
+ * FILE order - node_id (1..n, the root 0 is implicit), parent_id, 48-byte descriptor, weight, and word_of_node (the
+ * word id of a leaf, -1 for inner nodes); the order of a node's children is the file order, as after load().
+ * okc_vocabulary_transform: per feature the word id, its weight, and the node id at level `levels - levelsup`
+ * (0 = root when that is <= 0), exactly the (word_id, weight, nid) of transform(). BowVector / FeatureVector
+ * accumulation (std::map inserts, L1 normalisation) stays with the caller. Host buffers. */
+typedef struct okc_vocabulary okc_vocabulary;
+int okc_vocabulary_create(okc_context* ctx, int n, const int32_t* node_id, const int32_t* parent_id,
+                          const uint8_t* descriptors, const double* weights, const int32_t* word_of_node, int depth,
+                          okc_vocabulary** vocabulary);
+int okc_vocabulary_destroy(okc_vocabulary* vocabulary);
+int okc_vocabulary_transform(okc_vocabulary* vocabulary, const uint8_t* features, int n, int levels, int levelsup,
+                             uint32_t* word_id, double* weight, uint32_t* node_id);
+
 /* ---- Frame pipeline: the per-frame sequence of Frontend::detectAndDescribe followed by Frontend::matchToMap
  * (ThreadedSlam.cpp:676-717 -> Frontend.cpp:204-262, 1335-1536) with every intermediate product left in HBM.
  * The queries of the map match are the camera handle's own descriptors/keypoints of the frame just described,

@@ -66,6 +66,37 @@ class LandmarkViews(C.Structure):
                 ("desc", C.c_void_p), ("e_C", C.c_void_p), ("n_rows", C.c_int64)]
 
 
+class Vocabulary:
+    """DBoW2 vocabulary tree on the device (okc_vocabulary_*). Nodes in file order: node_id (1..n), parent_id,
+    descriptors [n,48], weights [n], word_of_node [n] (-1 for inner nodes); depth = L of the file."""
+
+    def __init__(self, ctx, node_id, parent_id, descriptors, weights, word_of_node, depth):
+        nid = np.ascontiguousarray(node_id, np.int32)
+        pid = np.ascontiguousarray(parent_id, np.int32)
+        d = np.ascontiguousarray(descriptors, np.uint8).reshape(-1, 48)
+        w = np.ascontiguousarray(weights, np.float64)
+        wo = np.ascontiguousarray(word_of_node, np.int32)
+        self.h = C.c_void_p()
+        self.depth = int(depth)
+        _check(lib().okc_vocabulary_create(ctx.h, len(nid), _p(nid), _p(pid), _p(d), _p(w), _p(wo), self.depth,
+                                           C.byref(self.h)), "okc_vocabulary_create")
+
+    def transform(self, features, levelsup=0):
+        f = np.ascontiguousarray(features, np.uint8).reshape(-1, 48)
+        n = len(f)
+        word = np.zeros(max(n, 1), np.uint32)
+        weight = np.zeros(max(n, 1), np.float64)
+        node = np.zeros(max(n, 1), np.uint32)
+        _check(lib().okc_vocabulary_transform(self.h, _p(f), n, self.depth, int(levelsup), _p(word), _p(weight), _p(node)),
+               "okc_vocabulary_transform")
+        return word[:n], weight[:n], node[:n]
+
+    def close(self):
+        if self.h:
+            lib().okc_vocabulary_destroy(self.h)
+            self.h = C.c_void_p()
+
+
 class DescribeParams(C.Structure):
     _fields_ = [("rotation_invariant", C.c_int), ("scale_invariant", C.c_int), ("extraction_direction", C.c_float * 3)]
 
@@ -104,6 +135,9 @@ def lib():
         L.okc_debug_set_select_wave.argtypes = [i]
         L.okc_back_project.argtypes = [vp, vp, vp, i, vp, vp, C.POINTER(i)]
         L.okc_keyframe_overlap.argtypes = [vp, i, vp, vp, vp, vp, vp, vp, vp]
+        L.okc_vocabulary_create.argtypes = [vp, i, vp, vp, vp, vp, vp, i, C.POINTER(vp)]
+        L.okc_vocabulary_destroy.argtypes = [vp]
+        L.okc_vocabulary_transform.argtypes = [vp, vp, i, i, i, vp, vp, vp]
         L.okc_prepare_landmarks.argtypes = [vp, vp, i, vp, vp, vp, vp, vp, vp, vp, C.c_double, i, vp, vp, C.POINTER(i), vp,
                                             vp, vp, vp, vp, vp]
         L.okc_project_landmarks.argtypes = [vp, vp, vp, vp, i, C.c_double, vp, vp, vp]

@@ -14,6 +14,9 @@
 // order Eigen evaluates them for fixed 2x2 / 3x3 sizes (inverse = adjugate * (1 / det); products coefficient by
 // coefficient). Eigen itself is not in this image, so this order is restated, not pinned.
 #include "common.cuh"
+#include <cstring>
+#include <new>
+#include <vector>
 
 namespace okc {
 
@@ -709,3 +712,173 @@ extern "C" int okc_prepare_landmarks(okc_context* ctx, const okc_landmark_views*
   cudaFree(d);
   return rc;
 }
+
+// ----------------------------------------------------------------------------------------------
+// Place-recognition front half: DBoW2::TemplatedVocabulary<FBrisk>::transform of one feature
+// (external/DBoW2/include/DBoW2/TemplatedVocabulary.h:1216-1257) - descend the vocabulary tree, at every level the
+// child with the smallest FBrisk::distance (= brisk::Hamming::PopcntofXORed over 48 bytes,
+// okvis_frontend/src/FBrisk.cpp:62-65), first child wins ties (strict '<') - for all descriptors of a frame at once.
+// Frontend::getFilteredDBoWResult / database.add (Frontend.cpp:605-671, 791-806) call it through
+// TemplatedDatabase::query / add (TemplatedDatabase.h:409-420, 571). One thread per feature; the tree (819 nodes of
+// 48 bytes for resources/small_voc.yml.gz) stays in L1/L2.
+// ----------------------------------------------------------------------------------------------
+struct okc_vocabulary {
+  okc_context* ctx = nullptr;
+  int n_nodes = 0;            // including the root (node id 0)
+  int* child_offset = nullptr;   // n_nodes + 1
+  int* children = nullptr;       // node ids, per parent in file order
+  uint4* desc = nullptr;         // n_nodes x 3
+  double* weight = nullptr;      // n_nodes
+  int* word = nullptr;           // n_nodes: word id of a leaf, -1 otherwise
+};
+
+namespace okc {
+
+__global__ void vocabulary_transform_kernel(const int* __restrict__ childOffset, const int* __restrict__ children,
+                                            const uint4* __restrict__ nodeDesc, const double* __restrict__ nodeWeight,
+                                            const int* __restrict__ nodeWord, const uint4* __restrict__ features, int n,
+                                            int nidLevel, unsigned* __restrict__ wordId, double* __restrict__ weight,
+                                            unsigned* __restrict__ nodeId) {
+  const int f = blockIdx.x * blockDim.x + threadIdx.x;
+  if (f >= n) return;
+  const uint4 q0 = features[3 * f], q1 = features[3 * f + 1], q2 = features[3 * f + 2];
+  int final_id = 0, current_level = 0;
+  unsigned nid = 0;   // "if (nid_level <= 0) *nid = 0" and the default when the level is never reached
+  do {
+    ++current_level;
+    const int b = childOffset[final_id], e = childOffset[final_id + 1];
+    unsigned best = 0xffffffffu;
+    int bestId = children[b];
+    for (int c = b; c < e; ++c) {
+      const int id = children[c];
+      const uint4 d0 = __ldg(nodeDesc + 3 * id), d1 = __ldg(nodeDesc + 3 * id + 1), d2 = __ldg(nodeDesc + 3 * id + 2);
+      const unsigned d = __popc(q0.x ^ d0.x) + __popc(q0.y ^ d0.y) + __popc(q0.z ^ d0.z) + __popc(q0.w ^ d0.w) +
+                         __popc(q1.x ^ d1.x) + __popc(q1.y ^ d1.y) + __popc(q1.z ^ d1.z) + __popc(q1.w ^ d1.w) +
+                         __popc(q2.x ^ d2.x) + __popc(q2.y ^ d2.y) + __popc(q2.z ^ d2.z) + __popc(q2.w ^ d2.w);
+      if (d < best) {   // the first child initialises, later ones need a strictly smaller distance
+        best = d;
+        bestId = id;
+      }
+    }
+    final_id = bestId;
+    if (current_level == nidLevel) nid = (unsigned)final_id;
+  } while (childOffset[final_id + 1] > childOffset[final_id]);   // !isLeaf()
+  wordId[f] = (unsigned)nodeWord[final_id];
+  weight[f] = nodeWeight[final_id];
+  nodeId[f] = nid;
+}
+
+}  // namespace okc
+
+extern "C" {
+
+int okc_vocabulary_destroy(okc_vocabulary* v) {
+  if (!v) return OKC_OK;
+  cudaFree(v->child_offset);
+  cudaFree(v->children);
+  cudaFree(v->desc);
+  cudaFree(v->weight);
+  cudaFree(v->word);
+  delete v;
+  return OKC_OK;
+}
+
+int okc_vocabulary_create(okc_context* ctx, int n, const int32_t* node_id, const int32_t* parent_id,
+                          const uint8_t* descriptors, const double* weights, const int32_t* word_of_node, int depth,
+                          okc_vocabulary** out) {
+  if (!ctx || !out || n <= 0 || !node_id || !parent_id || !descriptors || !weights || !word_of_node || depth <= 0)
+    return OKC_ERR_INVALID;
+  *out = nullptr;
+  const int N = n + 1;   // + root
+  std::vector<int> count(N, 0), offset(N + 1, 0), children(n), cursor, word(N, -1);
+  std::vector<uint8_t> desc((size_t)N * 48, 0);
+  std::vector<double> w(N, 0.0);
+  std::vector<char> seen(N, 0);
+  for (int i = 0; i < n; ++i) {
+    const int id = node_id[i], p = parent_id[i];
+    if (id <= 0 || id >= N || p < 0 || p >= N || seen[id]) {
+      okc::set_error("okc_vocabulary_create: node ids must be a permutation of 1..n, parents in 0..n");
+      return OKC_ERR_INVALID;
+    }
+    seen[id] = 1;
+    ++count[p];
+  }
+  for (int p = 0; p < N; ++p) offset[p + 1] = offset[p] + count[p];
+  cursor.assign(offset.begin(), offset.end() - 1);
+  for (int i = 0; i < n; ++i) {   // file order = the order children were appended on load (TemplatedVocabulary.h load())
+    const int id = node_id[i];
+    children[cursor[parent_id[i]]++] = id;
+    memcpy(&desc[(size_t)id * 48], descriptors + (size_t)i * 48, 48);
+    w[id] = weights[i];
+    word[id] = word_of_node[i];
+  }
+  if (count[0] == 0) return OKC_ERR_INVALID;
+  // every root-to-leaf walk must end within `depth` levels at a node with a word id (guards the device loop)
+  std::vector<int> parentOf(N, 0);
+  for (int i = 0; i < n; ++i) parentOf[node_id[i]] = parent_id[i];
+  for (int id = 1; id < N; ++id) {
+    int d = 0, x = id;
+    while (x != 0 && d <= depth) {
+      x = parentOf[x];
+      ++d;
+    }
+    if (x != 0 || (count[id] == 0 && word[id] < 0)) {
+      okc::set_error("okc_vocabulary_create: node %d is deeper than %d levels, detached, or a leaf without a word", id, depth);
+      return OKC_ERR_INVALID;
+    }
+  }
+  OKC_CUDA_TRY(cudaSetDevice(okc_context_device(ctx)));
+  okc_vocabulary* v = new (std::nothrow) okc_vocabulary();
+  if (!v) return OKC_ERR_CUDA;
+  v->ctx = ctx;
+  v->n_nodes = N;
+  cudaError_t e = cudaSuccess;
+  auto put = [&](void** dst, const void* src, size_t bytes) {
+    if (e == cudaSuccess) e = cudaMalloc(dst, bytes);
+    if (e == cudaSuccess) e = cudaMemcpy(*dst, src, bytes, cudaMemcpyHostToDevice);
+  };
+  put(reinterpret_cast<void**>(&v->child_offset), offset.data(), (size_t)(N + 1) * 4);
+  put(reinterpret_cast<void**>(&v->children), children.data(), (size_t)n * 4);
+  put(reinterpret_cast<void**>(&v->desc), desc.data(), (size_t)N * 48);
+  put(reinterpret_cast<void**>(&v->weight), w.data(), (size_t)N * 8);
+  put(reinterpret_cast<void**>(&v->word), word.data(), (size_t)N * 4);
+  if (e != cudaSuccess) {
+    okc::set_error("okc_vocabulary_create: %s", cudaGetErrorString(e));
+    okc_vocabulary_destroy(v);
+    return OKC_ERR_CUDA;
+  }
+  *out = v;
+  return OKC_OK;
+}
+
+int okc_vocabulary_transform(okc_vocabulary* v, const uint8_t* features, int n, int levels, int levelsup,
+                             uint32_t* word_id, double* weight, uint32_t* node_id) {
+  if (!v || n < 0 || (n > 0 && (!features || !word_id || !weight || !node_id))) return OKC_ERR_INVALID;
+  if (n == 0) return OKC_OK;
+  OKC_CUDA_TRY(cudaSetDevice(okc_context_device(v->ctx)));
+  uint8_t* d = nullptr;
+  const size_t oF = 0, oW = (size_t)n * 48, oWt = oW + (((size_t)n * 4 + 7) & ~(size_t)7), oN = oWt + (size_t)n * 8;
+  OKC_CUDA_TRY(cudaMalloc(&d, oN + (size_t)n * 4));
+  int rc = OKC_OK;
+  auto fail = [&](cudaError_t e, const char* what) {
+    if (e != cudaSuccess && rc == OKC_OK) {
+      okc::set_error("%s failed: %s", what, cudaGetErrorString(e));
+      rc = OKC_ERR_CUDA;
+    }
+  };
+  fail(cudaMemcpy(d + oF, features, (size_t)n * 48, cudaMemcpyHostToDevice), "cudaMemcpy");
+  if (rc == OKC_OK) {
+    okc::vocabulary_transform_kernel<<<(n + 127) / 128, 128>>>(
+        v->child_offset, v->children, v->desc, v->weight, v->word, reinterpret_cast<const uint4*>(d + oF), n,
+        levels - levelsup, reinterpret_cast<unsigned*>(d + oW), reinterpret_cast<double*>(d + oWt),
+        reinterpret_cast<unsigned*>(d + oN));
+    fail(cudaGetLastError(), "vocabulary_transform_kernel");
+    fail(cudaMemcpy(word_id, d + oW, (size_t)n * 4, cudaMemcpyDeviceToHost), "cudaMemcpy");
+    fail(cudaMemcpy(weight, d + oWt, (size_t)n * 8, cudaMemcpyDeviceToHost), "cudaMemcpy");
+    fail(cudaMemcpy(node_id, d + oN, (size_t)n * 4, cudaMemcpyDeviceToHost), "cudaMemcpy");
+  }
+  cudaFree(d);
+  return rc;
+}
+
+}  // extern "C"

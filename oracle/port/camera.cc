@@ -324,3 +324,41 @@ extern "C" int port_prepare_landmarks(int n_views, const double* C_WC, const dou
   }
   return nm;
 }
+
+// DBoW2::TemplatedVocabulary<FBrisk>::transform of one feature (external/DBoW2/include/DBoW2/TemplatedVocabulary.h:
+// 1216-1257) over a flattened tree: children[child_offset[id] .. child_offset[id+1]) in load order.
+extern "C" void port_vocabulary_transform(const int32_t* child_offset, const int32_t* children, const uint8_t* node_desc,
+                                          const double* node_weight, const int32_t* node_word, const uint8_t* features,
+                                          int n, int m_L, int levelsup, uint32_t* word_id, double* weight,
+                                          uint32_t* nid) {
+  auto distance = [](const uint8_t* a, const uint8_t* b) {
+    int d = 0;
+    for (int i = 0; i < 48; ++i) d += __builtin_popcount((unsigned)(a[i] ^ b[i]));
+    return double(d);
+  };
+  for (int f = 0; f < n; ++f) {
+    const uint8_t* feature = features + (size_t)f * 48;
+    const int nid_level = m_L - levelsup;
+    nid[f] = 0;
+    int final_id = 0;
+    int current_level = 0;
+    do {
+      ++current_level;
+      const int32_t* nodes = children + child_offset[final_id];
+      const int count = child_offset[final_id + 1] - child_offset[final_id];
+      final_id = nodes[0];
+      double best_d = distance(feature, node_desc + (size_t)final_id * 48);
+      for (int c = 1; c < count; ++c) {
+        const int id = nodes[c];
+        const double d = distance(feature, node_desc + (size_t)id * 48);
+        if (d < best_d) {
+          best_d = d;
+          final_id = id;
+        }
+      }
+      if (current_level == nid_level) nid[f] = (uint32_t)final_id;
+    } while (child_offset[final_id + 1] > child_offset[final_id]);
+    word_id[f] = (uint32_t)node_word[final_id];
+    weight[f] = node_weight[final_id];
+  }
+}

@@ -273,6 +273,34 @@ class Port:
         res["nm"] = int(n)
         return res
 
+    def vocabulary_transform(self, node_id, parent_id, descriptors, weights, word_of_node, depth, features, levelsup=0):
+        """Same inputs as okvis2x_b200.Vocabulary (file order); the tree is flattened here the way load() builds it."""
+        nid = np.asarray(node_id, np.int64)
+        pid = np.asarray(parent_id, np.int64)
+        N = len(nid) + 1
+        kids = [[] for _ in range(N)]
+        for i in range(len(nid)):
+            kids[pid[i]].append(int(nid[i]))
+        off = np.zeros(N + 1, np.int32)
+        off[1:] = np.cumsum([len(k) for k in kids])
+        children = np.array([c for k in kids for c in k], np.int32)
+        desc = np.zeros((N, 48), np.uint8)
+        desc[nid] = np.asarray(descriptors, np.uint8).reshape(-1, 48)
+        w = np.zeros(N, np.float64)
+        w[nid] = weights
+        word = np.full(N, -1, np.int32)
+        word[nid] = word_of_node
+        f = np.ascontiguousarray(features, np.uint8).reshape(-1, 48)
+        n = len(f)
+        wid = np.zeros(max(n, 1), np.uint32)
+        wt = np.zeros(max(n, 1), np.float64)
+        node = np.zeros(max(n, 1), np.uint32)
+        fn = self.L.port_vocabulary_transform
+        fn.argtypes = [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp, _vp, _vp]
+        fn(_ptr(off), _ptr(children), _ptr(desc), _ptr(w), _ptr(word), _ptr(f), n, int(depth), int(levelsup), _ptr(wid),
+           _ptr(wt), _ptr(node))
+        return wid[:n], wt[:n], node[:n]
+
     def keyframe_overlap(self, widths, heights, kp_offset, keypoints, matched):
         w = np.ascontiguousarray(widths, np.int32)
         h = np.ascontiguousarray(heights, np.int32)

@@ -175,3 +175,30 @@ def test_port_keyframe_overlap_equals_cv2_goldens(port):
     g = np.load(os.path.join(GOLDEN, "overlap_goldens.npz"))
     inter, uni = port.keyframe_overlap(g["width"], g["height"], g["kp_offset"], g["keypoints"], g["matched"])
     assert np.array_equal(inter, g["intersection"]) and np.array_equal(uni, g["union"])
+
+
+def test_port_vocabulary_descent_on_the_shipped_vocabulary(port):
+    """The reference's own fixture (resources/small_voc.yml.gz, k = 9, L = 3; only where /root/reference exists):
+    every node's descriptor must descend to a leaf below that node, and a word's own descriptor to that word."""
+    import gzip, re
+    path = "/root/reference/resources/small_voc.yml.gz"
+    if not os.path.exists(path):
+        pytest.skip("reference tree not present on this machine")
+    txt = gzip.open(path, "rt").read()
+    k, L = int(re.search(r"\bk: (\d+)", txt).group(1)), int(re.search(r"\bL: (\d+)", txt).group(1))
+    nodes = re.findall(r"nodeId:(\d+), parentId:(\d+), weight:([-+.\deE]+),\s*descriptor:\"([\d ]+)\"", txt)
+    words = dict((int(n), int(w)) for w, n in re.findall(r"wordId:(\d+), nodeId:(\d+)", txt))
+    nid = np.array([int(n[0]) for n in nodes], np.int32)
+    pid = np.array([int(n[1]) for n in nodes], np.int32)
+    wt = np.array([float(n[2]) for n in nodes])
+    desc = np.array([[int(v) for v in n[3].split()] for n in nodes], np.uint8)
+    assert (k, L) == (9, 3) and len(nid) == 9 + 81 + 729 and desc.shape[1] == 48 and len(words) == 729
+    word = np.array([words.get(int(i), -1) for i in nid], np.int32)
+    w, weight, node = port.vocabulary_transform(nid, pid, desc, wt, word, L, desc, levelsup=0)
+    leaf = word >= 0
+    assert np.array_equal(w[leaf], word[leaf].astype(np.uint32))        # a word's centre maps to the word
+    assert weight[leaf].tobytes() == wt[leaf].tobytes()
+    assert np.array_equal(node[leaf], nid[leaf].astype(np.uint32))      # levelsup 0: nid = the leaf itself
+    # levelsup = 1 stores the word's parent (getParentNode, TemplatedVocabulary.h:1263-1273)
+    _, _, up1 = port.vocabulary_transform(nid, pid, desc, wt, word, L, desc[leaf], levelsup=1)
+    assert np.array_equal(up1, pid[leaf].astype(np.uint32))
