@@ -142,29 +142,52 @@ __device__ __forceinline__ int box_rows(const BoxParams& b) { return (b.dy > 0 ?
 // kWords: the image base and the row pitch are multiples of 4, so a row segment is read as aligned 32-bit words
 // (one L1 sector lookup per 4 pixels instead of per pixel; the byte loads of scattered boxes are what bounds this
 // kernel) and the interior bytes are summed with a masked dp4a.
+// Word view of a box: the same for every row (x_left and dx are fixed), so the masks are built once per box.
+struct BoxWords {
+  int w0, nw;            // first 32-bit word of a row segment, number of words (<= kBoxWordsMax, else nw = 0: generic path)
+  unsigned mask[5];      // interior bytes (columns x_left+1 .. x_left+dx) of each word
+  int shFirst, shLast;   // bit offsets of row[0] in word 0 and of row[dx+1] in word nw-1
+};
+constexpr int kBoxWordsMax = 5;
+
+__device__ __forceinline__ BoxWords box_words(const BoxParams& b) {
+  BoxWords k;
+  const int p0 = b.x_left, pl = b.x_left + b.dx + 1;
+  k.w0 = p0 >> 2;
+  k.nw = (pl >> 2) - k.w0 + 1;
+  k.shFirst = 8 * (p0 & 3);
+  k.shLast = 8 * (pl & 3);
+#pragma unroll
+  for (int i = 0; i < kBoxWordsMax; ++i) {
+    const int w = k.w0 + i;
+    const int lo = (p0 + 1 > 4 * w ? p0 + 1 : 4 * w) - 4 * w;
+    const int hi = (pl - 1 < 4 * w + 3 ? pl - 1 : 4 * w + 3) - 4 * w;
+    k.mask[i] = (i < k.nw && hi >= lo) ? ((0xffffffffu >> (8 * (3 - hi))) & (0xffffffffu << (8 * lo))) : 0u;
+  }
+  if (k.nw > kBoxWordsMax) k.nw = 0;
+  return k;
+}
+
+// kWords: the image base and the row pitch are multiples of 4, so a row segment is read as aligned 32-bit words
+// (one L1 sector lookup per 4 pixels instead of per pixel; the byte loads of scattered boxes are what bounds this
+// kernel) and the interior bytes are summed with a masked dp4a.
 template <bool kWords>
-__device__ __forceinline__ int box_row(const uint8_t* __restrict__ img, int W, const BoxParams& b, int r) {
+__device__ __forceinline__ int box_row(const uint8_t* __restrict__ img, int W, const BoxParams& b, const BoxWords& k,
+                                       int r) {
   const uint8_t* row = img + b.x_left + (size_t)(b.y_top + r) * W;
   int mid = 0, first, last;
-  if (kWords) {
-    const unsigned* wrow = reinterpret_cast<const unsigned*>(img + (size_t)(b.y_top + r) * W);
-    const int p0 = b.x_left, pl = b.x_left + b.dx + 1;       // columns of row[0] and row[dx + 1]
-    const int w0 = p0 >> 2, w1 = pl >> 2;
-    unsigned wordFirst = 0, wordLast = 0, acc = 0;
-    for (int w = w0; w <= w1; ++w) {
-      const unsigned v = __ldg(wrow + w);
-      if (w == w0) wordFirst = v;
-      if (w == w1) wordLast = v;
-      const int lo = (p0 + 1 > 4 * w ? p0 + 1 : 4 * w) - 4 * w;            // interior bytes p0+1 .. pl-1 of this word
-      const int hi = (pl - 1 < 4 * w + 3 ? pl - 1 : 4 * w + 3) - 4 * w;
-      if (hi >= lo) {
-        const unsigned mask = (0xffffffffu >> (8 * (3 - hi))) & (0xffffffffu << (8 * lo));
-        acc = __dp4a(v & mask, 0x01010101u, acc);
-      }
-    }
+  if (kWords && k.nw > 0) {
+    const unsigned* wrow = reinterpret_cast<const unsigned*>(img + (size_t)(b.y_top + r) * W) + k.w0;
+    unsigned acc = 0;
+    const unsigned v0 = __ldg(wrow);
+    const unsigned vl = __ldg(wrow + k.nw - 1);
+    acc = __dp4a(v0 & k.mask[0], 0x01010101u, acc);
+#pragma unroll
+    for (int i = 1; i < kBoxWordsMax; ++i)
+      if (i < k.nw) acc = __dp4a(__ldg(wrow + i) & k.mask[i], 0x01010101u, acc);
     mid = (int)acc;
-    first = (int)((wordFirst >> (8 * (p0 & 3))) & 0xffu);
-    last = (int)((wordLast >> (8 * (pl & 3))) & 0xffu);
+    first = (int)((v0 >> k.shFirst) & 0xffu);
+    last = (int)((vl >> k.shLast) & 0xffu);
   } else {
     for (int c = 1; c <= b.dx; ++c) mid += (int)row[c];
     first = (int)row[0];
@@ -192,7 +215,8 @@ __device__ __forceinline__ int smoothed_intensity(const uint8_t* __restrict__ im
   if (b.mode != 2) return b.value;
   int ret = 0;
   const int rows = box_rows(b);
-  for (int r = 0; r < rows; ++r) ret += box_row<kWords>(img, W, b, r);
+  const BoxWords k = box_words(b);
+  for (int r = 0; r < rows; ++r) ret += box_row<kWords>(img, W, b, k, r);
   return ret / b.scaling2;
 }
 
@@ -209,7 +233,8 @@ __device__ __forceinline__ void sample_pattern(const uint8_t* __restrict__ img, 
   int part = 0;
   if (b.mode == 2) {
     const int rows = box_rows(b);
-    for (int r = j; r < rows; r += 16) part += box_row<kWords>(img, W, b, r);
+    const BoxWords k = box_words(b);
+    for (int r = j; r < rows; r += 16) part += box_row<kWords>(img, W, b, k, r);
   }
   for (int o = 8; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
   if (j == 0) values[s] = b.mode == 2 ? part / b.scaling2 : b.value;
