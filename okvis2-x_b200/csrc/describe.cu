@@ -278,7 +278,7 @@ __device__ __forceinline__ float jhypot(float a, float b) {
   return 0.0f;
 }
 
-__global__ void __launch_bounds__(kWarpsPerBlock * 32)
+__global__ void __launch_bounds__(kWarpsPerBlock * 32, 4)
 describe_kernel(const Slot* __restrict__ slots, const PatternPoint* __restrict__ pattern,
                 const uchar2* __restrict__ short_pairs, const LongPair* __restrict__ long_pairs, DescribeArgs a) {
   const Slot& slot = slots[blockIdx.z];
