@@ -2,7 +2,7 @@
 """bench.py - BASELINE.json's metric on BASELINE.json's config, one JSON line on stdout.
 
 Workload (configs[1]): EuRoC-config frontend on a synthetic 752x480 stereo sequence. One "step" = one pass of the
-hot path over one batch of --frames-per-batch (16) stereo frames; per frame and camera: BRISK detect (Harris + NMS +
+hot path over one batch of --frames-per-batch (32) stereo frames; per frame and camera: BRISK detect (Harris + NMS +
 uniformity + sub-pixel) -> camera-aware 48-byte describe -> matchToMap (3D-2D, pixel gate + Hamming < 60) against a
 2 000-landmark keyframe window. The metric is frames/s (= steps x frames per step / time).
 
@@ -41,11 +41,11 @@ DIRECTION = (0.05, 0.99, 0.1)   # gravity in the camera frame (Frontend.cpp:234-
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=1000, help="batches of --frames-per-batch stereo frames")
+    ap.add_argument("--steps", type=int, default=500, help="batches of --frames-per-batch stereo frames")
     ap.add_argument("--warmup", type=int, default=12)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--frames-per-batch", type=int, default=16, help="stereo frames per launch chain")
-    ap.add_argument("--in-flight", type=int, default=6, help="batches in flight (one stream each)")
+    ap.add_argument("--frames-per-batch", type=int, default=32, help="stereo frames per launch chain")
+    ap.add_argument("--in-flight", type=int, default=4, help="batches in flight (one stream each)")
     ap.add_argument("--no-sweep", action="store_true", help="skip the 10k x 1M matcher sweep in `extra`")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()

@@ -730,7 +730,7 @@ constexpr int kStatsThreads = 1024;
 constexpr int kStatsSmemEvents = 8192;
 
 __global__ void __launch_bounds__(kStatsThreads, 1) match_stats_kernel(const Slot* __restrict__ slots) {
-  extern __shared__ __align__(16) unsigned long long s_keys[];  // kStatsSmemEvents keys (dynamic: 64 KB)
+  extern __shared__ __align__(16) unsigned long long s_keys[];  // kStatsSmemEvents keys + as many distances (128 KB)
   __shared__ int s_begin[kMaxSlices + 1];
   const Slot& slot = slots[blockIdx.x];
   if (slot.map == nullptr) return;
@@ -780,16 +780,23 @@ __global__ void __launch_bounds__(kStatsThreads, 1) match_stats_kernel(const Slo
     for (int u = tprev + 1; u <= t; ++u) s_begin[u] = i;
   }
   __syncthreads();
+  // reprojection distances of all events in parallel (the loads are L2 round trips: serialised inside the per-slice
+  // sums they were most of this kernel's time), then the sequential sums in the reference's order from shared memory
+  double* s_dist = reinterpret_cast<double*>(s_keys + kStatsSmemEvents);
+  const bool distInSmem = E <= kStatsSmemEvents;
+  auto event_dist = [&](unsigned long long key) {
+    const unsigned o = (unsigned)(key >> 34) & 0xffffffu, k = (unsigned)(key >> 18) & 0xffffu;
+    const double rx = slot.proj[2 * o] - (double)slot.kp_desc[k].x, ry = slot.proj[2 * o + 1] - (double)slot.kp_desc[k].y;
+    return sqrt(rx * rx + ry * ry);
+  };
+  if (distInSmem)
+    for (int i = tid; i < E; i += kStatsThreads) s_dist[i] = event_dist(keys[i]);
+  __syncthreads();
   if (tid < T) {
     // s_begin[u] for slices after the last populated one stayed E; empty slices in between were filled above
     const int b = s_begin[tid], e = s_begin[tid + 1];
     double sum = 0.0;
-    for (int i = b; i < e; ++i) {
-      const unsigned long long key = keys[i];
-      const unsigned o = (unsigned)(key >> 34) & 0xffffffu, k = (unsigned)(key >> 18) & 0xffffu;
-      const double rx = slot.proj[2 * o] - (double)slot.kp_desc[k].x, ry = slot.proj[2 * o + 1] - (double)slot.kp_desc[k].y;
-      sum += sqrt(rx * rx + ry * ry);
-    }
+    for (int i = b; i < e; ++i) sum += distInSmem ? s_dist[i] : event_dist(keys[i]);
     slot.stats[tid].count = (unsigned long long)(e - b);
     slot.stats[tid].sum = sum;
   }
@@ -799,10 +806,10 @@ void launch_match_stats(const Slot* slots, int n, cudaStream_t s) {
   if (n <= 0) return;
   static bool configured = false;
   if (!configured) {
-    cudaFuncSetAttribute(match_stats_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kStatsSmemEvents * 8);
+    cudaFuncSetAttribute(match_stats_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kStatsSmemEvents * 16);
     configured = true;
   }
-  match_stats_kernel<<<n, kStatsThreads, kStatsSmemEvents * 8, s>>>(slots);
+  match_stats_kernel<<<n, kStatsThreads, kStatsSmemEvents * 16, s>>>(slots);   // keys + distances
 }
 
 // ----------------------------------------------------------------------------------------------

@@ -65,7 +65,7 @@ for f in sorted(os.listdir("gpurun_out")):
     lines.append("")
 open(os.path.join(out, "summary.md"), "w").write("\n".join(lines))
 json.dump({"_note": "dram__bytes_read.sum + dram__bytes_write.sum per launch from one `ncu --set full` capture per kernel of "
-                    "`python bench.py --steps 6 --warmup 3 --no-cpu-baseline` (tools/ncu_round.sh; frames_per_batch 16 = 32 "
+                    "`python bench.py --steps 6 --warmup 3 --no-cpu-baseline` (tools/ncu_round.sh; frames_per_batch 32 = 64 "
                     "images per launch); hamming_best_lb from the 10k x 1M sweep of the same run",
-           "images_per_launch": 32, "kernels": traffic}, open(os.path.join(out, "traffic.json"), "w"), indent=1)
+           "images_per_launch": 64, "kernels": traffic}, open(os.path.join(out, "traffic.json"), "w"), indent=1)
 print("\n".join(lines))
