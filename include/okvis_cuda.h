@@ -268,6 +268,24 @@ int okc_vocabulary_destroy(okc_vocabulary* vocabulary);
 int okc_vocabulary_transform(okc_vocabulary* vocabulary, const uint8_t* features, int n, int levels, int levelsup,
                              uint32_t* word_id, double* weight, uint32_t* node_id);
 
+/* Data formats either side of the descriptor. Host buffers.
+ * okc_descriptors_to_hex: the text form a saved map holds per keypoint, okvis_ceres/src/Component.cpp:434-437 -
+ * 96 lower-case hex characters per 48-byte descriptor, two per byte, no separator and no terminator (hex[n*96]).
+ * okc_descriptors_from_hex: the reader of the same file, Component.cpp:228-236 - every 2-character field goes
+ * through `std::stringstream >> std::hex >> uint32_t` and the low byte is kept, so upper-case digits are accepted,
+ * a field whose second character is no hex digit yields its first digit, a field without digits yields 0, and a
+ * sign is honoured ("-1" -> 255); a field of white space only leaves the reference's byte uninitialised and is 0
+ * here; hex[n*96] in, descriptors[n*48] out. The reference's std::out_of_range for a
+ * string shorter than 96 characters is the adapter's length check. */
+int okc_descriptors_to_hex(okc_context* ctx, const uint8_t* descriptors, int n, char* hex);
+int okc_descriptors_from_hex(okc_context* ctx, const char* hex, int n, uint8_t* descriptors);
+/* DBoW2 cluster centre, FBrisk::meanValue (okvis_frontend/src/FBrisk.cpp:25-60), for n_groups sets of descriptors at
+ * once: group g = rows group_start[g] .. group_start[g+1]-1 of descriptors[.*48] (k-means step of vocabulary
+ * training: one group per cluster). Bit b of mean[g*48 ..] is set when MORE than size/2 (integer division) rows
+ * have it set; an empty group gives 48 zero bytes. */
+int okc_descriptor_mean(okc_context* ctx, const uint8_t* descriptors, const int32_t* group_start, int n_groups,
+                        uint8_t* mean);
+
 /* ---- Frame pipeline: the per-frame sequence of Frontend::detectAndDescribe followed by Frontend::matchToMap
  * (ThreadedSlam.cpp:676-717 -> Frontend.cpp:204-262, 1335-1536) with every intermediate product left in HBM.
  * The queries of the map match are the camera handle's own descriptors/keypoints of the frame just described,

@@ -138,6 +138,9 @@ def lib():
         L.okc_vocabulary_create.argtypes = [vp, i, vp, vp, vp, vp, vp, i, C.POINTER(vp)]
         L.okc_vocabulary_destroy.argtypes = [vp]
         L.okc_vocabulary_transform.argtypes = [vp, vp, i, i, i, vp, vp, vp]
+        L.okc_descriptors_to_hex.argtypes = [vp, vp, i, vp]
+        L.okc_descriptors_from_hex.argtypes = [vp, vp, i, vp]
+        L.okc_descriptor_mean.argtypes = [vp, vp, vp, i, vp]
         L.okc_prepare_landmarks.argtypes = [vp, vp, i, vp, vp, vp, vp, vp, vp, vp, C.c_double, i, vp, vp, C.POINTER(i), vp,
                                             vp, vp, vp, vp, vp]
         L.okc_project_landmarks.argtypes = [vp, vp, vp, vp, i, C.c_double, vp, vp, vp]
@@ -278,6 +281,35 @@ class Context:
         _check(lib().okc_keyframe_overlap(self.h, n, _p(w), _p(h), _p(off), _p(kp), _p(m), _p(inter), _p(uni)),
                "okc_keyframe_overlap")
         return inter[:n], uni[:n]
+
+    # -- formats either side of the descriptor (Component.cpp:228-236, 434-437; FBrisk.cpp:25-60) --
+    def descriptors_to_hex(self, descriptors):
+        """The 96-character text form of each descriptor in a saved map -> list of str."""
+        d = np.ascontiguousarray(descriptors, np.uint8).reshape(-1, 48)
+        out = np.zeros((max(len(d), 1), 96), np.uint8)
+        _check(lib().okc_descriptors_to_hex(self.h, _p(d), len(d), _p(out)), "okc_descriptors_to_hex")
+        return [bytes(r).decode("ascii") for r in out[:len(d)]]
+
+    def descriptors_from_hex(self, strings):
+        """Inverse, with the reference reader's tolerance (see include/okvis_cuda.h). Every string must hold >= 96 characters."""
+        rows = [s.encode("latin-1") if isinstance(s, str) else bytes(s) for s in strings]
+        for r in rows:
+            if len(r) < 96:
+                raise IndexError("descriptor string shorter than 96 characters (std::out_of_range in the reference)")
+        h = np.frombuffer(b"".join(r[:96] for r in rows), np.uint8) if rows else np.zeros(0, np.uint8)
+        out = np.zeros((max(len(rows), 1), 48), np.uint8)
+        _check(lib().okc_descriptors_from_hex(self.h, _p(np.ascontiguousarray(h)), len(rows), _p(out)),
+               "okc_descriptors_from_hex")
+        return out[:len(rows)]
+
+    def descriptor_mean(self, descriptors, group_start):
+        """FBrisk::meanValue of every group of rows (group g = rows group_start[g]..group_start[g+1]-1)."""
+        d = np.ascontiguousarray(descriptors, np.uint8).reshape(-1, 48)
+        gs = np.ascontiguousarray(group_start, np.int32)
+        n = len(gs) - 1
+        out = np.zeros((max(n, 1), 48), np.uint8)
+        _check(lib().okc_descriptor_mean(self.h, _p(d), _p(gs), n, _p(out)), "okc_descriptor_mean")
+        return out[:n]
 
     # -- brute force (Frontend::verifyRecognisedPlace, Frontend.cpp:316-345; the 10k x 1M sweep) --
     def match_batched(self, queries, mp, threshold=60, index_offset=0):

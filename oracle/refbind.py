@@ -301,6 +301,33 @@ class Port:
            _ptr(wt), _ptr(node))
         return wid[:n], wt[:n], node[:n]
 
+    def descriptors_to_hex(self, descriptors):
+        d = np.ascontiguousarray(descriptors, np.uint8).reshape(-1, 48)
+        out = np.zeros((max(len(d), 1), 96), np.uint8)
+        fn = self.L.port_descriptors_to_hex
+        fn.argtypes = [_vp, _i, _vp]
+        fn(_ptr(d), len(d), _ptr(out))
+        return [bytes(r).decode("ascii") for r in out[:len(d)]]
+
+    def descriptors_from_hex(self, strings):
+        rows = [s.encode("latin-1") if isinstance(s, str) else bytes(s) for s in strings]
+        h = np.frombuffer(b"".join(r[:96] for r in rows), np.uint8).copy() if rows else np.zeros(1, np.uint8)
+        out = np.zeros((max(len(rows), 1), 48), np.uint8)
+        fn = self.L.port_descriptors_from_hex
+        fn.argtypes = [_vp, _i, _vp]
+        fn(_ptr(h), len(rows), _ptr(out))
+        return out[:len(rows)]
+
+    def descriptor_mean(self, descriptors, group_start):
+        d = np.ascontiguousarray(descriptors, np.uint8).reshape(-1, 48)
+        gs = np.ascontiguousarray(group_start, np.int32)
+        n = len(gs) - 1
+        out = np.zeros((max(n, 1), 48), np.uint8)
+        fn = self.L.port_descriptor_mean
+        fn.argtypes = [_vp, _vp, _i, _vp]
+        fn(_ptr(d), _ptr(gs), n, _ptr(out))
+        return out[:n]
+
     def keyframe_overlap(self, widths, heights, kp_offset, keypoints, matched):
         w = np.ascontiguousarray(widths, np.int32)
         h = np.ascontiguousarray(heights, np.int32)

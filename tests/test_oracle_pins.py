@@ -202,3 +202,22 @@ def test_port_vocabulary_descent_on_the_shipped_vocabulary(port):
     # levelsup = 1 stores the word's parent (getParentNode, TemplatedVocabulary.h:1263-1273)
     _, _, up1 = port.vocabulary_transform(nid, pid, desc, wt, word, L, desc[leaf], levelsup=1)
     assert np.array_equal(up1, pid[leaf].astype(np.uint32))
+
+
+def test_port_descriptor_formats(port):
+    """Text form of a saved map's descriptors (Component.cpp:228-236, 434-437) and FBrisk::meanValue (FBrisk.cpp:25-60):
+    the port runs the reference's own iostream calls; pinned here against Python's hex codec and a numpy majority vote."""
+    rng = np.random.default_rng(11)
+    d = rng.integers(0, 256, (300, 48), dtype=np.uint8)
+    text = port.descriptors_to_hex(d)
+    assert text == [bytes(r).hex() for r in d]
+    assert np.array_equal(port.descriptors_from_hex(text), d)
+    assert np.array_equal(port.descriptors_from_hex([t.upper() for t in text]), d)
+    odd = port.descriptors_from_hex([("-1" + "0x" + "+f" + "g1" + "7z" + " a") + "00" * 42])[0]
+    assert list(odd[:6]) == [255, 0, 15, 0, 7, 10]
+    gs = np.array([0, 0, 1, 3, 7, 300], np.int32)
+    m = port.descriptor_mean(d, gs)
+    bits = np.unpackbits(d, axis=1, bitorder="little")
+    for g in range(len(gs) - 1):
+        want = np.packbits(bits[gs[g]:gs[g + 1]].sum(0) > (gs[g + 1] - gs[g]) // 2, bitorder="little")
+        assert np.array_equal(m[g], want)
