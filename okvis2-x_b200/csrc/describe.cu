@@ -141,12 +141,13 @@ __device__ __forceinline__ int box_rows(const BoxParams& b) { return (b.dy > 0 ?
 
 // kWords: the image base and the row pitch are multiples of 4, so a row segment is read as aligned 32-bit words
 // (one L1 sector lookup per 4 pixels instead of per pixel; the byte loads of scattered boxes are what bounds this
-// kernel) and the interior bytes are summed with a masked dp4a.
-// Word view of a box: the same for every row (x_left and dx are fixed), so the masks are built once per box.
+// kernel). dp4a's second operand carries one weight per byte: 1 on the interior bytes sums them, a single 1 picks the
+// first / last pixel of the row - no masking, shifting or extraction instructions.
+// Word view of a box: the same for every row (x_left and dx are fixed), so the weights are built once per box.
 struct BoxWords {
-  int w0, nw;            // first 32-bit word of a row segment, number of words (<= kBoxWordsMax, else nw = 0: generic path)
-  unsigned mask[5];      // interior bytes (columns x_left+1 .. x_left+dx) of each word
-  int shFirst, shLast;   // bit offsets of row[0] in word 0 and of row[dx+1] in word nw-1
+  int w0, nw;                   // first 32-bit word of a row segment, number of words (<= kBoxWordsMax, else nw = 0: byte path)
+  unsigned wgt[5];              // 0x01 on the interior bytes (columns x_left+1 .. x_left+dx) of each word
+  unsigned selFirst, selLast;   // 0x01 on row[0] in word 0 and on row[dx+1] in word nw-1
 };
 constexpr int kBoxWordsMax = 5;
 
@@ -155,68 +156,83 @@ __device__ __forceinline__ BoxWords box_words(const BoxParams& b) {
   const int p0 = b.x_left, pl = b.x_left + b.dx + 1;
   k.w0 = p0 >> 2;
   k.nw = (pl >> 2) - k.w0 + 1;
-  k.shFirst = 8 * (p0 & 3);
-  k.shLast = 8 * (pl & 3);
+  k.selFirst = 1u << (8 * (p0 & 3));
+  k.selLast = 1u << (8 * (pl & 3));
 #pragma unroll
   for (int i = 0; i < kBoxWordsMax; ++i) {
     const int w = k.w0 + i;
     const int lo = (p0 + 1 > 4 * w ? p0 + 1 : 4 * w) - 4 * w;
     const int hi = (pl - 1 < 4 * w + 3 ? pl - 1 : 4 * w + 3) - 4 * w;
-    k.mask[i] = (i < k.nw && hi >= lo) ? ((0xffffffffu >> (8 * (3 - hi))) & (0xffffffffu << (8 * lo))) : 0u;
+    k.wgt[i] = (i < k.nw && hi >= lo) ? ((0x01010101u >> (8 * (3 - hi))) & (0x01010101u << (8 * lo))) : 0u;
   }
   if (k.nw > kBoxWordsMax) k.nw = 0;
   return k;
 }
 
-// kWords: the image base and the row pitch are multiples of 4, so a row segment is read as aligned 32-bit words
-// (one L1 sector lookup per 4 pixels instead of per pixel; the byte loads of scattered boxes are what bounds this
-// kernel) and the interior bytes are summed with a masked dp4a.
+// Adds row r of the box to three running sums: its first pixel, its last pixel, its interior pixels.
+template <bool kWords>
+__device__ __forceinline__ void box_row_sums(const uint8_t* __restrict__ img, int W, const BoxParams& b,
+                                             const BoxWords& k, int r, unsigned& first, unsigned& last, unsigned& mid) {
+  if (kWords && k.nw > 0) {
+    const unsigned* wrow = reinterpret_cast<const unsigned*>(img + (size_t)(b.y_top + r) * W) + k.w0;
+    const unsigned v0 = __ldg(wrow);
+    const unsigned vl = __ldg(wrow + k.nw - 1);
+    mid = __dp4a(v0, k.wgt[0], mid);
+#pragma unroll
+    for (int i = 1; i < kBoxWordsMax; ++i)
+      if (i < k.nw) mid = __dp4a(__ldg(wrow + i), k.wgt[i], mid);
+    first = __dp4a(v0, k.selFirst, first);
+    last = __dp4a(vl, k.selLast, last);
+  } else {
+    const uint8_t* row = img + b.x_left + (size_t)(b.y_top + r) * W;
+    for (int c = 1; c <= b.dx; ++c) mid += row[c];
+    first += row[0];
+    last += row[b.dx + 1];
+  }
+}
+
+// The two lower corner terms. Reference quirk kept on purpose: on the integral-image path (dx + dy > 2) the two lower
+// corner pixels are fetched with "ptr += dy * imagecols + 1" (:459), i.e. from row y_top + dy and one column to the
+// right; the loop path uses the bottom row's own first / last pixel.
+__device__ __forceinline__ int box_lower_corners(const uint8_t* __restrict__ img, int W, const BoxParams& b, int first,
+                                                 int last) {
+  if (b.dx + b.dy > 2) {
+    const uint8_t* q = img + b.x_left + (size_t)b.y_top * W + (b.dx + 1) + (size_t)b.dy * W + 1;
+    return b.C * (int)q[0] + b.D * (int)q[-(b.dx + 1)];
+  }
+  return b.D * first + b.C * last;
+}
+
+// One row's weighted contribution (used where the rows of a box are spread over lanes).
 template <bool kWords>
 __device__ __forceinline__ int box_row(const uint8_t* __restrict__ img, int W, const BoxParams& b, const BoxWords& k,
                                        int r) {
-  const uint8_t* row = img + b.x_left + (size_t)(b.y_top + r) * W;
-  int mid = 0, first, last;
-  if (kWords && k.nw > 0) {
-    const unsigned* wrow = reinterpret_cast<const unsigned*>(img + (size_t)(b.y_top + r) * W) + k.w0;
-    unsigned acc = 0;
-    const unsigned v0 = __ldg(wrow);
-    const unsigned vl = __ldg(wrow + k.nw - 1);
-    acc = __dp4a(v0 & k.mask[0], 0x01010101u, acc);
-#pragma unroll
-    for (int i = 1; i < kBoxWordsMax; ++i)
-      if (i < k.nw) acc = __dp4a(__ldg(wrow + i) & k.mask[i], 0x01010101u, acc);
-    mid = (int)acc;
-    first = (int)((v0 >> k.shFirst) & 0xffu);
-    last = (int)((vl >> k.shLast) & 0xffu);
-  } else {
-    for (int c = 1; c <= b.dx; ++c) mid += (int)row[c];
-    first = (int)row[0];
-    last = (int)row[b.dx + 1];
-  }
+  unsigned uf = 0, ul = 0, um = 0;
+  box_row_sums<kWords>(img, W, b, k, r, uf, ul, um);
+  const int first = (int)uf, last = (int)ul, mid = (int)um;
   if (r == 0) return b.A * first + b.B * last + mid * b.wy0;
   if (r < box_rows(b) - 1) return first * b.wx0 + last * b.wx1 + mid * b.scaling;
-  int ret = mid * b.wy1;
-  if (b.dx + b.dy > 2) {
-    // Reference quirk kept on purpose: on the integral-image path the two lower corner pixels are fetched with
-    // "ptr += dy * imagecols + 1" (:459), i.e. from row y_top + dy and one column to the right.
-    const uint8_t* q = img + b.x_left + (size_t)b.y_top * W + (b.dx + 1) + (size_t)b.dy * W + 1;
-    ret += b.C * (int)q[0] + b.D * (int)q[-(b.dx + 1)];
-  } else {
-    ret += b.D * first + b.C * last;
-  }
-  return ret;
+  return mid * b.wy1 + box_lower_corners(img, W, b, first, last);
 }
 
+// A whole box by one lane: the middle rows share their three weights, so their pixels are summed first and weighted
+// once (the reference's int32 result is a linear combination of pixel sums; the order of the additions is free).
 template <bool kWords>
 __device__ __forceinline__ int smoothed_intensity(const uint8_t* __restrict__ img, int W, int H, float key_x,
                                                   float key_y, PatternPoint p0, bool warped, const float* warp,
                                                   float warpScale) {
   const BoxParams b = box_params(img, W, H, key_x, key_y, p0, warped, warp, warpScale);
   if (b.mode != 2) return b.value;
-  int ret = 0;
   const int rows = box_rows(b);
   const BoxWords k = box_words(b);
-  for (int r = 0; r < rows; ++r) ret += box_row<kWords>(img, W, b, k, r);
+  unsigned tf = 0, tl = 0, tm = 0, mf = 0, ml = 0, mm = 0, bf = 0, bl = 0, bm = 0;
+  box_row_sums<kWords>(img, W, b, k, 0, tf, tl, tm);
+  box_row_sums<kWords>(img, W, b, k, rows - 1, bf, bl, bm);
+#pragma unroll 2
+  for (int r = 1; r < rows - 1; ++r) box_row_sums<kWords>(img, W, b, k, r, mf, ml, mm);
+  int ret = b.A * (int)tf + b.B * (int)tl + (int)tm * b.wy0;
+  ret += (int)mf * b.wx0 + (int)ml * b.wx1 + (int)mm * b.scaling;
+  ret += (int)bm * b.wy1 + box_lower_corners(img, W, b, (int)bf, (int)bl);
   return ret / b.scaling2;
 }
 

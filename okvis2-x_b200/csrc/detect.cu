@@ -79,13 +79,18 @@ __global__ void __launch_bounds__(32 * kHarrisWarps) harris_nms_kernel(const Slo
     }
     return w;
   };
-  unsigned wNext = load_row(q0 - 3), wNext2 = load_row(q0 - 2);
+  constexpr int kAhead = 5;   // rows in flight
+  unsigned wq[kAhead];
+#pragma unroll
+  for (int i = 0; i < kAhead; ++i) wq[i] = load_row(q0 - 3 + i);
   auto step = [&](auto Pc, int r) {
     constexpr int P = decltype(Pc)::value, A = (P + 1) % 3, B = (P + 2) % 3;
-    // ---- 1. pixels of row r; rows r+1, r+2 are already in flight ----
-    const unsigned w = wNext;
-    wNext = wNext2;
-    wNext2 = load_row(r + 2);
+    // ---- 1. pixels of row r; rows r+1 .. r+kAhead-1 are already in flight (the pixels come from DRAM: a step is
+    // ~300 instructions, three steps of the 4 warps of a scheduler cover its latency) ----
+    const unsigned w = wq[0];
+#pragma unroll
+    for (int i = 0; i + 1 < kAhead; ++i) wq[i] = wq[i + 1];
+    wq[kAhead - 1] = load_row(r + kAhead);
     const unsigned wl = __shfl_up_sync(0xffffffffu, w, 1), wr = __shfl_down_sync(0xffffffffu, w, 1);
     int px[6];
     px[0] = (int)(wl >> 24);

@@ -574,63 +574,70 @@ void launch_bin_projections(const Slot* slots, int n, cudaStream_t s) {
 constexpr int kBinnedWarps = 8;
 constexpr int kMaxHits = 64;   // rows inside the gate with dist < threshold, per keypoint (2 per lane); more: full scan
 
-__global__ void __launch_bounds__(kBinnedWarps * 32)
+__global__ void __launch_bounds__(kBinnedWarps * 32, 6)
 match_to_map_binned_kernel(const Slot* __restrict__ slots, int maxKp, double hammingThreshold) {
   const Slot& slot = slots[blockIdx.z];
   if (slot.map == nullptr) return;
   const int lane = threadIdx.x & 31;
   const int k = blockIdx.x * kBinnedWarps + (threadIdx.x >> 5);
-  const int nk = min(slot.counters[2], maxKp);
-  if (k >= nk) return;
-  unsigned q[kDescWords];
-  load_desc(slot.desc, k, q);
-  // cv::KeyPoint floats widen exactly to the Eigen::Vector2d the reference compares with (Frontend.cpp:1787-1790)
-  const double kx = (double)slot.kp_desc[k].x, ky = (double)slot.kp_desc[k].y;
-  const double threshSq = slot.thresh_sq;
+  // The kernel is a chain of dependent loads (slot table -> counters -> keypoint -> cell bounds -> rows ->
+  // descriptors); everything that only depends on the slot table is requested before the first branch. The
+  // keypoint and its descriptor are read at a clamped index: the arrays hold maxKp rows, the count is not known yet.
+  const int kSafe = k < maxKp ? k : maxKp - 1;
   const int ncells = slot.bins_x * slot.bins_y;
+  const int nkRaw = slot.counters[2];
+  const int notFinite = slot.bins_x > 0 ? slot.bin_start[ncells + 1] : 1;
+  const okc_keypoint kpt = slot.kp_desc[kSafe];
+  unsigned q[kDescWords];
+  load_desc(slot.desc, kSafe, q);
+  if (k >= min(nkRaw, maxKp)) return;
+  // cv::KeyPoint floats widen exactly to the Eigen::Vector2d the reference compares with (Frontend.cpp:1787-1790)
+  const double kx = (double)kpt.x, ky = (double)kpt.y;
+  const double threshSq = slot.thresh_sq;
 
   // hits of this keypoint, two per lane: row index, distance (an integer in [0, 384]), landmark slot
   int hm[2] = {0x7fffffff, 0x7fffffff}, ho[2] = {-1, -1};
   unsigned hd[2] = {0, 0};
   int nh = 0;            // hits held by this lane
   bool overflow = false;
-  const bool binned = slot.bins_x > 0 && slot.bin_start[ncells + 1] == 0;
-  auto consider = [&](bool inRange, int m, int o, double px, double py) {
-    bool hit = false;
-    unsigned d = 0;
-    if (inRange) {
-      const double rx = px - kx, ry = py - ky;
-      if (!(rx * rx + ry * ry > threshSq)) {
-        unsigned r[kDescWords];
-        load_desc(slot.map, m, r);
-        d = hamming384(q, r);
-        hit = (double)d < hammingThreshold;
-      }
-    }
-    if (hit) {
-      if (nh < 2) {
-        hm[nh] = m;
-        hd[nh] = d;
-        ho[nh] = o;
-        ++nh;
-      } else {
-        overflow = true;
-      }
-    }
-  };
+  const bool binned = notFinite == 0;
   if (binned) {
     const int cx = bin_cell_of(kx, slot.bin_pad, slot.bin_cell, slot.bins_x);
     const int cy = bin_cell_of(ky, slot.bin_pad, slot.bin_cell, slot.bins_y);
     if (cx >= 0 && cy >= 0) {   // (always, for a keypoint inside the image)
+      // the 3 x 3 cells are three runs of consecutive cells = three ranges of the binned rows; lanes 0..5 fetch the
+      // six bounds at once and the ranges are walked as one list
       const int x0 = cx > 0 ? cx - 1 : 0, x1 = cx + 1 < slot.bins_x ? cx + 1 : slot.bins_x - 1;
-      for (int yy = cy - 1; yy <= cy + 1; ++yy) {
-        if (yy < 0 || yy >= slot.bins_y) continue;
-        const int b = slot.bin_start[yy * slot.bins_x + x0], e = slot.bin_start[yy * slot.bins_x + x1 + 1];
-        for (int base = b; base < e; base += 32) {
-          const int i = base + lane;
-          const bool in = i < e;
-          consider(in, in ? slot.bin_rows[i] : 0, in ? slot.bin_owner[i] : 0, in ? slot.bin_px[i] : 0.0,
-                   in ? slot.bin_py[i] : 0.0);
+      int bound = 0;
+      {
+        const int yy = cy - 1 + (lane >> 1);
+        if (lane < 6 && yy >= 0 && yy < slot.bins_y) bound = slot.bin_start[yy * slot.bins_x + ((lane & 1) ? x1 + 1 : x0)];
+      }
+      const int b0 = __shfl_sync(0xffffffffu, bound, 0), n0 = __shfl_sync(0xffffffffu, bound, 1) - b0;
+      const int b1 = __shfl_sync(0xffffffffu, bound, 2), n1 = __shfl_sync(0xffffffffu, bound, 3) - b1;
+      const int b2 = __shfl_sync(0xffffffffu, bound, 4), n2 = __shfl_sync(0xffffffffu, bound, 5) - b2;
+      const int total = n0 + n1 + n2;
+      for (int base = 0; base < total; base += 32) {
+        const int t = base + lane;
+        if (t < total) {
+          const int i = t < n0 ? b0 + t : (t < n0 + n1 ? b1 + (t - n0) : b2 + (t - n0 - n1));
+          const double rx = slot.bin_px[i] - kx, ry = slot.bin_py[i] - ky;
+          if (!(rx * rx + ry * ry > threshSq)) {
+            const int m = slot.bin_rows[i];
+            unsigned r[kDescWords];
+            load_desc(slot.map, m, r);
+            const unsigned d = hamming384(q, r);
+            if ((double)d < hammingThreshold) {
+              if (nh < 2) {
+                hm[nh] = m;
+                hd[nh] = d;
+                ho[nh] = slot.bin_owner[i];
+                ++nh;
+              } else {
+                overflow = true;
+              }
+            }
+          }
         }
       }
     }
