@@ -79,6 +79,14 @@ __global__ void __launch_bounds__(32 * kHarrisWarps) harris_nms_kernel(const Slo
     }
     return w;
   };
+  // columns 2 .. W-3 carry a score (lane constants): all ones / zero per column, and as a 4-bit mask
+  int colKeep[4];
+  unsigned colBits = 0;
+#pragma unroll
+  for (int c = 0; c < 4; ++c) {
+    colKeep[c] = (x + c >= 2 && x + c <= W - 3) ? -1 : 0;
+    colBits |= (colKeep[c] & 1u) << c;
+  }
   constexpr int kAhead = 5;   // rows in flight
   unsigned wq[kAhead];
 #pragma unroll
@@ -103,10 +111,12 @@ __global__ void __launch_bounds__(32 * kHarrisWarps) harris_nms_kernel(const Slo
     int pxx[4], pxy[4], pyy[4];
 #pragma unroll
     for (int c = 0; c < 4; ++c) {
+      // Scharr with the reference's "<< 3" folded into the weights (|dx|, |dy| <= 32640: no int16 wrap to mirror);
+      // the smoothed-row history sH holds 8 * (3, 10, 3)-sums
       const int h2 = px[c] - px[c + 2];
-      const int s2 = 3 * (px[c] + px[c + 2]) + 10 * px[c + 1];
-      const int dx = (3 * (hH[A][c] + h2) + 10 * hH[B][c]) << 3;
-      const int dy = (sH[A][c] - s2) << 3;
+      const int s2 = 24 * (px[c] + px[c + 2]) + 80 * px[c + 1];
+      const int dx = 24 * (hH[A][c] + h2) + 80 * hH[B][c];
+      const int dy = sH[A][c] - s2;
       hH[P][c] = h2;
       sH[P][c] = s2;
       pxx[c] = (dx * dx) >> 16;
@@ -133,7 +143,7 @@ __global__ void __launch_bounds__(32 * kHarrisWarps) harris_nms_kernel(const Slo
     }
     // ---- 3. score of row p = r-2 ----
     const int p = r - 2;
-    const bool rowValid = p >= 2 && p <= H - 3;
+    const int rowKeep = (p >= 2 && p <= H - 3) ? -1 : 0;
 #pragma unroll
     for (int c = 0; c < 4; ++c) {
       const int a = (xxH[A][c] + 2 * xxH[B][c] + xx2[c]) >> 4;
@@ -144,7 +154,7 @@ __global__ void __launch_bounds__(32 * kHarrisWarps) harris_nms_kernel(const Slo
       xxH[P][c] = xx2[c];
       xyH[P][c] = xy2[c];
       yyH[P][c] = yy2[c];
-      scH[P][c] = (rowValid && x + c >= 2 && x + c <= W - 3) ? v : 0;
+      scH[P][c] = v & rowKeep & colKeep[c];
     }
     if (emit && p >= q0 && p < q1 && x < W) {
       int32_t* dst = scores + (size_t)p * W + x;
@@ -174,11 +184,11 @@ __global__ void __launch_bounds__(32 * kHarrisWarps) harris_nms_kernel(const Slo
       if (emit && q >= 2 && q <= H - 3) {
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
-          const int ctr = scH[B][c];
-          const bool isMax = x + c >= 2 && x + c <= W - 3 && ctr >= absThreshold &&
-                             ctr >= max(max(mTop[c], mH[P][c]), lrH[B][c]);
+          // >= the threshold and >= all 8 neighbours, as one comparison against the largest of them
+          const bool isMax = scH[B][c] >= max(max(mTop[c], mH[P][c]), max(lrH[B][c], absThreshold));
           nib |= (isMax ? 1u : 0u) << c;
         }
+        nib &= colBits;
       }
       unsigned v = nib << (4 * (lane & 7));
       v |= __shfl_xor_sync(0xffffffffu, v, 1);
