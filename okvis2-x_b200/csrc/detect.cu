@@ -22,7 +22,7 @@ namespace okc {
 // Harris score + 8-neighbour NMS
 // ----------------------------------------------------------------------------------------------
 // Register-marching stencil: a warp owns a strip of 128 columns (4 consecutive columns per lane) and walks down
-// kHarrisRows output rows; every intermediate (Scharr partial sums, gradient products, horizontally smoothed
+// rowsPerWarp output rows; every intermediate (Scharr partial sums, gradient products, horizontally smoothed
 // products, scores, row maxima) lives in registers, neighbours across lanes come from warp shuffles, and there is
 // no shared memory and no block-level synchronisation. Lanes 0 and 31 only feed their neighbours (halo), so a
 // warp emits 120 columns. Per pixel this is ~60 integer operations against ~320 in a shared-memory tile
@@ -37,7 +37,7 @@ namespace okc {
 // NMS survivors (harris-score-calculator.cc:76-117: >= threshold, no neighbour strictly greater) are published as a
 // bitmap with kStripWords words per (row, strip): bit b of word j of strip s is column 120 s - 4 + 32 j + b.
 // Row-major, strip-major, bit-ascending order = raster order, which order_candidates_kernel relies on.
-constexpr int kHarrisRows = 32;      // output rows per warp
+// output rows per warp: chosen per launch (harris_rows_per_warp), see launch_harris_nms
 constexpr int kHarrisWarps = 2;      // warps per block (independent: no shared memory, no barriers)
 constexpr int kStripCols = 120;      // output columns per warp
 constexpr int kStripWords = 4;
@@ -46,16 +46,16 @@ __host__ __device__ inline int harris_strips(int W) { return (W + kStripCols - 1
 
 template <bool ALIGNED>
 __global__ void __launch_bounds__(32 * kHarrisWarps) harris_nms_kernel(const Slot* __restrict__ slots, int W, int H,
-                                                         int absThreshold) {
+                                                         int absThreshold, int rowsPerWarp) {
   const Slot& slot = slots[blockIdx.z];
   const uint8_t* __restrict__ img = slot.image;
   int32_t* __restrict__ scores = slot.scores;
   uint32_t* __restrict__ bitmap = slot.bitmap;
   const int lane = threadIdx.x & 31;
   const int strip = blockIdx.x;
-  const int q0 = (blockIdx.y * kHarrisWarps + (threadIdx.x >> 5)) * kHarrisRows;
+  const int q0 = (blockIdx.y * kHarrisWarps + (threadIdx.x >> 5)) * rowsPerWarp;
   if (q0 >= H) return;
-  const int q1 = min(H, q0 + kHarrisRows);
+  const int q1 = min(H, q0 + rowsPerWarp);
   const int x = strip * kStripCols - 4 + 4 * lane;  // first of this lane's 4 columns
   const int wordsPerRow = harris_strips(W) * kStripWords;
   const bool emit = lane >= 1 && lane <= 30;
@@ -205,11 +205,40 @@ __global__ void __launch_bounds__(32 * kHarrisWarps) harris_nms_kernel(const Slo
   }
 }
 
+// Rows per warp: a warp computes rows + 6 halo rows (rounded up to the loop's 3 rows per trip), so tall chunks waste
+// less, but the grid must still fill the GPU in whole waves (8 CTAs of 128 registers x 64 threads per SM) and a
+// small batch wants short chunks for latency. Cost model: trips per warp x waves of CTAs.
+static int harris_rows_per_warp(int W, int H, int n) {
+  static int slots = 0;
+  if (slots == 0) {
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    slots = sms * 8;
+  }
+  const int candidates[] = {8, 12, 16, 24, 32, 48, 64, 96};
+  int best = 32;
+  long long bestCost = -1;
+  for (int rows : candidates) {
+    const int chunks = (H + rows - 1) / rows;
+    const long long ctas = (long long)harris_strips(W) * ((chunks + kHarrisWarps - 1) / kHarrisWarps) * n;
+    const long long waves = (ctas + slots - 1) / slots;
+    const long long trips = (rows + 6 + 2) / 3;
+    const long long cost = trips * waves;
+    if (bestCost < 0 || cost < bestCost) {
+      bestCost = cost;
+      best = rows;
+    }
+  }
+  return best;
+}
+
 void launch_harris_nms(const Slot* slots, int n, const DetectArgs& a, cudaStream_t s, bool aligned) {
-  const int chunks = (a.height + kHarrisRows - 1) / kHarrisRows;
+  const int rows = harris_rows_per_warp(a.width, a.height, n);
+  const int chunks = (a.height + rows - 1) / rows;
   dim3 grid(harris_strips(a.width), (chunks + kHarrisWarps - 1) / kHarrisWarps, n);
-  if (aligned) harris_nms_kernel<true><<<grid, 32 * kHarrisWarps, 0, s>>>(slots, a.width, a.height, a.abs_threshold);
-  else harris_nms_kernel<false><<<grid, 32 * kHarrisWarps, 0, s>>>(slots, a.width, a.height, a.abs_threshold);
+  if (aligned) harris_nms_kernel<true><<<grid, 32 * kHarrisWarps, 0, s>>>(slots, a.width, a.height, a.abs_threshold, rows);
+  else harris_nms_kernel<false><<<grid, 32 * kHarrisWarps, 0, s>>>(slots, a.width, a.height, a.abs_threshold, rows);
 }
 
 size_t harris_bitmap_words(int W, int H) { return (size_t)H * harris_strips(W) * kStripWords; }
