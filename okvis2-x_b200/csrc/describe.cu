@@ -170,25 +170,42 @@ __device__ __forceinline__ BoxWords box_words(const BoxParams& b) {
 }
 
 // Adds row r of the box to three running sums: its first pixel, its last pixel, its interior pixels.
+// Word form (needs k.nw > 0). Branch-free: always five loads, at word indices clamped to the last word of the
+// segment (a word past the segment has weight 0, and index 4 is always the last word). With "if (i < nw)" around
+// each load the compiler emits a divergent branch per word and every load's latency is exposed in turn.
+__device__ __forceinline__ void box_row_sums_words(const uint8_t* __restrict__ img, int W, const BoxParams& b,
+                                                   const BoxWords& k, int r, unsigned& first, unsigned& last,
+                                                   unsigned& mid) {
+  const unsigned* wrow = reinterpret_cast<const unsigned*>(img + (size_t)(b.y_top + r) * W) + k.w0;
+  const int l = k.nw - 1;
+  const unsigned v0 = __ldg(wrow);
+  const unsigned v1 = __ldg(wrow + min(1, l));
+  const unsigned v2 = __ldg(wrow + min(2, l));
+  const unsigned v3 = __ldg(wrow + min(3, l));
+  const unsigned v4 = __ldg(wrow + l);
+  mid = __dp4a(v0, k.wgt[0], mid);
+  mid = __dp4a(v1, k.wgt[1], mid);
+  mid = __dp4a(v2, k.wgt[2], mid);
+  mid = __dp4a(v3, k.wgt[3], mid);
+  mid = __dp4a(v4, k.wgt[4], mid);
+  first = __dp4a(v0, k.selFirst, first);
+  last = __dp4a(v4, k.selLast, last);
+}
+
+// Byte form (unaligned image, or a segment longer than kBoxWordsMax words).
+__device__ __forceinline__ void box_row_sums_bytes(const uint8_t* __restrict__ img, int W, const BoxParams& b, int r,
+                                                   unsigned& first, unsigned& last, unsigned& mid) {
+  const uint8_t* row = img + b.x_left + (size_t)(b.y_top + r) * W;
+  for (int c = 1; c <= b.dx; ++c) mid += row[c];
+  first += row[0];
+  last += row[b.dx + 1];
+}
+
 template <bool kWords>
 __device__ __forceinline__ void box_row_sums(const uint8_t* __restrict__ img, int W, const BoxParams& b,
                                              const BoxWords& k, int r, unsigned& first, unsigned& last, unsigned& mid) {
-  if (kWords && k.nw > 0) {
-    const unsigned* wrow = reinterpret_cast<const unsigned*>(img + (size_t)(b.y_top + r) * W) + k.w0;
-    const unsigned v0 = __ldg(wrow);
-    const unsigned vl = __ldg(wrow + k.nw - 1);
-    mid = __dp4a(v0, k.wgt[0], mid);
-#pragma unroll
-    for (int i = 1; i < kBoxWordsMax; ++i)
-      if (i < k.nw) mid = __dp4a(__ldg(wrow + i), k.wgt[i], mid);
-    first = __dp4a(v0, k.selFirst, first);
-    last = __dp4a(vl, k.selLast, last);
-  } else {
-    const uint8_t* row = img + b.x_left + (size_t)(b.y_top + r) * W;
-    for (int c = 1; c <= b.dx; ++c) mid += row[c];
-    first += row[0];
-    last += row[b.dx + 1];
-  }
+  if (kWords && k.nw > 0) box_row_sums_words(img, W, b, k, r, first, last, mid);
+  else box_row_sums_bytes(img, W, b, r, first, last, mid);
 }
 
 // The two lower corner terms. Reference quirk kept on purpose: on the integral-image path (dx + dy > 2) the two lower
@@ -226,10 +243,16 @@ __device__ __forceinline__ int smoothed_intensity(const uint8_t* __restrict__ im
   const int rows = box_rows(b);
   const BoxWords k = box_words(b);
   unsigned tf = 0, tl = 0, tm = 0, mf = 0, ml = 0, mm = 0, bf = 0, bl = 0, bm = 0;
-  box_row_sums<kWords>(img, W, b, k, 0, tf, tl, tm);
-  box_row_sums<kWords>(img, W, b, k, rows - 1, bf, bl, bm);
+  if (kWords && k.nw > 0) {   // decided once per box, so that the row loop is straight-line code
+    box_row_sums_words(img, W, b, k, 0, tf, tl, tm);
+    box_row_sums_words(img, W, b, k, rows - 1, bf, bl, bm);
 #pragma unroll 2
-  for (int r = 1; r < rows - 1; ++r) box_row_sums<kWords>(img, W, b, k, r, mf, ml, mm);
+    for (int r = 1; r < rows - 1; ++r) box_row_sums_words(img, W, b, k, r, mf, ml, mm);
+  } else {
+    box_row_sums_bytes(img, W, b, 0, tf, tl, tm);
+    box_row_sums_bytes(img, W, b, rows - 1, bf, bl, bm);
+    for (int r = 1; r < rows - 1; ++r) box_row_sums_bytes(img, W, b, r, mf, ml, mm);
+  }
   int ret = b.A * (int)tf + b.B * (int)tl + (int)tm * b.wy0;
   ret += (int)mf * b.wx0 + (int)ml * b.wx1 + (int)mm * b.scaling;
   ret += (int)bm * b.wy1 + box_lower_corners(img, W, b, (int)bf, (int)bl);

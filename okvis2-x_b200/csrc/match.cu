@@ -574,7 +574,7 @@ void launch_bin_projections(const Slot* slots, int n, cudaStream_t s) {
 constexpr int kBinnedWarps = 8;
 constexpr int kMaxHits = 64;   // rows inside the gate with dist < threshold, per keypoint (2 per lane); more: full scan
 
-__global__ void __launch_bounds__(kBinnedWarps * 32, 6)
+__global__ void __launch_bounds__(kBinnedWarps * 32, 48 / kBinnedWarps)
 match_to_map_binned_kernel(const Slot* __restrict__ slots, int maxKp, double hammingThreshold) {
   const Slot& slot = slots[blockIdx.z];
   if (slot.map == nullptr) return;
