@@ -133,6 +133,7 @@ def lib():
         L.okc_debug_host_tables.argtypes = [vp, C.POINTER(i), C.POINTER(i), vp, vp, vp]
         L.okc_debug_set_match_prefix.argtypes = [i]
         L.okc_debug_set_select_wave.argtypes = [i]
+        L.okc_debug_set_harris_rows.argtypes = [i]
         L.okc_back_project.argtypes = [vp, vp, vp, i, vp, vp, C.POINTER(i)]
         L.okc_keyframe_overlap.argtypes = [vp, i, vp, vp, vp, vp, vp, vp, vp]
         L.okc_vocabulary_create.argtypes = [vp, i, vp, vp, vp, vp, vp, i, C.POINTER(vp)]

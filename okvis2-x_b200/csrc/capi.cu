@@ -78,6 +78,7 @@ int launch_hamming_best(const void* queries, int nq, const void* map, long long 
                         unsigned long long indexOffset, unsigned long long* best, cudaStream_t s);
 extern int g_match_prefix;
 extern int g_select_wave;
+extern int g_harris_rows;
 }  // namespace okc
 
 extern "C" {
@@ -89,6 +90,13 @@ int okc_version(void) { return 100; }
 int okc_debug_set_select_wave(int on) {
   if (on != 0 && on != 2) return OKC_ERR_INVALID;
   okc::g_select_wave = on;
+  return OKC_OK;
+}
+
+/* Tests: rows of an image one Harris warp walks (0 = chosen per launch by the cost model). */
+int okc_debug_set_harris_rows(int rows) {
+  if (rows < 0 || rows > 4096) return OKC_ERR_INVALID;
+  okc::g_harris_rows = rows;
   return OKC_OK;
 }
 

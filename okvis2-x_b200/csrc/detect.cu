@@ -208,7 +208,10 @@ __global__ void __launch_bounds__(32 * kHarrisWarps) harris_nms_kernel(const Slo
 // Rows per warp: a warp computes rows + 6 halo rows (rounded up to the loop's 3 rows per trip), so tall chunks waste
 // less, but the grid must still fill the GPU in whole waves (8 CTAs of 128 registers x 64 threads per SM) and a
 // small batch wants short chunks for latency. Cost model: trips per warp x waves of CTAs.
+int g_harris_rows = 0;   // tests: force the rows per warp (0 = cost model)
+
 static int harris_rows_per_warp(int W, int H, int n) {
+  if (g_harris_rows > 0) return g_harris_rows;
   static int slots = 0;
   if (slots == 0) {
     int dev = 0, sms = 148;

@@ -259,3 +259,26 @@ def test_selection_kernels_agree(name, cases, mod, ctx):
     finally:
         mod.lib().okc_debug_set_select_wave(0)
         cam.close()
+
+
+@pytest.mark.parametrize("shape", [(480, 752), (41, 131), (540, 720), (101, 250)])
+def test_harris_rows_per_warp_do_not_change_the_result(shape, mod, ctx, syn):
+    """The launcher picks how many image rows a Harris warp walks (8..96, by batch size); scores, NMS candidates and
+    keypoints must not depend on it (halo rows, chunk ends that fall outside the image, 3-row loop trips)."""
+    h, w = shape
+    img = syn.scene_image(w, h, 21)
+    cam = mod.Camera(ctx, w, h, max_keypoints=2048)
+    try:
+        mod.lib().okc_debug_set_harris_rows(0)
+        scores = cam.debug_scores(img)
+        cands = cam.debug_candidates(img, 50)
+        kps = cam.detect(img, 30.0, 0, 50.0, 1500)
+        assert len(cands) > 0
+        for rows in (1, 2, 3, 5, 8, 12, 16, 24, 32, 48, 64, 96, 1000):
+            mod.lib().okc_debug_set_harris_rows(rows)
+            assert np.array_equal(cam.debug_scores(img), scores), rows
+            assert cam.debug_candidates(img, 50).tobytes() == cands.tobytes(), rows
+            assert cam.detect(img, 30.0, 0, 50.0, 1500).tobytes() == kps.tobytes(), rows
+    finally:
+        mod.lib().okc_debug_set_harris_rows(0)
+        cam.close()
