@@ -10,6 +10,7 @@
 // lane adds the pixels of its box directly (<= ~12x12 u8 reads, L1/L2 hits) and no (H+1)x(W+1) int32 image
 // is ever written to HBM. The weighted sum is identical term by term.
 #include "common.cuh"
+#include <type_traits>
 
 namespace okc {
 
@@ -173,23 +174,21 @@ __device__ __forceinline__ BoxWords box_words(const BoxParams& b) {
 // Word form (needs k.nw > 0). Branch-free: always five loads, at word indices clamped to the last word of the
 // segment (a word past the segment has weight 0, and index 4 is always the last word). With "if (i < nw)" around
 // each load the compiler emits a divergent branch per word and every load's latency is exposed in turn.
+template <int NW = kBoxWordsMax>   // NW: loads per row, >= the longest segment of the warp's boxes
 __device__ __forceinline__ void box_row_sums_words(const uint8_t* __restrict__ img, int W, const BoxParams& b,
                                                    const BoxWords& k, int r, unsigned& first, unsigned& last,
                                                    unsigned& mid) {
   const unsigned* wrow = reinterpret_cast<const unsigned*>(img + (size_t)(b.y_top + r) * W) + k.w0;
   const int l = k.nw - 1;
-  const unsigned v0 = __ldg(wrow);
-  const unsigned v1 = __ldg(wrow + min(1, l));
-  const unsigned v2 = __ldg(wrow + min(2, l));
-  const unsigned v3 = __ldg(wrow + min(3, l));
-  const unsigned v4 = __ldg(wrow + l);
-  mid = __dp4a(v0, k.wgt[0], mid);
-  mid = __dp4a(v1, k.wgt[1], mid);
-  mid = __dp4a(v2, k.wgt[2], mid);
-  mid = __dp4a(v3, k.wgt[3], mid);
-  mid = __dp4a(v4, k.wgt[4], mid);
-  first = __dp4a(v0, k.selFirst, first);
-  last = __dp4a(v4, k.selLast, last);
+  unsigned v[NW];
+  v[0] = __ldg(wrow);
+#pragma unroll
+  for (int i = 1; i < NW - 1; ++i) v[i] = __ldg(wrow + min(i, l));
+  if (NW > 1) v[NW - 1] = __ldg(wrow + l);   // index NW-1 is always the last word of the segment
+#pragma unroll
+  for (int i = 0; i < NW; ++i) mid = __dp4a(v[i], k.wgt[i], mid);
+  first = __dp4a(v[0], k.selFirst, first);
+  last = __dp4a(v[NW - 1], k.selLast, last);
 }
 
 // Byte form (unaligned image, or a segment longer than kBoxWordsMax words).
@@ -244,10 +243,19 @@ __device__ __forceinline__ int smoothed_intensity(const uint8_t* __restrict__ im
   const BoxWords k = box_words(b);
   unsigned tf = 0, tl = 0, tm = 0, mf = 0, ml = 0, mm = 0, bf = 0, bl = 0, bm = 0;
   if (kWords && k.nw > 0) {   // decided once per box, so that the row loop is straight-line code
-    box_row_sums_words(img, W, b, k, 0, tf, tl, tm);
-    box_row_sums_words(img, W, b, k, rows - 1, bf, bl, bm);
+    // loads per row = the longest segment among the boxes the warp is summing right now (warp-uniform: no divergence)
+    const int nwMax = __reduce_max_sync(__activemask(), k.nw);
+    auto sum_rows = [&](auto NWc) {
+      constexpr int NW = decltype(NWc)::value;
+      box_row_sums_words<NW>(img, W, b, k, 0, tf, tl, tm);
+      box_row_sums_words<NW>(img, W, b, k, rows - 1, bf, bl, bm);
 #pragma unroll 2
-    for (int r = 1; r < rows - 1; ++r) box_row_sums_words(img, W, b, k, r, mf, ml, mm);
+      for (int r = 1; r < rows - 1; ++r) box_row_sums_words<NW>(img, W, b, k, r, mf, ml, mm);
+    };
+    if (nwMax <= 2) sum_rows(std::integral_constant<int, 2>{});
+    else if (nwMax == 3) sum_rows(std::integral_constant<int, 3>{});
+    else if (nwMax == 4) sum_rows(std::integral_constant<int, 4>{});
+    else sum_rows(std::integral_constant<int, 5>{});
   } else {
     box_row_sums_bytes(img, W, b, 0, tf, tl, tm);
     box_row_sums_bytes(img, W, b, rows - 1, bf, bl, bm);
