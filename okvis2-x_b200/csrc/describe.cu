@@ -147,7 +147,7 @@ __device__ __forceinline__ int box_rows(const BoxParams& b) { return (b.dy > 0 ?
 // Word view of a box: the same for every row (x_left and dx are fixed), so the weights are built once per box.
 struct BoxWords {
   int w0, nw;                   // first 32-bit word of a row segment, number of words (<= kBoxWordsMax, else nw = 0: byte path)
-  unsigned wgt[5];              // 0x01 on the interior bytes (columns x_left+1 .. x_left+dx) of each word
+  int a, e;                     // first and last interior byte (columns x_left+1 .. x_left+dx), counted from word 0
   unsigned selFirst, selLast;   // 0x01 on row[0] in word 0 and on row[dx+1] in word nw-1
 };
 constexpr int kBoxWordsMax = 5;
@@ -157,27 +157,33 @@ __device__ __forceinline__ BoxWords box_words(const BoxParams& b) {
   const int p0 = b.x_left, pl = b.x_left + b.dx + 1;
   k.w0 = p0 >> 2;
   k.nw = (pl >> 2) - k.w0 + 1;
+  k.a = (p0 & 3) + 1;
+  k.e = k.a + b.dx - 1;
   k.selFirst = 1u << (8 * (p0 & 3));
   k.selLast = 1u << (8 * (pl & 3));
-#pragma unroll
-  for (int i = 0; i < kBoxWordsMax; ++i) {
-    const int w = k.w0 + i;
-    const int lo = (p0 + 1 > 4 * w ? p0 + 1 : 4 * w) - 4 * w;
-    const int hi = (pl - 1 < 4 * w + 3 ? pl - 1 : 4 * w + 3) - 4 * w;
-    k.wgt[i] = (i < k.nw && hi >= lo) ? ((0x01010101u >> (8 * (3 - hi))) & (0x01010101u << (8 * lo))) : 0u;
-  }
   if (k.nw > kBoxWordsMax) k.nw = 0;
   return k;
+}
+
+// 0x01 on the interior bytes of the first NW words of a row segment (zero past the segment): built once per box,
+// and only for as many words as the row loop will load.
+template <int NW>
+__device__ __forceinline__ void box_weights(const BoxWords& k, unsigned (&wgt)[NW]) {
+#pragma unroll
+  for (int i = 0; i < NW; ++i) {
+    const int lo = max(k.a - 4 * i, 0), hi = min(k.e - 4 * i, 3);
+    wgt[i] = hi >= lo ? ((0x01010101u >> (8 * (3 - hi))) & (0x01010101u << (8 * lo))) : 0u;
+  }
 }
 
 // Adds row r of the box to three running sums: its first pixel, its last pixel, its interior pixels.
 // Word form (needs k.nw > 0). Branch-free: always five loads, at word indices clamped to the last word of the
 // segment (a word past the segment has weight 0, and index 4 is always the last word). With "if (i < nw)" around
 // each load the compiler emits a divergent branch per word and every load's latency is exposed in turn.
-template <int NW = kBoxWordsMax>   // NW: loads per row, >= the longest segment of the warp's boxes
+template <int NW>   // NW: loads per row, >= the longest segment of the warp's boxes
 __device__ __forceinline__ void box_row_sums_words(const uint8_t* __restrict__ img, int W, const BoxParams& b,
-                                                   const BoxWords& k, int r, unsigned& first, unsigned& last,
-                                                   unsigned& mid) {
+                                                   const BoxWords& k, const unsigned (&wgt)[NW], int r,
+                                                   unsigned& first, unsigned& last, unsigned& mid) {
   const unsigned* wrow = reinterpret_cast<const unsigned*>(img + (size_t)(b.y_top + r) * W) + k.w0;
   const int l = k.nw - 1;
   unsigned v[NW];
@@ -186,7 +192,7 @@ __device__ __forceinline__ void box_row_sums_words(const uint8_t* __restrict__ i
   for (int i = 1; i < NW - 1; ++i) v[i] = __ldg(wrow + min(i, l));
   if (NW > 1) v[NW - 1] = __ldg(wrow + l);   // index NW-1 is always the last word of the segment
 #pragma unroll
-  for (int i = 0; i < NW; ++i) mid = __dp4a(v[i], k.wgt[i], mid);
+  for (int i = 0; i < NW; ++i) mid = __dp4a(v[i], wgt[i], mid);
   first = __dp4a(v[0], k.selFirst, first);
   last = __dp4a(v[NW - 1], k.selLast, last);
 }
@@ -203,8 +209,13 @@ __device__ __forceinline__ void box_row_sums_bytes(const uint8_t* __restrict__ i
 template <bool kWords>
 __device__ __forceinline__ void box_row_sums(const uint8_t* __restrict__ img, int W, const BoxParams& b,
                                              const BoxWords& k, int r, unsigned& first, unsigned& last, unsigned& mid) {
-  if (kWords && k.nw > 0) box_row_sums_words(img, W, b, k, r, first, last, mid);
-  else box_row_sums_bytes(img, W, b, r, first, last, mid);
+  if (kWords && k.nw > 0) {
+    unsigned wgt[kBoxWordsMax];
+    box_weights(k, wgt);
+    box_row_sums_words(img, W, b, k, wgt, r, first, last, mid);
+  } else {
+    box_row_sums_bytes(img, W, b, r, first, last, mid);
+  }
 }
 
 // The two lower corner terms. Reference quirk kept on purpose: on the integral-image path (dx + dy > 2) the two lower
@@ -247,10 +258,12 @@ __device__ __forceinline__ int smoothed_intensity(const uint8_t* __restrict__ im
     const int nwMax = __reduce_max_sync(__activemask(), k.nw);
     auto sum_rows = [&](auto NWc) {
       constexpr int NW = decltype(NWc)::value;
-      box_row_sums_words<NW>(img, W, b, k, 0, tf, tl, tm);
-      box_row_sums_words<NW>(img, W, b, k, rows - 1, bf, bl, bm);
+      unsigned wgt[NW];
+      box_weights(k, wgt);
+      box_row_sums_words(img, W, b, k, wgt, 0, tf, tl, tm);
+      box_row_sums_words(img, W, b, k, wgt, rows - 1, bf, bl, bm);
 #pragma unroll 2
-      for (int r = 1; r < rows - 1; ++r) box_row_sums_words<NW>(img, W, b, k, r, mf, ml, mm);
+      for (int r = 1; r < rows - 1; ++r) box_row_sums_words(img, W, b, k, wgt, r, mf, ml, mm);
     };
     if (nwMax <= 2) sum_rows(std::integral_constant<int, 2>{});
     else if (nwMax == 3) sum_rows(std::integral_constant<int, 3>{});
