@@ -44,7 +44,7 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=500, help="batches of --frames-per-batch stereo frames")
     ap.add_argument("--warmup", type=int, default=12)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--frames-per-batch", type=int, default=32, help="stereo frames per launch chain")
+    ap.add_argument("--frames-per-batch", type=int, default=32, help="stereo frames per launch chain (48 gives +3 % resident, -2 % end to end)")
     ap.add_argument("--in-flight", type=int, default=4, help="batches in flight (one stream each)")
     ap.add_argument("--no-sweep", action="store_true", help="skip the 10k x 1M matcher sweep in `extra`")
     ap.add_argument("--no-cpu-baseline", action="store_true")

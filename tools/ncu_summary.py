@@ -35,7 +35,7 @@ if os.path.exists("gpurun_out/launches.csv"):
         agg.setdefault((row["Kernel Name"].split("(")[0][:60], row.get("Grid Size", "").replace(" ", "")), []).append(v)
     tot = sum(sum(v) for v in agg.values())
     lines += ["## launch list (`ncu --metrics gpu__time_duration.sum --clock-control none`, cold-cache, serialised)", "",
-              "Grouped by grid: grid z (or x for the one-CTA-per-image kernels) = images in the batch; the 64-image rows are",
+              "Grouped by grid: grid z (or x for the one-CTA-per-image kernels) = images in the batch; the rows with the largest batch are",
               "the bench's timed batches, the 2-image rows its single-frame latency measurement.", "",
               "| kernel | grid | launches | mean us | share |", "|---|---|---|---|---|"]
     for (k, g), v in agg.items():
@@ -66,8 +66,16 @@ for f in sorted(os.listdir("gpurun_out")):
         pass
     lines.append("")
 open(os.path.join(out, "summary.md"), "w").write("\n".join(lines))
+# images per launch = 2 x frames_per_batch of the profiled command (its plain run's JSON line is in ncu_plain.log)
+frames = 32
+try:
+    for l in open("gpurun_out/ncu_plain.log"):
+        if l.startswith("{"):
+            frames = int(json.loads(l)["config"]["frames_per_batch"])
+except (OSError, ValueError, KeyError):
+    pass
 json.dump({"_note": "dram__bytes_read.sum + dram__bytes_write.sum per launch from one `ncu --set full` capture per kernel of "
-                    "`python bench.py --steps 6 --warmup 3 --no-cpu-baseline` (tools/ncu_round.sh; frames_per_batch 32 = 64 "
-                    "images per launch); hamming_best_lb from the 10k x 1M sweep of the same run",
-           "images_per_launch": 64, "kernels": traffic}, open(os.path.join(out, "traffic.json"), "w"), indent=1)
+                    "`python bench.py --steps 6 --warmup 3 --no-cpu-baseline` (tools/ncu_round.sh; frames_per_batch %d = %d "
+                    "images per launch); hamming_best_lb from the 10k x 1M sweep of the same run" % (frames, 2 * frames),
+           "images_per_launch": 2 * frames, "kernels": traffic}, open(os.path.join(out, "traffic.json"), "w"), indent=1)
 print("\n".join(lines))
