@@ -180,20 +180,26 @@ __global__ void __launch_bounds__(32 * kHarrisWarps) harris_nms_kernel(const Slo
     // ---- 4. NMS of row q = r-3: top = row r-4, middle = row r-3 (slot B), bottom = row r-2 (slot P) ----
     const int q = r - 3;
     if (q >= q0 && q < q1) {   // warp-uniform
-      unsigned nib = 0;
-      if (emit && q >= 2 && q <= H - 3) {
+      // a row segment without a single score at the threshold has no maxima: one vote instead of the comparisons
+      // and the three shuffles that assemble the bitmap words
+      const int rowMax = max(max(scH[B][0], scH[B][1]), max(scH[B][2], scH[B][3]));
+      unsigned v = 0;
+      if (__any_sync(0xffffffffu, rowMax >= absThreshold)) {
+        unsigned nib = 0;
+        if (emit && q >= 2 && q <= H - 3) {
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {
-          // >= the threshold and >= all 8 neighbours, as one comparison against the largest of them
-          const bool isMax = scH[B][c] >= max(max(mTop[c], mH[P][c]), max(lrH[B][c], absThreshold));
-          nib |= (isMax ? 1u : 0u) << c;
+          for (int c = 0; c < 4; ++c) {
+            // >= the threshold and >= all 8 neighbours, as one comparison against the largest of them
+            const bool isMax = scH[B][c] >= max(max(mTop[c], mH[P][c]), max(lrH[B][c], absThreshold));
+            nib |= (isMax ? 1u : 0u) << c;
+          }
+          nib &= colBits;
         }
-        nib &= colBits;
+        v = nib << (4 * (lane & 7));
+        v |= __shfl_xor_sync(0xffffffffu, v, 1);
+        v |= __shfl_xor_sync(0xffffffffu, v, 2);
+        v |= __shfl_xor_sync(0xffffffffu, v, 4);
       }
-      unsigned v = nib << (4 * (lane & 7));
-      v |= __shfl_xor_sync(0xffffffffu, v, 1);
-      v |= __shfl_xor_sync(0xffffffffu, v, 2);
-      v |= __shfl_xor_sync(0xffffffffu, v, 4);
       if ((lane & 7) == 0) bitmap[(size_t)q * wordsPerRow + strip * kStripWords + (lane >> 3)] = v;
     }
   };
