@@ -571,7 +571,7 @@ void launch_bin_projections(const Slot* slots, int n, cudaStream_t s) {
   if (n > 0) bin_projections_kernel<<<n, kBinThreads, 0, s>>>(slots);
 }
 
-constexpr int kBinnedWarps = 8;
+constexpr int kBinnedWarps = 4;
 constexpr int kMaxHits = 64;   // rows inside the gate with dist < threshold, per keypoint (2 per lane); more: full scan
 
 __global__ void __launch_bounds__(kBinnedWarps * 32, 48 / kBinnedWarps)
