@@ -38,7 +38,7 @@ namespace okc {
 // bitmap with kStripWords words per (row, strip): bit b of word j of strip s is column 120 s - 4 + 32 j + b.
 // Row-major, strip-major, bit-ascending order = raster order, which order_candidates_kernel relies on.
 // output rows per warp: chosen per launch (harris_rows_per_warp), see launch_harris_nms
-constexpr int kHarrisWarps = 2;      // warps per block (independent: no shared memory, no barriers)
+constexpr int kHarrisWarps = 1;      // warps per block (independent: no shared memory, no barriers)
 constexpr int kStripCols = 120;      // output columns per warp
 constexpr int kStripWords = 4;
 
@@ -212,7 +212,7 @@ __global__ void __launch_bounds__(32 * kHarrisWarps) harris_nms_kernel(const Slo
 }
 
 // Rows per warp: a warp computes rows + 6 halo rows (rounded up to the loop's 3 rows per trip), so tall chunks waste
-// less, but the grid must still fill the GPU in whole waves (8 CTAs of 128 registers x 64 threads per SM) and a
+// less, but the grid must still fill the GPU in whole waves (16 one-warp CTAs of 128 registers per SM) and a
 // small batch wants short chunks for latency. Cost model: trips per warp x waves of CTAs.
 int g_harris_rows = 0;   // tests: force the rows per warp (0 = cost model)
 
@@ -223,7 +223,7 @@ static int harris_rows_per_warp(int W, int H, int n) {
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    slots = sms * 8;
+    slots = sms * (16 / kHarrisWarps);
   }
   const int candidates[] = {8, 12, 16, 24, 32, 48, 64, 96};
   int best = 32;
