@@ -225,7 +225,7 @@ static int harris_rows_per_warp(int W, int H, int n) {
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     slots = sms * (16 / kHarrisWarps);
   }
-  const int candidates[] = {8, 12, 16, 24, 32, 48, 64, 96};
+  const int candidates[] = {8, 12, 16, 24, 32, 48, 64, 96, 120, 160, 240};
   int best = 32;
   long long bestCost = -1;
   for (int rows : candidates) {
