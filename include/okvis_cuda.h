@@ -18,6 +18,9 @@
 #ifdef __cplusplus
 extern "C" {
 #endif
+#if defined(__GNUC__)
+#pragma GCC visibility push(default) /* the library itself is built with -fvisibility=hidden */
+#endif
 
 enum {
   OKC_OK = 0,
@@ -360,6 +363,9 @@ void* okc_camera_stream(okc_camera* cam);
 int okc_debug_kernel_timing(okc_camera* cam, int enable);
 int okc_debug_kernel_times(okc_camera* cam, char* names, int names_cap, float* ms, int cap, int* n);
 
+#if defined(__GNUC__)
+#pragma GCC visibility pop
+#endif
 #ifdef __cplusplus
 }
 #endif

@@ -38,7 +38,10 @@ EXPORTS = [
 
 
 class OkcError(RuntimeError):
-    pass
+    """A non-zero status of the C ABI; `code` is the OKC_ERR_* value (1 invalid, 2 CUDA, 3 capacity)."""
+    def __init__(self, message, code=1):
+        super().__init__(message)
+        self.code = code
 
 
 class DetectParams(C.Structure):
@@ -187,7 +190,7 @@ def lib():
 
 def _check(rc, what):
     if rc != 0:
-        raise OkcError("%s failed (code %d): %s" % (what, rc, lib().okc_last_error_string().decode()))
+        raise OkcError("%s failed (code %d): %s" % (what, rc, lib().okc_last_error_string().decode()), rc)
 
 
 def _p(a):

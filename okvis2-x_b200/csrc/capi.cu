@@ -76,29 +76,37 @@ struct okc_descriptor_set {
 namespace okc {
 int launch_hamming_best(const void* queries, int nq, const void* map, long long nm, unsigned threshold,
                         unsigned long long indexOffset, unsigned long long* best, cudaStream_t s);
-extern int g_match_prefix;
-extern int g_select_wave;
-extern int g_harris_rows;
 }  // namespace okc
+
+namespace okc { Knobs g_knobs; }
 
 extern "C" {
 
 const char* okc_last_error_string(void) { return g_err; }
 int okc_version(void) { return 100; }
 
-/* A/B switch for tests: 2 = gather kernel, 0 = sequential-visit stamping kernel. */
-int okc_debug_set_select_wave(int on) {
-  if (on != 0 && on != 2) return OKC_ERR_INVALID;
-  okc::g_select_wave = on;
+/* Test hooks, declared in include/okvis_cuda_debug.h. */
+int okc_debug_set_select_wave(int variant) {   /* 0 = wave kernel (default), 1 = sequential-visit kernel */
+  if (variant != 0 && variant != 1) return OKC_ERR_INVALID;
+  okc::g_knobs.select_sequential = variant;
+  return OKC_OK;
+}
+int okc_debug_set_harris_rows(int rows) {      /* 0 = chosen per launch by the cost model */
+  if (rows < 0 || rows > 4096) return OKC_ERR_INVALID;
+  okc::g_knobs.harris_rows = rows;
+  return OKC_OK;
+}
+int okc_debug_set_match_prefix(int words) {    /* 0 = lower-bound sweep kernel (default), 12 = plain 12-word sweep */
+  if (words != 0 && words != 12) return OKC_ERR_INVALID;
+  okc::g_knobs.match_plain = words == 12 ? 1 : 0;
+  return OKC_OK;
+}
+int okc_debug_set_match_binned(int on) {       /* 1 = spatial bins (default), 0 = scan of every map row */
+  okc::g_knobs.match_tile_scan = on ? 0 : 1;
   return OKC_OK;
 }
 
-/* Tests: rows of an image one Harris warp walks (0 = chosen per launch by the cost model). */
-int okc_debug_set_harris_rows(int rows) {
-  if (rows < 0 || rows > 4096) return OKC_ERR_INVALID;
-  okc::g_harris_rows = rows;
-  return OKC_OK;
-}
+int okc_context_destroy(okc_context* c);
 
 int okc_context_create(int device, okc_context** out) {
   if (!out) return OKC_ERR_INVALID;
@@ -114,24 +122,32 @@ int okc_context_create(int device, okc_context** out) {
   okc_context* c = new (std::nothrow) okc_context();
   if (!c) return OKC_ERR_CUDA;
   c->device = device;
-  OKC_CUDA_TRY(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
-  build_host_tables(&c->host);
-  const HostTables& t = c->host;
-  OKC_CUDA_TRY(cudaMalloc(&c->tables.points, t.points.size() * sizeof(HostPatternPoint)));
-  OKC_CUDA_TRY(cudaMalloc(&c->tables.short_pairs, t.short_pairs.size()));
-  OKC_CUDA_TRY(cudaMalloc(&c->tables.long_pairs, t.long_pairs.size() * sizeof(HostLongPair)));
-  OKC_CUDA_TRY(cudaMalloc(&c->tables.lut, t.lut.size() * sizeof(float)));
-  OKC_CUDA_TRY(cudaMalloc(&c->tables.lut_upper, t.lut_upper.size() * sizeof(float)));
-  OKC_CUDA_TRY(cudaMemcpy(c->tables.lut_upper, t.lut_upper.data(), t.lut_upper.size() * sizeof(float),
-                          cudaMemcpyHostToDevice));
-  OKC_CUDA_TRY(cudaMemcpy(c->tables.points, t.points.data(), t.points.size() * sizeof(HostPatternPoint),
-                          cudaMemcpyHostToDevice));
-  OKC_CUDA_TRY(cudaMemcpy(c->tables.short_pairs, t.short_pairs.data(), t.short_pairs.size(), cudaMemcpyHostToDevice));
-  OKC_CUDA_TRY(cudaMemcpy(c->tables.long_pairs, t.long_pairs.data(), t.long_pairs.size() * sizeof(HostLongPair),
-                          cudaMemcpyHostToDevice));
-  OKC_CUDA_TRY(cudaMemcpy(c->tables.lut, t.lut.data(), t.lut.size() * sizeof(float), cudaMemcpyHostToDevice));
-  c->tables.border = t.border;
-  c->tables.basicscale = t.basicscale;
+  auto build = [&]() -> int {
+    OKC_CUDA_TRY(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    build_host_tables(&c->host);
+    const HostTables& t = c->host;
+    OKC_CUDA_TRY(cudaMalloc(&c->tables.points, t.points.size() * sizeof(HostPatternPoint)));
+    OKC_CUDA_TRY(cudaMalloc(&c->tables.short_pairs, t.short_pairs.size()));
+    OKC_CUDA_TRY(cudaMalloc(&c->tables.long_pairs, t.long_pairs.size() * sizeof(HostLongPair)));
+    OKC_CUDA_TRY(cudaMalloc(&c->tables.lut, t.lut.size() * sizeof(float)));
+    OKC_CUDA_TRY(cudaMalloc(&c->tables.lut_upper, t.lut_upper.size() * sizeof(float)));
+    OKC_CUDA_TRY(cudaMemcpy(c->tables.lut_upper, t.lut_upper.data(), t.lut_upper.size() * sizeof(float),
+                            cudaMemcpyHostToDevice));
+    OKC_CUDA_TRY(cudaMemcpy(c->tables.points, t.points.data(), t.points.size() * sizeof(HostPatternPoint),
+                            cudaMemcpyHostToDevice));
+    OKC_CUDA_TRY(cudaMemcpy(c->tables.short_pairs, t.short_pairs.data(), t.short_pairs.size(), cudaMemcpyHostToDevice));
+    OKC_CUDA_TRY(cudaMemcpy(c->tables.long_pairs, t.long_pairs.data(), t.long_pairs.size() * sizeof(HostLongPair),
+                            cudaMemcpyHostToDevice));
+    OKC_CUDA_TRY(cudaMemcpy(c->tables.lut, t.lut.data(), t.lut.size() * sizeof(float), cudaMemcpyHostToDevice));
+    c->tables.border = t.border;
+    c->tables.basicscale = t.basicscale;
+    return OKC_OK;
+  };
+  const int rc = build();
+  if (rc) {
+    okc_context_destroy(c);   // frees whatever was allocated before the failure
+    return rc;
+  }
   *out = c;
   return OKC_OK;
 }
@@ -139,7 +155,7 @@ int okc_context_create(int device, okc_context** out) {
 int okc_context_destroy(okc_context* c) {
   if (!c) return OKC_OK;
   cudaSetDevice(c->device);
-  cudaStreamSynchronize(c->stream);
+  if (c->stream) cudaStreamSynchronize(c->stream);
   cudaFree(c->tables.points);
   cudaFree(c->tables.short_pairs);
   cudaFree(c->tables.long_pairs);
@@ -147,7 +163,7 @@ int okc_context_destroy(okc_context* c) {
   cudaFree(c->tables.lut_upper);
   for (auto& b : c->d) b.release();
   for (auto& b : c->h) b.release();
-  cudaStreamDestroy(c->stream);
+  if (c->stream) cudaStreamDestroy(c->stream);
   delete c;
   return OKC_OK;
 }

@@ -4,8 +4,10 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <atomic>
 
 #include "../../include/okvis_cuda.h"
+#include "../../include/okvis_cuda_debug.h"
 
 namespace okc {
 
@@ -130,6 +132,16 @@ void launch_scale_nms(const int32_t* scores, uint32_t* bitmap, int W, int H, con
 void launch_concat_layers(const Slot* layers, int nLayers, const Slot& out, int maxOut, cudaStream_t s);
 
 void set_error(const char* fmt, ...);
+
+// Test hooks (include/okvis_cuda_debug.h): A/B baselines of the tests and forced launch shapes. Process-wide and read
+// at launch time; a test sets them while no other call is in flight. Production callers never touch them.
+struct Knobs {
+  std::atomic<int> select_sequential{0};  // 1: one-candidate-at-a-time selection kernel instead of the wave kernel
+  std::atomic<int> match_plain{0};        // 1: plain 12-word Hamming sweep instead of the lower-bound kernel
+  std::atomic<int> match_tile_scan{0};    // 1: frame-pipeline map match scans every row instead of the spatial bins
+  std::atomic<int> harris_rows{0};        // > 0: image rows one Harris warp walks (0: cost model)
+};
+extern Knobs g_knobs;
 
 }  // namespace okc
 

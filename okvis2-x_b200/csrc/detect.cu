@@ -214,17 +214,17 @@ __global__ void __launch_bounds__(32 * kHarrisWarps) harris_nms_kernel(const Slo
 // Rows per warp: a warp computes rows + 6 halo rows (rounded up to the loop's 3 rows per trip), so tall chunks waste
 // less, but the grid must still fill the GPU in whole waves (16 one-warp CTAs of 128 registers per SM) and a
 // small batch wants short chunks for latency. Cost model: trips per warp x waves of CTAs.
-int g_harris_rows = 0;   // tests: force the rows per warp (0 = cost model)
-
 static int harris_rows_per_warp(int W, int H, int n) {
-  if (g_harris_rows > 0) return g_harris_rows;
-  static int slots = 0;
-  if (slots == 0) {
-    int dev = 0, sms = 148;
-    cudaGetDevice(&dev);
+  if (g_knobs.harris_rows > 0) return g_knobs.harris_rows;   // tests: forced rows per warp
+  static int slotsOf[64] = {};   // resident one-warp CTAs per device
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (slotsOf[dev & 63] == 0) {
+    int sms = 148;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    slots = sms * (16 / kHarrisWarps);
+    slotsOf[dev & 63] = sms * (16 / kHarrisWarps);
   }
+  const int slots = slotsOf[dev & 63];
   const int candidates[] = {8, 12, 16, 24, 32, 48, 64, 96, 120, 160, 240};
   int best = 32;
   long long bestCost = -1;
@@ -564,10 +564,13 @@ size_t order_scratch_bytes() {
 }
 
 void launch_order_candidates(const Slot* slots, int n, const DetectArgs& a, cudaStream_t s) {
-  static bool configured = false;
-  if (!configured) {
+  // the attribute is per device (a process may hold contexts on several)
+  static bool configured[64] = {};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (!configured[dev & 63]) {
     cudaFuncSetAttribute(order_candidates_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kOrdSmemBytes);
-    configured = true;
+    configured[dev & 63] = true;
   }
   order_candidates_kernel<<<n, kOrdThreads, kOrdSmemBytes, s>>>(slots, a.width, a.height);
 }
@@ -690,6 +693,7 @@ select_keypoints_kernel(const Slot* __restrict__ slots, const float* __restrict_
   const int tid = threadIdx.x;
   int n = counters[0];
   if (n > kCandCap) n = kCandCap;
+  if (counters[3] == 1) n = 0;   // candidate overflow: cand[] was not written (reported as OKC_ERR_CAPACITY)
   for (int i = tid; i < 31 * 31; i += kSelThreads) lut[i] = lut_global[i];
   if (n == 0) {
     if (tid == 0) counters[1] = 0;
@@ -824,23 +828,35 @@ select_keypoints_kernel(const Slot* __restrict__ slots, const float* __restrict_
 }
 
 // ----------------------------------------------------------------------------------------------
-// Gather form of the greedy loop (default): no occupancy image at all. The occupancy the reference reads at a
-// candidate's cell is min(255, sum over the ACCEPTED earlier candidates a with |dx|,|dy| <= 15 of
-// ceil(LUT[dy+15][dx+15] * 0.99f * nsc1_a)): saturating u8 adds of non-negative values commute, so the sum can be
-// gathered from the accepted points instead of being read from an image they were stamped into. Accepted points go
-// into linked lists per bin of 16x16 occupancy cells; a candidate gathers from the 3x3 bins around its cell.
-// One warp walks the sorted candidates 32 at a time: every lane gathers against the points accepted before the
-// group, then the group is resolved in order - the lowest lane that still passes is accepted (all lower lanes are
-// final), broadcasts itself by shuffle, the higher lanes add its contribution - one iteration per accepted point.
-// No block-wide barrier, no 31x31 stamp: 10-15 us per image instead of 140-210 us for the stamping kernels.
+// Wave form of the greedy loop (default). The reference visits the sorted candidates one by one; a candidate's
+// decision reads the occupancy at ONE cell, and that cell is only ever changed by accepted candidates whose own
+// cell lies within +-15 cells (the 31x31 stamp). So a candidate is FINAL as soon as every lower-index candidate
+// within +-15 cells is decided, and all final candidates of a step can be decided - and stamped - at once.
+//   window : up to 2048 candidates that pass the occupancy pre-test (a failure is final: occupancy only grows),
+//            taken in sorted order, two per thread;
+//   round  : A. every pending entry re-tests its cell (fail -> rejected) and posts its window position into the bin
+//               of its cell with atomicMin (bins of 2^binShift >= 16 cells);
+//            B. an entry whose position is the minimum of the 3x3 bins around it has no lower pending entry within
+//               +-15 cells -> accepted, appended to the round's stamp list;
+//            C. the warps stamp the accepted entries, one entry per warp. Entries accepted in the same round are
+//               > 15 cells apart but their 31x31 footprints may overlap: the stamp is a packed saturating byte add
+//               (__vaddus4) committed per 32-bit word with atomicCAS, so concurrent stamps commute exactly like the
+//               reference's sequential saturating adds.
+//   The lowest pending position is always decided, so a window ends after at most its length in rounds; measured:
+//   30-70 rounds per image (tools/select_wave_model.py) instead of 400-2 500 sequential accept steps.
+//   The cap (kept == maxNumKpt, uniformity-enforcement-inl.h:199) cuts the accepted list in candidate order after a
+//   window: decisions never depend on higher-index candidates, so the first maxKpt accepted are the reference's.
 // ----------------------------------------------------------------------------------------------
-constexpr int kGatThreads = 128;
-constexpr int kGatBinShift = 4;
+constexpr int kWavThreads = 1024;
+constexpr int kWavSlots = 2;                       // window entries per thread
+constexpr int kWavCap = kWavThreads * kWavSlots;
+constexpr int kWavMaxBins = 2048;                  // padded bin grid (one empty bin all around)
 
-__global__ void __launch_bounds__(kGatThreads)
-select_keypoints_gather_kernel(const Slot* __restrict__ slots, const float* __restrict__ lut_global, int W, int H,
-                               float scaling, unsigned long long maxKpt, int maxOut, int nbx, int nby, double kpScale,
-                               double kpOffset, int octave) {
+template <bool kOccInSmem>
+__global__ void __launch_bounds__(kWavThreads, 1)
+select_keypoints_wave_kernel(const Slot* __restrict__ slots, const float* __restrict__ lut_global, int W, int H,
+                             float scaling, unsigned long long maxKpt, int maxOut, int binShift, int nbxP, int nbinsP,
+                             double kpScale, double kpOffset, int octave) {
   const Slot& slot = slots[blockIdx.x];
   const int32_t* __restrict__ scores = slot.scores;
   uint64_t* __restrict__ cand = slot.cand;
@@ -848,142 +864,230 @@ select_keypoints_gather_kernel(const Slot* __restrict__ slots, const float* __re
   okc_keypoint* __restrict__ out = slot.kp_detect;
   extern __shared__ __align__(16) uint8_t smem[];
   __shared__ float lut[31 * 31];
-  __shared__ int s_kept;
-  const int nbins = nbx * nby;
-  uint4* node = reinterpret_cast<uint4*>(smem);                       // maxOut x {cy << 16 | cx, 0.99f * nsc1, next, -}
-  int* head = reinterpret_cast<int*>(smem + (size_t)maxOut * 16);     // nbins list heads (-1 = empty)
+  __shared__ unsigned w_cyx[kWavCap];     // cy << 16 | cx of the window entries, in candidate order
+  __shared__ float w_nsc[kWavCap];        // nsc1
+  __shared__ int s_bin[kWavMaxBins];      // lowest pending window position per bin (INT_MAX: none)
+  __shared__ unsigned short s_acc[kWavCap];
+  __shared__ int s_warpcnt[32], s_warpoff[32], s_total, s_nacc, s_any;
 
-  const int tid = threadIdx.x;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   int n = counters[0];
   if (n > kCandCap) n = kCandCap;
+  if (counters[3] == 1) n = 0;   // candidate overflow: cand[] was not written (reported as OKC_ERR_CAPACITY)
+  for (int i = tid; i < 31 * 31; i += kWavThreads) lut[i] = lut_global[i];
   if (n == 0) {
     if (tid == 0) counters[1] = 0;
     return;
   }
-  for (int i = tid; i < 31 * 31; i += kGatThreads) lut[i] = lut_global[i];
-  for (int b = tid; b < nbins; b += kGatThreads) head[b] = -1;
-  __syncthreads();
-
-  if (tid < 32) {
-    const int lane = tid;
-    const unsigned long long cap = maxKpt ? maxKpt : ~0ull;  // the reference's "kept == maxNumKpt" never fires for 0
-    const float maxScore = (float)cand_score(cand[0]);
-    int kept = 0;
-    bool overflow = false;
-    unsigned accAll = 0u;
-    uint64_t keyNext = lane < n ? cand[lane] : 0ull;
-    for (int base = 0; base < n; base += 32) {
-      const int i = base + lane;
-      const uint64_t key = keyNext;
-      if (base + 32 + lane < n) keyNext = cand[base + 32 + lane];   // prefetch the next group
-      int cx = 0, cy = 0, sum = 0;
-      float nsc1 = 0.0f;
-      bool pending = false;
-      if (i < n) {
-        const int score = cand_score(key);
-        const uint32_t raster = (uint32_t)key;
-        const int y = raster / W, x = raster - y * W;
-        cy = (int)((float)y * scaling + 16.0f);
-        cx = (int)((float)x * scaling + 16.0f);
-        nsc1 = sqrtf(sqrtf((float)score / maxScore)) * 255.0f;
-        // gather from the points accepted before this group
-        const int bx = cx >> kGatBinShift, by = cy >> kGatBinShift;
-        pending = true;
-        for (int yy = by - 1; yy <= by + 1 && pending; ++yy) {
-          if (yy < 0 || yy >= nby) continue;
-          for (int xx = bx - 1; xx <= bx + 1 && pending; ++xx) {
-            if (xx < 0 || xx >= nbx) continue;
-            for (int a = head[yy * nbx + xx]; a >= 0;) {
-              const uint4 nd = node[a];
-              const int dx = cx - (int)(nd.x & 0xffffu) + 15, dy = cy - (int)(nd.x >> 16) + 15;
-              if ((unsigned)dx < 31u && (unsigned)dy < 31u) {
-                const float v = ceilf(lut[dy * 31 + dx] * __uint_as_float(nd.y));
-                sum += (v == v) ? ((int)v & 0xff) : 0;  // NaN -> 0, as cvttss2si + byte truncation
-                if (nsc1 < (float)(sum > 255 ? 255 : sum)) {  // fails now: fails for good (sums only grow)
-                  pending = false;
-                  break;
-                }
-              }
-              a = (int)nd.z;
-            }
-          }
-        }
-      }
-      // resolve the group in candidate order, several acceptances per step: near = lanes whose cell lies within
-      // +-15 of mine (only those can change my sum); a pending lane with no LOWER pending lane in `near` is final.
-      unsigned near = 0;
-#pragma unroll 8
-      for (int l = 0; l < 32; ++l) {
-        const int ox = __shfl_sync(0xffffffffu, cx, l), oy = __shfl_sync(0xffffffffu, cy, l);
-        if ((unsigned)(cx - ox + 15) < 31u && (unsigned)(cy - oy + 15) < 31u) near |= 1u << l;
-      }
-      const unsigned lower = (1u << lane) - 1u;
-      const float myn = 0.99f * nsc1;
-      for (;;) {
-        const unsigned pmask = __ballot_sync(0xffffffffu, pending);
-        if (pmask == 0u) break;
-        const unsigned amask = __ballot_sync(0xffffffffu, pending && (near & pmask & lower) == 0u);  // never empty
-        if ((amask >> lane) & 1u) pending = false;
-        // the lanes accepted in this step that are below me and in range add their stamp value at my cell
-        unsigned todo = pending ? (amask & near & lower) : 0u;
-        while (__any_sync(0xffffffffu, todo != 0u)) {
-          const int src = todo ? __ffs(todo) - 1 : lane;
-          const int ox = __shfl_sync(0xffffffffu, cx, src), oy = __shfl_sync(0xffffffffu, cy, src);
-          const float on = __shfl_sync(0xffffffffu, myn, src);
-          if (todo) {
-            todo &= todo - 1u;
-            const float v = ceilf(lut[(cy - oy + 15) * 31 + (cx - ox + 15)] * on);
-            sum += (v == v) ? ((int)v & 0xff) : 0;
-          }
-        }
-        if (pending && nsc1 < (float)(sum > 255 ? 255 : sum)) pending = false;
-        accAll |= amask;
-      }
-      // The group's accepted set does not depend on the cap (a lane never depends on higher lanes): cut it in
-      // candidate order, then number the survivors in candidate order = the reference's acceptance order.
-      {
-        const unsigned long long room = cap - (unsigned long long)kept;
-        if ((unsigned long long)__popc(accAll) > room) {
-          unsigned m = accAll;
-          for (unsigned long long k = 0; k < room; ++k) m &= m - 1u;
-          accAll &= ~m;
-        }
-        const int na = __popc(accAll);
-        if (kept + na > maxOut) {   // more keypoints than the handle can hold: flagged, the host raises OKC_ERR_CAPACITY
-          overflow = true;
-        } else {
-          // insert in lane order; same-bin lanes chain correctly because each insertion completes before the next
-          unsigned m = accAll;
-          while (m) {
-            const int l = __ffs(m) - 1;
-            m &= m - 1u;
-            if (lane == l) {
-              const int k = kept + __popc(accAll & lower);
-              const int bb = (cy >> kGatBinShift) * nbx + (cx >> kGatBinShift);
-              cand[kCandCap + k] = key;   // kept list lives behind the keys
-              node[k] = make_uint4(((unsigned)cy << 16) | (unsigned)cx, __float_as_uint(myn), (unsigned)head[bb], 0u);
-              head[bb] = k;
-            }
-            __syncwarp();
-          }
-          kept += na;
-        }
-        accAll = 0u;
-      }
-      __syncwarp();   // list insertions visible to the next group's gather
-      if (overflow || (unsigned long long)kept == cap) break;
-    }
-    if (lane == 0) {
-      s_kept = kept;
-      counters[1] = kept;
-      if (overflow) counters[3] = 2;
-    }
+  const int occRows = (int)((float)(H - 3) * scaling + 16.0f) + 16 + 1;
+  const int occStride = (((int)((float)(W - 3) * scaling + 16.0f) + 16 + 1) + 15) & ~15;
+  const size_t occBytes = (size_t)occRows * occStride;
+  uint8_t* occ = kOccInSmem ? smem : slot.occupancy;
+  unsigned* occw = reinterpret_cast<unsigned*>(occ);
+  // global fallback: the stamps are L2 atomics, so the reads must not be served by a stale L1 line
+  auto occ_at = [&](int o) -> int { return kOccInSmem ? (int)occ[o] : (int)__ldcg(occ + o); };
+  for (size_t i = (size_t)tid * 16; i < occBytes; i += (size_t)kWavThreads * 16)
+    *reinterpret_cast<uint4*>(occ + i) = make_uint4(0, 0, 0, 0);
+  for (int b = tid; b < nbinsP; b += kWavThreads) s_bin[b] = 0x7fffffff;
+  if (tid == 0) {
+    s_nacc = 0;
+    s_any = 0;
   }
   __syncthreads();
 
+  const float maxScore = (float)cand_score(cand[0]);
+  const unsigned long long cap = maxKpt ? maxKpt : ~0ull;   // "kept == maxNumKpt" never fires for 0
+  const unsigned ltMask = (1u << lane) - 1u;
+  const int strideW = occStride >> 2;
+  unsigned long long kept = 0;
+  int pos = 0, rounds = 0;
+
+  // exclusive block scan of a flag in thread order; every thread gets the total
+  auto scan = [&](bool flag, int& total) -> int {
+    const unsigned ballot = __ballot_sync(0xffffffffu, flag);
+    if (lane == 0) s_warpcnt[warp] = __popc(ballot);
+    __syncthreads();
+    if (warp == 0) {
+      const int c = s_warpcnt[lane];
+      int incl = c;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d) incl += t;
+      }
+      s_warpoff[lane] = incl - c;
+      if (lane == 31) s_total = incl;
+    }
+    __syncthreads();
+    const int r = s_warpoff[warp] + __popc(ballot & ltMask);
+    total = s_total;
+    __syncthreads();   // s_warpcnt / s_total may be rewritten by the next scan
+    return r;
+  };
+
+  while (pos < n && kept < cap) {
+    // ---- fill the window with candidates that pass the pre-test, in candidate order ----
+    int wcount = 0;
+    int myIdx[kWavSlots];   // candidate index of the thread's own entries (position tid + h * kWavThreads)
+    while (pos < n && wcount <= kWavCap - kWavThreads) {
+      const int i = pos + tid;
+      bool alive = false;
+      unsigned cyx = 0;
+      float nsc1 = 0.0f;
+      if (i < n) {
+        const uint64_t key = cand[i];
+        const int score = cand_score(key);
+        const uint32_t raster = (uint32_t)key;
+        const int y = raster / W, x = raster - y * W;
+        const int cy = (int)((float)y * scaling + 16.0f);
+        const int cx = (int)((float)x * scaling + 16.0f);
+        cyx = ((unsigned)cy << 16) | (unsigned)cx;
+        nsc1 = sqrtf(sqrtf((float)score / maxScore)) * 255.0f;
+        alive = !(nsc1 < (float)occ_at(cy * occStride + cx));
+      }
+      int total;
+      const int p = wcount + scan(alive, total);
+      if (alive) {
+        w_cyx[p] = cyx;
+        w_nsc[p] = nsc1;
+        // entry p is owned by thread p % kWavThreads, which keeps the candidate index in a register: hand it over
+        // as the offset inside the chunk (< kWavThreads) through the stamp list, idle during the fill
+        s_acc[p] = (unsigned short)tid;
+      }
+      __syncthreads();
+#pragma unroll
+      for (int h = 0; h < kWavSlots; ++h) {
+        const int e = tid + h * kWavThreads;
+        if (e >= wcount && e < wcount + total) myIdx[h] = pos + (int)s_acc[e];
+      }
+      wcount += total;
+      pos += kWavThreads;
+      __syncthreads();
+    }
+    if (wcount == 0) break;   // pos >= n and nothing left to decide
+
+    int st[kWavSlots], off[kWavSlots], bin[kWavSlots];   // st: 0 none / rejected, 1 pending, 2 accepted
+    float nsc1[kWavSlots];
+#pragma unroll
+    for (int h = 0; h < kWavSlots; ++h) {
+      const int e = tid + h * kWavThreads;
+      st[h] = e < wcount ? 1 : 0;
+      off[h] = 0;
+      bin[h] = 0;
+      nsc1[h] = 0.0f;
+      if (st[h]) {
+        const unsigned cyx = w_cyx[e];
+        const int cy = (int)(cyx >> 16), cx = (int)(cyx & 0xffffu);
+        off[h] = cy * occStride + cx;
+        bin[h] = ((cy >> binShift) + 1) * nbxP + (cx >> binShift) + 1;
+        nsc1[h] = w_nsc[e];
+      }
+    }
+
+    // ---- rounds ----
+    for (;;) {
+      ++rounds;
+      // A. re-test, post the position of the entries that are still pending
+#pragma unroll
+      for (int h = 0; h < kWavSlots; ++h) {
+        if (st[h] == 1) {
+          if (nsc1[h] < (float)occ_at(off[h])) st[h] = 0;
+          else atomicMin(&s_bin[bin[h]], tid + h * kWavThreads);
+        }
+      }
+      __syncthreads();
+      // B. final = lowest pending position of the 3x3 bins
+      bool waiting = false;
+#pragma unroll
+      for (int h = 0; h < kWavSlots; ++h) {
+        if (st[h] == 1) {
+          const int e = tid + h * kWavThreads;
+          const int* b = &s_bin[bin[h] - nbxP - 1];
+          int m = min(min(b[0], b[1]), b[2]);
+          b += nbxP;
+          m = min(m, min(min(b[0], b[1]), b[2]));
+          b += nbxP;
+          m = min(m, min(min(b[0], b[1]), b[2]));
+          if (m == e) {
+            st[h] = 2;
+            s_acc[atomicAdd(&s_nacc, 1)] = (unsigned short)e;
+          } else {
+            waiting = true;
+          }
+        }
+      }
+      if (waiting) s_any = 1;
+      __syncthreads();
+      const int nacc = s_nacc;
+      const bool again = s_any != 0;
+      // C. clear the bins for the next round; stamp the accepted entries, one per warp
+      for (int b = tid; b < nbinsP; b += kWavThreads) s_bin[b] = 0x7fffffff;
+      for (int a = warp; a < nacc; a += kWavThreads / 32) {
+        const int e = (int)s_acc[a];
+        const unsigned cyx = w_cyx[e];
+        const float nsc = 0.99f * w_nsc[e];
+        if (!(nsc == nsc)) continue;   // a NaN stamp adds 0 everywhere (cvttss2si + byte truncation in the reference)
+        const int cy = (int)(cyx >> 16), cx = (int)(cyx & 0xffffu);
+        const int first = (cy - 15) * occStride + (cx - 15);
+        const int al = first & 3;              // the same for every row: occStride % 16 == 0
+        unsigned* rowW = occw + (first >> 2);
+        // 31 rows x 9 words (the 31 bytes of a row span 8 or 9 aligned words) = 279 word updates over 32 lanes
+#pragma unroll 3
+        for (int it = 0; it < 9; ++it) {
+          const int t = lane + 32 * it;
+          if (t < 31 * 9) {
+            const int r = t / 9, w = t - r * 9;
+            unsigned add = 0;
+#pragma unroll
+            for (int bb = 0; bb < 4; ++bb) {
+              const int col = 4 * w + bb - al;
+              if ((unsigned)col < 31u) add |= ((unsigned)(int)ceilf(lut[r * 31 + col] * nsc) & 0xffu) << (8 * bb);
+            }
+            if (add) {
+              unsigned* pw = rowW + r * strideW + w;
+              unsigned old = kOccInSmem ? *pw : __ldcg(pw);
+              for (;;) {
+                const unsigned want = __vaddus4(old, add);
+                if (want == old) break;
+                const unsigned seen = atomicCAS(pw, old, want);
+                if (seen == old) break;
+                old = seen;
+              }
+            }
+          }
+        }
+      }
+      __syncthreads();
+      if (tid == 0) {
+        s_nacc = 0;
+        s_any = 0;
+      }
+      if (!again) break;
+    }
+
+    // ---- the window's accepted entries, in candidate order, behind the keys ----
+#pragma unroll
+    for (int h = 0; h < kWavSlots; ++h) {
+      int total;
+      const int r = scan(st[h] == 2, total);
+      if (st[h] == 2) {
+        const unsigned long long k = kept + (unsigned long long)r;
+        if (k < cap && k < (unsigned long long)maxOut) cand[kCandCap + k] = cand[myIdx[h]];
+      }
+      kept += (unsigned long long)total;
+    }
+    if (kept > cap) kept = cap;
+  }
+
   // ---- sub-pixel refinement -> cv::KeyPoint (scale-space-layer-inl.h:394-420) ----
-  const int nOut = s_kept;
-  for (int i = tid; i < nOut; i += kGatThreads) {
+  const int nOut = kept < (unsigned long long)maxOut ? (int)kept : maxOut;
+  if (tid == 0) {
+    counters[1] = nOut;
+    counters[5] = rounds;   // diagnostic (okc_debug_batch_counter)
+    if (kept > (unsigned long long)maxOut) counters[3] = 2;
+  }
+  __syncthreads();   // (block-wide: the kept list was written by other threads)
+  for (int i = tid; i < nOut; i += kWavThreads) {
     const uint64_t key = cand[kCandCap + i];
     const int score = cand_score(key);
     const uint32_t raster = (uint32_t)key;
@@ -993,6 +1097,7 @@ select_keypoints_gather_kernel(const Slot* __restrict__ slots, const float* __re
     subpixel2d((double)c[-W - 1], (double)c[-W], (double)c[-W + 1], (double)c[-1], (double)c[0], (double)c[1],
                (double)c[W - 1], (double)c[W], (double)c[W + 1], dx, dy);
     okc_keypoint kp;
+    // _scale * ((it->x + delta_x) + _offset): (float + float) widened, the rest in double, narrowed on assignment
     kp.x = (float)(kpScale * ((double)((float)u + dx) + kpOffset));
     kp.y = (float)(kpScale * ((double)((float)v + dy) + kpOffset));
     kp.size = (float)(kpScale * 12.0);
@@ -1004,56 +1109,55 @@ select_keypoints_gather_kernel(const Slot* __restrict__ slots, const float* __re
   }
 }
 
-int g_select_wave = 0;  // 0 = sequential-visit stamping kernel (default), 2 = gather kernel (no occupancy image; A/B tested)
-
-static int g_select_smem = 0;
-
 void launch_select_keypoints(const Slot* slots, int n, const float* lut, const DetectArgs& a, cudaStream_t s) {
-  static const bool envRead = [] {
-    if (const char* e = getenv("OKC_SELECT")) g_select_wave = atoi(e);
-    return true;
-  }();
-  (void)envRead;
-  if (g_select_wave == 2) {
-    const size_t rows = (size_t)((float)(a.height - 3) * a.scaling + 16.0f) + 17;
-    const size_t cols = (size_t)((float)(a.width - 3) * a.scaling + 16.0f) + 17;
-    const int nbx = (int)((cols + 15) >> 4), nby = (int)((rows + 15) >> 4);
-    const size_t smem = (size_t)a.max_out * 16 + (size_t)nbx * nby * 4;
-    static int gatherMax = 0;
-    if (gatherMax == 0) {
-      int dev = 0, maxOptin = 0;
-      cudaGetDevice(&dev);
-      cudaDeviceGetAttribute(&maxOptin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
-      gatherMax = maxOptin - 8192;
-      cudaFuncSetAttribute(select_keypoints_gather_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, gatherMax);
-    }
-    if (smem <= (size_t)gatherMax) {
-      select_keypoints_gather_kernel<<<n, kGatThreads, smem, s>>>(slots, lut, a.width, a.height, a.scaling, a.max_kpt,
-                                                                 a.max_out, nbx, nby, a.kp_scale, a.kp_offset, a.octave);
-      return;
-    }
-  }
-  if (g_select_smem == 0) {
-    int dev = 0, maxOptin = 0;
-    cudaGetDevice(&dev);
+  int dev = 0;
+  cudaGetDevice(&dev);
+  static int s_dyn[2][64] = {};   // per device: dynamic shared memory granted to the two <true> kernels
+  const size_t occRows = (size_t)((float)(a.height - 3) * a.scaling + 16.0f) + 17;
+  const size_t occCols = (size_t)((float)(a.width - 3) * a.scaling + 16.0f) + 17;
+  const size_t occStride = (occCols + 15) & ~(size_t)15;
+  const size_t want = (occRows * occStride + 15) & ~(size_t)15;
+  const int which = g_knobs.select_sequential ? 1 : 0;   // 1: the sequential-visit kernel, A/B baseline of the tests
+  int& granted = s_dyn[which][dev & 63];
+  if (granted == 0) {
+    int maxOptin = 0;
     cudaDeviceGetAttribute(&maxOptin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
     cudaFuncAttributes fa;
-    cudaFuncGetAttributes(&fa, select_keypoints_kernel<true>);
-    g_select_smem = (maxOptin - (int)fa.sharedSizeBytes - 1024) & ~15;  // dynamic part beside the static arrays
-    cudaFuncSetAttribute(select_keypoints_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, g_select_smem);
+    if (which == 1) cudaFuncGetAttributes(&fa, select_keypoints_kernel<true>);
+    else cudaFuncGetAttributes(&fa, select_keypoints_wave_kernel<true>);
+    granted = (maxOptin - (int)fa.sharedSizeBytes - 1024) & ~15;  // dynamic part beside the static arrays
+    if (which == 1)
+      cudaFuncSetAttribute(select_keypoints_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, granted);
+    else
+      cudaFuncSetAttribute(select_keypoints_wave_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, granted);
   }
-  // only as much dynamic shared memory as the occupancy image needs (more CTAs per SM when several images
-  // are selected at once); the global fallback is used when it does not fit
-  const size_t occRows = (size_t)((float)(a.height - 3) * a.scaling + 16.0f) + 17;
-  const size_t occStride = (((size_t)((float)(a.width - 3) * a.scaling + 16.0f) + 17) + 15) & ~(size_t)15;
-  size_t want = occRows * occStride;
-  int smem = want <= (size_t)g_select_smem ? (int)((want + 15) & ~(size_t)15) : 0;
+  // only as much dynamic shared memory as the occupancy image needs; the global fallback when it does not fit
+  const int smem = want <= (size_t)granted ? (int)want : 0;
+  if (which == 1) {
+    if (smem > 0)
+      select_keypoints_kernel<true><<<n, kSelThreads, smem, s>>>(slots, lut, a.width, a.height, a.scaling, a.max_kpt,
+                                                                 a.max_out, smem, a.kp_scale, a.kp_offset, a.octave);
+    else
+      select_keypoints_kernel<false><<<n, kSelThreads, 0, s>>>(slots, lut, a.width, a.height, a.scaling, a.max_kpt,
+                                                               a.max_out, 0, a.kp_scale, a.kp_offset, a.octave);
+    return;
+  }
+  // bins of 2^shift >= 16 occupancy cells, one empty bin all around, at most kWavMaxBins in total
+  int shift = 4, nbxP = 0, nbinsP = 0;
+  for (;; ++shift) {
+    nbxP = (int)((occCols + ((size_t)1 << shift) - 1) >> shift) + 2;
+    const int nbyP = (int)((occRows + ((size_t)1 << shift) - 1) >> shift) + 2;
+    nbinsP = nbxP * nbyP;
+    if (nbinsP <= kWavMaxBins) break;
+  }
   if (smem > 0)
-    select_keypoints_kernel<true><<<n, kSelThreads, smem, s>>>(slots, lut, a.width, a.height, a.scaling, a.max_kpt,
-                                                               a.max_out, smem, a.kp_scale, a.kp_offset, a.octave);
+    select_keypoints_wave_kernel<true><<<n, kWavThreads, smem, s>>>(slots, lut, a.width, a.height, a.scaling,
+                                                                   a.max_kpt, a.max_out, shift, nbxP, nbinsP,
+                                                                   a.kp_scale, a.kp_offset, a.octave);
   else
-    select_keypoints_kernel<false><<<n, kSelThreads, 0, s>>>(slots, lut, a.width, a.height, a.scaling, a.max_kpt,
-                                                             a.max_out, 0, a.kp_scale, a.kp_offset, a.octave);
+    select_keypoints_wave_kernel<false><<<n, kWavThreads, 0, s>>>(slots, lut, a.width, a.height, a.scaling,
+                                                                 a.max_kpt, a.max_out, shift, nbxP, nbinsP,
+                                                                 a.kp_scale, a.kp_offset, a.octave);
 }
 
 // ----------------------------------------------------------------------------------------------

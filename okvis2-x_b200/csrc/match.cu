@@ -296,7 +296,7 @@ static int pick_rows_per_chunk(int nq, long long nm, int ctasPerSm) {
   // Aim at 16 waves of 148 SMs x resident CTAs (measured: 2 waves 1189, 4 -> 1270, 16 -> 1350 Gpairs/s on the
   // 10k x 1M sweep: the tail of the last wave is what small grids lose), chunks a multiple of the stage size.
   const long long qTiles = (nq + kMbQTile - 1) / kMbQTile;
-  static const int waves = getenv("OKC_SWEEP_WAVES") ? atoi(getenv("OKC_SWEEP_WAVES")) : 16;
+  const int waves = 16;
   long long wantChunks = (148LL * ctasPerSm * waves + qTiles - 1) / qTiles;
   long long rows = (nm + wantChunks - 1) / wantChunks;
   rows = ((rows + kMbRows - 1) / kMbRows) * kMbRows;
@@ -305,25 +305,18 @@ static int pick_rows_per_chunk(int nq, long long nm, int ctasPerSm) {
   return (int)rows;
 }
 
-int g_match_prefix = 0;  // 0 = 2-POPC lower bound (default); 5 = carry-save prefix; 4/6/8/12 = plain prefixes (experiments)
-
 int launch_hamming_best(const void* queries, int nq, const void* map, long long nm, unsigned threshold,
                         unsigned long long indexOffset, unsigned long long* best, cudaStream_t s) {
   if (nq <= 0) return 0;
   cudaMemsetAsync(best, 0xff, sizeof(unsigned long long) * (size_t)nq, s);
   if (nm <= 0) return 0;
-  const int rowsPerChunk = pick_rows_per_chunk(nq, nm, g_match_prefix == 0 ? 3 : 2);
+  const bool plain = g_knobs.match_plain != 0;   // tests: the plain 12-word sweep as the A/B baseline
+  const int rowsPerChunk = pick_rows_per_chunk(nq, nm, plain ? 2 : 3);
   dim3 grid((unsigned)((nm + rowsPerChunk - 1) / rowsPerChunk), (unsigned)((nq + kMbQTile - 1) / kMbQTile));
   const uint4* q4 = static_cast<const uint4*>(queries);
   const uint4* m4 = static_cast<const uint4*>(map);
-  switch (g_match_prefix) {
-    case 0: hamming_best_lb_kernel<<<grid, kMbThreads, 0, s>>>(q4, nq, m4, nm, rowsPerChunk, threshold, indexOffset, best); break;
-    case 4: hamming_best_kernel<4><<<grid, kMbThreads, 0, s>>>(q4, nq, m4, nm, rowsPerChunk, threshold, indexOffset, best); break;
-    case 6: hamming_best_kernel<6><<<grid, kMbThreads, 0, s>>>(q4, nq, m4, nm, rowsPerChunk, threshold, indexOffset, best); break;
-    case 8: hamming_best_kernel<8><<<grid, kMbThreads, 0, s>>>(q4, nq, m4, nm, rowsPerChunk, threshold, indexOffset, best); break;
-    case 12: hamming_best_kernel<12><<<grid, kMbThreads, 0, s>>>(q4, nq, m4, nm, rowsPerChunk, threshold, indexOffset, best); break;
-    case 5: default: hamming_best_kernel<5><<<grid, kMbThreads, 0, s>>>(q4, nq, m4, nm, rowsPerChunk, threshold, indexOffset, best); break;
-  }
+  if (plain) hamming_best_kernel<12><<<grid, kMbThreads, 0, s>>>(q4, nq, m4, nm, rowsPerChunk, threshold, indexOffset, best);
+  else hamming_best_lb_kernel<<<grid, kMbThreads, 0, s>>>(q4, nq, m4, nm, rowsPerChunk, threshold, indexOffset, best);
   return (int)(grid.x * grid.y);
 }
 
@@ -811,10 +804,12 @@ __global__ void __launch_bounds__(kStatsThreads, 1) match_stats_kernel(const Slo
 
 void launch_match_stats(const Slot* slots, int n, cudaStream_t s) {
   if (n <= 0) return;
-  static bool configured = false;
-  if (!configured) {
+  static bool configured[64] = {};   // the attribute is per device
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (!configured[dev & 63]) {
     cudaFuncSetAttribute(match_stats_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kStatsSmemEvents * 16);
-    configured = true;
+    configured[dev & 63] = true;
   }
   match_stats_kernel<<<n, kStatsThreads, kStatsSmemEvents * 16, s>>>(slots);   // keys + distances
 }

@@ -10,10 +10,13 @@ import pytest
 from conftest import ROOT
 
 
-def declared_symbols():
-    src = open(os.path.join(ROOT, "include", "okvis_cuda.h")).read()
-    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
-    return sorted(set(re.findall(r"\b(okc_[a-z0-9_]+)\s*\(", src)))
+def declared_symbols(headers=("okvis_cuda.h", "okvis_cuda_debug.h")):
+    names = set()
+    for h in headers:
+        src = open(os.path.join(ROOT, "include", h)).read()
+        src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+        names |= set(re.findall(r"\b(okc_[a-z0-9_]+)\s*\(", src))
+    return sorted(names)
 
 
 def test_header_symbols_are_exported(mod):
@@ -24,6 +27,15 @@ def test_header_symbols_are_exported(mod):
         assert hasattr(L, n), "libokvis_cuda.so does not export %s" % n
     for n in mod.EXPORTS:
         assert n in names, "%s is bound by the host mirror but not declared in the header" % n
+
+
+def test_exports_are_exactly_the_declared_symbols(mod):
+    """The library is built with -fvisibility=hidden: nothing but the entry points of include/*.h is exported (no
+    undeclared test switches, no internal C++ symbols)."""
+    import subprocess
+    out = subprocess.run(["nm", "-D", "--defined-only", mod.LIB_PATH], capture_output=True, text=True).stdout
+    exported = sorted(l.split()[2] for l in out.splitlines() if len(l.split()) == 3 and l.split()[1] == "T")
+    assert exported == declared_symbols()
 
 
 def test_struct_layouts_match_header(mod):

@@ -157,11 +157,37 @@ def test_edge_cases(mod, ctx, ref, syn):
     # capacity overflow is reported, not truncated silently
     with pytest.raises(mod.OkcError):
         cam.detect(img, 2.0, 0, 1.0, 100000)
-    # more octaves than the image can carry is refused loudly
-    with pytest.raises(mod.OkcError):
-        cam2.detect(img, 10.0, 6, 20.0, 700)
+    # more octaves than the image can carry is refused loudly - every time, and the camera stays usable
+    # (a refused pyramid must not be left half-built behind the handle)
+    for _ in range(3):
+        with pytest.raises(mod.OkcError):
+            cam2.detect(img, 10.0, 6, 20.0, 700)
+    kp_assert_close(cam2.detect(img, 10.0, 1, 20.0, 700), ref.detect(img, 10.0, 1, 20.0, 700), TOL)
+    kp_assert_close(cam2.detect(img, 10.0, 0, 20.0, 700), ref.detect(img, 10.0, 0, 20.0, 700), TOL)
     cam.close()
     cam2.close()
+
+
+@pytest.mark.parametrize("variant", [0, 1])
+def test_candidate_overflow_is_reported_and_survivable(variant, mod, ctx, ref, syn):
+    """More than 131 072 NMS maxima (a flat image with threshold 0: every pixel is a plateau maximum,
+    harris-score-calculator.cc:90-110 keeps ties) is OKC_ERR_CAPACITY from both selection kernels - no stale or
+    unwritten candidate keys are consumed - and the same handle then detects normally."""
+    flat = np.full((480, 752), 90, np.uint8)
+    img = syn.scene_image(752, 480, 31)
+    cam = mod.Camera(ctx, 752, 480, max_keypoints=1024)
+    try:
+        mod.lib().okc_debug_set_select_wave(variant)
+        for _ in range(2):
+            with pytest.raises(mod.OkcError) as e:
+                cam.detect(flat, 38.0, 0, 0.0, 700)
+            assert e.value.code == 3  # OKC_ERR_CAPACITY
+            with pytest.raises(mod.OkcError):
+                cam.detect_describe(flat, 38.0, 0, 0.0, 700)
+        kp_assert_close(cam.detect(img, 38.0, 0, 150.0, 700), ref.detect(img, 38.0, 0, 150.0, 700), TOL)
+    finally:
+        mod.lib().okc_debug_set_select_wave(0)
+        cam.close()
 
 
 def cam_describe_ref_equal(mod, ctx, ref, img, rkp):
@@ -240,18 +266,18 @@ def test_scale_space_detect(name, octaves, cases, mod, ctx, ref):
 
 @pytest.mark.parametrize("name", CASE_NAMES)
 def test_selection_kernels_agree(name, cases, mod, ctx):
-    """The gather form of the uniformity selection (no occupancy image) against the sequential-visit stamping
-    kernel, which follows the reference loop literally: same keypoints, same order, binding and non-binding keypoint
-    caps, small radius (dense acceptance) included."""
+    """The wave form of the uniformity selection (many final candidates decided and stamped per round) against the
+    sequential-visit stamping kernel, which follows the reference loop literally: same keypoints, same order, binding
+    and non-binding keypoint caps, small radius (dense acceptance) included."""
     cfg, img = cases[name]
     h, w = img.shape
     cam = mod.Camera(ctx, w, h, max_keypoints=4096)
     try:
         for radius, thr, cap in [(cfg["radius"], cfg["abs_threshold"], cfg["max_kpt"]), (cfg["radius"], 5.0, 50),
                                  (20.0, cfg["abs_threshold"], 4000), (cfg["radius"], 1.0, 0)]:
-            mod.lib().okc_debug_set_select_wave(0)
+            mod.lib().okc_debug_set_select_wave(1)
             want = cam.detect(img, radius, 0, thr, cap)
-            for variant in (2,):
+            for variant in (0,):
                 mod.lib().okc_debug_set_select_wave(variant)
                 got = cam.detect(img, radius, 0, thr, cap)
                 assert len(got) == len(want), (variant, radius, thr, cap, len(got), len(want))

@@ -15,7 +15,7 @@ for name, (cfg, img) in cases.items():
     cam = mod.Camera(ctx, w, h, max_keypoints=4096)
     b = mod.Batch(ctx, [cam])
     res = {}
-    for wave in (0, 2):
+    for wave in (0, 1):
         mod.lib().okc_debug_set_select_wave(wave)
         b.kernel_timing(True)
         ts = []
@@ -26,7 +26,7 @@ for name, (cfg, img) in cases.items():
         v = [C.c_int(0) for _ in range(3)]
         for k, which in enumerate((0, 1, 5)):
             mod.lib().okc_debug_batch_counter(b.h, 0, which, C.byref(v[k]))
-        res[("seq", "wave", "gather")[wave]] = {"select_us": round(1e3 * float(np.median([t["select_keypoints"] for t in ts[2:]])), 1),
+        res[("wave", "seq")[wave]] = {"select_us": round(1e3 * float(np.median([t["select_keypoints"] for t in ts[2:]])), 1),
                                          "candidates": v[0].value, "kept": v[1].value, "rounds": v[2].value}
         b.kernel_timing(False)
     out[name] = res
