@@ -115,6 +115,7 @@ void harris_bitmap_pos(int W, int x, int y, size_t* word, int* bit);
 size_t order_scratch_bytes();
 void launch_order_candidates(const Slot* slots, int n, const DetectArgs& a, cudaStream_t s);
 void launch_select_keypoints(const Slot* slots, int n, const float* lut, const DetectArgs& a, cudaStream_t s);
+size_t select_scratch_bytes(const DetectArgs& a);   // per-slot Slot::occupancy bytes
 // kp_from_detect: describe the keypoints the detector left in kp_detect (count = counters[1])
 void launch_describe(const Slot* slots, int n, const PatternTables& t, const DescribeArgs& a, int max_kp,
                      cudaStream_t s);

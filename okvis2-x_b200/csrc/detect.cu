@@ -13,6 +13,7 @@
 //                        one CTA per image runs the greedy occupancy loop with the occupancy image in
 //                        shared memory, then refines.
 #include "common.cuh"
+#include <cstdio>
 #include <cstdlib>
 #include <type_traits>
 
@@ -586,14 +587,14 @@ constexpr int kSelCells = (31 * 31 + kSelThreads - 1) / kSelThreads;   // stamp 
 __device__ void subpixel2d(double s_0_0, double s_0_1, double s_0_2, double s_1_0, double s_1_1, double s_1_2,
                            double s_2_0, double s_2_1, double s_2_2, float& delta_x, float& delta_y) {
   double tmp1 = s_0_0 + s_0_2 - 2 * s_1_1 + s_2_0 + s_2_2;
-  double coeff1 = 3 * (tmp1 + s_0_1 - ((s_1_0 + s_1_2) / 2.0) + s_2_1);
-  double coeff2 = 3 * (tmp1 - ((s_0_1 + s_2_1) / 2.0) + s_1_0 + s_1_2);
+  double coeff1 = 3 * (tmp1 + s_0_1 - ((s_1_0 + s_1_2) * 0.5) + s_2_1);   // (x / 2.0: exact either way)
+  double coeff2 = 3 * (tmp1 - ((s_0_1 + s_2_1) * 0.5) + s_1_0 + s_1_2);
   double tmp2 = s_0_2 - s_2_0;
   double tmp3 = (s_0_0 + tmp2 - s_2_2);
   double tmp4 = tmp3 - 2 * tmp2;
   double coeff3 = -3 * (tmp3 + s_0_1 - s_2_1);
   double coeff4 = -3 * (tmp4 + s_1_0 - s_1_2);
-  double coeff5 = (s_0_0 - s_0_2 - s_2_0 + s_2_2) / 4.0;
+  double coeff5 = (s_0_0 - s_0_2 - s_2_0 + s_2_2) * 0.25;                  // (x / 4.0: exact either way)
   double H_det = 4 * coeff1 * coeff2 - coeff5 * coeff5;
   if (H_det == 0) {
     delta_x = 0.0f;
@@ -828,336 +829,570 @@ select_keypoints_kernel(const Slot* __restrict__ slots, const float* __restrict_
 }
 
 // ----------------------------------------------------------------------------------------------
-// Wave form of the greedy loop (default). The reference visits the sorted candidates one by one; a candidate's
-// decision reads the occupancy at ONE cell, and that cell is only ever changed by accepted candidates whose own
-// cell lies within +-15 cells (the 31x31 stamp). So a candidate is FINAL as soon as every lower-index candidate
-// within +-15 cells is decided, and all final candidates of a step can be decided - and stamped - at once.
-//   window : up to 2048 candidates that pass the occupancy pre-test (a failure is final: occupancy only grows),
-//            taken in sorted order, two per thread;
-//   round  : A. every pending entry re-tests its cell (fail -> rejected) and posts its window position into the bin
-//               of its cell with atomicMin (bins of 2^binShift >= 16 cells);
-//            B. an entry whose position is the minimum of the 3x3 bins around it has no lower pending entry within
-//               +-15 cells -> accepted, appended to the round's stamp list;
-//            C. the warps stamp the accepted entries, one entry per warp. Entries accepted in the same round are
-//               > 15 cells apart but their 31x31 footprints may overlap: the stamp is a packed saturating byte add
-//               (__vaddus4) committed per 32-bit word with atomicCAS, so concurrent stamps commute exactly like the
-//               reference's sequential saturating adds.
-//   The lowest pending position is always decided, so a window ends after at most its length in rounds; measured:
-//   30-70 rounds per image (tools/select_wave_model.py) instead of 400-2 500 sequential accept steps.
+// Dependency form of the greedy loop (default): no occupancy image, no 31x31 stamps, no barrier per decision.
+//
+// The reference visits the sorted candidates one by one; a candidate's decision reads the occupancy at ONE cell, and
+// that byte is min(255, sum of the stamp values of the ACCEPTED earlier candidates whose own cell lies within +-15
+// cells) - saturating adds of non-negative values commute. So a candidate only depends on the lower-position
+// candidates within +-15 cells ("blockers"), and once those are decided its own decision is final.
+//   window  : up to 1024 candidates in sorted order, one per thread. A new candidate is first tested against a lower
+//             bound of the occupancy (one read), then gathers its exact sum from the points accepted in earlier
+//             windows (CSR by spatial bin) and is dropped if that already rejects it (the sum only grows, so the
+//             reference would reject it at its turn).
+//   blockers: the window entries are binned (CSR over bins of >= 16 cells); every entry lists its blockers from the
+//             3x3 bins around it (an entry with more than blkCap of them - a dense cluster - keeps no list and
+//             re-reads the bins instead).
+//   resolve : every thread sweeps the blocker lists of its undecided entries: a rejected blocker is dropped, an
+//             accepted one adds ceil(LUT * 0.99 nsc1) and is dropped, an undecided one stays. Then the entry is
+//             rejected if nsc1 < min(255, sum) (early: more stamps cannot lower the sum), accepted when the list is
+//             empty. States only ever go 0 -> 1 or 0 -> 2 and are the only shared mutable data, so the warps sweep
+//             without any barrier until their entries are decided; the lowest undecided entry always has no
+//             undecided blocker, hence progress. The number of sweeps is the dependency depth (20-40,
+//             tools/select_worklist_model.py) instead of 400-2 500 sequential accept steps with a 961-cell stamp each.
 //   The cap (kept == maxNumKpt, uniformity-enforcement-inl.h:199) cuts the accepted list in candidate order after a
 //   window: decisions never depend on higher-index candidates, so the first maxKpt accepted are the reference's.
 // ----------------------------------------------------------------------------------------------
-constexpr int kWavThreads = 1024;
-constexpr int kWavSlots = 2;                       // window entries per thread
-constexpr int kWavCap = kWavThreads * kWavSlots;
-constexpr int kWavMaxBins = 2048;                  // padded bin grid (one empty bin all around)
+constexpr int kWlThreads = 1024;
+constexpr int kWlCap = kWlThreads;                // window capacity: one entry per thread
+constexpr int kWlMaxBins = 2048;                  // padded bin grid (one empty bin all around)
+constexpr int kWlMaxBlk = 48, kWlMinBlk = 8;      // blocker list capacity per entry (sized to the free shared memory)
 
-template <bool kOccInSmem>
-__global__ void __launch_bounds__(kWavThreads, 1)
+constexpr int kWlMinLut = 16 * 81;                // [py][px][by + 4][bx + 4], see the kernel
+
+struct WlSmem {                                   // dynamic shared memory: 2 x maxOut nodes | WlSmem | lower-bound image | blocker lists
+  float lut[31 * 31 + 3];
+  unsigned cyx[kWlCap];                           // cy << 16 | cx, window entries in candidate order
+  float nsc[kWlCap];                              // nsc1
+  int sum[kWlCap];                                // stamps received from the points of earlier windows
+  int state[kWlCap];                              // 0 undecided, 1 rejected, 2 accepted
+  int idx[kWlCap];                                // candidate index
+  int binStart[kWlMaxBins + 4];                   // CSR of the window entries by bin
+  int binFill[kWlMaxBins];
+  uint2 binEnt[kWlCap];                           // CSR payload: {cy << 16 | cx, position}
+  int binStartA[kWlMaxBins + 4];                  // CSR of the points accepted in earlier windows by bin
+  unsigned short nblk[kWlCap];                    // blockers found per entry (may exceed the list capacity)
+  float minLut[kWlMinLut];                        // smallest LUT value a point at (py, px) of its 4x4 block stamps into block (by, bx)
+  unsigned char nzBlock[16][81];                  // per (py, px): the blocks with a positive minLut, as (by + 4) << 4 | (bx + 4)
+  int nzCount[16];
+  int warpcnt[32], warpoff[32], total, posNext;
+};
+
+__device__ __forceinline__ int wl_stamp(const float* lut, int dy, int dx, float nsc) {
+  const float v = ceilf(lut[dy * 31 + dx] * nsc);
+  return (v == v) ? ((int)v & 0xff) : 0;          // NaN adds 0 (cvttss2si + byte truncation in the reference)
+}
+
+#ifdef OKC_SELECT_TRACE
+#define WL_T(i) do { if (tid == 0) tr[i] += clock64() - t0; t0 = clock64(); } while (0)
+#else
+#define WL_T(i) do { } while (0)
+#endif
+
+__global__ void __launch_bounds__(kWlThreads, 1)
 select_keypoints_wave_kernel(const Slot* __restrict__ slots, const float* __restrict__ lut_global, int W, int H,
                              float scaling, unsigned long long maxKpt, int maxOut, int binShift, int nbxP, int nbinsP,
-                             double kpScale, double kpOffset, int octave) {
+                             int blkCap, int lbW, int lbH) {
   const Slot& slot = slots[blockIdx.x];
-  const int32_t* __restrict__ scores = slot.scores;
   uint64_t* __restrict__ cand = slot.cand;
   int* __restrict__ counters = slot.counters;
-  okc_keypoint* __restrict__ out = slot.kp_detect;
   extern __shared__ __align__(16) uint8_t smem[];
-  __shared__ float lut[31 * 31];
-  __shared__ unsigned w_cyx[kWavCap];     // cy << 16 | cx of the window entries, in candidate order
-  __shared__ float w_nsc[kWavCap];        // nsc1
-  __shared__ int s_bin[kWavMaxBins];      // lowest pending window position per bin (INT_MAX: none)
-  __shared__ unsigned short s_acc[kWavCap];
-  __shared__ int s_warpcnt[32], s_warpoff[32], s_total, s_nacc, s_any;
+  uint2* node = reinterpret_cast<uint2*>(smem);   // accepted points {cy << 16 | cx, 0.99f * nsc1} in acceptance order
+  uint2* nodeS = node + maxOut;                   // the same, grouped by bin (CSR binStartA), rebuilt after a window
+  WlSmem& S = *reinterpret_cast<WlSmem*>(smem + 2 * (size_t)maxOut * sizeof(uint2));
+  // lower bound of the occupancy per 4x4 block of cells (four blocks of margin all around), see step 5
+  int* lb = reinterpret_cast<int*>(smem + 2 * (size_t)maxOut * sizeof(uint2) + sizeof(WlSmem));
+  // blocker lists, entry-minor: blk[i * kWlCap + e] = i-th remaining blocker of entry e
+  unsigned short* blk = reinterpret_cast<unsigned short*>(lb + (size_t)lbW * lbH);
+  volatile int* vstate = S.state;
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+#ifdef OKC_SELECT_TRACE
+  long long tr[12] = {}, t0 = clock64();
+#endif
   int n = counters[0];
   if (n > kCandCap) n = kCandCap;
   if (counters[3] == 1) n = 0;   // candidate overflow: cand[] was not written (reported as OKC_ERR_CAPACITY)
-  for (int i = tid; i < 31 * 31; i += kWavThreads) lut[i] = lut_global[i];
   if (n == 0) {
     if (tid == 0) counters[1] = 0;
     return;
   }
-  const int occRows = (int)((float)(H - 3) * scaling + 16.0f) + 16 + 1;
-  const int occStride = (((int)((float)(W - 3) * scaling + 16.0f) + 16 + 1) + 15) & ~15;
-  const size_t occBytes = (size_t)occRows * occStride;
-  uint8_t* occ = kOccInSmem ? smem : slot.occupancy;
-  unsigned* occw = reinterpret_cast<unsigned*>(occ);
-  // global fallback: the stamps are L2 atomics, so the reads must not be served by a stale L1 line
-  auto occ_at = [&](int o) -> int { return kOccInSmem ? (int)occ[o] : (int)__ldcg(occ + o); };
-  for (size_t i = (size_t)tid * 16; i < occBytes; i += (size_t)kWavThreads * 16)
-    *reinterpret_cast<uint4*>(occ + i) = make_uint4(0, 0, 0, 0);
-  for (int b = tid; b < nbinsP; b += kWavThreads) s_bin[b] = 0x7fffffff;
-  if (tid == 0) {
-    s_nacc = 0;
-    s_any = 0;
-  }
+  for (int i = tid; i < 31 * 31; i += kWlThreads) S.lut[i] = lut_global[i];
   __syncthreads();
 
   const float maxScore = (float)cand_score(cand[0]);
   const unsigned long long cap = maxKpt ? maxKpt : ~0ull;   // "kept == maxNumKpt" never fires for 0
   const unsigned ltMask = (1u << lane) - 1u;
-  const int strideW = occStride >> 2;
   unsigned long long kept = 0;
-  int pos = 0, rounds = 0;
+  int pos = 0, sweeps = 0, windows = 0;
+  bool overflow = false, lbReady = false;
+  // (a positive maximum keeps every stamp value below 256: no byte wrap, which the lower bound could not follow)
+  const bool lbUsable = maxScore > 0.0f;
 
   // exclusive block scan of a flag in thread order; every thread gets the total
   auto scan = [&](bool flag, int& total) -> int {
     const unsigned ballot = __ballot_sync(0xffffffffu, flag);
-    if (lane == 0) s_warpcnt[warp] = __popc(ballot);
+    if (lane == 0) S.warpcnt[warp] = __popc(ballot);
     __syncthreads();
     if (warp == 0) {
-      const int c = s_warpcnt[lane];
+      const int c = S.warpcnt[lane];
       int incl = c;
 #pragma unroll
       for (int d = 1; d < 32; d <<= 1) {
         const int t = __shfl_up_sync(0xffffffffu, incl, d);
         if (lane >= d) incl += t;
       }
-      s_warpoff[lane] = incl - c;
-      if (lane == 31) s_total = incl;
+      S.warpoff[lane] = incl - c;
+      if (lane == 31) S.total = incl;
     }
     __syncthreads();
-    const int r = s_warpoff[warp] + __popc(ballot & ltMask);
-    total = s_total;
-    __syncthreads();   // s_warpcnt / s_total may be rewritten by the next scan
+    const int r = S.warpoff[warp] + __popc(ballot & ltMask);
+    total = S.total;
+    __syncthreads();   // warpcnt / total may be rewritten by the next scan
     return r;
   };
+  auto bin_of = [&](unsigned cyx) -> int {
+    return ((int)((cyx >> 16) >> binShift) + 1) * nbxP + ((int)((cyx & 0xffffu) >> binShift) + 1);
+  };
+  // exclusive scan of S.binFill[0 .. nbinsP) -> start[0 .. nbinsP], two bins per thread (start[nbinsP] = total)
+  auto scan_bins = [&](int* start) {
+    const int b0 = 2 * tid, b1 = 2 * tid + 1;
+    const int c0 = b0 < nbinsP ? S.binFill[b0] : 0, c1 = b1 < nbinsP ? S.binFill[b1] : 0;
+    int incl = c0 + c1;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const int t = __shfl_up_sync(0xffffffffu, incl, d);
+      if (lane >= d) incl += t;
+    }
+    if (lane == 31) S.warpcnt[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+      const int c = S.warpcnt[lane];
+      int iv = c;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, iv, d);
+        if (lane >= d) iv += t;
+      }
+      S.warpoff[lane] = iv - c;
+    }
+    __syncthreads();
+    const int ex = S.warpoff[warp] + incl - (c0 + c1);
+    if (b0 <= nbinsP) start[b0] = ex;
+    if (b1 <= nbinsP) start[b1] = ex + c0;
+    __syncthreads();
+  };
 
-  while (pos < n && kept < cap) {
-    // ---- fill the window with candidates that pass the pre-test, in candidate order ----
+  while (pos < n && kept < cap && !overflow) {
+    // ---- 1. fill the window with candidates in order.
+    //   stage  : chunks of 1024 candidates are pre-tested against the lower bound of the occupancy (step 5, one read
+    //            each) and the survivors collected until 1024 are staged;
+    //   gather : every staged candidate sums the stamps of the points accepted in earlier windows that lie in the 3x3
+    //            bins around it (walked as one range, four points in flight) and is dropped as soon as the sum
+    //            rejects it: the sum only grows, so the reference would reject it at its turn;
+    //   the rest enters the window. ----
     int wcount = 0;
-    int myIdx[kWavSlots];   // candidate index of the thread's own entries (position tid + h * kWavThreads)
-    while (pos < n && wcount <= kWavCap - kWavThreads) {
-      const int i = pos + tid;
-      bool alive = false;
+    int* stIdx = reinterpret_cast<int*>(blk);   // staging (the blocker lists are idle here): candidate index,
+    uint2* stEnt = S.binEnt;                    // {cell, nsc1}
+    while (pos < n && wcount < kWlCap) {
+      int staged = 0;
+      while (pos < n && staged < kWlCap) {
+        const int i = pos + tid;
+        bool pass = false;
+        unsigned cyx = 0;
+        float nsc1 = 0.0f;
+        if (i < n) {
+          const uint64_t key = cand[i];
+          const int score = cand_score(key);
+          const uint32_t raster = (uint32_t)key;
+          const int y = raster / W, x = raster - y * W;
+          const int cy = (int)((float)y * scaling + 16.0f);
+          const int cx = (int)((float)x * scaling + 16.0f);
+          cyx = ((unsigned)cy << 16) | (unsigned)cx;
+          nsc1 = sqrtf(sqrtf((float)score / maxScore)) * 255.0f;
+          // the occupancy at the candidate's cell is at least the lower bound of its 4x4 block: a candidate that fails
+          // against the bound fails against the occupancy
+          pass = !(lbReady && lbUsable && nsc1 < (float)min(lb[((cy >> 2) + 4) * lbW + (cx >> 2) + 4], 255));
+        }
+        int total;
+        const int sp = staged + scan(pass, total);
+        if (pass) {
+          if (sp < kWlCap) {
+            stEnt[sp] = make_uint2(cyx, __float_as_uint(nsc1));
+            stIdx[sp] = i;
+          } else if (sp == kWlCap) {
+            S.posNext = i;   // the stage is full: this chunk's tail goes back to the list
+          }
+        }
+        staged += total;
+        pos += kWlThreads;
+        if (!lbReady) break;   // (no accepted points yet: nothing to pre-test or gather, a chunk is a stage)
+      }
+      __syncthreads();
+      if (staged > kWlCap) {
+        staged = kWlCap;
+        pos = S.posNext;
+      }
+      bool alive = tid < staged;
       unsigned cyx = 0;
       float nsc1 = 0.0f;
-      if (i < n) {
-        const uint64_t key = cand[i];
-        const int score = cand_score(key);
-        const uint32_t raster = (uint32_t)key;
-        const int y = raster / W, x = raster - y * W;
-        const int cy = (int)((float)y * scaling + 16.0f);
-        const int cx = (int)((float)x * scaling + 16.0f);
-        cyx = ((unsigned)cy << 16) | (unsigned)cx;
-        nsc1 = sqrtf(sqrtf((float)score / maxScore)) * 255.0f;
-        alive = !(nsc1 < (float)occ_at(cy * occStride + cx));
+      int sum = 0, idx = 0;
+      if (alive) {
+        const uint2 c = stEnt[tid];
+        cyx = c.x;
+        nsc1 = __uint_as_float(c.y);
+        idx = stIdx[tid];
+        if (kept > 0) {
+          const int cx = (int)(cyx & 0xffffu), cy = (int)(cyx >> 16);
+          const int bin = bin_of(cyx);
+          const int a0 = S.binStartA[bin - nbxP - 1], n0 = S.binStartA[bin - nbxP + 2] - a0;
+          const int a1 = S.binStartA[bin - 1], n1 = S.binStartA[bin + 2] - a1;
+          const int a2 = S.binStartA[bin + nbxP - 1], n2 = S.binStartA[bin + nbxP + 2] - a2;
+          const int n01 = n0 + n1, nAll = n01 + n2;
+          for (int t = 0; t < nAll && alive; t += 4) {
+            uint2 nd[4];   // four points in flight: the loop is a chain of shared-memory latencies otherwise
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              const int tt = t + u;
+              const int j = tt < n0 ? a0 + tt : (tt < n01 ? a1 + (tt - n0) : a2 + (tt - n01));
+              nd[u] = tt < nAll ? nodeS[j] : make_uint2(0xffffffffu, 0u);
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              const int dx = cx - (int)(nd[u].x & 0xffffu) + 15, dy = cy - (int)(nd[u].x >> 16) + 15;
+              if ((unsigned)dx < 31u && (unsigned)dy < 31u) sum += wl_stamp(S.lut, dy, dx, __uint_as_float(nd[u].y));
+            }
+            if (nsc1 < (float)min(sum, 255)) alive = false;
+          }
+        }
       }
+      __syncthreads();   // (every thread has read its staged candidate: the stage may be refilled)
       int total;
       const int p = wcount + scan(alive, total);
       if (alive) {
-        w_cyx[p] = cyx;
-        w_nsc[p] = nsc1;
-        // entry p is owned by thread p % kWavThreads, which keeps the candidate index in a register: hand it over
-        // as the offset inside the chunk (< kWavThreads) through the stamp list, idle during the fill
-        s_acc[p] = (unsigned short)tid;
-      }
-      __syncthreads();
-#pragma unroll
-      for (int h = 0; h < kWavSlots; ++h) {
-        const int e = tid + h * kWavThreads;
-        if (e >= wcount && e < wcount + total) myIdx[h] = pos + (int)s_acc[e];
-      }
-      wcount += total;
-      pos += kWavThreads;
-      __syncthreads();
-    }
-    if (wcount == 0) break;   // pos >= n and nothing left to decide
-
-    int st[kWavSlots], off[kWavSlots], bin[kWavSlots];   // st: 0 none / rejected, 1 pending, 2 accepted
-    float nsc1[kWavSlots];
-#pragma unroll
-    for (int h = 0; h < kWavSlots; ++h) {
-      const int e = tid + h * kWavThreads;
-      st[h] = e < wcount ? 1 : 0;
-      off[h] = 0;
-      bin[h] = 0;
-      nsc1[h] = 0.0f;
-      if (st[h]) {
-        const unsigned cyx = w_cyx[e];
-        const int cy = (int)(cyx >> 16), cx = (int)(cyx & 0xffffu);
-        off[h] = cy * occStride + cx;
-        bin[h] = ((cy >> binShift) + 1) * nbxP + (cx >> binShift) + 1;
-        nsc1[h] = w_nsc[e];
-      }
-    }
-
-    // ---- rounds ----
-    for (;;) {
-      ++rounds;
-      // A. re-test, post the position of the entries that are still pending
-#pragma unroll
-      for (int h = 0; h < kWavSlots; ++h) {
-        if (st[h] == 1) {
-          if (nsc1[h] < (float)occ_at(off[h])) st[h] = 0;
-          else atomicMin(&s_bin[bin[h]], tid + h * kWavThreads);
+        if (p < kWlCap) {
+          S.cyx[p] = cyx;
+          S.nsc[p] = nsc1;
+          S.sum[p] = sum;
+          S.state[p] = 0;
+          S.idx[p] = idx;
+        } else if (p == kWlCap) {
+          S.posNext = idx;   // the window is full: the rest of the stage goes back to the list
         }
       }
-      __syncthreads();
-      // B. final = lowest pending position of the 3x3 bins
-      bool waiting = false;
+      wcount += total;
+      if (wcount > kWlCap) {
+        __syncthreads();
+        pos = S.posNext;
+      }
+    }
+    if (wcount == 0) break;   // pos >= n and nothing left to decide
+    for (int b = tid; b < nbinsP; b += kWlThreads) S.binFill[b] = 0;
+    ++windows;
+    if (wcount > kWlCap) wcount = kWlCap;
+    __syncthreads();
+    WL_T(1);
+
+    // ---- 2. CSR of the window entries by bin ----
+    const int e = tid;           // this thread's entry (position in the window)
+    const bool live = e < wcount;
+    const unsigned myCyx = live ? S.cyx[e] : 0u;
+    const float myNsc = live ? S.nsc[e] : 0.0f;
+    const int myBin = bin_of(myCyx);
+    const int cx = (int)(myCyx & 0xffffu), cy = (int)(myCyx >> 16);
+    const int sum0 = live ? S.sum[e] : 0;
+    const int mySlot = live ? atomicAdd(&S.binFill[myBin], 1) : 0;
+    __syncthreads();
+    scan_bins(S.binStart);
+    if (live) S.binEnt[S.binStart[myBin] + mySlot] = make_uint2(myCyx, (unsigned)e);
+    __syncthreads();
+    WL_T(2);
+
+    // ---- 3. blocker lists: lower-position entries within +-15 cells. Built in CSR order - the lanes of a warp take
+    //         entries of the same or the next bin, so they walk (nearly) the same ranges without divergence ----
+    if (tid < wcount) {
+      const uint2 me = S.binEnt[tid];
+      const int ee = (int)me.y;
+      const int cxm = (int)(me.x & 0xffffu) - 15, cym = (int)(me.x >> 16) - 15;
+      const int bin = bin_of(me.x);
+      unsigned short* list = blk + ee;
+      int c = 0;
+      for (int row = -1; row <= 1; ++row) {
+        const int bb = bin + row * nbxP;
+        const int j1 = S.binStart[bb + 2];
+        for (int j = S.binStart[bb - 1]; j < j1; j += 4) {
+          uint2 ent[4];   // four entries in flight
 #pragma unroll
-      for (int h = 0; h < kWavSlots; ++h) {
-        if (st[h] == 1) {
-          const int e = tid + h * kWavThreads;
-          const int* b = &s_bin[bin[h] - nbxP - 1];
-          int m = min(min(b[0], b[1]), b[2]);
-          b += nbxP;
-          m = min(m, min(min(b[0], b[1]), b[2]));
-          b += nbxP;
-          m = min(m, min(min(b[0], b[1]), b[2]));
-          if (m == e) {
-            st[h] = 2;
-            s_acc[atomicAdd(&s_nacc, 1)] = (unsigned short)e;
-          } else {
-            waiting = true;
+          for (int u = 0; u < 4; ++u) ent[u] = j + u < j1 ? S.binEnt[j + u] : make_uint2(0u, 0x7fffffffu);
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            const unsigned dx = (unsigned)((int)(ent[u].x & 0xffffu) - cxm), dy = (unsigned)((int)(ent[u].x >> 16) - cym);
+            if ((int)ent[u].y < ee && dx < 31u && dy < 31u) {
+              if (c < blkCap) list[c * kWlCap] = (unsigned short)ent[u].y;
+              ++c;
+            }
           }
         }
       }
-      if (waiting) s_any = 1;
-      __syncthreads();
-      const int nacc = s_nacc;
-      const bool again = s_any != 0;
-      // C. clear the bins for the next round; stamp the accepted entries, one per warp
-      for (int b = tid; b < nbinsP; b += kWavThreads) s_bin[b] = 0x7fffffff;
-      for (int a = warp; a < nacc; a += kWavThreads / 32) {
-        const int e = (int)s_acc[a];
-        const unsigned cyx = w_cyx[e];
-        const float nsc = 0.99f * w_nsc[e];
-        if (!(nsc == nsc)) continue;   // a NaN stamp adds 0 everywhere (cvttss2si + byte truncation in the reference)
-        const int cy = (int)(cyx >> 16), cx = (int)(cyx & 0xffffu);
-        const int first = (cy - 15) * occStride + (cx - 15);
-        const int al = first & 3;              // the same for every row: occStride % 16 == 0
-        unsigned* rowW = occw + (first >> 2);
-        // 31 rows x 9 words (the 31 bytes of a row span 8 or 9 aligned words) = 279 word updates over 32 lanes
-#pragma unroll 3
-        for (int it = 0; it < 9; ++it) {
-          const int t = lane + 32 * it;
-          if (t < 31 * 9) {
-            const int r = t / 9, w = t - r * 9;
-            unsigned add = 0;
+      S.nblk[ee] = (unsigned short)c;
+    }
+    __syncthreads();
+    WL_T(3);
+
+    // ---- 4. resolve: barrier-free sweeps over the blocker lists ----
+    {
+      bool und = live;
+      int nb = live ? (int)S.nblk[e] : 0;   // > blkCap: the list does not hold every blocker (a dense cluster)
+      int sum = sum0;
+      const float nsc1 = myNsc;
+      for (;;) {
+        ++sweeps;
+        if (und) {
+          int total = sum;
+          bool blocked;
+          if (nb <= blkCap) {
+            int w = 0;
+            for (int i0 = 0; i0 < nb; i0 += 8) {
+              int q[8], st[8];   // eight blockers in flight (two dependent shared-memory reads each)
 #pragma unroll
-            for (int bb = 0; bb < 4; ++bb) {
-              const int col = 4 * w + bb - al;
-              if ((unsigned)col < 31u) add |= ((unsigned)(int)ceilf(lut[r * 31 + col] * nsc) & 0xffu) << (8 * bb);
+              for (int u = 0; u < 8; ++u) q[u] = i0 + u < nb ? (int)blk[(i0 + u) * kWlCap + e] : 0;
+#pragma unroll
+              for (int u = 0; u < 8; ++u) st[u] = i0 + u < nb ? vstate[q[u]] : 1;
+#pragma unroll
+              for (int u = 0; u < 8; ++u) {
+                if (st[u] == 0) {
+                  blk[w * kWlCap + e] = (unsigned short)q[u];
+                  ++w;
+                } else if (st[u] == 2) {
+                  const unsigned o = S.cyx[q[u]];
+                  total += wl_stamp(S.lut, cy - (int)(o >> 16) + 15, cx - (int)(o & 0xffffu) + 15, 0.99f * S.nsc[q[u]]);
+                }
+              }
             }
-            if (add) {
-              unsigned* pw = rowW + r * strideW + w;
-              unsigned old = kOccInSmem ? *pw : __ldcg(pw);
-              for (;;) {
-                const unsigned want = __vaddus4(old, add);
-                if (want == old) break;
-                const unsigned seen = atomicCAS(pw, old, want);
-                if (seen == old) break;
-                old = seen;
+            nb = w;
+            sum = total;
+            blocked = w != 0;
+          } else {
+            // no complete list: the sum of the blockers accepted so far, from the bins; it is a lower bound of the
+            // final sum, and the final sum once no blocker is undecided
+            blocked = false;
+            for (int row = -1; row <= 1; ++row) {
+              const int bb = myBin + row * nbxP;
+              const int j1 = S.binStart[bb + 2];
+              for (int j = S.binStart[bb - 1]; j < j1; ++j) {
+                const uint2 ent = S.binEnt[j];
+                const int dx = cx - (int)(ent.x & 0xffffu) + 15, dy = cy - (int)(ent.x >> 16) + 15;
+                if ((int)ent.y < e && (unsigned)dx < 31u && (unsigned)dy < 31u) {
+                  const int st = vstate[ent.y];
+                  if (st == 0) blocked = true;
+                  else if (st == 2) total += wl_stamp(S.lut, dy, dx, 0.99f * S.nsc[ent.y]);
+                }
               }
             }
           }
+          if (nsc1 < (float)min(total, 255)) {
+            vstate[e] = 1;
+            und = false;
+          } else if (!blocked) {
+            vstate[e] = 2;
+            und = false;
+          }
+        }
+        if (!__any_sync(0xffffffffu, und)) break;
+      }
+    }
+    WL_T(4);
+    __syncthreads();
+    WL_T(5);
+
+    // ---- 5. the window's accepted entries, in candidate order: kept list (behind the keys) + nodes ----
+    const bool acc = live && S.state[e] == 2;
+    int totalAcc;
+    const int rank = scan(acc, totalAcc);
+    if (acc) {
+      const unsigned long long k = kept + (unsigned long long)rank;
+      if (k < cap && k < (unsigned long long)maxOut) {
+        cand[kCandCap + k] = cand[S.idx[e]];
+        node[k] = make_uint2(myCyx, __float_as_uint(0.99f * myNsc));
+      }
+    }
+    kept += (unsigned long long)totalAcc;
+    if (kept > cap) kept = cap;
+    if (kept > (unsigned long long)maxOut) overflow = true;   // flagged below; the host raises OKC_ERR_CAPACITY
+    for (int b = tid; b < nbinsP; b += kWlThreads) S.binFill[b] = 0;
+    __syncthreads();
+    WL_T(6);
+    if (pos < n && kept < cap && !overflow) {
+      // Another window follows. (a) Lower bound of the occupancy per 4x4 block of cells, the pre-test of the fill: an
+      // accepted point at (py, px) inside its block adds at least ceil(minLut[py][px][by][bx] * 0.99 nsc1) to every
+      // cell of the block (by, bx) blocks away (ceil is monotone; minLut = the smallest LUT value over the 16 cells).
+      if (!lbReady) {
+        lbReady = true;
+        for (int t = tid; t < kWlMinLut; t += kWlThreads) {
+          const int bx = t % 9 - 4, by = (t / 9) % 9 - 4, px = (t / 81) & 3, py = t / 324;
+          float m = 1.0f;
+          for (int iy = 0; iy < 4; ++iy)
+            for (int ix = 0; ix < 4; ++ix) {
+              const int dy = 4 * by + iy - py + 15, dx = 4 * bx + ix - px + 15;
+              m = fminf(m, ((unsigned)dy < 31u && (unsigned)dx < 31u) ? S.lut[dy * 31 + dx] : 0.0f);
+            }
+          S.minLut[t] = m;
+        }
+        for (int t = tid; t < lbW * lbH; t += kWlThreads) lb[t] = 0;
+        __syncthreads();
+        if (warp < 16) {   // compact list of the blocks a point at (py, px) = warp reaches at all (about 20 of 81)
+          int base = 0;
+          for (int t0 = 0; t0 < 81; t0 += 32) {
+            const int t = t0 + lane;
+            const bool nz = t < 81 && S.minLut[warp * 81 + t] > 0.0f;
+            const unsigned b = __ballot_sync(0xffffffffu, nz);
+            if (nz) S.nzBlock[warp][base + __popc(b & ltMask)] = (unsigned char)(((t / 9) << 4) | (t % 9));
+            base += __popc(b);
+          }
+          if (lane == 0) S.nzCount[warp] = base;
+        }
+        __syncthreads();
+      }
+      WL_T(8);
+      if (acc) {   // (one thread per accepted entry: about 20 shared-memory atomics each, every lane of a warp busy)
+        const int variant = (cy & 3) * 4 + (cx & 3);
+        const float* ml = S.minLut + variant * 81;
+        int* dst = lb + (cy >> 2) * lbW + (cx >> 2);   // block (by, bx) = (-4, -4) of the margin-shifted image
+        const float nsc = 0.99f * myNsc;
+        const int nz = S.nzCount[variant];
+        for (int t = 0; t < nz; ++t) {
+          const int rc = (int)S.nzBlock[variant][t], row = rc >> 4, col = rc & 15;
+          const float v = ceilf(ml[row * 9 + col] * nsc);
+          const int add = (v == v) ? ((int)v & 0xff) : 0;
+          if (add) atomicAdd(dst + row * lbW + col, add);
         }
       }
+      WL_T(9);
+      // (b) every accepted point regrouped by bin, for the exact sums of the next window's entries
+      const int nk = (int)kept;
+      for (int k = tid; k < nk; k += kWlThreads) atomicAdd(&S.binFill[bin_of(node[k].x)], 1);
       __syncthreads();
-      if (tid == 0) {
-        s_nacc = 0;
-        s_any = 0;
+      scan_bins(S.binStartA);
+      for (int b = tid; b < nbinsP; b += kWlThreads) S.binFill[b] = S.binStartA[b];   // cursors
+      __syncthreads();
+      for (int k = tid; k < nk; k += kWlThreads) {
+        const uint2 nd = node[k];
+        nodeS[atomicAdd(&S.binFill[bin_of(nd.x)], 1)] = nd;
       }
-      if (!again) break;
+      __syncthreads();
+      // (the cursors ended at the bin ends: clear them again for the next window's CSR)
+      for (int b = tid; b < nbinsP; b += kWlThreads) S.binFill[b] = 0;
+      __syncthreads();
+      WL_T(0);
     }
-
-    // ---- the window's accepted entries, in candidate order, behind the keys ----
-#pragma unroll
-    for (int h = 0; h < kWavSlots; ++h) {
-      int total;
-      const int r = scan(st[h] == 2, total);
-      if (st[h] == 2) {
-        const unsigned long long k = kept + (unsigned long long)r;
-        if (k < cap && k < (unsigned long long)maxOut) cand[kCandCap + k] = cand[myIdx[h]];
-      }
-      kept += (unsigned long long)total;
-    }
-    if (kept > cap) kept = cap;
   }
 
-  // ---- sub-pixel refinement -> cv::KeyPoint (scale-space-layer-inl.h:394-420) ----
   const int nOut = kept < (unsigned long long)maxOut ? (int)kept : maxOut;
   if (tid == 0) {
-    counters[1] = nOut;
-    counters[5] = rounds;   // diagnostic (okc_debug_batch_counter)
+    counters[1] = nOut;     // the sub-pixel kernel that follows turns the kept keys into keypoints
+    counters[5] = sweeps;   // diagnostic (okc_debug_batch_counter): sweeps of warp 0
     if (kept > (unsigned long long)maxOut) counters[3] = 2;
   }
-  __syncthreads();   // (block-wide: the kept list was written by other threads)
-  for (int i = tid; i < nOut; i += kWavThreads) {
-    const uint64_t key = cand[kCandCap + i];
-    const int score = cand_score(key);
-    const uint32_t raster = (uint32_t)key;
-    const int v = raster / W, u = raster - v * W;
-    const int32_t* c = scores + (size_t)v * W + u;
-    float dx, dy;
-    subpixel2d((double)c[-W - 1], (double)c[-W], (double)c[-W + 1], (double)c[-1], (double)c[0], (double)c[1],
-               (double)c[W - 1], (double)c[W], (double)c[W + 1], dx, dy);
-    okc_keypoint kp;
-    // _scale * ((it->x + delta_x) + _offset): (float + float) widened, the rest in double, narrowed on assignment
-    kp.x = (float)(kpScale * ((double)((float)u + dx) + kpOffset));
-    kp.y = (float)(kpScale * ((double)((float)v + dy) + kpOffset));
-    kp.size = (float)(kpScale * 12.0);
-    kp.angle = -1.0f;
-    kp.response = (float)score;
-    kp.octave = octave;
-    kp.class_id = -1;
-    out[i] = kp;
-  }
+#ifdef OKC_SELECT_TRACE
+  __syncthreads();
+  WL_T(7);
+  if (tid == 0)
+    printf("select trace (cycles): fill %lld csr %lld lists %lld resolve(warp0) %lld wait %lld end %lld regroup %lld "
+           "(init %lld stamp %lld) tail %lld sweeps %d windows %d\n", tr[1], tr[2], tr[3], tr[4], tr[5], tr[6], tr[0], tr[8],
+           tr[9], tr[7], sweeps, windows);
+#endif
+}
+
+// Sub-pixel refinement of the kept candidates -> cv::KeyPoint (scale-space-layer-inl.h:394-420), after the selection
+// kernel: FP64 work for 700-2 500 points that spreads over the GPU instead of running on the selection CTA's one SM.
+__global__ void __launch_bounds__(128)
+subpixel_kernel(const Slot* __restrict__ slots, int W, double kpScale, double kpOffset, int octave) {
+  const Slot& slot = slots[blockIdx.y];
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= slot.counters[1]) return;
+  const uint64_t key = slot.cand[kCandCap + i];
+  const int score = cand_score(key);
+  const uint32_t raster = (uint32_t)key;
+  const int v = raster / W, u = raster - v * W;
+  const int32_t* c = slot.scores + (size_t)v * W + u;
+  float dx, dy;
+  subpixel2d((double)c[-W - 1], (double)c[-W], (double)c[-W + 1], (double)c[-1], (double)c[0], (double)c[1],
+             (double)c[W - 1], (double)c[W], (double)c[W + 1], dx, dy);
+  okc_keypoint kp;
+  // _scale * ((it->x + delta_x) + _offset): (float + float) widened, the rest in double, narrowed on assignment
+  kp.x = (float)(kpScale * ((double)((float)u + dx) + kpOffset));
+  kp.y = (float)(kpScale * ((double)((float)v + dy) + kpOffset));
+  kp.size = (float)(kpScale * 12.0);
+  kp.angle = -1.0f;
+  kp.response = (float)score;
+  kp.octave = octave;
+  kp.class_id = -1;
+  slot.kp_detect[i] = kp;
+}
+
+// Bytes of per-slot global scratch (Slot::occupancy) the selection kernels need: the occupancy image of the
+// sequential-visit kernel when it does not fit in shared memory.
+size_t select_scratch_bytes(const DetectArgs& a) {
+  const size_t rows = (size_t)((float)(a.height - 3) * a.scaling + 16.0f) + 17;
+  const size_t cols = (size_t)((float)(a.width - 3) * a.scaling + 16.0f) + 17;
+  const size_t stride = (cols + 15) & ~(size_t)15;
+  return rows * stride + 64;
 }
 
 void launch_select_keypoints(const Slot* slots, int n, const float* lut, const DetectArgs& a, cudaStream_t s) {
   int dev = 0;
   cudaGetDevice(&dev);
-  static int s_dyn[2][64] = {};   // per device: dynamic shared memory granted to the two <true> kernels
+  static int s_dyn[2][64] = {};   // per device: dynamic shared memory granted to the two kernels
   const size_t occRows = (size_t)((float)(a.height - 3) * a.scaling + 16.0f) + 17;
   const size_t occCols = (size_t)((float)(a.width - 3) * a.scaling + 16.0f) + 17;
-  const size_t occStride = (occCols + 15) & ~(size_t)15;
-  const size_t want = (occRows * occStride + 15) & ~(size_t)15;
-  const int which = g_knobs.select_sequential ? 1 : 0;   // 1: the sequential-visit kernel, A/B baseline of the tests
-  int& granted = s_dyn[which][dev & 63];
-  if (granted == 0) {
+  for (int which = 0; which < 2; ++which) {
+    int& granted = s_dyn[which][dev & 63];
+    if (granted != 0) continue;
     int maxOptin = 0;
     cudaDeviceGetAttribute(&maxOptin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
     cudaFuncAttributes fa;
     if (which == 1) cudaFuncGetAttributes(&fa, select_keypoints_kernel<true>);
-    else cudaFuncGetAttributes(&fa, select_keypoints_wave_kernel<true>);
+    else cudaFuncGetAttributes(&fa, select_keypoints_wave_kernel);
     granted = (maxOptin - (int)fa.sharedSizeBytes - 1024) & ~15;  // dynamic part beside the static arrays
     if (which == 1)
       cudaFuncSetAttribute(select_keypoints_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, granted);
     else
-      cudaFuncSetAttribute(select_keypoints_wave_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, granted);
+      cudaFuncSetAttribute(select_keypoints_wave_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, granted);
   }
-  // only as much dynamic shared memory as the occupancy image needs; the global fallback when it does not fit
-  const int smem = want <= (size_t)granted ? (int)want : 0;
-  if (which == 1) {
-    if (smem > 0)
-      select_keypoints_kernel<true><<<n, kSelThreads, smem, s>>>(slots, lut, a.width, a.height, a.scaling, a.max_kpt,
-                                                                 a.max_out, smem, a.kp_scale, a.kp_offset, a.octave);
-    else
-      select_keypoints_kernel<false><<<n, kSelThreads, 0, s>>>(slots, lut, a.width, a.height, a.scaling, a.max_kpt,
-                                                               a.max_out, 0, a.kp_scale, a.kp_offset, a.octave);
-    return;
-  }
-  // bins of 2^shift >= 16 occupancy cells, one empty bin all around, at most kWavMaxBins in total
+  // worklist kernel: bins of 2^shift >= 16 occupancy cells, one empty bin all around, at most kWlMaxBins in total
   int shift = 4, nbxP = 0, nbinsP = 0;
   for (;; ++shift) {
     nbxP = (int)((occCols + ((size_t)1 << shift) - 1) >> shift) + 2;
     const int nbyP = (int)((occRows + ((size_t)1 << shift) - 1) >> shift) + 2;
     nbinsP = nbxP * nbyP;
-    if (nbinsP <= kWavMaxBins) break;
+    if (nbinsP <= kWlMaxBins) break;
   }
+  // blocker lists take what the accepted-point nodes and the fixed arrays leave of the shared memory
+  const int lbW = (int)((occCols + 3) / 4) + 9, lbH = (int)((occRows + 3) / 4) + 9;   // 4x4 blocks, 4 of margin
+  const size_t wlFixed = 2 * (size_t)a.max_out * sizeof(uint2) + sizeof(WlSmem) + (size_t)lbW * lbH * sizeof(int);
+  int blkCap = 0;
+  if (wlFixed < (size_t)s_dyn[0][dev & 63]) {
+    blkCap = (int)(((size_t)s_dyn[0][dev & 63] - wlFixed) / ((size_t)kWlCap * sizeof(unsigned short)));
+    if (blkCap > kWlMaxBlk) blkCap = kWlMaxBlk;
+  }
+  // g_knobs.select_sequential: the sequential-visit kernel as the A/B baseline of the tests; it also serves handles
+  // whose max_keypoints leave no room for the blocker lists (> ~6 000 keypoints per image)
+  if (!g_knobs.select_sequential && blkCap >= kWlMinBlk && occCols < 65536 && occRows < 65536) {
+    const size_t wlBytes = wlFixed + (size_t)blkCap * kWlCap * sizeof(unsigned short);
+    select_keypoints_wave_kernel<<<n, kWlThreads, wlBytes, s>>>(slots, lut, a.width, a.height, a.scaling, a.max_kpt,
+                                                               a.max_out, shift, nbxP, nbinsP, blkCap, lbW, lbH);
+    subpixel_kernel<<<dim3((a.max_out + 127) / 128, n), 128, 0, s>>>(slots, a.width, a.kp_scale, a.kp_offset, a.octave);
+    return;
+  }
+  // only as much dynamic shared memory as the occupancy image needs; the global fallback when it does not fit
+  const size_t occStride = (occCols + 15) & ~(size_t)15;
+  const size_t want = (occRows * occStride + 15) & ~(size_t)15;
+  const int smem = want <= (size_t)s_dyn[1][dev & 63] ? (int)want : 0;
   if (smem > 0)
-    select_keypoints_wave_kernel<true><<<n, kWavThreads, smem, s>>>(slots, lut, a.width, a.height, a.scaling,
-                                                                   a.max_kpt, a.max_out, shift, nbxP, nbinsP,
-                                                                   a.kp_scale, a.kp_offset, a.octave);
+    select_keypoints_kernel<true><<<n, kSelThreads, smem, s>>>(slots, lut, a.width, a.height, a.scaling, a.max_kpt,
+                                                               a.max_out, smem, a.kp_scale, a.kp_offset, a.octave);
   else
-    select_keypoints_wave_kernel<false><<<n, kWavThreads, 0, s>>>(slots, lut, a.width, a.height, a.scaling,
-                                                                 a.max_kpt, a.max_out, shift, nbxP, nbinsP,
-                                                                 a.kp_scale, a.kp_offset, a.octave);
+    select_keypoints_kernel<false><<<n, kSelThreads, 0, s>>>(slots, lut, a.width, a.height, a.scaling, a.max_kpt,
+                                                             a.max_out, 0, a.kp_scale, a.kp_offset, a.octave);
 }
 
 // ----------------------------------------------------------------------------------------------

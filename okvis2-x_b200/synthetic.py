@@ -42,6 +42,21 @@ def scene_image(width, height, seed, rects=400, noise=3):
     return np.clip(img, 0, 255).astype(np.uint8)
 
 
+def dense_image(width, height, seed, rects=6000, size=(4, 24), noise=3):
+    """Many small rectangles: corner-dense texture that saturates the keypoint budgets (EuRoC: the 700 cap binds with
+    ~7 500 NMS candidates; 848x480 at radius 30: ~1 500 keypoints, the most the uniformity stamps leave room for)."""
+    rng = np.random.default_rng(seed)
+    img = np.full((height, width), 128.0, np.float32)
+    for _ in range(rects):
+        x0, y0 = int(rng.integers(0, width)), int(rng.integers(0, height))
+        w, h = (int(v) for v in rng.integers(size[0], size[1], 2))
+        img[y0:y0 + h, x0:x0 + w] = float(rng.integers(0, 256))
+    p = np.pad(img, 1, mode="edge")
+    img = sum(p[dy:dy + height, dx:dx + width] for dy in range(3) for dx in range(3)) / 9.0
+    img = img + rng.integers(-noise, noise + 1, (height, width))
+    return np.clip(img, 0, 255).astype(np.uint8)
+
+
 def noise_image(width, height, seed):
     """i.i.d. uniform u8: the reference's own test input (okvis_cv/test/TestFrame.cpp:62-65), worst case for NMS."""
     return np.random.default_rng(seed).integers(0, 256, (height, width), dtype=np.uint8)

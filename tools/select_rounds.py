@@ -1,4 +1,5 @@
-"""GPU-box tool: rounds of the wave-parallel uniformity selection and kernel times per config image."""
+"""GPU-box tool: kernel times of the uniformity selection (default dependency-form kernel vs the sequential-visit
+baseline) per config image; `rounds` = sweeps of warp 0 (diagnostic counter 5)."""
 import os, sys, json
 import numpy as np
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -8,7 +9,9 @@ mod = ge.load()
 syn = importlib.import_module("okvis2x_b200.synthetic")
 ctx = mod.Context(0)
 cases = {"euroc-scene": (syn.EUROC, syn.scene_image(752, 480, 1)), "euroc-noise": (syn.EUROC, syn.noise_image(752, 480, 2)),
-         "d455-scene": (syn.D455, syn.scene_image(848, 480, 8, rects=1500)), "hilti-scene": (syn.HILTI, syn.scene_image(720, 540, 3))}
+         "d455-scene": (syn.D455, syn.scene_image(848, 480, 8, rects=1500)), "hilti-scene": (syn.HILTI, syn.scene_image(720, 540, 3)),
+         "euroc-dense": (syn.EUROC, syn.dense_image(752, 480, 8)), "d455-dense": (syn.D455, syn.dense_image(848, 480, 8)),
+         "hilti-dense": (syn.HILTI, syn.dense_image(720, 540, 8)), "d455-noise": (syn.D455, syn.noise_image(848, 480, 9))}
 out = {}
 for name, (cfg, img) in cases.items():
     h, w = img.shape
