@@ -353,6 +353,91 @@ int okc_batch_slot_matches(okc_batch* batch, int slot, double* best_dist, int32_
 int okc_batch_read_all(okc_batch* batch, okc_keypoint* keypoints, int32_t* counts, uint8_t* descriptors,
                        double* best_dist, int32_t* best_owner, uint64_t* ctrs, double* repr_errors);
 void* okc_batch_stream(okc_batch* batch);
+
+/* ---- Frame pipeline, the stages that follow matchToMapByThread in Frontend::dataAssociationAndInitialization
+ * (Frontend.cpp:674-1143), device resident: a slot's descriptors, keypoints and back-projections are used where
+ * describe left them, the landmark pool of the keyframe window stays in HBM, and per frame only the poses go in and
+ * the match results come out. All calls below are enqueued on the batch's stream after okc_batch_enqueue of the same
+ * frame; okc_batch_finish brings every result to the host (one copy per result block). ---- */
+
+/* Geometry of a camera: enables Frame::computeBackProjections (okvis_cv/include/okvis/implementation/Frame.hpp:158-173)
+ * as a stage after describe in every chain that runs on this camera (single-camera entry points and batches), and
+ * gives the landmark stage its focal lengths. */
+int okc_camera_set_geometry(okc_camera* cam, const okc_pinhole* model);
+
+/* Pose of a slot's camera for the frame in flight: T_WC = T_WS * T_SC as rotation (row-major) + position, and its
+ * inverse T_CW as rotation + translation (the reference forms both, Frontend.cpp:1356-1358; passing both keeps the
+ * library free of a 3x3 inverse whose rounding would have to match Eigen's). */
+typedef struct okc_slot_pose {
+  double T_CW[12];
+  double C_WC[9];
+  double r_WC[3];
+} okc_slot_pose;
+int okc_batch_set_poses(okc_batch* batch, const okc_slot_pose* poses /* n_slots */);
+/* After okc_batch_finish: e_C[n*3], valid[n] and the number of valid back-projections of a slot (n = its keypoints). */
+int okc_batch_slot_back_projections(okc_batch* batch, int slot, double* e_C, uint8_t* valid, int* n_valid);
+
+/* The landmarks of the keyframe window with their observations (what Frontend::matchToMap walks, Frontend.cpp:1335-1508),
+ * uploaded once and kept in HBM: arguments as for okc_prepare_landmarks. okc_landmark_pool_update replaces the
+ * landmark positions / qualities and the poses of the observing views after an optimisation (NULL = unchanged). */
+typedef struct okc_landmark_pool okc_landmark_pool;
+int okc_landmark_pool_create(okc_context* ctx, const okc_landmark_views* views, int n_landmarks, const double* hp_W,
+                             const double* quality, const int64_t* obs_offset, const int32_t* obs_view,
+                             const int32_t* obs_kp, okc_landmark_pool** pool);
+int okc_landmark_pool_update(okc_landmark_pool* pool, const double* hp_W, const double* quality, const double* C_WC,
+                             const double* r_WC);
+int okc_landmark_pool_destroy(okc_landmark_pool* pool);
+
+/* Frontend::matchToMap for every slot of the batch (Frontend.cpp:1335-1716 without the estimator calls): landmark
+ * preparation for the slot's pose (projection, field-of-view test, is3d, viewpoint / scale pruning, best three
+ * descriptors, pool packing: okc_project_landmarks + okc_prepare_landmarks as kernels on the batch's stream),
+ * matchToMapByThread on the 3D landmarks and - with OKC_STAGE_UNINITIALISED - matchToMapByThreadUnitialised on the
+ * others, where a keypoint takes part when its back-projection is valid and matchToMapByThread left it without a
+ * landmark (a fresh frame has no other landmark ids). The reprojection gate is 3 + 0.06 f (3 + 0.34 f with
+ * OKC_STAGE_NO_IMU), f = 0.5 (fu + fv) of the slot's camera geometry (Frontend.cpp:1340-1342, 1760-1764).
+ * Needs okc_camera_set_geometry on every slot's camera and okc_batch_set_poses. */
+#define OKC_STAGE_UNINITIALISED 1
+#define OKC_STAGE_NO_IMU 2
+#define OKC_STAGE_LOOP_CLOSURE 4
+int okc_batch_match_landmarks_enqueue(okc_batch* batch, const okc_landmark_pool* pool, double hamming_threshold,
+                                      int num_slices, int flags);
+/* After okc_batch_finish. okc_batch_slot_matches returns the matchToMapByThread part (best_owner = landmark index).
+ * okc_batch_slot_uninitialised: what okc_match_to_map_uninitialised returns, for the slot's n keypoints.
+ * okc_batch_slot_landmarks: the prepared pool of a slot (copied from the device on demand; any pointer may be NULL):
+ * proj_xy[L*2], visible[L], is3d[L], rows[L], *nm and per row owner[nm], pool[nm*48]. */
+int okc_batch_slot_uninitialised(okc_batch* batch, int slot, double* best_dist, int32_t* best_owner, double* hps_W,
+                                 uint8_t* hps_written, uint64_t* ctrs);
+int okc_batch_slot_landmarks(okc_batch* batch, int slot, double* proj_xy, uint8_t* visible, uint8_t* is3d,
+                             int32_t* rows, int32_t* nm, int32_t* owner, uint8_t* pool);
+
+/* Frontend::matchStereo (Frontend.cpp:2259-2316) between slots of the batch (the cameras of one multiframe):
+ * pair p matches the keypoints of slot0[p] (k0) against those of slot1[p] (k1). Focal length f = 0.5 (fu + fv) of the
+ * cameras' geometry. After okc_batch_finish, okc_batch_pair_stereo returns what okc_match_stereo returns. */
+int okc_batch_match_stereo_enqueue(okc_batch* batch, int n_pairs, const int* slot0, const int* slot1,
+                                   double hamming_threshold);
+int okc_batch_pair_stereo(okc_batch* batch, int pair, double* dist, int32_t* k1_match, double* hp_W,
+                          uint8_t* initialisable);
+
+/* An older multiframe kept on the device for Frontend::matchMotionStereo (Frontend.cpp:1968-2150): okc_batch_retain
+ * copies the descriptors, keypoints and back-projections of n_views slots (device to device, on the batch's stream)
+ * after the frame was described; okc_keyframe_set_view gives a view its current pose (after an optimisation), focal
+ * length and - optionally - the eligibility flags of its keypoints (use0: not an initialised landmark, not observed;
+ * estimator state, Frontend.cpp:2056-2084; NULL = all eligible). */
+typedef struct okc_keyframe okc_keyframe;
+int okc_keyframe_create(okc_context* ctx, int n_views, int max_keypoints, okc_keyframe** keyframe);
+int okc_keyframe_destroy(okc_keyframe* keyframe);
+int okc_batch_retain(okc_batch* batch, int n_views, const int* slots, okc_keyframe* keyframe);
+int okc_keyframe_set_view(okc_keyframe* keyframe, int view, const double C_WC[9], const double r_WC[3], double f,
+                          const uint8_t* use0, int n_use0);
+/* Job j: the keypoints of view views[j] of keyframes[j] (k0) against the keypoints of slot slots[j] that have no
+ * landmark after the landmark stage (only_unmatched != 0; the reference packs them, Frontend.cpp:2034-2047) or against
+ * all of them. k1_match is the keypoint index inside the slot (the reference's k1s[k1]). After okc_batch_finish,
+ * okc_batch_job_motion returns what okc_match_motion_stereo returns, for the view's keypoints. */
+int okc_batch_match_motion_enqueue(okc_batch* batch, int n_jobs, const okc_keyframe* const* keyframes, const int* views,
+                                   const int* slots, double hamming_threshold, int only_unmatched);
+int okc_batch_job_motion(okc_batch* batch, int job, int* n0, double* dist, int32_t* k1_match, double* hp_W,
+                         uint8_t* initialisable, double* quality);
+
 int okc_debug_batch_kernel_timing(okc_batch* batch, int enable);
 int okc_debug_batch_kernel_times(okc_batch* batch, char* names, int names_cap, float* ms, int cap, int* n);
 

@@ -34,7 +34,13 @@ EXPORTS = [
     "okc_debug_kernel_times", "okc_batch_create", "okc_batch_destroy", "okc_batch_size", "okc_batch_enqueue",
     "okc_batch_finish", "okc_batch_slot_frame", "okc_batch_slot_matches", "okc_batch_read_all", "okc_batch_stream",
     "okc_debug_batch_kernel_timing", "okc_debug_batch_kernel_times",
+    "okc_camera_set_geometry", "okc_batch_set_poses", "okc_batch_slot_back_projections", "okc_landmark_pool_create",
+    "okc_landmark_pool_update", "okc_landmark_pool_destroy", "okc_batch_match_landmarks_enqueue",
+    "okc_batch_slot_uninitialised", "okc_batch_slot_landmarks", "okc_batch_match_stereo_enqueue",
+    "okc_batch_pair_stereo", "okc_keyframe_create", "okc_keyframe_destroy", "okc_batch_retain",
+    "okc_keyframe_set_view", "okc_batch_match_motion_enqueue", "okc_batch_job_motion",
 ]
+STAGE_UNINITIALISED, STAGE_NO_IMU, STAGE_LOOP_CLOSURE = 1, 2, 4
 
 
 class OkcError(RuntimeError):
@@ -184,6 +190,23 @@ def lib():
         L.okc_batch_stream.restype = vp
         L.okc_debug_batch_kernel_timing.argtypes = [vp, i]
         L.okc_debug_batch_kernel_times.argtypes = [vp, vp, i, vp, i, C.POINTER(i)]
+        L.okc_camera_set_geometry.argtypes = [vp, vp]
+        L.okc_batch_set_poses.argtypes = [vp, vp]
+        L.okc_batch_slot_back_projections.argtypes = [vp, i, vp, vp, C.POINTER(i)]
+        L.okc_landmark_pool_create.argtypes = [vp, vp, i, vp, vp, vp, vp, vp, C.POINTER(vp)]
+        L.okc_landmark_pool_update.argtypes = [vp, vp, vp, vp, vp]
+        L.okc_landmark_pool_destroy.argtypes = [vp]
+        L.okc_batch_match_landmarks_enqueue.argtypes = [vp, vp, d, i, i]
+        L.okc_batch_slot_uninitialised.argtypes = [vp, i, vp, vp, vp, vp, vp]
+        L.okc_batch_slot_landmarks.argtypes = [vp, i, vp, vp, vp, vp, C.POINTER(i), vp, vp]
+        L.okc_batch_match_stereo_enqueue.argtypes = [vp, i, vp, vp, d]
+        L.okc_batch_pair_stereo.argtypes = [vp, i, vp, vp, vp, vp]
+        L.okc_keyframe_create.argtypes = [vp, i, i, C.POINTER(vp)]
+        L.okc_keyframe_destroy.argtypes = [vp]
+        L.okc_batch_retain.argtypes = [vp, i, vp, vp]
+        L.okc_keyframe_set_view.argtypes = [vp, i, vp, vp, d, vp, i]
+        L.okc_batch_match_motion_enqueue.argtypes = [vp, i, vp, vp, vp, d, i]
+        L.okc_batch_job_motion.argtypes = [vp, i, C.POINTER(i), vp, vp, vp, vp, vp]
         _lib = L
     return _lib
 
@@ -436,6 +459,70 @@ class Context:
         return dist, k1, hp, init
 
 
+def slot_pose(C_WC, r_WC):
+    """okc_slot_pose row (24 doubles: T_CW[12], C_WC[9], r_WC[3]) of a camera pose T_WC = (C_WC, r_WC); the inverse
+    as okvis::kinematics::Transformation::inverse() forms it: C^T and -(C^T r)."""
+    Cm = np.asarray(C_WC, np.float64).reshape(3, 3)
+    r = np.asarray(r_WC, np.float64).reshape(3)
+    Ct = np.ascontiguousarray(Cm.T)
+    t = np.empty(3)
+    for a in range(3):   # coefficient-wise (x0 y0 + x1 y1) + x2 y2, then negated
+        t[a] = -((Ct[a, 0] * r[0] + Ct[a, 1] * r[1]) + Ct[a, 2] * r[2])
+    return np.concatenate([Ct.reshape(9), t, Cm.reshape(9), r])
+
+
+class LandmarkPool:
+    """Device-resident landmarks of the keyframe window (okc_landmark_pool): arguments as Context.prepare_landmarks."""
+
+    def __init__(self, ctx, views, hp_W, quality, obs_offset, obs_view, obs_kp):
+        Cw = np.ascontiguousarray(views["C_WC"], np.float64).reshape(-1, 9)
+        rw = np.ascontiguousarray(views["r_WC"], np.float64).reshape(-1, 3)
+        row0 = np.ascontiguousarray(views["row0"], np.int64)
+        desc = np.ascontiguousarray(views["desc"], np.uint8).reshape(-1, 48)
+        eC = np.ascontiguousarray(views["e_C"], np.float64).reshape(-1, 3)
+        lv = LandmarkViews(len(Cw), Cw.ctypes.data, rw.ctypes.data, row0.ctypes.data, desc.ctypes.data, eC.ctypes.data,
+                           len(desc))
+        hp = np.ascontiguousarray(hp_W, np.float64).reshape(-1, 4)
+        self.L = len(hp)
+        q = np.ascontiguousarray(quality, np.float64)
+        off = np.ascontiguousarray(obs_offset, np.int64)
+        ov = np.ascontiguousarray(obs_view, np.int32)
+        ok = np.ascontiguousarray(obs_kp, np.int32)
+        self.h = C.c_void_p()
+        _check(lib().okc_landmark_pool_create(ctx.h, C.byref(lv), self.L, _p(hp), _p(q), _p(off), _p(ov), _p(ok),
+                                              C.byref(self.h)), "okc_landmark_pool_create")
+
+    def update(self, hp_W=None, quality=None, C_WC=None, r_WC=None):
+        a = [None if x is None else np.ascontiguousarray(x, np.float64) for x in (hp_W, quality, C_WC, r_WC)]
+        _check(lib().okc_landmark_pool_update(self.h, *[_p(x) for x in a]), "okc_landmark_pool_update")
+
+    def close(self):
+        if self.h:
+            lib().okc_landmark_pool_destroy(self.h)
+            self.h = C.c_void_p()
+
+
+class Keyframe:
+    """An older multiframe retained on the device for matchMotionStereo (okc_keyframe)."""
+
+    def __init__(self, ctx, n_views, max_keypoints):
+        self.n_views, self.max_kp = n_views, max_keypoints
+        self.h = C.c_void_p()
+        _check(lib().okc_keyframe_create(ctx.h, n_views, max_keypoints, C.byref(self.h)), "okc_keyframe_create")
+
+    def set_view(self, view, C_WC, r_WC, f, use0=None):
+        Cw = np.ascontiguousarray(C_WC, np.float64).reshape(9)
+        rw = np.ascontiguousarray(r_WC, np.float64).reshape(3)
+        u = None if use0 is None else np.ascontiguousarray(use0, np.uint8)
+        _check(lib().okc_keyframe_set_view(self.h, view, _p(Cw), _p(rw), float(f), _p(u), 0 if u is None else len(u)),
+               "okc_keyframe_set_view")
+
+    def close(self):
+        if self.h:
+            lib().okc_keyframe_destroy(self.h)
+            self.h = C.c_void_p()
+
+
 class DescriptorSet:
     def __init__(self, ctx, rows):
         r = np.ascontiguousarray(rows, np.uint8).reshape(-1, 48)
@@ -484,6 +571,11 @@ class Camera:
         if self.h:
             lib().okc_camera_destroy(self.h)
             self.h = C.c_void_p()
+
+    def set_geometry(self, pinhole):
+        """Pinhole.make(...) of this camera: back-projections after describe, focal lengths of the landmark stage."""
+        _check(lib().okc_camera_set_geometry(self.h, C.byref(pinhole)), "okc_camera_set_geometry")
+        self.pinhole = pinhole
 
     def _img(self, image):
         img = np.asarray(image)
@@ -737,6 +829,90 @@ class Batch:
                                         _p(ctrs) if m else None, _p(errs) if m else None), "okc_batch_read_all")
         return out
 
+    # -- frame pipeline beyond matchToMapByThread --
+    def set_poses(self, poses):
+        """poses: [n, 24] rows of slot_pose()."""
+        p = np.ascontiguousarray(poses, np.float64).reshape(self.n, 24)
+        _check(lib().okc_batch_set_poses(self.h, _p(p)), "okc_batch_set_poses")
+
+    def slot_back_projections(self, slot, nk):
+        e = np.zeros((self.max_kp, 3), np.float64)
+        v = np.zeros(self.max_kp, np.uint8)
+        nv = C.c_int(0)
+        _check(lib().okc_batch_slot_back_projections(self.h, slot, _p(e), _p(v), C.byref(nv)),
+               "okc_batch_slot_back_projections")
+        return e[:nk], v[:nk], nv.value
+
+    def match_landmarks_enqueue(self, pool, hamming_threshold=60.0, num_slices=4, flags=0):
+        _check(lib().okc_batch_match_landmarks_enqueue(self.h, pool.h, float(hamming_threshold), int(num_slices),
+                                                       int(flags)), "okc_batch_match_landmarks_enqueue")
+        self._slices = int(num_slices)
+        self._matching = True
+        self._pool_L = pool.L
+
+    def slot_uninitialised(self, slot, nk):
+        bd = np.empty(self.max_kp, np.float64)
+        bo = np.empty(self.max_kp, np.int32)
+        hp = np.empty((self.max_kp, 4), np.float64)
+        hw = np.empty(self.max_kp, np.uint8)
+        ctrs = np.zeros(self._slices, np.uint64)
+        _check(lib().okc_batch_slot_uninitialised(self.h, slot, _p(bd), _p(bo), _p(hp), _p(hw), _p(ctrs)),
+               "okc_batch_slot_uninitialised")
+        return bd[:nk], bo[:nk], hp[:nk], hw[:nk], ctrs
+
+    def slot_landmarks(self, slot):
+        L = self._pool_L
+        out = dict(proj=np.zeros((max(L, 1), 2)), visible=np.zeros(max(L, 1), np.uint8), is3d=np.zeros(max(L, 1), np.uint8),
+                   rows=np.zeros(max(L, 1), np.int32), owner=np.zeros(max(3 * L, 1), np.int32),
+                   pool=np.zeros((max(3 * L, 1), 48), np.uint8))
+        nm = C.c_int(0)
+        _check(lib().okc_batch_slot_landmarks(self.h, slot, _p(out["proj"]), _p(out["visible"]), _p(out["is3d"]),
+                                              _p(out["rows"]), C.byref(nm), _p(out["owner"]), _p(out["pool"])),
+               "okc_batch_slot_landmarks")
+        n = nm.value
+        return dict(proj=out["proj"][:L], visible=out["visible"][:L], is3d=out["is3d"][:L], rows=out["rows"][:L], nm=n,
+                    owner=out["owner"][:n], pool=out["pool"][:n])
+
+    def match_stereo_enqueue(self, pairs, hamming_threshold=60.0):
+        s0 = np.ascontiguousarray([p[0] for p in pairs], np.int32)
+        s1 = np.ascontiguousarray([p[1] for p in pairs], np.int32)
+        _check(lib().okc_batch_match_stereo_enqueue(self.h, len(pairs), _p(s0), _p(s1), float(hamming_threshold)),
+               "okc_batch_match_stereo_enqueue")
+
+    def pair_stereo(self, pair, n0):
+        dist = np.empty(self.max_kp, np.float64)
+        k1 = np.empty(self.max_kp, np.int32)
+        hp = np.empty((self.max_kp, 4), np.float64)
+        init = np.empty(self.max_kp, np.uint8)
+        _check(lib().okc_batch_pair_stereo(self.h, pair, _p(dist), _p(k1), _p(hp), _p(init)), "okc_batch_pair_stereo")
+        return dist[:n0], k1[:n0], hp[:n0], init[:n0]
+
+    def retain(self, slots, keyframe):
+        s = np.ascontiguousarray(slots, np.int32)
+        _check(lib().okc_batch_retain(self.h, len(s), _p(s), keyframe.h), "okc_batch_retain")
+
+    def match_motion_enqueue(self, jobs, hamming_threshold=60.0, only_unmatched=True):
+        """jobs: [(keyframe, view, slot)]."""
+        kf = (C.c_void_p * len(jobs))(*[j[0].h for j in jobs])
+        v = np.ascontiguousarray([j[1] for j in jobs], np.int32)
+        s = np.ascontiguousarray([j[2] for j in jobs], np.int32)
+        self._motion_cap = max([self.max_kp] + [j[0].max_kp for j in jobs])
+        _check(lib().okc_batch_match_motion_enqueue(self.h, len(jobs), kf, _p(v), _p(s), float(hamming_threshold),
+                                                    int(bool(only_unmatched))), "okc_batch_match_motion_enqueue")
+
+    def job_motion(self, job):
+        cap = self._motion_cap
+        dist = np.empty(cap, np.float64)
+        k1 = np.empty(cap, np.int32)
+        hp = np.empty((cap, 4), np.float64)
+        init = np.empty(cap, np.uint8)
+        q = np.empty(cap, np.float64)
+        n0 = C.c_int(0)
+        _check(lib().okc_batch_job_motion(self.h, job, C.byref(n0), _p(dist), _p(k1), _p(hp), _p(init), _p(q)),
+               "okc_batch_job_motion")
+        n = n0.value
+        return dist[:n], k1[:n], hp[:n], init[:n], q[:n]
+
     def stream(self):
         return lib().okc_batch_stream(self.h)
 
@@ -744,9 +920,9 @@ class Batch:
         _check(lib().okc_debug_batch_kernel_timing(self.h, int(bool(enable))), "okc_debug_batch_kernel_timing")
 
     def kernel_times(self):
-        names = C.create_string_buffer(512)
-        ms = np.zeros(16, np.float32)
+        names = C.create_string_buffer(1024)
+        ms = np.zeros(32, np.float32)
         n = C.c_int(0)
-        _check(lib().okc_debug_batch_kernel_times(self.h, names, 512, _p(ms), 16, C.byref(n)),
+        _check(lib().okc_debug_batch_kernel_times(self.h, names, 1024, _p(ms), 32, C.byref(n)),
                "okc_debug_batch_kernel_times")
         return list(zip(names.value.decode().split("\n"), [float(v) for v in ms[:n.value]])) if n.value else []

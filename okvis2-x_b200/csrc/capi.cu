@@ -196,3 +196,4 @@ int okc_debug_host_tables(float* points /*1024*66*3*/, int* basicscale, int* bor
 #include "capi_match.inc"
 #include "capi_batch.inc"
 #include "capi_frame.inc"
+#include "capi_pipeline.inc"

@@ -89,7 +89,129 @@ struct Slot {
   int* bin_owner;          // nm landmark slots in bin order
   int bins_x, bins_y;      // 0: no bins for this slot (full scan)
   double bin_pad, bin_cell;   // cell(p) = floor((p + bin_pad) / bin_cell), bin_cell >= gate radius + 2 px = bin_pad
+  // ---- frame pipeline beyond matchToMapByThread ----
+  // back-projections of the described keypoints (Frame::computeBackProjections), written after describe when the
+  // slot's camera has a geometry
+  okc_pinhole pinhole;
+  int has_geometry;
+  double* e_C;             // max_keypoints x 3
+  uint8_t* bp_valid;       // max_keypoints; counters[6] = number of valid ones
+  // landmark pool packed on the device for this slot's pose (okc_batch_prepare_landmarks_enqueue): row count and the
+  // per-row / per-landmark side data of the two map matchers
+  const int* nm_dev;       // (per enqueue) rows in the pool, when it was packed on the device (else nm counts)
+  const uint8_t* is3d;     // (per enqueue) per landmark: matchToMapByThread takes the rows of 3D landmarks, the
+                           // uninitialised matcher the others; null: matchToMapByThread takes every row
+  // pose of the slot's camera for this frame: T_WC = T_WS * T_SC
+  double C_WC[9], r_WC[3]; // (per enqueue)
+  double focal_mean;       // 0.5 * (focalLengthU + focalLengthV)
 };
+
+// One side of a 2D-2D match (Frontend::matchStereo / matchMotionStereo): a view's descriptors, keypoint sizes,
+// back-projections and pose. Keypoint sizes come either as doubles (host-buffer entry points) or from the keypoints.
+struct StereoSide {
+  const uint8_t* desc;
+  const double* size_d;     // or null:
+  const okc_keypoint* kp;   //   (double)kp[k].size
+  const double* e_C;
+  const uint8_t* bp_valid;
+  const int* n_dev;         // count still on the device (a batch slot), or null
+  int n;                    // count, or the capacity when n_dev is set
+  double C[9], r[3], f;
+};
+struct StereoJob {
+  StereoSide v0, v1;
+  const uint8_t* use0;      // motion stereo: eligibility of k0 (estimator state), or null = every k0
+  // motion stereo against a batch slot: only the slot's keypoints without a landmark are candidates (the reference
+  // packs them, Frontend.cpp:2034-2047): skipped unless both owners are < 0; null = every k1
+  const int* v1_owner_a;
+  const int* v1_owner_b;
+  double* dist;
+  int* k1;
+  double* hp;
+  uint8_t* init;
+  double* quality;          // motion stereo only
+};
+
+struct UninitArgs {
+  double r_WC[3];
+  double cos26Sigma, cos6Sigma;   // sigma = 1 / focalLength; cos(2.6 sigma), cos(6 sigma) from the host's libm
+  double hammingThreshold;
+};
+// Frontend::matchToMapByThreadUnitialised for one camera image.
+struct UninitJob {
+  const uint8_t* queries;
+  const double* kp_e_W;     // world rays of the keypoints, or null: C_WC * e_C.normalized() from
+  const double* e_C;        //   the back-projections
+  const uint8_t* bp_valid;  //   and their validity (Frontend.cpp:1862-1872)
+  double C_WC[9];
+  const uint8_t* use;       // eligibility flags, or null: a keypoint is eligible when
+  const int* owner14;       //   matchToMapByThread left it without a landmark (owner14[k] < 0; null: always)
+  const int* previousOwner; // loop-closure mode only, or null
+  const int* nk_dev;
+  int nk;
+  const uint8_t* map;
+  const int* owner;
+  const uint8_t* is3d;      // rows of 3D landmarks are skipped (Frontend.cpp:1878-1880); null: no row is
+  const double* map_e_W;
+  const double* map_r_W;
+  const int* nm_dev;
+  int nm;
+  int num_slices;
+  UninitArgs a;
+  double* dist;
+  int* best;
+  double* hp;
+  uint8_t* hp_written;
+  unsigned* ctr;                  // per keypoint, or null
+  unsigned long long* slice_ctrs; // per thread slice (added to), or null
+};
+void launch_match_stereo_jobs(const StereoJob* jobs, int nJobs, int max0, bool motion, double hammingThreshold,
+                              cudaStream_t s);
+void launch_match_uninit_jobs(const UninitJob* jobs, int nJobs, int maxNk, cudaStream_t s);
+void launch_back_project_slots(const Slot* slots, int n, int max_kp, cudaStream_t s);
+
+// Landmark preparation of Frontend::matchToMap for one camera image (Frontend.cpp:1376-1500): inputs of the shared
+// landmark pool, the pose of this image, and where its pool is packed.
+struct PrepareArgs {
+  const double* hp_W;          // L x 4
+  const double* quality;       // L
+  const uint8_t* visible;      // L (okc_project_landmarks)
+  const long long* obs_offset; // L + 1
+  const int* obs_view;         // per observation: view (frame, camera) index, in the reference's iteration order
+  const int* obs_kp;           // per observation: keypoint index inside the view
+  const double* view_C;        // V x 9, T_WC_old.C() row-major
+  const double* view_r;        // V x 3, T_WC_old.r()
+  const long long* view_row0;  // V: first row of the view in the descriptor / back-projection pools
+  const uint8_t* desc;         // N x 48
+  const double* e_C;           // N x 3 (Frame::backProjections_)
+  double r_WC1[3];             // T_WC1.r() of the camera being matched
+  double focal_sum;            // focalLengthU() + focalLengthV() (Frontend.cpp:1361-1363)
+  int loop_closure;            // loopClosureLandmarksToUseExclusively != nullptr
+  int L;
+  // per landmark, 3 slots
+  uint8_t* is3d;
+  int* rows;                   // o + 1 for visible landmarks, 0 otherwise
+  int* slot_obs;               // L x 3: observation index that filled the slot (-1: never written)
+};
+struct PrepSlot {
+  PrepareArgs a;               // (a.visible = visible below)
+  okc_pinhole cam;
+  double T_CW[12];
+  double repr_threshold;
+  double* proj_xy;             // L x 2
+  uint8_t* status;             // L
+  uint8_t* visible;            // L
+  int* row_offset;             // L + 1; [L] = rows in the pool
+  uint8_t* pool;               // 3 L x 48
+  int* owner;                  // 3 L
+  double* e_W;                 // 3 L x 3
+  double* r_W;                 // 3 L x 3
+  uint8_t* filled;             // 3 L
+  int* row_obs;                // 3 L
+};
+void launch_prepare_landmarks_slots(const PrepSlot* prep, int n, int L, cudaStream_t s);
+int check_pinhole(const okc_pinhole* cam);   // OKC_OK or OKC_ERR_INVALID (with the error string set)
+
 
 struct DetectArgs {
   int width, height;

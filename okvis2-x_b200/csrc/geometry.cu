@@ -161,9 +161,9 @@ __host__ __device__ inline int project_point(const okc_pinhole& cam, double p0, 
   return p2 > 0.0 ? OKC_PROJ_SUCCESSFUL : OKC_PROJ_BEHIND;
 }
 
-__global__ void back_project_kernel(okc_pinhole cam, const okc_keypoint* __restrict__ kps, int n,
-                                    double* __restrict__ e_C, uint8_t* __restrict__ valid, int* __restrict__ nValid) {
-  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+__device__ __forceinline__ void back_project_body(const okc_pinhole& cam, const okc_keypoint* __restrict__ kps, int n,
+                                                  int k, double* __restrict__ e_C, uint8_t* __restrict__ valid,
+                                                  int* __restrict__ nValid) {
   bool ok = false;
   if (k < n) {
     // Eigen::Vector2d(ckp.pt.x, ckp.pt.y): the floats widen exactly
@@ -180,13 +180,27 @@ __global__ void back_project_kernel(okc_pinhole cam, const okc_keypoint* __restr
   if ((threadIdx.x & 31) == 0 && m) atomicAdd(nValid, __popc(m));
 }
 
+__global__ void back_project_kernel(okc_pinhole cam, const okc_keypoint* __restrict__ kps, int n,
+                                    double* __restrict__ e_C, uint8_t* __restrict__ valid, int* __restrict__ nValid) {
+  back_project_body(cam, kps, n, blockIdx.x * blockDim.x + threadIdx.x, e_C, valid, nValid);
+}
+
+// Frame pipeline: Frame::computeBackProjections of every slot's described keypoints, right after describe
+// (Frontend::detectAndDescribe, Frontend.cpp:246-248); the count is still on the device.
+__global__ void back_project_slots_kernel(const Slot* __restrict__ slots, int maxKp) {
+  const Slot& slot = slots[blockIdx.y];
+  if (!slot.has_geometry) return;
+  const int n = min(slot.counters[2], maxKp);
+  if ((int)(blockIdx.x * blockDim.x) >= n) return;
+  back_project_body(slot.pinhole, slot.kp_desc, n, blockIdx.x * blockDim.x + threadIdx.x, slot.e_C, slot.bp_valid,
+                    slot.counters + 6);
+}
+
 // T = {C row-major 3x3, r}: hp_C = [C * hp_W.head<3>() + r * hp_W[3]; hp_W[3]]
-__global__ void project_landmarks_kernel(okc_pinhole cam, const double* __restrict__ T_CW,
-                                         const double* __restrict__ hp_W, int n, double reprThreshold,
-                                         double* __restrict__ proj_xy, uint8_t* __restrict__ status,
-                                         uint8_t* __restrict__ visible) {
-  const int l = blockIdx.x * blockDim.x + threadIdx.x;
-  if (l >= n) return;
+__device__ __forceinline__ void project_landmark_body(const okc_pinhole& cam, const double* __restrict__ T_CW,
+                                                      const double* __restrict__ hp_W, int l, double reprThreshold,
+                                                      double* __restrict__ proj_xy, uint8_t* __restrict__ status,
+                                                      uint8_t* __restrict__ visible) {
   const double x = hp_W[4 * l], y = hp_W[4 * l + 1], z = hp_W[4 * l + 2], s = hp_W[4 * l + 3];
   double c[3];
   for (int i = 0; i < 3; ++i)
@@ -210,6 +224,15 @@ __global__ void project_landmarks_kernel(okc_pinhole cam, const double* __restri
   visible[l] = vis ? 1 : 0;
 }
 
+__global__ void project_landmarks_kernel(okc_pinhole cam, const double* __restrict__ T_CW,
+                                         const double* __restrict__ hp_W, int n, double reprThreshold,
+                                         double* __restrict__ proj_xy, uint8_t* __restrict__ status,
+                                         uint8_t* __restrict__ visible) {
+  const int l = blockIdx.x * blockDim.x + threadIdx.x;
+  if (l >= n) return;
+  project_landmark_body(cam, T_CW, hp_W, l, reprThreshold, proj_xy, status, visible);
+}
+
 int check_pinhole(const okc_pinhole* cam) {
   if (!cam || cam->width <= 0 || cam->height <= 0) return OKC_ERR_INVALID;
   if (cam->distortion != OKC_DISTORTION_NONE && cam->distortion != OKC_DISTORTION_RADTAN &&
@@ -224,6 +247,10 @@ int check_pinhole(const okc_pinhole* cam) {
 void launch_back_project(const okc_pinhole& cam, const okc_keypoint* kps, int n, double* e_C, uint8_t* valid,
                          int* nValid, cudaStream_t s) {
   if (n > 0) back_project_kernel<<<(n + 127) / 128, 128, 0, s>>>(cam, kps, n, e_C, valid, nValid);
+}
+
+void launch_back_project_slots(const Slot* slots, int n, int max_kp, cudaStream_t s) {
+  if (n > 0 && max_kp > 0) back_project_slots_kernel<<<dim3((max_kp + 127) / 128, n), 128, 0, s>>>(slots, max_kp);
 }
 
 void launch_project_landmarks(const okc_pinhole& cam, const double* T_CW, const double* hp_W, int n,
@@ -443,28 +470,6 @@ extern "C" int okc_keyframe_overlap(okc_context* ctx, int n_views, const int* wi
 // ----------------------------------------------------------------------------------------------
 namespace okc {
 
-struct PrepareArgs {
-  const double* hp_W;          // L x 4
-  const double* quality;       // L
-  const uint8_t* visible;      // L (okc_project_landmarks)
-  const long long* obs_offset; // L + 1
-  const int* obs_view;         // per observation: view (frame, camera) index, in the reference's iteration order
-  const int* obs_kp;           // per observation: keypoint index inside the view
-  const double* view_C;        // V x 9, T_WC_old.C() row-major
-  const double* view_r;        // V x 3, T_WC_old.r()
-  const long long* view_row0;  // V: first row of the view in the descriptor / back-projection pools
-  const uint8_t* desc;         // N x 48
-  const double* e_C;           // N x 3 (Frame::backProjections_)
-  double r_WC1[3];             // T_WC1.r() of the camera being matched
-  double focal_sum;            // focalLengthU() + focalLengthV() (Frontend.cpp:1361-1363)
-  int loop_closure;            // loopClosureLandmarksToUseExclusively != nullptr
-  int L;
-  // per landmark, 3 slots
-  uint8_t* is3d;
-  int* rows;                   // o + 1 for visible landmarks, 0 otherwise
-  int* slot_obs;               // L x 3: observation index that filled the slot (-1: never written)
-};
-
 __device__ __forceinline__ double dot3(const double a[3], const double b[3]) { return (a[0] * b[0] + a[1] * b[1]) + a[2] * b[2]; }
 __device__ __forceinline__ void normalized3(const double v[3], double o[3]) {
   const double n2 = dot3(v, v);
@@ -480,9 +485,7 @@ __device__ __forceinline__ void normalized3(const double v[3], double o[3]) {
   }
 }
 
-__global__ void prune_observations_kernel(PrepareArgs a) {
-  const int l = blockIdx.x * blockDim.x + threadIdx.x;
-  if (l >= a.L) return;
+__device__ __forceinline__ void prune_observations_body(const PrepareArgs& a, int l) {
   int* so = a.slot_obs + 3 * l;
   so[0] = so[1] = so[2] = -1;
   a.is3d[l] = 0;
@@ -537,8 +540,13 @@ __global__ void prune_observations_kernel(PrepareArgs a) {
   a.rows[l] = o + 1;
 }
 
+__global__ void prune_observations_kernel(PrepareArgs a) {
+  const int l = blockIdx.x * blockDim.x + threadIdx.x;
+  if (l < a.L) prune_observations_body(a, l);
+}
+
 // exclusive scan of rows[] -> row_offset[L + 1] (one block; L is a few thousand)
-__global__ void __launch_bounds__(1024) scan_rows_kernel(const int* __restrict__ rows, int L, int* __restrict__ offset) {
+__device__ __forceinline__ void scan_rows_body(const int* __restrict__ rows, int L, int* __restrict__ offset) {
   __shared__ int s_part[1024];
   const int tid = threadIdx.x;
   const int per = (L + 1023) / 1024;
@@ -561,11 +569,15 @@ __global__ void __launch_bounds__(1024) scan_rows_kernel(const int* __restrict__
   if (tid == 1023) offset[L] = s_part[1023];
 }
 
+__global__ void __launch_bounds__(1024) scan_rows_kernel(const int* __restrict__ rows, int L, int* __restrict__ offset) {
+  scan_rows_body(rows, L, offset);
+}
+
 // pool rows: descriptor, owner (landmark index), e_W = C_old * e_C.normalized(), r_W = r_old, filled flag
-__global__ void pack_pool_kernel(PrepareArgs a, const int* __restrict__ offset, uint8_t* __restrict__ pool,
-                                 int* __restrict__ owner, double* __restrict__ e_W, double* __restrict__ r_W,
-                                 uint8_t* __restrict__ filled, int* __restrict__ row_obs) {
-  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+__device__ __forceinline__ void pack_pool_body(const PrepareArgs& a, int t, const int* __restrict__ offset,
+                                               uint8_t* __restrict__ pool, int* __restrict__ owner,
+                                               double* __restrict__ e_W, double* __restrict__ r_W,
+                                               uint8_t* __restrict__ filled, int* __restrict__ row_obs) {
   const int l = t / 3, n = t - 3 * l;
   if (l >= a.L || n >= a.rows[l]) return;
   const int row = offset[l] + n;
@@ -594,6 +606,43 @@ __global__ void pack_pool_kernel(PrepareArgs a, const int* __restrict__ offset, 
     e_W[3 * row + r] = (C[3 * r] * en[0] + C[3 * r + 1] * en[1]) + C[3 * r + 2] * en[2];
     r_W[3 * row + r] = a.view_r[3 * v + r];
   }
+}
+
+__global__ void pack_pool_kernel(PrepareArgs a, const int* __restrict__ offset, uint8_t* __restrict__ pool,
+                                 int* __restrict__ owner, double* __restrict__ e_W, double* __restrict__ r_W,
+                                 uint8_t* __restrict__ filled, int* __restrict__ row_obs) {
+  pack_pool_body(a, blockIdx.x * blockDim.x + threadIdx.x, offset, pool, owner, e_W, r_W, filled, row_obs);
+}
+
+// Frame pipeline (okc_batch_prepare_landmarks_enqueue): the same three steps plus the projection for every slot of a
+// batch at once, blockIdx.y = slot. The landmark pool (points, observations, descriptors of the keyframe window) stays
+// in HBM; per frame only the slot's pose changes.
+__global__ void project_landmarks_slots_kernel(const PrepSlot* __restrict__ prep) {
+  const PrepSlot& p = prep[blockIdx.y];
+  const int l = blockIdx.x * blockDim.x + threadIdx.x;
+  if (l < p.a.L) project_landmark_body(p.cam, p.T_CW, p.a.hp_W, l, p.repr_threshold, p.proj_xy, p.status, p.visible);
+}
+__global__ void prune_observations_slots_kernel(const PrepSlot* __restrict__ prep) {
+  const PrepSlot& p = prep[blockIdx.y];
+  const int l = blockIdx.x * blockDim.x + threadIdx.x;
+  if (l < p.a.L) prune_observations_body(p.a, l);
+}
+__global__ void __launch_bounds__(1024) scan_rows_slots_kernel(const PrepSlot* __restrict__ prep) {
+  const PrepSlot& p = prep[blockIdx.x];
+  scan_rows_body(p.a.rows, p.a.L, p.row_offset);
+}
+__global__ void pack_pool_slots_kernel(const PrepSlot* __restrict__ prep) {
+  const PrepSlot& p = prep[blockIdx.y];
+  pack_pool_body(p.a, blockIdx.x * blockDim.x + threadIdx.x, p.row_offset, p.pool, p.owner, p.e_W, p.r_W, p.filled,
+                 p.row_obs);
+}
+
+void launch_prepare_landmarks_slots(const PrepSlot* prep, int n, int L, cudaStream_t s) {
+  if (n <= 0 || L <= 0) return;
+  project_landmarks_slots_kernel<<<dim3((L + 127) / 128, n), 128, 0, s>>>(prep);
+  prune_observations_slots_kernel<<<dim3((L + 127) / 128, n), 128, 0, s>>>(prep);
+  scan_rows_slots_kernel<<<n, 1024, 0, s>>>(prep);
+  pack_pool_slots_kernel<<<dim3((3 * L + 127) / 128, n), 128, 0, s>>>(prep);
 }
 
 }  // namespace okc

@@ -348,7 +348,8 @@ __device__ __forceinline__ void
 match_to_map_body(const uint8_t* __restrict__ queries, const double* __restrict__ kp_xy,
                     const okc_keypoint* __restrict__ kp_f, const uint8_t* __restrict__ use, int nkMax,
                     const int* __restrict__ nkDev, const uint8_t* __restrict__ map,
-                    const int* __restrict__ owner, int nm, const double* __restrict__ proj_xy, double threshSq,
+                    const int* __restrict__ owner, const uint8_t* __restrict__ is3d, int nm,
+                    const double* __restrict__ proj_xy, double threshSq,
                     double hammingThreshold, double* __restrict__ bestDist, int* __restrict__ bestOwner,
                     unsigned long long* __restrict__ events, int eventSlab,
                     unsigned long long* __restrict__ eventsOverflow, int eventCap, int* __restrict__ eventCount) {
@@ -383,8 +384,10 @@ match_to_map_body(const uint8_t* __restrict__ queries, const double* __restrict_
       if (m < nm) {
         const int o = owner[m];
         s_owner[i] = o;
-        s_px[i] = proj_xy[2 * o];
-        s_py[i] = proj_xy[2 * o + 1];
+        // a row of a landmark that is not 3D yet never passes the gate: matchToMapByThread skips it (Frontend.cpp:1779)
+        const bool skip = is3d && !is3d[o];
+        s_px[i] = skip ? INFINITY : proj_xy[2 * o];
+        s_py[i] = skip ? INFINITY : proj_xy[2 * o + 1];
       }
     }
     __syncthreads();
@@ -433,8 +436,8 @@ match_to_map_kernel(const uint8_t* __restrict__ queries, const double* __restric
                     int nm, const double* __restrict__ proj_xy, double threshSq, double hammingThreshold,
                     double* __restrict__ bestDist, int* __restrict__ bestOwner, unsigned long long* __restrict__ events,
                     int eventCap, int* __restrict__ eventCount) {
-  match_to_map_body(queries, kp_xy, kp_f, use, nkMax, nkDev, map, owner, nm, proj_xy, threshSq, hammingThreshold,
-                    bestDist, bestOwner, events, eventCap, nullptr, eventCap, eventCount);
+  match_to_map_body(queries, kp_xy, kp_f, use, nkMax, nkDev, map, owner, nullptr, nm, proj_xy, threshSq,
+                    hammingThreshold, bestDist, bestOwner, events, eventCap, nullptr, eventCap, eventCount);
 }
 
 // Frame-pipeline form: one launch for all slots of a batch; queries are the slot's own descriptors / keypoints of
@@ -443,9 +446,10 @@ __global__ void __launch_bounds__(256)
 match_to_map_slots_kernel(const Slot* __restrict__ slots, int maxKp, double hammingThreshold) {
   const Slot& slot = slots[blockIdx.z];
   if (slot.map == nullptr) return;  // no map match requested for this slot
-  match_to_map_body(slot.desc, nullptr, slot.kp_desc, nullptr, maxKp, slot.counters + 2, slot.map, slot.owner, slot.nm,
-                    slot.proj, slot.thresh_sq, hammingThreshold, slot.best_dist, slot.best_owner, slot.events,
-                    slot.event_cap, nullptr, slot.event_cap, slot.counters + 4);
+  match_to_map_body(slot.desc, nullptr, slot.kp_desc, nullptr, maxKp, slot.counters + 2, slot.map, slot.owner, slot.is3d,
+                    slot.nm_dev ? min(*slot.nm_dev, slot.nm) : slot.nm, slot.proj, slot.thresh_sq, hammingThreshold,
+                    slot.best_dist, slot.best_owner, slot.events, slot.event_cap, nullptr, slot.event_cap,
+                    slot.counters + 4);
 }
 
 // ----------------------------------------------------------------------------------------------
@@ -473,12 +477,13 @@ __global__ void __launch_bounds__(kBinThreads, 1) bin_projections_kernel(const S
   __shared__ int s_warp[32];
   __shared__ int s_flag;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int ncells = slot.bins_x * slot.bins_y, nm = slot.nm;
+  const int ncells = slot.bins_x * slot.bins_y, nm = slot.nm_dev ? min(*slot.nm_dev, slot.nm) : slot.nm;
   for (int c = tid; c < kMaxBinCells; c += kBinThreads) s_cnt[c] = 0;
   if (tid == 0) s_flag = 0;
   __syncthreads();
   auto cell_of_row = [&](int m, double* px, double* py, int* o) {
     *o = slot.owner[m];
+    if (slot.is3d && !slot.is3d[*o]) return -1;   // matchToMapByThread skips landmarks that are not 3D (Frontend.cpp:1779)
     *px = slot.proj[2 * *o];
     *py = slot.proj[2 * *o + 1];
     const int cx = bin_cell_of(*px, slot.bin_pad, slot.bin_cell, slot.bins_x);
@@ -665,14 +670,15 @@ match_to_map_binned_kernel(const Slot* __restrict__ slots, int maxKp, double ham
     }
   } else {
     // full scan in row order (no bins for this slot, a non-finite projection, or too many hits): rare
-    for (int base = 0; base < slot.nm; base += 32) {
+    const int nmAll = slot.nm_dev ? min(*slot.nm_dev, slot.nm) : slot.nm;
+    for (int base = 0; base < nmAll; base += 32) {
       const int m = base + lane;
       unsigned d = 0xffffffffu;
       int o = -1;
-      if (m < slot.nm) {
+      if (m < nmAll) {
         o = slot.owner[m];
         const double rx = slot.proj[2 * o] - kx, ry = slot.proj[2 * o + 1] - ky;
-        if (!(rx * rx + ry * ry > threshSq)) {
+        if (!(slot.is3d && !slot.is3d[o]) && !(rx * rx + ry * ry > threshSq)) {
           unsigned r[kDescWords];
           load_desc(slot.map, m, r);
           d = hamming384(q, r);
@@ -887,37 +893,39 @@ __device__ V3 triangulate_fast(V3 p1, V3 e1, V3 p2, V3 e2, double c26, double c6
 // ----------------------------------------------------------------------------------------------
 // C. 2D-2D stereo matching, Frontend::matchStereo inner loops (Frontend.cpp:2259-2316)
 // ----------------------------------------------------------------------------------------------
-struct StereoDev {
-  const uint8_t* desc;
-  const double* size;
-  const double* e_C;
-  const uint8_t* bp_valid;
-  int n;
-  double C[9];
-  double r[3];
-  double f;
-};
-
 // MOTION = false: Frontend::matchStereo (Frontend.cpp:2259-2316).
 // MOTION = true : the worker lambda of Frontend::matchMotionStereo (Frontend.cpp:2053-2137): k0 must be eligible
 // (use0: not an initialised landmark, not observed, back-projection valid - estimator state, decided by the
 // caller), sigma from size0 only, an extra e0.e1 >= 0.5 pre-gate, 0.2 m depth gates, and the triangulation quality
 // acos(...) of the accepted match as an additional output.
+// One launch serves every job of a batch (blockIdx.y = job): camera pairs of a multiframe, or (keyframe view, current
+// image) pairs. A side is either host-uploaded arrays or a batch slot whose keypoint count is still on the device.
+__device__ __forceinline__ double side_size(const StereoSide& v, int k) {
+  return v.size_d ? v.size_d[k] : (double)v.kp[k].size;
+}
+
 template <bool MOTION>
 __global__ void __launch_bounds__(256)
-match_stereo_kernel(StereoDev v0, StereoDev v1, const uint8_t* __restrict__ use0, double hammingThreshold,
-                    double* __restrict__ outDist, int* __restrict__ outK1, double* __restrict__ outHp,
-                    uint8_t* __restrict__ outInit, double* __restrict__ outQuality) {
+match_stereo_kernel(const StereoJob* __restrict__ jobs, double hammingThreshold) {
+  const StereoJob& job = jobs[blockIdx.y];
+  const StereoSide& v0 = job.v0;
+  const StereoSide& v1 = job.v1;
   const int lane = threadIdx.x & 31;
   const int k0 = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  if (k0 >= v0.n) return;
-  if (MOTION && !(use0[k0] && v0.bp_valid[k0])) {
+  const int n0 = v0.n_dev ? min(*v0.n_dev, v0.n) : v0.n;
+  const int n1 = v1.n_dev ? min(*v1.n_dev, v1.n) : v1.n;
+  if (k0 >= n0) return;
+  double* __restrict__ outDist = job.dist;
+  int* __restrict__ outK1 = job.k1;
+  double* __restrict__ outHp = job.hp;
+  uint8_t* __restrict__ outInit = job.init;
+  if (MOTION && !((!job.use0 || job.use0[k0]) && v0.bp_valid[k0])) {
     if (lane == 0) {
       outDist[k0] = hammingThreshold;
       outK1[k0] = -1;
       outHp[4 * k0 + 0] = outHp[4 * k0 + 1] = outHp[4 * k0 + 2] = outHp[4 * k0 + 3] = 0.0;
       outInit[k0] = 0;
-      outQuality[k0] = 0.0;
+      job.quality[k0] = 0.0;
     }
     return;
   }
@@ -930,10 +938,10 @@ match_stereo_kernel(StereoDev v0, StereoDev v1, const uint8_t* __restrict__ use0
   double quality = 0.0;
   const V3 r0 = v3(v0.r[0], v0.r[1], v0.r[2]), r1 = v3(v1.r[0], v1.r[1], v1.r[2]);
 
-  for (int base = 0; base < v1.n; base += 32) {
+  for (int base = 0; base < n1; base += 32) {
     const int k1 = base + lane;
     double d = 1e9;
-    if (k1 < v1.n) {
+    if (k1 < n1 && !(job.v1_owner_a && job.v1_owner_a[k1] >= 0) && !(job.v1_owner_b && job.v1_owner_b[k1] >= 0)) {
       unsigned r[kDescWords];
       load_desc(v1.desc, k1, r);
       d = (double)hamming384(q, r);
@@ -947,7 +955,8 @@ match_stereo_kernel(StereoDev v0, StereoDev v1, const uint8_t* __restrict__ use0
       if (!(dc < distances)) continue;
       if (!v0.bp_valid[k0]) continue;
       if (!v1.bp_valid[kc]) continue;
-      const double sigma = MOTION ? v0.size[k0] / v0.f * 0.125 : fmax(v0.size[k0] / v0.f, v1.size[kc] / v1.f) * 0.125;
+      const double sigma = MOTION ? side_size(v0, k0) / v0.f * 0.125
+                                  : fmax(side_size(v0, k0) / v0.f, side_size(v1, kc) / v1.f) * 0.125;
       const V3 e0_W = normalized(matvec(v0.C, v3(v0.e_C[3 * k0], v0.e_C[3 * k0 + 1], v0.e_C[3 * k0 + 2])));
       const V3 e1_W = normalized(matvec(v1.C, v3(v1.e_C[3 * kc], v1.e_C[3 * kc + 1], v1.e_C[3 * kc + 2])));
       if (MOTION && dot(e0_W, e1_W) < 0.5) continue;
@@ -979,22 +988,17 @@ match_stereo_kernel(StereoDev v0, StereoDev v1, const uint8_t* __restrict__ use0
     outHp[4 * k0 + 2] = hps.z / 1.0;
     outHp[4 * k0 + 3] = (MOTION && k1_match < 0) ? 0.0 : 1.0;
     outInit[k0] = initialisable ? 1 : 0;
-    if (MOTION) outQuality[k0] = quality;
+    if (MOTION) job.quality[k0] = quality;
   }
 }
 
-void launch_match_stereo(const StereoDev& v0, const StereoDev& v1, const uint8_t* use0, bool motion,
-                         double hammingThreshold, double* outDist, int* outK1, double* outHp, uint8_t* outInit,
-                         double* outQuality, cudaStream_t s) {
-  if (v0.n <= 0) return;
+void launch_match_stereo_jobs(const StereoJob* jobs, int nJobs, int max0, bool motion, double hammingThreshold,
+                              cudaStream_t s) {
+  if (nJobs <= 0 || max0 <= 0) return;
   const int warpsPerBlock = 8;
-  const int blocks = (v0.n + warpsPerBlock - 1) / warpsPerBlock;
-  if (motion)
-    match_stereo_kernel<true><<<blocks, warpsPerBlock * 32, 0, s>>>(v0, v1, use0, hammingThreshold, outDist, outK1,
-                                                                   outHp, outInit, outQuality);
-  else
-    match_stereo_kernel<false><<<blocks, warpsPerBlock * 32, 0, s>>>(v0, v1, use0, hammingThreshold, outDist, outK1,
-                                                                    outHp, outInit, outQuality);
+  const dim3 grid((max0 + warpsPerBlock - 1) / warpsPerBlock, nJobs);
+  if (motion) match_stereo_kernel<true><<<grid, warpsPerBlock * 32, 0, s>>>(jobs, hammingThreshold);
+  else match_stereo_kernel<false><<<grid, warpsPerBlock * 32, 0, s>>>(jobs, hammingThreshold);
 }
 
 // ----------------------------------------------------------------------------------------------
@@ -1005,38 +1009,42 @@ void launch_match_stereo(const StereoDev& v0, const StereoDev& v1, const uint8_t
 // (:1922-1927), >= 0.2 m from both centres (:1930-1936). Loop-closure rule (:1941-1944): an accepted row of the
 // keypoint's previous landmark only counts and ends that landmark's rows for this keypoint. hps_W is overwritten
 // only by non-parallel accepts (stale value kept otherwise, :1946-1951).
-struct UninitArgs {
-  double r_WC[3];
-  double cos26Sigma, cos6Sigma;   // sigma = 1 / focalLength; cos(2.6 sigma), cos(6 sigma) from the host's libm
-  double hammingThreshold;
-};
-
-__global__ void __launch_bounds__(256)
-match_uninitialised_kernel(const uint8_t* __restrict__ queries, const double* __restrict__ kp_e_W,
-                           const uint8_t* __restrict__ use, const int* __restrict__ previousOwner, int nk,
-                           const uint8_t* __restrict__ map, const int* __restrict__ owner,
-                           const double* __restrict__ map_e_W, const double* __restrict__ map_r_W, int nm,
-                           UninitArgs a, double* __restrict__ outDist, int* __restrict__ outOwner,
-                           double* __restrict__ outHp, uint8_t* __restrict__ outHpWritten,
-                           unsigned* __restrict__ outCtr) {
+__global__ void __launch_bounds__(256) match_uninitialised_kernel(const UninitJob* __restrict__ jobs) {
+  const UninitJob& job = jobs[blockIdx.y];
+  const UninitArgs& a = job.a;
   const int lane = threadIdx.x & 31;
   const int k = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int nk = job.nk_dev ? min(*job.nk_dev, job.nk) : job.nk;
   if (k >= nk) return;
+  const int nm = job.nm_dev ? min(*job.nm_dev, job.nm) : job.nm;
+  const uint8_t* __restrict__ map = job.map;
+  const int* __restrict__ owner = job.owner;
+  const double* __restrict__ map_e_W = job.map_e_W;
+  const double* __restrict__ map_r_W = job.map_r_W;
   double best = a.hammingThreshold;
   int bestO = -1, skipOwner = -1;
   unsigned ctr = 0;
   V3 hps = v3(0.0, 0.0, 0.0);
   bool hpWritten = false;
-  if (use[k]) {
+  // Frontend.cpp:1862-1872: a keypoint takes part when its back-projection is valid and it has no landmark yet
+  bool use = job.use ? job.use[k] != 0 : true;
+  if (job.bp_valid && !job.bp_valid[k]) use = false;
+  if (job.owner14 && job.owner14[k] >= 0) use = false;
+  if (use) {
     unsigned q[kDescWords];
-    load_desc(queries, k, q);
-    const V3 e1_W = v3(kp_e_W[3 * k], kp_e_W[3 * k + 1], kp_e_W[3 * k + 2]);
+    load_desc(job.queries, k, q);
+    V3 e1_W;
+    if (job.kp_e_W) {
+      e1_W = v3(job.kp_e_W[3 * k], job.kp_e_W[3 * k + 1], job.kp_e_W[3 * k + 2]);
+    } else {   // T_WC1.C() * e1_C.normalized()
+      e1_W = matvec(job.C_WC, normalized(v3(job.e_C[3 * k], job.e_C[3 * k + 1], job.e_C[3 * k + 2])));
+    }
     const V3 rC = v3(a.r_WC[0], a.r_WC[1], a.r_WC[2]);
-    const int prev = previousOwner ? previousOwner[k] : -1;
+    const int prev = job.previousOwner ? job.previousOwner[k] : -1;
     for (int base = 0; base < nm; base += 32) {
       const int m = base + lane;
       double d = 1e9;
-      if (m < nm) {
+      if (m < nm && !(job.is3d && job.is3d[owner[m]])) {
         unsigned r[kDescWords];
         load_desc(map, m, r);
         d = (double)hamming384(q, r);
@@ -1082,28 +1090,28 @@ match_uninitialised_kernel(const uint8_t* __restrict__ queries, const double* __
     }
   }
   if (lane == 0) {
-    outDist[k] = best;
-    outOwner[k] = bestO;
-    outHp[4 * k + 0] = hps.x;
-    outHp[4 * k + 1] = hps.y;
-    outHp[4 * k + 2] = hps.z;
-    outHp[4 * k + 3] = hpWritten ? 1.0 : 0.0;
-    outHpWritten[k] = hpWritten ? 1 : 0;
-    outCtr[k] = ctr;
+    job.dist[k] = best;
+    job.best[k] = bestO;
+    job.hp[4 * k + 0] = hps.x;
+    job.hp[4 * k + 1] = hps.y;
+    job.hp[4 * k + 2] = hps.z;
+    job.hp[4 * k + 3] = hpWritten ? 1.0 : 0.0;
+    job.hp_written[k] = hpWritten ? 1 : 0;
+    if (job.ctr) job.ctr[k] = ctr;
+    if (job.slice_ctrs && ctr) {
+      // ctrs[t] of thread slice t (Frontend.cpp:1853-1855): segment = numKeypoints / numThreads, the last takes the rest
+      const int segment = nk / job.num_slices;
+      int t = segment == 0 ? job.num_slices - 1 : k / segment;
+      if (t >= job.num_slices) t = job.num_slices - 1;
+      atomicAdd(job.slice_ctrs + t, (unsigned long long)ctr);
+    }
   }
 }
 
-void launch_match_uninitialised(const uint8_t* queries, const double* kp_e_W, const uint8_t* use,
-                                const int* previousOwner, int nk, const uint8_t* map, const int* owner,
-                                const double* map_e_W, const double* map_r_W, int nm, const UninitArgs& a,
-                                double* outDist, int* outOwner, double* outHp, uint8_t* outHpWritten, unsigned* outCtr,
-                                cudaStream_t s) {
-  if (nk <= 0) return;
+void launch_match_uninit_jobs(const UninitJob* jobs, int nJobs, int maxNk, cudaStream_t s) {
+  if (nJobs <= 0 || maxNk <= 0) return;
   const int warpsPerBlock = 8;
-  const int blocks = (nk + warpsPerBlock - 1) / warpsPerBlock;
-  match_uninitialised_kernel<<<blocks, warpsPerBlock * 32, 0, s>>>(queries, kp_e_W, use, previousOwner, nk, map, owner,
-                                                                  map_e_W, map_r_W, nm, a, outDist, outOwner, outHp,
-                                                                  outHpWritten, outCtr);
+  match_uninitialised_kernel<<<dim3((maxNk + warpsPerBlock - 1) / warpsPerBlock, nJobs), warpsPerBlock * 32, 0, s>>>(jobs);
 }
 
 }  // namespace okc

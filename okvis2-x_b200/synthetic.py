@@ -223,3 +223,99 @@ def sequence_window(desc0, kp_xy0, shift, num_landmarks, seed, width, height):
     proj0 = win["proj"][win["is3d"]]
     proj = proj0[None, :, :] - shift[:, None, :].astype(np.float64)
     return rows, owner, np.ascontiguousarray(proj)
+
+
+# ------------------------------------------------------------------------------------------------------------
+# A geometrically consistent world for the stages after describe (landmark preparation, the two map matchers,
+# matchMotionStereo, matchStereo): a fronto-parallel textured plane at depth Z0 seen by a rig of cameras that look
+# along +z (C_WC = identity) and translate parallel to the plane. Then every camera image is the master canvas cut
+# at an integer offset: `step` px per frame, `disparity` px per camera.
+# ------------------------------------------------------------------------------------------------------------
+def rig_sequence(n_frames, n_cams, width, height, seed, step=(2, 1), disparity=24, dense=False, rects=900):
+    """images[c][f] (u8 H x W): camera c of frame f = master[f * step_y :, 48 + f * step_x - c * disparity :]."""
+    mw = width + step[0] * (n_frames - 1) + disparity * (n_cams - 1) + 64
+    mh = height + step[1] * (n_frames - 1)
+    master = dense_image(mw, mh, seed) if dense else scene_image(mw, mh, seed, rects=rects)
+    x_base = 16 + disparity * (n_cams - 1)
+    out = np.empty((n_cams, n_frames, height, width), np.uint8)
+    for c in range(n_cams):
+        for f in range(n_frames):
+            x0, y0 = x_base + step[0] * f - disparity * c, step[1] * f
+            out[c, f] = master[y0:y0 + height, x0:x0 + width]
+    return out
+
+
+def rig_poses(n_frames, n_cams, fx, fy, step=(2, 1), disparity=24, Z0=3.0):
+    """r_WC[f][c] of the rig above (C_WC = I): content moves by -step px per frame and +disparity px per camera."""
+    tx, ty, B = step[0] * Z0 / fx, step[1] * Z0 / fy, disparity * Z0 / fx
+    r = np.zeros((n_frames, n_cams, 3))
+    for f in range(n_frames):
+        for c in range(n_cams):
+            r[f, c] = (f * tx - c * B, f * ty, 0.0)
+    return r
+
+
+def hamming_rows(a, b):
+    return int(np.unpackbits(np.bitwise_xor(a, b)).sum())
+
+
+def plane_landmarks(views, Z0, fx, max_landmarks, seed, quality=(0.002, 1.0), uninitialised=0.3, keep=0.6):
+    """Landmarks of a keyframe window from its views' keypoints.
+
+    views: list (oldest first) of dict(kp, desc, e_C, valid, r_WC) with C_WC = I. A keypoint's world point is its ray
+    cut with the plane z = Z0; keypoints of different views within one pixel footprint and with Hamming distance
+    < 60 are observations of the same landmark; a fraction `uninitialised` of them gets a quality of 1e-6 and so
+    is not 3D yet. Returns the arguments of okc_landmark_pool_create /
+    okc_prepare_landmarks: (views dict, hp_W, quality, obs_offset, obs_view, obs_kp); observations newest first,
+    as the reference walks them (Frontend.cpp:1420-1424)."""
+    rng = np.random.default_rng(seed)
+    cell = 1.5 * Z0 / fx
+    grid = {}
+    pos, first_desc, obs = [], [], []
+    for v, view in enumerate(views):
+        e, ok = view["e_C"], view["valid"]
+        for k in range(len(view["kp"])):
+            if not ok[k]:
+                continue
+            P = view["r_WC"] + e[k] * (Z0 / e[k][2])
+            gx, gy = int(np.floor(P[0] / cell)), int(np.floor(P[1] / cell))
+            hit = -1
+            for yy in (gy - 1, gy, gy + 1):
+                for xx in (gx - 1, gx, gx + 1):
+                    for l in grid.get((xx, yy), ()):
+                        if abs(pos[l][0] - P[0]) < cell and abs(pos[l][1] - P[1]) < cell and \
+                                hamming_rows(first_desc[l], view["desc"][k]) < 60:
+                            hit = l
+                            break
+            if hit < 0:
+                # (only a fraction `keep` of the scene points are landmarks: the rest stays for matchMotionStereo)
+                if len(pos) >= max_landmarks or ((gx * 73856093) ^ (gy * 19349663)) % 1000 >= int(keep * 1000):
+                    continue
+                hit = len(pos)
+                pos.append(P)
+                first_desc.append(view["desc"][k])
+                obs.append([])
+                grid.setdefault((gx, gy), []).append(hit)
+            if all(o[0] != v for o in obs[hit]):
+                obs[hit].append((v, k))
+    L = len(pos)
+    w = rng.uniform(0.5, 2.0, (L, 1))
+    hp_W = np.concatenate([np.asarray(pos).reshape(L, 3) * w, w], 1)
+    q = rng.uniform(quality[0], quality[1], L)
+    # a landmark of (near) zero quality fails the reference's is3d test (Frontend.cpp:1431-1438): it is matched by
+    # matchToMapByThreadUnitialised instead of matchToMapByThread
+    q[rng.random(L) < uninitialised] = 1e-6
+    obs_offset = np.zeros(L + 1, np.int64)
+    obs_view, obs_kp = [], []
+    for l in range(L):
+        for v, k in reversed(obs[l]):
+            obs_view.append(v)
+            obs_kp.append(k)
+        obs_offset[l + 1] = len(obs_view)
+    n_per = [len(v["kp"]) for v in views]
+    row0 = np.concatenate([[0], np.cumsum(n_per)[:-1]]).astype(np.int64)
+    eye = np.eye(3).reshape(9)
+    vd = dict(C_WC=np.array([eye for _ in views]), r_WC=np.array([v["r_WC"] for v in views]), row0=row0,
+              desc=np.concatenate([v["desc"] for v in views]).reshape(-1, 48),
+              e_C=np.concatenate([v["e_C"] for v in views]).reshape(-1, 3))
+    return vd, hp_W, q, obs_offset, np.asarray(obs_view, np.int32), np.asarray(obs_kp, np.int32)

@@ -1,0 +1,194 @@
+"""GPU parity of the device-resident frame pipeline (rows a15-a17 inside the pipeline, f1 and f2 as
+stages): back-projections after describe, landmark preparation + matchToMapByThread + matchToMapByThreadUnitialised
+from a landmark pool kept in HBM, matchStereo between slots, matchMotionStereo against retained keyframes - against the
+CPU restatement (oracle/pipeline_port.py -> oracle/port) fed with the very same keypoints / descriptors, and against
+the host-buffer entry points. Bar: integer outputs and FP64 results of +, -, *, /, sqrt bit-exact; acos within 1e-12.
+"""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+Z0, DISP, STEP = 3.0, 24, (2, 1)
+
+
+def _rig(mod, syn, ctx, cfgname, n_cams, max_kp):
+    if cfgname == "euroc":
+        cfg, c = syn.EUROC, syn.EUROC["cams"][0]
+        model = mod.Pinhole.make(752, 480, c["f"], c["c"], "radialtangential", c["d"])
+        W, H = 752, 480
+    elif cfgname == "d455":
+        cfg = syn.D455
+        W, H = 848, 480
+        model = mod.Pinhole.make(W, H, (425.0, 424.2), (423.1, 238.7), "radialtangential", (-0.05, 0.06, 3e-4, -2e-4))
+    else:
+        cfg = syn.HILTI
+        W, H = 720, 540
+        model = mod.Pinhole.make(W, H, (351.3, 351.5), (367.7, 253.8), "equidistant", (-0.03696, -0.008917, 0.008912, -0.003785))
+    cams = [mod.Camera(ctx, W, H, max_keypoints=max_kp) for _ in range(n_cams)]
+    for cam in cams:
+        cam.set_geometry(model)
+    return cfg, model, cams, W, H
+
+
+def _poses(mod, r_WC):
+    eye = np.eye(3)
+    return np.stack([mod.slot_pose(eye, r) for r in r_WC])
+
+
+def _view(kp, desc, e_C, valid, r_WC, f):
+    return dict(desc=desc, size=kp["size"].astype(np.float64), e_C=e_C, bp_valid=valid, C_WC=np.eye(3).reshape(9),
+                r_WC=np.asarray(r_WC, np.float64), f=f)
+
+
+@pytest.mark.parametrize("cfgname,n_cams,dense", [("euroc", 2, False), ("euroc", 2, True), ("d455", 2, True),
+                                                   ("hilti", 3, False)])
+def test_frame_pipeline_vs_port(cfgname, n_cams, dense, mod, ctx, port, ref, syn):
+    import pipeline_port
+    max_kp = 2048 if cfgname == "d455" else 768
+    cfg, model, cams, W, H = _rig(mod, syn, ctx, cfgname, n_cams, max_kp)
+    tol = 1e-12 if cfgname == "hilti" else 0.0     # equidistant: atan / sqrt of glibc vs the device (last ulp)
+    n_frames, n_kf = 7, 3
+    imgs = syn.rig_sequence(n_frames, n_cams, W, H, seed=17, step=STEP, disparity=DISP, dense=dense)
+    r_all = syn.rig_poses(n_frames, n_cams, model.fu, model.fv, STEP, DISP, Z0)
+    f_mean = 0.5 * (model.fu + model.fv)
+    det = (cfg["radius"], 0, cfg["abs_threshold"], cfg["max_kpt"])
+    dirs = [(0.0, 1.0, 0.0)] * n_cams
+    batch = mod.Batch(ctx, cams)
+    cpu = pipeline_port.CpuPipeline(ref, port)
+    # ---- keyframes: frames 0 .. n_kf-1, retained on the device; their data also read back to build the world ----
+    kfs, views = [], []
+    for f in range(n_kf):
+        batch.enqueue([imgs[c, f] for c in range(n_cams)], *det, dirs)
+        batch.set_poses(_poses(mod, r_all[f]))
+        kf = mod.Keyframe(ctx, n_cams, max_kp)
+        batch.retain(list(range(n_cams)), kf)
+        batch.finish()
+        for c in range(n_cams):
+            kp, desc = batch.slot_frame(c)
+            e_C, valid, nv = batch.slot_back_projections(c, len(kp))
+            pe, pvalid, pnv = port.back_project(model, kp)
+            assert np.array_equal(valid, pvalid) and nv == pnv
+            assert (e_C.tobytes() == pe.tobytes()) if tol == 0.0 else float(np.abs(e_C - pe).max()) <= tol
+            views.append(dict(kp=kp, desc=desc, e_C=e_C, valid=valid, r_WC=r_all[f, c], frame=f, cam=c))
+            assert len(kp) > 50
+        kfs.append(kf)
+    pool_args = syn.plane_landmarks(views, Z0, model.fu, 2000, seed=5)
+    vd, hp_W, quality, off, ov, ok = pool_args
+    assert len(hp_W) > 200 and (np.diff(off) > 1).sum() > 50       # real multi-view landmarks
+    pool = mod.LandmarkPool(ctx, vd, hp_W, quality, off, ov, ok)
+    # eligibility flags of the keyframes' keypoints (estimator state in the reference): a seeded 80 %
+    rng = np.random.default_rng(3)
+    use0 = {}
+    for i, v in enumerate(views):
+        use0[(v["frame"], v["cam"])] = (rng.random(len(v["kp"])) < 0.8).astype(np.uint8)
+        kfs[v["frame"]].set_view(v["cam"], np.eye(3), v["r_WC"], f_mean, use0[(v["frame"], v["cam"])])
+    # ---- the frame under test ----
+    f = n_frames - 1
+    batch.enqueue([imgs[c, f] for c in range(n_cams)], *det, dirs)
+    batch.set_poses(_poses(mod, r_all[f]))
+    batch.match_landmarks_enqueue(pool, 60.0, cfg["slices"], mod.STAGE_UNINITIALISED)
+    pairs = [(c, c + 1) for c in range(n_cams - 1)]
+    batch.match_stereo_enqueue(pairs, 60.0)
+    jobs = [(kfs[k], c, c) for k in range(n_kf) for c in range(n_cams)]
+    batch.match_motion_enqueue(jobs, 60.0, only_unmatched=True)
+    batch.finish()
+    cur = []
+    n3d_matches = n2d_matches = 0
+    for c in range(n_cams):
+        kp, desc = batch.slot_frame(c)
+        assert len(kp) > 50
+        e_C, valid, nv = batch.slot_back_projections(c, len(kp))
+        pe, pvalid, _ = port.back_project(model, kp)
+        assert np.array_equal(valid, pvalid)
+        assert (e_C.tobytes() == pe.tobytes()) if tol == 0.0 else float(np.abs(e_C - pe).max()) <= tol
+        pose = (np.eye(3), r_all[f, c], mod.slot_pose(np.eye(3), r_all[f, c])[:12])
+        want = cpu.landmark_stage(model, pose, kp, desc, e_C, valid, pool_args, 60.0, cfg["slices"])
+        lm = batch.slot_landmarks(c)
+        prep = want["prep"]
+        assert np.array_equal(lm["visible"], want["visible"]) and lm["nm"] == prep["nm"] > 0
+        vis = want["visible"] != 0
+        if tol == 0.0:
+            assert lm["proj"].tobytes() == want["proj"].tobytes()
+        else:
+            assert float(np.abs(lm["proj"][vis] - want["proj"][vis]).max()) <= 1e-9
+        for k in ("is3d", "rows"):
+            assert np.array_equal(lm[k], prep[k]), k
+        assert np.array_equal(lm["owner"], prep["owner"]) and np.array_equal(lm["pool"], prep["pool"])
+        assert 0 < prep["is3d"].sum() < vis.sum()            # both map matchers have landmarks
+        bd, bo, ctrs, errs = batch.slot_matches(c, len(kp))
+        wd, wo, wc, we = want["a14"]
+        assert np.array_equal(bd, wd) and np.array_equal(bo, wo) and np.array_equal(ctrs, wc)
+        if tol == 0.0:
+            assert errs.tobytes() == we.tobytes()
+        else:
+            assert np.allclose(errs, we, rtol=1e-9, atol=0, equal_nan=True)
+        ud, uo, uhp, uhw, uc = batch.slot_uninitialised(c, len(kp))
+        xd, xo, xhp, xhw, xc = want["a15"]
+        assert np.array_equal(ud, xd) and np.array_equal(uo, xo) and np.array_equal(uhw, xhw) and np.array_equal(uc, xc)
+        assert uhp[:, :3].tobytes() == xhp[:, :3].tobytes() if tol == 0.0 else np.allclose(uhp[:, :3], xhp[:, :3], rtol=1e-9)
+        n3d_matches += int((bo >= 0).sum())
+        n2d_matches += int((uo >= 0).sum())
+        cur.append(dict(kp=kp, desc=desc, e_C=e_C, valid=valid, unmatched=(bo < 0) & (uo < 0)))
+    assert n3d_matches > 20 and n2d_matches > 0
+    # ---- matchStereo between the cameras ----
+    stereo_matches = 0
+    for p, (c0, c1) in enumerate(pairs):
+        v0 = _view(cur[c0]["kp"], cur[c0]["desc"], cur[c0]["e_C"], cur[c0]["valid"], r_all[f, c0], f_mean)
+        v1 = _view(cur[c1]["kp"], cur[c1]["desc"], cur[c1]["e_C"], cur[c1]["valid"], r_all[f, c1], f_mean)
+        got = batch.pair_stereo(p, len(cur[c0]["kp"]))
+        want = port.match_stereo(v0, v1, 60.0)
+        host = ctx.match_stereo(v0, v1, 60.0)          # the host-buffer entry point runs the same kernel
+        for g, w, hst in zip(got, want, host):
+            assert g.tobytes() == w.tobytes() == hst.tobytes()
+        stereo_matches += int((got[0] < 60.0).sum())
+    assert stereo_matches > 20
+    # ---- matchMotionStereo against the retained keyframes ----
+    motion_matches = 0
+    for j, (kf, view, slot) in enumerate(jobs):
+        k = j // n_cams
+        v = views[k * n_cams + view]
+        v0 = _view(v["kp"], v["desc"], v["e_C"], v["valid"], v["r_WC"], f_mean)
+        v1 = _view(cur[slot]["kp"], cur[slot]["desc"], cur[slot]["e_C"], cur[slot]["valid"], r_all[f, slot], f_mean)
+        got = batch.job_motion(j)
+        want = cpu.motion(v0, use0[(k, view)], v1, cur[slot]["unmatched"], 60.0)
+        assert len(got[0]) == len(v["kp"])
+        for name, g, w in zip(("dist", "k1", "hp", "init"), got[:4], want[:4]):
+            assert g.tobytes() == w.tobytes(), (j, name)
+        assert float(np.abs(got[4] - want[4]).max()) <= 1e-12
+        motion_matches += int((got[1] >= 0).sum())
+    assert motion_matches > 20
+    for kf in kfs:
+        kf.close()
+    pool.close()
+    batch.close()
+    for cam in cams:
+        cam.close()
+
+
+def test_pipeline_stage_errors(mod, ctx, syn):
+    """The stages refuse loudly what they cannot do: no geometry, no poses, slots out of range."""
+    cam = mod.Camera(ctx, 320, 240, max_keypoints=256)
+    batch = mod.Batch(ctx, [cam, cam])
+    img = syn.scene_image(320, 240, 2, rects=100)
+    batch.enqueue([img, img], 20.0, 0, 50.0, 200, [(0.0, 1.0, 0.0)] * 2)
+    with pytest.raises(mod.OkcError):
+        batch.match_stereo_enqueue([(0, 1)])          # no geometry
+    batch.finish()
+    model = mod.Pinhole.make(320, 240, (200.0, 200.0), (160.0, 120.0), "none", ())
+    cam.set_geometry(model)
+    batch.enqueue([img, img], 20.0, 0, 50.0, 200, [(0.0, 1.0, 0.0)] * 2)
+    with pytest.raises(mod.OkcError):
+        batch.match_stereo_enqueue([(0, 1)])          # no poses
+    batch.set_poses(np.stack([mod.slot_pose(np.eye(3), (0, 0, 0)), mod.slot_pose(np.eye(3), (0.1, 0, 0))]))
+    with pytest.raises(mod.OkcError):
+        batch.match_stereo_enqueue([(0, 5)])          # slot out of range
+    batch.match_stereo_enqueue([(0, 1)])
+    batch.finish()
+    kp, desc = batch.slot_frame(0)
+    dist, k1, hp, init = batch.pair_stereo(0, len(kp))
+    assert len(dist) == len(kp)
+    with pytest.raises(mod.OkcError):
+        mod.Camera(ctx, 320, 240, max_keypoints=16).set_geometry(mod.Pinhole.make(640, 480, (1, 1), (1, 1), "none", ()))
+    batch.close()
+    cam.close()
