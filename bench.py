@@ -1,20 +1,22 @@
 #!/usr/bin/env python3
-"""bench.py - BASELINE.json's metric on BASELINE.json's config, one JSON line on stdout.
+"""bench.py - BASELINE.json's metric on BASELINE.json's configs, one JSON line on stdout.
 
-Workload (configs[1]): EuRoC-config frontend on a synthetic 752x480 stereo sequence. One "step" = one pass of the
-hot path over one batch of --frames-per-batch (32) stereo frames; per frame and camera: BRISK detect (Harris + NMS +
-uniformity + sub-pixel) -> camera-aware 48-byte describe -> matchToMap (3D-2D, pixel gate + Hamming < 60) against a
-2 000-landmark keyframe window. The metric is frames/s (= steps x frames per step / time).
+Headline workload (configs[1]): EuRoC-config frontend on a synthetic 752x480 stereo sequence. One "step" = one pass of
+the hot path over one batch of --frames-per-batch stereo frames; per frame and camera: BRISK detect (Harris + NMS +
+uniformity + sub-pixel) -> camera-aware 48-byte describe -> back-projections -> Frontend::matchToMap against a
+2 000-landmark keyframe window kept in HBM (landmark preparation for the frame's pose, matchToMapByThread on the 3D
+landmarks, matchToMapByThreadUnitialised on the others). The metric is frames/s (= steps x frames per step / time).
 
-  value  frames/s with every input already in HBM (200-frame image pool = 144 MB > L2, projections, map window),
-         results left on the device; CUDA events around the K steps; max over ranks.
-  e2e    frames/s through the drop-in C ABI with HOST buffers: H2D of the images and projections, D2H of keypoints,
+  value  frames/s with every input already in HBM (image pool larger than L2, landmark pool), results left on the
+         device; CUDA events around the K steps; max over ranks.
+  e2e    frames/s through the drop-in C ABI with HOST buffers: H2D of the images and poses, D2H of keypoints,
          descriptors and match lists inside the timed region, every step.
+  extra.configs   the same three numbers (+ CPU baseline + in-run parity count) for every BASELINE.json config:
+         [0] stereo pair + matchStereo, [1] the headline, [2] Hilti22 5 x 720x540 multiframe (cameras sharded over ranks
+         under --gpus N, keypoints + descriptors all-gathered over NCCL for the cross-camera matchStereo),
+         [3] D455 848x480 at a 2 500-keypoint budget with matchMotionStereo against 5 keyframes, [4] the 10k x 1M sweep.
   --impl reference   the reference's own CPU code (oracle/_ref = external/brisk compiled unchanged, + the restated
-         Frontend.cpp matchers) on all host cores, same workload.
-
-N > 1 (torchrun): frames are sharded round-robin over ranks, no data-path collective ("weak"); the matcher sweep
-in `extra` shards map rows and gathers per-shard bests over NCCL.
+         Frontend.cpp / okvis_cv loops of oracle/port) on all host cores, headline workload.
 """
 import argparse
 import ctypes as C
@@ -31,23 +33,42 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-N_FRAMES = 200          # image pool: 200 x 2 x 360 960 B = 144 MB, larger than the 126 MB L2
-NUM_LANDMARKS = 2000
 E2E_REPEATS = 3
-MAX_KP = 768            # camera handle capacity (config budget is 700)
 DIRECTION = (0.05, 0.99, 0.1)   # gravity in the camera frame (Frontend.cpp:234-238); any fixed unit-ish vector
+Z0, DISPARITY, STEP = 3.0, 24, (2, 1)   # the synthetic world: see okvis2-x_b200/synthetic.py (rig_sequence)
+HAMMING = 60.0
+
+# name -> (rig, frames in the image pool (> L2), keyframes, stages, dense scene)
+CONFIGS = {
+    "stereo_pair": dict(index=0, rig="euroc", frames=200, keyframes=0, landmarks=False, stereo=True, motion=False,
+                        what="configs[0]: 752x480 stereo pair, 2x(detect+describe+back-project) + matchStereo"),
+    "euroc_sequence": dict(index=1, rig="euroc", frames=200, keyframes=5, landmarks=True, stereo=False, motion=False,
+                           what="configs[1]: EuRoC 752x480 stereo sequence, per frame 2x(detect+describe+back-project) + "
+                                "matchToMap (landmark preparation, matchToMapByThread, matchToMapByThreadUnitialised) vs a "
+                                "2000-landmark keyframe window"),
+    "hilti_multiframe": dict(index=2, rig="hilti", frames=80, keyframes=5, landmarks=True, stereo=True, motion=False,
+                             what="configs[2]: Hilti22 5 x 720x540 multiframe, per camera detect+describe+back-project + "
+                                  "matchToMap, matchStereo over the 4 adjacent camera pairs"),
+    "d455_sequence": dict(index=3, rig="d455", frames=180, keyframes=5, landmarks=True, stereo=False, motion=True,
+                          what="configs[3]: D455 848x480 stereo at max_num_keypoints 2500, per frame 2x(detect+describe+"
+                               "back-project) + matchToMap + matchMotionStereo vs 5 keyframes"),
+}
+HEADLINE = "euroc_sequence"
+NUM_LANDMARKS = 2000
 
 
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=500, help="batches of --frames-per-batch stereo frames")
-    ap.add_argument("--warmup", type=int, default=12)
+    ap.add_argument("--steps", type=int, default=300, help="batches of --frames-per-batch frames (headline config)")
+    ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--frames-per-batch", type=int, default=32, help="stereo frames per launch chain (48 gives +3 % resident, -2 % end to end)")
+    ap.add_argument("--frames-per-batch", type=int, default=32, help="frames (multiframes) per launch chain")
     ap.add_argument("--in-flight", type=int, default=4, help="batches in flight (one stream each)")
     ap.add_argument("--no-sweep", action="store_true", help="skip the 10k x 1M matcher sweep in `extra`")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--only", default="", help="comma-separated config names (default: all; the headline always runs)")
+    ap.add_argument("--sparse", action="store_true", help="round-1 scene (400 large rectangles) instead of the dense one")
     return ap.parse_args()
 
 
@@ -107,110 +128,127 @@ class ClockSampler:
         return out
 
 
-def build_workload(syn):
-    """Everything a step reads, as host arrays (pure function of the seeds)."""
-    cfg = syn.EUROC
-    W, H = cfg["width"], cfg["height"]
-    left, right, shift = syn.stereo_sequence(N_FRAMES, W, H, seed=2)
-    cams = []
-    for c in cfg["cams"]:
-        rays, jac = syn.camera_maps(W, H, c["f"], c["c"], c["d"])
-        cams.append(dict(rays=rays, jac=jac, focal=c["f"][0], fmean=0.5 * (c["f"][0] + c["f"][1])))
-    return dict(cfg=cfg, W=W, H=H, images=(left, right), shift=shift, cams=cams)
+# ------------------------------------------------------------------------------------------------------------
+# Workload: everything a step reads, as host arrays (pure functions of the seeds + the keyframe views, which are
+# produced by whichever implementation builds the world)
+# ------------------------------------------------------------------------------------------------------------
+def build_images(syn, name, sparse=False):
+    conf = CONFIGS[name]
+    rig = syn.RIGS[conf["rig"]]
+    W, H, n_cams = rig["width"], rig["height"], rig["n_cams"]
+    imgs = syn.rig_sequence(conf["frames"], n_cams, W, H, seed=2 + conf["index"], step=STEP, disparity=DISPARITY,
+                            dense=not sparse, rects=400)
+    rays, jac = syn.rig_maps(rig)
+    r_all = syn.rig_poses(conf["frames"], n_cams, rig["f"][0], rig["f"][1], STEP, DISPARITY, Z0)
+    kf_frames = [int(round((i + 0.5) * conf["frames"] / conf["keyframes"])) for i in range(conf["keyframes"])]
+    return dict(name=name, conf=conf, rig=rig, cfg=rig["cfg"], W=W, H=H, n_cams=n_cams, images=imgs, rays=rays, jac=jac,
+                r_all=r_all, kf_frames=kf_frames, f_mean=0.5 * (rig["f"][0] + rig["f"][1]))
+
+
+def build_world(syn, wl, keyframe_views):
+    """keyframe_views[(frame, cam)] = dict(kp, desc, e_C, valid): the landmark pool of the keyframe window and the
+    eligibility flags of the keyframes' keypoints (estimator state in the reference: a seeded 80 %)."""
+    views = []
+    for f in wl["kf_frames"]:
+        for c in range(wl["n_cams"]):
+            v = dict(keyframe_views[(f, c)])
+            v["r_WC"] = wl["r_all"][f, c]
+            views.append(v)
+    wl["views"] = views
+    if wl["conf"]["landmarks"]:
+        wl["pool_args"] = syn.plane_landmarks(views, Z0, wl["rig"]["f"][0], NUM_LANDMARKS, seed=5)
+    rng = np.random.default_rng(11)
+    wl["use0"] = [(rng.random(len(v["kp"])) < 0.8).astype(np.uint8) for v in views]
+    return wl
 
 
 # ------------------------------------------------------------------------------------------------------------
-# CPU arm: the reference's own code (oracle/_ref) + the restated matchers (oracle/port). Checker/baseline only.
+# CPU arm: the reference's own code (oracle/_ref) + the restated okvis loops (oracle/port). Checker / baseline only.
 # ------------------------------------------------------------------------------------------------------------
 class CpuFrontend:
-    def __init__(self, wl):
+    def __init__(self, mod, syn, wl):
         sys.path.insert(0, os.path.join(ROOT, "oracle"))
+        import pipeline_port
         import refbind
-        self.rb = refbind
-        self.wl = wl
+        self.rb, self.mod, self.syn, self.wl = refbind, mod, syn, wl
         self.ref = refbind.Ref()
         self.port = refbind.Port()
-        self.kind = "reference"  # detect/describe/Hamming = compiled reference; matcher loop = restated port
-        self.windows = None
+        self.pipe = pipeline_port.CpuPipeline(self.ref, self.port)
+        rig = wl["rig"]
+        self.model = mod.Pinhole.make(wl["W"], wl["H"], rig["f"], rig["c"], rig["distortion"], rig["k"])
+        self.kind = "reference"  # detect/describe/Hamming = compiled reference; okvis loops = restated port
+        c = wl["cfg"]
+        self.det = (c["radius"], 0, c["abs_threshold"], c["max_kpt"])
 
     def extractors(self):
         """One camera-aware extractor per camera (not thread-safe: one set per worker)."""
         out = []
-        for c in self.wl["cams"]:
+        for _ in range(self.wl["n_cams"]):
             e = self.rb.RefExtractor(self.ref, True, False)
-            e.set_camera(c["rays"], c["jac"], np.float32(c["focal"]))
+            e.set_camera(self.wl["rays"], self.wl["jac"], np.float32(self.wl["rig"]["f"][0]))
             e.set_direction(np.asarray(DIRECTION, np.float32))
             out.append(e)
         return out
 
-    def detect_describe(self, ext, cam, f):
-        cfg = self.wl["cfg"]
-        img = self.wl["images"][cam][f]
-        kp = self.ref.detect(img, cfg["radius"], 0, cfg["abs_threshold"], cfg["max_kpt"])
-        return ext.describe(img, kp)
+    def view_of(self, f, c, ext):
+        kp, desc = self.pipe.detect_describe(ext, self.wl["images"][c, f], self.det)
+        e_C, valid, _ = self.port.back_project(self.model, kp)
+        return dict(kp=kp, desc=desc, e_C=e_C, valid=valid)
 
-    def set_windows(self, windows):
-        """windows[cam] = (rows, owner, proj[n_frames, L, 2]); adds row_start for the port's landmark-major loop."""
-        self.windows = []
-        for rows, owner, proj in windows:
-            L = proj.shape[1]
-            row_start = np.searchsorted(owner.astype(np.int64), np.arange(L + 1)).astype(np.int32)
-            self.windows.append((np.ascontiguousarray(rows), row_start, proj, L))
+    def keyframe_views(self, exts):
+        return {(f, c): self.view_of(f, c, exts[c]) for f in self.wl["kf_frames"] for c in range(self.wl["n_cams"])}
 
-    def match_slice(self, cam, f, kp, desc, t, slices, dist, ids, ctrs, errs, use):
-        rows, row_start, proj, L = self.windows[cam]
-        kp_xy = np.stack([kp["x"], kp["y"]], 1).astype(np.float64)
-        gate = (3.0 + self.wl["cams"][cam]["fmean"] * 0.06) ** 2
-        p = lambda a: C.c_void_p(a.ctypes.data)
-        self.port.L.port_match_to_map_thread(t, slices, p(desc), p(kp_xy), p(use), len(desc), p(rows), p(row_start), L,
-                                             p(np.ascontiguousarray(proj[f])), None, float(gate), p(dist), p(ids),
-                                             p(ctrs), p(errs))
+    def stereo_view(self, v, r_WC):
+        return dict(desc=v["desc"], size=v["kp"]["size"].astype(np.float64), e_C=v["e_C"], bp_valid=v["valid"],
+                    C_WC=np.eye(3).reshape(9), r_WC=np.asarray(r_WC, np.float64), f=self.wl["f_mean"])
 
-    def match(self, cam, f, kp, desc, threaded):
-        slices = self.wl["cfg"]["slices"]
-        n = len(desc)
-        dist = np.full(n, 60.0, np.float64)
-        ids = np.full(n, -1, np.int32)
-        ctrs = np.zeros(slices, np.uint64)
-        errs = np.zeros(slices, np.float64)
-        use = np.ones(n, np.uint8)
-        args = (cam, f, kp, np.ascontiguousarray(desc), )
-        if threaded:
-            th = [threading.Thread(target=self.match_slice, args=args + (t, slices, dist, ids, ctrs, errs, use))
-                  for t in range(slices)]
-            for x in th:
-                x.start()
-            for x in th:
-                x.join()
-        else:
-            for t in range(slices):
-                self.match_slice(*args, t, slices, dist, ids, ctrs, errs, use)
-        return dist, ids, ctrs, errs
+    def stages(self, f, cur, threaded):
+        """Everything after describe for the multiframe `f` whose per-camera views are `cur`."""
+        wl, conf = self.wl, self.wl["conf"]
+        out = {"lm": [], "stereo": [], "motion": []}
+        n_cams = wl["n_cams"]
+        if conf["landmarks"]:
+            for c in range(n_cams):
+                r = wl["r_all"][f, c]
+                pose = (np.eye(3), r, self.mod.slot_pose(np.eye(3), r)[:12])
+                v = cur[c]
+                out["lm"].append(self.pipe.landmark_stage(self.model, pose, v["kp"], v["desc"], v["e_C"], v["valid"],
+                                                          wl["pool_args"], HAMMING, wl["cfg"]["slices"], threaded=threaded))
+        if conf["motion"]:
+            nk = len(wl["kf_frames"])
+            for k in range(nk):
+                for c in range(n_cams):
+                    kv = wl["views"][k * n_cams + c]
+                    v0 = self.stereo_view(kv, kv["r_WC"])
+                    v1 = self.stereo_view(cur[c], wl["r_all"][f, c])
+                    lm = out["lm"][c]
+                    unmatched = (lm["a14"][1] < 0) & (lm["a15"][1] < 0)
+                    out["motion"].append(self.pipe.motion(v0, wl["use0"][k * n_cams + c], v1, unmatched, HAMMING))
+        if conf["stereo"]:
+            for c in range(n_cams - 1):
+                out["stereo"].append(self.port.match_stereo(self.stereo_view(cur[c], wl["r_all"][f, c]),
+                                                            self.stereo_view(cur[c + 1], wl["r_all"][f, c + 1]), HAMMING))
+        return out
 
     def frame_like_reference(self, exts, f):
         """Threading as the reference does it: one thread per camera for detect+describe (ThreadedSlam.cpp:676-693),
-        then num_matching_threads slices per camera (Frontend.cpp:1519-1536)."""
-        out = [None, None]
+        num_matching_threads slices per camera for the two map matchers (Frontend.cpp:1519-1536, 1631-1645), the rest
+        on the calling thread."""
+        n_cams = self.wl["n_cams"]
+        cur = [None] * n_cams
 
-        def dd(cam):
-            out[cam] = self.detect_describe(exts[cam], cam, f)
-        th = [threading.Thread(target=dd, args=(c,)) for c in range(2)]
+        def dd(c):
+            cur[c] = self.view_of(f, c, exts[c])
+        th = [threading.Thread(target=dd, args=(c,)) for c in range(n_cams)]
         for x in th:
             x.start()
         for x in th:
             x.join()
-        res = []
-        for cam in range(2):
-            kp, desc = out[cam]
-            res.append((kp, desc) + self.match(cam, f, kp, desc, True))
-        return res
+        return cur, self.stages(f, cur, True)
 
     def frame_sequential(self, exts, f):
-        res = []
-        for cam in range(2):
-            kp, desc = self.detect_describe(exts[cam], cam, f)
-            res.append((kp, desc) + self.match(cam, f, kp, desc, False))
-        return res
+        cur = [self.view_of(f, c, exts[c]) for c in range(self.wl["n_cams"])]
+        return cur, self.stages(f, cur, False)
 
     def throughput_all_cores(self, frames, cores):
         """One whole frame per worker at a time, `cores` workers: the most the host can do with this code.
@@ -237,29 +275,489 @@ class CpuFrontend:
         return len(frames) / (time.perf_counter() - t0)
 
 
-def make_windows(syn, wl, frame0):
-    """frame0[cam] = (kp, desc) of frame 0 -> per-camera (rows, owner, proj[n_frames, L, 2])."""
-    out = []
-    for cam in range(2):
-        kp, desc = frame0[cam]
-        kp_xy = np.stack([kp["x"], kp["y"]], 1).astype(np.float64)
-        out.append(syn.sequence_window(desc, kp_xy, wl["shift"], NUM_LANDMARKS, 7 + cam, wl["W"], wl["H"]))
-    return out
-
-
 # ------------------------------------------------------------------------------------------------------------
 # B200 arm
 # ------------------------------------------------------------------------------------------------------------
-def pad256(n):
-    return (n + 255) & ~255
+def stage_bytes(kernel, W, H, K, M, L):
+    """ALGORITHMIC bytes of the stage a kernel belongs to, per image (SURVEY.md 8(d), DESIGN.md 'Roofline')."""
+    if kernel in ("harris_nms", "order_candidates", "select_keypoints"):
+        return W * H + K * 28                       # detect: image in, keypoints out
+    if kernel == "border_filter+describe":
+        return W * H + K * (28 + 4 * 12 + 24) + K * (48 + 28)   # image + kp + 4 rays + 1 Jacobian in; desc + kp out
+    if kernel == "back_project":
+        return K * (28 + 24 + 1)
+    if kernel == "prepare_landmarks":
+        return L * (32 + 8) + M * (48 + 48 + 4 + 48)            # points in; rows, rays, centres, owners out
+    return (K + M) * 48 + K * 16                    # any matcher: descriptors in, (dist, id) out
+
+
+class GpuConfig:
+    """One BASELINE.json frame config on this rank's GPU: handles, pools, batches and the step loops."""
+
+    def __init__(self, args, mod, syn, torch, ctx, wl, rank, world, shard_cameras=False):
+        self.args, self.mod, self.syn, self.torch, self.ctx, self.wl = args, mod, syn, torch, ctx, wl
+        self.rank, self.world = rank, world
+        conf, rig = wl["conf"], wl["rig"]
+        self.conf = conf
+        W, H = wl["W"], wl["H"]
+        # camera-sharded multiframe (configs[2] under --gpus N): camera c lives on rank c mod N
+        self.cams_here = [c for c in range(wl["n_cams"]) if (not shard_cameras) or c % world == rank]
+        self.shard_cameras = shard_cameras
+        self.nc = len(self.cams_here)
+        self.max_kp = rig["max_kp"]
+        self.model = mod.Pinhole.make(W, H, rig["f"], rig["c"], rig["distortion"], rig["k"])
+        self.cams = [mod.Camera(ctx, W, H, wl["rays"], wl["jac"], focal=rig["f"][0], max_keypoints=self.max_kp)
+                     for _ in self.cams_here]
+        for cam in self.cams:
+            cam.set_geometry(self.model)
+        c = wl["cfg"]
+        self.det = (c["radius"], 0, c["abs_threshold"], c["max_kpt"])
+        self.slices = c["slices"]
+        self.F = args.frames_per_batch if conf["index"] != 2 else max(1, (args.frames_per_batch * 2) // wl["n_cams"])
+        self.D = args.in_flight
+        self.n_frames = conf["frames"]
+        self.pool = None
+        self.kfs = []
+
+    # ---- the world: keyframes through the product itself (their data also goes to the CPU arm as input) ----
+    def build_world(self):
+        mod, wl = self.mod, self.wl
+        if not wl["kf_frames"]:
+            return build_world(self.syn, wl, {})
+        all_cams = [mod.Camera(self.ctx, wl["W"], wl["H"], wl["rays"], wl["jac"], focal=wl["rig"]["f"][0],
+                               max_keypoints=self.max_kp) for _ in range(wl["n_cams"])]
+        for cam in all_cams:
+            cam.set_geometry(self.model)
+        b = mod.Batch(self.ctx, all_cams)
+        views = {}
+        for k, f in enumerate(wl["kf_frames"]):
+            b.enqueue([wl["images"][c, f] for c in range(wl["n_cams"])], *self.det, [DIRECTION] * wl["n_cams"])
+            b.set_poses(np.stack([mod.slot_pose(np.eye(3), wl["r_all"][f, c]) for c in range(wl["n_cams"])]))
+            kf = mod.Keyframe(self.ctx, wl["n_cams"], self.max_kp)
+            b.retain(list(range(wl["n_cams"])), kf)
+            b.finish()
+            for c in range(wl["n_cams"]):
+                kp, desc = b.slot_frame(c)
+                e_C, valid, _ = b.slot_back_projections(c, len(kp))
+                views[(f, c)] = dict(kp=kp.copy(), desc=desc.copy(), e_C=e_C.copy(), valid=valid.copy())
+            self.kfs.append(kf)
+        b.close()
+        for cam in all_cams:
+            cam.close()
+        build_world(self.syn, wl, views)
+        if self.conf["landmarks"]:
+            self.pool = mod.LandmarkPool(self.ctx, *wl["pool_args"])
+        for k in range(len(wl["kf_frames"])):
+            for c in range(wl["n_cams"]):
+                v = wl["views"][k * wl["n_cams"] + c]
+                self.kfs[k].set_view(c, np.eye(3), v["r_WC"], wl["f_mean"], wl["use0"][k * wl["n_cams"] + c])
+        return wl
+
+    # ---- batches ----
+    def setup(self):
+        mod, torch, wl = self.mod, self.torch, self.wl
+        F, nc = self.F, self.nc
+        # slot order inside a batch: camera-major (slot j * F + i = frame i of this rank's j-th camera), so that
+        # consecutive frames of one camera are adjacent in the pinned host pool and travel in one copy
+        self.batches = [mod.Batch(self.ctx, [self.cams[s // F] for s in range(nc * F)]) for _ in range(self.D)]
+        for b in self.batches:
+            b.configure(*self.det, [DIRECTION] * (nc * F))
+        self.d_img = [torch.from_numpy(wl["images"][c]).cuda() for c in self.cams_here]
+        self.h_img = [torch.from_numpy(wl["images"][c]).pin_memory() for c in self.cams_here]
+        self.img_stride = wl["W"] * wl["H"]
+        self.streams = [torch.cuda.ExternalStream(b.stream()) for b in self.batches]
+        self.pairs = []
+        if self.conf["stereo"] and not self.shard_cameras:
+            self.pairs = [(j * F + i, (j + 1) * F + i) for i in range(F) for j in range(nc - 1)]
+        self.jobs = []
+        if self.conf["motion"]:
+            self.jobs = [(self.kfs[k], self.cams_here[j], j * F + i) for i in range(F) for k in range(len(self.kfs))
+                         for j in range(nc)]
+        self.outs, self.stage_outs = {}, {}
+
+    def frame_of(self, k):
+        """Frame index of this rank's k-th frame: frames round-robin over ranks (cameras when they are sharded)."""
+        g = k if self.shard_cameras else k * self.world + self.rank
+        return g % self.n_frames
+
+    def slot_args(self, k0, device):
+        F, nc = self.F, self.nc
+        k = np.arange(k0, k0 + F)
+        f = (k if self.shard_cameras else k * self.world + self.rank) % self.n_frames
+        imgs = np.empty(nc * F, np.uint64)
+        poses = np.empty((nc * F, 24))
+        for j, c in enumerate(self.cams_here):
+            base = (self.d_img[j] if device else self.h_img[j]).data_ptr()
+            imgs[j * F:(j + 1) * F] = base + f.astype(np.uint64) * np.uint64(self.img_stride)
+            poses[j * F:(j + 1) * F] = self.pose_rows[f, c]
+        return imgs, poses
+
+    def enqueue(self, b, imgs, poses, device):
+        b.enqueue_addrs(imgs, device)
+        if self.conf["landmarks"] or self.pairs or self.jobs:
+            b.set_poses(poses)
+        if self.conf["landmarks"]:
+            b.match_landmarks_enqueue(self.pool, HAMMING, self.slices, self.mod.STAGE_UNINITIALISED)
+        if self.pairs:
+            b.match_stereo_enqueue(self.pairs, HAMMING)
+        if self.jobs:
+            b.match_motion_enqueue(self.jobs, HAMMING, only_unmatched=True)
+
+    def launches_per_batch(self):
+        n = 6                                        # harris_nms, order, select, sub-pixel, border_filter, describe
+        n += 1                                       # back-projections
+        if self.conf["landmarks"]:
+            n += 4 + 3 + 1                           # prepare (4), bin + match + stats, uninitialised
+        n += 1 if self.pairs else 0
+        n += 1 if self.jobs else 0
+        return n
+
+    def read(self, b):
+        r = b.read_all(self.outs.get(id(b)))
+        self.outs[id(b)] = r
+        s = None
+        if self.conf["landmarks"] or self.pairs or self.jobs:
+            s = b.read_stages(self.stage_outs.get(id(b)), len(self.pairs), len(self.jobs), self.conf["landmarks"])
+            self.stage_outs[id(b)] = s
+        return r, s
+
+    def precompute_poses(self):
+        wl = self.wl
+        self.pose_rows = np.empty((self.n_frames, wl["n_cams"], 24))
+        for f in range(self.n_frames):
+            for c in range(wl["n_cams"]):
+                self.pose_rows[f, c] = self.mod.slot_pose(np.eye(3), wl["r_all"][f, c])
+
+    # ---- timed loops ----
+    def run_value(self, n_steps, n_warm, barrier, max_over_ranks):
+        torch, F, D = self.torch, self.F, self.D
+        for j in range(n_warm):
+            self.enqueue(self.batches[j % D], *self.slot_args(j * F, True), True)
+        work = [self.slot_args((n_warm + j) * F, True) for j in range(n_steps)]
+        barrier()
+        start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        cur = torch.cuda.current_stream()
+        start.record(cur)
+        for s in self.streams:
+            s.wait_event(start)
+        t_host = time.perf_counter()
+        for j, (imgs, poses) in enumerate(work):
+            self.enqueue(self.batches[j % D], imgs, poses, True)
+        t_host = time.perf_counter() - t_host
+        for s in self.streams:
+            e = torch.cuda.Event()
+            e.record(s)
+            cur.wait_event(e)
+        end.record(cur)
+        end.synchronize()
+        ms = max_over_ranks(start.elapsed_time(end))
+        barrier()
+        for b in self.batches:
+            b.finish()
+        return ms, t_host / max(n_steps, 1)
+
+    def run_e2e(self, k_begin, k_end, keep=None):
+        F, D = self.F, self.D
+        pending = []
+        for j, k in enumerate(range(k_begin, k_end, F)):
+            b = self.batches[j % D]
+            if len(pending) == D:
+                pb, pk = pending.pop(0)
+                pb.finish()
+                r = self.read(pb)
+                if keep is not None:
+                    keep(pk, r)
+            self.enqueue(b, *self.slot_args(k, False), False)
+            pending.append((b, k))
+        for pb, pk in pending:
+            pb.finish()
+            r = self.read(pb)
+            if keep is not None:
+                keep(pk, r)
+
+    def time_e2e(self, n_steps, n_warm, barrier, max_over_ranks):
+        F = self.F
+        self.run_e2e(0, max(self.D, n_warm) * F)
+        runs = []
+        for _ in range(E2E_REPEATS):
+            barrier()
+            t0 = time.perf_counter()
+            self.run_e2e(n_warm * F, (n_warm + n_steps) * F)
+            self.torch.cuda.synchronize()
+            runs.append(max_over_ranks((time.perf_counter() - t0) * 1e3))
+        return float(np.median(runs)), runs
+
+    def bytes_per_frame(self):
+        """(H2D, D2H) bytes one multiframe moves in the e2e arm (this rank's cameras), from the copies the library makes."""
+        wl, mk = self.wl, self.max_kp
+        pad = lambda n: (n + 255) & ~255
+        h2d = self.nc * (wl["W"] * wl["H"] + 24 * 8 + 600)                      # image + pose + slot table / job records
+        arena = pad(mk * 28) + pad(mk * 48)
+        if self.conf["landmarks"]:
+            arena += pad(mk * 8) + pad(mk * 4) + 1024                           # matchToMapByThread: dist, owner, stats
+            arena += pad(mk * 8) + pad(mk * 4) + pad(mk * 32) + pad(mk) + 512   # uninitialised: dist, owner, hps, flags, ctrs
+        d2h = self.nc * (arena + 32)
+        job = pad(mk * 8) + pad(mk * 4) + pad(mk * 32) + pad(mk) + pad(mk * 8)
+        d2h += (len(self.pairs) + len(self.jobs)) // self.F * job
+        return h2d, d2h
+
+    def kernel_times(self, n_batches):
+        b0 = self.batches[0]
+        b0.kernel_timing(True)
+        acc, cnt = {}, 0
+        for j in range(n_batches):
+            self.enqueue(b0, *self.slot_args(j * self.F, True), True)
+            for name, ms in b0.kernel_times():
+                acc[name] = acc.get(name, 0.0) + ms
+            cnt += 1
+        b0.kernel_timing(False)
+        b0.finish()
+        return {n: v / cnt for n, v in acc.items()}
+
+    def latency(self, n=60):
+        """One multiframe alone through the C ABI with host buffers: wall clock around enqueue / finish / read."""
+        F_save, batches_save, streams_save, pairs_save, jobs_save = self.F, self.batches, self.streams, self.pairs, self.jobs
+        self.F = 1
+        self.setup_single()
+        lat = []
+        for i in range(n + 10):
+            imgs, poses = self.slot_args(i, False)
+            t1 = time.perf_counter()
+            self.enqueue(self.batches[0], imgs, poses, False)
+            self.batches[0].finish()
+            self.read(self.batches[0])
+            lat.append((time.perf_counter() - t1) * 1e3)
+        self.batches[0].close()
+        self.F, self.batches, self.streams, self.pairs, self.jobs = F_save, batches_save, streams_save, pairs_save, jobs_save
+        self.outs, self.stage_outs = {}, {}
+        return float(np.median(lat[10:]))
+
+    def setup_single(self):
+        nc = self.nc
+        b = self.mod.Batch(self.ctx, [self.cams[j] for j in range(nc)])
+        b.configure(*self.det, [DIRECTION] * nc)
+        self.batches = [b]
+        self.pairs = [(j, j + 1) for j in range(nc - 1)] if (self.conf["stereo"] and not self.shard_cameras) else []
+        self.jobs = [(self.kfs[k], self.cams_here[j], j) for k in range(len(self.kfs)) for j in range(nc)] \
+            if self.conf["motion"] else []
+        self.outs, self.stage_outs = {}, {}
+
+    def close(self):
+        for b in self.batches:
+            b.close()
+        for k in self.kfs:
+            k.close()
+        if self.pool:
+            self.pool.close()
+        for c in self.cams:
+            c.close()
+        self.d_img = self.h_img = None
+
+
+def parity_check(gc, cpu, n_frames):
+    """The product's e2e results on the first frames against the CPU pipeline fed with the SAME keypoints and
+    descriptors (so that every later stage sees bit-identical inputs); detect / describe against the reference's own
+    output. Returns (multiframes checked, mismatching items, items)."""
+    wl, F, nc = gc.wl, gc.F, gc.nc
+    got = {}
+
+    bp = {}
+    bp_tol = 1e-12 if wl["rig"]["distortion"] == "equidistant" else 0.0
+
+    def keep(k0, rs):
+        r, s = rs
+        b = [x for x in gc.batches if id(x) in gc.outs and gc.outs[id(x)] is r][0]
+        for i in range(F):
+            got[k0 + i] = (i, {k: v.copy() for k, v in r.items()}, None if s is None else {k: v.copy() for k, v in s.items()})
+            if k0 + i < n_frames:
+                for j in range(nc):
+                    e_C, valid, _ = b.slot_back_projections(j * F + i, int(r["n"][j * F + i]))
+                    bp[(k0 + i, j)] = (e_C.copy(), valid.copy())
+    gc.run_e2e(0, ((n_frames + F - 1) // F) * F, keep)
+    exts = cpu.extractors()
+    bad = items = 0
+
+    def check(ok):
+        nonlocal bad, items
+        items += 1
+        bad += 0 if ok else 1
+    slices = gc.slices
+    for k in range(n_frames):
+        i, r, s = got[k]
+        f = gc.frame_of(k)
+        cur = []
+        for j, c in enumerate(gc.cams_here):
+            slot = j * F + i
+            n = int(r["n"][slot])
+            kp, desc = r["kp"][slot, :n], r["desc"][slot, :n]
+            want = cpu.view_of(f, c, exts[c])
+            check(len(want["kp"]) == n and np.array_equal(want["desc"], desc)
+                  and np.array_equal(want["kp"]["response"], kp["response"])
+                  and float(np.abs(want["kp"]["x"] - kp["x"]).max(initial=0)) <= 1e-4
+                  and float(np.abs(want["kp"]["y"] - kp["y"]).max(initial=0)) <= 1e-4
+                  and float(np.abs(want["kp"]["angle"] - kp["angle"]).max(initial=0)) <= 1e-4)
+            pe, pvalid, _ = cpu.port.back_project(cpu.model, kp)
+            e_C, valid = bp[(k, j)]
+            # radial-tangential: +, -, *, / only -> bit-exact; equidistant: atan / sqrt of glibc vs the device, last ulp
+            check(np.array_equal(valid, pvalid) and ((e_C.tobytes() == pe.tobytes()) if bp_tol == 0.0
+                                                     else float(np.abs(e_C - pe).max(initial=0)) <= bp_tol))
+            cur.append(dict(kp=kp, desc=desc, e_C=e_C, valid=valid))
+        st = cpu.stages(f, cur, False) if gc.cams_here == list(range(wl["n_cams"])) else None
+        if st is None:
+            continue
+        for j in range(nc):
+            slot = j * F + i
+            n = int(r["n"][slot])
+            if gc.conf["landmarks"]:
+                lm = st["lm"][j]
+                check(np.array_equal(r["dist"][slot, :n], lm["a14"][0]) and np.array_equal(r["owner"][slot, :n], lm["a14"][1]))
+                ctrs = r["ctrs"].reshape(-1)[slot * slices:(slot + 1) * slices]
+                errs = r["errs"].reshape(-1)[slot * slices:(slot + 1) * slices]
+                # (equidistant cameras: the projections go through atan, so the summed reprojection errors agree to 1e-9)
+                check(np.array_equal(ctrs, lm["a14"][2]) and
+                      (np.array_equal(errs, lm["a14"][3], equal_nan=True) if bp_tol == 0.0
+                       else np.allclose(errs, lm["a14"][3], rtol=1e-9, atol=0.0, equal_nan=True)))
+                uc = s["u_ctrs"].reshape(-1)[slot * slices:(slot + 1) * slices]
+                check(np.array_equal(s["u_dist"][slot, :n], lm["a15"][0]) and np.array_equal(s["u_owner"][slot, :n], lm["a15"][1])
+                      and np.array_equal(s["u_written"][slot, :n], lm["a15"][3]) and np.array_equal(uc, lm["a15"][4])
+                      and np.array_equal(s["u_hps"][slot, :n, :3], lm["a15"][2][:, :3]))
+        for p, (s0, s1) in enumerate(gc.pairs):
+            if s0 % F != i:
+                continue
+            n0 = int(r["n"][s0])
+            w = st["stereo"][s0 // F]
+            check(np.array_equal(s["s_dist"][p, :n0], w[0]) and np.array_equal(s["s_k1"][p, :n0], w[1])
+                  and np.array_equal(s["s_hp"][p, :n0], w[2]) and np.array_equal(s["s_init"][p, :n0], w[3]))
+        nk = len(gc.kfs)
+        for q, (kf, c, slot) in enumerate(gc.jobs):
+            if slot % F != i:
+                continue
+            k_idx = (q // nc) % nk
+            w = st["motion"][k_idx * nc + slot // F]
+            n0 = int(s["m_n0"][q])
+            check(n0 == len(w[0]) and np.array_equal(s["m_dist"][q, :n0], w[0]) and np.array_equal(s["m_k1"][q, :n0], w[1])
+                  and np.array_equal(s["m_hp"][q, :n0], w[2]) and np.array_equal(s["m_init"][q, :n0], w[3])
+                  and float(np.abs(s["m_quality"][q, :n0] - w[4]).max(initial=0)) <= 1e-12)
+    for e in exts:
+        e.close()
+    return n_frames, bad, items
+
+
+def cpu_baseline(cpu, n_frames_pool, frame_of, budget_s):
+    """The CPU code with the reference's own threading on a bounded sample of the same workload."""
+    exts = cpu.extractors()
+    for f in range(2):
+        cpu.frame_like_reference(exts, frame_of(f))
+    n, t_cpu = 0, 0.0
+    while n < n_frames_pool and t_cpu < budget_s:
+        t0 = time.perf_counter()
+        cpu.frame_like_reference(exts, frame_of(n))
+        t_cpu += time.perf_counter() - t0
+        n += 1
+    for e in exts:
+        e.close()
+    wl = cpu.wl
+    return {"value": round(n / t_cpu, 2), "unit": "frames/s", "cores": max(wl["n_cams"], wl["cfg"]["slices"]),
+            "kind": cpu.kind,
+            "sample": "%d multiframes of the same sequence; threading as the reference: %d threads (one per camera) for "
+                      "detect+describe, %d matching slices per camera for the map matchers, the 2D-2D matchers on one "
+                      "thread; host has %d cores" % (n, wl["n_cams"], wl["cfg"]["slices"], os.cpu_count())}
+
+
+def run_frame_config(args, name, mod, syn, torch, dist, ctx, rank, world, headline, sampler_box):
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    wl = build_images(syn, name, args.sparse)
+    shard_cameras = CONFIGS[name]["index"] == 2 and world > 1
+    gc = GpuConfig(args, mod, syn, torch, ctx, wl, rank, world, shard_cameras)
+    gc.build_world()
+    gc.precompute_poses()
+    gc.setup()
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    n_steps = max(args.steps, 1) if headline else max(min(args.steps, 60), 1)
+    n_warm = max(args.warmup, 3)
+    if headline and rank == 0:
+        # the clock sampler starts before the warm-up so that nvidia-smi's start-up (which takes driver locks) is over
+        # when the timed region begins; it keeps sampling every 100 ms until after the e2e arm
+        sampler_box.append(ClockSampler(local))
+    F = gc.F
+    gather = None
+    if shard_cameras and gc.conf["stereo"]:
+        sh = __import__("importlib").import_module("okvis2x_b200.sharding")
+        gather = sh.CameraGather(mod, torch, dist, ctx, gc, HAMMING)
+    dev_ms, t_host = gc.run_value(n_steps, n_warm, barrier, max_over_ranks)
+    gather_ms = gather.time_steps(min(n_steps, 20), barrier, max_over_ranks) if gather else None
+    e2e_ms, e2e_runs = gc.time_e2e(n_steps, n_warm, barrier, max_over_ranks)
+    barrier()
+    clocks = sampler_box.pop().stop() if (headline and rank == 0 and sampler_box) else None
+    lat = gc.latency() if (rank == 0 or world == 1) else None
+    kms = gc.kernel_times(min(n_steps, 20))
+    frames_per_step = F * (1 if shard_cameras else world)
+    total = n_steps * frames_per_step
+    h2d, d2h = gc.bytes_per_frame()
+    r0, _ = gc.read(gc.batches[0]) if False else (None, None)
+    gc.run_e2e(0, F)   # one batch so that the arena of batch 0 holds a frame to take K from
+    r0 = gc.outs[id(gc.batches[0])]
+    K = float(np.mean(r0["n"]))
+    L = len(wl["pool_args"][1]) if gc.conf["landmarks"] else 0
+    M = 3.0 * L
+    peak, peak_src = peaks()
+    imgs_per_launch = gc.nc * F
+    per_kernel = {}
+    for kname, ms in kms.items():
+        alg = stage_bytes(kname, wl["W"], wl["H"], K, M, L) * imgs_per_launch
+        per_kernel[kname] = {"ms": round(ms, 5), "algorithmic_bytes": int(alg), "gbs": round(alg / (ms * 1e-3) / 1e9, 2),
+                             "frac": round(alg / (ms * 1e-3) / 1e9 / peak, 6)}
+    dom = max(kms, key=kms.get)
+    roofline = {"bound": "hbm", "kernel": dom, "achieved": per_kernel[dom]["gbs"], "peak": peak, "unit": "GB/s",
+                "frac": per_kernel[dom]["frac"], "traffic": ncu_traffic(dom, imgs_per_launch), "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": per_kernel[dom]["algorithmic_bytes"], "images_per_launch": imgs_per_launch,
+                "dominant": "the longest kernel of the chain (every kernel is listed in `kernels`)", "kernels": per_kernel,
+                "note": "per-launch times of one batch running alone; in the timed loop %d batches overlap" % gc.D}
+    out = {
+        "workload": gc.conf["what"], "value": round(total / (dev_ms * 1e-3), 2), "unit": "frames/s",
+        "ms_per_step": round(dev_ms / n_steps, 5), "steps": n_steps,
+        "step": "one batch = %d multiframes (%d images on this rank) through the whole launch chain" % (F, imgs_per_launch),
+        "frames_in_pool": gc.n_frames, "keypoints_per_image": round(K, 1), "landmarks": L,
+        "sharding": ("cameras over ranks (camera c -> rank c mod N), keypoints + descriptors all-gathered for matchStereo"
+                     if shard_cameras else "frames round-robin over ranks"),
+        "host_enqueue_us_per_batch": round(t_host * 1e6, 1),
+        "e2e": {"value": round(total / (e2e_ms * 1e-3), 2), "unit": "frames/s", "ms_per_step": round(e2e_ms / n_steps, 5),
+                "h2d_bytes_per_step": h2d * F, "d2h_bytes_per_step": d2h * F,
+                "timed": "median of %d runs of K steps (ms: %s)" % (E2E_REPEATS, ", ".join("%.1f" % v for v in e2e_runs)),
+                "pcie_gbs_per_gpu": round(n_steps * F * (h2d + d2h) / (e2e_ms * 1e-3) / 1e9, 1)},
+        "gpu_launches": gc.launches_per_batch() * n_steps,
+        "roofline": roofline,
+    }
+    if gather_ms is not None:
+        out["camera_gather"] = gather_ms
+    if lat is not None:
+        out["single_multiframe_latency_ms"] = round(lat, 4)
+    if clocks is not None:
+        out["clocks"] = clocks
+    st = dict(gc=gc, wl=wl, F=F)
+    return out, st
 
 
 def ncu_traffic(kernel, images_per_launch):
     """DRAM bytes per launch of `kernel` from the newest committed ncu capture (profiles/*/traffic.json), or None when
     there is none for this batch size. Never measured under this run: it is the committed profile's number."""
     import glob
-    key = {"border_filter+describe": "describe_kernel", "match_to_map": "match_to_map_binned"}.get(kernel, kernel)
-    for path in sorted(glob.glob(os.path.join(ROOT, "profiles", "*", "traffic.json")), reverse=True):
+    key = {"border_filter+describe": "describe_kernel", "match_to_map": "match_to_map_binned",
+           "select_keypoints": "select_keypoints_wave"}.get(kernel, kernel)
+    for path in sorted(glob.glob(os.path.join(ROOT, "profiles", "r02*", "traffic.json")), reverse=True):
         try:
             d = json.load(open(path))
             if d.get("images_per_launch") != images_per_launch:
@@ -272,13 +770,59 @@ def ncu_traffic(kernel, images_per_launch):
     return None
 
 
-def stage_bytes(kernel, W, H, K, M):
-    """ALGORITHMIC bytes of the stage a kernel belongs to, per image (SURVEY.md 8(d), DESIGN.md 'Roofline')."""
-    if kernel in ("harris_nms", "order_candidates", "select_keypoints"):
-        return W * H + K * 28                       # detect: image in, keypoints out
-    if kernel == "border_filter+describe":
-        return W * H + K * (28 + 4 * 12 + 24) + K * (48 + 28)   # image + kp + 4 rays + 1 Jacobian in; desc + kp out
-    return (K + M) * 48 + K * 16                    # match: descriptors in, (dist, id) out
+def run_sweep(torch, dist, mod, ctx, syn, rank, world, variant="iid", iters=5):
+    """BASELINE config 5 (the metric's second half): 10k x 1M Hamming sweep, map rows sharded over ranks, per-shard
+    bests min-reduced over NCCL. L2 is flushed between iterations (the 48 MB map would fit in it)."""
+    nq, nm = 10000, 1000000
+    import importlib
+    sh = importlib.import_module("okvis2x_b200.sharding")
+    q, m, note = sh.sweep_inputs(syn, variant, nq, nm, mod, ctx)
+    lo, hi = sh.map_row_shard(rank, world, nm)
+    qs, ms = ctx.descriptor_set(q), ctx.descriptor_set(m[lo:hi])
+    best = torch.empty(nq, dtype=torch.int64, device="cuda")
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    # a non-default stream: handle 0 would select the library's own stream, which torch events do not see
+    cur = torch.cuda.Stream()
+    torch.cuda.set_stream(cur)
+    times, ktimes = [], []
+    res = None
+    for it in range(iters + 2):
+        flush.fill_(it & 0xff)
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+        e0.record(cur)
+        ctx.match_sets_ordered(qs, ms, 60, lo, best.data_ptr(), cur.cuda_stream)
+        e1.record(cur)
+        res = sh.merge_best(best, world, dist)   # one NCCL all-reduce(min) on the keys (identity at world == 1)
+        e2.record(cur)
+        e2.synchronize()
+        if it >= 2:
+            times.append(e0.elapsed_time(e2))
+            ktimes.append(e0.elapsed_time(e1))
+    torch.cuda.set_stream(torch.cuda.default_stream())
+    t = float(np.median(times))
+    if world > 1:
+        tt = torch.tensor([t], dtype=torch.float64, device="cuda")
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        t = float(tt.item())
+    peak, _ = peaks()
+    pairs = float(nq) * nm
+    alg = (nq + nm) * 48 + nq * 8
+    matched = int((res != sh.ORDERED_NO_MATCH).sum().item())
+    # fraction of the pairs whose 6-word lower bound is below the threshold, i.e. that take the exact 12-word path
+    # (a property of the input, computed on a sample on the host)
+    exact = sh.exact_path_fraction(q, m, 60)
+    for s in (qs, ms):
+        s.close()
+    del flush
+    return {"workload": "configs[4]: 10k x 1M descriptors (48 B), threshold 60, map rows sharded over ranks",
+            "input": note, "gpairs_per_s": round(pairs / (t * 1e-3) / 1e9, 2), "ms": round(t, 4),
+            "kernel_ms_rank0": round(float(np.median(ktimes)), 4), "matched": matched,
+            "pairs_on_exact_path_frac": exact,
+            "hbm_algorithmic_gbs": round(alg / (t * 1e-3) / 1e9, 2), "hbm_frac": round(alg / (t * 1e-3) / 1e9 / peak, 5),
+            "l2": "flushed between iterations (256 MB write)", "scaling": "strong"}
 
 
 def run_b200(args, rank, world):
@@ -298,346 +842,112 @@ def run_b200(args, rank, world):
     mod.lib()
     import importlib
     syn = importlib.import_module("okvis2x_b200.synthetic")
-    wl = build_workload(syn)
-    cfg, W, H = wl["cfg"], wl["W"], wl["H"]
-    det = (cfg["radius"], 0, cfg["abs_threshold"], cfg["max_kpt"])
-    slices = cfg["slices"]
-    F, D = args.frames_per_batch, args.in_flight
     ctx = mod.Context(local)
-    cams = [mod.Camera(ctx, W, H, c["rays"], c["jac"], focal=c["focal"], max_keypoints=MAX_KP) for c in wl["cams"]]
-    frame0 = [cams[c].detect_describe(wl["images"][c][0], *det, direction=DIRECTION) for c in range(2)]
-    win_h = make_windows(syn, wl, frame0)
-    windows = [mod.MapWindow(ctx, rows, owner, proj.shape[1]) for rows, owner, proj in win_h]
-    gates = [(3.0 + c["fmean"] * 0.06) ** 2 for c in wl["cams"]]
-    # device-resident pools (value arm) and pinned host pools (e2e arm)
-    d_img = [torch.from_numpy(wl["images"][c]).cuda() for c in range(2)]
-    d_proj = [torch.from_numpy(win_h[c][2]).cuda() for c in range(2)]
-    h_img = [torch.from_numpy(wl["images"][c]).pin_memory() for c in range(2)]
-    h_proj = [torch.from_numpy(win_h[c][2]).pin_memory() for c in range(2)]
-    img_stride = W * H
-    proj_strides = [win_h[c][2].shape[1] * 16 for c in range(2)]
-    sh = importlib.import_module("okvis2x_b200.sharding")
-    frame_of = lambda k: sh.frame_of(k, rank, world, N_FRAMES)
-
-    def make_batches(nframes):
-        return [mod.Batch(ctx, [cams[s // nframes] for s in range(2 * nframes)]) for _ in range(D)]
-
-    batches = make_batches(F)
-    rem, rem_batches = 0, None          # a step is a whole batch: no partial batches
-    n_steps, n_warm = max(args.steps, 1), max(args.warmup, 3)   # timing rule: at least 3 warm-up steps
-    # slot order inside a batch: camera-major (slot c * nframes + i = frame i, camera c), so that consecutive frames of
-    # one camera are adjacent in the pinned host pool and travel in one copy
-    def slot_args(k0, nframes, device):
-        """Address arrays (np.uint64) of the batch that covers steps k0 .. k0+nframes-1."""
-        imgs = np.empty(2 * nframes, np.uint64)
-        proj = np.empty(2 * nframes, np.uint64)
-        for c in range(2):
-            ib = (d_img[c] if device else h_img[c]).data_ptr()
-            pb = (d_proj[c] if device else h_proj[c]).data_ptr()
-            for i in range(nframes):
-                f = frame_of(k0 + i)
-                imgs[c * nframes + i] = ib + f * img_stride
-                proj[c * nframes + i] = pb + f * proj_strides[c]
-        return imgs, proj
-
-    configured = set()
-
-    def enqueue(batch, nframes, imgs, proj, device):
-        if id(batch) not in configured:
-            batch.configure(*det, [DIRECTION] * (2 * nframes), windows=[windows[s // nframes] for s in range(2 * nframes)],
-                            gates=[gates[s // nframes] for s in range(2 * nframes)], hamming_threshold=60.0,
-                            num_slices=slices)
-            configured.add(id(batch))
-        batch.enqueue_addrs(imgs, device, proj, device)
-
-    def plan(k_begin, k_end, device):
-        """[(batch handle list, nframes, imgs, proj)] covering steps [k_begin, k_end)."""
-        out, k = [], k_begin
-        while k < k_end:
-            n = F if k_end - k >= F else k_end - k
-            hs = batches if n == F else rem_batches
-            if n != F and n != rem:
-                raise SystemExit("internal: partial batch of %d frames" % n)
-            out.append((hs, n) + slot_args(k, n, device))
-            k += n
-        return out
-
-    def barrier():
-        torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    def max_over_ranks(x):
-        if world == 1:
-            return x
-        t = torch.tensor([x], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
-
-    all_streams = [torch.cuda.ExternalStream(b.stream()) for b in batches + (rem_batches or [])]
-
-    # ---- value: inputs resident in HBM, results left on the device, CUDA events around K steps ----
-    # the clock sampler starts before the warm-up so that nvidia-smi's start-up (which takes driver locks) is over
-    # when the timed region begins; it keeps sampling every 100 ms until after the e2e arm
-    sampler = ClockSampler(local) if rank == 0 else None
-    warm = n_warm * F
-    frames = n_steps * F
-    for j, (hs, n, imgs, proj) in enumerate(plan(0, warm, True)):
-        enqueue(hs[j % D], n, imgs, proj, True)
-    work = plan(warm, warm + frames, True)
-    barrier()
-    start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    cur = torch.cuda.current_stream()
-    start.record(cur)
-    for s in all_streams:
-        s.wait_event(start)
-    t_host = time.perf_counter()
-    for j, (hs, n, imgs, proj) in enumerate(work):
-        enqueue(hs[j % D], n, imgs, proj, True)
-    t_host = time.perf_counter() - t_host
-    for s in all_streams:
-        e = torch.cuda.Event()
-        e.record(s)
-        cur.wait_event(e)
-    end.record(cur)
-    end.synchronize()
-    dev_ms = max_over_ranks(start.elapsed_time(end))
-    barrier()
-
-    # ---- e2e: pinned host images + host projections in, keypoints/descriptors/matches out, every step ----
-    outs = {}
-
-    def run_e2e(k_begin, k_end, keep=None):
-        pending = []   # (handle, nframes, first step)
-        k = k_begin
-        for j, (hs, n, imgs, proj) in enumerate(plan(k_begin, k_end, False)):
-            h = hs[j % D]
-            if len(pending) == D:
-                ph, pn, pk = pending.pop(0)
-                ph.finish()
-                r = ph.read_all(outs.setdefault(id(ph), None))
-                outs[id(ph)] = r
-                if keep is not None:
-                    keep(pk, pn, r)
-            enqueue(h, n, imgs, proj, False)
-            pending.append((h, n, k))
-            k += n
-        for ph, pn, pk in pending:
-            ph.finish()
-            r = ph.read_all(outs.setdefault(id(ph), None))
-            outs[id(ph)] = r
-            if keep is not None:
-                keep(pk, pn, r)
-
-    run_e2e(0, max(F * D, warm))
-    # the K-step e2e region is timed E2E_REPEATS times and the median is reported: it moves ~45 GB/s over PCIe and a
-    # single host hiccup (page faults of the pinned pools, the clock sampler) otherwise decides the number
-    e2e_runs = []
-    for _ in range(E2E_REPEATS):
-        barrier()
-        t0 = time.perf_counter()
-        run_e2e(warm, warm + frames)
-        torch.cuda.synchronize()
-        e2e_runs.append(max_over_ranks((time.perf_counter() - t0) * 1e3))
-    e2e_ms = float(np.median(e2e_runs))
-    barrier()
-    clocks = sampler.stop() if sampler else None
-    # ---- latency of ONE stereo frame through the C ABI with host buffers (what a SLAM front end waits for) ----
-    lat_b = mod.Batch(ctx, [cams[0], cams[1]])
-    lat, lat_out = [], None
-    for i in range(70):
-        imgs, proj = slot_args(warm + i, 1, False)
-        t1 = time.perf_counter()
-        enqueue(lat_b, 1, imgs, proj, False)
-        lat_b.finish()
-        lat_out = lat_b.read_all(lat_out)
-        lat.append((time.perf_counter() - t1) * 1e3)
-    latency_ms = float(np.median(lat[10:]))
-    L = [win_h[c][2].shape[1] for c in range(2)]
-    h2d = sum(W * H + L[c] * 16 for c in range(2)) + 2 * 256          # images + projections + slot table share
-    b0 = batches[0]
-    d2h = 2 * (32 + MAX_KP * 28 + MAX_KP * 48 + pad256(MAX_KP * 8) + pad256(MAX_KP * 4) + 1024)
-
-    # ---- per-kernel device times (separate pass; one batch at a time, events around every launch) ----
-    b0.kernel_timing(True)
-    acc, cnt = {}, 0
-    tw = plan(warm, warm + F * min(n_steps, 25), True)
-    for hs, n, imgs, proj in tw:
-        enqueue(b0, n, imgs, proj, True)
-        for name, ms in b0.kernel_times():
-            acc[name] = acc.get(name, 0.0) + ms
-        cnt += 1
-    b0.kernel_timing(False)
-    kernel_ms = {n: v / cnt for n, v in acc.items()}
-    b0.finish()
-    r = b0.read_all()
-    K = float(np.mean(r["n"]))
-    M = float(np.mean([windows[c].nm for c in range(2)]))
-    # dominant kernel = the longest of the GPU-wide ones (Harris, describe, map match): they share the SMs and bound the
-    # step; the one-CTA-per-image kernels (order, select, bin, stats) run beside other batches' GPU-wide kernels
-    wide = [n for n in kernel_ms if n in ("harris_nms", "border_filter+describe", "match_to_map")] or list(kernel_ms)
-    dom = max(wide, key=kernel_ms.get)
-    peak, peak_src = peaks()
-    alg = stage_bytes(dom, W, H, K, M) * 2 * F
-    achieved = alg / (kernel_ms[dom] * 1e-3) / 1e9
-    roofline = {"bound": "hbm", "kernel": dom, "achieved": round(achieved, 3), "peak": peak, "unit": "GB/s",
-                "frac": round(achieved / peak, 6), "traffic": ncu_traffic(dom, 2 * F), "peak_source": peak_src,
-                "algorithmic_bytes_per_launch": alg, "images_per_launch": 2 * F,
-                "kernel_ms": {n: round(v, 5) for n, v in kernel_ms.items()},
-                "note": "per-launch times of one batch running alone; in the timed loop %d batches overlap" % D}
-    n_batches = len(work)
+    only = [x for x in args.only.split(",") if x]
+    names = [n for n in CONFIGS if (not only or n in only or n == HEADLINE)]
+    names.sort(key=lambda n: (n != HEADLINE, CONFIGS[n]["index"]))   # the headline first (clock sampler, fresh box)
+    results, sampler_box = {}, []
+    cpu_done = {}
+    for name in names:
+        headline = name == HEADLINE
+        out, st = run_frame_config(args, name, mod, syn, torch, dist, ctx, rank, world, headline, sampler_box)
+        if rank == 0 and world == 1 and not args.no_cpu_baseline:
+            cpu = CpuFrontend(mod, syn, st["wl"])
+            n_check = 3 if CONFIGS[name]["index"] in (2, 3) else 6
+            checked, bad, items = parity_check(st["gc"], cpu, n_check)
+            out["parity"] = {"multiframes_checked": checked, "items": items, "mismatching": bad,
+                             "what": "keypoints (1e-4) / descriptors vs the compiled reference; back-projections, map "
+                                     "matches incl. ctrs / reprErrors, uninitialised matches, matchStereo, "
+                                     "matchMotionStereo bit-exact vs the CPU restatement on the same keypoints"}
+            out["cpu_baseline"] = cpu_baseline(cpu, st["gc"].n_frames, st["gc"].frame_of, 12.0 if headline else 6.0)
+            cpu_done[name] = True
+        st["gc"].close()
+        del st
+        torch.cuda.empty_cache()
+        results[name] = out
+    head = results[HEADLINE]
     out = {
-        "metric": "frontend_frames_per_s", "value": round(world * frames / (dev_ms * 1e-3), 2), "unit": "frames/s",
-        "n_gpus": world, "steps": n_steps, "warmup": n_warm, "ms_per_step": round(dev_ms / n_steps, 5),
+        "metric": "frontend_frames_per_s", "value": head["value"], "unit": "frames/s", "n_gpus": world,
+        "steps": head["steps"], "warmup": max(args.warmup, 3), "ms_per_step": head["ms_per_step"],
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8/int32 (f32+f64 gates)",
         "data": "synthetic",
-        "config": {"workload": "configs[1]: EuRoC 752x480 stereo sequence, per frame 2x(detect+describe)+2x matchToMap "
-                               "vs 2000-landmark window",
-                   "frames_in_pool": N_FRAMES, "keypoints_per_image": K, "map_rows_per_camera": M,
-                   "step": "one batch = %d stereo frames (%d images) through the whole launch chain" % (F, 2 * F),
-                   "frames_per_batch": F, "batches_in_flight": D,
-                   "host_enqueue_us_per_batch": round(t_host / max(len(work), 1) * 1e6, 1),
-                   "l2": "inputs larger than L2 (144 MB image pool cycled)", "sharding": "frames round-robin over ranks"},
-        "e2e": {"value": round(world * frames / (e2e_ms * 1e-3), 2), "unit": "frames/s",
-                "h2d_bytes_per_step": h2d * F, "d2h_bytes_per_step": d2h * F, "ms_per_step": round(e2e_ms / n_steps, 5),
-                "timed": "median of %d runs of K steps (ms: %s)" % (E2E_REPEATS, ", ".join("%.1f" % v for v in e2e_runs)),
-                "pcie_gbs": round(world * frames * (h2d + d2h) / (e2e_ms * 1e-3) / 1e9 / world, 1)},
-        "gpu_launches": 8 * n_batches,   # harris_nms, order, select, border_filter, describe, bin_projections, match, stats
-        "roofline": roofline,
-        "clocks": clocks,
+        "config": {"workload": head["workload"], "frames_in_pool": head["frames_in_pool"],
+                   "keypoints_per_image": head["keypoints_per_image"], "landmarks": head["landmarks"],
+                   "step": head["step"], "frames_per_batch": args.frames_per_batch, "batches_in_flight": args.in_flight,
+                   "host_enqueue_us_per_batch": head["host_enqueue_us_per_batch"],
+                   "scene": "sparse (400 rectangles)" if args.sparse else "dense (corner-rich texture: the keypoint budget binds)",
+                   "l2": "inputs larger than L2 (144 MB image pool cycled)", "sharding": head["sharding"]},
+        "e2e": head["e2e"],
+        "gpu_launches": head["gpu_launches"],
+        "roofline": head["roofline"],
+        "clocks": head.get("clocks"),
     }
-    out["single_frame_latency_ms"] = round(latency_ms, 4)
-    return out, dict(mod=mod, ctx=ctx, cams=cams, wl=wl, win_h=win_h, run_e2e=run_e2e, frame_of=frame_of, syn=syn,
-                     torch=torch, dist=dist, local=local, F=F)
-
-
-def run_sweep(st, rank, world, iters=5):
-    """BASELINE config 5 (the metric's second half): 10k x 1M Hamming sweep, map rows sharded over ranks, per-shard
-    bests gathered over NCCL and min-reduced. L2 is flushed between iterations (the 48 MB map would fit in it)."""
-    torch, dist, mod, ctx, syn = st["torch"], st["dist"], st["mod"], st["ctx"], st["syn"]
-    nq, nm = 10000, 1000000
-    q, m = syn.sweep_inputs(nq, nm, seed=5)
-    import importlib
-    sh = importlib.import_module("okvis2x_b200.sharding")
-    lo, hi = sh.map_row_shard(rank, world, nm)
-    qs, ms = ctx.descriptor_set(q), ctx.descriptor_set(m[lo:hi])
-    best = torch.empty(nq, dtype=torch.int64, device="cuda")
-    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
-    # a non-default stream: handle 0 would select the library's own stream, which torch events do not see
-    cur = torch.cuda.Stream()
-    torch.cuda.set_stream(cur)
-    times, ktimes = [], []
-    for it in range(iters + 2):
-        flush.fill_(it & 0xff)
-        torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier()
-        e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
-        e0.record(cur)
-        ctx.match_sets(qs, ms, 60, index_offset=lo, best_device=best.data_ptr(), stream=cur.cuda_stream,
-                       want_host=False)
-        e1.record(cur)
-        res = sh.merge_best(best, world, dist)   # NCCL all-gather + min (identity at world == 1)
-        e2.record(cur)
-        e2.synchronize()
-        if it >= 2:
-            times.append(e0.elapsed_time(e2))
-            ktimes.append(e0.elapsed_time(e1))
-    t = float(np.median(times))
+    if "cpu_baseline" in head:
+        out["cpu_baseline"] = dict(head["cpu_baseline"], parity=head.get("parity"))
+    extra = {"configs": {}}
+    for name, r in results.items():
+        r = dict(r)
+        r.pop("clocks", None)
+        extra["configs"]["configs[%d] %s" % (CONFIGS[name]["index"], name)] = r
+    if not args.no_sweep:
+        sweeps = {}
+        for variant in ("iid", "natural", "adversarial"):
+            sweeps[variant] = run_sweep(torch, dist, mod, ctx, syn, rank, world, variant)
+        extra["configs"]["configs[4] matcher_sweep"] = sweeps["iid"]
+        extra["matcher_sweep_inputs"] = sweeps
+    extra["single_frame_latency"] = {
+        "ms": head.get("single_multiframe_latency_ms"),
+        "what": "one stereo frame alone (batch of 2 images, nothing else in flight): host images in, keypoints + "
+                "descriptors + matches out, wall clock around enqueue/finish/read, median of 60"}
+    if "cpu_baseline" in head and head["cpu_baseline"].get("value"):
+        extra["single_frame_latency"]["reference_ms"] = round(1e3 / head["cpu_baseline"]["value"], 3)
+    out["extra"] = extra
+    ctx.close()
     if world > 1:
-        tt = torch.tensor([t], dtype=torch.float64, device="cuda")
-        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        t = float(tt.item())
-    peak, _ = peaks()
-    pairs = float(nq) * nm
-    alg = (nq + nm) * 48 + nq * 8
-    matched = int((res != sh.NO_MATCH_I64).sum().item())
-    for s in (qs, ms):
-        s.close()
-    return {"workload": "configs[4]: 10k x 1M descriptors (48 B), threshold 60, map rows sharded over ranks",
-            "gpairs_per_s": round(pairs / (t * 1e-3) / 1e9, 2), "ms": round(t, 4),
-            "kernel_ms_rank0": round(float(np.median(ktimes)), 4), "matched": matched,
-            "hbm_algorithmic_gbs": round(alg / (t * 1e-3) / 1e9, 2), "hbm_frac": round(alg / (t * 1e-3) / 1e9 / peak, 5),
-            "popc32_equivalent_per_s": round(pairs * 12 / (t * 1e-3), 0), "l2": "flushed between iterations (256 MB write)",
-            "scaling": "strong"}
-
-
-def run_cpu_baseline(st, budget_s=12.0):
-    """The reference's CPU code with the reference's own threading on a bounded sample of the same workload, and a
-    parity check of the B200 results (through the batched e2e path) on the first frames of that sample."""
-    wl, F = st["wl"], st["F"]
-    cpu = CpuFrontend(wl)
-    cpu.set_windows(st["win_h"])
-    exts = cpu.extractors()
-    for f in range(2):
-        cpu.frame_like_reference(exts, f)
-    n_check = 3 * F
-    gpu = {}
-
-    def keep(k0, nframes, r):
-        for i in range(nframes):
-            for c in range(2):
-                s = c * nframes + i
-                n = int(r["n"][s])
-                gpu[(k0 + i, c)] = (r["kp"][s, :n].copy(), r["desc"][s, :n].copy(), r["dist"][s, :n].copy(),
-                                    r["owner"][s, :n].copy())
-    st["run_e2e"](0, n_check, keep)
-    n, mism, t_cpu = 0, 0, 0.0
-    while n < N_FRAMES and t_cpu < budget_s:
-        f = st["frame_of"](n)
-        t0 = time.perf_counter()
-        res = cpu.frame_like_reference(exts, f)
-        t_cpu += time.perf_counter() - t0
-        if n < n_check:  # parity of the product on the same frames (the oracle is only the checker here)
-            for c in range(2):
-                kp, desc, dist, ids, ctrs, errs = res[c]
-                gk, gd, gbd, gbo = gpu[(n, c)]
-                ok = (len(gk) == len(kp) and np.array_equal(gd, desc) and np.array_equal(gk["response"], kp["response"])
-                      and float(np.abs(gk["x"] - kp["x"]).max()) <= 1e-4 and float(np.abs(gk["y"] - kp["y"]).max()) <= 1e-4
-                      and float(np.abs(gk["angle"] - kp["angle"]).max()) <= 1e-4
-                      and np.array_equal(gbd, dist) and np.array_equal(gbo, ids))
-                mism += 0 if ok else 1
-        n += 1
-    for e in exts:
-        e.close()
-    return {"value": round(n / t_cpu, 2), "unit": "frames/s", "cores": 4, "kind": cpu.kind,
-            "sample": "%d frames of the same sequence; threading as the reference: 2 threads (one per camera) for "
-                      "detect+describe, then 4 matching slices per camera; host has %d cores" % (n, os.cpu_count()),
-            "parity": {"frames_checked": min(n, n_check), "camera_frames_mismatching": mism}}
+        dist.barrier()
+        dist.destroy_process_group()
+    return out
 
 
 def run_reference(args, rank, world):
-    """--impl reference: the reference's CPU implementation on all host cores (rank 0 only)."""
+    """--impl reference: the reference's CPU implementation on all host cores (rank 0 only), headline workload."""
     if rank != 0:
         return None
     import __graft_entry__ as g
-    g.load()
+    mod = g.load()
     import importlib
     syn = importlib.import_module("okvis2x_b200.synthetic")
-    wl = build_workload(syn)
-    cpu = CpuFrontend(wl)
+    wl = build_images(syn, HEADLINE, args.sparse)
+    cpu = CpuFrontend(mod, syn, wl)
     exts = cpu.extractors()
-    frame0 = [cpu.detect_describe(exts[c], c, 0) for c in range(2)]
+    build_world(syn, wl, cpu.keyframe_views(exts))
     for e in exts:
         e.close()
-    cpu.set_windows(make_windows(syn, wl, frame0))
     cores = os.cpu_count() or 1
     sample = max(cores * 2, 32)  # frames per step: a bounded sample of the sequence
-    for _ in range(min(args.warmup, 2)):
+    n_frames = CONFIGS[HEADLINE]["frames"]
+    warm = max(args.warmup, 0)
+    steps = max(args.steps, 1)
+    # every step is one bounded sample; the whole run is kept within a few minutes by shrinking the sample, never the
+    # step count: the first warm-up step calibrates the rate
+    t0 = time.perf_counter()
+    cpu.throughput_all_cores(range(sample), cores)
+    rate = sample / (time.perf_counter() - t0)
+    budget_s = 150.0
+    sample = int(max(cores, min(sample, rate * budget_s / (steps + warm))))
+    for _ in range(max(warm - 1, 0)):
         cpu.throughput_all_cores(range(sample), cores)
-    steps = min(args.steps, 10)
     t0 = time.perf_counter()
     for s in range(steps):
-        cpu.throughput_all_cores([(s * sample + i) % N_FRAMES for i in range(sample)], cores)
+        cpu.throughput_all_cores([(s * sample + i) % n_frames for i in range(sample)], cores)
     dt = time.perf_counter() - t0
     fps = steps * sample / dt
     return {"impl": "reference", "metric": "frontend_frames_per_s", "value": round(fps, 2), "unit": "frames/s",
-            "n_gpus": world, "steps": steps, "warmup": min(args.warmup, 2), "ms_per_step": round(dt / steps * 1e3, 3),
+            "n_gpus": world, "steps": steps, "warmup": warm, "ms_per_step": round(dt / steps * 1e3, 3),
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8/int32 (f32+f64 gates)",
             "data": "synthetic",
-            "config": {"workload": "configs[1]: EuRoC 752x480 stereo sequence, per frame 2x(detect+describe)+2x "
-                                   "matchToMap vs 2000-landmark window", "frames_per_step": sample},
+            "config": {"workload": CONFIGS[HEADLINE]["what"], "frames_per_step": sample,
+                       "scene": "sparse (400 rectangles)" if args.sparse else "dense (corner-rich texture: the keypoint budget binds)"},
             "cpu_baseline": {"value": round(fps, 2), "unit": "frames/s", "cores": cores, "kind": cpu.kind,
                              "sample": "%d steps x %d frames, one whole frame per worker thread, %d workers"
                                        % (steps, sample, cores)},
@@ -657,22 +967,7 @@ def main():
         if out is not None:
             print(json.dumps(out), file=json_out, flush=True)
         return
-    out, st = run_b200(args, rank, world)
-    extra = {}
-    if not args.no_sweep:
-        extra["matcher_sweep"] = run_sweep(st, rank, world)
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        out["cpu_baseline"] = run_cpu_baseline(st)
-    extra["single_frame_latency"] = {
-        "ms": out.pop("single_frame_latency_ms"),
-        "what": "one stereo frame alone (batch of 2 images, nothing else in flight): host images in, keypoints + "
-                "descriptors + matches out, wall clock around enqueue/finish/read, median of 60"}
-    if "cpu_baseline" in out and out["cpu_baseline"].get("value"):
-        extra["single_frame_latency"]["reference_ms"] = round(1e3 / out["cpu_baseline"]["value"], 3)
-    out["extra"] = extra
-    if world > 1:
-        st["dist"].barrier()
-        st["dist"].destroy_process_group()
+    out = run_b200(args, rank, world)
     if rank == 0:
         print(json.dumps(out), file=json_out, flush=True)
 

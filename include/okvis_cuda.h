@@ -128,6 +128,11 @@ int okc_descriptor_set_destroy(okc_descriptor_set* set);
 int okc_match_sets(okc_context* ctx, const okc_descriptor_set* queries, const okc_descriptor_set* map,
                    uint32_t threshold, uint64_t index_offset, uint64_t* best_host, void* best_device,
                    void* stream_handle);
+/* The same into a device buffer of int64 keys with INT64_MAX (instead of OKC_NO_MATCH) for "no match": the keys of all
+ * shards then merge with ONE NCCL all-reduce(min) - distance first, global row index second, i.e. the reference's
+ * first-wins rule - without an epilogue kernel. */
+int okc_match_sets_ordered(okc_context* ctx, const okc_descriptor_set* queries, const okc_descriptor_set* map,
+                           uint32_t threshold, uint64_t index_offset, void* best_device_i64, void* stream_handle);
 
 /* 3D-2D map matching, Frontend::matchToMapByThread (Frontend.cpp:1744-1827) for all thread slices at once.
  * Keypoint k (descriptor queries[k], position kp_xy[2k..]) with use[k] != 0 is compared with every
@@ -418,6 +423,18 @@ int okc_batch_match_stereo_enqueue(okc_batch* batch, int n_pairs, const int* slo
 int okc_batch_pair_stereo(okc_batch* batch, int pair, double* dist, int32_t* k1_match, double* hp_W,
                           uint8_t* initialisable);
 
+/* Camera-sharded multiframes (one GPU per camera subset): matchStereo needs both cameras of an overlapping pair, so
+ * the ranks exchange their views. okc_batch_pack_views copies the views of `n` slots (keypoint count, keypoints,
+ * descriptors, back-projections, validity flags) into consecutive records of okc_packed_view_bytes(max_keypoints)
+ * bytes in caller-provided DEVICE memory, on the batch's stream - the send buffer of one NCCL all-gather.
+ * okc_batch_match_stereo_packed_enqueue then matches slot0[p] (k0) against record packed_index[p] of the gathered
+ * buffer (k1), whose camera has pose (C_WC, r_WC) = poses1[p] and focal length f1[p]. Results: okc_batch_pair_stereo. */
+size_t okc_packed_view_bytes(int max_keypoints);
+int okc_batch_pack_views(okc_batch* batch, int n, const int* slots, void* packed_device);
+int okc_batch_match_stereo_packed_enqueue(okc_batch* batch, int n_pairs, const int* slot0, const void* packed_device,
+                                          const int* packed_index, const okc_slot_pose* poses1, const double* f1,
+                                          double hamming_threshold);
+
 /* An older multiframe kept on the device for Frontend::matchMotionStereo (Frontend.cpp:1968-2150): okc_batch_retain
  * copies the descriptors, keypoints and back-projections of n_views slots (device to device, on the batch's stream)
  * after the frame was described; okc_keyframe_set_view gives a view its current pose (after an optimisation), focal
@@ -431,12 +448,21 @@ int okc_keyframe_set_view(okc_keyframe* keyframe, int view, const double C_WC[9]
                           const uint8_t* use0, int n_use0);
 /* Job j: the keypoints of view views[j] of keyframes[j] (k0) against the keypoints of slot slots[j] that have no
  * landmark after the landmark stage (only_unmatched != 0; the reference packs them, Frontend.cpp:2034-2047) or against
- * all of them. k1_match is the keypoint index inside the slot (the reference's k1s[k1]). After okc_batch_finish,
+ * all of them. k1_match is the keypoint index inside the slot (the reference's k1s[k1]). One call per frame with every
+ * job (okc_batch_match_stereo_enqueue likewise); a keyframe can be matched once the frame it was retained from is
+ * finished. After okc_batch_finish,
  * okc_batch_job_motion returns what okc_match_motion_stereo returns, for the view's keypoints. */
 int okc_batch_match_motion_enqueue(okc_batch* batch, int n_jobs, const okc_keyframe* const* keyframes, const int* views,
                                    const int* slots, double hamming_threshold, int only_unmatched);
 int okc_batch_job_motion(okc_batch* batch, int job, int* n0, double* dist, int32_t* k1_match, double* hp_W,
                          uint8_t* initialisable, double* quality);
+/* All stage results of a finished frame at once into caller arrays (a group whose first pointer is NULL is skipped):
+ * uninitialised-landmark matches per slot with stride max_keypoints (u_ctrs: num_slices per slot), stereo pairs with
+ * stride max_keypoints, motion jobs with stride = the largest max_keypoints among the batch and the keyframes
+ * (m_n0[j] = keypoints of job j's keyframe view). */
+int okc_batch_read_stages(okc_batch* batch, double* u_dist, int32_t* u_owner, double* u_hps, uint8_t* u_written,
+                          uint64_t* u_ctrs, double* s_dist, int32_t* s_k1, double* s_hp, uint8_t* s_init, int32_t* m_n0,
+                          double* m_dist, int32_t* m_k1, double* m_hp, uint8_t* m_init, double* m_quality);
 
 int okc_debug_batch_kernel_timing(okc_batch* batch, int enable);
 int okc_debug_batch_kernel_times(okc_batch* batch, char* names, int names_cap, float* ms, int cap, int* n);

@@ -38,7 +38,8 @@ EXPORTS = [
     "okc_landmark_pool_update", "okc_landmark_pool_destroy", "okc_batch_match_landmarks_enqueue",
     "okc_batch_slot_uninitialised", "okc_batch_slot_landmarks", "okc_batch_match_stereo_enqueue",
     "okc_batch_pair_stereo", "okc_keyframe_create", "okc_keyframe_destroy", "okc_batch_retain",
-    "okc_keyframe_set_view", "okc_batch_match_motion_enqueue", "okc_batch_job_motion",
+    "okc_keyframe_set_view", "okc_batch_match_motion_enqueue", "okc_batch_job_motion", "okc_batch_read_stages",
+    "okc_packed_view_bytes", "okc_batch_pack_views", "okc_batch_match_stereo_packed_enqueue", "okc_match_sets_ordered",
 ]
 STAGE_UNINITIALISED, STAGE_NO_IMU, STAGE_LOOP_CLOSURE = 1, 2, 4
 
@@ -207,6 +208,12 @@ def lib():
         L.okc_keyframe_set_view.argtypes = [vp, i, vp, vp, d, vp, i]
         L.okc_batch_match_motion_enqueue.argtypes = [vp, i, vp, vp, vp, d, i]
         L.okc_batch_job_motion.argtypes = [vp, i, C.POINTER(i), vp, vp, vp, vp, vp]
+        L.okc_batch_read_stages.argtypes = [vp] + [vp] * 15
+        L.okc_packed_view_bytes.argtypes = [i]
+        L.okc_packed_view_bytes.restype = C.c_size_t
+        L.okc_batch_pack_views.argtypes = [vp, i, vp, vp]
+        L.okc_batch_match_stereo_packed_enqueue.argtypes = [vp, i, vp, vp, vp, vp, vp, d]
+        L.okc_match_sets_ordered.argtypes = [vp, vp, vp, u32, u64, vp, vp]
         _lib = L
     return _lib
 
@@ -358,6 +365,12 @@ class Context:
         return best
 
     # -- Frontend::matchToMapByThread, Frontend.cpp:1744-1827 --
+    def match_sets_ordered(self, qset, mset, threshold, index_offset, best_device_ptr, stream=None):
+        """Per-shard best keys as int64 with INT64_MAX for "no match" (ready for an NCCL min all-reduce)."""
+        _check(lib().okc_match_sets_ordered(self.h, qset.h, mset.h, int(threshold), int(index_offset),
+                                            C.c_void_p(int(best_device_ptr)), C.c_void_p(stream) if stream else None),
+               "okc_match_sets_ordered")
+
     def match_to_map(self, queries, kp_xy, use, mp, map_owner, proj_xy, thresh_sq, hamming_threshold=60.0,
                      num_slices=4):
         q = np.ascontiguousarray(queries, np.uint8).reshape(-1, 48)
@@ -457,6 +470,10 @@ class Context:
         _check(lib().okc_match_stereo(self.h, C.byref(s0), C.byref(s1), float(hamming_threshold), _p(dist), _p(k1),
                                       _p(hp), _p(init)), "okc_match_stereo")
         return dist, k1, hp, init
+
+
+def packed_view_bytes(max_keypoints):
+    return int(lib().okc_packed_view_bytes(int(max_keypoints)))
 
 
 def slot_pose(C_WC, r_WC):
@@ -821,7 +838,7 @@ class Batch:
                        desc=np.empty((self.n, self.max_kp, 48), np.uint8),
                        dist=np.empty((self.n, self.max_kp), np.float64), owner=np.empty((self.n, self.max_kp), np.int32),
                        ctrs=np.zeros((self.n, 64), np.uint64), errs=np.zeros((self.n, 64), np.float64))
-        m = self._matching
+        m = self._matching or getattr(self, "_pool_matching", False)
         ctrs = out["ctrs"].reshape(-1)
         errs = out["errs"].reshape(-1)
         _check(lib().okc_batch_read_all(self.h, _p(out["kp"]), _p(out["n"]), _p(out["desc"]),
@@ -847,7 +864,7 @@ class Batch:
         _check(lib().okc_batch_match_landmarks_enqueue(self.h, pool.h, float(hamming_threshold), int(num_slices),
                                                        int(flags)), "okc_batch_match_landmarks_enqueue")
         self._slices = int(num_slices)
-        self._matching = True
+        self._pool_matching = True   # read_all returns the matchToMapByThread results of the landmark stage
         self._pool_L = pool.L
 
     def slot_uninitialised(self, slot, nk):
@@ -874,8 +891,13 @@ class Batch:
                     owner=out["owner"][:n], pool=out["pool"][:n])
 
     def match_stereo_enqueue(self, pairs, hamming_threshold=60.0):
-        s0 = np.ascontiguousarray([p[0] for p in pairs], np.int32)
-        s1 = np.ascontiguousarray([p[1] for p in pairs], np.int32)
+        """pairs: [(slot0, slot1)]; the marshalled arrays are cached per list object (pipelines pass the same list)."""
+        c = getattr(self, "_pairs_cache", None)
+        if c is None or c[0] is not pairs:
+            c = (pairs, np.ascontiguousarray([p[0] for p in pairs], np.int32),
+                 np.ascontiguousarray([p[1] for p in pairs], np.int32))
+            self._pairs_cache = c
+        s0, s1 = c[1], c[2]
         _check(lib().okc_batch_match_stereo_enqueue(self.h, len(pairs), _p(s0), _p(s1), float(hamming_threshold)),
                "okc_batch_match_stereo_enqueue")
 
@@ -892,11 +914,14 @@ class Batch:
         _check(lib().okc_batch_retain(self.h, len(s), _p(s), keyframe.h), "okc_batch_retain")
 
     def match_motion_enqueue(self, jobs, hamming_threshold=60.0, only_unmatched=True):
-        """jobs: [(keyframe, view, slot)]."""
-        kf = (C.c_void_p * len(jobs))(*[j[0].h for j in jobs])
-        v = np.ascontiguousarray([j[1] for j in jobs], np.int32)
-        s = np.ascontiguousarray([j[2] for j in jobs], np.int32)
-        self._motion_cap = max([self.max_kp] + [j[0].max_kp for j in jobs])
+        """jobs: [(keyframe, view, slot)]; the marshalled arrays are cached per list object."""
+        c = getattr(self, "_jobs_cache", None)
+        if c is None or c[0] is not jobs:
+            c = (jobs, (C.c_void_p * len(jobs))(*[j[0].h for j in jobs]), np.ascontiguousarray([j[1] for j in jobs], np.int32),
+                 np.ascontiguousarray([j[2] for j in jobs], np.int32), max([self.max_kp] + [j[0].max_kp for j in jobs]))
+            self._jobs_cache = c
+        kf, v, s = c[1], c[2], c[3]
+        self._motion_cap = c[4]
         _check(lib().okc_batch_match_motion_enqueue(self.h, len(jobs), kf, _p(v), _p(s), float(hamming_threshold),
                                                     int(bool(only_unmatched))), "okc_batch_match_motion_enqueue")
 
@@ -912,6 +937,41 @@ class Batch:
                "okc_batch_job_motion")
         n = n0.value
         return dist[:n], k1[:n], hp[:n], init[:n], q[:n]
+
+    def pack_views(self, slots, packed_device_ptr):
+        """Views of `slots` into consecutive records of packed_view_bytes(max_kp) bytes of caller device memory."""
+        s = np.ascontiguousarray(slots, np.int32)
+        _check(lib().okc_batch_pack_views(self.h, len(s), _p(s), C.c_void_p(int(packed_device_ptr))),
+               "okc_batch_pack_views")
+
+    def match_stereo_packed_enqueue(self, slot0, packed_device_ptr, packed_index, poses1, f1, hamming_threshold=60.0):
+        s0 = np.ascontiguousarray(slot0, np.int32)
+        pi = np.ascontiguousarray(packed_index, np.int32)
+        ps = np.ascontiguousarray(poses1, np.float64).reshape(len(s0), 24)
+        ff = np.ascontiguousarray(f1, np.float64)
+        _check(lib().okc_batch_match_stereo_packed_enqueue(self.h, len(s0), _p(s0), C.c_void_p(int(packed_device_ptr)),
+                                                           _p(pi), _p(ps), _p(ff), float(hamming_threshold)),
+               "okc_batch_match_stereo_packed_enqueue")
+
+    def read_stages(self, out=None, n_pairs=0, n_jobs=0, uninitialised=False):
+        """All stage results of a finished frame into (reusable) arrays: dict(u_dist, u_owner, u_hps, u_written, u_ctrs,
+        s_dist, s_k1, s_hp, s_init, m_n0, m_dist, m_k1, m_hp, m_init, m_quality)."""
+        if out is None:
+            mk, rows = self.max_kp, getattr(self, "_motion_cap", self.max_kp)
+            out = dict(u_dist=np.empty((self.n, mk)), u_owner=np.empty((self.n, mk), np.int32), u_hps=np.empty((self.n, mk, 4)),
+                       u_written=np.empty((self.n, mk), np.uint8), u_ctrs=np.zeros((self.n, 64), np.uint64),
+                       s_dist=np.empty((max(n_pairs, 1), mk)), s_k1=np.empty((max(n_pairs, 1), mk), np.int32),
+                       s_hp=np.empty((max(n_pairs, 1), mk, 4)), s_init=np.empty((max(n_pairs, 1), mk), np.uint8),
+                       m_n0=np.zeros(max(n_jobs, 1), np.int32), m_dist=np.empty((max(n_jobs, 1), rows)),
+                       m_k1=np.empty((max(n_jobs, 1), rows), np.int32), m_hp=np.empty((max(n_jobs, 1), rows, 4)),
+                       m_init=np.empty((max(n_jobs, 1), rows), np.uint8), m_quality=np.empty((max(n_jobs, 1), rows)))
+        u = [out[k] if uninitialised else None for k in ("u_dist", "u_owner", "u_hps", "u_written")]
+        uc = out["u_ctrs"].reshape(-1) if uninitialised else None
+        s_ = [out[k] if n_pairs else None for k in ("s_dist", "s_k1", "s_hp", "s_init")]
+        m_ = [out[k] if n_jobs else None for k in ("m_n0", "m_dist", "m_k1", "m_hp", "m_init", "m_quality")]
+        _check(lib().okc_batch_read_stages(self.h, *[_p(x) for x in u], _p(uc), *[_p(x) for x in s_], *[_p(x) for x in m_]),
+               "okc_batch_read_stages")
+        return out
 
     def stream(self):
         return lib().okc_batch_stream(self.h)

@@ -75,7 +75,8 @@ struct okc_descriptor_set {
 
 namespace okc {
 int launch_hamming_best(const void* queries, int nq, const void* map, long long nm, unsigned threshold,
-                        unsigned long long indexOffset, unsigned long long* best, cudaStream_t s);
+                        unsigned long long indexOffset, unsigned long long* best, cudaStream_t s,
+                        unsigned long long noMatch = ~0ull);
 }  // namespace okc
 
 namespace okc { Knobs g_knobs; }

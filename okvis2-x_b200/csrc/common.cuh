@@ -103,6 +103,7 @@ struct Slot {
                            // uninitialised matcher the others; null: matchToMapByThread takes every row
   // pose of the slot's camera for this frame: T_WC = T_WS * T_SC
   double C_WC[9], r_WC[3]; // (per enqueue)
+  double T_CW[12];         // (per enqueue) its inverse: rotation row-major, then translation
   double focal_mean;       // 0.5 * (focalLengthU + focalLengthV)
 };
 
@@ -117,6 +118,7 @@ struct StereoSide {
   const int* n_dev;         // count still on the device (a batch slot), or null
   int n;                    // count, or the capacity when n_dev is set
   double C[9], r[3], f;
+  const Slot* pose_slot;    // a batch slot: C / r are read from its record (refreshed every frame) instead
 };
 struct StereoJob {
   StereoSide v0, v1;
@@ -125,6 +127,8 @@ struct StereoJob {
   // packs them, Frontend.cpp:2034-2047): skipped unless both owners are < 0; null = every k1
   const int* v1_owner_a;
   const int* v1_owner_b;
+  const int* v1_list;       // or: the candidates k1, ascending (a precompacted list of those keypoints), with
+  const int* v1_list_n;     //   their number on the device
   double* dist;
   int* k1;
   double* hp;
@@ -144,6 +148,7 @@ struct UninitJob {
   const double* e_C;        //   the back-projections
   const uint8_t* bp_valid;  //   and their validity (Frontend.cpp:1862-1872)
   double C_WC[9];
+  const Slot* pose_slot;    // a batch slot: C_WC and a.r_WC are read from its record (refreshed every frame) instead
   const uint8_t* use;       // eligibility flags, or null: a keypoint is eligible when
   const int* owner14;       //   matchToMapByThread left it without a landmark (owner14[k] < 0; null: always)
   const int* previousOwner; // loop-closure mode only, or null
@@ -156,6 +161,8 @@ struct UninitJob {
   const double* map_r_W;
   const int* nm_dev;
   int nm;
+  const int* row_list;      // the rows to sweep, ascending (a precompacted list of the non-3D rows), or null: all rows
+  const int* n_list_dev;    //   and their number
   int num_slices;
   UninitArgs a;
   double* dist;
@@ -169,6 +176,10 @@ void launch_match_stereo_jobs(const StereoJob* jobs, int nJobs, int max0, bool m
                               cudaStream_t s);
 void launch_match_uninit_jobs(const UninitJob* jobs, int nJobs, int maxNk, cudaStream_t s);
 void launch_back_project_slots(const Slot* slots, int n, int max_kp, cudaStream_t s);
+// per slot: the keypoints without a landmark after the two map matchers (owner_a[k] < 0 and owner_b[k] < 0; a null
+// array counts as "none matched"), ascending, into list[slot * max_kp ..] with their number in count[slot]
+struct UnmatchedArgs { const int* owner_a; const int* owner_b; const int* nk_dev; int* list; int* count; };
+void launch_unmatched_lists(const UnmatchedArgs* args, int n, int max_kp, cudaStream_t s);
 
 // Landmark preparation of Frontend::matchToMap for one camera image (Frontend.cpp:1376-1500): inputs of the shared
 // landmark pool, the pose of this image, and where its pool is packed.
@@ -197,6 +208,7 @@ struct PrepSlot {
   PrepareArgs a;               // (a.visible = visible below)
   okc_pinhole cam;
   double T_CW[12];
+  const Slot* pose_slot;       // a batch slot: T_CW and a.r_WC1 are read from its record (refreshed every frame) instead
   double repr_threshold;
   double* proj_xy;             // L x 2
   uint8_t* status;             // L
@@ -208,6 +220,9 @@ struct PrepSlot {
   double* r_W;                 // 3 L x 3
   uint8_t* filled;             // 3 L
   int* row_obs;                // 3 L
+  int* u_count;                // L     scratch
+  int* u_offset;               // L + 1 rows of the non-3D landmarks before landmark l; [L] = their number
+  int* u_rows;                 // 3 L   those rows (indices into the pool), ascending
 };
 void launch_prepare_landmarks_slots(const PrepSlot* prep, int n, int L, cudaStream_t s);
 int check_pinhole(const okc_pinhole* cam);   // OKC_OK or OKC_ERR_INVALID (with the error string set)

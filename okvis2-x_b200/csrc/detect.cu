@@ -260,26 +260,6 @@ void harris_bitmap_pos(int W, int x, int y, size_t* word, int* bit) {
   *bit = off & 31;
 }
 
-__device__ __forceinline__ void bitonic_sort(uint64_t* keys, int npad) {
-  // keys[0..npad) ascending; npad is a power of two; all threads of the CTA participate.
-  for (int k = 2; k <= npad; k <<= 1) {
-    for (int j = k >> 1; j > 0; j >>= 1) {
-      for (int i = threadIdx.x; i < npad; i += 1024) {
-        int ixj = i ^ j;
-        if (ixj > i) {
-          uint64_t a = keys[i], b = keys[ixj];
-          bool up = (i & k) == 0;
-          if ((a > b) == up) {
-            keys[i] = b;
-            keys[ixj] = a;
-          }
-        }
-      }
-      __syncthreads();
-    }
-  }
-}
-
 // ----------------------------------------------------------------------------------------------
 // order_candidates: raster-ordered candidate list + the reference's std::sort order
 // ----------------------------------------------------------------------------------------------
@@ -294,12 +274,15 @@ __device__ __forceinline__ void bitonic_sort(uint64_t* keys, int npad) {
 //     sequential two-pointer partition is replaced by its closed form: the i-th "left stop" (score <= pivot,
 //     scanning up) is swapped with the i-th "right stop" (score >= pivot, scanning down) while L_i < R_i.
 //   * __final_insertion_sort is a stable insertion sort, i.e. the final order = a stable sort by score of the
-//     array the partition phase leaves behind -> one bitonic sort on (score desc, position asc) keys.
+//     array the partition phase leaves behind. That array is a chain of segments between consecutive cuts (at most
+//     16 elements each, or heap-sorted) in which no element of a later segment belongs before an earlier one, so
+//     every segment is sorted on its own, by ranking its elements in parallel (a global bitonic sort of 64-bit keys
+//     was 40 % of the kernel).
 // tools/introsort_model.py checks this formulation against the real std::sort (oracle/_ref) on tie-heavy and
 // adversarial (heapsort-triggering) inputs.
 constexpr int kOrdThreads = 1024;
-constexpr int kOrdSmemCap = 8192;                         // candidates handled entirely in shared memory
-constexpr int kOrdQueueSmem = 512;                        // >= kOrdSmemCap / 17 ranges per level
+constexpr int kOrdSmemCap = 11264;                        // candidates handled entirely in shared memory (188 KB)
+constexpr int kOrdQueueSmem = 704;                        // >= kOrdSmemCap / 17 ranges per level
 constexpr int kOrdQueueGlobal = kCandCap / 16;            // >= kCandCap / 17
 
 struct OrdArrays {
@@ -308,7 +291,6 @@ struct OrdArrays {
   int* lp;          // left stops of the range being partitioned (positions), stored inside the range
   int* rp;          // right stops
   int2* q[2];       // range queues of the current / next level
-  uint64_t* keys;   // final sort keys (may alias sc/lp/rp: they are dead by then)
 };
 
 __device__ __forceinline__ void ord_swap(const OrdArrays& A, int i, int j) {
@@ -419,6 +401,102 @@ __device__ int ord_warp_partition(const OrdArrays& A, int f, int l, int lane) {
   return cut;
 }
 
+// The same partition by the whole CTA, for the long ranges at the top of the recursion (one warp walking 7 000
+// elements twice was most of the kernel): the warps classify contiguous chunks, a scan over the warps places the
+// stop lists, and because the left stops ascend while the right stops descend, "L_i < R_i" holds for a prefix of the
+// pairs, so the number of swaps is a plain count. Called by every thread; returns the cut to every thread.
+struct OrdBlockScratch { int cntL[32], cntR[32], offL[32], offR[32], nL, nR, t; };
+
+__device__ int ord_block_partition(const OrdArrays& A, int f, int l, OrdBlockScratch& S) {
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid == 0) {  // __move_median_to_first(first, first + 1, mid, last - 1)
+    const int a = f + 1, b = f + (l - f) / 2, c = l - 1;
+    const int sa = A.sc[a], sb = A.sc[b], s_c = A.sc[c];
+    int pick;
+    if (sa > sb) pick = (sb > s_c) ? b : ((sa > s_c) ? c : a);
+    else pick = (sa > s_c) ? a : ((sb > s_c) ? c : b);
+    ord_swap(A, f, pick);
+    S.t = 0;
+  }
+  __syncthreads();
+  const int pv = A.sc[f];
+  const int len = l - f;
+  const unsigned lt = (1u << lane) - 1u;
+  const int chunk = (((len + 31) / 32 + 31) / 32) * 32;   // indices per warp, a multiple of 32
+  const int i0 = warp * chunk, i1 = min(len, i0 + chunk);
+  int nL = 0, nR = 0;
+  for (int base = i0; base < i1; base += 32) {
+    const int i = base + lane;
+    const int pL = f + 1 + i, pR = l - 1 - i;
+    const bool isL = i < i1 && pL < l && !(A.sc[pL] > pv);
+    const bool isR = i < i1 && !(pv > A.sc[pR]);
+    nL += __popc(__ballot_sync(0xffffffffu, isL));
+    nR += __popc(__ballot_sync(0xffffffffu, isR));
+  }
+  if (lane == 0) {
+    S.cntL[warp] = nL;
+    S.cntR[warp] = nR;
+  }
+  __syncthreads();
+  if (warp == 0) {
+    const int cl = S.cntL[lane], cr = S.cntR[lane];
+    int il = cl, ir = cr;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const int tl = __shfl_up_sync(0xffffffffu, il, d), tr = __shfl_up_sync(0xffffffffu, ir, d);
+      if (lane >= d) {
+        il += tl;
+        ir += tr;
+      }
+    }
+    S.offL[lane] = il - cl;
+    S.offR[lane] = ir - cr;
+    if (lane == 31) {
+      S.nL = il;
+      S.nR = ir;
+    }
+  }
+  __syncthreads();
+  int oL = S.offL[warp], oR = S.offR[warp];
+  for (int base = i0; base < i1; base += 32) {
+    const int i = base + lane;
+    const int pL = f + 1 + i, pR = l - 1 - i;
+    const bool isL = i < i1 && pL < l && !(A.sc[pL] > pv);
+    const bool isR = i < i1 && !(pv > A.sc[pR]);
+    const unsigned bL = __ballot_sync(0xffffffffu, isL), bR = __ballot_sync(0xffffffffu, isR);
+    if (isL) A.lp[f + 1 + oL + __popc(bL & lt)] = pL;
+    if (isR) A.rp[f + oR + __popc(bR & lt)] = pR;
+    oL += __popc(bL);
+    oR += __popc(bR);
+  }
+  __syncthreads();
+  const int NL = S.nL, NR = S.nR;
+  const int m = NL < NR ? NL : NR;
+  int mine = 0;
+  for (int i = tid; i < m; i += kOrdThreads) mine += A.lp[f + 1 + i] < A.rp[f + i] ? 1 : 0;
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) mine += __shfl_xor_sync(0xffffffffu, mine, d);
+  if (lane == 0 && mine) atomicAdd(&S.t, mine);
+  __syncthreads();
+  const int t = S.t;
+  int cut;
+  if (t == 0) {
+    cut = NL > 0 ? A.lp[f + 1] : l;
+  } else {
+    cut = A.rp[f + t - 1];
+    if (t < NL) {
+      const int nextL = A.lp[f + 1 + t];
+      if (nextL < cut) cut = nextL;
+    }
+  }
+  __syncthreads();   // (the stop lists are read above, the swaps below move the elements they point at)
+  for (int i = tid; i < t; i += kOrdThreads) ord_swap(A, A.lp[f + 1 + i], A.rp[f + i]);
+  __syncthreads();
+  return cut;
+}
+
+constexpr int kOrdCoopLen = 1024;   // ranges at least this long are partitioned by the whole CTA
+
 __global__ void __launch_bounds__(kOrdThreads, 1)
 order_candidates_kernel(const Slot* __restrict__ slots, int W, int H) {
   const Slot& slot = slots[blockIdx.x];
@@ -430,15 +508,26 @@ order_candidates_kernel(const Slot* __restrict__ slots, int W, int H) {
   extern __shared__ __align__(16) uint8_t smem[];
   __shared__ int s_warp[32];
   __shared__ int s_n, s_qcount[2];
+  __shared__ unsigned s_cut[kCandCap / 32 + 1];
+  __shared__ OrdBlockScratch s_blk;
+  __shared__ int2 s_big[2][kCandCap / kOrdCoopLen + 1];   // ranges of the current / next level long enough for the CTA
+  __shared__ int s_bigcount[2];   // bit i: a partition cut (or the start) lies at position i
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+#ifdef OKC_ORDER_TRACE
+  long long tr[6] = {}, t0 = clock64();
+#define ORD_T(i) do { __syncthreads(); if (tid == 0) tr[i] += clock64() - t0; t0 = clock64(); } while (0)
+#else
+#define ORD_T(i) do { } while (0)
+#endif
 
   // ---- A. candidate count and raster-ordered offsets from the bitmap ----
   const int wordsPerRow = harris_strips(W) * kStripWords;
   const int words = H * wordsPerRow;
-  const int chunk = (words + kOrdThreads - 1) / kOrdThreads;
-  const int w0 = tid * chunk, w1 = min(words, w0 + chunk);
+  // every warp owns a contiguous block of bitmap words and reads it 32 words at a time (coalesced)
+  const int chunk = (((words + 31) / 32 + 31) / 32) * 32;   // words per warp, a multiple of 32
+  const int w0 = warp * chunk, w1 = min(words, w0 + chunk);
   int mine = 0;
-  for (int w = w0; w < w1; ++w) mine += __popc(bitmap[w]);
+  for (int w = w0 + lane; w < w1; w += 32) mine += __popc(bitmap[w]);
   int incl = mine;
   for (int d = 1; d < 32; d <<= 1) {
     const int v = __shfl_up_sync(0xffffffffu, incl, d);
@@ -481,13 +570,21 @@ order_candidates_kernel(const Slot* __restrict__ slots, int W, int H) {
     A.sc = reinterpret_cast<int*>(u);
     A.lp = A.sc + cap;
     A.rp = A.lp + cap;
-    // shared memory: the keys overlay sc/lp/rp (12 * cap bytes >= 8 * cap); global: their own region
-    A.keys = inSmem ? reinterpret_cast<uint64_t*>(u) : reinterpret_cast<uint64_t*>(u + cap * 12);
   }
+  for (int w = tid; w <= (n >> 5); w += kOrdThreads) s_cut[w] = w == 0 ? 1u : 0u;
   {
-    int pos = s_warp[warp] + incl - mine;
-    for (int w = w0; w < w1; ++w) {
-      unsigned bits = bitmap[w];
+    int base = s_warp[warp];   // candidates in front of this warp's block
+    for (int wb = w0; wb < w1; wb += 32) {
+      const int w = wb + lane;
+      unsigned bits = w < w1 ? bitmap[w] : 0u;
+      const int c = __popc(bits);
+      int inc = c;
+      for (int d = 1; d < 32; d <<= 1) {
+        const int v = __shfl_up_sync(0xffffffffu, inc, d);
+        if (lane >= d) inc += v;
+      }
+      int pos = base + inc - c;
+      base += __shfl_sync(0xffffffffu, inc, 31);
       const int y = w / wordsPerRow, rem = w - y * wordsPerRow;
       const int xb = (rem / kStripWords) * kStripCols - 4 + ((rem % kStripWords) << 5);
       while (bits) {
@@ -501,18 +598,37 @@ order_candidates_kernel(const Slot* __restrict__ slots, int W, int H) {
     }
   }
   if (tid == 0) {
-    A.q[0][0] = make_int2(0, n);
-    s_qcount[0] = n > 16 ? 1 : 0;
-    s_qcount[1] = 0;
+    s_qcount[0] = s_qcount[1] = s_bigcount[0] = s_bigcount[1] = 0;
+    if (n >= kOrdCoopLen) s_big[0][s_bigcount[0]++] = make_int2(0, n);
+    else if (n > 16) A.q[0][s_qcount[0]++] = make_int2(0, n);
   }
   __syncthreads();
+  ORD_T(0);
 
   // ---- B. introsort partition phase, level by level ----
   int depthLimit = 2 * (31 - __clz(n));
   int cur = 0;
   while (true) {
-    const int cnt = s_qcount[cur];
-    if (cnt == 0) break;
+    const int cnt = s_qcount[cur], cntBig = s_bigcount[cur];
+    if (cnt == 0 && cntBig == 0) break;
+    // a range that is split further goes to the next level's queue: the CTA's when it is long, else the warps'
+    auto push = [&](int a, int b) {
+      if (b - a >= kOrdCoopLen) s_big[cur ^ 1][atomicAdd(&s_bigcount[cur ^ 1], 1)] = make_int2(a, b);
+      else if (b - a > 16) A.q[cur ^ 1][atomicAdd(&s_qcount[cur ^ 1], 1)] = make_int2(a, b);
+    };
+    for (int s = 0; s < cntBig; ++s) {   // the long ranges, by the whole CTA (uniform loop: every thread takes part)
+      const int2 r = s_big[cur][s];
+      if (depthLimit == 0) {
+        if (tid == 0) ord_heap_sort(A, r.x, r.y);
+        continue;
+      }
+      const int cut = ord_block_partition(A, r.x, r.y, s_blk);
+      if (tid == 0) {
+        atomicOr(&s_cut[cut >> 5], 1u << (cut & 31));
+        push(r.x, cut);
+        push(cut, r.y);
+      }
+    }
     for (int s = warp; s < cnt; s += kOrdThreads / 32) {
       const int2 r = A.q[cur][s];
       if (depthLimit == 0) {
@@ -521,42 +637,63 @@ order_candidates_kernel(const Slot* __restrict__ slots, int W, int H) {
       }
       const int cut = ord_warp_partition(A, r.x, r.y, lane);
       if (lane == 0) {
-        if (cut - r.x > 16) A.q[cur ^ 1][atomicAdd(&s_qcount[cur ^ 1], 1)] = make_int2(r.x, cut);
-        if (r.y - cut > 16) A.q[cur ^ 1][atomicAdd(&s_qcount[cur ^ 1], 1)] = make_int2(cut, r.y);
+        atomicOr(&s_cut[cut >> 5], 1u << (cut & 31));
+        push(r.x, cut);
+        push(cut, r.y);
       }
     }
     __syncthreads();
-    if (tid == 0) s_qcount[cur] = 0;
+    if (tid == 0) s_qcount[cur] = s_bigcount[cur] = 0;
     cur ^= 1;
     --depthLimit;
     __syncthreads();
   }
-
-  // ---- C. __final_insertion_sort == stable sort by score (desc) of what the partitions left ----
-  int npad = 1;
-  while (npad < n) npad <<= 1;
-  if (inSmem) {
-    int mys[kOrdSmemCap / kOrdThreads];
-#pragma unroll
-    for (int k = 0; k < kOrdSmemCap / kOrdThreads; ++k) {
-      const int i = tid + k * kOrdThreads;
-      mys[k] = i < n ? A.sc[i] : 0;
+  ORD_T(1);
+  // ---- C. __final_insertion_sort = a stable insertion sort of the whole array. The partitions leave it as a chain
+  //         of segments between consecutive cuts - at most 16 elements each, or heap-sorted - where no element of a
+  //         later segment belongs in front of an earlier one, so the stable sort of the array is the stable sort of
+  //         every segment ----
+  // Every element finds its segment [start, end) in the cut bitmap and its rank inside it - the elements with a larger
+  // score plus the equal ones in front of it - i.e. its place after a stable sort. Segments longer than 16 elements
+  // only come from the heapsort path and are sorted already.
+  for (int i = tid; i < n; i += kOrdThreads) {
+    int start, end = n;
+    {
+      int w = i >> 5;
+      unsigned bits = s_cut[w] & (0xffffffffu >> (31 - (i & 31)));   // cuts at or before i in its word
+      while (!bits) bits = s_cut[--w];                                // (bit 0 of word 0 is always set)
+      start = (w << 5) + 31 - __clz(bits);
+      w = i >> 5;
+      bits = (i & 31) == 31 ? 0u : (s_cut[w] & (0xffffffffu << ((i & 31) + 1)));   // cuts behind i
+      for (;;) {
+        if (bits) {
+          end = min(n, (w << 5) + __ffs(bits) - 1);
+          break;
+        }
+        if (++w > (n >> 5)) break;
+        bits = s_cut[w];
+      }
     }
-    __syncthreads();  // sc/lp/rp are dead from here on: the keys overlay them
-#pragma unroll
-    for (int k = 0; k < kOrdSmemCap / kOrdThreads; ++k) {
-      const int i = tid + k * kOrdThreads;
-      if (i < npad) A.keys[i] = i < n ? cand_key(mys[k], (uint32_t)i) : ~0ull;
+    const int vs = A.sc[i];
+    int pos = i;
+    if (end - start <= 16) {
+      int ahead = 0;
+      for (int j = start; j < end; ++j) {
+        const int sj = A.sc[j];
+        ahead += (sj > vs || (sj == vs && j < i)) ? 1 : 0;
+      }
+      pos = start + ahead;
     }
-  } else {
-    for (int i = tid; i < npad; i += kOrdThreads) A.keys[i] = i < n ? cand_key(A.sc[i], (uint32_t)i) : ~0ull;
+    A.lp[pos] = vs;
+    A.rp[pos] = (int)A.ra[i];
   }
   __syncthreads();
-  bitonic_sort(A.keys, npad);
-  for (int i = tid; i < n; i += kOrdThreads) {
-    const uint64_t k = A.keys[i];
-    cand[i] = cand_key(cand_score(k), A.ra[(uint32_t)k]);
-  }
+  ORD_T(3);
+  for (int i = tid; i < n; i += kOrdThreads) cand[i] = cand_key(A.lp[i], (uint32_t)A.rp[i]);
+#ifdef OKC_ORDER_TRACE
+  ORD_T(4);
+  if (tid == 0) printf("order trace (cycles): n %d gather %lld partition %lld segments %lld write %lld\n", n, tr[0], tr[1], tr[3], tr[4]);
+#endif
 }
 
 constexpr size_t kOrdSmemBytes = (size_t)kOrdSmemCap * 4 + 2 * (size_t)kOrdQueueSmem * 8 + (size_t)kOrdSmemCap * 12;

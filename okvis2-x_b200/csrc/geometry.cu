@@ -485,7 +485,7 @@ __device__ __forceinline__ void normalized3(const double v[3], double o[3]) {
   }
 }
 
-__device__ __forceinline__ void prune_observations_body(const PrepareArgs& a, int l) {
+__device__ __forceinline__ void prune_observations_body(const PrepareArgs& a, int l, const double* __restrict__ r_WC1) {
   int* so = a.slot_obs + 3 * l;
   so[0] = so[1] = so[2] = -1;
   a.is3d[l] = 0;
@@ -493,7 +493,7 @@ __device__ __forceinline__ void prune_observations_body(const PrepareArgs& a, in
   if (!a.visible[l]) return;
   const double* hp = a.hp_W + 4 * l;
   const double p_W[3] = {hp[0] / hp[3], hp[1] / hp[3], hp[2] / hp[3]};
-  const double r_W[3] = {p_W[0] - a.r_WC1[0], p_W[1] - a.r_WC1[1], p_W[2] - a.r_WC1[2]};
+  const double r_W[3] = {p_W[0] - r_WC1[0], p_W[1] - r_WC1[1], p_W[2] - r_WC1[2]};
   double e_W[3];
   normalized3(r_W, e_W);
   const double rn = sqrt(dot3(r_W, r_W));
@@ -542,7 +542,7 @@ __device__ __forceinline__ void prune_observations_body(const PrepareArgs& a, in
 
 __global__ void prune_observations_kernel(PrepareArgs a) {
   const int l = blockIdx.x * blockDim.x + threadIdx.x;
-  if (l < a.L) prune_observations_body(a, l);
+  if (l < a.L) prune_observations_body(a, l, a.r_WC1);
 }
 
 // exclusive scan of rows[] -> row_offset[L + 1] (one block; L is a few thousand)
@@ -620,21 +620,31 @@ __global__ void pack_pool_kernel(PrepareArgs a, const int* __restrict__ offset, 
 __global__ void project_landmarks_slots_kernel(const PrepSlot* __restrict__ prep) {
   const PrepSlot& p = prep[blockIdx.y];
   const int l = blockIdx.x * blockDim.x + threadIdx.x;
-  if (l < p.a.L) project_landmark_body(p.cam, p.T_CW, p.a.hp_W, l, p.repr_threshold, p.proj_xy, p.status, p.visible);
+  if (l < p.a.L)
+    project_landmark_body(p.cam, p.pose_slot ? p.pose_slot->T_CW : p.T_CW, p.a.hp_W, l, p.repr_threshold, p.proj_xy,
+                          p.status, p.visible);
 }
 __global__ void prune_observations_slots_kernel(const PrepSlot* __restrict__ prep) {
   const PrepSlot& p = prep[blockIdx.y];
   const int l = blockIdx.x * blockDim.x + threadIdx.x;
-  if (l < p.a.L) prune_observations_body(p.a, l);
+  if (l < p.a.L) prune_observations_body(p.a, l, p.pose_slot ? p.pose_slot->r_WC : p.a.r_WC1);
 }
 __global__ void __launch_bounds__(1024) scan_rows_slots_kernel(const PrepSlot* __restrict__ prep) {
   const PrepSlot& p = prep[blockIdx.x];
   scan_rows_body(p.a.rows, p.a.L, p.row_offset);
+  // the rows of the landmarks that are not 3D (what matchToMapByThreadUnitialised sweeps), counted the same way:
+  // u_count[l] = is3d[l] ? 0 : rows[l] is written over slot_obs' neighbour scratch first
+  __syncthreads();
+  for (int l = threadIdx.x; l < p.a.L; l += 1024) p.u_count[l] = p.a.is3d[l] ? 0 : p.a.rows[l];
+  __syncthreads();
+  scan_rows_body(p.u_count, p.a.L, p.u_offset);
 }
 __global__ void pack_pool_slots_kernel(const PrepSlot* __restrict__ prep) {
   const PrepSlot& p = prep[blockIdx.y];
-  pack_pool_body(p.a, blockIdx.x * blockDim.x + threadIdx.x, p.row_offset, p.pool, p.owner, p.e_W, p.r_W, p.filled,
-                 p.row_obs);
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  pack_pool_body(p.a, t, p.row_offset, p.pool, p.owner, p.e_W, p.r_W, p.filled, p.row_obs);
+  const int l = t / 3, n = t - 3 * l;
+  if (l < p.a.L && n < p.a.rows[l] && !p.a.is3d[l]) p.u_rows[p.u_offset[l] + n] = p.row_offset[l] + n;
 }
 
 void launch_prepare_landmarks_slots(const PrepSlot* prep, int n, int L, cudaStream_t s) {

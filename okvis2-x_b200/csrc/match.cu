@@ -305,10 +305,19 @@ static int pick_rows_per_chunk(int nq, long long nm, int ctasPerSm) {
   return (int)rows;
 }
 
+__global__ void fill_keys_kernel(unsigned long long* __restrict__ best, int n, unsigned long long v) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) best[i] = v;
+}
+
+// noMatch: the key of "no row below the threshold" (~0 = OKC_NO_MATCH, or INT64_MAX for keys that are min-reduced as
+// signed integers); any value above every real key (dist <= 384 in bits 32..40) works with the kernels' atomicMin
 int launch_hamming_best(const void* queries, int nq, const void* map, long long nm, unsigned threshold,
-                        unsigned long long indexOffset, unsigned long long* best, cudaStream_t s) {
+                        unsigned long long indexOffset, unsigned long long* best, cudaStream_t s,
+                        unsigned long long noMatch) {
   if (nq <= 0) return 0;
-  cudaMemsetAsync(best, 0xff, sizeof(unsigned long long) * (size_t)nq, s);
+  if (noMatch == ~0ull) cudaMemsetAsync(best, 0xff, sizeof(unsigned long long) * (size_t)nq, s);
+  else fill_keys_kernel<<<(nq + 255) / 256, 256, 0, s>>>(best, nq, noMatch);
   if (nm <= 0) return 0;
   const bool plain = g_knobs.match_plain != 0;   // tests: the plain 12-word sweep as the A/B baseline
   const int rowsPerChunk = pick_rows_per_chunk(nq, nm, plain ? 2 : 3);
@@ -913,7 +922,9 @@ match_stereo_kernel(const StereoJob* __restrict__ jobs, double hammingThreshold)
   const int lane = threadIdx.x & 31;
   const int k0 = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int n0 = v0.n_dev ? min(*v0.n_dev, v0.n) : v0.n;
-  const int n1 = v1.n_dev ? min(*v1.n_dev, v1.n) : v1.n;
+  // candidates k1: every keypoint of v1, or a precompacted ascending list (the slot's keypoints without a landmark)
+  const int* __restrict__ list1 = job.v1_list;
+  const int n1 = list1 ? min(*job.v1_list_n, v1.n) : (v1.n_dev ? min(*v1.n_dev, v1.n) : v1.n);
   if (k0 >= n0) return;
   double* __restrict__ outDist = job.dist;
   int* __restrict__ outK1 = job.k1;
@@ -936,12 +947,18 @@ match_stereo_kernel(const StereoJob* __restrict__ jobs, double hammingThreshold)
   V3 hps = v3(0.0, 0.0, 0.0);
   int k1_match = MOTION ? -1 : 0;
   double quality = 0.0;
-  const V3 r0 = v3(v0.r[0], v0.r[1], v0.r[2]), r1 = v3(v1.r[0], v1.r[1], v1.r[2]);
+  // poses: by value, or from the batch slot's record (the job table then stays valid from frame to frame)
+  const double* __restrict__ C0 = v0.pose_slot ? v0.pose_slot->C_WC : v0.C;
+  const double* __restrict__ C1 = v1.pose_slot ? v1.pose_slot->C_WC : v1.C;
+  const double* __restrict__ p0 = v0.pose_slot ? v0.pose_slot->r_WC : v0.r;
+  const double* __restrict__ p1 = v1.pose_slot ? v1.pose_slot->r_WC : v1.r;
+  const V3 r0 = v3(p0[0], p0[1], p0[2]), r1 = v3(p1[0], p1[1], p1[2]);
 
   for (int base = 0; base < n1; base += 32) {
-    const int k1 = base + lane;
+    const int i1 = base + lane;
+    const int k1 = i1 < n1 ? (list1 ? list1[i1] : i1) : 0;
     double d = 1e9;
-    if (k1 < n1 && !(job.v1_owner_a && job.v1_owner_a[k1] >= 0) && !(job.v1_owner_b && job.v1_owner_b[k1] >= 0)) {
+    if (i1 < n1 && !(job.v1_owner_a && job.v1_owner_a[k1] >= 0) && !(job.v1_owner_b && job.v1_owner_b[k1] >= 0)) {
       unsigned r[kDescWords];
       load_desc(v1.desc, k1, r);
       d = (double)hamming384(q, r);
@@ -951,21 +968,21 @@ match_stereo_kernel(const StereoJob* __restrict__ jobs, double hammingThreshold)
       const int src = __ffs(pending) - 1;
       pending &= pending - 1;
       const double dc = __shfl_sync(0xffffffffu, d, src);
-      const int kc = base + src;
+      const int kc = __shfl_sync(0xffffffffu, k1, src);
       if (!(dc < distances)) continue;
       if (!v0.bp_valid[k0]) continue;
       if (!v1.bp_valid[kc]) continue;
       const double sigma = MOTION ? side_size(v0, k0) / v0.f * 0.125
                                   : fmax(side_size(v0, k0) / v0.f, side_size(v1, kc) / v1.f) * 0.125;
-      const V3 e0_W = normalized(matvec(v0.C, v3(v0.e_C[3 * k0], v0.e_C[3 * k0 + 1], v0.e_C[3 * k0 + 2])));
-      const V3 e1_W = normalized(matvec(v1.C, v3(v1.e_C[3 * kc], v1.e_C[3 * kc + 1], v1.e_C[3 * kc + 2])));
+      const V3 e0_W = normalized(matvec(C0, v3(v0.e_C[3 * k0], v0.e_C[3 * k0 + 1], v0.e_C[3 * k0 + 2])));
+      const V3 e1_W = normalized(matvec(C1, v3(v1.e_C[3 * kc], v1.e_C[3 * kc + 1], v1.e_C[3 * kc + 2])));
       if (MOTION && dot(e0_W, e1_W) < 0.5) continue;
       bool isValid = false, isParallel = false;
       const V3 hp = triangulate_fast(r0, e0_W, r1, e1_W, cos(2.6 * sigma), cos(6.0 * sigma), isValid, isParallel);
       if (MOTION && !isValid) continue;
       // T_WC.inverse() * hp_W with w = 1: C^T * p + (-(C^T * r)) * 1; z / w compared with 0.1
-      const V3 t0 = matTvec(v0.C, r0), t1 = matTvec(v1.C, r1);
-      const V3 c0 = matTvec(v0.C, hp), c1 = matTvec(v1.C, hp);
+      const V3 t0 = matTvec(C0, r0), t1 = matTvec(C1, r1);
+      const V3 c0 = matTvec(C0, hp), c1 = matTvec(C1, hp);
       const double z0 = c0.z + (-t0.z) * 1.0, z1 = c1.z + (-t1.z) * 1.0;
       const double minDepth = MOTION ? 0.2 : 0.1;
       if (z0 / 1.0 < minDepth) isValid = false;
@@ -1016,7 +1033,9 @@ __global__ void __launch_bounds__(256) match_uninitialised_kernel(const UninitJo
   const int k = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int nk = job.nk_dev ? min(*job.nk_dev, job.nk) : job.nk;
   if (k >= nk) return;
-  const int nm = job.nm_dev ? min(*job.nm_dev, job.nm) : job.nm;
+  // rows to sweep: all of the pool, or a precompacted ascending list (the rows of the non-3D landmarks)
+  const int* __restrict__ rowList = job.row_list;
+  const int nm = rowList ? min(*job.n_list_dev, job.nm) : (job.nm_dev ? min(*job.nm_dev, job.nm) : job.nm);
   const uint8_t* __restrict__ map = job.map;
   const int* __restrict__ owner = job.owner;
   const double* __restrict__ map_e_W = job.map_e_W;
@@ -1037,14 +1056,17 @@ __global__ void __launch_bounds__(256) match_uninitialised_kernel(const UninitJo
     if (job.kp_e_W) {
       e1_W = v3(job.kp_e_W[3 * k], job.kp_e_W[3 * k + 1], job.kp_e_W[3 * k + 2]);
     } else {   // T_WC1.C() * e1_C.normalized()
-      e1_W = matvec(job.C_WC, normalized(v3(job.e_C[3 * k], job.e_C[3 * k + 1], job.e_C[3 * k + 2])));
+      e1_W = matvec(job.pose_slot ? job.pose_slot->C_WC : job.C_WC,
+                    normalized(v3(job.e_C[3 * k], job.e_C[3 * k + 1], job.e_C[3 * k + 2])));
     }
-    const V3 rC = v3(a.r_WC[0], a.r_WC[1], a.r_WC[2]);
+    const double* __restrict__ rc = job.pose_slot ? job.pose_slot->r_WC : a.r_WC;
+    const V3 rC = v3(rc[0], rc[1], rc[2]);
     const int prev = job.previousOwner ? job.previousOwner[k] : -1;
     for (int base = 0; base < nm; base += 32) {
-      const int m = base + lane;
+      const int i = base + lane;
+      const int m = i < nm ? (rowList ? rowList[i] : i) : 0;
       double d = 1e9;
-      if (m < nm && !(job.is3d && job.is3d[owner[m]])) {
+      if (i < nm && !(!rowList && job.is3d && job.is3d[owner[m]])) {
         unsigned r[kDescWords];
         load_desc(map, m, r);
         d = (double)hamming384(q, r);
@@ -1054,7 +1076,7 @@ __global__ void __launch_bounds__(256) match_uninitialised_kernel(const UninitJo
         const int src = __ffs(pending) - 1;
         pending &= pending - 1;
         const double dc = __shfl_sync(0xffffffffu, d, src);
-        const int mc = base + src;
+        const int mc = __shfl_sync(0xffffffffu, m, src);
         if (!(dc < best)) continue;
         const int oc = owner[mc];
         if (oc == skipOwner) continue;  // "break" out of this landmark's descriptor loop happened earlier
@@ -1106,6 +1128,40 @@ __global__ void __launch_bounds__(256) match_uninitialised_kernel(const UninitJo
       atomicAdd(job.slice_ctrs + t, (unsigned long long)ctr);
     }
   }
+}
+
+// ordered compaction of a slot's keypoints without a landmark (one CTA per slot)
+__global__ void __launch_bounds__(1024) unmatched_lists_kernel(const UnmatchedArgs* __restrict__ args, int maxKp) {
+  const UnmatchedArgs& a = args[blockIdx.x];
+  __shared__ int s_warp[32];
+  __shared__ int s_base;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int nk = min(*a.nk_dev, maxKp);
+  int* __restrict__ list = a.list + (size_t)blockIdx.x * maxKp;
+  if (tid == 0) s_base = 0;
+  __syncthreads();
+  for (int k0 = 0; k0 < nk; k0 += 1024) {
+    const int k = k0 + tid;
+    const bool un = k < nk && !(a.owner_a && a.owner_a[k] >= 0) && !(a.owner_b && a.owner_b[k] >= 0);
+    const unsigned b = __ballot_sync(0xffffffffu, un);
+    if (lane == 0) s_warp[warp] = __popc(b);
+    __syncthreads();
+    int before = s_base;
+    for (int w = 0; w < warp; ++w) before += s_warp[w];
+    if (un) list[before + __popc(b & ((1u << lane) - 1u))] = k;
+    __syncthreads();
+    if (tid == 0) {
+      int t = 0;
+      for (int w = 0; w < 32; ++w) t += s_warp[w];
+      s_base += t;
+    }
+    __syncthreads();
+  }
+  if (tid == 0) a.count[blockIdx.x] = s_base;
+}
+
+void launch_unmatched_lists(const UnmatchedArgs* args, int n, int max_kp, cudaStream_t s) {
+  if (n > 0 && max_kp > 0) unmatched_lists_kernel<<<n, 1024, 0, s>>>(args, max_kp);
 }
 
 void launch_match_uninit_jobs(const UninitJob* jobs, int nJobs, int maxNk, cudaStream_t s) {

@@ -235,7 +235,8 @@ def rig_sequence(n_frames, n_cams, width, height, seed, step=(2, 1), disparity=2
     """images[c][f] (u8 H x W): camera c of frame f = master[f * step_y :, 48 + f * step_x - c * disparity :]."""
     mw = width + step[0] * (n_frames - 1) + disparity * (n_cams - 1) + 64
     mh = height + step[1] * (n_frames - 1)
-    master = dense_image(mw, mh, seed) if dense else scene_image(mw, mh, seed, rects=rects)
+    area = (mw * mh) / float(752 * 480)   # rectangle counts are quoted for a 752 x 480 canvas
+    master = dense_image(mw, mh, seed, rects=int(6000 * area)) if dense else scene_image(mw, mh, seed, rects=int(rects * area))
     x_base = 16 + disparity * (n_cams - 1)
     out = np.empty((n_cams, n_frames, height, width), np.uint8)
     for c in range(n_cams):
@@ -319,3 +320,75 @@ def plane_landmarks(views, Z0, fx, max_landmarks, seed, quality=(0.002, 1.0), un
               desc=np.concatenate([v["desc"] for v in views]).reshape(-1, 48),
               e_C=np.concatenate([v["e_C"] for v in views]).reshape(-1, 3))
     return vd, hp_W, q, obs_offset, np.asarray(obs_view, np.int32), np.asarray(obs_kp, np.int32)
+
+
+def _equidistant_distort(x, y, k):
+    k1, k2, k3, k4 = k
+    r = np.sqrt(x * x + y * y)
+    th = np.arctan(r)
+    th2 = th * th
+    poly = 1.0 + th2 * (k1 + th2 * (k2 + th2 * (k3 + th2 * k4)))
+    thd = th * poly
+    safe = np.where(r > 1e-8, r, 1.0)
+    s = np.where(r > 1e-8, thd / safe, 1.0)
+    # d(thd)/d(th) and ds/dr for the Jacobian
+    dthd = 1.0 + th2 * (3 * k1 + th2 * (5 * k2 + th2 * (7 * k3 + th2 * 9 * k4)))
+    ds = np.where(r > 1e-8, (dthd / (1.0 + r * r) * safe - thd) / (safe * safe), 0.0)
+    j00 = s + ds * x * x / safe
+    j01 = ds * x * y / safe
+    j11 = s + ds * y * y / safe
+    return s * x, s * y, j00, j01, j01, j11
+
+
+def camera_maps_equidistant(width, height, f, c, k):
+    """(rays float32 HxWx3, jacobians float32 HxWx6) for a pinhole + equidistant camera (Hilti22 config): the same
+    construction as camera_maps (PinholeCamera.hpp:172-200), an INPUT of the path to both the product and the oracle."""
+    fu, fv = f
+    cu, cv = c
+    u, v = np.meshgrid(np.arange(width, dtype=np.float64), np.arange(height, dtype=np.float64))
+    xd, yd = (u - cu) / fu, (v - cv) / fv
+    # undistort: theta_d = |(xd, yd)|, Newton on theta
+    rd = np.sqrt(xd * xd + yd * yd)
+    th = rd.copy()
+    k1, k2, k3, k4 = k
+    for _ in range(10):
+        th2 = th * th
+        fth = th * (1.0 + th2 * (k1 + th2 * (k2 + th2 * (k3 + th2 * k4)))) - rd
+        dfth = 1.0 + th2 * (3 * k1 + th2 * (5 * k2 + th2 * (7 * k3 + th2 * 9 * k4)))
+        th = th - fth / dfth
+    ok = (th > -1e-9) & (th < 1.5)
+    th = np.clip(th, 0.0, 1.5)
+    scale = np.where(rd > 1e-8, np.tan(th) / np.where(rd > 1e-8, rd, 1.0), 1.0)
+    x, y = xd * scale, yd * scale
+    n = np.sqrt(x * x + y * y + 1.0)
+    rays = np.stack([x / n, y / n, 1.0 / n], -1)
+    rays[~ok] = 0.0
+    X, Y, Z = rays[..., 0], rays[..., 1], np.where(ok, rays[..., 2], 1.0)
+    _, _, d00, d01, d10, d11 = _equidistant_distort(X / Z, Y / Z, k)
+    rz, rz2 = 1.0 / Z, 1.0 / (Z * Z)
+    J = np.stack([fu * d00 * rz, fu * d01 * rz, -fu * (X * d00 + Y * d01) * rz2,
+                  fv * d10 * rz, fv * d11 * rz, -fv * (X * d10 + Y * d11) * rz2], -1)
+    J[~ok] = 0.0
+    return np.ascontiguousarray(rays, np.float32), np.ascontiguousarray(J, np.float32)
+
+
+# frontend configurations of the shipped okvis2.yaml files (SURVEY.md Appendix B) with one camera model per rig:
+# every camera of a synthetic rig uses the first camera's intrinsics so that the constant disparity between its images
+# is geometrically consistent (rig_sequence / rig_poses)
+RIGS = dict(
+    euroc=dict(cfg=EUROC, width=752, height=480, n_cams=2, distortion="radialtangential",
+               f=EUROC["cams"][0]["f"], c=EUROC["cams"][0]["c"], k=EUROC["cams"][0]["d"], max_kp=768),
+    # config/hilti22/okvis2.yaml:3-74 (cam0)
+    hilti=dict(cfg=HILTI, width=720, height=540, n_cams=5, distortion="equidistant",
+               f=(351.31400364193297, 351.4911744656785), c=(367.8522793375995, 253.8402144980996),
+               k=(-0.03696737352869157, -0.008917880497032812, 0.008912969593422046, -0.0037685977496087313), max_kp=768),
+    # config/rsD455/okvis2.yaml (848x480 as BASELINE.json names the shape; intrinsics scaled from the 640x480 file)
+    d455=dict(cfg=D455, width=848, height=480, n_cams=2, distortion="radialtangential",
+              f=(425.0, 424.2), c=(423.1, 238.7), k=(-0.05, 0.06, 3e-4, -2e-4), max_kp=2560),
+)
+
+
+def rig_maps(rig):
+    if rig["distortion"] == "equidistant":
+        return camera_maps_equidistant(rig["width"], rig["height"], rig["f"], rig["c"], rig["k"])
+    return camera_maps(rig["width"], rig["height"], rig["f"], rig["c"], rig["k"])

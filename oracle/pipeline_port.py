@@ -9,9 +9,12 @@ Frontend::dataAssociationAndInitialization, okvis_frontend/src/Frontend.cpp:204-
   matchMotionStereo worker, matchStereo loops                            (oracle/port/matchers.cc)
 Only tests/, __graft_entry__.smoke() and bench.py's CPU legs may import this module.
 """
+import threading
+
 import numpy as np
 
 import refbind
+from refbind import _ptr
 
 
 def normalized_rows(e):
@@ -40,7 +43,7 @@ class CpuPipeline:
         return ext.describe(img, kp)
 
     def landmark_stage(self, cam, pose, kp, desc, e_C, valid, pool_args, threshold=60.0, slices=4, uninitialised=True,
-                       use_imu=True, loop_closure=False):
+                       use_imu=True, loop_closure=False, threaded=False):
         """pose = (C_WC [3,3], r_WC [3], T_CW [12]); pool_args = (views, hp_W, quality, obs_offset, obs_view, obs_kp).
         Returns dict(prep=..., a14=(dist, owner, ctrs, errs), a15=(dist, owner, hps, hw, ctrs))."""
         C_WC, r_WC, T_CW = pose
@@ -51,19 +54,67 @@ class CpuPipeline:
         prep = self.port.prepare_landmarks(views, hp_W, quality, vis, off, ov, ok, r_WC, cam.fu + cam.fv, loop_closure)
         kp_xy = np.stack([kp["x"], kp["y"]], 1).astype(np.float64)
         n = len(kp)
-        a14 = self.port.match_to_map(desc, kp_xy, np.ones(n, np.uint8), prep["pool"], prep["owner"], proj, prep["is3d"],
-                                     repr_thr * repr_thr, threshold, slices)
+        a14 = self._a14(desc, kp_xy, prep, proj, repr_thr * repr_thr, threshold, slices, threaded)
         out = dict(proj=proj, visible=vis, prep=prep, a14=a14)
         if uninitialised:
             e_W = rotate_rows(C_WC, normalized_rows(e_C))
             use = (np.asarray(valid) != 0) & (a14[1] < 0)
             # rows of 3D landmarks are skipped by the uninitialised matcher (Frontend.cpp:1878-1880)
-            sel = prep["is3d"][prep["owner"]] == 0
-            rows = np.nonzero(sel)[0]
-            out["a15"] = self.port.match_to_map_uninitialised(
-                desc, e_W, use.astype(np.uint8), None, prep["pool"][rows], prep["owner"][rows], prep["e_W"][rows],
-                prep["r_W"][rows], len(hp_W), r_WC, f, threshold, slices)
+            rows = np.nonzero(prep["is3d"][prep["owner"]] == 0)[0]
+            out["a15"] = self._a15(desc, e_W, use.astype(np.uint8), prep, rows, len(hp_W), r_WC, f, threshold, slices,
+                                   threaded)
         return out
+
+    @staticmethod
+    def _run(fn, slices, threaded):
+        """The reference's num_matching_threads workers (Frontend.cpp:1519-1536, 1631-1645) or the slices in turn."""
+        if threaded and slices > 1:
+            th = [threading.Thread(target=fn, args=(t,)) for t in range(slices)]
+            for x in th:
+                x.start()
+            for x in th:
+                x.join()
+        else:
+            for t in range(slices):
+                fn(t)
+
+    def _a14(self, desc, kp_xy, prep, proj, thresh_sq, threshold, slices, threaded):
+        q = np.ascontiguousarray(desc, np.uint8).reshape(-1, 48)
+        kp = np.ascontiguousarray(kp_xy, np.float64)
+        m = np.ascontiguousarray(prep["pool"], np.uint8).reshape(-1, 48)
+        pr = np.ascontiguousarray(proj, np.float64)
+        L = len(pr)
+        row_start = np.searchsorted(prep["owner"].astype(np.int64), np.arange(L + 1)).astype(np.int32)
+        i3 = np.ascontiguousarray(prep["is3d"], np.uint8)
+        nk = len(q)
+        us = np.ones(nk, np.uint8)
+        dist = np.full(nk, float(threshold), np.float64)
+        ids = np.full(nk, -1, np.int32)
+        ctrs = np.zeros(slices, np.uint64)
+        errs = np.zeros(slices, np.float64)
+        self._run(lambda t: self.port.L.port_match_to_map_thread(
+            t, slices, _ptr(q), _ptr(kp), _ptr(us), nk, _ptr(m), _ptr(row_start), L, _ptr(pr), _ptr(i3), float(thresh_sq),
+            _ptr(dist), _ptr(ids), _ptr(ctrs), _ptr(errs)), slices, threaded)
+        return dist, ids, ctrs, errs
+
+    def _a15(self, desc, e_W, use, prep, rows, L, r_WC, focal, threshold, slices, threaded):
+        q = np.ascontiguousarray(desc, np.uint8).reshape(-1, 48)
+        ke = np.ascontiguousarray(e_W, np.float64)
+        m = np.ascontiguousarray(prep["pool"][rows])
+        me = np.ascontiguousarray(prep["e_W"][rows])
+        mr = np.ascontiguousarray(prep["r_W"][rows])
+        rc = np.ascontiguousarray(r_WC, np.float64)
+        row_start = np.searchsorted(prep["owner"][rows].astype(np.int64), np.arange(L + 1)).astype(np.int32)
+        nk = len(q)
+        dist = np.full(nk, float(threshold), np.float64)
+        ids = np.full(nk, -1, np.int32)
+        hps = np.zeros((nk, 4), np.float64)
+        hw = np.zeros(nk, np.uint8)
+        ctrs = np.zeros(slices, np.uint64)
+        self._run(lambda t: self.port.L.port_match_uninit_thread(
+            t, slices, _ptr(q), _ptr(ke), _ptr(use), None, nk, _ptr(m), _ptr(row_start), int(L), _ptr(me), _ptr(mr),
+            _ptr(rc), float(focal), _ptr(dist), _ptr(ids), _ptr(hps), _ptr(hw), _ptr(ctrs)), slices, threaded)
+        return dist, ids, hps, hw, ctrs
 
     def stereo(self, v0, v1, threshold=60.0):
         return self.port.match_stereo(v0, v1, threshold)

@@ -38,13 +38,14 @@ def _worker(rank, world, port, nq, nm, out_dir):
     m[5] = m[nm - 3] = q[0]            # a tie across shards: the lower global row must win
     lo, hi = sh.map_row_shard(rank, world, nm)
     local = refbind.Port().hamming_best(q, m[lo:hi], 60, index_offset=lo)
-    merged = sh.merge_best(torch.from_numpy(local.view(np.int64)), world, dist)
+    # ordered int64 keys (INT64_MAX = no match), as okc_match_sets_ordered leaves them: one all-reduce(min)
+    merged = sh.merge_best(torch.from_numpy(sh.to_ordered(local)), world, dist)
     # frames: every frame of the pool is visited exactly once per sweep over all ranks
     mine = [sh.frame_of(k, rank, world, 12) for k in range(12 // world)]
     allf = [None] * world
     dist.all_gather_object(allf, mine)
     if rank == 0:
-        np.save(os.path.join(out_dir, "merged.npy"), merged.numpy().view(np.uint64))
+        np.save(os.path.join(out_dir, "merged.npy"), sh.from_ordered(merged.numpy()))
         np.save(os.path.join(out_dir, "frames.npy"), np.sort(np.concatenate(allf)))
     dist.barrier()
     dist.destroy_process_group()
@@ -62,6 +63,22 @@ def test_sharded_sweep_and_frames_gloo(world, tmp_path, port, syn, mod):
     assert want[0] == 5
     if 12 % world == 0:
         assert np.array_equal(np.load(os.path.join(str(tmp_path), "frames.npy")), np.arange(12))
+
+
+def test_camera_shards_cover_every_camera_and_split_adjacent_pairs(mod):
+    """configs[2]: camera c -> rank c mod N; with N >= 2 the two cameras of an adjacent pair never share a rank, so
+    every matchStereo pair is served by the view exchange."""
+    import importlib
+    sh = importlib.import_module("okvis2x_b200.sharding")
+    for world in (1, 2, 4, 5, 8):
+        shards = [sh.camera_shard(r, world, 5) for r in range(world)]
+        assert sorted(c for s in shards for c in s) == list(range(5))
+        if world >= 2:
+            for c in range(4):
+                assert c % world != (c + 1) % world
+    k = np.array([5, 0xFFFFFFFFFFFFFFFF, (60 << 32) | 7], np.uint64)
+    assert np.array_equal(sh.from_ordered(sh.to_ordered(k)), k)
+    assert sh.to_ordered(k)[1] == sh.ORDERED_NO_MATCH and np.all(np.diff(np.sort(sh.to_ordered(k))) > 0)
 
 
 def test_shard_bounds(mod):

@@ -8,7 +8,7 @@ syn = importlib.import_module("okvis2x_b200.synthetic")
 name = sys.argv[1] if len(sys.argv) > 1 else "euroc-noise"
 B = int(sys.argv[2]) if len(sys.argv) > 2 else 1
 cases = {"euroc-scene": (syn.EUROC, lambda s: syn.scene_image(752, 480, 1 + s)),
-         "euroc-noise": (syn.EUROC, lambda s: syn.noise_image(752, 480, 2 + s)),
+         "euroc-noise": (syn.EUROC, lambda s: syn.noise_image(752, 480, 2 + s)), "euroc-dense": (syn.EUROC, lambda s: syn.dense_image(752, 480, 8 + s)), "d455-dense": (syn.D455, lambda s: syn.dense_image(848, 480, 8 + s)),
          "d455-scene": (syn.D455, lambda s: syn.scene_image(848, 480, 8 + s, rects=1500)),
          "d455-noise": (syn.D455, lambda s: syn.noise_image(848, 480, 9 + s))}
 cfg, gen = cases[name]
