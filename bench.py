@@ -318,6 +318,7 @@ class GpuConfig:
         self.n_frames = conf["frames"]
         self.pool = None
         self.kfs = []
+        self.gather = None
 
     # ---- the world: keyframes through the product itself (their data also goes to the CPU arm as input) ----
     def build_world(self):
@@ -392,7 +393,7 @@ class GpuConfig:
             poses[j * F:(j + 1) * F] = self.pose_rows[f, c]
         return imgs, poses
 
-    def enqueue(self, b, imgs, poses, device):
+    def enqueue(self, b, imgs, poses, device, k0=0):
         b.enqueue_addrs(imgs, device)
         if self.conf["landmarks"] or self.pairs or self.jobs:
             b.set_poses(poses)
@@ -402,6 +403,8 @@ class GpuConfig:
             b.match_stereo_enqueue(self.pairs, HAMMING)
         if self.jobs:
             b.match_motion_enqueue(self.jobs, HAMMING, only_unmatched=True)
+        if self.gather is not None:   # camera-sharded multiframe: view exchange + cross-camera matchStereo
+            self.gather.step(self.batches.index(b), k0)
 
     def launches_per_batch(self):
         n = 6                                        # harris_nms, order, select, sub-pixel, border_filter, describe
@@ -409,15 +412,17 @@ class GpuConfig:
         if self.conf["landmarks"]:
             n += 4 + 3 + 1                           # prepare (4), bin + match + stats, uninitialised
         n += 1 if self.pairs else 0
-        n += 1 if self.jobs else 0
+        n += 2 if self.jobs else 0                   # unmatched lists, matchMotionStereo
+        n += 2 if self.gather is not None else 0     # pack views, cross-camera matchStereo (+ one NCCL all-gather)
         return n
 
     def read(self, b):
         r = b.read_all(self.outs.get(id(b)))
         self.outs[id(b)] = r
         s = None
-        if self.conf["landmarks"] or self.pairs or self.jobs:
-            s = b.read_stages(self.stage_outs.get(id(b)), len(self.pairs), len(self.jobs), self.conf["landmarks"])
+        n_pairs = len(self.gather.slot0) if self.gather is not None else len(self.pairs)
+        if self.conf["landmarks"] or n_pairs or self.jobs:
+            s = b.read_stages(self.stage_outs.get(id(b)), n_pairs, len(self.jobs), self.conf["landmarks"])
             self.stage_outs[id(b)] = s
         return r, s
 
@@ -432,7 +437,7 @@ class GpuConfig:
     def run_value(self, n_steps, n_warm, barrier, max_over_ranks):
         torch, F, D = self.torch, self.F, self.D
         for j in range(n_warm):
-            self.enqueue(self.batches[j % D], *self.slot_args(j * F, True), True)
+            self.enqueue(self.batches[j % D], *self.slot_args(j * F, True), True, j * F)
         work = [self.slot_args((n_warm + j) * F, True) for j in range(n_steps)]
         barrier()
         start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -442,7 +447,7 @@ class GpuConfig:
             s.wait_event(start)
         t_host = time.perf_counter()
         for j, (imgs, poses) in enumerate(work):
-            self.enqueue(self.batches[j % D], imgs, poses, True)
+            self.enqueue(self.batches[j % D], imgs, poses, True, (n_warm + j) * F)
         t_host = time.perf_counter() - t_host
         for s in self.streams:
             e = torch.cuda.Event()
@@ -467,7 +472,7 @@ class GpuConfig:
                 r = self.read(pb)
                 if keep is not None:
                     keep(pk, r)
-            self.enqueue(b, *self.slot_args(k, False), False)
+            self.enqueue(b, *self.slot_args(k, False), False, k)
             pending.append((b, k))
         for pb, pk in pending:
             pb.finish()
@@ -506,7 +511,7 @@ class GpuConfig:
         b0.kernel_timing(True)
         acc, cnt = {}, 0
         for j in range(n_batches):
-            self.enqueue(b0, *self.slot_args(j * self.F, True), True)
+            self.enqueue(b0, *self.slot_args(j * self.F, True), True, j * self.F)
             for name, ms in b0.kernel_times():
                 acc[name] = acc.get(name, 0.0) + ms
             cnt += 1
@@ -517,6 +522,7 @@ class GpuConfig:
     def latency(self, n=60):
         """One multiframe alone through the C ABI with host buffers: wall clock around enqueue / finish / read."""
         F_save, batches_save, streams_save, pairs_save, jobs_save = self.F, self.batches, self.streams, self.pairs, self.jobs
+        gather_save, self.gather = self.gather, None   # (the latency of this rank's cameras alone)
         self.F = 1
         self.setup_single()
         lat = []
@@ -529,6 +535,7 @@ class GpuConfig:
             lat.append((time.perf_counter() - t1) * 1e3)
         self.batches[0].close()
         self.F, self.batches, self.streams, self.pairs, self.jobs = F_save, batches_save, streams_save, pairs_save, jobs_save
+        self.gather = gather_save
         self.outs, self.stage_outs = {}, {}
         return float(np.median(lat[10:]))
 
@@ -693,12 +700,15 @@ def run_frame_config(args, name, mod, syn, torch, dist, ctx, rank, world, headli
         # when the timed region begins; it keeps sampling every 100 ms until after the e2e arm
         sampler_box.append(ClockSampler(local))
     F = gc.F
-    gather = None
+    without_exchange = None
     if shard_cameras and gc.conf["stereo"]:
+        # first the step without the exchange (how the per-camera work scales), then the complete config
+        ms0, _ = gc.run_value(min(n_steps, 20), n_warm, barrier, max_over_ranks)
+        without_exchange = {"value": round(min(n_steps, 20) * F / (ms0 * 1e-3), 2), "unit": "frames/s",
+                            "what": "the per-camera stages only (no view exchange, no cross-camera matchStereo)"}
         sh = __import__("importlib").import_module("okvis2x_b200.sharding")
-        gather = sh.CameraGather(mod, torch, dist, ctx, gc, HAMMING)
+        gc.gather = sh.CameraGather(mod, torch, dist, ctx, gc, HAMMING)
     dev_ms, t_host = gc.run_value(n_steps, n_warm, barrier, max_over_ranks)
-    gather_ms = gather.time_steps(min(n_steps, 20), barrier, max_over_ranks) if gather else None
     e2e_ms, e2e_runs = gc.time_e2e(n_steps, n_warm, barrier, max_over_ranks)
     barrier()
     clocks = sampler_box.pop().stop() if (headline and rank == 0 and sampler_box) else None
@@ -741,8 +751,9 @@ def run_frame_config(args, name, mod, syn, torch, dist, ctx, rank, world, headli
         "gpu_launches": gc.launches_per_batch() * n_steps,
         "roofline": roofline,
     }
-    if gather_ms is not None:
-        out["camera_gather"] = gather_ms
+    if without_exchange is not None:
+        out["without_exchange"] = without_exchange
+        out["exchange"] = gc.gather.describe()
     if lat is not None:
         out["single_multiframe_latency_ms"] = round(lat, 4)
     if clocks is not None:

@@ -180,6 +180,11 @@ void launch_back_project_slots(const Slot* slots, int n, int max_kp, cudaStream_
 // array counts as "none matched"), ascending, into list[slot * max_kp ..] with their number in count[slot]
 struct UnmatchedArgs { const int* owner_a; const int* owner_b; const int* nk_dev; int* list; int* count; };
 void launch_unmatched_lists(const UnmatchedArgs* args, int n, int max_kp, cudaStream_t s);
+// exchange records of camera-sharded multiframes: count | keypoints | descriptors | back-projections | validity of the
+// slots listed in slot_index[0 .. n), live rows only, into consecutive records of record_bytes
+struct PackLayout { size_t off_n, off_kp, off_desc, off_eC, off_valid, bytes; };
+void launch_pack_views(const Slot* slots, const int* slot_index, int n, int max_kp, PackLayout layout, uint8_t* dst,
+                       cudaStream_t s);
 
 // Landmark preparation of Frontend::matchToMap for one camera image (Frontend.cpp:1376-1500): inputs of the shared
 // landmark pool, the pose of this image, and where its pool is packed.

@@ -1160,6 +1160,33 @@ __global__ void __launch_bounds__(1024) unmatched_lists_kernel(const UnmatchedAr
   if (tid == 0) a.count[blockIdx.x] = s_base;
 }
 
+// One CTA per view: the live rows of a slot's keypoints / descriptors / back-projections / validity flags and their
+// count into an exchange record (16-byte moves; every section of the record and of the arena is 16-byte aligned).
+__global__ void __launch_bounds__(256) pack_views_kernel(const Slot* __restrict__ slots, const int* __restrict__ slotIndex,
+                                                        int maxKp, PackLayout L, uint8_t* __restrict__ dst) {
+  const Slot& slot = slots[slotIndex[blockIdx.x]];
+  uint8_t* __restrict__ rec = dst + L.bytes * (size_t)blockIdx.x;
+  const int n = min(slot.counters[2], maxKp);
+  if (threadIdx.x == 0) *reinterpret_cast<int*>(rec + L.off_n) = n;
+  auto copy = [&](const void* src, size_t off, size_t bytes) {
+    const uint4* s4 = static_cast<const uint4*>(src);
+    uint4* d4 = reinterpret_cast<uint4*>(rec + off);
+    const size_t q = (bytes + 15) / 16;
+    for (size_t i = threadIdx.x; i < q; i += blockDim.x) d4[i] = s4[i];
+  };
+  copy(slot.kp_desc, L.off_kp, (size_t)n * sizeof(okc_keypoint));
+  copy(slot.desc, L.off_desc, (size_t)n * 48);
+  // (the back-projection arrays of a slot are only 8- / 1-byte aligned for an arbitrary max_keypoints)
+  double* __restrict__ de = reinterpret_cast<double*>(rec + L.off_eC);
+  for (int i = threadIdx.x; i < 3 * n; i += blockDim.x) de[i] = slot.e_C[i];
+  for (int i = threadIdx.x; i < n; i += blockDim.x) rec[L.off_valid + i] = slot.bp_valid[i];
+}
+
+void launch_pack_views(const Slot* slots, const int* slot_index, int n, int max_kp, PackLayout layout, uint8_t* dst,
+                       cudaStream_t s) {
+  if (n > 0) pack_views_kernel<<<n, 256, 0, s>>>(slots, slot_index, max_kp, layout, dst);
+}
+
 void launch_unmatched_lists(const UnmatchedArgs* args, int n, int max_kp, cudaStream_t s) {
   if (n > 0 && max_kp > 0) unmatched_lists_kernel<<<n, 1024, 0, s>>>(args, max_kp);
 }

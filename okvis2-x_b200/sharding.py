@@ -168,34 +168,7 @@ class CameraGather:
         if self.slot0:
             b.match_stereo_packed_enqueue(self.slot0, self.recv[bi].ptr, self.index1, poses1, self.f1, self.hamming)
 
-    def time_steps(self, n_steps, barrier, max_over_ranks):
-        """Device time of K full steps (detect .. matchToMap + exchange + cross-camera matchStereo), inputs resident."""
-        gc, torch = self.gc, self.torch
-        F, D = gc.F, gc.D
-        for j in range(3):
-            gc.enqueue(gc.batches[j % D], *gc.slot_args(j * F, True), True)
-            self.step(j % D, j * F)
-        barrier()
-        start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        cur = torch.cuda.current_stream()
-        start.record(cur)
-        for s in gc.streams:
-            s.wait_event(start)
-        for j in range(n_steps):
-            gc.enqueue(gc.batches[j % D], *gc.slot_args((3 + j) * F, True), True)
-            self.step(j % D, (3 + j) * F)
-        for s in gc.streams:
-            e = torch.cuda.Event()
-            e.record(s)
-            cur.wait_event(e)
-        end.record(cur)
-        end.synchronize()
-        ms = max_over_ranks(start.elapsed_time(end))
-        barrier()
-        pairs = 0
-        for b in gc.batches:
-            b.finish()
-        return {"value": round(n_steps * F / (ms * 1e-3), 2), "unit": "frames/s", "ms_per_step": round(ms / n_steps, 5),
-                "what": "the same step plus the view exchange (one NCCL all-gather of %d bytes per rank and step) and "
-                        "matchStereo of every adjacent camera pair on the rank that owns the first camera"
-                        % (self.rec * self.per_rank * F), "steps": n_steps}
+    def describe(self):
+        return {"collective": "one NCCL all_gather_into_tensor per step on the batch's stream",
+                "bytes_per_rank_and_step": self.rec * self.per_rank * self.gc.F,
+                "pairs_matched_on_this_rank_per_step": len(self.slot0)}

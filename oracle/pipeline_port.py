@@ -17,19 +17,28 @@ import refbind
 from refbind import _ptr
 
 
-def normalized_rows(e):
-    """Eigen's v.normalized() row-wise: v / sqrt((x x + y y) + z z), element-wise division."""
+def normalized_rows(e, variant=0):
+    """Eigen's v.normalized() row-wise: v / sqrt((x x + y y) + z z), element-wise division. variant: the
+    PORT_EIGEN_VARIANT bits of the sensitivity builds (bit 0: other dot order, bit 1: multiply by the reciprocal)."""
     e = np.asarray(e, np.float64).reshape(-1, 3)
-    n2 = (e[:, 0] * e[:, 0] + e[:, 1] * e[:, 1]) + e[:, 2] * e[:, 2]
+    if variant & 1:
+        n2 = e[:, 0] * e[:, 0] + (e[:, 1] * e[:, 1] + e[:, 2] * e[:, 2])
+    else:
+        n2 = (e[:, 0] * e[:, 0] + e[:, 1] * e[:, 1]) + e[:, 2] * e[:, 2]
     out = e.copy()
     nz = n2 > 0.0
-    out[nz] = e[nz] / np.sqrt(n2[nz])[:, None]
+    if variant & 2:
+        out[nz] = e[nz] * (1.0 / np.sqrt(n2[nz]))[:, None]
+    else:
+        out[nz] = e[nz] / np.sqrt(n2[nz])[:, None]
     return out
 
 
-def rotate_rows(C, e):
-    """C * e per row with Eigen's 3x3 * 3x1 order ((c0 x + c1 y) + c2 z)."""
+def rotate_rows(C, e, variant=0):
+    """C * e per row with Eigen's 3x3 * 3x1 order ((c0 x + c1 y) + c2 z); variant bit 3: c0 x + (c1 y + c2 z)."""
     C = np.asarray(C, np.float64).reshape(3, 3)
+    if variant & 8:
+        return np.stack([C[r, 0] * e[:, 0] + (C[r, 1] * e[:, 1] + C[r, 2] * e[:, 2]) for r in range(3)], 1)
     return np.stack([(C[r, 0] * e[:, 0] + C[r, 1] * e[:, 1]) + C[r, 2] * e[:, 2] for r in range(3)], 1)
 
 
@@ -57,7 +66,8 @@ class CpuPipeline:
         a14 = self._a14(desc, kp_xy, prep, proj, repr_thr * repr_thr, threshold, slices, threaded)
         out = dict(proj=proj, visible=vis, prep=prep, a14=a14)
         if uninitialised:
-            e_W = rotate_rows(C_WC, normalized_rows(e_C))
+            vb = getattr(self.port, "variant", 0)
+            e_W = rotate_rows(C_WC, normalized_rows(e_C, vb), vb)
             use = (np.asarray(valid) != 0) & (a14[1] < 0)
             # rows of 3D landmarks are skipped by the uninitialised matcher (Frontend.cpp:1878-1880)
             rows = np.nonzero(prep["is3d"][prep["owner"]] == 0)[0]

@@ -232,16 +232,25 @@ extern "C" void port_keyframe_overlap(int n_views, const int* width, const int* 
 // Landmark preparation of Frontend::matchToMap, second half (okvis_frontend/src/Frontend.cpp:1409-1500): restated
 // with plain doubles in the reference's statement order. Eigen pieces: normalized() = v / sqrt(v.v) (v.v > 0),
 // 3-vector sums (x0 y0 + x1 y1) + x2 y2.
+#ifndef PORT_EIGEN_VARIANT
+#define PORT_EIGEN_VARIANT 0   // see matchers.cc
+#endif
 namespace {
 struct V3 { double x, y, z; };
 inline V3 sub(V3 a, V3 b) { return {a.x - b.x, a.y - b.y, a.z - b.z}; }
 inline V3 mul(double s, V3 a) { return {s * a.x, s * a.y, s * a.z}; }
-inline double dot(V3 a, V3 b) { return (a.x * b.x + a.y * b.y) + a.z * b.z; }
+inline double dot(V3 a, V3 b) {
+  return (PORT_EIGEN_VARIANT & 1) ? a.x * b.x + (a.y * b.y + a.z * b.z) : (a.x * b.x + a.y * b.y) + a.z * b.z;
+}
 inline double norm(V3 a) { return std::sqrt(dot(a, a)); }
 inline V3 normalized(V3 a) {
   const double n2 = dot(a, a);
   if (n2 > 0.0) {
     const double n = std::sqrt(n2);
+    if (PORT_EIGEN_VARIANT & 2) {
+      const double r = 1.0 / n;
+      return {a.x * r, a.y * r, a.z * r};
+    }
     return {a.x / n, a.y / n, a.z / n};
   }
   return a;
@@ -317,7 +326,8 @@ extern "C" int port_prepare_landmarks(int n_views, const double* C_WC, const dou
       const V3 en = normalized(V3{e_C[3 * src], e_C[3 * src + 1], e_C[3 * src + 2]});
       const double* C = C_WC + 9 * v;
       for (int c = 0; c < 3; ++c) {
-        e_W[3 * nm + c] = (C[3 * c] * en.x + C[3 * c + 1] * en.y) + C[3 * c + 2] * en.z;
+        e_W[3 * nm + c] = (PORT_EIGEN_VARIANT & 8) ? C[3 * c] * en.x + (C[3 * c + 1] * en.y + C[3 * c + 2] * en.z)
+                                                   : (C[3 * c] * en.x + C[3 * c + 1] * en.y) + C[3 * c + 2] * en.z;
         r_Wout[3 * nm + c] = r_WC[3 * v + c];
       }
     }

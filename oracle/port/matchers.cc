@@ -13,6 +13,14 @@
 #include <thread>
 #include <vector>
 
+// PORT_EIGEN_VARIANT (sensitivity builds, tests/test_eigen_order_sensitivity.py): the other evaluation orders an Eigen
+// version / flag set could produce for the same expressions. bit 0: 3-vector dot as x0 y0 + (x1 y1 + x2 y2) (Eigen's
+// non-vectorised unrolled redux); bit 1: normalized() as v * (1 / sqrt(v.v)); bit 2: 2x2 inverse by per-element
+// division instead of a multiplication with 1 / det; bit 3: 3x3 * 3x1 rows as c0 x + (c1 y + c2 z).
+#ifndef PORT_EIGEN_VARIANT
+#define PORT_EIGEN_VARIANT 0
+#endif
+
 namespace {
 
 // brisk::Hamming::PopcntofXORed(a, b, 3) (external/brisk/include/brisk/internal/hamming-inl.h:95-144):
@@ -33,24 +41,31 @@ inline V3 mk(double x, double y, double z) { return V3{x, y, z}; }
 inline V3 add(V3 a, V3 b) { return mk(a.x + b.x, a.y + b.y, a.z + b.z); }
 inline V3 sub(V3 a, V3 b) { return mk(a.x - b.x, a.y - b.y, a.z - b.z); }
 inline V3 scale(double s, V3 a) { return mk(s * a.x, s * a.y, s * a.z); }
-inline double dot(V3 a, V3 b) { return (a.x * b.x + a.y * b.y) + a.z * b.z; }
+inline double dot(V3 a, V3 b) {
+  return (PORT_EIGEN_VARIANT & 1) ? a.x * b.x + (a.y * b.y + a.z * b.z) : (a.x * b.x + a.y * b.y) + a.z * b.z;
+}
 inline V3 cross(V3 a, V3 b) { return mk(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x); }
 inline double norm(V3 a) { return std::sqrt(dot(a, a)); }
 inline V3 normalized(V3 a) {
   const double z = dot(a, a);
   if (z > 0.0) {
     const double n = std::sqrt(z);
+    if (PORT_EIGEN_VARIANT & 2) {
+      const double r = 1.0 / n;
+      return mk(a.x * r, a.y * r, a.z * r);
+    }
     return mk(a.x / n, a.y / n, a.z / n);
   }
   return a;
 }
+inline double row3(double c0, double c1, double c2, V3 v) {
+  return (PORT_EIGEN_VARIANT & 8) ? c0 * v.x + (c1 * v.y + c2 * v.z) : (c0 * v.x + c1 * v.y) + c2 * v.z;
+}
 inline V3 matvec(const double* C, V3 v) {
-  return mk((C[0] * v.x + C[1] * v.y) + C[2] * v.z, (C[3] * v.x + C[4] * v.y) + C[5] * v.z,
-            (C[6] * v.x + C[7] * v.y) + C[8] * v.z);
+  return mk(row3(C[0], C[1], C[2], v), row3(C[3], C[4], C[5], v), row3(C[6], C[7], C[8], v));
 }
 inline V3 matTvec(const double* C, V3 v) {
-  return mk((C[0] * v.x + C[3] * v.y) + C[6] * v.z, (C[1] * v.x + C[4] * v.y) + C[7] * v.z,
-            (C[2] * v.x + C[5] * v.y) + C[8] * v.z);
+  return mk(row3(C[0], C[3], C[6], v), row3(C[1], C[4], C[7], v), row3(C[2], C[5], C[8], v));
 }
 
 // triangulation::triangulateFast, okvis_frontend/src/stereo_triangulation.cpp:30-111
@@ -65,7 +80,9 @@ V3 triangulateFast(V3 p1, V3 e1, V3 p2, V3 e2, double sigma, bool& isValid, bool
   double l0 = 0.0, l1 = 0.0;
   if (invertible) {
     const double invdet = 1.0 / det;
-    const double i00 = A11 * invdet, i01 = -A01 * invdet, i10 = -A10 * invdet, i11 = A00 * invdet;
+    const bool byDiv = (PORT_EIGEN_VARIANT & 4) != 0;
+    const double i00 = byDiv ? A11 / det : A11 * invdet, i01 = byDiv ? -A01 / det : -A01 * invdet,
+                 i10 = byDiv ? -A10 / det : -A10 * invdet, i11 = byDiv ? A00 / det : A00 * invdet;
     l0 = i00 * b0 + i01 * b1;
     l1 = i10 * b0 + i11 * b1;
   }

@@ -206,10 +206,13 @@ class PortStereoView(C.Structure):
 class Port:
     """Our CPU restatement of the Frontend.cpp matchers (oracle/port/matchers.cc)."""
 
-    def __init__(self):
-        if not os.path.exists(PORT_PATH):
-            raise FileNotFoundError(PORT_PATH + " missing: run `make -C oracle port`")
-        L = self.L = C.CDLL(PORT_PATH)
+    def __init__(self, variant=0):
+        """variant != 0: a sensitivity build (PORT_EIGEN_VARIANT bits, oracle/port/matchers.cc)."""
+        self.variant = int(variant)
+        path = PORT_PATH if not variant else PORT_PATH.replace(".so", "_v%d.so" % variant)
+        if not os.path.exists(path):
+            raise FileNotFoundError(path + " missing: run `make -C oracle port variants`")
+        L = self.L = C.CDLL(path)
         L.port_hamming.argtypes = [_vp, _vp]
         L.port_hamming.restype = C.c_uint32
         L.port_hamming_best.argtypes = [_vp, _i, _vp, C.c_int64, C.c_uint32, _u64, _vp, _i]
