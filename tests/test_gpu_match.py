@@ -253,75 +253,104 @@ def test_frame_pipeline_equals_separate_calls(mod, ctx, port, syn):
     cam.close()
 
 
-@pytest.mark.parametrize("on_device", [False, True])
-def test_batch_equals_single_calls(on_device, mod, ctx, port, syn):
-    """A batch of 6 slots (3 stereo frames of a sequence: cam0, cam1, cam0, ...) == the single-camera entry points,
-    slot by slot, with and without the map match; host (pageable / pinned) and device inputs."""
+def _rig_case(mod, ctx, syn, rigname, n_frames):
+    """Cameras, images (slot k = camera k % n_cams of frame k // n_cams), detection parameters and slice count of a
+    shipped configuration: EuRoC keeps its two calibrations and the sparse stereo sequence; Hilti (5 equidistant
+    cameras, 720x540) and D455 (848x480, budget 2500, 3 slices) use dense scenes that saturate their budgets."""
+    rig = syn.RIGS[rigname]
+    cfg, W, H, n_cams = rig["cfg"], rig["width"], rig["height"], rig["n_cams"]
+    cams, focals = [], []
+    if rigname == "euroc":
+        for c in syn.EUROC["cams"]:
+            rays, jac = syn.camera_maps(W, H, c["f"], c["c"], c["d"])
+            cams.append(mod.Camera(ctx, W, H, rays, jac, focal=c["f"][0], max_keypoints=rig["max_kp"]))
+            focals.append(0.5 * (c["f"][0] + c["f"][1]))
+        left, right, shift = syn.stereo_sequence(n_frames, W, H, seed=2)
+        imgs = [(left, right)[k % 2][k // 2] for k in range(2 * n_frames)]
+    else:
+        rays, jac = syn.rig_maps(rig)
+        for _ in range(n_cams):
+            cams.append(mod.Camera(ctx, W, H, rays, jac, focal=rig["f"][0], max_keypoints=rig["max_kp"]))
+            focals.append(0.5 * (rig["f"][0] + rig["f"][1]))
+        seq = syn.rig_sequence(n_frames, n_cams, W, H, seed=4, dense=True)
+        imgs = [seq[k % n_cams, k // n_cams] for k in range(n_cams * n_frames)]
+        shift = np.asarray([(2 * f, f) for f in range(n_frames)], np.int64)
+    det = (cfg["radius"], 0, cfg["abs_threshold"], cfg["max_kpt"])
+    return dict(cams=cams, imgs=imgs, shift=shift, det=det, slices=cfg["slices"], n_cams=n_cams, W=W, H=H,
+                gates=[(3.0 + f * 0.06) ** 2 for f in focals], landmarks=3 * cfg["max_kpt"] // 2 + 450)
+
+
+@pytest.mark.parametrize("rigname,on_device", [("euroc", False), ("euroc", True), ("hilti", False), ("hilti", True),
+                                               ("d455", False), ("d455", True)])
+def test_batch_equals_single_calls(rigname, on_device, mod, ctx, port, syn):
+    """A batch of slots (frames of a sequence: cam0, cam1, ..., cam0, ...) == the single-camera entry points, slot by
+    slot, with and without the map match; host (pageable / pinned) and device inputs; at the shapes, detection
+    parameters and slice counts of the EuRoC, Hilti22 and D455 configurations."""
     import torch
-    W, H = 752, 480
-    cams = []
-    for c in syn.EUROC["cams"]:
-        rays, jac = syn.camera_maps(W, H, c["f"], c["c"], c["d"])
-        cams.append(mod.Camera(ctx, W, H, rays, jac, focal=c["f"][0], max_keypoints=768))
-    left, right, shift = syn.stereo_sequence(3, W, H, seed=2)
-    imgs = [left[0], right[0], left[1], right[1], left[2], right[2]]
-    slot_cams = [cams[k % 2] for k in range(6)]
-    dirs = [(0.05, 0.99, 0.1) if k % 2 == 0 else (-0.02, 0.98, 0.15) for k in range(6)]
-    single = [slot_cams[k].detect_describe(imgs[k], 38.0, 0, 150.0, 700, direction=dirs[k]) for k in range(6)]
+    n_frames = 3 if rigname != "hilti" else 2
+    rc = _rig_case(mod, ctx, syn, rigname, n_frames)
+    cams, imgs, det, S, nc = rc["cams"], rc["imgs"], rc["det"], rc["slices"], rc["n_cams"]
+    ns = len(imgs)
+    slot_cams = [cams[k % nc] for k in range(ns)]
+    dirs = [(0.05, 0.99, 0.1) if k % 2 == 0 else (-0.02, 0.98, 0.15) for k in range(ns)]
+    single = [slot_cams[k].detect_describe(imgs[k], *det, direction=dirs[k]) for k in range(ns)]
+    if rigname != "euroc":     # dense scenes: the uniformity radius (Hilti: 50 px) or  (D455: 30 px) binds, not the threshold
+        assert min(len(s[0]) for s in single) > (400 if rigname == "hilti" else 1000), [len(s[0]) for s in single]
     wins_h = []
-    for cam_i in range(2):
+    for cam_i in range(nc):
         kp, desc = single[cam_i]
         kp_xy = np.stack([kp["x"], kp["y"]], 1).astype(np.float64)
-        wins_h.append(syn.sequence_window(desc, kp_xy, shift, 1500, 7 + cam_i, W, H))
+        wins_h.append(syn.sequence_window(desc, kp_xy, rc["shift"], rc["landmarks"], 7 + cam_i, rc["W"], rc["H"]))
     wins = [mod.MapWindow(ctx, r, o, p.shape[1]) for r, o, p in wins_h]
-    gates = [(3.0 + 0.5 * (c["f"][0] + c["f"][1]) * 0.06) ** 2 for c in syn.EUROC["cams"]]
+    gates = rc["gates"]
     batch = mod.Batch(ctx, slot_cams)
     keep = []
     if on_device:
         d = [torch.from_numpy(i).cuda() for i in imgs]
-        dp = [torch.from_numpy(np.ascontiguousarray(wins_h[k % 2][2][k // 2])).cuda() for k in range(6)]
+        dp = [torch.from_numpy(np.ascontiguousarray(wins_h[k % nc][2][k // nc])).cuda() for k in range(ns)]
         torch.cuda.synchronize()
         keep = [d, dp]
         img_arg, proj_arg = [t.data_ptr() for t in d], [t.data_ptr() for t in dp]
     else:
-        pinned = torch.from_numpy(imgs[1]).pin_memory()   # one pinned source among pageable ones
+        pinned = torch.from_numpy(np.ascontiguousarray(imgs[1])).pin_memory()   # one pinned source among pageable ones
         keep = [pinned]
         img_arg = [imgs[0], pinned.data_ptr()] + imgs[2:]
-        proj_arg = [np.ascontiguousarray(wins_h[k % 2][2][k // 2]) for k in range(6)]
+        proj_arg = [np.ascontiguousarray(wins_h[k % nc][2][k // nc]) for k in range(ns)]
     # without the map match
-    batch.enqueue(img_arg, 38.0, 0, 150.0, 700, dirs, images_on_device=on_device)
+    batch.enqueue(img_arg, *det, dirs, images_on_device=on_device)
     batch.finish()
-    for k in range(6):
+    for k in range(ns):
         kp, desc = batch.slot_frame(k)
         assert kp.tobytes() == single[k][0].tobytes() and np.array_equal(desc, single[k][1]), k
     # with it, twice (idempotent handles)
     for rep in range(2):
-        batch.enqueue(img_arg, 38.0, 0, 150.0, 700, dirs, images_on_device=on_device,
-                      windows=[wins[k % 2] for k in range(6)], proj=proj_arg, gates=[gates[k % 2] for k in range(6)],
-                      proj_on_device=on_device)
+        batch.enqueue(img_arg, *det, dirs, images_on_device=on_device,
+                      windows=[wins[k % nc] for k in range(ns)], proj=proj_arg, gates=[gates[k % nc] for k in range(ns)],
+                      proj_on_device=on_device, num_slices=S)
         batch.finish()
-        for k in range(6):
+        for k in range(ns):
             kp, desc = batch.slot_frame(k)
             assert kp.tobytes() == single[k][0].tobytes() and np.array_equal(desc, single[k][1]), k
             bd, bo, ctrs, errs = batch.slot_matches(k, len(kp))
-            rows, owner, proj = wins_h[k % 2]
+            rows, owner, proj = wins_h[k % nc]
             kp_xy = np.stack([kp["x"], kp["y"]], 1).astype(np.float64)
-            pd, po, pc, pe = port.match_to_map(desc, kp_xy, np.ones(len(kp), np.uint8), rows, owner, proj[k // 2], None,
-                                               gates[k % 2], 60.0, 4)
-            assert np.array_equal(bd, pd) and np.array_equal(bo, po) and np.array_equal(ctrs, pc), k
-            assert errs.tobytes() == pe.tobytes(), k
-            if k < 2:
+            pd, po, pc, pe = port.match_to_map(desc, kp_xy, np.ones(len(kp), np.uint8), rows, owner, proj[k // nc], None,
+                                               gates[k % nc], 60.0, S)
+            assert np.array_equal(bd, pd) and np.array_equal(bo, po) and np.array_equal(ctrs[:S], pc), k
+            assert errs[:S].tobytes() == pe.tobytes(), k
+            if k < nc:
                 assert (bo >= 0).sum() > 100
         allr = batch.read_all()
-        for k in range(6):
+        for k in range(ns):
             n = int(allr["n"][k])
             kp, desc = batch.slot_frame(k)
             bd, bo, ctrs, errs = batch.slot_matches(k, n)
             assert n == len(kp) and allr["kp"][k, :n].tobytes() == kp.tobytes()
             assert np.array_equal(allr["desc"][k, :n], desc) and np.array_equal(allr["dist"][k, :n], bd)
             assert np.array_equal(allr["owner"][k, :n], bo)
-            assert np.array_equal(allr["ctrs"].reshape(-1)[k * 4:k * 4 + 4], ctrs)
-            assert allr["errs"].reshape(-1)[k * 4:k * 4 + 4].tobytes() == errs.tobytes()
+            stride = S
+            assert np.array_equal(allr["ctrs"].reshape(-1)[k * stride:k * stride + len(ctrs)], ctrs)
+            assert allr["errs"].reshape(-1)[k * stride:k * stride + len(errs)].tobytes() == errs.tobytes()
     batch.close()
     for w in wins:
         w.close()
@@ -394,19 +423,24 @@ def test_match_motion_stereo_vs_port(mod, ctx, port, syn):
         assert (want[1] >= 0).sum() > 50 and np.all(want[1][use0 == 0] == -1)
 
 
-def test_binned_map_match_equals_tile_scan(mod, ctx, port, syn):
+@pytest.mark.parametrize("rigname", ["euroc", "hilti", "d455"])
+def test_binned_map_match_equals_tile_scan(rigname, mod, ctx, port, syn):
     """Frame-pipeline map match through spatial bins of the projections (default) against the scan of every row and
     against the port: ordinary window, a non-finite projection (bins unusable -> ordered full scan), projections far
     outside the image, a tiny gate (grid coarsened to the cell cap), and one keypoint with more hits than the per-warp
-    hit buffer holds (100 copies of its descriptor projected onto it)."""
-    W, H = 752, 480
-    cam = mod.Camera(ctx, W, H, max_keypoints=768)
-    img = syn.scene_image(W, H, 1)
-    kp, desc = cam.detect_describe(img, 38.0, 0, 150.0, 700)
+    hit buffer holds (100 copies of its descriptor projected onto it). At the image shape, detection parameters,
+    gate and slice count of each shipped configuration (D455: 2500 keypoints against 4200 landmarks, 3 slices)."""
+    rig = syn.RIGS[rigname]
+    cfg, W, H = rig["cfg"], rig["width"], rig["height"]
+    det = (cfg["radius"], 0, cfg["abs_threshold"], cfg["max_kpt"])
+    S = cfg["slices"]
+    cam = mod.Camera(ctx, W, H, max_keypoints=rig["max_kp"])
+    img = syn.scene_image(W, H, 1) if rigname == "euroc" else syn.dense_image(W, H, 1)
+    kp, desc = cam.detect_describe(img, *det)
     kp_xy = np.stack([kp["x"], kp["y"]], 1).astype(np.float64)
-    win = syn.map_window(desc, kp_xy, 1500, 7, W, H)
+    win = syn.map_window(desc, kp_xy, 3 * cfg["max_kpt"] // 2 + 450, 7, W, H)
     rows, owner, proj = win["map"], win["owner"].astype(np.int32), win["proj"].copy()
-    gate = (3.0 + 458.0 * 0.06) ** 2
+    gate = (3.0 + 0.5 * (rig["f"][0] + rig["f"][1]) * 0.06) ** 2
 
     def variants():
         yield "plain", rows, owner, proj, gate
@@ -436,14 +470,14 @@ def test_binned_map_match_equals_tile_scan(mod, ctx, port, syn):
             for binned in (0, 1):
                 mod.lib().okc_debug_set_match_binned(binned)
                 batch = mod.Batch(ctx, [cam])
-                batch.enqueue([img], 38.0, 0, 150.0, 700, [(0.0, 1.0, 0.0)], windows=[w], proj=[np.ascontiguousarray(p)],
-                              gates=[g], num_slices=4)
+                batch.enqueue([img], *det, [(0.0, 1.0, 0.0)], windows=[w], proj=[np.ascontiguousarray(p)],
+                              gates=[g], num_slices=S)
                 batch.finish()
                 k2, d2 = batch.slot_frame(0)
                 assert k2.tobytes() == kp.tobytes() and np.array_equal(d2, desc)
                 res.append(batch.slot_matches(0, len(kp)))
                 batch.close()
-            pd, po, pc, pe = port.match_to_map(desc, kp_xy, np.ones(len(kp), np.uint8), r, o, p, None, g, 60.0, 4)
+            pd, po, pc, pe = port.match_to_map(desc, kp_xy, np.ones(len(kp), np.uint8), r, o, p, None, g, 60.0, S)
             for bd, bo, ctrs, errs in res:
                 assert np.array_equal(bd, pd) and np.array_equal(bo, po), name
                 assert np.array_equal(ctrs, pc), name
