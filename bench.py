@@ -57,7 +57,7 @@ HEADLINE = "euroc_sequence"
 NUM_LANDMARKS = 2000
 
 
-def parse_args():
+def parse_args(argv=None):
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=300, help="batches of --frames-per-batch frames (headline config)")
@@ -69,7 +69,8 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--only", default="", help="comma-separated config names (default: all; the headline always runs)")
     ap.add_argument("--sparse", action="store_true", help="round-1 scene (400 large rectangles) instead of the dense one")
-    return ap.parse_args()
+    ap.add_argument("--no-graph", action="store_true", help="plain kernel launches instead of CUDA-graph replay of the chains")
+    return ap.parse_args(argv)
 
 
 def peaks():
@@ -363,6 +364,7 @@ class GpuConfig:
         self.batches = [mod.Batch(self.ctx, [self.cams[s // F] for s in range(nc * F)]) for _ in range(self.D)]
         for b in self.batches:
             b.configure(*self.det, [DIRECTION] * (nc * F))
+            b.set_graph(not self.args.no_graph)
         self.d_img = [torch.from_numpy(wl["images"][c]).cuda() for c in self.cams_here]
         self.h_img = [torch.from_numpy(wl["images"][c]).pin_memory() for c in self.cams_here]
         self.img_stride = wl["W"] * wl["H"]
@@ -519,12 +521,26 @@ class GpuConfig:
         b0.finish()
         return {n: v / cnt for n, v in acc.items()}
 
-    def latency(self, n=60):
+    def host_enqueue_us(self, n=40):
+        """Host time of enqueueing one batch (every stage call; device-resident inputs, the batch idle before each
+        enqueue so that nothing blocks): median wall clock."""
+        b = self.batches[0]
+        t = []
+        for i in range(n + 5):
+            imgs, poses = self.slot_args(i * self.F, True)
+            t0 = time.perf_counter()
+            self.enqueue(b, imgs, poses, True, i * self.F)
+            t.append((time.perf_counter() - t0) * 1e6)
+            b.finish()
+        return float(np.median(t[5:]))
+
+    def latency(self, n=60, graph=True):
         """One multiframe alone through the C ABI with host buffers: wall clock around enqueue / finish / read."""
         F_save, batches_save, streams_save, pairs_save, jobs_save = self.F, self.batches, self.streams, self.pairs, self.jobs
         gather_save, self.gather = self.gather, None   # (the latency of this rank's cameras alone)
         self.F = 1
         self.setup_single()
+        self.batches[0].set_graph(graph)
         lat = []
         for i in range(n + 10):
             imgs, poses = self.slot_args(i, False)
@@ -712,7 +728,9 @@ def run_frame_config(args, name, mod, syn, torch, dist, ctx, rank, world, headli
     e2e_ms, e2e_runs = gc.time_e2e(n_steps, n_warm, barrier, max_over_ranks)
     barrier()
     clocks = sampler_box.pop().stop() if (headline and rank == 0 and sampler_box) else None
-    lat = gc.latency() if (rank == 0 or world == 1) else None
+    lat = gc.latency(graph=not args.no_graph) if (rank == 0 or world == 1) else None
+    lat_plain = gc.latency(graph=False) if (rank == 0 or world == 1) and not args.no_graph else None
+    t_enq = gc.host_enqueue_us() if gc.gather is None else None
     kms = gc.kernel_times(min(n_steps, 20))
     frames_per_step = F * (1 if shard_cameras else world)
     total = n_steps * frames_per_step
@@ -743,7 +761,8 @@ def run_frame_config(args, name, mod, syn, torch, dist, ctx, rank, world, headli
         "frames_in_pool": gc.n_frames, "keypoints_per_image": round(K, 1), "landmarks": L,
         "sharding": ("cameras over ranks (camera c -> rank c mod N), keypoints + descriptors all-gathered for matchStereo"
                      if shard_cameras else "frames round-robin over ranks"),
-        "host_enqueue_us_per_batch": round(t_host * 1e6, 1),
+        "host_enqueue_us_per_batch": round(t_enq, 1) if t_enq is not None else None,
+        "launch_chains": "plain launches" if args.no_graph else "CUDA graphs (one per chain, captured at the second use)",
         "e2e": {"value": round(total / (e2e_ms * 1e-3), 2), "unit": "frames/s", "ms_per_step": round(e2e_ms / n_steps, 5),
                 "h2d_bytes_per_step": h2d * F, "d2h_bytes_per_step": d2h * F,
                 "timed": "median of %d runs of K steps (ms: %s)" % (E2E_REPEATS, ", ".join("%.1f" % v for v in e2e_runs)),
@@ -756,6 +775,8 @@ def run_frame_config(args, name, mod, syn, torch, dist, ctx, rank, world, headli
         out["exchange"] = gc.gather.describe()
     if lat is not None:
         out["single_multiframe_latency_ms"] = round(lat, 4)
+        if lat_plain is not None:
+            out["single_multiframe_latency_ms_plain_launches"] = round(lat_plain, 4)
     if clocks is not None:
         out["clocks"] = clocks
     st = dict(gc=gc, wl=wl, F=F)
@@ -908,6 +929,7 @@ def run_b200(args, rank, world):
         extra["matcher_sweep_inputs"] = sweeps
     extra["single_frame_latency"] = {
         "ms": head.get("single_multiframe_latency_ms"),
+        "ms_plain_launches": head.get("single_multiframe_latency_ms_plain_launches"),
         "what": "one stereo frame alone (batch of 2 images, nothing else in flight): host images in, keypoints + "
                 "descriptors + matches out, wall clock around enqueue/finish/read, median of 60"}
     if "cpu_baseline" in head and head["cpu_baseline"].get("value"):

@@ -335,6 +335,11 @@ typedef struct okc_batch okc_batch;
 int okc_batch_create(okc_context* ctx, okc_camera* const* cams, int n_slots, okc_batch** batch);
 int okc_batch_destroy(okc_batch* batch);
 int okc_batch_size(const okc_batch* batch);
+/* The kernel chains of okc_batch_enqueue and okc_batch_match_landmarks_enqueue are replayed as CUDA graphs (captured
+ * the second time a configuration is seen; one cudaGraphLaunch per chain instead of a launch per kernel): everything
+ * that changes per frame reaches the kernels through device-resident tables. enable = 0 turns that off (plain
+ * launches); the results are identical. Default: on. */
+int okc_batch_set_graph(okc_batch* batch, int enable);
 /* images[i]: u8[H*W]; host memory (pinned buffers are DMA'd in place, pageable ones are staged) or, with
  * images_on_device != 0, device memory. xp: n_slots describe parameter blocks (extraction direction per slot).
  * windows == NULL: no map match; else windows[i] (may be NULL per slot), proj_xy[i] = double[2*num_landmarks] in

@@ -31,7 +31,7 @@ EXPORTS = [
     "okc_match_to_map", "okc_match_stereo", "okc_match_to_map_uninitialised", "okc_match_motion_stereo",
     "okc_detect_describe_enqueue_device", "okc_map_window_create", "okc_map_window_destroy",
     "okc_camera_match_to_map_enqueue", "okc_camera_frame_finish", "okc_camera_stream", "okc_debug_kernel_timing",
-    "okc_debug_kernel_times", "okc_batch_create", "okc_batch_destroy", "okc_batch_size", "okc_batch_enqueue",
+    "okc_debug_kernel_times", "okc_batch_create", "okc_batch_destroy", "okc_batch_size", "okc_batch_set_graph", "okc_batch_enqueue",
     "okc_batch_finish", "okc_batch_slot_frame", "okc_batch_slot_matches", "okc_batch_read_all", "okc_batch_stream",
     "okc_debug_batch_kernel_timing", "okc_debug_batch_kernel_times",
     "okc_camera_set_geometry", "okc_batch_set_poses", "okc_batch_slot_back_projections", "okc_landmark_pool_create",
@@ -182,6 +182,7 @@ def lib():
         L.okc_batch_create.argtypes = [vp, vp, i, C.POINTER(vp)]
         L.okc_batch_destroy.argtypes = [vp]
         L.okc_batch_size.argtypes = [vp]
+        L.okc_batch_set_graph.argtypes = [vp, C.c_int]
         L.okc_batch_enqueue.argtypes = [vp, vp, i, C.POINTER(DetectParams), vp, vp, vp, i, vp, d, i]
         L.okc_batch_read_all.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp]
         L.okc_batch_finish.argtypes = [vp]
@@ -820,6 +821,10 @@ class Batch:
         _check(lib().okc_batch_slot_frame(self.h, slot, _p(kp), self.max_kp, C.byref(n), _p(desc)),
                "okc_batch_slot_frame")
         return kp[:n.value], desc[:n.value]
+
+    def set_graph(self, enable):
+        """CUDA-graph replay of the launch chains (default on); the results do not depend on it."""
+        _check(lib().okc_batch_set_graph(self.h, int(bool(enable))), "okc_batch_set_graph")
 
     def slot_matches(self, slot, nk):
         bd = np.empty(self.max_kp, np.float64)

@@ -242,6 +242,7 @@ struct DetectArgs {
   // keypoint coordinates of the layer: x = kp_scale * ((x + dx) + kp_offset) (scale-space-layer-inl.h:412-419)
   double kp_scale = 1.0, kp_offset = 0.0;
   int octave = 0;          // _layerNumber / 2
+  bool dense_scores = false;   // write the whole score map (scale-space layers, okc_debug_scores), not only the maxima
 };
 
 struct DescribeArgs {

@@ -45,7 +45,13 @@ constexpr int kStripWords = 4;
 
 __host__ __device__ inline int harris_strips(int W) { return (W + kStripCols - 1) / kStripCols; }
 
-template <bool ALIGNED>
+//
+// Score map: the only scores anything reads back are those of the NMS survivors (order_candidates_kernel builds its
+// sort keys from them); the 3x3 ring of the sub-pixel fit is recomputed from the pixels for the few hundred KEPT
+// points (harris_ring_scores). So by default (DENSE = false) a lane stores the score of a survivor only - 4 bytes
+// per candidate instead of 4 bytes per pixel, which was 2/3 of the kernel's DRAM traffic. DENSE = true writes the
+// whole map: scale-space layers (scale_nms_kernel interpolates in the neighbouring layers' maps) and okc_debug_scores.
+template <bool ALIGNED, bool DENSE>
 __global__ void __launch_bounds__(32 * kHarrisWarps) harris_nms_kernel(const Slot* __restrict__ slots, int W, int H,
                                                          int absThreshold, int rowsPerWarp) {
   const Slot& slot = slots[blockIdx.z];
@@ -157,7 +163,7 @@ __global__ void __launch_bounds__(32 * kHarrisWarps) harris_nms_kernel(const Slo
       yyH[P][c] = yy2[c];
       scH[P][c] = v & rowKeep & colKeep[c];
     }
-    if (emit && p >= q0 && p < q1 && x < W) {
+    if (DENSE && emit && p >= q0 && p < q1 && x < W) {
       int32_t* dst = scores + (size_t)p * W + x;
       if (ALIGNED) {
         *reinterpret_cast<int4*>(dst) = make_int4(scH[P][0], scH[P][1], scH[P][2], scH[P][3]);
@@ -195,6 +201,11 @@ __global__ void __launch_bounds__(32 * kHarrisWarps) harris_nms_kernel(const Slo
             nib |= (isMax ? 1u : 0u) << c;
           }
           nib &= colBits;
+          if (!DENSE && nib) {
+#pragma unroll
+            for (int c = 0; c < 4; ++c)
+              if (nib & (1u << c)) scores[(size_t)q * W + x + c] = scH[B][c];
+          }
         }
         v = nib << (4 * (lane & 7));
         v |= __shfl_xor_sync(0xffffffffu, v, 1);
@@ -247,8 +258,9 @@ void launch_harris_nms(const Slot* slots, int n, const DetectArgs& a, cudaStream
   const int rows = harris_rows_per_warp(a.width, a.height, n);
   const int chunks = (a.height + rows - 1) / rows;
   dim3 grid(harris_strips(a.width), (chunks + kHarrisWarps - 1) / kHarrisWarps, n);
-  if (aligned) harris_nms_kernel<true><<<grid, 32 * kHarrisWarps, 0, s>>>(slots, a.width, a.height, a.abs_threshold, rows);
-  else harris_nms_kernel<false><<<grid, 32 * kHarrisWarps, 0, s>>>(slots, a.width, a.height, a.abs_threshold, rows);
+  auto k = a.dense_scores ? (aligned ? harris_nms_kernel<true, true> : harris_nms_kernel<false, true>)
+                          : (aligned ? harris_nms_kernel<true, false> : harris_nms_kernel<false, false>);
+  k<<<grid, 32 * kHarrisWarps, 0, s>>>(slots, a.width, a.height, a.abs_threshold, rows);
 }
 
 size_t harris_bitmap_words(int W, int H) { return (size_t)H * harris_strips(W) * kStripWords; }
@@ -810,13 +822,69 @@ __device__ void subpixel2d(double s_0_0, double s_0_1, double s_0_2, double s_1_
   }
 }
 
+// The 3x3 block of Harris scores around pixel (u, v), recomputed from the image with the arithmetic of
+// harris_nms_kernel (same integers, so the same values): 7x7 pixels -> 5x5 gradient products -> 3x5 horizontally
+// smoothed -> 3x3 scores; 0 outside rows 2..H-3 / columns 2..W-3 as in the map. out[3 * (dv + 1) + (du + 1)].
+__device__ __forceinline__ void harris_ring_scores(const uint8_t* __restrict__ img, int W, int H, int u, int v,
+                                                   int out[9]) {
+  int h[7][5], sm[7][5];   // per pixel row v-3..v+3, columns u-2..u+2: I[x-1] - I[x+1] and 8 * (3, 10, 3)-sums
+#pragma unroll
+  for (int pr = 0; pr < 7; ++pr) {
+    const int r = v - 3 + pr;
+    const int rr = r < 0 ? 0 : (r >= H ? H - 1 : r);
+    int px[7];
+#pragma unroll
+    for (int i = 0; i < 7; ++i) {
+      const int xx = u - 3 + i;
+      px[i] = (xx >= 0 && xx < W) ? (int)__ldg(img + (size_t)rr * W + xx) : 0;
+    }
+#pragma unroll
+    for (int i = 0; i < 5; ++i) {
+      h[pr][i] = px[i] - px[i + 2];
+      sm[pr][i] = 24 * (px[i] + px[i + 2]) + 80 * px[i + 1];
+    }
+  }
+  int sxx[5][3], sxy[5][3], syy[5][3];   // horizontally smoothed products: gradient rows v-2..v+2, columns u-1..u+1
+#pragma unroll
+  for (int g = 0; g < 5; ++g) {          // gradient row v-2+g reads pixel rows g, g+1, g+2 of the 7
+    int pxx[5], pxy[5], pyy[5];
+#pragma unroll
+    for (int i = 0; i < 5; ++i) {
+      const int dx = 24 * (h[g][i] + h[g + 2][i]) + 80 * h[g + 1][i];
+      const int dy = sm[g][i] - sm[g + 2][i];
+      pxx[i] = (dx * dx) >> 16;
+      pxy[i] = (dx * dy) >> 16;
+      pyy[i] = (dy * dy) >> 16;
+    }
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+      sxx[g][i] = pxx[i] + 2 * pxx[i + 1] + pxx[i + 2];
+      sxy[g][i] = pxy[i] + 2 * pxy[i + 1] + pxy[i + 2];
+      syy[g][i] = pyy[i] + 2 * pyy[i + 1] + pyy[i + 2];
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 3; ++j) {
+    const int y = v - 1 + j;
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+      const int x = u - 1 + i;
+      const int a = (sxx[j][i] + 2 * sxx[j + 1][i] + sxx[j + 2][i]) >> 4;
+      const int b = (syy[j][i] + 2 * syy[j + 1][i] + syy[j + 2][i]) >> 4;
+      const int d = (sxy[j][i] + 2 * sxy[j + 1][i] + sxy[j + 2][i]) >> 4;
+      const int t = (a + b) >> 1;
+      const int sc = a * b - d * d - (int)((unsigned)(t * t) / 5u);
+      out[3 * j + i] = (y >= 2 && y <= H - 3 && x >= 2 && x <= W - 3) ? sc : 0;
+    }
+  }
+}
+
 template <bool kOccInSmem>
 __global__ void __launch_bounds__(kSelThreads, 1)
 select_keypoints_kernel(const Slot* __restrict__ slots, const float* __restrict__ lut_global, int W, int H,
                         float scaling, unsigned long long maxKpt, int maxOut, int smemBytes, double kpScale,
                         double kpOffset, int octave) {
   const Slot& slot = slots[blockIdx.x];
-  const int32_t* __restrict__ scores = slot.scores;
   uint64_t* __restrict__ cand = slot.cand;
   int* __restrict__ counters = slot.counters;
   uint8_t* __restrict__ occ_global = slot.occupancy;
@@ -948,10 +1016,11 @@ select_keypoints_kernel(const Slot* __restrict__ slots, const float* __restrict_
     const int score = cand_score(key);
     const uint32_t raster = (uint32_t)key;
     const int v = raster / W, u = raster - v * W;
-    const int32_t* c = scores + (size_t)v * W + u;
+    int c[9];
+    harris_ring_scores(slot.image, W, H, u, v, c);
     float dx, dy;
-    subpixel2d((double)c[-W - 1], (double)c[-W], (double)c[-W + 1], (double)c[-1], (double)c[0], (double)c[1],
-               (double)c[W - 1], (double)c[W], (double)c[W + 1], dx, dy);
+    subpixel2d((double)c[0], (double)c[1], (double)c[2], (double)c[3], (double)c[4], (double)c[5], (double)c[6],
+               (double)c[7], (double)c[8], dx, dy);
     okc_keypoint kp;
     // _scale * ((it->x + delta_x) + _offset): (float + float) widened, the rest in double, narrowed on assignment
     kp.x = (float)(kpScale * ((double)((float)u + dx) + kpOffset));
@@ -1442,7 +1511,7 @@ select_keypoints_wave_kernel(const Slot* __restrict__ slots, const float* __rest
 // Sub-pixel refinement of the kept candidates -> cv::KeyPoint (scale-space-layer-inl.h:394-420), after the selection
 // kernel: FP64 work for 700-2 500 points that spreads over the GPU instead of running on the selection CTA's one SM.
 __global__ void __launch_bounds__(128)
-subpixel_kernel(const Slot* __restrict__ slots, int W, double kpScale, double kpOffset, int octave) {
+subpixel_kernel(const Slot* __restrict__ slots, int W, int H, double kpScale, double kpOffset, int octave) {
   const Slot& slot = slots[blockIdx.y];
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= slot.counters[1]) return;
@@ -1450,10 +1519,11 @@ subpixel_kernel(const Slot* __restrict__ slots, int W, double kpScale, double kp
   const int score = cand_score(key);
   const uint32_t raster = (uint32_t)key;
   const int v = raster / W, u = raster - v * W;
-  const int32_t* c = slot.scores + (size_t)v * W + u;
+  int c[9];
+  harris_ring_scores(slot.image, W, H, u, v, c);
   float dx, dy;
-  subpixel2d((double)c[-W - 1], (double)c[-W], (double)c[-W + 1], (double)c[-1], (double)c[0], (double)c[1],
-             (double)c[W - 1], (double)c[W], (double)c[W + 1], dx, dy);
+  subpixel2d((double)c[0], (double)c[1], (double)c[2], (double)c[3], (double)c[4], (double)c[5], (double)c[6],
+             (double)c[7], (double)c[8], dx, dy);
   okc_keypoint kp;
   // _scale * ((it->x + delta_x) + _offset): (float + float) widened, the rest in double, narrowed on assignment
   kp.x = (float)(kpScale * ((double)((float)u + dx) + kpOffset));
@@ -1517,7 +1587,8 @@ void launch_select_keypoints(const Slot* slots, int n, const float* lut, const D
     const size_t wlBytes = wlFixed + (size_t)blkCap * kWlCap * sizeof(unsigned short);
     select_keypoints_wave_kernel<<<n, kWlThreads, wlBytes, s>>>(slots, lut, a.width, a.height, a.scaling, a.max_kpt,
                                                                a.max_out, shift, nbxP, nbinsP, blkCap, lbW, lbH);
-    subpixel_kernel<<<dim3((a.max_out + 127) / 128, n), 128, 0, s>>>(slots, a.width, a.kp_scale, a.kp_offset, a.octave);
+    subpixel_kernel<<<dim3((a.max_out + 127) / 128, n), 128, 0, s>>>(slots, a.width, a.height, a.kp_scale,
+                                                                     a.kp_offset, a.octave);
     return;
   }
   // only as much dynamic shared memory as the occupancy image needs; the global fallback when it does not fit

@@ -1021,18 +1021,65 @@ void launch_match_stereo_jobs(const StereoJob* jobs, int nJobs, int max0, bool m
 // ----------------------------------------------------------------------------------------------
 // D. 3D-2D matching of uninitialised landmarks, Frontend::matchToMapByThreadUnitialised (Frontend.cpp:1830-1956)
 // ----------------------------------------------------------------------------------------------
-// One warp per keypoint, rows in landmark-major order. A row that beats the running best must pass, in this order:
+// Rows in landmark-major order. A row that beats the running best must pass, in this order:
 // the epipolar-plane / divergence test unless the rays are (nearly) parallel (:1907-1917), triangulateFast valid
 // (:1922-1927), >= 0.2 m from both centres (:1930-1936). Loop-closure rule (:1941-1944): an accepted row of the
 // keypoint's previous landmark only counts and ends that landmark's rows for this keypoint. hps_W is overwritten
 // only by non-parallel accepts (stale value kept otherwise, :1946-1951).
+//
+// Work layout: a CTA takes a chunk of 8 * Q consecutive keypoints, compacts those that take part (most keypoints of
+// a tracked frame already have a landmark from matchToMapByThread) and gives every warp Q of them. A warp loads a
+// tile of 32 rows ONCE (one row per lane, in registers) and compares it with its Q queries: the row sweep is bound
+// by the L1/L2 traffic of the rows, so Q queries per load divide the time by almost Q. The running best of a query
+// is kept as an integer bound for the fast test (d < best with integer d  <=>  d < ceil(best)); the rare rows that
+// pass it go through the FP64 gates with the per-query state in shared memory, in ascending row order per query,
+// exactly as the one-query-per-warp formulation did.
+struct UninitState {
+  double best;
+  V3 hps, e1;
+  int bestO, skipOwner, prev, k;
+  unsigned ctr;
+  int hpWritten;
+};
+
+template <int Q>
 __global__ void __launch_bounds__(256) match_uninitialised_kernel(const UninitJob* __restrict__ jobs) {
+  constexpr int kWarps = 8, kChunk = kWarps * Q;
+  static_assert(kChunk <= 32, "one ballot compacts the chunk");
+  __shared__ int s_list[kChunk];
+  __shared__ int s_n;
+  __shared__ UninitState s_state[kWarps][Q];
   const UninitJob& job = jobs[blockIdx.y];
   const UninitArgs& a = job.a;
-  const int lane = threadIdx.x & 31;
-  const int k = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int nk = job.nk_dev ? min(*job.nk_dev, job.nk) : job.nk;
-  if (k >= nk) return;
+  const int k0 = blockIdx.x * kChunk;
+  if (k0 >= nk) return;
+  if (warp == 0) {
+    const int k = k0 + lane;
+    const bool inChunk = lane < kChunk && k < nk;
+    // Frontend.cpp:1862-1872: a keypoint takes part when its back-projection is valid and it has no landmark yet
+    bool use = inChunk && (job.use ? job.use[k] != 0 : true);
+    if (use && job.bp_valid && !job.bp_valid[k]) use = false;
+    if (use && job.owner14 && job.owner14[k] >= 0) use = false;
+    const unsigned bal = __ballot_sync(0xffffffffu, use);
+    if (use) s_list[__popc(bal & ((1u << lane) - 1u))] = k;
+    if (lane == 0) s_n = __popc(bal);
+    if (inChunk && !use) {   // untouched outputs of a keypoint that does not take part
+      job.dist[k] = a.hammingThreshold;
+      job.best[k] = -1;
+      job.hp[4 * k + 0] = 0.0;
+      job.hp[4 * k + 1] = 0.0;
+      job.hp[4 * k + 2] = 0.0;
+      job.hp[4 * k + 3] = 0.0;
+      job.hp_written[k] = 0;
+      if (job.ctr) job.ctr[k] = 0;
+    }
+  }
+  __syncthreads();
+  const int g0 = warp * Q;
+  if (g0 >= s_n) return;
+  const int nq = min(Q, s_n - g0);
   // rows to sweep: all of the pool, or a precompacted ascending list (the rows of the non-3D landmarks)
   const int* __restrict__ rowList = job.row_list;
   const int nm = rowList ? min(*job.n_list_dev, job.nm) : (job.nm_dev ? min(*job.nm_dev, job.nm) : job.nm);
@@ -1040,42 +1087,58 @@ __global__ void __launch_bounds__(256) match_uninitialised_kernel(const UninitJo
   const int* __restrict__ owner = job.owner;
   const double* __restrict__ map_e_W = job.map_e_W;
   const double* __restrict__ map_r_W = job.map_r_W;
-  double best = a.hammingThreshold;
-  int bestO = -1, skipOwner = -1;
-  unsigned ctr = 0;
-  V3 hps = v3(0.0, 0.0, 0.0);
-  bool hpWritten = false;
-  // Frontend.cpp:1862-1872: a keypoint takes part when its back-projection is valid and it has no landmark yet
-  bool use = job.use ? job.use[k] != 0 : true;
-  if (job.bp_valid && !job.bp_valid[k]) use = false;
-  if (job.owner14 && job.owner14[k] >= 0) use = false;
-  if (use) {
-    unsigned q[kDescWords];
-    load_desc(job.queries, k, q);
-    V3 e1_W;
+  const double* __restrict__ rc = job.pose_slot ? job.pose_slot->r_WC : a.r_WC;
+  const V3 rC = v3(rc[0], rc[1], rc[2]);
+  unsigned q[Q][kDescWords];
+  int bound[Q];   // ceil(best): the integer form of "d < best"
+#pragma unroll
+  for (int j = 0; j < Q; ++j) {
+    const int k = s_list[g0 + min(j, nq - 1)];
+    load_desc(job.queries, k, q[j]);
+    bound[j] = j < nq ? (int)ceil(a.hammingThreshold) : 0;
+  }
+  if (lane < nq) {
+    UninitState& st = s_state[warp][lane];
+    const int k = s_list[g0 + lane];
+    st.k = k;
+    st.best = a.hammingThreshold;
+    st.bestO = -1;
+    st.skipOwner = -1;
+    st.ctr = 0;
+    st.hps = v3(0.0, 0.0, 0.0);
+    st.hpWritten = 0;
+    st.prev = job.previousOwner ? job.previousOwner[k] : -1;
     if (job.kp_e_W) {
-      e1_W = v3(job.kp_e_W[3 * k], job.kp_e_W[3 * k + 1], job.kp_e_W[3 * k + 2]);
+      st.e1 = v3(job.kp_e_W[3 * k], job.kp_e_W[3 * k + 1], job.kp_e_W[3 * k + 2]);
     } else {   // T_WC1.C() * e1_C.normalized()
-      e1_W = matvec(job.pose_slot ? job.pose_slot->C_WC : job.C_WC,
-                    normalized(v3(job.e_C[3 * k], job.e_C[3 * k + 1], job.e_C[3 * k + 2])));
+      st.e1 = matvec(job.pose_slot ? job.pose_slot->C_WC : job.C_WC,
+                     normalized(v3(job.e_C[3 * k], job.e_C[3 * k + 1], job.e_C[3 * k + 2])));
     }
-    const double* __restrict__ rc = job.pose_slot ? job.pose_slot->r_WC : a.r_WC;
-    const V3 rC = v3(rc[0], rc[1], rc[2]);
-    const int prev = job.previousOwner ? job.previousOwner[k] : -1;
-    for (int base = 0; base < nm; base += 32) {
-      const int i = base + lane;
-      const int m = i < nm ? (rowList ? rowList[i] : i) : 0;
-      double d = 1e9;
-      if (i < nm && !(!rowList && job.is3d && job.is3d[owner[m]])) {
-        unsigned r[kDescWords];
-        load_desc(map, m, r);
-        d = (double)hamming384(q, r);
-      }
-      unsigned pending = __ballot_sync(0xffffffffu, d < best);
+  }
+  __syncwarp();
+  for (int base = 0; base < nm; base += 32) {
+    const int i = base + lane;
+    const int m = i < nm ? (rowList ? rowList[i] : i) : 0;
+    const bool live = i < nm && !(!rowList && job.is3d && job.is3d[owner[m]]);
+    unsigned r[kDescWords];
+    if (live) load_desc(map, m, r);
+#pragma unroll
+    for (int j = 0; j < Q; ++j) {
+      const int d = live ? (int)hamming384(q[j], r) : (1 << 20);
+      unsigned pending = __ballot_sync(0xffffffffu, d < bound[j]);
+      if (!pending) continue;
+      // the state of query j, warp-uniform in registers for the duration of this tile's candidates
+      UninitState& st = s_state[warp][j];
+      double best = st.best;
+      int bestO = st.bestO, skipOwner = st.skipOwner, hpWritten = st.hpWritten;
+      unsigned ctr = st.ctr;
+      V3 hps = st.hps;
+      const V3 e1_W = st.e1;
+      const int prev = st.prev;
       while (pending) {
         const int src = __ffs(pending) - 1;
         pending &= pending - 1;
-        const double dc = __shfl_sync(0xffffffffu, d, src);
+        const double dc = (double)__shfl_sync(0xffffffffu, d, src);
         const int mc = __shfl_sync(0xffffffffu, m, src);
         if (!(dc < best)) continue;
         const int oc = owner[mc];
@@ -1106,26 +1169,39 @@ __global__ void __launch_bounds__(256) match_uninitialised_kernel(const UninitJo
         ++ctr;
         if (!isParallel) {
           hps = hp;
-          hpWritten = true;
+          hpWritten = 1;
         }
       }
+      if (lane == 0) {
+        st.best = best;
+        st.bestO = bestO;
+        st.skipOwner = skipOwner;
+        st.hpWritten = hpWritten;
+        st.ctr = ctr;
+        st.hps = hps;
+      }
+      __syncwarp();
+      bound[j] = (int)ceil(best);
     }
   }
-  if (lane == 0) {
-    job.dist[k] = best;
-    job.best[k] = bestO;
-    job.hp[4 * k + 0] = hps.x;
-    job.hp[4 * k + 1] = hps.y;
-    job.hp[4 * k + 2] = hps.z;
-    job.hp[4 * k + 3] = hpWritten ? 1.0 : 0.0;
-    job.hp_written[k] = hpWritten ? 1 : 0;
-    if (job.ctr) job.ctr[k] = ctr;
-    if (job.slice_ctrs && ctr) {
+  __syncwarp();
+  if (lane < nq) {
+    const UninitState& st = s_state[warp][lane];
+    const int k = st.k;
+    job.dist[k] = st.best;
+    job.best[k] = st.bestO;
+    job.hp[4 * k + 0] = st.hps.x;
+    job.hp[4 * k + 1] = st.hps.y;
+    job.hp[4 * k + 2] = st.hps.z;
+    job.hp[4 * k + 3] = st.hpWritten ? 1.0 : 0.0;
+    job.hp_written[k] = st.hpWritten ? 1 : 0;
+    if (job.ctr) job.ctr[k] = st.ctr;
+    if (job.slice_ctrs && st.ctr) {
       // ctrs[t] of thread slice t (Frontend.cpp:1853-1855): segment = numKeypoints / numThreads, the last takes the rest
       const int segment = nk / job.num_slices;
       int t = segment == 0 ? job.num_slices - 1 : k / segment;
       if (t >= job.num_slices) t = job.num_slices - 1;
-      atomicAdd(job.slice_ctrs + t, (unsigned long long)ctr);
+      atomicAdd(job.slice_ctrs + t, (unsigned long long)st.ctr);
     }
   }
 }
@@ -1193,8 +1269,8 @@ void launch_unmatched_lists(const UnmatchedArgs* args, int n, int max_kp, cudaSt
 
 void launch_match_uninit_jobs(const UninitJob* jobs, int nJobs, int maxNk, cudaStream_t s) {
   if (nJobs <= 0 || maxNk <= 0) return;
-  const int warpsPerBlock = 8;
-  match_uninitialised_kernel<<<dim3((maxNk + warpsPerBlock - 1) / warpsPerBlock, nJobs), warpsPerBlock * 32, 0, s>>>(jobs);
+  constexpr int Q = 4, chunk = 8 * Q;   // keypoints per CTA (8 warps x Q queries)
+  match_uninitialised_kernel<Q><<<dim3((maxNk + chunk - 1) / chunk, nJobs), 256, 0, s>>>(jobs);
 }
 
 }  // namespace okc

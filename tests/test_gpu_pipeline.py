@@ -192,3 +192,54 @@ def test_pipeline_stage_errors(mod, ctx, syn):
         mod.Camera(ctx, 320, 240, max_keypoints=16).set_geometry(mod.Pinhole.make(640, 480, (1, 1), (1, 1), "none", ()))
     batch.close()
     cam.close()
+
+
+def test_graph_replay_equals_plain_launches(mod, ctx, syn):
+    """The launch chains replayed as CUDA graphs (default) against plain launches: five frames of a sequence, each
+    with the landmark stage; every output byte equal. The graphs are captured at the second frame, so frames 2-4 are
+    replays with new images, poses and extraction directions reaching the kernels through the device tables."""
+    cfg, model, cams, W, H = _rig(mod, syn, ctx, "euroc", 2, 768)
+    n_frames = 6
+    imgs = syn.rig_sequence(n_frames, 2, W, H, seed=31, step=STEP, disparity=DISP, dense=True)
+    r_all = syn.rig_poses(n_frames, 2, model.fu, model.fv, STEP, DISP, Z0)
+    det = (cfg["radius"], 0, cfg["abs_threshold"], cfg["max_kpt"])
+    # world from frame 0
+    b0 = mod.Batch(ctx, cams)
+    b0.enqueue([imgs[c, 0] for c in range(2)], *det, [(0.0, 1.0, 0.0)] * 2)
+    b0.finish()
+    views = []
+    for c in range(2):
+        kp, desc = b0.slot_frame(c)
+        e_C, valid, _ = b0.slot_back_projections(c, len(kp))
+        views.append(dict(kp=kp, desc=desc, e_C=e_C, valid=valid, r_WC=r_all[0, c]))
+    b0.close()
+    pool = mod.LandmarkPool(ctx, *syn.plane_landmarks(views, Z0, model.fu, 2000, seed=5))
+    results = {}
+    for graph in (False, True):
+        batch = mod.Batch(ctx, cams)
+        batch.set_graph(graph)
+        outs = []
+        for f in range(1, n_frames):
+            d = (0.05 * f, 1.0 - 0.01 * f, 0.1)
+            batch.enqueue([imgs[c, f] for c in range(2)], *det, [d, d])
+            batch.set_poses(_poses(mod, r_all[f]))
+            batch.match_landmarks_enqueue(pool, 60.0, cfg["slices"], mod.STAGE_UNINITIALISED)
+            batch.match_stereo_enqueue([(0, 1)], 60.0)
+            batch.finish()
+            frame = []
+            for c in range(2):
+                kp, desc = batch.slot_frame(c)
+                assert len(kp) > 300
+                frame += [kp.tobytes(), desc.tobytes()]
+                frame += [x.tobytes() for x in batch.slot_matches(c, len(kp))]
+                frame += [x.tobytes() for x in batch.slot_uninitialised(c, len(kp))]
+                frame += [x.tobytes() for x in batch.slot_back_projections(c, len(kp))[:2]]
+            frame += [x.tobytes() for x in batch.pair_stereo(0, len(batch.slot_frame(0)[0]))]
+            outs.append(frame)
+        results[graph] = outs
+        batch.close()
+    assert results[False] == results[True]
+    assert len(set(tuple(f) for f in results[True])) == n_frames - 1      # (the frames really differ)
+    pool.close()
+    for cam in cams:
+        cam.close()
