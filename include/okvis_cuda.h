@@ -469,6 +469,38 @@ int okc_batch_read_stages(okc_batch* batch, double* u_dist, int32_t* u_owner, do
                           uint64_t* u_ctrs, double* s_dist, int32_t* s_k1, double* s_hp, uint8_t* s_init, int32_t* m_n0,
                           double* m_dist, int32_t* m_k1, double* m_hp, uint8_t* m_init, double* m_quality);
 
+/* The same results WITHOUT a copy: okc_batch_finish leaves everything in pinned host memory owned by the batch, and
+ * this returns where (the way the reference's callers read keypoints_ / descriptors_ / the match vectors in place
+ * out of okvis::Frame). Contents are valid from okc_batch_finish until the next enqueue on this batch; the pointers
+ * until the stage set-up grows (more pairs / jobs / landmarks) or the batch is destroyed. Rows beyond a count are
+ * unspecified. A group whose base pointer is NULL did not run for this frame. */
+typedef struct okc_match_stats { uint64_t count; double sum; } okc_match_stats; /* ctrs[t], reprErrors[t] * ctrs[t] */
+typedef struct okc_job_view {      /* result blocks of matchStereo pairs or matchMotionStereo jobs */
+  const uint8_t* base;             /* block j at base + j * stride */
+  size_t stride;
+  size_t off_dist, off_k1, off_hp, off_initialisable, off_quality; /* double[rows], int32[rows], double[rows][4], u8[rows], double[rows] (motion only) */
+  int n, rows;                     /* blocks, row capacity of a block */
+} okc_job_view;
+typedef struct okc_batch_view {
+  int n_slots, max_keypoints, num_slices;
+  const int32_t* counters;         /* [n_slots][8]: [2] = keypoints after describe (live rows of every per-keypoint array) */
+  const uint8_t* slots;            /* slot i at slots + i * slot_stride */
+  size_t slot_stride;
+  size_t off_keypoints, off_descriptors;      /* okc_keypoint[max_keypoints], u8[max_keypoints][48] */
+  size_t off_best_dist, off_best_owner;       /* matchToMapByThread: double[max_keypoints], int32[max_keypoints] */
+  size_t off_stats;                           /* okc_match_stats[num_slices] */
+  int map_match;                              /* 0: no map match ran (the three offsets above are meaningless) */
+  const uint8_t* uninit;           /* matchToMapByThreadUnitialised: slot i at uninit + i * uninit_stride, or NULL */
+  size_t uninit_stride;
+  size_t u_off_dist, u_off_owner, u_off_hps, u_off_written; /* double[], int32[], double[][4], u8[] per keypoint */
+  const uint64_t* uninit_ctrs;     /* [n_slots][uninit_ctrs_stride], the first num_slices of a row are used */
+  int uninit_ctrs_stride;
+  okc_job_view stereo;             /* rows of pair p: counters[8 * slot0 + 2] of its first slot */
+  okc_job_view motion;             /* rows of job j: motion_n0[j] */
+  const int32_t* motion_n0;
+} okc_batch_view;
+int okc_batch_view_results(okc_batch* batch, okc_batch_view* view);
+
 int okc_debug_batch_kernel_timing(okc_batch* batch, int enable);
 int okc_debug_batch_kernel_times(okc_batch* batch, char* names, int names_cap, float* ms, int cap, int* n);
 

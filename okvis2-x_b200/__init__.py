@@ -23,6 +23,23 @@ KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4
 PWS_DTYPE = np.dtype([("score", "<i4"), ("x", "<u2"), ("y", "<u2")])
 NO_MATCH = np.uint64(0xFFFFFFFFFFFFFFFF)
 
+class JobView(C.Structure):
+    _fields_ = [("base", C.c_void_p), ("stride", C.c_size_t), ("off_dist", C.c_size_t), ("off_k1", C.c_size_t),
+                ("off_hp", C.c_size_t), ("off_initialisable", C.c_size_t), ("off_quality", C.c_size_t), ("n", C.c_int),
+                ("rows", C.c_int)]
+
+
+class BatchView(C.Structure):
+    """okc_batch_view (include/okvis_cuda.h)."""
+    _fields_ = [("n_slots", C.c_int), ("max_keypoints", C.c_int), ("num_slices", C.c_int), ("counters", C.c_void_p),
+                ("slots", C.c_void_p), ("slot_stride", C.c_size_t), ("off_keypoints", C.c_size_t),
+                ("off_descriptors", C.c_size_t), ("off_best_dist", C.c_size_t), ("off_best_owner", C.c_size_t),
+                ("off_stats", C.c_size_t), ("map_match", C.c_int), ("uninit", C.c_void_p), ("uninit_stride", C.c_size_t),
+                ("u_off_dist", C.c_size_t), ("u_off_owner", C.c_size_t), ("u_off_hps", C.c_size_t),
+                ("u_off_written", C.c_size_t), ("uninit_ctrs", C.c_void_p), ("uninit_ctrs_stride", C.c_int),
+                ("stereo", JobView), ("motion", JobView), ("motion_n0", C.c_void_p)]
+
+
 EXPORTS = [
     "okc_last_error_string", "okc_version", "okc_context_create", "okc_context_destroy", "okc_context_device",
     "okc_camera_create", "okc_camera_destroy", "okc_detect", "okc_describe", "okc_detect_describe",
@@ -31,7 +48,7 @@ EXPORTS = [
     "okc_match_to_map", "okc_match_stereo", "okc_match_to_map_uninitialised", "okc_match_motion_stereo",
     "okc_detect_describe_enqueue_device", "okc_map_window_create", "okc_map_window_destroy",
     "okc_camera_match_to_map_enqueue", "okc_camera_frame_finish", "okc_camera_stream", "okc_debug_kernel_timing",
-    "okc_debug_kernel_times", "okc_batch_create", "okc_batch_destroy", "okc_batch_size", "okc_batch_set_graph", "okc_batch_enqueue",
+    "okc_debug_kernel_times", "okc_batch_create", "okc_batch_destroy", "okc_batch_size", "okc_batch_set_graph", "okc_batch_view_results", "okc_batch_enqueue",
     "okc_batch_finish", "okc_batch_slot_frame", "okc_batch_slot_matches", "okc_batch_read_all", "okc_batch_stream",
     "okc_debug_batch_kernel_timing", "okc_debug_batch_kernel_times",
     "okc_camera_set_geometry", "okc_batch_set_poses", "okc_batch_slot_back_projections", "okc_landmark_pool_create",
@@ -183,6 +200,7 @@ def lib():
         L.okc_batch_destroy.argtypes = [vp]
         L.okc_batch_size.argtypes = [vp]
         L.okc_batch_set_graph.argtypes = [vp, C.c_int]
+        L.okc_batch_view_results.argtypes = [vp, vp]
         L.okc_batch_enqueue.argtypes = [vp, vp, i, C.POINTER(DetectParams), vp, vp, vp, i, vp, d, i]
         L.okc_batch_read_all.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp]
         L.okc_batch_finish.argtypes = [vp]
@@ -976,6 +994,55 @@ class Batch:
         m_ = [out[k] if n_jobs else None for k in ("m_n0", "m_dist", "m_k1", "m_hp", "m_init", "m_quality")]
         _check(lib().okc_batch_read_stages(self.h, *[_p(x) for x in u], _p(uc), *[_p(x) for x in s_], *[_p(x) for x in m_]),
                "okc_batch_read_stages")
+        return out
+
+    def view(self):
+        """okc_batch_view_results: the results of a finished frame as numpy arrays that ALIAS the batch's pinned host
+        memory (no copy; valid until the next enqueue on this batch). dict(n [slots], kp [slots, max_kp], desc
+        [slots, max_kp, 48], dist / owner [slots, max_kp], stats (count, sum) [slots, slices], u_dist / u_owner /
+        u_hps / u_written [slots, max_kp(,4)], u_ctrs [slots, slices], s_* [pairs, rows(,4)], m_* [jobs, rows(,4)],
+        m_n0 [jobs]); groups of stages that did not run are absent."""
+        v = BatchView()
+        _check(lib().okc_batch_view_results(self.h, C.byref(v)), "okc_batch_view_results")
+        key = bytes(v)
+        cached = getattr(self, "_view_cache", None)
+        if cached is not None and cached[0] == key:
+            return cached[1]
+        B, mk, S = v.n_slots, v.max_keypoints, max(v.num_slices, 1)
+
+        def arr(base, nbytes, off, shape, strides, dtype):
+            raw = np.ctypeslib.as_array((C.c_uint8 * nbytes).from_address(base))
+            return np.ndarray(shape, dtype, raw, off, strides)
+
+        out = {"n": np.ctypeslib.as_array((C.c_int32 * (8 * B)).from_address(v.counters)).reshape(B, 8)[:, 2]}
+        tot = v.slot_stride * B
+        out["kp"] = arr(v.slots, tot, v.off_keypoints, (B, mk), (v.slot_stride, 28), KP_DTYPE)
+        out["desc"] = arr(v.slots, tot, v.off_descriptors, (B, mk, 48), (v.slot_stride, 48, 1), np.uint8)
+        if v.map_match:
+            out["dist"] = arr(v.slots, tot, v.off_best_dist, (B, mk), (v.slot_stride, 8), np.float64)
+            out["owner"] = arr(v.slots, tot, v.off_best_owner, (B, mk), (v.slot_stride, 4), np.int32)
+            out["stats"] = arr(v.slots, tot, v.off_stats, (B, S), (v.slot_stride, 16),
+                               np.dtype([("count", "<u8"), ("sum", "<f8")]))
+        if v.uninit:
+            ut = v.uninit_stride * B
+            out["u_dist"] = arr(v.uninit, ut, v.u_off_dist, (B, mk), (v.uninit_stride, 8), np.float64)
+            out["u_owner"] = arr(v.uninit, ut, v.u_off_owner, (B, mk), (v.uninit_stride, 4), np.int32)
+            out["u_hps"] = arr(v.uninit, ut, v.u_off_hps, (B, mk, 4), (v.uninit_stride, 32, 8), np.float64)
+            out["u_written"] = arr(v.uninit, ut, v.u_off_written, (B, mk), (v.uninit_stride, 1), np.uint8)
+            out["u_ctrs"] = np.ctypeslib.as_array((C.c_uint64 * (v.uninit_ctrs_stride * B)).from_address(v.uninit_ctrs)) \
+                .reshape(B, v.uninit_ctrs_stride)[:, :S]
+        for tag, jv in (("s", v.stereo), ("m", v.motion)):
+            if not jv.base:
+                continue
+            jt, J, R = jv.stride * jv.n, jv.n, jv.rows
+            out[tag + "_dist"] = arr(jv.base, jt, jv.off_dist, (J, R), (jv.stride, 8), np.float64)
+            out[tag + "_k1"] = arr(jv.base, jt, jv.off_k1, (J, R), (jv.stride, 4), np.int32)
+            out[tag + "_hp"] = arr(jv.base, jt, jv.off_hp, (J, R, 4), (jv.stride, 32, 8), np.float64)
+            out[tag + "_init"] = arr(jv.base, jt, jv.off_initialisable, (J, R), (jv.stride, 1), np.uint8)
+            if tag == "m":
+                out["m_quality"] = arr(jv.base, jt, jv.off_quality, (J, R), (jv.stride, 8), np.float64)
+                out["m_n0"] = np.ctypeslib.as_array((C.c_int32 * J).from_address(v.motion_n0))
+        self._view_cache = (key, out)
         return out
 
     def stream(self):

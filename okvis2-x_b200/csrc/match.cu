@@ -913,109 +913,169 @@ __device__ __forceinline__ double side_size(const StereoSide& v, int k) {
   return v.size_d ? v.size_d[k] : (double)v.kp[k].size;
 }
 
-template <bool MOTION>
+// Work layout as in match_uninitialised_kernel below: a CTA takes 8 * Q consecutive k0, compacts the eligible ones,
+// every warp sweeps the k1 rows once for its Q queries (integer bound for the fast test, FP64 gates for the few
+// rows that pass it, per-query state in shared memory).
+struct StereoState {
+  double dist, quality, size0;
+  V3 hps, e0;
+  int k1, k0, init, valid0;
+};
+
+template <bool MOTION, int Q>
 __global__ void __launch_bounds__(256)
 match_stereo_kernel(const StereoJob* __restrict__ jobs, double hammingThreshold) {
+  constexpr int kWarps = 8, kChunk = kWarps * Q;
+  static_assert(kChunk <= 32, "one ballot compacts the chunk");
+  __shared__ int s_list[kChunk];
+  __shared__ int s_n;
+  __shared__ StereoState s_state[kWarps][Q];
   const StereoJob& job = jobs[blockIdx.y];
   const StereoSide& v0 = job.v0;
   const StereoSide& v1 = job.v1;
-  const int lane = threadIdx.x & 31;
-  const int k0 = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int n0 = v0.n_dev ? min(*v0.n_dev, v0.n) : v0.n;
-  // candidates k1: every keypoint of v1, or a precompacted ascending list (the slot's keypoints without a landmark)
-  const int* __restrict__ list1 = job.v1_list;
-  const int n1 = list1 ? min(*job.v1_list_n, v1.n) : (v1.n_dev ? min(*v1.n_dev, v1.n) : v1.n);
-  if (k0 >= n0) return;
+  const int kBase = blockIdx.x * kChunk;
+  if (kBase >= n0) return;
   double* __restrict__ outDist = job.dist;
   int* __restrict__ outK1 = job.k1;
   double* __restrict__ outHp = job.hp;
   uint8_t* __restrict__ outInit = job.init;
-  if (MOTION && !((!job.use0 || job.use0[k0]) && v0.bp_valid[k0])) {
-    if (lane == 0) {
+  if (warp == 0) {
+    const int k0 = kBase + lane;
+    const bool inChunk = lane < kChunk && k0 < n0;
+    const bool use = inChunk && (!MOTION || ((!job.use0 || job.use0[k0]) && v0.bp_valid[k0]));
+    const unsigned bal = __ballot_sync(0xffffffffu, use);
+    if (use) s_list[__popc(bal & ((1u << lane) - 1u))] = k0;
+    if (lane == 0) s_n = __popc(bal);
+    if (inChunk && !use) {   // (MOTION only) a k0 that is not eligible
       outDist[k0] = hammingThreshold;
       outK1[k0] = -1;
       outHp[4 * k0 + 0] = outHp[4 * k0 + 1] = outHp[4 * k0 + 2] = outHp[4 * k0 + 3] = 0.0;
       outInit[k0] = 0;
       job.quality[k0] = 0.0;
     }
-    return;
   }
-  unsigned q[kDescWords];
-  load_desc(v0.desc, k0, q);
-  double distances = hammingThreshold;
-  bool initialisable = false;
-  V3 hps = v3(0.0, 0.0, 0.0);
-  int k1_match = MOTION ? -1 : 0;
-  double quality = 0.0;
+  __syncthreads();
+  const int g0 = warp * Q;
+  if (g0 >= s_n) return;
+  const int nq = min(Q, s_n - g0);
+  // candidates k1: every keypoint of v1, or a precompacted ascending list (the slot's keypoints without a landmark)
+  const int* __restrict__ list1 = job.v1_list;
+  const int n1 = list1 ? min(*job.v1_list_n, v1.n) : (v1.n_dev ? min(*v1.n_dev, v1.n) : v1.n);
   // poses: by value, or from the batch slot's record (the job table then stays valid from frame to frame)
   const double* __restrict__ C0 = v0.pose_slot ? v0.pose_slot->C_WC : v0.C;
   const double* __restrict__ C1 = v1.pose_slot ? v1.pose_slot->C_WC : v1.C;
   const double* __restrict__ p0 = v0.pose_slot ? v0.pose_slot->r_WC : v0.r;
   const double* __restrict__ p1 = v1.pose_slot ? v1.pose_slot->r_WC : v1.r;
   const V3 r0 = v3(p0[0], p0[1], p0[2]), r1 = v3(p1[0], p1[1], p1[2]);
-
+  unsigned q[Q][kDescWords];
+  int bound[Q];   // ceil(running best): the integer form of "d < distances"
+#pragma unroll
+  for (int j = 0; j < Q; ++j) {
+    load_desc(v0.desc, s_list[g0 + min(j, nq - 1)], q[j]);
+    bound[j] = j < nq ? (int)ceil(hammingThreshold) : 0;
+  }
+  if (lane < nq) {
+    StereoState& st = s_state[warp][lane];
+    const int k0 = s_list[g0 + lane];
+    st.k0 = k0;
+    st.dist = hammingThreshold;
+    st.quality = 0.0;
+    st.hps = v3(0.0, 0.0, 0.0);
+    st.k1 = MOTION ? -1 : 0;
+    st.init = 0;
+    st.valid0 = v0.bp_valid[k0] ? 1 : 0;
+    st.size0 = side_size(v0, k0);
+    st.e0 = normalized(matvec(C0, v3(v0.e_C[3 * k0], v0.e_C[3 * k0 + 1], v0.e_C[3 * k0 + 2])));
+  }
+  __syncwarp();
   for (int base = 0; base < n1; base += 32) {
     const int i1 = base + lane;
     const int k1 = i1 < n1 ? (list1 ? list1[i1] : i1) : 0;
-    double d = 1e9;
-    if (i1 < n1 && !(job.v1_owner_a && job.v1_owner_a[k1] >= 0) && !(job.v1_owner_b && job.v1_owner_b[k1] >= 0)) {
-      unsigned r[kDescWords];
-      load_desc(v1.desc, k1, r);
-      d = (double)hamming384(q, r);
-    }
-    unsigned pending = __ballot_sync(0xffffffffu, d < distances);
-    while (pending) {  // sparse: geometry only for candidates below the running best, in k1 order
-      const int src = __ffs(pending) - 1;
-      pending &= pending - 1;
-      const double dc = __shfl_sync(0xffffffffu, d, src);
-      const int kc = __shfl_sync(0xffffffffu, k1, src);
-      if (!(dc < distances)) continue;
-      if (!v0.bp_valid[k0]) continue;
-      if (!v1.bp_valid[kc]) continue;
-      const double sigma = MOTION ? side_size(v0, k0) / v0.f * 0.125
-                                  : fmax(side_size(v0, k0) / v0.f, side_size(v1, kc) / v1.f) * 0.125;
-      const V3 e0_W = normalized(matvec(C0, v3(v0.e_C[3 * k0], v0.e_C[3 * k0 + 1], v0.e_C[3 * k0 + 2])));
-      const V3 e1_W = normalized(matvec(C1, v3(v1.e_C[3 * kc], v1.e_C[3 * kc + 1], v1.e_C[3 * kc + 2])));
-      if (MOTION && dot(e0_W, e1_W) < 0.5) continue;
-      bool isValid = false, isParallel = false;
-      const V3 hp = triangulate_fast(r0, e0_W, r1, e1_W, cos(2.6 * sigma), cos(6.0 * sigma), isValid, isParallel);
-      if (MOTION && !isValid) continue;
-      // T_WC.inverse() * hp_W with w = 1: C^T * p + (-(C^T * r)) * 1; z / w compared with 0.1
-      const V3 t0 = matTvec(C0, r0), t1 = matTvec(C1, r1);
-      const V3 c0 = matTvec(C0, hp), c1 = matTvec(C1, hp);
-      const double z0 = c0.z + (-t0.z) * 1.0, z1 = c1.z + (-t1.z) * 1.0;
-      const double minDepth = MOTION ? 0.2 : 0.1;
-      if (z0 / 1.0 < minDepth) isValid = false;
-      if (z1 / 1.0 < minDepth) isValid = false;
-      if (dot(e0_W, e1_W) < 0.8) isValid = false;
-      if (isValid) {
-        distances = dc;
-        hps = hp;
-        k1_match = kc;
-        initialisable = !isParallel;
-        if (MOTION) quality = acos(dot(normalized(hp - r0), normalized(hp - r1)));
+    const bool live =
+        i1 < n1 && !(job.v1_owner_a && job.v1_owner_a[k1] >= 0) && !(job.v1_owner_b && job.v1_owner_b[k1] >= 0);
+    unsigned r[kDescWords];
+    if (live) load_desc(v1.desc, k1, r);
+#pragma unroll
+    for (int j = 0; j < Q; ++j) {
+      const int d = live ? (int)hamming384(q[j], r) : (1 << 20);
+      unsigned pending = __ballot_sync(0xffffffffu, d < bound[j]);
+      if (!pending) continue;
+      StereoState& st = s_state[warp][j];
+      double distances = st.dist, quality = st.quality;
+      V3 hps = st.hps;
+      int k1_match = st.k1, initialisable = st.init;
+      const V3 e0_W = st.e0;
+      const double size0 = st.size0;
+      const bool valid0 = st.valid0 != 0;
+      bool changed = false;
+      while (pending) {  // sparse: geometry only for candidates below the running best, in k1 order
+        const int src = __ffs(pending) - 1;
+        pending &= pending - 1;
+        const double dc = (double)__shfl_sync(0xffffffffu, d, src);
+        const int kc = __shfl_sync(0xffffffffu, k1, src);
+        if (!(dc < distances)) continue;
+        if (!valid0) continue;
+        if (!v1.bp_valid[kc]) continue;
+        const double sigma = MOTION ? size0 / v0.f * 0.125 : fmax(size0 / v0.f, side_size(v1, kc) / v1.f) * 0.125;
+        const V3 e1_W = normalized(matvec(C1, v3(v1.e_C[3 * kc], v1.e_C[3 * kc + 1], v1.e_C[3 * kc + 2])));
+        if (MOTION && dot(e0_W, e1_W) < 0.5) continue;
+        bool isValid = false, isParallel = false;
+        const V3 hp = triangulate_fast(r0, e0_W, r1, e1_W, cos(2.6 * sigma), cos(6.0 * sigma), isValid, isParallel);
+        if (MOTION && !isValid) continue;
+        // T_WC.inverse() * hp_W with w = 1: C^T * p + (-(C^T * r)) * 1; z / w compared with 0.1
+        const V3 t0 = matTvec(C0, r0), t1 = matTvec(C1, r1);
+        const V3 c0 = matTvec(C0, hp), c1 = matTvec(C1, hp);
+        const double z0 = c0.z + (-t0.z) * 1.0, z1 = c1.z + (-t1.z) * 1.0;
+        const double minDepth = MOTION ? 0.2 : 0.1;
+        if (z0 / 1.0 < minDepth) isValid = false;
+        if (z1 / 1.0 < minDepth) isValid = false;
+        if (dot(e0_W, e1_W) < 0.8) isValid = false;
+        if (isValid) {
+          distances = dc;
+          hps = hp;
+          k1_match = kc;
+          initialisable = isParallel ? 0 : 1;
+          if (MOTION) quality = acos(dot(normalized(hp - r0), normalized(hp - r1)));
+          changed = true;
+        }
       }
+      if (changed) {
+        if (lane == 0) {
+          st.dist = distances;
+          st.quality = quality;
+          st.hps = hps;
+          st.k1 = k1_match;
+          st.init = initialisable;
+        }
+        bound[j] = (int)ceil(distances);
+      }
+      __syncwarp();
     }
   }
-  if (lane == 0) {
-    outDist[k0] = distances;
-    outK1[k0] = k1_match;
-    outHp[4 * k0 + 0] = hps.x / 1.0;
-    outHp[4 * k0 + 1] = hps.y / 1.0;
-    outHp[4 * k0 + 2] = hps.z / 1.0;
-    outHp[4 * k0 + 3] = (MOTION && k1_match < 0) ? 0.0 : 1.0;
-    outInit[k0] = initialisable ? 1 : 0;
-    if (MOTION) job.quality[k0] = quality;
+  __syncwarp();
+  if (lane < nq) {
+    const StereoState& st = s_state[warp][lane];
+    const int k0 = st.k0;
+    outDist[k0] = st.dist;
+    outK1[k0] = st.k1;
+    outHp[4 * k0 + 0] = st.hps.x / 1.0;
+    outHp[4 * k0 + 1] = st.hps.y / 1.0;
+    outHp[4 * k0 + 2] = st.hps.z / 1.0;
+    outHp[4 * k0 + 3] = (MOTION && st.k1 < 0) ? 0.0 : 1.0;
+    outInit[k0] = st.init ? 1 : 0;
+    if (MOTION) job.quality[k0] = st.quality;
   }
 }
 
 void launch_match_stereo_jobs(const StereoJob* jobs, int nJobs, int max0, bool motion, double hammingThreshold,
                               cudaStream_t s) {
   if (nJobs <= 0 || max0 <= 0) return;
-  const int warpsPerBlock = 8;
-  const dim3 grid((max0 + warpsPerBlock - 1) / warpsPerBlock, nJobs);
-  if (motion) match_stereo_kernel<true><<<grid, warpsPerBlock * 32, 0, s>>>(jobs, hammingThreshold);
-  else match_stereo_kernel<false><<<grid, warpsPerBlock * 32, 0, s>>>(jobs, hammingThreshold);
+  constexpr int Q = 4, chunk = 8 * Q;   // k0 per CTA (8 warps x Q queries)
+  const dim3 grid((max0 + chunk - 1) / chunk, nJobs);
+  if (motion) match_stereo_kernel<true, Q><<<grid, 256, 0, s>>>(jobs, hammingThreshold);
+  else match_stereo_kernel<false, Q><<<grid, 256, 0, s>>>(jobs, hammingThreshold);
 }
 
 // ----------------------------------------------------------------------------------------------

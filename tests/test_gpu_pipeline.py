@@ -41,6 +41,37 @@ def _view(kp, desc, e_C, valid, r_WC, f):
                 r_WC=np.asarray(r_WC, np.float64), f=f)
 
 
+def _check_view(batch, pairs=(), n_jobs=0):
+    """okc_batch_view_results (zero-copy arrays over the pinned arena) == the copying readers, live rows only."""
+    v = batch.view()
+    for c in range(batch.n):
+        kp, desc = batch.slot_frame(c)
+        n = len(kp)
+        assert int(v["n"][c]) == n
+        assert v["kp"][c, :n].tobytes() == kp.tobytes() and np.array_equal(v["desc"][c, :n], desc)
+        if "dist" in v:
+            bd, bo, ctrs, errs = batch.slot_matches(c, n)
+            assert np.array_equal(v["dist"][c, :n], bd) and np.array_equal(v["owner"][c, :n], bo)
+            assert np.array_equal(v["stats"]["count"][c], ctrs)
+            with np.errstate(invalid="ignore", divide="ignore"):
+                assert np.array_equal(v["stats"]["sum"][c] / v["stats"]["count"][c].astype(np.float64), errs, equal_nan=True)
+        if "u_dist" in v:
+            ud, uo, uhp, uhw, uc = batch.slot_uninitialised(c, n)
+            assert np.array_equal(v["u_dist"][c, :n], ud) and np.array_equal(v["u_owner"][c, :n], uo)
+            assert v["u_hps"][c, :n].tobytes() == uhp.tobytes() and np.array_equal(v["u_written"][c, :n], uhw)
+            assert np.array_equal(v["u_ctrs"][c], uc)
+    for p, (c0, _) in enumerate(pairs):
+        got = batch.pair_stereo(p, int(v["n"][c0]))
+        for name, g in zip(("s_dist", "s_k1", "s_hp", "s_init"), got):
+            assert v[name][p, :len(g)].tobytes() == g.tobytes(), name
+    for j in range(n_jobs):
+        got = batch.job_motion(j)
+        n0 = int(v["m_n0"][j])
+        assert n0 == len(got[0])
+        for name, g in zip(("m_dist", "m_k1", "m_hp", "m_init", "m_quality"), got):
+            assert v[name][j, :n0].tobytes() == g.tobytes(), name
+
+
 @pytest.mark.parametrize("cfgname,n_cams,dense", [("euroc", 2, False), ("euroc", 2, True), ("d455", 2, True),
                                                    ("hilti", 3, False)])
 def test_frame_pipeline_vs_port(cfgname, n_cams, dense, mod, ctx, port, ref, syn):
@@ -158,6 +189,7 @@ def test_frame_pipeline_vs_port(cfgname, n_cams, dense, mod, ctx, port, ref, syn
         assert float(np.abs(got[4] - want[4]).max()) <= 1e-12
         motion_matches += int((got[1] >= 0).sum())
     assert motion_matches > 20
+    _check_view(batch, pairs, len(jobs))
     for kf in kfs:
         kf.close()
     pool.close()
@@ -235,6 +267,7 @@ def test_graph_replay_equals_plain_launches(mod, ctx, syn):
                 frame += [x.tobytes() for x in batch.slot_uninitialised(c, len(kp))]
                 frame += [x.tobytes() for x in batch.slot_back_projections(c, len(kp))[:2]]
             frame += [x.tobytes() for x in batch.pair_stereo(0, len(batch.slot_frame(0)[0]))]
+            _check_view(batch, [(0, 1)])
             outs.append(frame)
         results[graph] = outs
         batch.close()
