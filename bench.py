@@ -315,6 +315,7 @@ class GpuConfig:
         self.det = (c["radius"], 0, c["abs_threshold"], c["max_kpt"])
         self.slices = c["slices"]
         self.F = args.frames_per_batch if conf["index"] != 2 else max(1, (args.frames_per_batch * 2) // wl["n_cams"])
+        self.F_shard = self.F      # block size of the frame sharding (latency() temporarily runs with F = 1)
         self.D = args.in_flight
         self.n_frames = conf["frames"]
         self.pool = None
@@ -379,14 +380,18 @@ class GpuConfig:
         self.outs, self.stage_outs = {}, {}
 
     def frame_of(self, k):
-        """Frame index of this rank's k-th frame: frames round-robin over ranks (cameras when they are sharded)."""
-        g = k if self.shard_cameras else k * self.world + self.rank
-        return g % self.n_frames
+        """Frame index of this rank's k-th frame. Frames are sharded in blocks of F consecutive frames (one batch),
+        blocks round-robin over the ranks: a batch's images are then adjacent in the host pool and travel in one copy
+        per camera, as they do on one GPU (frame-wise round-robin made that 64 copies of 361 KB per batch and cost a
+        third of the 2-GPU end-to-end throughput). Cameras sharded: every rank sees every frame."""
+        if self.shard_cameras:
+            return k % self.n_frames
+        F = self.F_shard
+        return ((k // F) * self.world * F + self.rank * F + k % F) % self.n_frames
 
     def slot_args(self, k0, device):
         F, nc = self.F, self.nc
-        k = np.arange(k0, k0 + F)
-        f = (k if self.shard_cameras else k * self.world + self.rank) % self.n_frames
+        f = np.asarray([self.frame_of(k) for k in range(k0, k0 + F)])
         imgs = np.empty(nc * F, np.uint64)
         poses = np.empty((nc * F, 24))
         for j, c in enumerate(self.cams_here):
@@ -445,6 +450,8 @@ class GpuConfig:
         for j in range(n_warm):
             self.enqueue(self.batches[j % D], *self.slot_args(j * F, True), True, j * F)
         work = [self.slot_args((n_warm + j) * F, True) for j in range(n_steps)]
+        for b in self.batches:
+            b.finish()
         barrier()
         start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         cur = torch.cuda.current_stream()
@@ -453,8 +460,6 @@ class GpuConfig:
             s.wait_event(start)
         # a batch is finished (results in pinned host memory) before it is enqueued again: D batches in flight, as a
         # caller that consumes the results runs it (deeper queues per stream measured 0-10 % slower)
-        for b in self.batches:
-            b.finish()
         t_host = time.perf_counter()
         for j, (imgs, poses) in enumerate(work):
             if j >= D:
@@ -703,7 +708,17 @@ def run_frame_config(args, name, mod, syn, torch, dist, ctx, rank, world, headli
     local = int(os.environ.get("LOCAL_RANK", 0))
     wl = build_images(syn, name, args.sparse)
     shard_cameras = CONFIGS[name]["index"] == 2 and world > 1
+    group = None
+    if shard_cameras and world > wl["n_cams"]:
+        # more GPUs than cameras: camera c -> rank c, the other ranks sit this config out (a multiframe has no more
+        # independent units); collectives of the config run on the members' group
+        group = dist.new_group(list(range(wl["n_cams"])))
+        if rank >= wl["n_cams"]:
+            dist.barrier()
+            return None, None
+        world = wl["n_cams"]
     gc = GpuConfig(args, mod, syn, torch, ctx, wl, rank, world, shard_cameras)
+    gc.group = group
     gc.build_world()
     gc.precompute_poses()
     gc.setup()
@@ -711,14 +726,14 @@ def run_frame_config(args, name, mod, syn, torch, dist, ctx, rank, world, headli
     def barrier():
         torch.cuda.synchronize()
         if world > 1:
-            dist.barrier()
+            dist.barrier(group=group)
         torch.cuda.synchronize()
 
     def max_over_ranks(x):
         if world == 1:
             return x
         t = torch.tensor([x], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX, group=group)
         return float(t.item())
 
     n_steps = max(args.steps, 1) if headline else max(min(args.steps, 60), 1)
@@ -772,7 +787,7 @@ def run_frame_config(args, name, mod, syn, torch, dist, ctx, rank, world, headli
         "step": "one batch = %d multiframes (%d images on this rank) through the whole launch chain" % (F, imgs_per_launch),
         "frames_in_pool": gc.n_frames, "keypoints_per_image": round(K, 1), "landmarks": L,
         "sharding": ("cameras over ranks (camera c -> rank c mod N), keypoints + descriptors all-gathered for matchStereo"
-                     if shard_cameras else "frames round-robin over ranks"),
+                     if shard_cameras else "batches of consecutive frames round-robin over ranks"),
         "host_enqueue_us_per_batch": round(t_enq, 1) if t_enq is not None else None,
         "launch_chains": "plain launches" if args.no_graph else "CUDA graphs (one per chain, captured at the second use)",
         "e2e": {"value": round(total / (e2e_ms * 1e-3), 2), "unit": "frames/s", "ms_per_step": round(e2e_ms / n_steps, 5),
@@ -792,6 +807,9 @@ def run_frame_config(args, name, mod, syn, torch, dist, ctx, rank, world, headli
     if clocks is not None:
         out["clocks"] = clocks
     st = dict(gc=gc, wl=wl, F=F)
+    if group is not None:
+        dist.barrier()     # (the ranks without a camera wait here)
+        out["sharding"] += "; %d of the ranks hold a camera" % world
     return out, st
 
 
@@ -895,6 +913,8 @@ def run_b200(args, rank, world):
     for name in names:
         headline = name == HEADLINE
         out, st = run_frame_config(args, name, mod, syn, torch, dist, ctx, rank, world, headline, sampler_box)
+        if st is None:
+            continue
         if rank == 0 and world == 1 and not args.no_cpu_baseline:
             cpu = CpuFrontend(mod, syn, st["wl"])
             n_check = 3 if CONFIGS[name]["index"] in (2, 3) else 6

@@ -162,7 +162,7 @@ class CameraGather:
         b = gc.batches[bi]
         b.pack_views(list(range(gc.nc * gc.F)), self.send[bi].ptr)
         with torch.cuda.stream(gc.streams[bi]):
-            self.dist.all_gather_into_tensor(self.recv[bi].t, self.send[bi].t)
+            self.dist.all_gather_into_tensor(self.recv[bi].t, self.send[bi].t, group=getattr(gc, "group", None))
         poses1 = np.stack([gc.pose_rows[gc.frame_of(k0 + s % gc.F), c1] for s, c1 in zip(self.slot0, self.cam1)]) \
             if self.slot0 else np.zeros((0, 24))
         if self.slot0:
