@@ -510,18 +510,10 @@ class GpuConfig:
         return float(np.median(runs)), runs
 
     def bytes_per_frame(self):
-        """(H2D, D2H) bytes one multiframe moves in the e2e arm (this rank's cameras), from the copies the library makes."""
-        wl, mk = self.wl, self.max_kp
-        pad = lambda n: (n + 255) & ~255
-        h2d = self.nc * (wl["W"] * wl["H"] + 24 * 8 + 600)                      # image + pose + slot table / job records
-        arena = pad(mk * 28) + pad(mk * 48)
-        if self.conf["landmarks"]:
-            arena += pad(mk * 8) + pad(mk * 4) + 1024                           # matchToMapByThread: dist, owner, stats
-            arena += pad(mk * 8) + pad(mk * 4) + pad(mk * 32) + pad(mk) + 512   # uninitialised: dist, owner, hps, flags, ctrs
-        d2h = self.nc * (arena + 32)
-        job = pad(mk * 8) + pad(mk * 4) + pad(mk * 32) + pad(mk) + pad(mk * 8)
-        d2h += (len(self.pairs) + len(self.jobs)) // self.F * job
-        return h2d, d2h
+        """(H2D, D2H) bytes one multiframe moves in the e2e arm (this rank's cameras): counted by the library at the
+        copies it issues (okc_batch_transfer_bytes), mean over the batches of the last e2e run."""
+        t = [b.transfer_bytes() for b in self.batches]
+        return (sum(x[0] for x in t) / len(t) / self.F, sum(x[1] for x in t) / len(t) / self.F)
 
     def kernel_times(self, n_batches):
         b0 = self.batches[0]
@@ -753,6 +745,7 @@ def run_frame_config(args, name, mod, syn, torch, dist, ctx, rank, world, headli
         gc.gather = sh.CameraGather(mod, torch, dist, ctx, gc, HAMMING)
     dev_ms, t_host = gc.run_value(n_steps, n_warm, barrier, max_over_ranks)
     e2e_ms, e2e_runs = gc.time_e2e(n_steps, n_warm, barrier, max_over_ranks)
+    h2d, d2h = gc.bytes_per_frame()     # (of the e2e run's last batches)
     barrier()
     clocks = sampler_box.pop().stop() if (headline and rank == 0 and sampler_box) else None
     lat = gc.latency(graph=not args.no_graph) if (rank == 0 or world == 1) else None
@@ -761,8 +754,6 @@ def run_frame_config(args, name, mod, syn, torch, dist, ctx, rank, world, headli
     kms = gc.kernel_times(min(n_steps, 20))
     frames_per_step = F * (1 if shard_cameras else world)
     total = n_steps * frames_per_step
-    h2d, d2h = gc.bytes_per_frame()
-    r0, _ = gc.read(gc.batches[0]) if False else (None, None)
     gc.run_e2e(0, F)   # one batch so that the arena of batch 0 holds a frame to take K from
     r0 = gc.outs[id(gc.batches[0])]
     K = float(np.mean(r0["n"]))
@@ -791,9 +782,11 @@ def run_frame_config(args, name, mod, syn, torch, dist, ctx, rank, world, headli
         "host_enqueue_us_per_batch": round(t_enq, 1) if t_enq is not None else None,
         "launch_chains": "plain launches" if args.no_graph else "CUDA graphs (one per chain, captured at the second use)",
         "e2e": {"value": round(total / (e2e_ms * 1e-3), 2), "unit": "frames/s", "ms_per_step": round(e2e_ms / n_steps, 5),
-                "h2d_bytes_per_step": h2d * F, "d2h_bytes_per_step": d2h * F,
+                "h2d_bytes_per_step": int(h2d * F), "d2h_bytes_per_step": int(d2h * F),
                 "timed": "median of %d runs of K steps (ms: %s)" % (E2E_REPEATS, ", ".join("%.1f" % v for v in e2e_runs)),
-                "pcie_gbs_per_gpu": round(n_steps * F * (h2d + d2h) / (e2e_ms * 1e-3) / 1e9, 1)},
+                "pcie_gbs_per_gpu": round(n_steps * F * (h2d + d2h) / (e2e_ms * 1e-3) / 1e9, 1),
+                "pcie_ceiling_gbs_per_gpu": pcie_ceiling(world if not shard_cameras else min(world, wl["n_cams"])),
+                "pcie_ceiling_source": "profiles/r02_pcie_ceiling.json (copies only, same block sizes, same N)"},
         "gpu_launches": gc.launches_per_batch() * n_steps,
         "roofline": roofline,
     }
@@ -811,6 +804,18 @@ def run_frame_config(args, name, mod, syn, torch, dist, ctx, rank, world, headli
         dist.barrier()     # (the ranks without a camera wait here)
         out["sharding"] += "; %d of the ranks hold a camera" % world
     return out, st
+
+
+def pcie_ceiling(n_gpus):
+    """The committed copy-only ceiling of the box for n_gpus ranks (tools/pcie_ceiling.py), GB/s per GPU with both
+    directions active; None when no run for that N is committed."""
+    p = os.path.join(ROOT, "profiles", "r02_pcie_ceiling.json")
+    if not os.path.exists(p):
+        return None
+    for r in json.load(open(p))["runs"]:
+        if r["n_gpus"] == n_gpus:
+            return r["both_gbs_per_gpu"]
+    return None
 
 
 def ncu_traffic(kernel, images_per_launch):

@@ -500,6 +500,8 @@ typedef struct okc_batch_view {
   const int32_t* motion_n0;
 } okc_batch_view;
 int okc_batch_view_results(okc_batch* batch, okc_batch_view* view);
+/* Measurement hook: the bytes the copies of the last frame (enqueue .. finish) moved host->device and device->host. */
+int okc_batch_transfer_bytes(const okc_batch* batch, uint64_t* h2d, uint64_t* d2h);
 
 int okc_debug_batch_kernel_timing(okc_batch* batch, int enable);
 int okc_debug_batch_kernel_times(okc_batch* batch, char* names, int names_cap, float* ms, int cap, int* n);

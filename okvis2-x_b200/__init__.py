@@ -48,7 +48,7 @@ EXPORTS = [
     "okc_match_to_map", "okc_match_stereo", "okc_match_to_map_uninitialised", "okc_match_motion_stereo",
     "okc_detect_describe_enqueue_device", "okc_map_window_create", "okc_map_window_destroy",
     "okc_camera_match_to_map_enqueue", "okc_camera_frame_finish", "okc_camera_stream", "okc_debug_kernel_timing",
-    "okc_debug_kernel_times", "okc_batch_create", "okc_batch_destroy", "okc_batch_size", "okc_batch_set_graph", "okc_batch_view_results", "okc_batch_enqueue",
+    "okc_debug_kernel_times", "okc_batch_create", "okc_batch_destroy", "okc_batch_size", "okc_batch_set_graph", "okc_batch_view_results", "okc_batch_transfer_bytes", "okc_batch_enqueue",
     "okc_batch_finish", "okc_batch_slot_frame", "okc_batch_slot_matches", "okc_batch_read_all", "okc_batch_stream",
     "okc_debug_batch_kernel_timing", "okc_debug_batch_kernel_times",
     "okc_camera_set_geometry", "okc_batch_set_poses", "okc_batch_slot_back_projections", "okc_landmark_pool_create",
@@ -201,6 +201,7 @@ def lib():
         L.okc_batch_size.argtypes = [vp]
         L.okc_batch_set_graph.argtypes = [vp, C.c_int]
         L.okc_batch_view_results.argtypes = [vp, vp]
+        L.okc_batch_transfer_bytes.argtypes = [vp, vp, vp]
         L.okc_batch_enqueue.argtypes = [vp, vp, i, C.POINTER(DetectParams), vp, vp, vp, i, vp, d, i]
         L.okc_batch_read_all.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp]
         L.okc_batch_finish.argtypes = [vp]
@@ -995,6 +996,12 @@ class Batch:
         _check(lib().okc_batch_read_stages(self.h, *[_p(x) for x in u], _p(uc), *[_p(x) for x in s_], *[_p(x) for x in m_]),
                "okc_batch_read_stages")
         return out
+
+    def transfer_bytes(self):
+        """(host->device, device->host) bytes the last frame's copies moved."""
+        a, b = C.c_uint64(0), C.c_uint64(0)
+        _check(lib().okc_batch_transfer_bytes(self.h, C.byref(a), C.byref(b)), "okc_batch_transfer_bytes")
+        return int(a.value), int(b.value)
 
     def view(self):
         """okc_batch_view_results: the results of a finished frame as numpy arrays that ALIAS the batch's pinned host

@@ -44,5 +44,53 @@ feats = rng.integers(0, 256, (1400, 48), dtype=np.uint8)
 out["vocabulary_transform_1400"] = {"gpu_ms": timed(lambda: voc.transform(feats, 1)),
                                     "cpu_port_ms": timed(lambda: port.vocabulary_transform(*tree, 3, feats, 1), 5),
                                     "note": "the port's time includes flattening the tree in numpy"}
+
+# ---- the same stages as DEVICE-RESIDENT pipeline stages (SURVEY 8 f1 / f2 as built in round 2): the landmark pool
+# lives in HBM (okc_landmark_pool), the pose is the only per-frame input, projections / pruned pool / back-projections
+# never leave the device. Per-stage device time (CUDA events around the stage's launches on the batch's stream) for a
+# batch of B images, next to the CPU port doing the same work for B images one after the other.
+pool = mod.LandmarkPool(ctx, views, hp_W, quality, off, ov, ok)
+for B in (2, 32):
+    cams = [mod.Camera(ctx, 752, 480, max_keypoints=768) for _ in range(2)]
+    for c in cams:
+        c.set_geometry(cam)
+    batch = mod.Batch(ctx, [cams[i % 2] for i in range(B)])
+    imgs = [syn.dense_image(752, 480, 40 + i) for i in range(B)]
+    r_WC = [np.array([0.01 * i, 0.0, -0.2]) for i in range(B)]
+    poses = np.stack([mod.slot_pose(np.eye(3), r) for r in r_WC])
+    batch.kernel_timing(True)
+    acc = {}
+    for rep in range(12):
+        batch.enqueue(imgs, 38.0, 0, 150.0, 700, [(0.0, 1.0, 0.0)] * B)
+        batch.set_poses(poses)
+        batch.match_landmarks_enqueue(pool, 60.0, 4, mod.STAGE_UNINITIALISED)
+        batch.finish()
+        if rep >= 2:
+            for name, ms_ in batch.kernel_times():
+                acc.setdefault(name, []).append(ms_)
+    batch.kernel_timing(False)
+    kp0, _ = batch.slot_frame(0)
+    n_kp = len(kp0)
+    lm = batch.slot_landmarks(0)
+
+    def cpu_landmarks():
+        for i in range(B):
+            T = mod.slot_pose(np.eye(3), r_WC[i])[:12]
+            proj, status, vis = port.project_landmarks(cam, T, hp_W, 30.5)
+            port.prepare_landmarks(views, hp_W, quality, vis, off, ov, ok, r_WC[i], cam.fu + cam.fv)
+
+    def cpu_bp():
+        for i in range(B):
+            port.back_project(cam, kp0)
+    g_prep, g_bp = float(np.median(acc["prepare_landmarks"])), float(np.median(acc["back_project"]))
+    c_prep, c_bp = timed(cpu_landmarks, 3), timed(cpu_bp, 5)
+    out["device_resident_B%d" % B] = {
+        "landmarks": len(hp_W), "visible_landmarks_slot0": int(lm["visible"].sum()), "pool_rows_slot0": int(lm["nm"]),
+        "project+prepare_landmarks": {"gpu_stage_ms": round(g_prep, 4), "cpu_port_ms": c_prep, "speedup": round(c_prep / g_prep, 1)},
+        "back_project_%dkp" % n_kp: {"gpu_stage_ms": round(g_bp, 4), "cpu_port_ms": c_bp, "speedup": round(c_bp / g_bp, 1)}}
+    batch.close()
+    for c in cams:
+        c.close()
+pool.close()
 out["_note"] = "host-buffer calls: cudaMalloc + H2D + kernel + D2H + cudaFree per call dominate the GPU column at these sizes"
 print(json.dumps(out))
