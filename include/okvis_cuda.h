@@ -134,6 +134,24 @@ int okc_match_sets(okc_context* ctx, const okc_descriptor_set* queries, const ok
 int okc_match_sets_ordered(okc_context* ctx, const okc_descriptor_set* queries, const okc_descriptor_set* map,
                            uint32_t threshold, uint64_t index_offset, void* best_device_i64, void* stream_handle);
 
+/* No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it). The same result as
+ * okc_match_batched / okc_match_sets - best[q] = (dist << 32) | (row + index_offset) of the map row with the smallest
+ * Hamming distance strictly below `threshold`, first row wins ties, OKC_NO_MATCH otherwise - with every buffer supplied
+ * by the caller as DEVICE pointers (queries_dev: u8[nq][48], map_dev: u8[nm][48], both 16-byte aligned; best_dev:
+ * uint64[nq]) and the kernels' scratch (per-chunk partial results) in a fixed device array inside the library: the call
+ * allocates nothing - no cudaMalloc / cudaFree / allocating library routine - and only enqueues two kernels on
+ * `stream_handle` (a cudaStream_t, or 0 for the default stream); it does not synchronise.
+ * Limits: nq <= OKC_NO_ALLOC_MAX_QUERIES and nm <= OKC_NO_ALLOC_MAX_MAP_ROWS, beyond them OKC_ERR_CAPACITY. The scratch
+ * (2 MiB) is held by every GPU that loads the library until the process exits, and is shared by ALL calls: calls that
+ * overlap on the GPU (different streams, concurrent graph launches) race on it - serialise them. Nothing in it needs
+ * clearing between calls (a call overwrites every cell it later reads). device < 0: the current device. The first call
+ * on a device looks up the scratch address (cudaGetSymbolAddress): make one call (nq = 0 suffices) before a capture. */
+#define OKC_NO_ALLOC_MAX_QUERIES 4096
+#define OKC_NO_ALLOC_MAX_MAP_ROWS 2147483647LL
+int okc_match_device_no_alloc(int device, const void* queries_dev, int nq, const void* map_dev, int64_t nm,
+                              uint32_t threshold, uint64_t index_offset, uint64_t* best_dev, void* stream_handle);
+
 /* 3D-2D map matching, Frontend::matchToMapByThread (Frontend.cpp:1744-1827) for all thread slices at once.
  * Keypoint k (descriptor queries[k], position kp_xy[2k..]) with use[k] != 0 is compared with every
  * descriptor row m (owner landmark slot map_owner[m], ascending = std::map order) whose landmark projection

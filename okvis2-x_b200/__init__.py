@@ -48,7 +48,7 @@ EXPORTS = [
     "okc_match_to_map", "okc_match_stereo", "okc_match_to_map_uninitialised", "okc_match_motion_stereo",
     "okc_detect_describe_enqueue_device", "okc_map_window_create", "okc_map_window_destroy",
     "okc_camera_match_to_map_enqueue", "okc_camera_frame_finish", "okc_camera_stream", "okc_debug_kernel_timing",
-    "okc_debug_kernel_times", "okc_batch_create", "okc_batch_destroy", "okc_batch_size", "okc_batch_set_graph", "okc_batch_view_results", "okc_batch_transfer_bytes", "okc_batch_enqueue",
+    "okc_debug_kernel_times", "okc_batch_create", "okc_batch_destroy", "okc_batch_size", "okc_batch_set_graph", "okc_batch_view_results", "okc_batch_transfer_bytes", "okc_match_device_no_alloc", "okc_batch_enqueue",
     "okc_batch_finish", "okc_batch_slot_frame", "okc_batch_slot_matches", "okc_batch_read_all", "okc_batch_stream",
     "okc_debug_batch_kernel_timing", "okc_debug_batch_kernel_times",
     "okc_camera_set_geometry", "okc_batch_set_poses", "okc_batch_slot_back_projections", "okc_landmark_pool_create",
@@ -202,6 +202,7 @@ def lib():
         L.okc_batch_set_graph.argtypes = [vp, C.c_int]
         L.okc_batch_view_results.argtypes = [vp, vp]
         L.okc_batch_transfer_bytes.argtypes = [vp, vp, vp]
+        L.okc_match_device_no_alloc.argtypes = [C.c_int, vp, C.c_int, vp, C.c_int64, C.c_uint32, C.c_uint64, vp, vp]
         L.okc_batch_enqueue.argtypes = [vp, vp, i, C.POINTER(DetectParams), vp, vp, vp, i, vp, d, i]
         L.okc_batch_read_all.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp]
         L.okc_batch_finish.argtypes = [vp]
