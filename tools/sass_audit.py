@@ -74,10 +74,11 @@ def main():
             continue
         text = subprocess.run(["nvdisasm", "-g", "-c", cubin], cwd=tmp, capture_output=True, text=True).stdout
         fn, where, sub = None, None, None
+        newton = 0      # instructions left in the window after the head of an inline Newton sequence
         for ln in text.split("\n"):
             m = FUNC.match(ln)
             if m:
-                fn, where, sub = m.group(1), None, None
+                fn, where, sub, newton = m.group(1), None, None, 0
                 continue
             m = SUB.match(ln)
             if m:       # out-of-line slow path of a division / sqrt, placed after the kernel body in the same section
@@ -92,6 +93,10 @@ def main():
             m = FMA.search(ln)
             if re.search(r"^\s+/\*[0-9a-f]{4}\*/", ln):
                 instr[fn] += 1
+                newton -= 1
+            # head of the inline IEEE sqrt / division sequences: the residual 1 - x * y of the MUFU seed's refinement
+            if re.search(r"DFMA R\d+, -?R\d+, -?R\d+, 1 ;", ln):
+                newton = 10
             if m:
                 op = m.group(1)
                 per_kernel[fn][op] += 1
@@ -102,6 +107,8 @@ def main():
                     key = (op, "<constant>", 0, None, None)
                 else:
                     key = (op,) + (where or ("?", 0, None, None))
+                if newton > 0 and op == "DFMA" and not sub:
+                    key = key[:1] + (key[1] + "#newton",) + key[2:]
                 sites[fn][key] += 1
     names = demangle(sorted(per_kernel))
     rows, classes = [], collections.Counter()
@@ -109,6 +116,8 @@ def main():
     for fn in sorted(per_kernel, key=lambda f: -sum(per_kernel[f].values())):
         short = re.sub(r"\(.*", "", names[fn])
         for (op, path, line, ipath, iline), n in sorted(sites[fn].items(), key=lambda kv: (kv[0][1], kv[0][2])):
+            in_newton = path.endswith("#newton")
+            path = path[:-7] if in_newton else path
             text = src(path, line)
             if path == "<constant>":
                 cls, text = "constant load (HFMA2 Rd, -RZ, RZ, imm: no data operand)", ""
@@ -127,10 +136,11 @@ def main():
             if cls.startswith("OTHER") and ipath:
                 cls2 = classify(src(ipath, iline), op)
                 cls = cls2 if not cls2.startswith("OTHER") else cls
-            if path.endswith("sm_32_intrinsics.hpp"):
-                # the MUFU.RSQ64H seed + DFMA(x, -x, 1) / DFMA(.., 0.5) Newton steps + residual of an inline dsqrt that
-                # the scheduler hoisted between the instructions of an inlined __ldg (checked by hand on this build)
-                cls = "IEEE sqrt sequence"
+            if cls.startswith("OTHER") and in_newton or path.endswith("sm_32_intrinsics.hpp"):
+                # MUFU seed + DFMA(x, -y, 1) residual + refinement steps of an inline dsqrt / ddiv that the scheduler moved
+                # next to instructions of another source line (a loop header, an inlined __ldg): recognised by the
+                # sequence's head, the DFMAs of the 10 instructions after it belong to it (checked by hand on this build)
+                cls = "IEEE division / sqrt sequence (moved by the scheduler; recognised by its Newton pattern)"
             if cls.startswith("OTHER") and ("/usr/local/cuda" in path or "libdevice" in path or path == "?"):
                 cls = "libdevice math function"
             classes[(op, cls)] += n
