@@ -253,6 +253,7 @@ struct DescribeArgs {
 // All launchers: `slots` = device array, `n` = number of slots in this launch.
 // aligned: every slot's image pointer is 4-byte aligned and width % 4 == 0 (32-bit pixel loads, int4 score stores)
 void launch_harris_nms(const Slot* slots, int n, const DetectArgs& a, cudaStream_t s, bool aligned);
+size_t harris_score_ints(int W, int H);
 size_t harris_bitmap_words(int W, int H);
 void harris_bitmap_pos(int W, int x, int y, size_t* word, int* bit);
 size_t order_scratch_bytes();

@@ -48,8 +48,10 @@ __host__ __device__ inline int harris_strips(int W) { return (W + kStripCols - 1
 //
 // Score map: the only scores anything reads back are those of the NMS survivors (order_candidates_kernel builds its
 // sort keys from them); the 3x3 ring of the sub-pixel fit is recomputed from the pixels for the few hundred KEPT
-// points (harris_ring_scores). So by default (DENSE = false) a lane stores the score of a survivor only - 4 bytes
-// per candidate instead of 4 bytes per pixel, which was 2/3 of the kernel's DRAM traffic. DENSE = true writes the
+// points (harris_ring_scores). So by default (DENSE = false) only the survivors' scores are stored, compacted per
+// (row, strip) segment: segment (q, strip) holds its survivors' scores in column order at
+// scores[(q * strips + strip) * kStripCols ...] (harris_score_ints() ints per image) - 4 bytes per candidate instead
+// of 4 bytes per pixel, which was 2/3 of the kernel's DRAM traffic. DENSE = true writes the
 // whole map: scale-space layers (scale_nms_kernel interpolates in the neighbouring layers' maps) and okc_debug_scores.
 template <bool ALIGNED, bool DENSE>
 __global__ void __launch_bounds__(32 * kHarrisWarps) harris_nms_kernel(const Slot* __restrict__ slots, int W, int H,
@@ -201,16 +203,27 @@ __global__ void __launch_bounds__(32 * kHarrisWarps) harris_nms_kernel(const Slo
             nib |= (isMax ? 1u : 0u) << c;
           }
           nib &= colBits;
-          if (!DENSE && nib) {
-#pragma unroll
-            for (int c = 0; c < 4; ++c)
-              if (nib & (1u << c)) scores[(size_t)q * W + x + c] = scH[B][c];
-          }
         }
         v = nib << (4 * (lane & 7));
         v |= __shfl_xor_sync(0xffffffffu, v, 1);
         v |= __shfl_xor_sync(0xffffffffu, v, 2);
         v |= __shfl_xor_sync(0xffffffffu, v, 4);
+        if (!DENSE) {
+          // the survivors' scores, compacted per (row, strip) segment in column order: a segment's scores share
+          // 32-byte sectors (scattered 4-byte stores into a dense map cost a sector each, in the store and again in
+          // order_candidates_kernel's load)
+          const int cw = __popc(v);   // survivors of this lane's word (the same in its 8 lanes)
+          const int c0 = __shfl_sync(0xffffffffu, cw, 0), c1 = __shfl_sync(0xffffffffu, cw, 8),
+                    c2 = __shfl_sync(0xffffffffu, cw, 16);
+          if (nib) {
+            const int g = lane >> 3;
+            int rank = (g > 0 ? c0 : 0) + (g > 1 ? c1 : 0) + (g > 2 ? c2 : 0) + __popc(v & ((1u << (4 * (lane & 7))) - 1u));
+            int32_t* seg = scores + ((size_t)q * gridDim.x + strip) * kStripCols;
+#pragma unroll
+            for (int c = 0; c < 4; ++c)
+              if (nib & (1u << c)) seg[rank++] = scH[B][c];
+          }
+        }
       }
       if ((lane & 7) == 0) bitmap[(size_t)q * wordsPerRow + strip * kStripWords + (lane >> 3)] = v;
     }
@@ -261,6 +274,12 @@ void launch_harris_nms(const Slot* slots, int n, const DetectArgs& a, cudaStream
   auto k = a.dense_scores ? (aligned ? harris_nms_kernel<true, true> : harris_nms_kernel<false, true>)
                           : (aligned ? harris_nms_kernel<true, false> : harris_nms_kernel<false, false>);
   k<<<grid, 32 * kHarrisWarps, 0, s>>>(slots, a.width, a.height, a.abs_threshold, rows);
+}
+
+// ints of a slot's score buffer: the dense map (W * H) or the per-segment compact form, whichever is larger
+size_t harris_score_ints(int W, int H) {
+  const size_t seg = (size_t)H * harris_strips(W) * kStripCols, px = (size_t)W * H;
+  return seg > px ? seg : px;
 }
 
 size_t harris_bitmap_words(int W, int H) { return (size_t)H * harris_strips(W) * kStripWords; }
@@ -510,7 +529,7 @@ __device__ int ord_block_partition(const OrdArrays& A, int f, int l, OrdBlockScr
 constexpr int kOrdCoopLen = 1024;   // ranges at least this long are partitioned by the whole CTA
 
 __global__ void __launch_bounds__(kOrdThreads, 1)
-order_candidates_kernel(const Slot* __restrict__ slots, int W, int H) {
+order_candidates_kernel(const Slot* __restrict__ slots, int W, int H, bool denseScores) {
   const Slot& slot = slots[blockIdx.x];
   const int32_t* __restrict__ scores = slot.scores;
   const uint32_t* __restrict__ bitmap = slot.bitmap;
@@ -599,11 +618,16 @@ order_candidates_kernel(const Slot* __restrict__ slots, int W, int H) {
       base += __shfl_sync(0xffffffffu, inc, 31);
       const int y = w / wordsPerRow, rem = w - y * wordsPerRow;
       const int xb = (rem / kStripWords) * kStripCols - 4 + ((rem % kStripWords) << 5);
+      // compact scores (harris_nms_kernel<.., false>): the 4 words of a (row, strip) segment sit in 4 adjacent lanes
+      // (wb is a multiple of 32), a candidate's score is at its rank inside the segment
+      const int excl = inc - c;
+      int segRank = excl - __shfl_sync(0xffffffffu, excl, lane & ~(kStripWords - 1));
+      const int32_t* __restrict__ seg = scores + (size_t)(w / kStripWords) * kStripCols;
       while (bits) {
         const int b = __ffs(bits) - 1;
         bits &= bits - 1;
         const uint32_t raster = (uint32_t)(y * W + xb + b);
-        A.sc[pos] = scores[raster];
+        A.sc[pos] = denseScores ? scores[raster] : seg[segRank++];
         A.ra[pos] = raster;
         ++pos;
       }
@@ -722,7 +746,7 @@ void launch_order_candidates(const Slot* slots, int n, const DetectArgs& a, cuda
     cudaFuncSetAttribute(order_candidates_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kOrdSmemBytes);
     configured[dev & 63] = true;
   }
-  order_candidates_kernel<<<n, kOrdThreads, kOrdSmemBytes, s>>>(slots, a.width, a.height);
+  order_candidates_kernel<<<n, kOrdThreads, kOrdSmemBytes, s>>>(slots, a.width, a.height, a.dense_scores);
 }
 
 // ----------------------------------------------------------------------------------------------
