@@ -134,6 +134,9 @@ struct StereoJob {
   double* hp;
   uint8_t* init;
   double* quality;          // motion stereo only
+  // scratch of the two-kernel scheme (match.cu): per k0 up to kCandPerQuery candidates (k1 << 9) | dist and their count
+  unsigned* cand;
+  int* cand_count;
 };
 
 struct UninitArgs {
@@ -171,10 +174,15 @@ struct UninitJob {
   uint8_t* hp_written;
   unsigned* ctr;                  // per keypoint, or null
   unsigned long long* slice_ctrs; // per thread slice (added to), or null
+  // scratch of the two-kernel scheme (match.cu): per keypoint up to kCandPerQuery candidates (row << 9) | dist, count
+  unsigned* cand;
+  int* cand_count;
 };
-void launch_match_stereo_jobs(const StereoJob* jobs, int nJobs, int max0, bool motion, double hammingThreshold,
-                              cudaStream_t s);
-void launch_match_uninit_jobs(const UninitJob* jobs, int nJobs, int maxNk, cudaStream_t s);
+constexpr int kCandPerQuery = 32;   // candidate rows kept per query by the filter kernels of the gated matchers
+void launch_match_stereo_jobs(const StereoJob* jobs, int nJobs, int max0, int max1, bool motion, double hammingThreshold,
+                              int* cand_counts, size_t n_counts, cudaStream_t s);
+void launch_match_uninit_jobs(const UninitJob* jobs, int nJobs, int maxNk, int maxRows, double hammingThreshold,
+                              int* cand_counts, size_t n_counts, cudaStream_t s);
 void launch_back_project_slots(const Slot* slots, int n, int max_kp, cudaStream_t s);
 // per slot: the keypoints without a landmark after the two map matchers (owner_a[k] < 0 and owner_b[k] < 0; a null
 // array counts as "none matched"), ascending, into list[slot * max_kp ..] with their number in count[slot]

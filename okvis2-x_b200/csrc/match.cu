@@ -913,169 +913,241 @@ __device__ __forceinline__ double side_size(const StereoSide& v, int k) {
   return v.size_d ? v.size_d[k] : (double)v.kp[k].size;
 }
 
-// Work layout as in match_uninitialised_kernel below: a CTA takes 8 * Q consecutive k0, compacts the eligible ones,
-// every warp sweeps the k1 rows once for its Q queries (integer bound for the fast test, FP64 gates for the few
-// rows that pass it, per-query state in shared memory).
-struct StereoState {
-  double dist, quality, size0;
-  V3 hps, e0;
-  int k1, k0, init, valid0;
-};
+// Work layout (shared with the uninitialised-landmark matcher below): two kernels.
+//   1. filter  - every (query, row) pair's Hamming distance, the whole GPU at once: a CTA compacts the eligible ones of
+//      32 consecutive queries, a warp keeps Q of them in registers and sweeps ITS chunk of the rows (grid.z), one row
+//      per lane and tile, the next tile requested before this one is compared. A pair below the threshold is appended
+//      to the query's candidate list ((row << 9) | dist, kCandPerQuery entries; more -> the count says "overflow").
+//      Unrelated descriptors are ~192 bits apart, so the lists hold the true match and a few look-alikes.
+//   2. resolve - one thread per query runs the reference's loop body over its candidates in ascending row order (= the
+//      order in which the reference visits them). A query whose list overflowed walks all rows itself with the same
+//      code - results are identical either way.
+// The reference's loop is sequential per query only through the running best; everything else is per pair.
+constexpr int kFilterQ = 4;         // queries a filter warp keeps in registers
+constexpr int kFilterRows = 512;    // rows per filter CTA (grid.z chunks)
+constexpr int kCandRowShift = 9;    // candidate = (row << 9) | dist, dist <= 384
+constexpr int kCandMaxRows = 1 << (32 - kCandRowShift);
 
-template <bool MOTION, int Q>
-__global__ void __launch_bounds__(256)
-match_stereo_kernel(const StereoJob* __restrict__ jobs, double hammingThreshold) {
-  constexpr int kWarps = 8, kChunk = kWarps * Q;
-  static_assert(kChunk <= 32, "one ballot compacts the chunk");
-  __shared__ int s_list[kChunk];
+// rows [lo, hi) of `rowDesc` (through `rowOf`: row index and liveness of sweep position i) against the Q queries of a
+// warp; q[j] valid for j < nq, out[j] = the query's index into cand / count
+template <class RowOf>
+__device__ __forceinline__ void filter_sweep(const uint8_t* __restrict__ rowDesc, RowOf rowOf, int lo, int hi,
+                                             const unsigned (&q)[kFilterQ][kDescWords], int nq, const int (&out)[kFilterQ],
+                                             int thr, unsigned* __restrict__ cand, int* __restrict__ count) {
+  const int lane = threadIdx.x & 31;
+  unsigned r[kDescWords], rNext[kDescWords];
+  int m = 0, mNext = 0;
+  bool live = rowOf(lo + lane, hi, m), liveNext = false;
+  if (live) load_desc(rowDesc, m, r);
+  for (int base = lo; base < hi; base += 32) {
+    liveNext = rowOf(base + 32 + lane, hi, mNext);
+    if (liveNext) load_desc(rowDesc, mNext, rNext);
+    // first the 6-word prefix (a lower bound of the distance): most tiles hold no pair below the threshold
+    int d6[kFilterQ];
+    bool any = false;
+#pragma unroll
+    for (int j = 0; j < kFilterQ; ++j) {
+      int d = 0;
+#pragma unroll
+      for (int w = 0; w < 6; ++w) d += __popc(q[j][w] ^ r[w]);
+      d6[j] = d;
+      any |= live && j < nq && d < thr;
+    }
+    if (__any_sync(0xffffffffu, any)) {
+#pragma unroll
+      for (int j = 0; j < kFilterQ; ++j) {
+        int d = d6[j];
+#pragma unroll
+        for (int w = 6; w < kDescWords; ++w) d += __popc(q[j][w] ^ r[w]);
+        if (live && j < nq && d < thr) {
+          const int pos = atomicAdd(count + out[j], 1);
+          if (pos < kCandPerQuery) cand[(size_t)out[j] * kCandPerQuery + pos] = ((unsigned)m << kCandRowShift) | (unsigned)d;
+        }
+      }
+    }
+#pragma unroll
+    for (int w = 0; w < kDescWords; ++w) r[w] = rNext[w];
+    m = mNext;
+    live = liveNext;
+  }
+}
+
+__device__ __forceinline__ bool stereo_takes_part(const StereoJob& job, int k0, bool motion) {
+  // motion stereo: k0 must be eligible (Frontend.cpp:2056-2064, 2082-2084); plain stereo accepts no candidate for a k0
+  // without a valid back-projection (:2275-2277), so the filter can leave it out
+  return motion ? ((!job.use0 || job.use0[k0]) && job.v0.bp_valid[k0]) : job.v0.bp_valid[k0] != 0;
+}
+struct StereoRowOf {
+  const int* list1;
+  const int* oa;
+  const int* ob;
+  __device__ __forceinline__ bool operator()(int i, int hi, int& k1) const {
+    if (i >= hi) return false;
+    k1 = list1 ? list1[i] : i;
+    return !(oa && oa[k1] >= 0) && !(ob && ob[k1] >= 0);
+  }
+};
+__device__ __forceinline__ int stereo_rows(const StereoJob& job) {
+  // candidates k1: every keypoint of v1, or a precompacted ascending list (the slot's keypoints without a landmark)
+  const StereoSide& v1 = job.v1;
+  return job.v1_list ? min(*job.v1_list_n, v1.n) : (v1.n_dev ? min(*v1.n_dev, v1.n) : v1.n);
+}
+
+template <bool MOTION>
+__global__ void __launch_bounds__(128) stereo_filter_kernel(const StereoJob* __restrict__ jobs, int thr) {
+  __shared__ int s_list[32];
   __shared__ int s_n;
-  __shared__ StereoState s_state[kWarps][Q];
   const StereoJob& job = jobs[blockIdx.y];
   const StereoSide& v0 = job.v0;
-  const StereoSide& v1 = job.v1;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int n0 = v0.n_dev ? min(*v0.n_dev, v0.n) : v0.n;
-  const int kBase = blockIdx.x * kChunk;
-  if (kBase >= n0) return;
-  double* __restrict__ outDist = job.dist;
-  int* __restrict__ outK1 = job.k1;
-  double* __restrict__ outHp = job.hp;
-  uint8_t* __restrict__ outInit = job.init;
+  const int kBase = blockIdx.x * 32;
+  const int n1 = stereo_rows(job);
+  const int lo = blockIdx.z * kFilterRows;
+  if (kBase >= n0 || lo >= n1) return;
+  const int hi = min(n1, lo + kFilterRows);
   if (warp == 0) {
     const int k0 = kBase + lane;
-    const bool inChunk = lane < kChunk && k0 < n0;
-    const bool use = inChunk && (!MOTION || ((!job.use0 || job.use0[k0]) && v0.bp_valid[k0]));
+    const bool use = k0 < n0 && stereo_takes_part(job, k0, MOTION);
     const unsigned bal = __ballot_sync(0xffffffffu, use);
     if (use) s_list[__popc(bal & ((1u << lane) - 1u))] = k0;
     if (lane == 0) s_n = __popc(bal);
-    if (inChunk && !use) {   // (MOTION only) a k0 that is not eligible
-      outDist[k0] = hammingThreshold;
-      outK1[k0] = -1;
-      outHp[4 * k0 + 0] = outHp[4 * k0 + 1] = outHp[4 * k0 + 2] = outHp[4 * k0 + 3] = 0.0;
-      outInit[k0] = 0;
-      job.quality[k0] = 0.0;
-    }
   }
   __syncthreads();
-  const int g0 = warp * Q;
-  if (g0 >= s_n) return;
-  const int nq = min(Q, s_n - g0);
-  // candidates k1: every keypoint of v1, or a precompacted ascending list (the slot's keypoints without a landmark)
-  const int* __restrict__ list1 = job.v1_list;
-  const int n1 = list1 ? min(*job.v1_list_n, v1.n) : (v1.n_dev ? min(*v1.n_dev, v1.n) : v1.n);
+  const int nUse = s_n;
+  const StereoRowOf rowOf{job.v1_list, job.v1_owner_a, job.v1_owner_b};
+  for (int g0 = warp * kFilterQ; g0 < nUse; g0 += 4 * kFilterQ) {
+    const int nq = min(kFilterQ, nUse - g0);
+    unsigned q[kFilterQ][kDescWords];
+    int out[kFilterQ];
+#pragma unroll
+    for (int j = 0; j < kFilterQ; ++j) {
+      out[j] = s_list[g0 + min(j, nq - 1)];
+      load_desc(v0.desc, out[j], q[j]);
+    }
+    filter_sweep(job.v1.desc, rowOf, lo, hi, q, nq, out, thr, job.cand, job.cand_count);
+  }
+}
+
+// next candidate of a query in ascending row order: the smallest packed value above `last` (lists are short: a scan)
+__device__ __forceinline__ unsigned next_candidate(const unsigned* __restrict__ list, int cnt, unsigned last, bool first) {
+  unsigned best = ~0u;
+  for (int i = 0; i < cnt; ++i) {
+    const unsigned v = list[i];
+    if ((first || v > last) && v < best) best = v;
+  }
+  return best;
+}
+
+// resolve: one THREAD per k0. The gates are ~3 000 FP64 instructions (IEEE divisions, square roots, cos, acos) per
+// candidate that beats the running best and a query has about one candidate: a warp per query would run them for one
+// lane's benefit.
+template <bool MOTION>
+__global__ void __launch_bounds__(128)
+match_stereo_kernel(const StereoJob* __restrict__ jobs, double hammingThreshold) {
+  const StereoJob& job = jobs[blockIdx.y];
+  const StereoSide& v0 = job.v0;
+  const StereoSide& v1 = job.v1;
+  const int k0 = blockIdx.x * blockDim.x + threadIdx.x;
+  const int n0 = v0.n_dev ? min(*v0.n_dev, v0.n) : v0.n;
+  if (k0 >= n0) return;
+  if (MOTION && !stereo_takes_part(job, k0, true)) {
+    job.dist[k0] = hammingThreshold;
+    job.k1[k0] = -1;
+    job.hp[4 * k0 + 0] = job.hp[4 * k0 + 1] = job.hp[4 * k0 + 2] = job.hp[4 * k0 + 3] = 0.0;
+    job.init[k0] = 0;
+    job.quality[k0] = 0.0;
+    return;
+  }
   // poses: by value, or from the batch slot's record (the job table then stays valid from frame to frame)
   const double* __restrict__ C0 = v0.pose_slot ? v0.pose_slot->C_WC : v0.C;
   const double* __restrict__ C1 = v1.pose_slot ? v1.pose_slot->C_WC : v1.C;
   const double* __restrict__ p0 = v0.pose_slot ? v0.pose_slot->r_WC : v0.r;
   const double* __restrict__ p1 = v1.pose_slot ? v1.pose_slot->r_WC : v1.r;
   const V3 r0 = v3(p0[0], p0[1], p0[2]), r1 = v3(p1[0], p1[1], p1[2]);
-  unsigned q[Q][kDescWords];
-  int bound[Q];   // ceil(running best): the integer form of "d < distances"
-#pragma unroll
-  for (int j = 0; j < Q; ++j) {
-    load_desc(v0.desc, s_list[g0 + min(j, nq - 1)], q[j]);
-    bound[j] = j < nq ? (int)ceil(hammingThreshold) : 0;
-  }
-  if (lane < nq) {
-    StereoState& st = s_state[warp][lane];
-    const int k0 = s_list[g0 + lane];
-    st.k0 = k0;
-    st.dist = hammingThreshold;
-    st.quality = 0.0;
-    st.hps = v3(0.0, 0.0, 0.0);
-    st.k1 = MOTION ? -1 : 0;
-    st.init = 0;
-    st.valid0 = v0.bp_valid[k0] ? 1 : 0;
-    st.size0 = side_size(v0, k0);
-    st.e0 = normalized(matvec(C0, v3(v0.e_C[3 * k0], v0.e_C[3 * k0 + 1], v0.e_C[3 * k0 + 2])));
-  }
-  __syncwarp();
-  for (int base = 0; base < n1; base += 32) {
-    const int i1 = base + lane;
-    const int k1 = i1 < n1 ? (list1 ? list1[i1] : i1) : 0;
-    const bool live =
-        i1 < n1 && !(job.v1_owner_a && job.v1_owner_a[k1] >= 0) && !(job.v1_owner_b && job.v1_owner_b[k1] >= 0);
-    unsigned r[kDescWords];
-    if (live) load_desc(v1.desc, k1, r);
-#pragma unroll
-    for (int j = 0; j < Q; ++j) {
-      const int d = live ? (int)hamming384(q[j], r) : (1 << 20);
-      unsigned pending = __ballot_sync(0xffffffffu, d < bound[j]);
-      if (!pending) continue;
-      StereoState& st = s_state[warp][j];
-      double distances = st.dist, quality = st.quality;
-      V3 hps = st.hps;
-      int k1_match = st.k1, initialisable = st.init;
-      const V3 e0_W = st.e0;
-      const double size0 = st.size0;
-      const bool valid0 = st.valid0 != 0;
-      bool changed = false;
-      while (pending) {  // sparse: geometry only for candidates below the running best, in k1 order
-        const int src = __ffs(pending) - 1;
-        pending &= pending - 1;
-        const double dc = (double)__shfl_sync(0xffffffffu, d, src);
-        const int kc = __shfl_sync(0xffffffffu, k1, src);
-        if (!(dc < distances)) continue;
-        if (!valid0) continue;
-        if (!v1.bp_valid[kc]) continue;
-        const double sigma = MOTION ? size0 / v0.f * 0.125 : fmax(size0 / v0.f, side_size(v1, kc) / v1.f) * 0.125;
-        const V3 e1_W = normalized(matvec(C1, v3(v1.e_C[3 * kc], v1.e_C[3 * kc + 1], v1.e_C[3 * kc + 2])));
-        if (MOTION && dot(e0_W, e1_W) < 0.5) continue;
-        bool isValid = false, isParallel = false;
-        const V3 hp = triangulate_fast(r0, e0_W, r1, e1_W, cos(2.6 * sigma), cos(6.0 * sigma), isValid, isParallel);
-        if (MOTION && !isValid) continue;
-        // T_WC.inverse() * hp_W with w = 1: C^T * p + (-(C^T * r)) * 1; z / w compared with 0.1
-        const V3 t0 = matTvec(C0, r0), t1 = matTvec(C1, r1);
-        const V3 c0 = matTvec(C0, hp), c1 = matTvec(C1, hp);
-        const double z0 = c0.z + (-t0.z) * 1.0, z1 = c1.z + (-t1.z) * 1.0;
-        const double minDepth = MOTION ? 0.2 : 0.1;
-        if (z0 / 1.0 < minDepth) isValid = false;
-        if (z1 / 1.0 < minDepth) isValid = false;
-        if (dot(e0_W, e1_W) < 0.8) isValid = false;
-        if (isValid) {
-          distances = dc;
-          hps = hp;
-          k1_match = kc;
-          initialisable = isParallel ? 0 : 1;
-          if (MOTION) quality = acos(dot(normalized(hp - r0), normalized(hp - r1)));
-          changed = true;
-        }
+  const bool valid0 = v0.bp_valid[k0] != 0;
+  // running state of the reference's loop over k1
+  double distances = hammingThreshold, quality = 0.0;
+  V3 hps = v3(0.0, 0.0, 0.0);
+  int k1_match = MOTION ? -1 : 0;
+  bool initialisable = false;
+  const int cnt = valid0 ? job.cand_count[k0] : 0;
+  if (cnt > 0) {
+    const double size0 = side_size(v0, k0);
+    const V3 e0_W = normalized(matvec(C0, v3(v0.e_C[3 * k0], v0.e_C[3 * k0 + 1], v0.e_C[3 * k0 + 2])));
+    auto visit = [&](int kc, double dc) {   // the body of the reference's loop for a k1 with dist < threshold
+      if (!(dc < distances)) return;
+      if (!v1.bp_valid[kc]) return;
+      const double sigma = MOTION ? size0 / v0.f * 0.125 : fmax(size0 / v0.f, side_size(v1, kc) / v1.f) * 0.125;
+      const V3 e1_W = normalized(matvec(C1, v3(v1.e_C[3 * kc], v1.e_C[3 * kc + 1], v1.e_C[3 * kc + 2])));
+      if (MOTION && dot(e0_W, e1_W) < 0.5) return;
+      bool isValid = false, isParallel = false;
+      const V3 hp = triangulate_fast(r0, e0_W, r1, e1_W, cos(2.6 * sigma), cos(6.0 * sigma), isValid, isParallel);
+      if (MOTION && !isValid) return;
+      // T_WC.inverse() * hp_W with w = 1: C^T * p + (-(C^T * r)) * 1; z / w compared with 0.1
+      const V3 t0 = matTvec(C0, r0), t1 = matTvec(C1, r1);
+      const V3 c0 = matTvec(C0, hp), c1 = matTvec(C1, hp);
+      const double z0 = c0.z + (-t0.z) * 1.0, z1 = c1.z + (-t1.z) * 1.0;
+      const double minDepth = MOTION ? 0.2 : 0.1;
+      if (z0 / 1.0 < minDepth) isValid = false;
+      if (z1 / 1.0 < minDepth) isValid = false;
+      if (dot(e0_W, e1_W) < 0.8) isValid = false;
+      if (isValid) {
+        distances = dc;
+        hps = hp;
+        k1_match = kc;
+        initialisable = !isParallel;
+        if (MOTION) quality = acos(dot(normalized(hp - r0), normalized(hp - r1)));
       }
-      if (changed) {
-        if (lane == 0) {
-          st.dist = distances;
-          st.quality = quality;
-          st.hps = hps;
-          st.k1 = k1_match;
-          st.init = initialisable;
-        }
-        bound[j] = (int)ceil(distances);
+    };
+    if (cnt <= kCandPerQuery) {   // the listed candidates, in k1 order
+      const unsigned* __restrict__ list = job.cand + (size_t)k0 * kCandPerQuery;
+      unsigned last = 0;
+      for (int i = 0; i < cnt; ++i) {
+        last = next_candidate(list, cnt, last, i == 0);
+        visit((int)(last >> kCandRowShift), (double)(last & ((1u << kCandRowShift) - 1u)));
       }
-      __syncwarp();
+    } else {                      // the list overflowed (or no filter ran): every row, as the reference does
+      const int n1 = stereo_rows(job);
+      const StereoRowOf rowOf{job.v1_list, job.v1_owner_a, job.v1_owner_b};
+      unsigned q[kDescWords];
+      load_desc(v0.desc, k0, q);
+      for (int i = 0; i < n1; ++i) {
+        int kc;
+        if (!rowOf(i, n1, kc)) continue;
+        unsigned r[kDescWords];
+        load_desc(v1.desc, kc, r);
+        visit(kc, (double)hamming384(q, r));
+      }
     }
   }
-  __syncwarp();
-  if (lane < nq) {
-    const StereoState& st = s_state[warp][lane];
-    const int k0 = st.k0;
-    outDist[k0] = st.dist;
-    outK1[k0] = st.k1;
-    outHp[4 * k0 + 0] = st.hps.x / 1.0;
-    outHp[4 * k0 + 1] = st.hps.y / 1.0;
-    outHp[4 * k0 + 2] = st.hps.z / 1.0;
-    outHp[4 * k0 + 3] = (MOTION && st.k1 < 0) ? 0.0 : 1.0;
-    outInit[k0] = st.init ? 1 : 0;
-    if (MOTION) job.quality[k0] = st.quality;
-  }
+  job.dist[k0] = distances;
+  job.k1[k0] = k1_match;
+  job.hp[4 * k0 + 0] = hps.x / 1.0;
+  job.hp[4 * k0 + 1] = hps.y / 1.0;
+  job.hp[4 * k0 + 2] = hps.z / 1.0;
+  job.hp[4 * k0 + 3] = (MOTION && k1_match < 0) ? 0.0 : 1.0;
+  job.init[k0] = initialisable ? 1 : 0;
+  if (MOTION) job.quality[k0] = quality;
 }
 
-void launch_match_stereo_jobs(const StereoJob* jobs, int nJobs, int max0, bool motion, double hammingThreshold,
-                              cudaStream_t s) {
+// cand_counts: the jobs' candidate counters (one int per query), n_counts of them, cleared here; max1: upper bound of
+// the rows (k1) of a job
+void launch_match_stereo_jobs(const StereoJob* jobs, int nJobs, int max0, int max1, bool motion, double hammingThreshold,
+                              int* cand_counts, size_t n_counts, cudaStream_t s) {
   if (nJobs <= 0 || max0 <= 0) return;
-  constexpr int Q = 4, chunk = 8 * Q;   // k0 per CTA (8 warps x Q queries)
-  const dim3 grid((max0 + chunk - 1) / chunk, nJobs);
-  if (motion) match_stereo_kernel<true, Q><<<grid, 256, 0, s>>>(jobs, hammingThreshold);
-  else match_stereo_kernel<false, Q><<<grid, 256, 0, s>>>(jobs, hammingThreshold);
+  const int thr = (int)ceil(hammingThreshold);
+  const bool filter = max1 > 0 && max1 < kCandMaxRows && thr <= 385;
+  // (counters of 0x7f7f7f7f = "overflow": every query then sweeps the rows itself)
+  cudaMemsetAsync(cand_counts, filter ? 0 : 0x7f, n_counts * sizeof(int), s);
+  if (filter) {
+    const dim3 fgrid((max0 + 31) / 32, nJobs, (max1 + kFilterRows - 1) / kFilterRows);
+    if (motion) stereo_filter_kernel<true><<<fgrid, 128, 0, s>>>(jobs, thr);
+    else stereo_filter_kernel<false><<<fgrid, 128, 0, s>>>(jobs, thr);
+  }
+  const dim3 grid((max0 + 127) / 128, nJobs);
+  if (motion) match_stereo_kernel<true><<<grid, 128, 0, s>>>(jobs, hammingThreshold);
+  else match_stereo_kernel<false><<<grid, 128, 0, s>>>(jobs, hammingThreshold);
 }
 
 // ----------------------------------------------------------------------------------------------
@@ -1086,183 +1158,161 @@ void launch_match_stereo_jobs(const StereoJob* jobs, int nJobs, int max0, bool m
 // (:1922-1927), >= 0.2 m from both centres (:1930-1936). Loop-closure rule (:1941-1944): an accepted row of the
 // keypoint's previous landmark only counts and ends that landmark's rows for this keypoint. hps_W is overwritten
 // only by non-parallel accepts (stale value kept otherwise, :1946-1951).
-//
-// Work layout: a CTA takes a chunk of 8 * Q consecutive keypoints, compacts those that take part (most keypoints of
-// a tracked frame already have a landmark from matchToMapByThread) and gives every warp Q of them. A warp loads a
-// tile of 32 rows ONCE (one row per lane, in registers) and compares it with its Q queries: the row sweep is bound
-// by the L1/L2 traffic of the rows, so Q queries per load divide the time by almost Q. The running best of a query
-// is kept as an integer bound for the fast test (d < best with integer d  <=>  d < ceil(best)); the rare rows that
-// pass it go through the FP64 gates with the per-query state in shared memory, in ascending row order per query,
-// exactly as the one-query-per-warp formulation did.
-struct UninitState {
-  double best;
-  V3 hps, e1;
-  int bestO, skipOwner, prev, k;
-  unsigned ctr;
-  int hpWritten;
+// Same two kernels as the 2D-2D matchers above: uninit_filter_kernel lists the rows below the threshold per keypoint,
+// match_uninitialised_kernel resolves a keypoint per warp.
+__device__ __forceinline__ bool uninit_takes_part(const UninitJob& job, int k) {
+  // Frontend.cpp:1862-1872: a keypoint takes part when its back-projection is valid and it has no landmark yet
+  if (job.use && job.use[k] == 0) return false;
+  if (job.bp_valid && !job.bp_valid[k]) return false;
+  if (job.owner14 && job.owner14[k] >= 0) return false;
+  return true;
+}
+struct UninitRowOf {
+  const int* rowList;
+  const uint8_t* is3d;
+  const int* owner;
+  __device__ __forceinline__ bool operator()(int i, int hi, int& m) const {
+    if (i >= hi) return false;
+    m = rowList ? rowList[i] : i;
+    return !(!rowList && is3d && is3d[owner[m]]);
+  }
 };
+__device__ __forceinline__ int uninit_rows(const UninitJob& job) {
+  // rows to sweep: all of the pool, or a precompacted ascending list (the rows of the non-3D landmarks)
+  return job.row_list ? min(*job.n_list_dev, job.nm) : (job.nm_dev ? min(*job.nm_dev, job.nm) : job.nm);
+}
 
-template <int Q>
-__global__ void __launch_bounds__(256) match_uninitialised_kernel(const UninitJob* __restrict__ jobs) {
-  constexpr int kWarps = 8, kChunk = kWarps * Q;
-  static_assert(kChunk <= 32, "one ballot compacts the chunk");
-  __shared__ int s_list[kChunk];
+__global__ void __launch_bounds__(128) uninit_filter_kernel(const UninitJob* __restrict__ jobs) {
+  __shared__ int s_list[32];
   __shared__ int s_n;
-  __shared__ UninitState s_state[kWarps][Q];
   const UninitJob& job = jobs[blockIdx.y];
-  const UninitArgs& a = job.a;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int nk = job.nk_dev ? min(*job.nk_dev, job.nk) : job.nk;
-  const int k0 = blockIdx.x * kChunk;
-  if (k0 >= nk) return;
+  const int kBase = blockIdx.x * 32;
+  const int nm = uninit_rows(job);
+  const int lo = blockIdx.z * kFilterRows;
+  if (kBase >= nk || lo >= nm) return;
+  const int hi = min(nm, lo + kFilterRows);
   if (warp == 0) {
-    const int k = k0 + lane;
-    const bool inChunk = lane < kChunk && k < nk;
-    // Frontend.cpp:1862-1872: a keypoint takes part when its back-projection is valid and it has no landmark yet
-    bool use = inChunk && (job.use ? job.use[k] != 0 : true);
-    if (use && job.bp_valid && !job.bp_valid[k]) use = false;
-    if (use && job.owner14 && job.owner14[k] >= 0) use = false;
+    const int k = kBase + lane;
+    const bool use = k < nk && uninit_takes_part(job, k);
     const unsigned bal = __ballot_sync(0xffffffffu, use);
     if (use) s_list[__popc(bal & ((1u << lane) - 1u))] = k;
     if (lane == 0) s_n = __popc(bal);
-    if (inChunk && !use) {   // untouched outputs of a keypoint that does not take part
-      job.dist[k] = a.hammingThreshold;
-      job.best[k] = -1;
-      job.hp[4 * k + 0] = 0.0;
-      job.hp[4 * k + 1] = 0.0;
-      job.hp[4 * k + 2] = 0.0;
-      job.hp[4 * k + 3] = 0.0;
-      job.hp_written[k] = 0;
-      if (job.ctr) job.ctr[k] = 0;
-    }
   }
   __syncthreads();
-  const int g0 = warp * Q;
-  if (g0 >= s_n) return;
-  const int nq = min(Q, s_n - g0);
-  // rows to sweep: all of the pool, or a precompacted ascending list (the rows of the non-3D landmarks)
-  const int* __restrict__ rowList = job.row_list;
-  const int nm = rowList ? min(*job.n_list_dev, job.nm) : (job.nm_dev ? min(*job.nm_dev, job.nm) : job.nm);
-  const uint8_t* __restrict__ map = job.map;
-  const int* __restrict__ owner = job.owner;
-  const double* __restrict__ map_e_W = job.map_e_W;
-  const double* __restrict__ map_r_W = job.map_r_W;
-  const double* __restrict__ rc = job.pose_slot ? job.pose_slot->r_WC : a.r_WC;
-  const V3 rC = v3(rc[0], rc[1], rc[2]);
-  unsigned q[Q][kDescWords];
-  int bound[Q];   // ceil(best): the integer form of "d < best"
+  const int nUse = s_n;
+  const UninitRowOf rowOf{job.row_list, job.is3d, job.owner};
+  const int thr = (int)ceil(job.a.hammingThreshold);
+  for (int g0 = warp * kFilterQ; g0 < nUse; g0 += 4 * kFilterQ) {
+    const int nq = min(kFilterQ, nUse - g0);
+    unsigned q[kFilterQ][kDescWords];
+    int out[kFilterQ];
 #pragma unroll
-  for (int j = 0; j < Q; ++j) {
-    const int k = s_list[g0 + min(j, nq - 1)];
-    load_desc(job.queries, k, q[j]);
-    bound[j] = j < nq ? (int)ceil(a.hammingThreshold) : 0;
+    for (int j = 0; j < kFilterQ; ++j) {
+      out[j] = s_list[g0 + min(j, nq - 1)];
+      load_desc(job.queries, out[j], q[j]);
+    }
+    filter_sweep(job.map, rowOf, lo, hi, q, nq, out, thr, job.cand, job.cand_count);
   }
-  if (lane < nq) {
-    UninitState& st = s_state[warp][lane];
-    const int k = s_list[g0 + lane];
-    st.k = k;
-    st.best = a.hammingThreshold;
-    st.bestO = -1;
-    st.skipOwner = -1;
-    st.ctr = 0;
-    st.hps = v3(0.0, 0.0, 0.0);
-    st.hpWritten = 0;
-    st.prev = job.previousOwner ? job.previousOwner[k] : -1;
+}
+
+// resolve: one thread per keypoint (see match_stereo_kernel)
+__global__ void __launch_bounds__(128) match_uninitialised_kernel(const UninitJob* __restrict__ jobs) {
+  const UninitJob& job = jobs[blockIdx.y];
+  const UninitArgs& a = job.a;
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  const int nk = job.nk_dev ? min(*job.nk_dev, job.nk) : job.nk;
+  if (k >= nk) return;
+  // running state of the reference's loop over the rows
+  double best = a.hammingThreshold;
+  int bestO = -1, skipOwner = -1;
+  bool hpWritten = false;
+  unsigned ctr = 0;
+  V3 hps = v3(0.0, 0.0, 0.0);
+  const int cnt = uninit_takes_part(job, k) ? job.cand_count[k] : 0;
+  if (cnt > 0) {
+    const int* __restrict__ owner = job.owner;
+    const double* __restrict__ map_e_W = job.map_e_W;
+    const double* __restrict__ map_r_W = job.map_r_W;
+    V3 e1_W;
     if (job.kp_e_W) {
-      st.e1 = v3(job.kp_e_W[3 * k], job.kp_e_W[3 * k + 1], job.kp_e_W[3 * k + 2]);
+      e1_W = v3(job.kp_e_W[3 * k], job.kp_e_W[3 * k + 1], job.kp_e_W[3 * k + 2]);
     } else {   // T_WC1.C() * e1_C.normalized()
-      st.e1 = matvec(job.pose_slot ? job.pose_slot->C_WC : job.C_WC,
-                     normalized(v3(job.e_C[3 * k], job.e_C[3 * k + 1], job.e_C[3 * k + 2])));
+      e1_W = matvec(job.pose_slot ? job.pose_slot->C_WC : job.C_WC,
+                    normalized(v3(job.e_C[3 * k], job.e_C[3 * k + 1], job.e_C[3 * k + 2])));
     }
-  }
-  __syncwarp();
-  for (int base = 0; base < nm; base += 32) {
-    const int i = base + lane;
-    const int m = i < nm ? (rowList ? rowList[i] : i) : 0;
-    const bool live = i < nm && !(!rowList && job.is3d && job.is3d[owner[m]]);
-    unsigned r[kDescWords];
-    if (live) load_desc(map, m, r);
-#pragma unroll
-    for (int j = 0; j < Q; ++j) {
-      const int d = live ? (int)hamming384(q[j], r) : (1 << 20);
-      unsigned pending = __ballot_sync(0xffffffffu, d < bound[j]);
-      if (!pending) continue;
-      // the state of query j, warp-uniform in registers for the duration of this tile's candidates
-      UninitState& st = s_state[warp][j];
-      double best = st.best;
-      int bestO = st.bestO, skipOwner = st.skipOwner, hpWritten = st.hpWritten;
-      unsigned ctr = st.ctr;
-      V3 hps = st.hps;
-      const V3 e1_W = st.e1;
-      const int prev = st.prev;
-      while (pending) {
-        const int src = __ffs(pending) - 1;
-        pending &= pending - 1;
-        const double dc = (double)__shfl_sync(0xffffffffu, d, src);
-        const int mc = __shfl_sync(0xffffffffu, m, src);
-        if (!(dc < best)) continue;
-        const int oc = owner[mc];
-        if (oc == skipOwner) continue;  // "break" out of this landmark's descriptor loop happened earlier
-        const V3 e0_W = v3(map_e_W[3 * mc], map_e_W[3 * mc + 1], map_e_W[3 * mc + 2]);
-        const V3 r0_W = v3(map_r_W[3 * mc], map_r_W[3 * mc + 1], map_r_W[3 * mc + 2]);
-        if (dot(e0_W, e1_W) < a.cos6Sigma) {
-          const V3 et_W = normalized(rC - r0_W);
-          const V3 n0_W = normalized(cross(e0_W, et_W));
-          const V3 n1_W = normalized(cross(e1_W, et_W));
-          if (dot(n0_W, n1_W) < a.cos6Sigma) continue;                             // not in the epipolar plane
-          if (dot(cross(e0_W, e1_W), normalized(n0_W + n0_W)) > 0.0) continue;     // divergent rays ("n0 + n0" sic)
-        }
-        bool isValid = false, isParallel = false;
-        const V3 hp = triangulate_fast(r0_W, e0_W, rC, e1_W, a.cos26Sigma, a.cos6Sigma, isValid, isParallel);
-        if (!isValid) continue;
-        const V3 p_W = v3(hp.x / 1.0, hp.y / 1.0, hp.z / 1.0);
-        if (norm(p_W - r0_W) < 0.2) isValid = false;
-        if (norm(p_W - rC) < 0.2) isValid = false;
-        if (!isValid) continue;
-        if (oc == prev) {
-          ++ctr;
-          skipOwner = oc;
-          continue;
-        }
-        best = dc;
-        bestO = oc;
+    const double* __restrict__ rc = job.pose_slot ? job.pose_slot->r_WC : a.r_WC;
+    const V3 rC = v3(rc[0], rc[1], rc[2]);
+    const int prev = job.previousOwner ? job.previousOwner[k] : -1;
+    auto visit = [&](int m, double dc) {   // the body of the reference's loop for a row with dist < threshold
+      if (!(dc < best)) return;
+      const int oc = owner[m];
+      if (oc == skipOwner) return;  // "break" out of this landmark's descriptor loop happened earlier
+      const V3 e0_W = v3(map_e_W[3 * m], map_e_W[3 * m + 1], map_e_W[3 * m + 2]);
+      const V3 r0_W = v3(map_r_W[3 * m], map_r_W[3 * m + 1], map_r_W[3 * m + 2]);
+      if (dot(e0_W, e1_W) < a.cos6Sigma) {
+        const V3 et_W = normalized(rC - r0_W);
+        const V3 n0_W = normalized(cross(e0_W, et_W));
+        const V3 n1_W = normalized(cross(e1_W, et_W));
+        if (dot(n0_W, n1_W) < a.cos6Sigma) return;                             // not in the epipolar plane
+        if (dot(cross(e0_W, e1_W), normalized(n0_W + n0_W)) > 0.0) return;     // divergent rays ("n0 + n0" sic)
+      }
+      bool isValid = false, isParallel = false;
+      const V3 hp = triangulate_fast(r0_W, e0_W, rC, e1_W, a.cos26Sigma, a.cos6Sigma, isValid, isParallel);
+      if (!isValid) return;
+      const V3 p_W = v3(hp.x / 1.0, hp.y / 1.0, hp.z / 1.0);
+      if (norm(p_W - r0_W) < 0.2) isValid = false;
+      if (norm(p_W - rC) < 0.2) isValid = false;
+      if (!isValid) return;
+      if (oc == prev) {               // loop-closure rule (:1941-1944)
         ++ctr;
-        if (!isParallel) {
-          hps = hp;
-          hpWritten = 1;
-        }
+        skipOwner = oc;
+        return;
       }
-      if (lane == 0) {
-        st.best = best;
-        st.bestO = bestO;
-        st.skipOwner = skipOwner;
-        st.hpWritten = hpWritten;
-        st.ctr = ctr;
-        st.hps = hps;
+      best = dc;
+      bestO = oc;
+      ++ctr;
+      if (!isParallel) {
+        hps = hp;
+        hpWritten = true;
       }
-      __syncwarp();
-      bound[j] = (int)ceil(best);
+    };
+    if (cnt <= kCandPerQuery) {   // the listed candidates, in row order
+      const unsigned* __restrict__ list = job.cand + (size_t)k * kCandPerQuery;
+      unsigned last = 0;
+      for (int i = 0; i < cnt; ++i) {
+        last = next_candidate(list, cnt, last, i == 0);
+        visit((int)(last >> kCandRowShift), (double)(last & ((1u << kCandRowShift) - 1u)));
+      }
+    } else {                      // the list overflowed (or no filter ran): every row, as the reference does
+      const int nm = uninit_rows(job);
+      const UninitRowOf rowOf{job.row_list, job.is3d, job.owner};
+      unsigned q[kDescWords];
+      load_desc(job.queries, k, q);
+      for (int i = 0; i < nm; ++i) {
+        int m;
+        if (!rowOf(i, nm, m)) continue;
+        unsigned r[kDescWords];
+        load_desc(job.map, m, r);
+        visit(m, (double)hamming384(q, r));
+      }
     }
   }
-  __syncwarp();
-  if (lane < nq) {
-    const UninitState& st = s_state[warp][lane];
-    const int k = st.k;
-    job.dist[k] = st.best;
-    job.best[k] = st.bestO;
-    job.hp[4 * k + 0] = st.hps.x;
-    job.hp[4 * k + 1] = st.hps.y;
-    job.hp[4 * k + 2] = st.hps.z;
-    job.hp[4 * k + 3] = st.hpWritten ? 1.0 : 0.0;
-    job.hp_written[k] = st.hpWritten ? 1 : 0;
-    if (job.ctr) job.ctr[k] = st.ctr;
-    if (job.slice_ctrs && st.ctr) {
-      // ctrs[t] of thread slice t (Frontend.cpp:1853-1855): segment = numKeypoints / numThreads, the last takes the rest
-      const int segment = nk / job.num_slices;
-      int t = segment == 0 ? job.num_slices - 1 : k / segment;
-      if (t >= job.num_slices) t = job.num_slices - 1;
-      atomicAdd(job.slice_ctrs + t, (unsigned long long)st.ctr);
-    }
+  job.dist[k] = best;
+  job.best[k] = bestO;
+  job.hp[4 * k + 0] = hps.x;
+  job.hp[4 * k + 1] = hps.y;
+  job.hp[4 * k + 2] = hps.z;
+  job.hp[4 * k + 3] = hpWritten ? 1.0 : 0.0;
+  job.hp_written[k] = hpWritten ? 1 : 0;
+  if (job.ctr) job.ctr[k] = ctr;
+  if (job.slice_ctrs && ctr) {
+    // ctrs[t] of thread slice t (Frontend.cpp:1853-1855): segment = numKeypoints / numThreads, the last takes the rest
+    const int segment = nk / job.num_slices;
+    int t = segment == 0 ? job.num_slices - 1 : k / segment;
+    if (t >= job.num_slices) t = job.num_slices - 1;
+    atomicAdd(job.slice_ctrs + t, (unsigned long long)ctr);
   }
 }
 
@@ -1327,10 +1377,16 @@ void launch_unmatched_lists(const UnmatchedArgs* args, int n, int max_kp, cudaSt
   if (n > 0 && max_kp > 0) unmatched_lists_kernel<<<n, 1024, 0, s>>>(args, max_kp);
 }
 
-void launch_match_uninit_jobs(const UninitJob* jobs, int nJobs, int maxNk, cudaStream_t s) {
+// cand_counts: the jobs' candidate counters (one int per keypoint), n_counts of them, cleared here; maxRows: upper
+// bound of the rows a job sweeps
+void launch_match_uninit_jobs(const UninitJob* jobs, int nJobs, int maxNk, int maxRows, double hammingThreshold,
+                              int* cand_counts, size_t n_counts, cudaStream_t s) {
   if (nJobs <= 0 || maxNk <= 0) return;
-  constexpr int Q = 4, chunk = 8 * Q;   // keypoints per CTA (8 warps x Q queries)
-  match_uninitialised_kernel<Q><<<dim3((maxNk + chunk - 1) / chunk, nJobs), 256, 0, s>>>(jobs);
+  const bool filter = maxRows > 0 && maxRows < kCandMaxRows && hammingThreshold <= 385.0;
+  cudaMemsetAsync(cand_counts, filter ? 0 : 0x7f, n_counts * sizeof(int), s);   // (0x7f7f7f7f = "overflow": full sweeps)
+  if (filter)
+    uninit_filter_kernel<<<dim3((maxNk + 31) / 32, nJobs, (maxRows + kFilterRows - 1) / kFilterRows), 128, 0, s>>>(jobs);
+  match_uninitialised_kernel<<<dim3((maxNk + 127) / 128, nJobs), 128, 0, s>>>(jobs);
 }
 
 }  // namespace okc
