@@ -1001,32 +1001,52 @@ __global__ void __launch_bounds__(128) stereo_filter_kernel(const StereoJob* __r
   const StereoSide& v0 = job.v0;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int n0 = v0.n_dev ? min(*v0.n_dev, v0.n) : v0.n;
-  const int kBase = blockIdx.x * 32;
   const int n1 = stereo_rows(job);
-  const int lo = blockIdx.z * kFilterRows;
-  if (kBase >= n0 || lo >= n1) return;
-  const int hi = min(n1, lo + kFilterRows);
-  if (warp == 0) {
-    const int k0 = kBase + lane;
-    const bool use = k0 < n0 && stereo_takes_part(job, k0, MOTION);
-    const unsigned bal = __ballot_sync(0xffffffffu, use);
-    if (use) s_list[__popc(bal & ((1u << lane) - 1u))] = k0;
-    if (lane == 0) s_n = __popc(bal);
-  }
-  __syncthreads();
-  const int nUse = s_n;
   const StereoRowOf rowOf{job.v1_list, job.v1_owner_a, job.v1_owner_b};
-  for (int g0 = warp * kFilterQ; g0 < nUse; g0 += 4 * kFilterQ) {
-    const int nq = min(kFilterQ, nUse - g0);
-    unsigned q[kFilterQ][kDescWords];
-    int out[kFilterQ];
-#pragma unroll
-    for (int j = 0; j < kFilterQ; ++j) {
-      out[j] = s_list[g0 + min(j, nq - 1)];
-      load_desc(v0.desc, out[j], q[j]);
+  // work items of the job: (chunk of 32 queries) x (chunk of kFilterRows rows), dealt round-robin to the job's CTAs
+  const int kChunks = (n0 + 31) / 32, items = kChunks * ((n1 + kFilterRows - 1) / kFilterRows);
+  for (int item = blockIdx.x; item < items; item += gridDim.x) {
+    const int kBase = (item % kChunks) * 32, lo = (item / kChunks) * kFilterRows;
+    const int hi = min(n1, lo + kFilterRows);
+    __syncthreads();
+    if (warp == 0) {
+      const int k0 = kBase + lane;
+      const bool use = k0 < n0 && stereo_takes_part(job, k0, MOTION);
+      const unsigned bal = __ballot_sync(0xffffffffu, use);
+      if (use) s_list[__popc(bal & ((1u << lane) - 1u))] = k0;
+      if (lane == 0) s_n = __popc(bal);
     }
-    filter_sweep(job.v1.desc, rowOf, lo, hi, q, nq, out, thr, job.cand, job.cand_count);
+    __syncthreads();
+    const int nUse = s_n;
+    for (int g0 = warp * kFilterQ; g0 < nUse; g0 += 4 * kFilterQ) {
+      const int nq = min(kFilterQ, nUse - g0);
+      unsigned q[kFilterQ][kDescWords];
+      int out[kFilterQ];
+#pragma unroll
+      for (int j = 0; j < kFilterQ; ++j) {
+        out[j] = s_list[g0 + min(j, nq - 1)];
+        load_desc(v0.desc, out[j], q[j]);
+      }
+      filter_sweep(job.v1.desc, rowOf, lo, hi, q, nq, out, thr, job.cand, job.cand_count);
+    }
   }
+}
+
+// CTAs per job of a filter launch: enough to fill the GPU a few times over, never more than the job has work items
+// (the counts are only known on the device: a job's CTAs share its items round-robin, none is launched just to exit)
+static int filter_ctas_per_job(int maxQueries, int maxRows, int nJobs) {
+  static int sms[64] = {};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (sms[dev & 63] == 0) {
+    int v = 148;
+    cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev);
+    sms[dev & 63] = v;
+  }
+  const long long items = (long long)((maxQueries + 31) / 32) * ((maxRows + kFilterRows - 1) / kFilterRows);
+  long long want = ((long long)sms[dev & 63] * 12 + nJobs - 1) / nJobs;
+  if (want > items) want = items;
+  return (int)(want < 1 ? 1 : want);
 }
 
 // next candidate of a query in ascending row order: the smallest packed value above `last` (lists are short: a scan)
@@ -1141,7 +1161,7 @@ void launch_match_stereo_jobs(const StereoJob* jobs, int nJobs, int max0, int ma
   // (counters of 0x7f7f7f7f = "overflow": every query then sweeps the rows itself)
   cudaMemsetAsync(cand_counts, filter ? 0 : 0x7f, n_counts * sizeof(int), s);
   if (filter) {
-    const dim3 fgrid((max0 + 31) / 32, nJobs, (max1 + kFilterRows - 1) / kFilterRows);
+    const dim3 fgrid(filter_ctas_per_job(max0, max1, nJobs), nJobs);
     if (motion) stereo_filter_kernel<true><<<fgrid, 128, 0, s>>>(jobs, thr);
     else stereo_filter_kernel<false><<<fgrid, 128, 0, s>>>(jobs, thr);
   }
@@ -1188,32 +1208,35 @@ __global__ void __launch_bounds__(128) uninit_filter_kernel(const UninitJob* __r
   const UninitJob& job = jobs[blockIdx.y];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int nk = job.nk_dev ? min(*job.nk_dev, job.nk) : job.nk;
-  const int kBase = blockIdx.x * 32;
   const int nm = uninit_rows(job);
-  const int lo = blockIdx.z * kFilterRows;
-  if (kBase >= nk || lo >= nm) return;
-  const int hi = min(nm, lo + kFilterRows);
-  if (warp == 0) {
-    const int k = kBase + lane;
-    const bool use = k < nk && uninit_takes_part(job, k);
-    const unsigned bal = __ballot_sync(0xffffffffu, use);
-    if (use) s_list[__popc(bal & ((1u << lane) - 1u))] = k;
-    if (lane == 0) s_n = __popc(bal);
-  }
-  __syncthreads();
-  const int nUse = s_n;
   const UninitRowOf rowOf{job.row_list, job.is3d, job.owner};
   const int thr = (int)ceil(job.a.hammingThreshold);
-  for (int g0 = warp * kFilterQ; g0 < nUse; g0 += 4 * kFilterQ) {
-    const int nq = min(kFilterQ, nUse - g0);
-    unsigned q[kFilterQ][kDescWords];
-    int out[kFilterQ];
-#pragma unroll
-    for (int j = 0; j < kFilterQ; ++j) {
-      out[j] = s_list[g0 + min(j, nq - 1)];
-      load_desc(job.queries, out[j], q[j]);
+  // work items of the job: (chunk of 32 keypoints) x (chunk of kFilterRows rows), dealt round-robin to the job's CTAs
+  const int kChunks = (nk + 31) / 32, items = kChunks * ((nm + kFilterRows - 1) / kFilterRows);
+  for (int item = blockIdx.x; item < items; item += gridDim.x) {
+    const int kBase = (item % kChunks) * 32, lo = (item / kChunks) * kFilterRows;
+    const int hi = min(nm, lo + kFilterRows);
+    __syncthreads();
+    if (warp == 0) {
+      const int k = kBase + lane;
+      const bool use = k < nk && uninit_takes_part(job, k);
+      const unsigned bal = __ballot_sync(0xffffffffu, use);
+      if (use) s_list[__popc(bal & ((1u << lane) - 1u))] = k;
+      if (lane == 0) s_n = __popc(bal);
     }
-    filter_sweep(job.map, rowOf, lo, hi, q, nq, out, thr, job.cand, job.cand_count);
+    __syncthreads();
+    const int nUse = s_n;
+    for (int g0 = warp * kFilterQ; g0 < nUse; g0 += 4 * kFilterQ) {
+      const int nq = min(kFilterQ, nUse - g0);
+      unsigned q[kFilterQ][kDescWords];
+      int out[kFilterQ];
+#pragma unroll
+      for (int j = 0; j < kFilterQ; ++j) {
+        out[j] = s_list[g0 + min(j, nq - 1)];
+        load_desc(job.queries, out[j], q[j]);
+      }
+      filter_sweep(job.map, rowOf, lo, hi, q, nq, out, thr, job.cand, job.cand_count);
+    }
   }
 }
 
@@ -1385,7 +1408,7 @@ void launch_match_uninit_jobs(const UninitJob* jobs, int nJobs, int maxNk, int m
   const bool filter = maxRows > 0 && maxRows < kCandMaxRows && hammingThreshold <= 385.0;
   cudaMemsetAsync(cand_counts, filter ? 0 : 0x7f, n_counts * sizeof(int), s);   // (0x7f7f7f7f = "overflow": full sweeps)
   if (filter)
-    uninit_filter_kernel<<<dim3((maxNk + 31) / 32, nJobs, (maxRows + kFilterRows - 1) / kFilterRows), 128, 0, s>>>(jobs);
+    uninit_filter_kernel<<<dim3(filter_ctas_per_job(maxNk, maxRows, nJobs), nJobs), 128, 0, s>>>(jobs);
   match_uninitialised_kernel<<<dim3((maxNk + 127) / 128, nJobs), 128, 0, s>>>(jobs);
 }
 
