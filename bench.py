@@ -292,6 +292,12 @@ def stage_bytes(kernel, W, H, K, M, L):
     return (K + M) * 48 + K * 16                    # any matcher: descriptors in, (dist, id) out
 
 
+def wl_ptr(arr):
+    """Address of a (C-contiguous) numpy image stack."""
+    assert arr.flags["C_CONTIGUOUS"]
+    return arr.ctypes.data
+
+
 class GpuConfig:
     """One BASELINE.json frame config on this rank's GPU: handles, pools, batches and the step loops."""
 
@@ -389,13 +395,15 @@ class GpuConfig:
         F = self.F_shard
         return ((k // F) * self.world * F + self.rank * F + k % F) % self.n_frames
 
-    def slot_args(self, k0, device):
+    def slot_args(self, k0, device, pageable=False):
+        """(image addresses, poses) of the batch of frames k0 .. k0 + F - 1: images in HBM (device), in pinned host
+        memory, or in ordinary pageable host memory (numpy arrays: the library stages them through its pinned block)."""
         F, nc = self.F, self.nc
         f = np.asarray([self.frame_of(k) for k in range(k0, k0 + F)])
         imgs = np.empty(nc * F, np.uint64)
         poses = np.empty((nc * F, 24))
         for j, c in enumerate(self.cams_here):
-            base = (self.d_img[j] if device else self.h_img[j]).data_ptr()
+            base = wl_ptr(self.wl["images"][c]) if pageable else (self.d_img[j] if device else self.h_img[j]).data_ptr()
             imgs[j * F:(j + 1) * F] = base + f.astype(np.uint64) * np.uint64(self.img_stride)
             poses[j * F:(j + 1) * F] = self.pose_rows[f, c]
         return imgs, poses
@@ -478,7 +486,7 @@ class GpuConfig:
             b.finish()
         return ms, t_host / max(n_steps, 1)
 
-    def run_e2e(self, k_begin, k_end, keep=None):
+    def run_e2e(self, k_begin, k_end, keep=None, pageable=False):
         F, D = self.F, self.D
         pending = []
         for j, k in enumerate(range(k_begin, k_end, F)):
@@ -489,7 +497,7 @@ class GpuConfig:
                 r = self.read(pb)
                 if keep is not None:
                     keep(pk, r)
-            self.enqueue(b, *self.slot_args(k, False), False, k)
+            self.enqueue(b, *self.slot_args(k, False, pageable), False, k)
             pending.append((b, k))
         for pb, pk in pending:
             pb.finish()
@@ -497,14 +505,14 @@ class GpuConfig:
             if keep is not None:
                 keep(pk, r)
 
-    def time_e2e(self, n_steps, n_warm, barrier, max_over_ranks):
+    def time_e2e(self, n_steps, n_warm, barrier, max_over_ranks, pageable=False):
         F = self.F
-        self.run_e2e(0, max(self.D, n_warm) * F)
+        self.run_e2e(0, max(self.D, n_warm) * F, None, pageable)
         runs = []
         for _ in range(E2E_REPEATS):
             barrier()
             t0 = time.perf_counter()
-            self.run_e2e(n_warm * F, (n_warm + n_steps) * F)
+            self.run_e2e(n_warm * F, (n_warm + n_steps) * F, None, pageable)
             self.torch.cuda.synchronize()
             runs.append(max_over_ranks((time.perf_counter() - t0) * 1e3))
         return float(np.median(runs)), runs
@@ -746,6 +754,9 @@ def run_frame_config(args, name, mod, syn, torch, dist, ctx, rank, world, headli
     dev_ms, t_host = gc.run_value(n_steps, n_warm, barrier, max_over_ranks)
     e2e_ms, e2e_runs = gc.time_e2e(n_steps, n_warm, barrier, max_over_ranks)
     h2d, d2h = gc.bytes_per_frame()     # (of the e2e run's last batches)
+    pageable_ms = None
+    if headline and world == 1:   # the same arm with the images in pageable host memory (staged by the library)
+        pageable_ms, _ = gc.time_e2e(min(n_steps, 60), n_warm, barrier, max_over_ranks, pageable=True)
     barrier()
     clocks = sampler_box.pop().stop() if (headline and rank == 0 and sampler_box) else None
     lat = gc.latency(graph=not args.no_graph) if (rank == 0 or world == 1) else None
@@ -786,10 +797,15 @@ def run_frame_config(args, name, mod, syn, torch, dist, ctx, rank, world, headli
                 "timed": "median of %d runs of K steps (ms: %s)" % (E2E_REPEATS, ", ".join("%.1f" % v for v in e2e_runs)),
                 "pcie_gbs_per_gpu": round(n_steps * F * (h2d + d2h) / (e2e_ms * 1e-3) / 1e9, 1),
                 "pcie_ceiling_gbs_per_gpu": pcie_ceiling(world if not shard_cameras else min(world, wl["n_cams"])),
-                "pcie_ceiling_source": "profiles/r02_pcie_ceiling.json (copies only, same block sizes, same N)"},
+                "pcie_ceiling_source": "profiles/r02_pcie_ceiling.json (copies only, same block sizes, same N)",
+                "host_memory": "pinned (cudaMallocHost ring of frames); pageable: see e2e_pageable"},
         "gpu_launches": gc.launches_per_batch() * n_steps,
         "roofline": roofline,
     }
+    if pageable_ms is not None:
+        out["e2e_pageable"] = {"value": round(min(n_steps, 60) * frames_per_step / (pageable_ms * 1e-3), 2), "unit": "frames/s",
+                               "what": "the e2e arm with the caller's images in pageable host memory: the library "
+                                       "copies them into its pinned staging block (host memcpy) before the DMA"}
     if without_exchange is not None:
         out["without_exchange"] = without_exchange
         out["exchange"] = gc.gather.describe()

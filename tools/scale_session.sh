@@ -1,7 +1,7 @@
 #!/bin/bash
 # One 8-GPU box: the copy ceiling at N = 2, 4, 8 and the bench at N = 8, 4, 2 (run under gpurun --gpus 8).
 mkdir -p gpurun_out
-for N in 2 4 8; do
+for N in ${PCIE_N:-2 4 8}; do
   timeout 200 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port $((29500 + N)) \
     tools/pcie_ceiling.py 2>/dev/null | tail -1 > gpurun_out/pcie_$N.json
   cat gpurun_out/pcie_$N.json
