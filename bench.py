@@ -409,9 +409,9 @@ class GpuConfig:
         return imgs, poses
 
     def enqueue(self, b, imgs, poses, device, k0=0):
-        b.enqueue_addrs(imgs, device)
         if self.conf["landmarks"] or self.pairs or self.jobs:
-            b.set_poses(poses)
+            b.set_poses(poses)   # (before the enqueue: the slot table then travels once per frame)
+        b.enqueue_addrs(imgs, device)
         if self.conf["landmarks"]:
             b.match_landmarks_enqueue(self.pool, HAMMING, self.slices, self.mod.STAGE_UNINITIALISED)
         if self.pairs:

@@ -40,9 +40,10 @@ def main():
         acc = {}
         for i in range(a.reps + 20):
             imgs, poses = gc.slot_args(i * gc.F, label == "batch")
-            steps = [("enqueue_addrs", lambda: b.enqueue_addrs(imgs, label == "batch"))]
+            steps = []
             if gc.conf["landmarks"] or gc.pairs or gc.jobs:
                 steps.append(("set_poses", lambda: b.set_poses(poses)))
+            steps.append(("enqueue_addrs", lambda: b.enqueue_addrs(imgs, label == "batch")))
             if gc.conf["landmarks"]:
                 steps.append(("match_landmarks_enqueue",
                               lambda: b.match_landmarks_enqueue(gc.pool, bench.HAMMING, gc.slices, mod.STAGE_UNINITIALISED)))
