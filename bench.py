@@ -42,6 +42,11 @@ HAMMING = 60.0
 CONFIGS = {
     "stereo_pair": dict(index=0, rig="euroc", frames=200, keyframes=0, landmarks=False, stereo=True, motion=False,
                         what="configs[0]: 752x480 stereo pair, 2x(detect+describe+back-project) + matchStereo"),
+    "stereo_pair_noise": dict(index=0, rig="euroc", frames=64, keyframes=0, landmarks=False, stereo=True, motion=False,
+                              noise=True,
+                              what="configs[0], variant S-noise: i.i.d. uniform u8 images (the reference's own test input, "
+                                   "okvis_cv/test/TestFrame.cpp:62-65) - the worst case for the number of NMS candidates; "
+                                   "2x(detect+describe+back-project) + matchStereo"),
     "euroc_sequence": dict(index=1, rig="euroc", frames=200, keyframes=5, landmarks=True, stereo=False, motion=False,
                            what="configs[1]: EuRoC 752x480 stereo sequence, per frame 2x(detect+describe+back-project) + "
                                 "matchToMap (landmark preparation, matchToMapByThread, matchToMapByThreadUnitialised) vs a "
@@ -137,8 +142,11 @@ def build_images(syn, name, sparse=False):
     conf = CONFIGS[name]
     rig = syn.RIGS[conf["rig"]]
     W, H, n_cams = rig["width"], rig["height"], rig["n_cams"]
-    imgs = syn.rig_sequence(conf["frames"], n_cams, W, H, seed=2 + conf["index"], step=STEP, disparity=DISPARITY,
-                            dense=not sparse, rects=400)
+    if conf.get("noise"):
+        imgs = np.random.default_rng(77).integers(0, 256, (n_cams, conf["frames"], H, W), dtype=np.uint8)
+    else:
+        imgs = syn.rig_sequence(conf["frames"], n_cams, W, H, seed=2 + conf["index"], step=STEP, disparity=DISPARITY,
+                                dense=not sparse, rects=400)
     rays, jac = syn.rig_maps(rig)
     r_all = syn.rig_poses(conf["frames"], n_cams, rig["f"][0], rig["f"][1], STEP, DISPARITY, Z0)
     kf_frames = [int(round((i + 0.5) * conf["frames"] / conf["keyframes"])) for i in range(conf["keyframes"])]
