@@ -916,7 +916,8 @@ __device__ __forceinline__ double side_size(const StereoSide& v, int k) {
 // Work layout (shared with the uninitialised-landmark matcher below): two kernels.
 //   1. filter  - every (query, row) pair's Hamming distance, the whole GPU at once: a CTA compacts the eligible ones of
 //      32 consecutive queries, a warp keeps Q of them in registers and sweeps ITS chunk of the rows (grid.z), one row
-//      per lane and tile, the next tile requested before this one is compared. A pair below the threshold is appended
+//      per lane and tile, the next tile requested before this one is compared (first the 6-word prefix of every pair,
+//      the exact distance only for the queued few, see filter_sweep). A pair below the threshold is appended
 //      to the query's candidate list ((row << 9) | dist, kCandPerQuery entries; more -> the count says "overflow").
 //      Unrelated descriptors are ~192 bits apart, so the lists hold the true match and a few look-alikes.
 //   2. resolve - one thread per query runs the reference's loop body over its candidates in ascending row order (= the
@@ -929,47 +930,71 @@ constexpr int kCandRowShift = 9;    // candidate = (row << 9) | dist, dist <= 38
 constexpr int kCandMaxRows = 1 << (32 - kCandRowShift);
 
 // rows [lo, hi) of `rowDesc` (through `rowOf`: row index and liveness of sweep position i) against the Q queries of a
-// warp; q[j] valid for j < nq, out[j] = the query's index into cand / count
+// warp; q[j] valid for j < nq, out[j] = the query's index into qDesc / cand / count.
+// Two passes, because the popcount pipe (16 lanes per clock and SM) is what bounds the sweep: every pair gets the
+// distance over the first 6 of its 12 words (a lower bound of the distance); the few pairs whose bound is below the
+// threshold are queued in shared memory (one queue per warp) and get the exact distance later, one pair per lane.
+// (Two rows per lane and step - four loads in flight - was measured: slower, 116 registers.)
+constexpr int kFilterQueue = 256;   // entries per warp: a tile adds at most 32 * kFilterQ = 128
 template <class RowOf>
-__device__ __forceinline__ void filter_sweep(const uint8_t* __restrict__ rowDesc, RowOf rowOf, int lo, int hi,
-                                             const unsigned (&q)[kFilterQ][kDescWords], int nq, const int (&out)[kFilterQ],
-                                             int thr, unsigned* __restrict__ cand, int* __restrict__ count) {
+__device__ __forceinline__ void filter_sweep(const uint8_t* __restrict__ qDesc, const uint8_t* __restrict__ rowDesc,
+                                             RowOf rowOf, int lo, int hi, const unsigned (&q)[kFilterQ][kDescWords],
+                                             int nq, const int (&out)[kFilterQ], int thr, unsigned* __restrict__ cand,
+                                             int* __restrict__ count, uint2* __restrict__ queue) {
   const int lane = threadIdx.x & 31;
-  unsigned r[kDescWords], rNext[kDescWords];
+  const unsigned lt = (1u << lane) - 1u;
+  int queued = 0;
+  auto drain = [&]() {
+    __syncwarp();
+    for (int e0 = 0; e0 < queued; e0 += 32) {
+      const int e = e0 + lane;
+      if (e < queued) {
+        const uint2 it = queue[e];
+        unsigned a[kDescWords], b[kDescWords];
+        load_desc(qDesc, it.x, a);
+        load_desc(rowDesc, it.y, b);
+        const int d = (int)hamming384(a, b);
+        if (d < thr) {
+          const int pos = atomicAdd(count + it.x, 1);
+          if (pos < kCandPerQuery) cand[(size_t)it.x * kCandPerQuery + pos] = (it.y << kCandRowShift) | (unsigned)d;
+        }
+      }
+    }
+    __syncwarp();
+    queued = 0;
+  };
+  unsigned r[6], rNext[6];
   int m = 0, mNext = 0;
+  auto fetch6 = [&](int row, unsigned (&w)[6]) {
+    const uint4* p = reinterpret_cast<const uint4*>(rowDesc) + (size_t)row * 3;
+    const uint4 a = __ldg(p);
+    const uint2 b = __ldg(reinterpret_cast<const uint2*>(p + 1));
+    w[0] = a.x; w[1] = a.y; w[2] = a.z; w[3] = a.w; w[4] = b.x; w[5] = b.y;
+  };
   bool live = rowOf(lo + lane, hi, m), liveNext = false;
-  if (live) load_desc(rowDesc, m, r);
+  if (live) fetch6(m, r);
   for (int base = lo; base < hi; base += 32) {
     liveNext = rowOf(base + 32 + lane, hi, mNext);
-    if (liveNext) load_desc(rowDesc, mNext, rNext);
-    // first the 6-word prefix (a lower bound of the distance): most tiles hold no pair below the threshold
-    int d6[kFilterQ];
-    bool any = false;
+    if (liveNext) fetch6(mNext, rNext);
 #pragma unroll
     for (int j = 0; j < kFilterQ; ++j) {
       int d = 0;
 #pragma unroll
       for (int w = 0; w < 6; ++w) d += __popc(q[j][w] ^ r[w]);
-      d6[j] = d;
-      any |= live && j < nq && d < thr;
-    }
-    if (__any_sync(0xffffffffu, any)) {
-#pragma unroll
-      for (int j = 0; j < kFilterQ; ++j) {
-        int d = d6[j];
-#pragma unroll
-        for (int w = 6; w < kDescWords; ++w) d += __popc(q[j][w] ^ r[w]);
-        if (live && j < nq && d < thr) {
-          const int pos = atomicAdd(count + out[j], 1);
-          if (pos < kCandPerQuery) cand[(size_t)out[j] * kCandPerQuery + pos] = ((unsigned)m << kCandRowShift) | (unsigned)d;
-        }
+      const bool pass = live && j < nq && d < thr;
+      const unsigned mask = __ballot_sync(0xffffffffu, pass);
+      if (mask) {
+        if (pass) queue[queued + __popc(mask & lt)] = make_uint2((unsigned)out[j], (unsigned)m);
+        queued += __popc(mask);
       }
     }
+    if (queued > kFilterQueue - 32 * kFilterQ) drain();
 #pragma unroll
-    for (int w = 0; w < kDescWords; ++w) r[w] = rNext[w];
+    for (int w = 0; w < 6; ++w) r[w] = rNext[w];
     m = mNext;
     live = liveNext;
   }
+  drain();
 }
 
 __device__ __forceinline__ bool stereo_takes_part(const StereoJob& job, int k0, bool motion) {
@@ -997,6 +1022,7 @@ template <bool MOTION>
 __global__ void __launch_bounds__(128) stereo_filter_kernel(const StereoJob* __restrict__ jobs, int thr) {
   __shared__ int s_list[32];
   __shared__ int s_n;
+  __shared__ uint2 s_queue[4][kFilterQueue];
   const StereoJob& job = jobs[blockIdx.y];
   const StereoSide& v0 = job.v0;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -1027,7 +1053,7 @@ __global__ void __launch_bounds__(128) stereo_filter_kernel(const StereoJob* __r
         out[j] = s_list[g0 + min(j, nq - 1)];
         load_desc(v0.desc, out[j], q[j]);
       }
-      filter_sweep(job.v1.desc, rowOf, lo, hi, q, nq, out, thr, job.cand, job.cand_count);
+      filter_sweep(v0.desc, job.v1.desc, rowOf, lo, hi, q, nq, out, thr, job.cand, job.cand_count, s_queue[warp]);
     }
   }
 }
@@ -1205,6 +1231,7 @@ __device__ __forceinline__ int uninit_rows(const UninitJob& job) {
 __global__ void __launch_bounds__(128) uninit_filter_kernel(const UninitJob* __restrict__ jobs) {
   __shared__ int s_list[32];
   __shared__ int s_n;
+  __shared__ uint2 s_queue[4][kFilterQueue];
   const UninitJob& job = jobs[blockIdx.y];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int nk = job.nk_dev ? min(*job.nk_dev, job.nk) : job.nk;
@@ -1235,7 +1262,7 @@ __global__ void __launch_bounds__(128) uninit_filter_kernel(const UninitJob* __r
         out[j] = s_list[g0 + min(j, nq - 1)];
         load_desc(job.queries, out[j], q[j]);
       }
-      filter_sweep(job.map, rowOf, lo, hi, q, nq, out, thr, job.cand, job.cand_count);
+      filter_sweep(job.queries, job.map, rowOf, lo, hi, q, nq, out, thr, job.cand, job.cand_count, s_queue[warp]);
     }
   }
 }
