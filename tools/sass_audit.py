@@ -96,7 +96,7 @@ def main():
                 newton -= 1
             # head of the inline IEEE sqrt / division sequences: the residual 1 - x * y of the MUFU seed's refinement
             if re.search(r"DFMA R\d+, -?R\d+, -?R\d+, 1 ;", ln):
-                newton = 10
+                newton = 20
             if m:
                 op = m.group(1)
                 per_kernel[fn][op] += 1
@@ -139,7 +139,7 @@ def main():
             if cls.startswith("OTHER") and in_newton or path.endswith("sm_32_intrinsics.hpp"):
                 # MUFU seed + DFMA(x, -y, 1) residual + refinement steps of an inline dsqrt / ddiv that the scheduler moved
                 # next to instructions of another source line (a loop header, an inlined __ldg): recognised by the
-                # sequence's head, the DFMAs of the 10 instructions after it belong to it (checked by hand on this build)
+                # sequence's head, the DFMAs of the 20 instructions after it belong to it (checked by hand on this build)
                 cls = "IEEE division / sqrt sequence (moved by the scheduler; recognised by its Newton pattern)"
             if cls.startswith("OTHER") and ("/usr/local/cuda" in path or "libdevice" in path or path == "?"):
                 cls = "libdevice math function"
