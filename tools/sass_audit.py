@@ -95,8 +95,8 @@ def main():
                 instr[fn] += 1
                 newton -= 1
             # head of the inline IEEE sqrt / division sequences: the residual 1 - x * y of the MUFU seed's refinement
-            if re.search(r"DFMA R\d+, -?R\d+, -?R\d+, 1 ;", ln):
-                newton = 20
+            if re.search(r"DFMA R\d+, -?R\d+, -?R\d+, 1 ;", ln) or re.search(r"MUFU\.(RCP|RSQ)(64H)? ", ln):
+                newton = 24
             if m:
                 op = m.group(1)
                 per_kernel[fn][op] += 1
@@ -107,7 +107,7 @@ def main():
                     key = (op, "<constant>", 0, None, None)
                 else:
                     key = (op,) + (where or ("?", 0, None, None))
-                if newton > 0 and op == "DFMA" and not sub:
+                if newton > 0 and op in ("DFMA", "FFMA") and not sub:
                     key = key[:1] + (key[1] + "#newton",) + key[2:]
                 sites[fn][key] += 1
     names = demangle(sorted(per_kernel))
@@ -139,7 +139,7 @@ def main():
             if cls.startswith("OTHER") and in_newton or path.endswith("sm_32_intrinsics.hpp"):
                 # MUFU seed + DFMA(x, -y, 1) residual + refinement steps of an inline dsqrt / ddiv that the scheduler moved
                 # next to instructions of another source line (a loop header, an inlined __ldg): recognised by the
-                # sequence's head, the DFMAs of the 20 instructions after it belong to it (checked by hand on this build)
+                # sequence's head, the fused instructions of the 24 instructions after a MUFU.RCP / MUFU.RSQ seed or after the residual's head belong to it (checked by hand on this build)
                 cls = "IEEE division / sqrt sequence (moved by the scheduler; recognised by its Newton pattern)"
             if cls.startswith("OTHER") and ("/usr/local/cuda" in path or "libdevice" in path or path == "?"):
                 cls = "libdevice math function"
