@@ -2,16 +2,18 @@
 //
 //  harris_nms_kernel   = brisk::HarrisScoresSSE (brisk/src/harris-scores.cc:65-301) fused with
 //                        HarrisScoreCalculator::Get2dMaxima (brisk/src/harris-score-calculator.cc:70-119):
-//                        one pass over the u8 image, no int16 planes in HBM; writes the int32 score map
-//                        (needed by the sub-pixel fit) and a bitmap of the NMS survivors.
+//                        one pass over the u8 image, no int16 planes and no score map in HBM; writes a bitmap of
+//                        the NMS survivors and their scores, compacted per (row, strip) segment.
 //  order_candidates_kernel = the std::sort at the top of EnforceKeyPointUniformity, tie order included
 //                        (libstdc++ introsort reproduced exactly; see the comment at the kernel).
-//  select_keypoints_kernel = the greedy loop of EnforceKeyPointUniformity
-//                        (brisk/include/brisk/internal/uniformity-enforcement-inl.h:57-207)
-//                        + the Subpixel2D tail of DetectScaleSpaceMaxima
-//                        (brisk/include/brisk/internal/scale-space-layer-inl.h:394-420, 568-701):
-//                        one CTA per image runs the greedy occupancy loop with the occupancy image in
-//                        shared memory, then refines.
+//  select_keypoints_wave_kernel = the greedy loop of EnforceKeyPointUniformity
+//                        (brisk/include/brisk/internal/uniformity-enforcement-inl.h:57-207) in its dependency
+//                        form (default); select_keypoints_kernel = the same loop one candidate at a time with the
+//                        occupancy image in shared memory (A/B baseline, and for more keypoints per image than the
+//                        dependency form's lists hold).
+//  subpixel_kernel     = the Subpixel2D tail of DetectScaleSpaceMaxima
+//                        (brisk/include/brisk/internal/scale-space-layer-inl.h:394-420, 568-701); the 3x3 scores
+//                        around a kept point are recomputed from the pixels (harris_ring_scores).
 #include "common.cuh"
 #include <cstdio>
 #include <cstdlib>
