@@ -276,3 +276,76 @@ def test_graph_replay_equals_plain_launches(mod, ctx, syn):
     pool.close()
     for cam in cams:
         cam.close()
+
+
+def test_large_batch_equals_small_batches(mod, ctx, syn):
+    """Four stereo frames in ONE batch of 8 slots against the same frames as four batches of 2 slots: every output
+    byte equal. The two shapes take different code paths on purpose - 8 slots: live-row result copies, 48-register
+    builds of the one-CTA-per-image kernels, everything on one stream; 2 slots: whole-section copies, 64-register
+    builds, landmark preparation and match statistics on the side stream."""
+    cfg, model, cams, W, H = _rig(mod, syn, ctx, "euroc", 2, 768)
+    n_frames = 6
+    imgs = syn.rig_sequence(n_frames, 2, W, H, seed=41, step=STEP, disparity=DISP, dense=True)
+    r_all = syn.rig_poses(n_frames, 2, model.fu, model.fv, STEP, DISP, Z0)
+    det = (cfg["radius"], 0, cfg["abs_threshold"], cfg["max_kpt"])
+    f_mean = 0.5 * (model.fu + model.fv)
+    # world and one retained keyframe from frame 0
+    small = mod.Batch(ctx, cams)
+    small.enqueue([imgs[c, 0] for c in range(2)], *det, [(0.0, 1.0, 0.0)] * 2)
+    small.set_poses(_poses(mod, r_all[0]))
+    kf = mod.Keyframe(ctx, 2, 768)
+    small.retain([0, 1], kf)
+    small.finish()
+    views = []
+    for c in range(2):
+        kp, desc = small.slot_frame(c)
+        e_C, valid, _ = small.slot_back_projections(c, len(kp))
+        views.append(dict(kp=kp, desc=desc, e_C=e_C, valid=valid, r_WC=r_all[0, c]))
+        kf.set_view(c, np.eye(3), r_all[0, c], f_mean, (np.arange(len(kp)) % 5 != 0).astype(np.uint8))
+    pool = mod.LandmarkPool(ctx, *syn.plane_landmarks(views, Z0, model.fu, 2000, seed=5))
+    frames = [2, 3, 4, 5]
+
+    def collect(batch, slots, pair, jobs):
+        out = []
+        for s in slots:
+            kp, desc = batch.slot_frame(s)
+            assert len(kp) > 300
+            out += [kp.tobytes(), desc.tobytes()]
+            out += [x.tobytes() for x in batch.slot_matches(s, len(kp))]
+            out += [x.tobytes() for x in batch.slot_uninitialised(s, len(kp))]
+            out += [x.tobytes() for x in batch.slot_back_projections(s, len(kp))[:2]]
+        out += [x.tobytes() for x in batch.pair_stereo(pair, len(batch.slot_frame(slots[0])[0]))]
+        for j in jobs:
+            out += [x.tobytes() for x in batch.job_motion(j)]
+        return out
+
+    def run(batch, fs):
+        """slots: camera-major per frame (frame i: slots 2 i, 2 i + 1)"""
+        n = len(fs)
+        batch.set_poses(np.concatenate([_poses(mod, r_all[f]) for f in fs]))
+        batch.enqueue([imgs[c, f] for f in fs for c in range(2)], *det, [(0.05, 0.99, 0.1)] * (2 * n))
+        batch.match_landmarks_enqueue(pool, 60.0, cfg["slices"], mod.STAGE_UNINITIALISED)
+        batch.match_stereo_enqueue([(2 * i, 2 * i + 1) for i in range(n)], 60.0)
+        batch.match_motion_enqueue([(kf, c, 2 * i + c) for i in range(n) for c in range(2)], 60.0, only_unmatched=True)
+        batch.finish()
+        return [collect(batch, [2 * i, 2 * i + 1], i, [2 * i, 2 * i + 1]) for i in range(n)]
+
+    want, d2h_small = [], 0
+    for rep in range(2):      # (twice: the second pass replays the graphs)
+        want, d2h_small = [], 0
+        for f in frames:
+            want.append(run(small, [f])[0])
+            d2h_small += small.transfer_bytes()[1]
+    big = mod.Batch(ctx, [cams[s % 2] for s in range(8)])
+    for rep in range(2):
+        got = run(big, frames)
+        assert got == want
+        h2d, d2h = big.transfer_bytes()
+        assert h2d >= 8 * W * H and 0 < d2h < 0.9 * d2h_small    # live rows only (about 560 of 768 rows per section)
+    assert len(set(tuple(x) for x in want)) == len(frames)
+    big.close()
+    small.close()
+    kf.close()
+    pool.close()
+    for cam in cams:
+        cam.close()
