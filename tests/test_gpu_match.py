@@ -489,3 +489,40 @@ def test_binned_map_match_equals_tile_scan(rigname, mod, ctx, port, syn):
     finally:
         mod.lib().okc_debug_set_match_binned(1)
         cam.close()
+
+
+@pytest.mark.parametrize("case", ["identical-descriptors", "threshold-above-384"])
+def test_gated_matchers_when_the_candidate_lists_overflow(case, mod, ctx, port, syn):
+    """The filter kernels keep 32 candidates per query. Identical descriptors on both sides (every pair at distance 0)
+    overflow every list, a threshold above 384 switches the filter off: both make the resolve kernels walk all rows
+    themselves - same results as the port, for matchStereo, matchMotionStereo and the uninitialised-landmark matcher."""
+    v0, v1 = stereo_views(mod, ctx, syn)
+    thr = 60.0
+    if case == "identical-descriptors":
+        one = v0["desc"][:1]
+        v0 = dict(v0, desc=np.repeat(one, len(v0["desc"]), 0))
+        v1 = dict(v1, desc=np.repeat(one, len(v1["desc"]), 0))
+    else:
+        thr = 400.0
+    got, want = ctx.match_stereo(v0, v1, thr), port.match_stereo(v0, v1, thr)
+    for g, w in zip(got, want):
+        assert g.tobytes() == w.tobytes()
+    assert (got[1] > 0).sum() > 20          # matches other than the initial k1 = 0 were accepted
+    use0 = (np.arange(len(v0["desc"])) % 7 != 0).astype(np.uint8)
+    got, want = ctx.match_motion_stereo(v0, use0, v1, thr), port.match_motion_stereo(v0, use0, v1, thr)
+    for g, w in zip(got[:4], want[:4]):
+        assert g.tobytes() == w.tobytes()
+    assert np.allclose(got[4], want[4], rtol=0, atol=1e-12) and (got[1] >= 0).sum() > 20
+    # uninitialised landmarks: 2 rows per landmark, landmarks = the other view's keypoints
+    e0 = _world_rays(v0)
+    rows = np.repeat(v0["desc"], 2, 0)
+    owner = np.repeat(np.arange(len(v0["desc"]), dtype=np.int32), 2)
+    e_rows, r_rows = np.repeat(e0, 2, 0), np.repeat(np.asarray(v0["r_WC"])[None, :], 2 * len(e0), 0)
+    kp_e = _world_rays(v1)
+    use = v1["bp_valid"] > 0
+    args = (v1["desc"], kp_e, use, None, rows, owner, e_rows, r_rows)
+    got = ctx.match_to_map_uninitialised(*args, v1["r_WC"], v1["f"], thr, 4)
+    want = port.match_to_map_uninitialised(*args, len(v0["desc"]), v1["r_WC"], v1["f"], thr, 4)
+    assert np.array_equal(got[0], want[0]) and np.array_equal(got[1], want[1])
+    assert got[2].tobytes() == want[2].tobytes() and np.array_equal(got[3], want[3]) and np.array_equal(got[4], want[4])
+    assert (want[1] >= 0).sum() > 20
