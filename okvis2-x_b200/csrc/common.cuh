@@ -166,6 +166,7 @@ struct UninitJob {
   int nm;
   const int* row_list;      // the rows to sweep, ascending (a precompacted list of the non-3D rows), or null: all rows
   const int* n_list_dev;    //   and their number
+  const uint8_t* row_desc;  //   and, optionally, their descriptors in list order (contiguous: coalesced tile loads)
   int num_slices;
   UninitArgs a;
   double* dist;
@@ -236,6 +237,7 @@ struct PrepSlot {
   int* u_count;                // L     scratch
   int* u_offset;               // L + 1 rows of the non-3D landmarks before landmark l; [L] = their number
   int* u_rows;                 // 3 L   those rows (indices into the pool), ascending
+  uint8_t* u_desc;             // 3 L x 48: their descriptors, contiguous in list order (the filter kernel's rows)
 };
 void launch_prepare_landmarks_slots(const PrepSlot* prep, int n, int L, cudaStream_t s);
 int check_pinhole(const okc_pinhole* cam);   // OKC_OK or OKC_ERR_INVALID (with the error string set)

@@ -644,7 +644,16 @@ __global__ void pack_pool_slots_kernel(const PrepSlot* __restrict__ prep) {
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
   pack_pool_body(p.a, t, p.row_offset, p.pool, p.owner, p.e_W, p.r_W, p.filled, p.row_obs);
   const int l = t / 3, n = t - 3 * l;
-  if (l < p.a.L && n < p.a.rows[l] && !p.a.is3d[l]) p.u_rows[p.u_offset[l] + n] = p.row_offset[l] + n;
+  if (l < p.a.L && n < p.a.rows[l] && !p.a.is3d[l]) {
+    const int row = p.row_offset[l] + n, pos = p.u_offset[l] + n;
+    p.u_rows[pos] = row;
+    // (this thread wrote pool row `row` just above)
+    const uint4* src = reinterpret_cast<const uint4*>(p.pool) + (size_t)row * 3;
+    uint4* dst = reinterpret_cast<uint4*>(p.u_desc) + (size_t)pos * 3;
+    dst[0] = src[0];
+    dst[1] = src[1];
+    dst[2] = src[2];
+  }
 }
 
 void launch_prepare_landmarks_slots(const PrepSlot* prep, int n, int L, cudaStream_t s) {

@@ -1236,7 +1236,11 @@ __global__ void __launch_bounds__(128) uninit_filter_kernel(const UninitJob* __r
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int nk = job.nk_dev ? min(*job.nk_dev, job.nk) : job.nk;
   const int nm = uninit_rows(job);
-  const UninitRowOf rowOf{job.row_list, job.is3d, job.owner};
+  // rows: the compact copy of the listed rows' descriptors when there is one (sweep position = list position; the
+  // resolve kernel maps it back through row_list), else the pool through the list / the is3d test
+  const bool compact = job.row_list && job.row_desc;
+  const UninitRowOf rowOf{compact ? nullptr : job.row_list, compact ? nullptr : job.is3d, job.owner};
+  const uint8_t* __restrict__ rowDesc = compact ? job.row_desc : job.map;
   const int thr = (int)ceil(job.a.hammingThreshold);
   // work items of the job: (chunk of 32 keypoints) x (chunk of kFilterRows rows), dealt round-robin to the job's CTAs
   const int kChunks = (nk + 31) / 32, items = kChunks * ((nm + kFilterRows - 1) / kFilterRows);
@@ -1262,7 +1266,7 @@ __global__ void __launch_bounds__(128) uninit_filter_kernel(const UninitJob* __r
         out[j] = s_list[g0 + min(j, nq - 1)];
         load_desc(job.queries, out[j], q[j]);
       }
-      filter_sweep(job.queries, job.map, rowOf, lo, hi, q, nq, out, thr, job.cand, job.cand_count, s_queue[warp]);
+      filter_sweep(job.queries, rowDesc, rowOf, lo, hi, q, nq, out, thr, job.cand, job.cand_count, s_queue[warp]);
     }
   }
 }
@@ -1295,6 +1299,7 @@ __global__ void __launch_bounds__(128) match_uninitialised_kernel(const UninitJo
     const double* __restrict__ rc = job.pose_slot ? job.pose_slot->r_WC : a.r_WC;
     const V3 rC = v3(rc[0], rc[1], rc[2]);
     const int prev = job.previousOwner ? job.previousOwner[k] : -1;
+    const bool compact = job.row_list && job.row_desc;   // candidates are list positions (uninit_filter_kernel)
     auto visit = [&](int m, double dc) {   // the body of the reference's loop for a row with dist < threshold
       if (!(dc < best)) return;
       const int oc = owner[m];
@@ -1333,7 +1338,8 @@ __global__ void __launch_bounds__(128) match_uninitialised_kernel(const UninitJo
       unsigned last = 0;
       for (int i = 0; i < cnt; ++i) {
         last = next_candidate(list, cnt, last, i == 0);
-        visit((int)(last >> kCandRowShift), (double)(last & ((1u << kCandRowShift) - 1u)));
+        const int pos = (int)(last >> kCandRowShift);
+        visit(compact ? job.row_list[pos] : pos, (double)(last & ((1u << kCandRowShift) - 1u)));
       }
     } else {                      // the list overflowed (or no filter ran): every row, as the reference does
       const int nm = uninit_rows(job);
