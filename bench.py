@@ -430,13 +430,14 @@ class GpuConfig:
             self.gather.step(self.batches.index(b), k0)
 
     def launches_per_batch(self):
+        """Kernels of this library launched per batch (memsets and copies not counted)."""
         n = 6                                        # harris_nms, order, select, sub-pixel, border_filter, describe
         n += 1                                       # back-projections
         if self.conf["landmarks"]:
-            n += 4 + 3 + 1                           # prepare (4), bin + match + stats, uninitialised
-        n += 1 if self.pairs else 0
-        n += 2 if self.jobs else 0                   # unmatched lists, matchMotionStereo
-        n += 2 if self.gather is not None else 0     # pack views, cross-camera matchStereo (+ one NCCL all-gather)
+            n += 4 + 3 + 2                           # prepare (4), bin + match + stats, uninitialised: filter + resolve
+        n += 2 if self.pairs else 0                  # matchStereo: filter + resolve
+        n += 3 if self.jobs else 0                   # unmatched lists, matchMotionStereo: filter + resolve
+        n += 3 if self.gather is not None else 0     # pack views, cross-camera matchStereo (+ one NCCL all-gather)
         return n
 
     def read(self, b):
