@@ -29,6 +29,12 @@ int okc_debug_set_match_binned(int on);
  * the last okc_batch_finish. */
 int okc_debug_batch_counter(okc_batch* batch, int slot, int which, int* value);
 
+/* How many cudaMalloc / cudaMallocHost calls (allocations) and cudaFree / cudaFreeHost calls (releases) the library
+ * has made in this process so far; every such call of the library is counted. The per-frame entry points of a batch
+ * (okc_batch_enqueue*, okc_batch_set_poses, okc_batch_match_*_enqueue, okc_batch_finish, okc_batch_view_results)
+ * leave both numbers unchanged once the batch has seen its largest inputs: tests/test_gpu_pipeline.py checks that. */
+int okc_debug_alloc_counts(uint64_t* allocations, uint64_t* releases);
+
 /* The reference's std::sort order of `n` PointWithScore-like scores (raster order in), for the tie-order tests. */
 int okc_debug_std_sort(okc_camera* cam, const int32_t* scores, int n, uint32_t* order);
 

@@ -174,6 +174,7 @@ def lib():
         L.okc_project_landmarks.argtypes = [vp, vp, vp, vp, i, C.c_double, vp, vp, vp]
         L.okc_debug_set_match_binned.argtypes = [i]
         L.okc_debug_batch_counter.argtypes = [vp, i, i, C.POINTER(i)]
+        L.okc_debug_alloc_counts.argtypes = [C.POINTER(u64), C.POINTER(u64)]
         L.okc_debug_std_sort.argtypes = [vp, vp, i, vp]
         L.okc_match_batched.argtypes = [vp, vp, i, vp, i64, u32, u64, vp]
         L.okc_descriptor_set_create.argtypes = [vp, vp, i64, C.POINTER(vp)]

@@ -79,7 +79,10 @@ int launch_hamming_best(const void* queries, int nq, const void* map, long long 
                         unsigned long long noMatch = ~0ull);
 }  // namespace okc
 
-namespace okc { Knobs g_knobs; }
+namespace okc {
+Knobs g_knobs;
+std::atomic<unsigned long long> g_alloc_calls{0}, g_free_calls{0};
+}
 
 extern "C" {
 

@@ -300,6 +300,35 @@ extern Knobs g_knobs;
 
 }  // namespace okc
 
+// Every allocation and release the library makes goes through these wrappers (the macros below rewrite the call
+// sites), so that a test can show that the per-frame entry points allocate nothing once a batch is warm:
+// okc_debug_alloc_counts (include/okvis_cuda_debug.h) reads the counters.
+namespace okc {
+extern std::atomic<unsigned long long> g_alloc_calls, g_free_calls;
+template <typename T>
+inline cudaError_t counted_malloc(T** p, size_t n) {
+  g_alloc_calls.fetch_add(1, std::memory_order_relaxed);
+  return ::cudaMalloc(reinterpret_cast<void**>(p), n);
+}
+template <typename T>
+inline cudaError_t counted_malloc_host(T** p, size_t n) {
+  g_alloc_calls.fetch_add(1, std::memory_order_relaxed);
+  return ::cudaMallocHost(reinterpret_cast<void**>(p), n);
+}
+inline cudaError_t counted_free(void* p) {
+  g_free_calls.fetch_add(1, std::memory_order_relaxed);
+  return ::cudaFree(p);
+}
+inline cudaError_t counted_free_host(void* p) {
+  g_free_calls.fetch_add(1, std::memory_order_relaxed);
+  return ::cudaFreeHost(p);
+}
+}  // namespace okc
+#define cudaMalloc(p, n) okc::counted_malloc((p), (n))
+#define cudaMallocHost(p, n) okc::counted_malloc_host((p), (n))
+#define cudaFree(p) okc::counted_free((p))
+#define cudaFreeHost(p) okc::counted_free_host((p))
+
 #define OKC_CUDA_TRY(expr)                                                                  \
   do {                                                                                      \
     cudaError_t _e = (expr);                                                                \

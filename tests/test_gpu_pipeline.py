@@ -349,3 +349,76 @@ def test_large_batch_equals_small_batches(mod, ctx, syn):
     pool.close()
     for cam in cams:
         cam.close()
+
+
+def test_per_frame_calls_allocate_nothing_once_warm(mod, ctx, syn):
+    """No cudaMalloc / cudaMallocHost / cudaFree on the per-frame path: the library counts every allocation and release
+    it makes (okc_debug_alloc_counts); after two warm-up frames with every stage, six more frames - new images, poses,
+    pool update, landmark / stereo / motion matchers, retain into a keyframe, finish, views and the copying readers, with graph replay
+    and with plain launches, on a 2-slot and an 8-slot batch - leave both counters where they were."""
+    import ctypes as C
+    cfg, model, cams, W, H = _rig(mod, syn, ctx, "euroc", 2, 768)
+    n_frames = 10
+    imgs = syn.rig_sequence(n_frames, 2, W, H, seed=43, step=STEP, disparity=DISP, dense=True)
+    r_all = syn.rig_poses(n_frames, 2, model.fu, model.fv, STEP, DISP, Z0)
+    det = (cfg["radius"], 0, cfg["abs_threshold"], cfg["max_kpt"])
+    f_mean = 0.5 * (model.fu + model.fv)
+
+    def counts():
+        a, r = C.c_uint64(), C.c_uint64()
+        assert mod.lib().okc_debug_alloc_counts(C.byref(a), C.byref(r)) == 0
+        return a.value, r.value
+
+    small = mod.Batch(ctx, cams)
+    big = mod.Batch(ctx, [cams[s % 2] for s in range(8)])
+    kf, kf2 = mod.Keyframe(ctx, 2, 768), mod.Keyframe(ctx, 2, 768)
+    small.enqueue([imgs[c, 0] for c in range(2)], *det, [(0.0, 1.0, 0.0)] * 2)
+    small.set_poses(_poses(mod, r_all[0]))
+    small.retain([0, 1], kf)
+    small.finish()
+    views = []
+    for c in range(2):
+        kp, desc = small.slot_frame(c)
+        e_C, valid, _ = small.slot_back_projections(c, len(kp))
+        views.append(dict(kp=kp, desc=desc, e_C=e_C, valid=valid, r_WC=r_all[0, c]))
+        kf.set_view(c, np.eye(3), r_all[0, c], f_mean, (np.arange(len(kp)) % 5 != 0).astype(np.uint8))
+    world = syn.plane_landmarks(views, Z0, model.fu, 2000, seed=5)
+    pool = mod.LandmarkPool(ctx, *world)
+    assert counts()[0] > 20                                    # (set-up does allocate, and is counted)
+
+    def frame(batch, fs, first):
+        n = len(fs)
+        pool.update(hp_W=world[1], quality=world[2])
+        batch.set_poses(np.concatenate([_poses(mod, r_all[f]) for f in fs]))
+        batch.enqueue([imgs[c, f] for f in fs for c in range(2)], *det, [(0.05, 0.99, 0.1)] * (2 * n))
+        batch.match_landmarks_enqueue(pool, 60.0, cfg["slices"], mod.STAGE_UNINITIALISED)
+        batch.match_stereo_enqueue([(2 * i, 2 * i + 1) for i in range(n)], 60.0)
+        batch.match_motion_enqueue([(kf, c, 2 * i + c) for i in range(n) for c in range(2)], 60.0, only_unmatched=True)
+        batch.retain([0, 1], kf2)
+        batch.finish()
+        _check_view(batch, [(2 * i, 2 * i + 1) for i in range(n)], 2 * n)
+        nk = 0
+        for s in range(2 * n):
+            kp, _ = batch.slot_frame(s)
+            batch.slot_matches(s, len(kp)), batch.slot_uninitialised(s, len(kp)), batch.slot_back_projections(s, len(kp))
+            nk += len(kp)
+        batch.pair_stereo(0, len(batch.slot_frame(0)[0])), batch.job_motion(0), batch.transfer_bytes()
+        assert nk > 300 * 2 * n
+        return nk
+
+    for graph in (True, False):
+        small.set_graph(graph), big.set_graph(graph)
+        for f in (1, 2):                                        # warm: buffers grow to their sizes, graphs are captured
+            frame(small, [f], True)
+            frame(big, [f, f + 1, f + 2, f + 3], True)
+        before = counts()
+        for f in (3, 4, 5, 6):
+            frame(small, [f], False)
+        for f in (3, 4):
+            frame(big, [f, f + 1, f + 2, f + 3], False)
+        assert counts() == before, (graph, before, counts())
+    before = counts()
+    for x in (big, small, kf, kf2, pool, *cams):
+        x.close()
+    after = counts()
+    assert after[0] == before[0] and after[1] > before[1] + 20     # (releases are counted too)
