@@ -337,7 +337,7 @@ __device__ __forceinline__ void ord_swap(const OrdArrays& A, int i, int j) {
 
 // std::__partial_sort(first, last, last) = make_heap + sort_heap with comp(x, y) = x.score > y.score
 // (bits/stl_heap.h: __adjust_heap / __push_heap). Sequential; only reached on adversarial inputs.
-__device__ void ord_heap_sort(const OrdArrays& A, int f, int l) {
+__device__ __noinline__ void ord_heap_sort(const OrdArrays& A, int f, int l) {
   const int n = l - f;
   if (n < 2) return;
   auto adjust = [&](int hole, int length, int vs, uint32_t vr) {
@@ -380,7 +380,7 @@ __device__ void ord_heap_sort(const OrdArrays& A, int f, int l) {
 }
 
 // std::__unguarded_partition_pivot on [f, l) by one warp; returns the cut.
-__device__ int ord_warp_partition(const OrdArrays& A, int f, int l, int lane) {
+__device__ __forceinline__ int ord_warp_partition(const OrdArrays& A, int f, int l, int lane) {
   if (lane == 0) {  // __move_median_to_first(first, first + 1, mid, last - 1)
     const int a = f + 1, b = f + (l - f) / 2, c = l - 1;
     const int sa = A.sc[a], sb = A.sc[b], s_c = A.sc[c];
@@ -434,13 +434,85 @@ __device__ int ord_warp_partition(const OrdArrays& A, int f, int l, int lane) {
   return cut;
 }
 
+// The same for a range of at most 32 elements (60 % of all partitions of a tree): one element per lane, in registers;
+// median, pivot and the exchange of the swapped pairs by shuffles; only the two stop lists go through shared memory.
+// A third of the instructions of the general form - the partitions are bound by the length of their dependent
+// instruction chain (narrow levels of the tree) or by instruction issue (wide levels).
+__device__ __forceinline__ int ord_warp_partition_small(const OrdArrays& A, int f, int l, int lane) {
+  const int len = l - f;   // 17 .. 32
+  const bool in = lane < len;
+  int sc = in ? A.sc[f + lane] : 0;
+  uint32_t ra = in ? A.ra[f + lane] : 0u;
+  const int mid = len >> 1;
+  int pick;
+  {  // __move_median_to_first(first, first + 1, mid, last - 1)
+    const int sa = __shfl_sync(0xffffffffu, sc, 1), sb = __shfl_sync(0xffffffffu, sc, mid),
+              s_c = __shfl_sync(0xffffffffu, sc, len - 1);
+    if (sa > sb) pick = (sb > s_c) ? mid : ((sa > s_c) ? len - 1 : 1);
+    else pick = (sa > s_c) ? 1 : ((sb > s_c) ? len - 1 : mid);
+  }
+  const int s0 = __shfl_sync(0xffffffffu, sc, 0), pv = __shfl_sync(0xffffffffu, sc, pick);
+  const uint32_t r0 = __shfl_sync(0xffffffffu, ra, 0), rp = __shfl_sync(0xffffffffu, ra, pick);
+  if (lane == 0) {
+    sc = pv;
+    ra = rp;
+  } else if (lane == pick) {
+    sc = s0;
+    ra = r0;
+  }
+  const bool isL = in && lane >= 1 && !(sc > pv);   // "while (comp(*first, pivot)) ++first" stops here
+  const bool isR = in && !(pv > sc);                // "while (comp(pivot, *last)) --last" stops here (lane 0 = sentinel)
+  const unsigned bL = __ballot_sync(0xffffffffu, isL), bR = __ballot_sync(0xffffffffu, isR);
+  const int nL = __popc(bL), nR = __popc(bR);
+  const unsigned lt = (1u << lane) - 1u;
+  const int rL = __popc(bL & lt);                       // rank among the left stops, ascending
+  const int rR = __popc(bR & ~(lt | (1u << lane)));     // rank among the right stops, descending
+  if (isL) A.lp[f + 1 + rL] = lane;
+  if (isR) A.rp[f + rR] = lane;
+  __syncwarp();
+  // pair j = (j-th left stop, j-th right stop) is swapped while L_j < R_j; an element equal to the pivot is a stop of
+  // both kinds but can belong to one swapped pair only
+  int partner = lane;
+  bool leftOfPair = false;
+  if (isL && rL < nR) {
+    const int p = A.rp[f + rL];
+    if (lane < p) {
+      partner = p;
+      leftOfPair = true;
+    }
+  }
+  if (!leftOfPair && isR && rR < nL) {
+    const int p = A.lp[f + 1 + rR];
+    if (p < lane) partner = p;
+  }
+  const int t = __popc(__ballot_sync(0xffffffffu, leftOfPair));
+  const int nsc = __shfl_sync(0xffffffffu, sc, partner);
+  const uint32_t nra = __shfl_sync(0xffffffffu, ra, partner);
+  if (in) {
+    A.sc[f + lane] = nsc;
+    A.ra[f + lane] = nra;
+  }
+  int cut;
+  if (t == 0) {
+    cut = nL > 0 ? __ffs(bL) - 1 : len;
+  } else {
+    cut = A.rp[f + t - 1];
+    if (t < nL) {
+      const int nextL = A.lp[f + 1 + t];
+      if (nextL < cut) cut = nextL;
+    }
+  }
+  __syncwarp();
+  return f + cut;
+}
+
 // The same partition by the whole CTA, for the long ranges at the top of the recursion (one warp walking 7 000
 // elements twice was most of the kernel): the warps classify contiguous chunks, a scan over the warps places the
 // stop lists, and because the left stops ascend while the right stops descend, "L_i < R_i" holds for a prefix of the
 // pairs, so the number of swaps is a plain count. Called by every thread; returns the cut to every thread.
 struct OrdBlockScratch { int cntL[32], cntR[32], offL[32], offR[32], nL, nR, t; };
 
-__device__ int ord_block_partition(const OrdArrays& A, int f, int l, OrdBlockScratch& S) {
+__device__ __forceinline__ int ord_block_partition(const OrdArrays& A, int f, int l, OrdBlockScratch& S) {
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   if (tid == 0) {  // __move_median_to_first(first, first + 1, mid, last - 1)
     const int a = f + 1, b = f + (l - f) / 2, c = l - 1;
@@ -522,7 +594,7 @@ __device__ int ord_block_partition(const OrdArrays& A, int f, int l, OrdBlockScr
       if (nextL < cut) cut = nextL;
     }
   }
-  __syncthreads();   // (the stop lists are read above, the swaps below move the elements they point at)
+  // (no barrier: the swaps move elements of A.sc / A.ra, the stop lists read above hold positions)
   for (int i = tid; i < t; i += kOrdThreads) ord_swap(A, A.lp[f + 1 + i], A.rp[f + i]);
   __syncthreads();
   return cut;
@@ -552,7 +624,7 @@ order_candidates_kernel(const Slot* __restrict__ slots, int W, int H, bool dense
   __shared__ int s_bigcount[2];   // bit i: a partition cut (or the start) lies at position i
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 #ifdef OKC_ORDER_TRACE
-  long long tr[6] = {}, t0 = clock64();
+  long long tr[10] = {}, t0 = clock64();
 #define ORD_T(i) do { __syncthreads(); if (tid == 0) tr[i] += clock64() - t0; t0 = clock64(); } while (0)
 #else
 #define ORD_T(i) do { } while (0)
@@ -564,8 +636,29 @@ order_candidates_kernel(const Slot* __restrict__ slots, int W, int H, bool dense
   // every warp owns a contiguous block of bitmap words and reads it 32 words at a time (coalesced)
   const int chunk = (((words + 31) / 32 + 31) / 32) * 32;   // words per warp, a multiple of 32
   const int w0 = warp * chunk, w1 = min(words, w0 + chunk);
+  // Usual image sizes (<= 16 384 words = 491 520 pixels): a thread keeps 16 consecutive words (64 bytes, 4 independent
+  // 16-byte loads) in registers for both passes, and its candidates are consecutive in raster order - one scan per
+  // warp instead of one per 32 words (the per-word-row scans and divisions made this phase instruction-issue bound:
+  // 15 000 cycles for 13 440 words). Larger images: the strided two-pass form.
+  constexpr int kLaneWords = 16;
+  const bool fast = words <= kOrdThreads * kLaneWords && (reinterpret_cast<uintptr_t>(bitmap) & 15) == 0;
+  unsigned wreg[kLaneWords];
   int mine = 0;
-  for (int w = w0 + lane; w < w1; w += 32) mine += __popc(bitmap[w]);
+  if (fast) {
+#pragma unroll
+    for (int u = 0; u < kLaneWords / 4; ++u) {
+      const int w = tid * kLaneWords + 4 * u;   // (words is a multiple of kStripWords = 4)
+      const uint4 v = w < words ? __ldg(reinterpret_cast<const uint4*>(bitmap + w)) : make_uint4(0, 0, 0, 0);
+      wreg[4 * u] = v.x;
+      wreg[4 * u + 1] = v.y;
+      wreg[4 * u + 2] = v.z;
+      wreg[4 * u + 3] = v.w;
+    }
+#pragma unroll
+    for (int j = 0; j < kLaneWords; ++j) mine += __popc(wreg[j]);
+  } else {
+    for (int w = w0 + lane; w < w1; w += 32) mine += __popc(bitmap[w]);
+  }
   int incl = mine;
   for (int d = 1; d < 32; d <<= 1) {
     const int v = __shfl_up_sync(0xffffffffu, incl, d);
@@ -584,6 +677,7 @@ order_candidates_kernel(const Slot* __restrict__ slots, int W, int H, bool dense
   }
   __syncthreads();
   int total = s_n;
+  ORD_T(6);
   if (total > kCandCap) {
     if (tid == 0) {
       counters[0] = kCandCap;
@@ -595,8 +689,12 @@ order_candidates_kernel(const Slot* __restrict__ slots, int W, int H, bool dense
   if (tid == 0) counters[0] = n;
   if (n == 0) return;
 
+  // The body is instantiated twice - arrays in shared memory (n <= kOrdSmemCap) or in the slot's global scratch - so
+  // that the shared-memory instance is compiled to LDS / STS with 32-bit addresses: through one generic pointer for
+  // both, every access of the partitions' dependent load -> compare -> store chains was a generic LD.E / ST.E.
+  auto body = [&](auto inSmemTag) {
   OrdArrays A;
-  const bool inSmem = n <= kOrdSmemCap;
+  constexpr bool inSmem = decltype(inSmemTag)::value;
   {
     uint8_t* base = inSmem ? smem : gscratch;
     const size_t cap = inSmem ? kOrdSmemCap : kCandCap;
@@ -610,7 +708,33 @@ order_candidates_kernel(const Slot* __restrict__ slots, int W, int H, bool dense
     A.rp = A.lp + cap;
   }
   for (int w = tid; w <= (n >> 5); w += kOrdThreads) s_cut[w] = w == 0 ? 1u : 0u;
-  {
+  if (fast) {
+    // (thread order = raster order: `incl` is the inclusive scan of `mine` over the warp's lanes, from the first pass)
+    int pos = s_warp[warp] + incl - mine;
+    const int wFirst = tid * kLaneWords;
+    int y = wFirst / wordsPerRow, rem = wFirst - y * wordsPerRow;
+    int segAt = 0;
+#pragma unroll
+    for (int j = 0; j < kLaneWords; ++j) {
+      unsigned bits = wreg[j];
+      // compact scores (harris_nms_kernel<.., false>): a (row, strip) segment = 4 words; a candidate's score is at its
+      // rank inside the segment. Stored first: WHERE the score is; the scores follow in one pass of independent loads
+      if ((j & (kStripWords - 1)) == 0) segAt = ((wFirst + j) / kStripWords) * kStripCols;
+      const int xb = (rem / kStripWords) * kStripCols - 4 + ((rem % kStripWords) << 5);
+      while (bits) {
+        const int b = __ffs(bits) - 1;
+        bits &= bits - 1;
+        const uint32_t raster = (uint32_t)(y * W + xb + b);
+        A.sc[pos] = denseScores ? (int)raster : segAt++;
+        A.ra[pos] = raster;
+        ++pos;
+      }
+      if (++rem == wordsPerRow) {
+        rem = 0;
+        ++y;
+      }
+    }
+  } else {
     int base = s_warp[warp];   // candidates in front of this warp's block
     for (int wb = w0; wb < w1; wb += 32) {
       const int w = wb + lane;
@@ -629,16 +753,30 @@ order_candidates_kernel(const Slot* __restrict__ slots, int W, int H, bool dense
       // (wb is a multiple of 32), a candidate's score is at its rank inside the segment
       const int excl = inc - c;
       int segRank = excl - __shfl_sync(0xffffffffu, excl, lane & ~(kStripWords - 1));
-      const int32_t* __restrict__ seg = scores + (size_t)(w / kStripWords) * kStripCols;
+      // first WHERE the score is (its index in the score buffer), then all scores in one pass of independent loads:
+      // a load per candidate inside this loop was a chain of L2 round trips (2/3 of the time of this phase)
+      int segAt = (w / kStripWords) * kStripCols + segRank;
       while (bits) {
         const int b = __ffs(bits) - 1;
         bits &= bits - 1;
         const uint32_t raster = (uint32_t)(y * W + xb + b);
-        A.sc[pos] = denseScores ? scores[raster] : seg[segRank++];
+        A.sc[pos] = denseScores ? (int)raster : segAt++;
         A.ra[pos] = raster;
         ++pos;
       }
     }
+  }
+  __syncthreads();
+  ORD_T(7);
+  for (int i0 = tid; i0 < n; i0 += 8 * kOrdThreads) {
+    int at[8], v[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) at[u] = i0 + u * kOrdThreads < n ? A.sc[i0 + u * kOrdThreads] : 0;
+#pragma unroll
+    for (int u = 0; u < 8; ++u) v[u] = __ldg(scores + at[u]);
+#pragma unroll
+    for (int u = 0; u < 8; ++u)
+      if (i0 + u * kOrdThreads < n) A.sc[i0 + u * kOrdThreads] = v[u];
   }
   if (tid == 0) {
     s_qcount[0] = s_qcount[1] = s_bigcount[0] = s_bigcount[1] = 0;
@@ -659,6 +797,11 @@ order_candidates_kernel(const Slot* __restrict__ slots, int W, int H, bool dense
       if (b - a >= kOrdCoopLen) s_big[cur ^ 1][atomicAdd(&s_bigcount[cur ^ 1], 1)] = make_int2(a, b);
       else if (b - a > 16) A.q[cur ^ 1][atomicAdd(&s_qcount[cur ^ 1], 1)] = make_int2(a, b);
     };
+#ifdef OKC_ORDER_TRACE
+    long long tl0 = clock64(), tl1 = 0;
+    int trMax = 0;
+    for (int s = 0; s < cnt; ++s) trMax = max(trMax, A.q[cur][s].y - A.q[cur][s].x);
+#endif
     for (int s = 0; s < cntBig; ++s) {   // the long ranges, by the whole CTA (uniform loop: every thread takes part)
       const int2 r = s_big[cur][s];
       if (depthLimit == 0) {
@@ -672,13 +815,17 @@ order_candidates_kernel(const Slot* __restrict__ slots, int W, int H, bool dense
         push(cut, r.y);
       }
     }
+#ifdef OKC_ORDER_TRACE
+    __syncthreads();
+    tl1 = clock64();
+#endif
     for (int s = warp; s < cnt; s += kOrdThreads / 32) {
       const int2 r = A.q[cur][s];
       if (depthLimit == 0) {
         if (lane == 0) ord_heap_sort(A, r.x, r.y);
         continue;
       }
-      const int cut = ord_warp_partition(A, r.x, r.y, lane);
+      const int cut = r.y - r.x <= 32 ? ord_warp_partition_small(A, r.x, r.y, lane) : ord_warp_partition(A, r.x, r.y, lane);
       if (lane == 0) {
         atomicOr(&s_cut[cut >> 5], 1u << (cut & 31));
         push(r.x, cut);
@@ -686,6 +833,9 @@ order_candidates_kernel(const Slot* __restrict__ slots, int W, int H, bool dense
       }
     }
     __syncthreads();
+#ifdef OKC_ORDER_TRACE
+    if (tid == 0 && n == 7517) printf("  level: %d long (%lld cycles), %d warp ranges, longest %d (%lld cycles)\n", cntBig, tl1 - tl0, cnt, trMax, clock64() - tl1);
+#endif
     if (tid == 0) s_qcount[cur] = s_bigcount[cur] = 0;
     cur ^= 1;
     --depthLimit;
@@ -735,8 +885,12 @@ order_candidates_kernel(const Slot* __restrict__ slots, int W, int H, bool dense
   for (int i = tid; i < n; i += kOrdThreads) cand[i] = cand_key(A.lp[i], (uint32_t)A.rp[i]);
 #ifdef OKC_ORDER_TRACE
   ORD_T(4);
+  if (tid == 0) printf("  gather: count %lld place %lld scores+rest %lld\n", tr[6], tr[7], tr[0]);
   if (tid == 0) printf("order trace (cycles): n %d gather %lld partition %lld segments %lld write %lld\n", n, tr[0], tr[1], tr[3], tr[4]);
 #endif
+  };
+  if (n <= kOrdSmemCap) body(std::true_type{});
+  else body(std::false_type{});
 }
 
 constexpr size_t kOrdSmemBytes = (size_t)kOrdSmemCap * 4 + 2 * (size_t)kOrdQueueSmem * 8 + (size_t)kOrdSmemCap * 12;
