@@ -1302,6 +1302,7 @@ select_keypoints_wave_kernel(const Slot* __restrict__ slots, const float* __rest
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 #ifdef OKC_SELECT_TRACE
   long long tr[12] = {}, t0 = clock64();
+  int trStages = 0;
 #endif
   int n = counters[0];
   if (n > kCandCap) n = kCandCap;
@@ -1422,6 +1423,7 @@ select_keypoints_wave_kernel(const Slot* __restrict__ slots, const float* __rest
         if (!lbReady) break;   // (no accepted points yet: nothing to pre-test or gather, a chunk is a stage)
       }
       __syncthreads();
+      WL_T(10);
       if (staged > kWlCap) {
         staged = kWlCap;
         pos = S.posNext;
@@ -1460,6 +1462,10 @@ select_keypoints_wave_kernel(const Slot* __restrict__ slots, const float* __rest
         }
       }
       __syncthreads();   // (every thread has read its staged candidate: the stage may be refilled)
+      WL_T(11);
+#ifdef OKC_SELECT_TRACE
+      if (tid == 0) ++trStages;
+#endif
       int total;
       const int p = wcount + scan(alive, total);
       if (alive) {
@@ -1691,8 +1697,8 @@ select_keypoints_wave_kernel(const Slot* __restrict__ slots, const float* __rest
   WL_T(7);
   if (tid == 0)
     printf("select trace (cycles): fill %lld csr %lld lists %lld resolve(warp0) %lld wait %lld end %lld regroup %lld "
-           "(init %lld stamp %lld) tail %lld sweeps %d windows %d\n", tr[1], tr[2], tr[3], tr[4], tr[5], tr[6], tr[0], tr[8],
-           tr[9], tr[7], sweeps, windows);
+           "(init %lld stamp %lld) tail %lld sweeps %d windows %d | stages %d: pre-test %lld gather %lld\n", tr[1], tr[2], tr[3], tr[4], tr[5], tr[6], tr[0], tr[8],
+           tr[9], tr[7], sweeps, windows, trStages, tr[10], tr[11]);
 #endif
 }
 

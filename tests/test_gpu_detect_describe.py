@@ -56,6 +56,28 @@ def test_nms_candidate_set(name, cases, mod, ctx, ref):
     cam.close()
 
 
+def test_large_image_takes_the_strided_gather(mod, ctx, ref, syn):
+    """1280 x 800: more bitmap words than order_candidates keeps in registers (16 per thread), so the candidate
+    gather runs in its strided two-pass form; candidates in std::sort order, keypoints and descriptors against the
+    compiled reference."""
+    import refbind
+    cfg, img = syn.EUROC, syn.scene_image(1280, 800, 6, rects=1200)
+    H, W = img.shape
+    cam = mod.Camera(ctx, W, H, max_keypoints=4096)
+    thr = int(cfg["abs_threshold"])
+    cand, rc = cam.debug_candidates(img, thr), ref.maxima(img, thr)
+    assert len(rc) > 1500 and cand.tobytes() == ref.std_sort(rc).tobytes()
+    rkp = ref.detect(img, cfg["radius"], 0, cfg["abs_threshold"], 2000)
+    kp, desc = cam.detect_describe(img, cfg["radius"], 0, cfg["abs_threshold"], 2000)
+    ext = refbind.RefExtractor(ref)
+    rkd, rdd = ext.describe(img, rkp)
+    ext.close()
+    assert len(rkd) > 300
+    kp_assert_close(kp, rkd, TOL)
+    assert np.array_equal(desc, rdd)
+    cam.close()
+
+
 @pytest.mark.parametrize("name", CASE_NAMES)
 def test_detect_keypoints(name, cases, mod, ctx, ref):
     cfg, img = cases[name]
