@@ -339,7 +339,7 @@ int okc_project_landmarks(okc_context* ctx, const okc_pinhole* cam, const double
 // per (frame, camera) two H/10 x W/10 masks - every keypoint / every matched keypoint drawn as a filled circle of
 // radius int(min(rows, cols) * 0.09) at cv::Point(keypoint.pt * 0.1) - and the pixel counts of their AND and OR.
 // cv::circle(..., cv::FILLED) fills, for each row dy, the columns |dx| <= floor(sqrt(r^2 - dy^2)), clipped to the
-// image (pinned against cv2 4.13 goldens, tests/golden/overlap_discs.npz). One CTA per view, masks in shared memory;
+// image (pinned against cv2 4.13 goldens, tests/golden/overlap_goldens.npz). One CTA per view, masks in shared memory;
 // the stores are idempotent (255), so overlapping circles need no ordering.
 // ----------------------------------------------------------------------------------------------
 namespace okc {
