@@ -464,6 +464,14 @@ class GpuConfig:
     # ---- timed loops ----
     def run_value(self, n_steps, n_warm, barrier, max_over_ranks):
         torch, F, D = self.torch, self.F, self.D
+        # set-up, untimed and apart from the W warm-up steps: every batch in flight runs its launch chain three times
+        # (plain launches at first sight of a configuration, graph capture at the second, first replay), so that a short
+        # run (--steps 20 --warmup 5 covers batch 0 twice and the others once) has no graph capture in its timed steps
+        for rep in range(3):
+            for j in range(D):
+                self.enqueue(self.batches[j], *self.slot_args(j * F, True), True, j * F)
+            for b in self.batches:
+                b.finish()
         for j in range(n_warm):
             self.enqueue(self.batches[j % D], *self.slot_args(j * F, True), True, j * F)
         work = [self.slot_args((n_warm + j) * F, True) for j in range(n_steps)]
@@ -516,7 +524,7 @@ class GpuConfig:
 
     def time_e2e(self, n_steps, n_warm, barrier, max_over_ranks, pageable=False):
         F = self.F
-        self.run_e2e(0, max(self.D, n_warm) * F, None, pageable)
+        self.run_e2e(0, max(3 * self.D, n_warm) * F, None, pageable)   # (3 uses per batch: plain, capture, replay)
         runs = []
         for _ in range(E2E_REPEATS):
             barrier()
