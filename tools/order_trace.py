@@ -1,3 +1,7 @@
+"""GPU-box tool: in-kernel cycle counts of order_candidates / the selection kernel for ONE image of three cases.
+The kernels print them only in a trace build of the library (never the shipped one):
+  cd okvis2-x_b200/csrc && nvcc <NVCC_FLAGS of __graft_entry__.py> -DOKC_ORDER_TRACE [-DOKC_SELECT_TRACE] -o ../libokvis_cuda.so <SOURCES>
+then `gpurun -- python tools/order_trace.py`, then rebuild without the flags (`__graft_entry__.build(force=True)`)."""
 import os, sys, importlib
 sys.path.insert(0, "/root/repo")
 import __graft_entry__ as ge
